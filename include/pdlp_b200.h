@@ -1,0 +1,159 @@
+/* C ABI of the B200-native PDLP solver: the drop-in boundary for
+ *   SolverResult PrimalDualHybridGradient(QuadraticProgram, PrimalDualHybridGradientParams,
+ *                                         [initial_solution], interrupt_solve, callback)
+ * of /root/reference/ortools/pdlp/primal_dual_hybrid_gradient.h:140-156.
+ *
+ * The reference has no FFI layer of its own for this path (it is a C++ free function
+ * plus two protobuf schemas; its Python binding is pybind11 over that function,
+ * ortools/pdlp/python/pdlp.cc:143-150).  These entry points are what such a binding
+ * would call: plain pointers and sizes, serialized protobuf messages for the two
+ * schema types (wire-compatible with ortools/pdlp/solvers.proto and solve_log.proto).
+ * INTEGRATION.md shows the reference-side stub.
+ *
+ * Error convention: solver-level failures (invalid problem / parameters / initial
+ * solution) are a NORMAL return with termination_reason set in the SolveLog, exactly
+ * as the reference does (primal_dual_hybrid_gradient.cc:717-725).  The return status
+ * is non-zero only for ABI-level failures (null pointers, CUDA errors, out of memory).
+ * There is no CPU fallback: without a usable CUDA device every solve returns
+ * PDLP_B200_CUDA_ERROR.
+ */
+#ifndef PDLP_B200_H_
+#define PDLP_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  PDLP_B200_OK = 0,
+  PDLP_B200_BAD_ARGUMENT = 1, /* null pointer / negative size / unparsable params bytes */
+  PDLP_B200_CUDA_ERROR = 2,   /* no device, launch failure, out of device memory */
+  PDLP_B200_INTERNAL_ERROR = 3
+} pdlp_b200_status;
+
+/* The QuadraticProgram of ortools/pdlp/quadratic_program.h:53-143, by borrowed
+ * pointers.  The constraint matrix is compressed sparse column (the layout of a
+ * compressed Eigen::SparseMatrix<double, ColMajor, int64_t>: outerIndexPtr /
+ * innerIndexPtr / valuePtr).  Infinite bounds are +-INFINITY.  Nothing is modified. */
+typedef struct {
+  int64_t num_variables;    /* n */
+  int64_t num_constraints;  /* m */
+  int64_t num_nonzeros;
+  const int64_t* col_ptr;   /* n + 1 */
+  const int64_t* row_idx;   /* num_nonzeros */
+  const double* values;     /* num_nonzeros */
+  const double* objective_vector;           /* n */
+  const double* objective_matrix_diagonal;  /* n, or NULL for a linear program */
+  const double* variable_lower_bounds;      /* n */
+  const double* variable_upper_bounds;      /* n */
+  const double* constraint_lower_bounds;    /* m */
+  const double* constraint_upper_bounds;    /* m */
+  double objective_offset;
+  double objective_scaling_factor;          /* -1 encodes maximisation */
+  const char* problem_name;                 /* NULL if unnamed */
+} pdlp_b200_problem;
+
+/* IterationCallbackInfo (primal_dual_hybrid_gradient.h:62-93): iteration_type is the
+ * IterationType enum value; iteration_stats is a serialized IterationStats message;
+ * bound_norms = {l2_norm_primal_linear_objective, l2_norm_constraint_bounds,
+ * l_inf_norm_primal_linear_objective, l_inf_norm_constraint_bounds}.  Runs synchronously
+ * on the calling thread at every termination check and once at exit; it may set the
+ * interrupt flag. */
+typedef void (*pdlp_b200_callback)(int iteration_type, const uint8_t* iteration_stats, size_t iteration_stats_len,
+                                   const double* bound_norms /*4*/, void* user);
+
+typedef struct {
+  long long kernel_launches;
+  long long trial_steps;        /* accepted + rejected PDHG steps */
+  double setup_seconds;         /* upload + transpose + stats + rescaling */
+  double loop_seconds;          /* host wall time of the iteration loop */
+  double device_loop_seconds;   /* CUDA-event time of the iteration loop */
+} pdlp_b200_counters;
+
+/* Solves `problem`.
+ *   params / params_len   serialized PrimalDualHybridGradientParams (NULL / 0 = defaults)
+ *   initial_primal/dual   both NULL (start at zero) or both given (sizes n and m)
+ *   interrupt             NULL, or a flag polled during the solve (non-zero = stop)
+ *   device                CUDA device ordinal, or -1 for the current device
+ *   primal/dual/reduced   caller-allocated outputs of sizes n, m, n; written only when
+ *                         the result carries a solution (*has_solution = 1)
+ *   solve_log             callee-allocated serialized SolveLog; free with pdlp_b200_free
+ *   counters              optional (NULL allowed)
+ */
+pdlp_b200_status pdlp_b200_solve(const pdlp_b200_problem* problem, const uint8_t* params, size_t params_len,
+                                 const double* initial_primal_solution, const double* initial_dual_solution,
+                                 const volatile int* interrupt, pdlp_b200_callback callback, void* callback_user, int device,
+                                 double* primal_solution, double* dual_solution, double* reduced_costs, int* has_solution,
+                                 uint8_t** solve_log, size_t* solve_log_len, pdlp_b200_counters* counters);
+
+/* ValidatePrimalDualHybridGradientParams (solvers_proto_validation.cc:171-298): returns
+ * PDLP_B200_OK and *message = NULL when valid, else *message = malloc'ed status text. */
+pdlp_b200_status pdlp_b200_validate_params(const uint8_t* params, size_t params_len, char** message);
+
+/* Serialized PrimalDualHybridGradientParams holding every schema default. */
+pdlp_b200_status pdlp_b200_default_params(uint8_t** params, size_t* params_len);
+
+/* Line-oriented description of the two schemas (message / field / number / type /
+ * default), from which language bindings build their message classes. */
+pdlp_b200_status pdlp_b200_describe_schema(char** text);
+
+/* Text of the last ABI-level error on this thread (valid until the next call). */
+const char* pdlp_b200_last_error(void);
+
+void pdlp_b200_free(void* p);
+
+/* ---- kernel-level entry points (unit parity tests, ncu captures) ----
+ * A handle owns the device copy of a problem (both matrix orientations). */
+typedef struct pdlp_b200_device_problem pdlp_b200_device_problem;
+
+pdlp_b200_status pdlp_b200_problem_create(const pdlp_b200_problem* problem, int device, pdlp_b200_device_problem** out);
+void pdlp_b200_problem_destroy(pdlp_b200_device_problem* h);
+
+/* TransposedMatrixVectorProduct (sharder.cc:163-176): which = 0 -> out[n] = K^T v[m],
+ * which = 1 -> out[m] = K v[n].  Host in / host out; `repeat` launches are timed on
+ * the device, *seconds_per_launch (optional) receives the CUDA-event average. */
+pdlp_b200_status pdlp_b200_matvec(pdlp_b200_device_problem* h, int which, const double* v, double* out, int repeat, double* seconds_per_launch);
+
+/* ScaledColLInfNorm / ScaledColL2Norm (sharder.cc:291-335) of diag(row_scale) K
+ * diag(col_scale): which = 0 -> column norms (n), 1 -> row norms (m); l2 = 0 / 1. */
+pdlp_b200_status pdlp_b200_scaled_norms(pdlp_b200_device_problem* h, int which, int l2, const double* row_scale, const double* col_scale, double* out);
+
+/* ComputeStats (sharded_optimization_utils.cc:270-343): serialized QuadraticProgramStats. */
+pdlp_b200_status pdlp_b200_stats(pdlp_b200_device_problem* h, uint8_t** stats, size_t* stats_len);
+
+/* ApplyRescaling (sharded_optimization_utils.cc:423-444) in place on the handle;
+ * outputs the cumulative scaling vectors (row: m, col: n) and, optionally, the scaled
+ * matrix values in CSC order (nnz). */
+pdlp_b200_status pdlp_b200_rescale(pdlp_b200_device_problem* h, int l_inf_ruiz_iterations, int l2_norm_rescaling, double* row_scale, double* col_scale,
+                                   double* scaled_values);
+
+/* ComputeConvergenceInformation + ComputeInfeasibilityInformation
+ * (iteration_stats.cc:349-518) at (x, y) of the handle's current (possibly rescaled)
+ * problem: serialized IterationStats with one entry of each. */
+pdlp_b200_status pdlp_b200_kkt_stats(pdlp_b200_device_problem* h, const uint8_t* params, size_t params_len, const double* x, const double* y,
+                                     uint8_t** stats, size_t* stats_len);
+
+/* ReducedCosts (iteration_stats.cc:533-565). */
+pdlp_b200_status pdlp_b200_reduced_costs(pdlp_b200_device_problem* h, const uint8_t* params, size_t params_len, const double* x, const double* y,
+                                         int use_zero_primal_objective, double* reduced_costs);
+
+/* ComputeLocalizedLagrangianBounds, Euclidean norm (trust_region.cc:886-1016):
+ * out = {lagrangian_value, lower_bound, upper_bound, radius}. */
+pdlp_b200_status pdlp_b200_localized_bounds(pdlp_b200_device_problem* h, const double* x, const double* y, double primal_weight, double radius,
+                                            int use_diagonal_qp_trust_region_solver, double diagonal_qp_trust_region_solver_tolerance, double* out);
+
+/* `steps` trial steps of the adaptive rule from (x, y) with the given step size and
+ * primal weight, nothing else (no restarts, no checks): the timed unit of the
+ * benchmark.  Outputs the iterate after the last accepted step and the step state:
+ * state_out = {step_size, iterations_completed, num_rejected_steps, last_movement,
+ * last_nonlinearity}; *seconds (optional) = CUDA-event time of the whole batch. */
+pdlp_b200_status pdlp_b200_trial_steps(pdlp_b200_device_problem* h, int steps, double step_size, double primal_weight, double* x /*n, in-out*/,
+                                       double* y /*m, in-out*/, double* state_out /*5*/, double* seconds, long long* launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PDLP_B200_H_ */

@@ -1,0 +1,533 @@
+// The C++ entry points (primal_dual_hybrid_gradient.h) and the C ABI (include/pdlp_b200.h).
+//   follows ortools/pdlp/primal_dual_hybrid_gradient.cc:2778-2831 (entry checks),
+//           ortools/pdlp/quadratic_program.cc:37-90 (dimension / bound validation).
+#include <cstdlib>
+#include <cstring>
+
+#include "pdlp_b200.h"
+#include "pdlp_driver.h"
+
+namespace pdlp_b200 {
+
+std::string ValidateQuadraticProgramDimensions(const QuadraticProgram& qp) {  // quadratic_program.cc:37-80
+  const int64_t var_lb_size = qp.variable_lower_bounds.size();
+  const int64_t con_lb_size = qp.constraint_lower_bounds.size();
+  auto S = [](int64_t v) { return std::to_string(v); };
+  if (var_lb_size != static_cast<int64_t>(qp.variable_upper_bounds.size()))
+    return "Inconsistent dimensions: variable lower bound vector has size " + S(var_lb_size) + " while variable upper bound vector has size " +
+           S(qp.variable_upper_bounds.size());
+  if (var_lb_size != static_cast<int64_t>(qp.objective_vector.size()))
+    return "Inconsistent dimensions: variable lower bound vector has size " + S(var_lb_size) + " while objective vector has size " +
+           S(qp.objective_vector.size());
+  if (var_lb_size != qp.constraint_matrix.cols)
+    return "Inconsistent dimensions: variable lower bound vector has size " + S(var_lb_size) + " while constraint matrix has " +
+           S(qp.constraint_matrix.cols) + " columns";
+  if (qp.objective_matrix.has_value() && var_lb_size != static_cast<int64_t>(qp.objective_matrix->size()))
+    return "Inconsistent dimensions: variable lower bound vector has size " + S(var_lb_size) + " while objective matrix has " +
+           S(qp.objective_matrix->size()) + " rows";
+  if (con_lb_size != static_cast<int64_t>(qp.constraint_upper_bounds.size()))
+    return "Inconsistent dimensions: constraint lower bound vector has size " + S(con_lb_size) + " while constraint upper bound vector has size " +
+           S(qp.constraint_upper_bounds.size());
+  if (con_lb_size != qp.constraint_matrix.rows)
+    return "Inconsistent dimensions: constraint lower bound vector has size " + S(con_lb_size) + " while constraint matrix has " +
+           S(qp.constraint_matrix.rows) + " rows ";
+  return "";
+}
+
+namespace {
+
+bool BoundsAreValid(const double* lb, const double* ub, int64_t count) {
+  for (int64_t i = 0; i < count; ++i) if (!(lb[i] <= ub[i])) return false;
+  return true;
+}
+
+// The checks of pdhg.cc:2787-2826 that need the data (not the dimensions), then the solve.
+SolverResult SolveView(const QpView& qp, const PrimalDualHybridGradientParams& params, const double* x0, const double* y0,
+                       const InterruptFlag* interrupt, IterationCallback callback) {
+  if (!BoundsAreValid(qp.clb, qp.cub, qp.m) || !BoundsAreValid(qp.vlb, qp.vub, qp.n))
+    return ErrorSolverResult(TERMINATION_REASON_INVALID_PROBLEM, "The input problem has inconsistent bounds.");
+  if (qp.objective_scaling_factor == 0) return ErrorSolverResult(TERMINATION_REASON_INVALID_PROBLEM, "The objective scaling factor cannot be zero.");
+  if (qp.q != nullptr) {
+    for (int64_t j = 0; j < qp.n; ++j)
+      if (qp.q[j] < 0.0)
+        return ErrorSolverResult(TERMINATION_REASON_INVALID_PROBLEM, "The objective is not convex (i.e., the objective matrix contains negative entries).");
+  }
+  if (params.use_feasibility_polishing && qp.q != nullptr)
+    return ErrorSolverResult(TERMINATION_REASON_INVALID_PARAMETER, "use_feasibility_polishing is only implemented for linear programs.");
+  if (params.presolve_options->use_glop)
+    return ErrorSolverResult(TERMINATION_REASON_INVALID_PARAMETER,
+                             "presolve_options.use_glop is not supported by the device path: Glop presolve is host-only (run it before the call).");
+  PreprocessSolver solver(qp, params);
+  return solver.PreprocessAndSolve(params, x0, y0, interrupt, std::move(callback));
+}
+
+QpView ViewOf(const QuadraticProgram& qp) {
+  QpView v;
+  v.n = qp.variable_lower_bounds.size();
+  v.m = qp.constraint_lower_bounds.size();
+  v.nnz = qp.constraint_matrix.nonZeros();
+  v.col_ptr = qp.constraint_matrix.outer_index.data();
+  v.row_idx = qp.constraint_matrix.inner_index.data();
+  v.val = qp.constraint_matrix.values.data();
+  v.c = qp.objective_vector.data();
+  v.q = qp.objective_matrix.has_value() ? qp.objective_matrix->data() : nullptr;
+  v.vlb = qp.variable_lower_bounds.data(); v.vub = qp.variable_upper_bounds.data();
+  v.clb = qp.constraint_lower_bounds.data(); v.cub = qp.constraint_upper_bounds.data();
+  v.objective_offset = qp.objective_offset;
+  v.objective_scaling_factor = qp.objective_scaling_factor;
+  v.name = qp.problem_name.has_value() ? qp.problem_name->c_str() : nullptr;
+  return v;
+}
+
+}  // namespace
+
+bool HasValidBounds(const QuadraticProgram& qp) {  // quadratic_program.cc:82-90
+  return BoundsAreValid(qp.constraint_lower_bounds.data(), qp.constraint_upper_bounds.data(), qp.constraint_lower_bounds.size()) &&
+         BoundsAreValid(qp.variable_lower_bounds.data(), qp.variable_upper_bounds.data(), qp.variable_lower_bounds.size());
+}
+
+SolverResult PrimalDualHybridGradient(QuadraticProgram qp, const PrimalDualHybridGradientParams& params, const std::atomic<bool>* interrupt_solve,
+                                      std::function<void(const IterationCallbackInfo&)> iteration_stats_callback) {
+  return PrimalDualHybridGradient(std::move(qp), params, std::nullopt, interrupt_solve, std::move(iteration_stats_callback));
+}
+
+SolverResult PrimalDualHybridGradient(QuadraticProgram qp, const PrimalDualHybridGradientParams& params,
+                                      std::optional<PrimalAndDualSolution> initial_solution, const std::atomic<bool>* interrupt_solve,
+                                      std::function<void(const IterationCallbackInfo&)> iteration_stats_callback) {
+  const std::string perr = ValidatePrimalDualHybridGradientParams(params);
+  if (!perr.empty()) return ErrorSolverResult(TERMINATION_REASON_INVALID_PARAMETER, perr);
+  const int64_t n = qp.variable_lower_bounds.size();
+  if (static_cast<int64_t>(qp.constraint_matrix.outer_index.size()) != qp.constraint_matrix.cols + 1 ||
+      qp.constraint_matrix.inner_index.size() != qp.constraint_matrix.values.size()) {
+    return ErrorSolverResult(TERMINATION_REASON_INVALID_PROBLEM, "constraint_matrix must be in compressed format. Call constraint_matrix.makeCompressed()");
+  }
+  const std::string derr = ValidateQuadraticProgramDimensions(qp);
+  if (!derr.empty()) return ErrorSolverResult(TERMINATION_REASON_INVALID_PROBLEM, "INVALID_ARGUMENT: " + derr);
+  const int64_t m = qp.constraint_lower_bounds.size();
+  const double* x0 = nullptr;
+  const double* y0 = nullptr;
+  if (initial_solution.has_value()) {  // size checks of pdhg.cc:899-947
+    if (static_cast<int64_t>(initial_solution->primal_solution.size()) != n)
+      return ErrorSolverResult(TERMINATION_REASON_INVALID_INITIAL_SOLUTION, "Initial primal solution has size " + std::to_string(initial_solution->primal_solution.size()) +
+                                                                                " which differs from problem primal size " + std::to_string(n));
+    if (static_cast<int64_t>(initial_solution->dual_solution.size()) != m)
+      return ErrorSolverResult(TERMINATION_REASON_INVALID_INITIAL_SOLUTION, "Initial dual solution has size " + std::to_string(initial_solution->dual_solution.size()) +
+                                                                                " which differs from problem dual size " + std::to_string(m));
+    x0 = initial_solution->primal_solution.data();
+    y0 = initial_solution->dual_solution.data();
+    // A zero-sized vector's data() may be null: keep "given" distinguishable from "absent".
+    static const double kEmpty = 0.0;
+    if (x0 == nullptr) x0 = &kEmpty;
+    if (y0 == nullptr) y0 = &kEmpty;
+  }
+  InterruptFlag flag;
+  flag.atomic_flag = interrupt_solve;
+  return SolveView(ViewOf(qp), params, x0, y0, interrupt_solve != nullptr ? &flag : nullptr, std::move(iteration_stats_callback));
+}
+
+}  // namespace pdlp_b200
+
+// ---------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------
+using namespace pdlp_b200;
+
+namespace {
+
+thread_local std::string g_last_error;
+
+pdlp_b200_status Fail(pdlp_b200_status s, const std::string& msg) {
+  g_last_error = msg;
+  return s;
+}
+
+template <class F>
+pdlp_b200_status Guard(F&& f) {
+  try {
+    return f();
+  } catch (const std::invalid_argument& e) {
+    return Fail(PDLP_B200_BAD_ARGUMENT, e.what());
+  } catch (const std::runtime_error& e) {
+    const std::string what = e.what();
+    return Fail(what.rfind("CUDA error", 0) == 0 ? PDLP_B200_CUDA_ERROR : PDLP_B200_INTERNAL_ERROR, what);
+  } catch (const std::exception& e) {
+    return Fail(PDLP_B200_INTERNAL_ERROR, e.what());
+  }
+}
+
+void SelectDevice(int device) {
+  int count = 0;
+  PDLP_CUDA_CHECK(cudaGetDeviceCount(&count));
+  if (count == 0) throw std::runtime_error("CUDA error: no CUDA device (pdlp_b200 has no CPU fallback)");
+  if (device >= 0) PDLP_CUDA_CHECK(cudaSetDevice(device));
+}
+
+uint8_t* DupBytes(const std::string& s) {
+  uint8_t* p = static_cast<uint8_t*>(std::malloc(s.size() > 0 ? s.size() : 1));
+  if (!s.empty()) std::memcpy(p, s.data(), s.size());
+  return p;
+}
+char* DupString(const std::string& s) {
+  char* p = static_cast<char*>(std::malloc(s.size() + 1));
+  std::memcpy(p, s.c_str(), s.size() + 1);
+  return p;
+}
+
+bool ParseParams(const uint8_t* bytes, size_t len, PrimalDualHybridGradientParams* out) {
+  if (bytes == nullptr || len == 0) return true;
+  return Parse(bytes, len, out);
+}
+
+bool ProblemPointersOk(const pdlp_b200_problem* p) {
+  if (p == nullptr || p->num_variables < 0 || p->num_constraints < 0 || p->num_nonzeros < 0) return false;
+  if (p->col_ptr == nullptr) return false;
+  if (p->num_nonzeros > 0 && (p->row_idx == nullptr || p->values == nullptr)) return false;
+  if (p->num_variables > 0 && (p->objective_vector == nullptr || p->variable_lower_bounds == nullptr || p->variable_upper_bounds == nullptr)) return false;
+  if (p->num_constraints > 0 && (p->constraint_lower_bounds == nullptr || p->constraint_upper_bounds == nullptr)) return false;
+  return true;
+}
+
+QpView ViewOfC(const pdlp_b200_problem* p) {
+  QpView v;
+  v.n = p->num_variables; v.m = p->num_constraints; v.nnz = p->num_nonzeros;
+  v.col_ptr = p->col_ptr; v.row_idx = p->row_idx; v.val = p->values;
+  v.c = p->objective_vector; v.q = p->objective_matrix_diagonal;
+  v.vlb = p->variable_lower_bounds; v.vub = p->variable_upper_bounds;
+  v.clb = p->constraint_lower_bounds; v.cub = p->constraint_upper_bounds;
+  v.objective_offset = p->objective_offset; v.objective_scaling_factor = p->objective_scaling_factor;
+  v.name = p->problem_name;
+  return v;
+}
+
+}  // namespace
+
+struct pdlp_b200_device_problem {
+  std::unique_ptr<PreprocessSolver> pre;
+  std::unique_ptr<Iterate> iterate;
+  int device = 0;
+};
+
+extern "C" {
+
+const char* pdlp_b200_last_error(void) { return g_last_error.c_str(); }
+void pdlp_b200_free(void* p) { std::free(p); }
+
+pdlp_b200_status pdlp_b200_solve(const pdlp_b200_problem* problem, const uint8_t* params_bytes, size_t params_len, const double* x0, const double* y0,
+                                 const volatile int* interrupt, pdlp_b200_callback callback, void* callback_user, int device, double* primal,
+                                 double* dual, double* reduced, int* has_solution, uint8_t** solve_log, size_t* solve_log_len,
+                                 pdlp_b200_counters* counters) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (!ProblemPointersOk(problem) || solve_log == nullptr || solve_log_len == nullptr || has_solution == nullptr)
+      return Fail(PDLP_B200_BAD_ARGUMENT, "null or negative-sized argument");
+    if ((x0 == nullptr) != (y0 == nullptr)) {
+      // A zero-length side may legitimately be null when the other is given.
+      if (!((x0 == nullptr && problem->num_variables == 0) || (y0 == nullptr && problem->num_constraints == 0)))
+        return Fail(PDLP_B200_BAD_ARGUMENT, "initial primal and dual solutions must be given together");
+    }
+    PrimalDualHybridGradientParams params;
+    if (!ParseParams(params_bytes, params_len, &params)) return Fail(PDLP_B200_BAD_ARGUMENT, "params is not a serialized PrimalDualHybridGradientParams");
+    *has_solution = 0;
+    SolverResult result;
+    const std::string perr = ValidatePrimalDualHybridGradientParams(params);
+    if (!perr.empty()) {
+      result = ErrorSolverResult(TERMINATION_REASON_INVALID_PARAMETER, perr);
+    } else {
+      SelectDevice(device);
+      InterruptFlag flag;
+      flag.int_flag = interrupt;
+      IterationCallback cb;
+      if (callback != nullptr) {
+        cb = [&](const IterationCallbackInfo& info) {
+          const std::string bytes = Serialize(info.iteration_stats);
+          const double norms[4] = {info.bound_norms.l2_norm_primal_linear_objective, info.bound_norms.l2_norm_constraint_bounds,
+                                   info.bound_norms.l_inf_norm_primal_linear_objective, info.bound_norms.l_inf_norm_constraint_bounds};
+          callback(static_cast<int>(info.iteration_type), reinterpret_cast<const uint8_t*>(bytes.data()), bytes.size(), norms, callback_user);
+        };
+      }
+      static const double kEmpty = 0.0;
+      const bool warm = x0 != nullptr || y0 != nullptr;
+      result = SolveView(ViewOfC(problem), params, warm ? (x0 ? x0 : &kEmpty) : nullptr, warm ? (y0 ? y0 : &kEmpty) : nullptr,
+                         interrupt != nullptr ? &flag : nullptr, std::move(cb));
+    }
+    if (static_cast<int64_t>(result.primal_solution.size()) == problem->num_variables &&
+        static_cast<int64_t>(result.dual_solution.size()) == problem->num_constraints &&
+        result.solve_log.termination_reason != TERMINATION_REASON_INVALID_PROBLEM &&
+        result.solve_log.termination_reason != TERMINATION_REASON_INVALID_PARAMETER &&
+        result.solve_log.termination_reason != TERMINATION_REASON_INVALID_INITIAL_SOLUTION) {
+      *has_solution = 1;
+      if (primal != nullptr) std::copy(result.primal_solution.begin(), result.primal_solution.end(), primal);
+      if (dual != nullptr) std::copy(result.dual_solution.begin(), result.dual_solution.end(), dual);
+      if (reduced != nullptr) std::copy(result.reduced_costs.begin(), result.reduced_costs.end(), reduced);
+    }
+    const std::string bytes = Serialize(result.solve_log);
+    *solve_log = DupBytes(bytes);
+    *solve_log_len = bytes.size();
+    if (counters != nullptr) {
+      const SolveCounters& c = LastSolveCounters();
+      counters->kernel_launches = c.kernel_launches;
+      counters->trial_steps = c.trial_steps;
+      counters->setup_seconds = c.setup_seconds;
+      counters->loop_seconds = c.loop_seconds;
+      counters->device_loop_seconds = c.device_loop_seconds;
+    }
+    return PDLP_B200_OK;
+  });
+}
+
+pdlp_b200_status pdlp_b200_validate_params(const uint8_t* params_bytes, size_t params_len, char** message) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (message == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "message is null");
+    PrimalDualHybridGradientParams params;
+    if (!ParseParams(params_bytes, params_len, &params)) return Fail(PDLP_B200_BAD_ARGUMENT, "params is not a serialized PrimalDualHybridGradientParams");
+    const std::string e = ValidatePrimalDualHybridGradientParams(params);
+    *message = e.empty() ? nullptr : DupString(e);
+    return PDLP_B200_OK;
+  });
+}
+
+pdlp_b200_status pdlp_b200_default_params(uint8_t** params, size_t* params_len) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (params == nullptr || params_len == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "null output");
+    const std::string bytes = Serialize(PrimalDualHybridGradientParams());
+    *params = DupBytes(bytes);
+    *params_len = bytes.size();
+    return PDLP_B200_OK;
+  });
+}
+
+pdlp_b200_status pdlp_b200_describe_schema(char** text) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (text == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "null output");
+    *text = DupString(DescribeSchema());
+    return PDLP_B200_OK;
+  });
+}
+
+pdlp_b200_status pdlp_b200_problem_create(const pdlp_b200_problem* problem, int device, pdlp_b200_device_problem** out) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (!ProblemPointersOk(problem) || out == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "null or negative-sized argument");
+    SelectDevice(device);
+    auto h = std::make_unique<pdlp_b200_device_problem>();
+    PDLP_CUDA_CHECK(cudaGetDevice(&h->device));
+    QpView v = ViewOfC(problem);
+    v.name = nullptr;
+    h->pre = std::make_unique<PreprocessSolver>(v, PrimalDualHybridGradientParams());
+    *out = h.release();
+    return PDLP_B200_OK;
+  });
+}
+
+void pdlp_b200_problem_destroy(pdlp_b200_device_problem* h) {
+  if (h == nullptr) return;
+  cudaSetDevice(h->device);
+  h->iterate.reset();
+  h->pre.reset();
+  delete h;
+}
+
+pdlp_b200_status pdlp_b200_matvec(pdlp_b200_device_problem* h, int which, const double* v, double* out, int repeat, double* seconds_per_launch) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (h == nullptr || v == nullptr || out == nullptr || (which != 0 && which != 1)) return Fail(PDLP_B200_BAD_ARGUMENT, "bad argument");
+    PDLP_CUDA_CHECK(cudaSetDevice(h->device));
+    Workspace& ws = h->pre->ws();
+    DeviceProblem& p = h->pre->problem();
+    const int64_t in_size = which == 0 ? p.m : p.n, out_size = which == 0 ? p.n : p.m;
+    DVec& din = which == 0 ? ws.scratch_m[0] : ws.scratch_n[0];
+    DVec& dout = which == 0 ? ws.scratch_n[1] : ws.scratch_m[1];
+    din.Upload(v, in_size, ws.stream);
+    const SparseRows& s = which == 0 ? p.K.by_col : p.K.by_row;
+    if (repeat < 1) repeat = 1;
+    cudaEvent_t e0, e1;
+    PDLP_CUDA_CHECK(cudaEventCreate(&e0));
+    PDLP_CUDA_CHECK(cudaEventCreate(&e1));
+    RowDot(ws, s, din.get(), dout.get());  // warm-up (also the result)
+    PDLP_CUDA_CHECK(cudaEventRecord(e0, ws.stream));
+    for (int r = 0; r < repeat; ++r) RowDot(ws, s, din.get(), dout.get());
+    PDLP_CUDA_CHECK(cudaEventRecord(e1, ws.stream));
+    dout.Download(out, out_size, ws.stream);
+    PDLP_CUDA_CHECK(cudaGetLastError());
+    ws.Sync();
+    float ms = 0;
+    PDLP_CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (seconds_per_launch != nullptr) *seconds_per_launch = ms * 1e-3 / repeat;
+    return PDLP_B200_OK;
+  });
+}
+
+pdlp_b200_status pdlp_b200_scaled_norms(pdlp_b200_device_problem* h, int which, int l2, const double* row_scale, const double* col_scale, double* out) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (h == nullptr || row_scale == nullptr || col_scale == nullptr || out == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "bad argument");
+    PDLP_CUDA_CHECK(cudaSetDevice(h->device));
+    Workspace& ws = h->pre->ws();
+    DeviceProblem& p = h->pre->problem();
+    ws.scratch_m[0].Upload(row_scale, p.m, ws.stream);
+    ws.scratch_n[0].Upload(col_scale, p.n, ws.stream);
+    if (which == 0) {
+      ScaledRowNorms(ws, p.K.by_col, ws.scratch_m[0].get(), ws.scratch_n[0].get(), l2 != 0, ws.scratch_n[1].get());
+      ws.scratch_n[1].Download(out, p.n, ws.stream);
+    } else {
+      ScaledRowNorms(ws, p.K.by_row, ws.scratch_n[0].get(), ws.scratch_m[0].get(), l2 != 0, ws.scratch_m[1].get());
+      ws.scratch_m[1].Download(out, p.m, ws.stream);
+    }
+    PDLP_CUDA_CHECK(cudaGetLastError());
+    ws.Sync();
+    return PDLP_B200_OK;
+  });
+}
+
+pdlp_b200_status pdlp_b200_stats(pdlp_b200_device_problem* h, uint8_t** stats, size_t* stats_len) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (h == nullptr || stats == nullptr || stats_len == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "bad argument");
+    PDLP_CUDA_CHECK(cudaSetDevice(h->device));
+    SolveLog carrier;  // QuadraticProgramStats travels inside a SolveLog (one codec entry point)
+    carrier.original_problem_stats.mut() = h->pre->ComputeStats();
+    const std::string bytes = Serialize(carrier);
+    *stats = DupBytes(bytes);
+    *stats_len = bytes.size();
+    return PDLP_B200_OK;
+  });
+}
+
+pdlp_b200_status pdlp_b200_rescale(pdlp_b200_device_problem* h, int l_inf_ruiz_iterations, int l2_norm_rescaling, double* row_scale, double* col_scale,
+                                   double* scaled_values) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (h == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "bad argument");
+    PDLP_CUDA_CHECK(cudaSetDevice(h->device));
+    Workspace& ws = h->pre->ws();
+    DeviceProblem& p = h->pre->problem();
+    PrimalDualHybridGradientParams params;
+    params.l_inf_ruiz_iterations = l_inf_ruiz_iterations;
+    params.l2_norm_rescaling = l2_norm_rescaling != 0;
+    h->pre->RescaleForTest(params);
+    if (row_scale != nullptr) p.row_scale.Download(row_scale, p.m, ws.stream);
+    if (col_scale != nullptr) p.col_scale.Download(col_scale, p.n, ws.stream);
+    if (scaled_values != nullptr) p.K.by_col.val.Download(scaled_values, p.K.by_col.nnz, ws.stream);
+    PDLP_CUDA_CHECK(cudaGetLastError());
+    ws.Sync();
+    return PDLP_B200_OK;
+  });
+}
+
+pdlp_b200_status pdlp_b200_kkt_stats(pdlp_b200_device_problem* h, const uint8_t* params_bytes, size_t params_len, const double* x, const double* y,
+                                     uint8_t** stats, size_t* stats_len) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (h == nullptr || stats == nullptr || stats_len == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "bad argument");
+    PrimalDualHybridGradientParams params;
+    if (!ParseParams(params_bytes, params_len, &params)) return Fail(PDLP_B200_BAD_ARGUMENT, "unparsable params");
+    PDLP_CUDA_CHECK(cudaSetDevice(h->device));
+    Workspace& ws = h->pre->ws();
+    DeviceProblem& p = h->pre->problem();
+    DVec dx(p.n > 0 ? p.n : 1), dy(p.m > 0 ? p.m : 1);
+    dx.Upload(x, p.n, ws.stream);
+    dy.Upload(y, p.m, ws.stream);
+    IterationStats out;
+    ConvergenceInformation ci;
+    InfeasibilityInformation ii;
+    PointMetadata md;
+    h->pre->ComputeConvergenceAndInfeasibility(params, dx.get(), dy.get(), dx.get(), dy.get(), POINT_TYPE_CURRENT_ITERATE, &ci, &ii, &md);
+    out.convergence_information.push_back(ci);
+    out.infeasibility_information.push_back(ii);
+    out.point_metadata.push_back(md);
+    const std::string bytes = Serialize(out);
+    *stats = DupBytes(bytes);
+    *stats_len = bytes.size();
+    return PDLP_B200_OK;
+  });
+}
+
+pdlp_b200_status pdlp_b200_reduced_costs(pdlp_b200_device_problem* h, const uint8_t* params_bytes, size_t params_len, const double* x, const double* y,
+                                         int use_zero_primal_objective, double* reduced_costs) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (h == nullptr || reduced_costs == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "bad argument");
+    PrimalDualHybridGradientParams params;
+    if (!ParseParams(params_bytes, params_len, &params)) return Fail(PDLP_B200_BAD_ARGUMENT, "unparsable params");
+    PDLP_CUDA_CHECK(cudaSetDevice(h->device));
+    Workspace& ws = h->pre->ws();
+    DeviceProblem& p = h->pre->problem();
+    DVec dx(p.n > 0 ? p.n : 1), dy(p.m > 0 ? p.m : 1), rc(p.n > 0 ? p.n : 1);
+    dx.Upload(x, p.n, ws.stream);
+    dy.Upload(y, p.m, ws.stream);
+    ComputeReducedCosts(ws, p, dx.get(), dy.get(), use_zero_primal_objective != 0, params.handle_some_primal_gradients_on_finite_bounds_as_residuals, rc.get());
+    rc.Download(reduced_costs, p.n, ws.stream);
+    PDLP_CUDA_CHECK(cudaGetLastError());
+    ws.Sync();
+    return PDLP_B200_OK;
+  });
+}
+
+pdlp_b200_status pdlp_b200_localized_bounds(pdlp_b200_device_problem* h, const double* x, const double* y, double primal_weight, double radius,
+                                            int use_diagonal, double diagonal_tol, double* out) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (h == nullptr || out == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "bad argument");
+    PDLP_CUDA_CHECK(cudaSetDevice(h->device));
+    Workspace& ws = h->pre->ws();
+    DeviceProblem& p = h->pre->problem();
+    DVec dx(p.n > 0 ? p.n : 1), dy(p.m > 0 ? p.m : 1);
+    dx.Upload(x, p.n, ws.stream);
+    dy.Upload(y, p.m, ws.stream);
+    const LocalizedBounds b = ComputeLocalizedLagrangianBounds(ws, p, dx.get(), dy.get(), nullptr, primal_weight, radius, use_diagonal != 0, diagonal_tol, nullptr);
+    out[0] = b.lagrangian_value; out[1] = b.lower_bound; out[2] = b.upper_bound; out[3] = b.radius;
+    return PDLP_B200_OK;
+  });
+}
+
+pdlp_b200_status pdlp_b200_trial_steps(pdlp_b200_device_problem* h, int steps, double step_size, double primal_weight, double* x, double* y,
+                                       double* state_out, double* seconds, long long* launches) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (h == nullptr || steps < 0) return Fail(PDLP_B200_BAD_ARGUMENT, "bad argument");
+    PDLP_CUDA_CHECK(cudaSetDevice(h->device));
+    Workspace& ws = h->pre->ws();
+    DeviceProblem& p = h->pre->problem();
+    if (!h->iterate) {
+      h->iterate = std::make_unique<Iterate>();
+      h->iterate->Init(p.n, p.m);
+    }
+    Iterate& it = *h->iterate;
+    if (x != nullptr) it.x[0].Upload(x, p.n, ws.stream); else it.x[0].Zero(ws.stream);
+    if (y != nullptr) it.y[0].Upload(y, p.m, ws.stream); else it.y[0].Zero(ws.stream);
+    it.avg_x.Zero(ws.stream);
+    it.avg_y.Zero(ws.stream);
+    RowDot(ws, p.K.by_col, it.y[0].get(), it.kty[0].get());
+    StepState st{};
+    st.active = 1;
+    st.target_iteration = 2147483647;
+    st.step_size = step_size;
+    st.primal_weight = primal_weight;
+    st.ratio_last_two_step_sizes = 1.0;
+    st.kkt_pass_limit = std::numeric_limits<double>::infinity();
+    st.passes_per_rejected_step = 1.0;
+    st.reduction_exponent = 0.3;
+    st.growth_exponent = 0.6;
+    st.mp_tau = -1.0;
+    st.mp_new_tau = -1.0;
+    PDLP_CUDA_CHECK(cudaMemcpyAsync(it.state.get(), &st, sizeof(st), cudaMemcpyHostToDevice, ws.stream));
+    ws.Sync();
+    cudaEvent_t e0, e1;
+    PDLP_CUDA_CHECK(cudaEventCreate(&e0));
+    PDLP_CUDA_CHECK(cudaEventCreate(&e1));
+    const long long before = ws.launches;
+    PDLP_CUDA_CHECK(cudaEventRecord(e0, ws.stream));
+    EnqueueAdaptiveTrials(ws, p, it, steps, false);
+    PDLP_CUDA_CHECK(cudaEventRecord(e1, ws.stream));
+    PDLP_CUDA_CHECK(cudaMemcpyAsync(&st, it.state.get(), sizeof(st), cudaMemcpyDeviceToHost, ws.stream));
+    ws.Sync();
+    float ms = 0;
+    PDLP_CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (seconds != nullptr) *seconds = ms * 1e-3;
+    if (launches != nullptr) *launches = ws.launches - before;
+    if (x != nullptr) it.x[st.cur].Download(x, p.n, ws.stream);
+    if (y != nullptr) it.y[st.cur].Download(y, p.m, ws.stream);
+    ws.Sync();
+    if (state_out != nullptr) {
+      state_out[0] = st.step_size; state_out[1] = st.iterations_completed; state_out[2] = st.num_rejected_steps;
+      state_out[3] = st.last_movement; state_out[4] = st.last_nonlinearity;
+    }
+    return PDLP_B200_OK;
+  });
+}
+
+}  // extern "C"

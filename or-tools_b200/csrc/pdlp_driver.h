@@ -1,0 +1,159 @@
+// Internal declarations of the host driver: the two classes that mirror
+// PreprocessSolver and Solver of ortools/pdlp/primal_dual_hybrid_gradient.cc:318-709.
+// The control flow stays on the host; vectors never leave the device until the result
+// is built.
+#ifndef PDLP_B200_DRIVER_H_
+#define PDLP_B200_DRIVER_H_
+
+#include <chrono>
+#include <memory>
+
+#include "pdlp_ops.cuh"
+#include "primal_dual_hybrid_gradient.h"
+
+namespace pdlp_b200 {
+
+// Borrowed view of a QuadraticProgram (the C ABI passes caller memory straight through).
+struct QpView {
+  int64_t n = 0, m = 0, nnz = 0;
+  const int64_t* col_ptr = nullptr;
+  const int64_t* row_idx = nullptr;
+  const double* val = nullptr;
+  const double* c = nullptr;
+  const double* q = nullptr;  // null for an LP
+  const double* vlb = nullptr; const double* vub = nullptr;
+  const double* clb = nullptr; const double* cub = nullptr;
+  double objective_offset = 0.0, objective_scaling_factor = 1.0;
+  const char* name = nullptr;
+};
+
+using IterationCallback = std::function<void(const IterationCallbackInfo&)>;
+
+class WallTimer {
+ public:
+  void Start() { running_ = true; t0_ = Clock::now(); }
+  void Stop() { if (running_) { acc_ += Elapsed(); running_ = false; } }
+  double Get() const { return acc_ + (running_ ? Elapsed() : 0.0); }
+ private:
+  using Clock = std::chrono::steady_clock;
+  double Elapsed() const { return std::chrono::duration<double>(Clock::now() - t0_).count(); }
+  Clock::time_point t0_;
+  double acc_ = 0.0;
+  bool running_ = false;
+};
+
+SolverResult ErrorSolverResult(int reason, const std::string& message);  // pdhg.cc:717-725
+extern thread_local SolveCounters g_last_counters;
+
+class Solver;
+
+// pdhg.cc:318-502.
+class PreprocessSolver {
+ public:
+  PreprocessSolver(const QpView& qp, const PrimalDualHybridGradientParams& params);
+  ~PreprocessSolver();
+  SolverResult PreprocessAndSolve(const PrimalDualHybridGradientParams& params, const double* x0, const double* y0,
+                                  const InterruptFlag* interrupt, IterationCallback callback);
+
+  // pdhg.cc:1434-1518.  Points are device pointers; avg / delta may be null.
+  std::optional<TerminationReasonAndPointType> UpdateIterationStatsAndCheckTermination(
+      const PrimalDualHybridGradientParams& params, bool force_numerical_termination, const double* x_cur, const double* y_cur,
+      const double* x_avg, const double* y_avg, const double* dx, const double* dy, const double* x_start, const double* y_start,
+      const InterruptFlag* interrupt, IterationType type, const IterationStats& full_stats, IterationStats& stats);
+  // pdhg.cc:1520-1564.
+  void ComputeConvergenceAndInfeasibility(const PrimalDualHybridGradientParams& params, const double* x, const double* y, const double* x_start,
+                                          const double* y_start, int candidate_type, ConvergenceInformation* ci, InfeasibilityInformation* ii,
+                                          PointMetadata* md);
+  // pdhg.cc:1568-1643.  x, y are device pointers into the scaled space.
+  SolverResult ConstructOriginalSolverResult(const PrimalDualHybridGradientParams& params, const double* x, const double* y, SolveLog log);
+
+  QuadraticProgramStats ComputeStats();
+  // Kernel-level entry (pdlp_b200_rescale): ApplyRescaling on the resident problem.
+  void RescaleForTest(const PrimalDualHybridGradientParams& params) { ApplyRescaling(params); }
+  Workspace& ws() { return ws_; }
+  DeviceProblem& problem() { return problem_; }
+  const QuadraticProgramBoundNorms& OriginalBoundNorms() const { return original_bound_norms_; }
+  const std::vector<int32_t>& RandomProjectionSeeds() const { return seeds_; }
+
+ private:
+  void ApplyRescaling(const PrimalDualHybridGradientParams& params);
+  void AddRandomProjections(const double* x, const double* y, PointMetadata* md);
+
+  QpView view_;
+  Workspace ws_;
+  DeviceProblem problem_;
+  QuadraticProgramBoundNorms original_bound_norms_;
+  IterationCallback callback_;
+  std::vector<int32_t> seeds_;
+};
+
+enum class InnerStepOutcome { kSuccessful, kForceNumericalTermination };
+
+// pdhg.cc:504-709.  Owns the iterate buffers and the device-resident step state.
+class Solver {
+ public:
+  // x0 / y0 are device pointers (scaled space), copied into the iterate buffers.
+  Solver(const PrimalDualHybridGradientParams& params, const double* x0, const double* y0, double initial_step_size, double initial_primal_weight,
+         PreprocessSolver* preprocess_solver);
+  // Returns the log plus the device pointers of the chosen point (valid until the
+  // Solver is destroyed).
+  struct Outcome {
+    SolveLog log;
+    const double* x = nullptr;
+    const double* y = nullptr;
+  };
+  Outcome Solve(IterationType type, const InterruptFlag* interrupt, SolveLog log);
+  long long TrialSteps() const { return host_.total_trials; }
+  double DeviceLoopSeconds() const { return device_loop_seconds_; }
+
+ private:
+  struct Bounds { double lagrangian_value, lower_bound, upper_bound, radius; };
+  const double* X() const { return it_.x[host_.cur].get(); }
+  const double* Y() const { return it_.y[host_.cur].get(); }
+  const double* Kty() const { return it_.kty[host_.cur].get(); }
+  bool AverageHasWeight() const { return host_.avg_weight_sum > 0.0; }
+  const double* PrimalAverage() const { return host_.avg_weight_sum > 0.0 ? it_.avg_x.get() : X(); }
+  const double* DualAverage() const { return host_.avg_weight_sum_dual > 0.0 ? it_.avg_y.get() : Y(); }
+
+  void PushState();
+  void PullState();
+  void RunDeviceIterations(int target_iteration);
+  int NextEventIteration(int k, IterationType type, int next_polishing_iteration) const;
+
+  IterationStats CreateSimpleIterationStats(int restart_used) const;
+  double DistanceTraveledFromLastStart(const double* x, const double* y);
+  Bounds BoundsAtCurrent();
+  Bounds BoundsAtAverage();
+  bool ShouldDoAdaptiveRestartHeuristic(double candidate_normalized_gap) const;
+  int DetermineDistanceBasedRestartChoice();
+  int ChooseRestartToApply(bool is_major_iteration);
+  double ComputeNewPrimalWeight();
+  void ApplyRestartChoice(int restart_to_apply);
+  std::optional<Outcome> MajorIterationAndTerminationCheck(IterationType type, bool force_numerical_termination, const InterruptFlag* interrupt,
+                                                            const IterationStats& work_from_feasibility_polishing, SolveLog& log);
+  Outcome PickSolutionAndConstructOutcome(const IterationStats& stats, int reason, int point_type, SolveLog log);
+  IterationStats TotalWorkSoFar(const SolveLog& log) const;
+  std::optional<Outcome> TryFeasibilityPolishing(int iteration_limit, const InterruptFlag* interrupt, SolveLog& log);
+
+  const PrimalDualHybridGradientParams params_;
+  PreprocessSolver* pre_;
+  Workspace& ws_;
+  DeviceProblem& problem_;
+  Iterate it_;
+  StepState host_{};  // mirror of the device state, valid after PullState()
+  int iterations_completed_ = 0;
+  bool have_delta_ = false;
+  double normalized_gap_at_last_trial_ = std::numeric_limits<double>::infinity();
+  double normalized_gap_at_last_restart_ = std::numeric_limits<double>::infinity();
+  double preprocessing_time_sec_ = 0.0;
+  WallTimer timer_;
+  struct { double distance_moved_last_restart_period = std::numeric_limits<double>::infinity(); int length_of_last_restart_period = 1; } distance_info_;
+  int poll_iterations_ = 8;
+  bool poll_always_ = false;
+  double device_loop_seconds_ = 0.0;
+  // Holders for the result of feasibility polishing (device vectors must outlive Solve()).
+  DVec polished_x_, polished_y_;
+};
+
+}  // namespace pdlp_b200
+#endif  // PDLP_B200_DRIVER_H_

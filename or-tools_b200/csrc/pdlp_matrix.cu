@@ -1,0 +1,156 @@
+// Upload of CSC(K) and device-side construction of CSR(K).  One-time setup per solve:
+// replaces `transposed_constraint_matrix_ = qp_.constraint_matrix.transpose()`
+// (ortools/pdlp/sharded_quadratic_program.cc:66-67).  The stable radix sort is CUB's
+// (library code, setup only); everything on the iteration path is hand-written.
+#include "pdlp_matrix.cuh"
+
+#include <cub/device/device_radix_sort.cuh>
+
+namespace pdlp_b200 {
+
+namespace {
+
+__global__ void narrow_offsets_kernel(const int64_t* in, int* out, int64_t count, int64_t nnz, int* bad) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < count; i += stride) {
+    const int64_t v = in[i];
+    if (v < 0 || v > nnz || (i > 0 && in[i - 1] > v) || (i == 0 && v != 0) || (i == count - 1 && v != nnz)) *bad = 1;
+    out[i] = static_cast<int>(v);
+  }
+}
+
+__global__ void narrow_indices_kernel(const int64_t* in, int* out, int* iota, int64_t count, int64_t limit, int* bad) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < count; i += stride) {
+    const int64_t v = in[i];
+    if (v < 0 || v >= limit) *bad = 2;
+    out[i] = static_cast<int>(v);
+    iota[i] = static_cast<int>(i);
+  }
+}
+
+// For each transposed position p: source nonzero perm[p]; its column is the last j with
+// col_ptr[j] <= perm[p].
+__global__ void gather_transposed_kernel(const int* perm, const int* col_ptr, int n, const double* val, int64_t nnz, int* out_idx, double* out_val) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t p = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; p < nnz; p += stride) {
+    const int src = perm[p];
+    int lo = 0, hi = n;  // invariant: col_ptr[lo] <= src < col_ptr[hi]
+    while (hi - lo > 1) {
+      const int mid = lo + ((hi - lo) >> 1);
+      if (col_ptr[mid] <= src) lo = mid; else hi = mid;
+    }
+    out_idx[p] = lo;
+    out_val[p] = val[src];
+  }
+}
+
+// row_ptr[r] = number of sorted keys < r.
+__global__ void row_offsets_kernel(const int* sorted_rows, int64_t nnz, int m, int* row_ptr) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t r = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; r <= m; r += stride) {
+    int64_t lo = 0, hi = nnz;  // first position with key >= r
+    while (lo < hi) {
+      const int64_t mid = lo + ((hi - lo) >> 1);
+      if (sorted_rows[mid] < r) lo = mid + 1; else hi = mid;
+    }
+    row_ptr[r] = static_cast<int>(lo);
+  }
+}
+
+void SetBlocks(SparseRows* s, const std::vector<int>& host_ptr, cudaStream_t stream) {
+  std::vector<int> blocks = PartitionRows(host_ptr.data(), s->rows, &s->max_row_nnz);
+  s->num_blocks = static_cast<int>(blocks.size()) - 1;
+  s->block_start.Resize(blocks.size());
+  s->block_start.Upload(blocks.data(), blocks.size(), stream);
+  PDLP_CUDA_CHECK(cudaStreamSynchronize(stream));
+}
+
+}  // namespace
+
+std::vector<int> PartitionRows(const int* ptr, int rows, int* max_row_nnz) {
+  constexpr int kMaxRowsPerBlock = 4 * kBlock;
+  std::vector<int> starts;
+  starts.push_back(0);
+  int mx = 0;
+  int r = 0;
+  while (r < rows) {
+    const int begin = r;
+    int nz = ptr[r + 1] - ptr[r];
+    mx = nz > mx ? nz : mx;
+    ++r;
+    if (nz <= kStreamChunk) {
+      while (r < rows && r - begin < kMaxRowsPerBlock) {
+        const int next = ptr[r + 1] - ptr[r];
+        if (nz + next > kStreamChunk) break;
+        nz += next;
+        mx = next > mx ? next : mx;
+        ++r;
+      }
+    }
+    starts.push_back(r);
+  }
+  if (max_row_nnz != nullptr) *max_row_nnz = mx;
+  return starts;
+}
+
+void BuildDeviceMatrix(int64_t n, int64_t m, int64_t nnz, const int64_t* col_ptr, const int64_t* row_idx, const double* val,
+                       cudaStream_t stream, DeviceMatrix* out) {
+  if (nnz >= (int64_t{1} << 31) - 1 || n >= (int64_t{1} << 31) - 1 || m >= (int64_t{1} << 31) - 1) {
+    throw std::runtime_error("pdlp_b200: one device block must have fewer than 2^31 rows, columns and nonzeros");
+  }
+  SparseRows& csc = out->by_col;
+  SparseRows& csr = out->by_row;
+  csc.rows = static_cast<int>(n); csc.cols = static_cast<int>(m); csc.nnz = nnz;
+  csr.rows = static_cast<int>(m); csr.cols = static_cast<int>(n); csr.nnz = nnz;
+  csc.ptr.Resize(n + 1); csc.idx.Resize(nnz); csc.val.Resize(nnz);
+  csr.ptr.Resize(m + 1); csr.idx.Resize(nnz); csr.val.Resize(nnz);
+
+  DeviceArray<int> bad(1);
+  bad.Zero(stream);
+  DeviceArray<int> iota(nnz);
+  {
+    DeviceArray<int64_t> wide_ptr(n + 1), wide_idx(nnz);
+    wide_ptr.Upload(col_ptr, n + 1, stream);
+    wide_idx.Upload(row_idx, nnz, stream);
+    csc.val.Upload(val, nnz, stream);
+    narrow_offsets_kernel<<<GridFor(n + 1), kBlock, 0, stream>>>(wide_ptr.get(), csc.ptr.get(), n + 1, nnz, bad.get());
+    narrow_indices_kernel<<<GridFor(nnz), kBlock, 0, stream>>>(wide_idx.get(), csc.idx.get(), iota.get(), nnz, m, bad.get());
+    PDLP_CUDA_CHECK(cudaGetLastError());
+    int host_bad = 0;
+    bad.Download(&host_bad, 1, stream);
+    PDLP_CUDA_CHECK(cudaStreamSynchronize(stream));
+    if (host_bad != 0) throw std::invalid_argument("pdlp_b200: constraint matrix is not a valid compressed CSC matrix");
+  }
+
+  // Stable sort of (row, position) pairs: CSR order with columns ascending per row.
+  if (nnz > 0) {
+    DeviceArray<int> sorted_rows(nnz), perm(nnz);
+    int end_bit = 1;
+    while (end_bit < 31 && (int64_t{1} << end_bit) < m) ++end_bit;
+    size_t temp_bytes = 0;
+    PDLP_CUDA_CHECK(cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, csc.idx.get(), sorted_rows.get(), iota.get(), perm.get(),
+                                                    static_cast<int>(nnz), 0, end_bit, stream));
+    DeviceArray<unsigned char> temp(temp_bytes);
+    PDLP_CUDA_CHECK(cub::DeviceRadixSort::SortPairs(temp.get(), temp_bytes, csc.idx.get(), sorted_rows.get(), iota.get(), perm.get(),
+                                                    static_cast<int>(nnz), 0, end_bit, stream));
+    gather_transposed_kernel<<<GridFor(nnz), kBlock, 0, stream>>>(perm.get(), csc.ptr.get(), static_cast<int>(n), csc.val.get(), nnz,
+                                                                 csr.idx.get(), csr.val.get());
+    row_offsets_kernel<<<GridFor(m + 1), kBlock, 0, stream>>>(sorted_rows.get(), nnz, static_cast<int>(m), csr.ptr.get());
+    PDLP_CUDA_CHECK(cudaGetLastError());
+    PDLP_CUDA_CHECK(cudaStreamSynchronize(stream));
+  } else {
+    csr.ptr.Zero(stream);
+  }
+
+  // Work-block partitions (host, from the offsets).
+  std::vector<int> host_ptr(n + 1);
+  for (int64_t j = 0; j <= n; ++j) host_ptr[j] = static_cast<int>(col_ptr[j]);
+  SetBlocks(&csc, host_ptr, stream);
+  host_ptr.assign(m + 1, 0);
+  csr.ptr.Download(host_ptr.data(), m + 1, stream);
+  PDLP_CUDA_CHECK(cudaStreamSynchronize(stream));
+  SetBlocks(&csr, host_ptr, stream);
+}
+
+}  // namespace pdlp_b200

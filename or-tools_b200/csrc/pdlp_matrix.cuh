@@ -1,0 +1,44 @@
+// Device-resident constraint matrix in both orientations, the replacement of
+// ShardedQuadraticProgram's `qp_.constraint_matrix` + `transposed_constraint_matrix_`
+// (ortools/pdlp/sharded_quadratic_program.cc:63-93).  fp64 values, int32 indices and
+// offsets (the reference uses int64, quadratic_program.h:130; one GPU's block must
+// hold fewer than 2^31 nonzeros).
+#ifndef PDLP_B200_MATRIX_CUH_
+#define PDLP_B200_MATRIX_CUH_
+
+#include <vector>
+
+#include "pdlp_common.cuh"
+
+namespace pdlp_b200 {
+
+// A matrix stored by compressed "rows".  For CSC(K) a "row" is a column of K.
+struct SparseRows {
+  int rows = 0, cols = 0;
+  int64_t nnz = 0;
+  DeviceArray<int> ptr;  // rows + 1
+  DeviceArray<int> idx;  // nnz
+  DVec val;              // nnz
+  DeviceArray<int> block_start;  // num_blocks + 1
+  int num_blocks = 0;
+  int max_row_nnz = 0;
+  RowBlocks View() const { return RowBlocks{ptr.get(), block_start.get(), num_blocks, rows}; }
+  int Grid() const { return num_blocks < 1 ? 1 : (num_blocks > kMaxGrid ? kMaxGrid : num_blocks); }
+};
+
+struct DeviceMatrix {
+  SparseRows by_col;  // CSC of K: n compressed columns, indices are constraint rows
+  SparseRows by_row;  // CSR of K: m compressed rows, indices are variable columns
+};
+
+// Cuts [0, rows) into work blocks for rowstream_kernel from a host copy of the offsets.
+std::vector<int> PartitionRows(const int* ptr, int rows, int* max_row_nnz);
+
+// Uploads CSC(K) given with int64 offsets/indices and builds CSR(K) on the device
+// (stable: columns ascending inside every row, exactly the order of Eigen's
+// `.transpose()` materialisation).  Throws std::runtime_error on CUDA failure.
+void BuildDeviceMatrix(int64_t n, int64_t m, int64_t nnz, const int64_t* col_ptr, const int64_t* row_idx, const double* val,
+                       cudaStream_t stream, DeviceMatrix* out);
+
+}  // namespace pdlp_b200
+#endif  // PDLP_B200_MATRIX_CUH_

@@ -1,0 +1,149 @@
+// Host-callable launchers for every device operation of the PDHG path, plus the
+// device-resident problem / iterate / step-state records they work on.  Each launcher
+// cites the reference function it replaces (files under /root/reference/ortools/pdlp/).
+#ifndef PDLP_B200_OPS_CUH_
+#define PDLP_B200_OPS_CUH_
+
+#include <cmath>
+#include <limits>
+
+#include "pdlp_matrix.cuh"
+
+namespace pdlp_b200 {
+
+// The (rescaled) problem in HBM.  Primal-side vectors have length n, dual-side m.
+struct DeviceProblem {
+  int64_t n = 0, m = 0;
+  DeviceMatrix K;
+  DVec c, q;             // q empty for an LP (diagonal of the objective matrix otherwise)
+  DVec vlb, vub;         // variable bounds
+  DVec clb, cub;         // constraint bounds
+  DVec col_scale, row_scale;
+  bool is_lp = true;
+  double objective_offset = 0.0, objective_scaling_factor = 1.0;
+  const double* q_or_null() const { return is_lp ? nullptr : q.get(); }
+};
+
+// Launch context: stream, per-kernel partial buffers, totals, pinned read-back.
+struct Workspace {
+  cudaStream_t stream = nullptr;
+  DVec partials[3];          // kMaxGrid * kMaxSlots each
+  DVec totals;               // kMaxSlots * 4
+  double* host_totals = nullptr;  // pinned, kMaxSlots * 4
+  DVec scratch_n[3], scratch_m[3], scratch_nm[2];  // sized n, m, n+m on demand
+  int64_t n = 0, m = 0;
+  long long launches = 0;    // kernels launched (bench "gpu_launches")
+  void Init(int64_t n_, int64_t m_);
+  void Destroy();
+  void Sync() { PDLP_CUDA_CHECK(cudaStreamSynchronize(stream)); }
+};
+
+// Device-side loop control and step-size state of Solver (primal_dual_hybrid_gradient.cc
+// :504-709 members step_size_, primal_weight_, num_rejected_steps_, iterations_completed_,
+// the averages' weight/term counters).  Lives in HBM; the host reads it back only at
+// major-iteration / termination-check / restart boundaries.
+struct StepState {
+  int active;                // device keeps taking trial steps while 1
+  int cur;                   // which of the two iterate buffers holds the current iterate
+  int iterations_completed;
+  int target_iteration;      // stop when iterations_completed reaches this
+  int num_rejected_steps;
+  int inner;                 // 0-based trial index inside the current inner loop
+  int force_numerical;       // InnerStepOutcome::kForceNumericalTermination
+  int reset_average;         // ResetAverageToCurrent() requested
+  int accepted_last;         // last trial accepted (consumed by the averaging kernel)
+  int avg_num_terms;
+  int first_mp_add_pending;  // Malitsky-Pock: old x must be added to the empty average
+  int reserved;
+  long long total_trials;
+  double step_size, primal_weight;
+  double avg_weight_sum, avg_weight_sum_dual;  // differ only under Malitsky-Pock (:2260-2272)
+  double avg_ratio, avg_ratio_dual;            // w / (W + w) of the pending average update
+  double avg_ratio_old_x;    // Malitsky-Pock first-step extra term
+  double ratio_last_two_step_sizes;
+  double kkt_pass_limit, passes_per_rejected_step;
+  double reduction_exponent, growth_exponent;
+  double mp_downscaling, mp_contraction, mp_interpolation;
+  double mp_tau, mp_new_tau;  // Malitsky-Pock inner-loop scalars
+  double last_movement, last_nonlinearity;
+};
+
+// Iterate storage: double-buffered x, y, K^T y so an accepted trial is a flip of `cur`.
+struct Iterate {
+  DVec x[2], y[2], kty[2];
+  DVec xbar;
+  DVec avg_x, avg_y;
+  DVec x_start, y_start;       // last restart point
+  DeviceArray<StepState> state;
+  void Init(int64_t n, int64_t m);
+};
+
+// ---- setup (one-time per solve) ----
+struct VectorInfo {  // sharded_optimization_utils.cc:117-177 VectorInfoAccumulator
+  int64_t num_finite_nonzero = 0, num_infinite = 0, num_zero = 0;
+  double largest = 0, smallest = 0, average = 0, l2_norm = 0;
+};
+enum class InfoKind { kPlain, kCombinedBounds, kGap };
+// kPlain: a[i]; kCombinedBounds: CombineBounds(a[i], b[i]) (sou.cc:83-92); kGap: b[i]-a[i].
+VectorInfo ComputeVectorInfo(Workspace& ws, InfoKind kind, const double* a, const double* b, int64_t count);
+
+// sharded_quadratic_program.cc:119-130,169-175.
+void ReplaceLargeBoundsWithInfinity(Workspace& ws, double* clb, double* cub, int64_t m, double threshold);
+
+// Norms of the compressed rows of diag(idx_scale) M diag(row_scale) (sharder.cc:291-335):
+// l2 == false -> Linf, true -> L2.  out has s.rows entries.
+void ScaledRowNorms(Workspace& ws, const SparseRows& s, const double* idx_scale, const double* row_scale, bool l2, double* out);
+// v[i] /= sqrt(divisor[i]) where divisor[i] != 0 (sou.cc:354-365).
+void DivideBySqrtOfDivisor(Workspace& ws, const double* divisor, double* v, int64_t count);
+void FillVector(Workspace& ws, double* v, int64_t count, double value);
+// val[k] *= idx_scale[idx[k]] * row_scale[row] (sharded_quadratic_program.cc:97-117).
+void ScaleMatrixValues(Workspace& ws, SparseRows& s, const double* idx_scale, const double* row_scale);
+// sharded_quadratic_program.cc:134-167 vector part.
+void ScaleProblemVectors(Workspace& ws, DeviceProblem& p, const double* col_scale, const double* row_scale);
+// sou.cc:721-750.
+void ProjectToPrimalBounds(Workspace& ws, const DeviceProblem& p, double* x);
+void ProjectToDualBounds(Workspace& ws, const DeviceProblem& p, double* y);
+void DivideInPlace(Workspace& ws, double* v, const double* divisor, int64_t count);
+void MultiplyInPlace(Workspace& ws, double* v, const double* factor, int64_t count);
+void CopyVector(Workspace& ws, double* dst, const double* src, int64_t count);
+// dst = a - b.
+void SubtractVectors(Workspace& ws, double* dst, const double* a, const double* b, int64_t count);
+// NaN / magnitude screen of an initial solution: out = {sum of squares, max |v|}.
+void NormAndMax(Workspace& ws, const double* v, int64_t count, double* l2, double* linf);
+
+// out = M v by rows (K^T y with the CSC copy, K x with the CSR copy); sharder.cc:163-176.
+void RowDot(Workspace& ws, const SparseRows& s, const double* v, double* out);
+
+// ---- the iteration (primal_dual_hybrid_gradient.cc:2295-2376 and :2378-2406) ----
+// Enqueues `trials` trial steps of the adaptive (or constant) rule; no host sync.
+void EnqueueAdaptiveTrials(Workspace& ws, const DeviceProblem& p, Iterate& it, int trials, bool constant_step);
+// Malitsky-Pock (primal_dual_hybrid_gradient.cc:2211-2293): `trials` dual trials.
+void EnqueueMalitskyPockTrials(Workspace& ws, const DeviceProblem& p, Iterate& it, int trials);
+
+// ---- termination statistics (iteration_stats.cc:66-518, pdhg.cc:1343-1412) ----
+struct KktTotals {
+  // dual side (rows)
+  double primal_res_sumsq, primal_res_linf, primal_res_cw, dual_bounds_term, y_linf, y_sumsq, primal_res_linf_homogeneous;
+  double active_dual_count, active_dual_change;
+  // primal side (columns)
+  double c_dot_x, x_q_x, correction, full_correction, dual_res_linf, dual_res_sumsq, dual_res_cw, x_linf, x_sumsq;
+  double ray_correction, ray_dual_res_linf, sign_violation, qx_linf, active_primal_count, active_primal_change;
+};
+// One K x pass and one K^T y pass produce every reduction ComputeConvergenceInformation
+// and ComputeInfeasibilityInformation need for the point (x, y).
+KktTotals ComputeKktTotals(Workspace& ws, const DeviceProblem& p, const double* x, const double* y, const double* x_start, const double* y_start,
+                           double cw_primal_offset, double cw_dual_offset, bool handle_some_primal_gradients_on_finite_bounds_as_residuals);
+// iteration_stats.cc:533-565; rc must not alias x.
+void ComputeReducedCosts(Workspace& ws, const DeviceProblem& p, const double* x, const double* y, bool zero_objective,
+                         bool handle_some_primal_gradients_on_finite_bounds_as_residuals, double* rc);
+
+// ---- restarts (trust_region.cc:886-1016, sou.cc:446-527) ----
+double SquaredDistance(Workspace& ws, const double* a, const double* b, int64_t count);
+struct LocalizedBounds { double lagrangian_value, lower_bound, upper_bound, radius; };
+// Euclidean-norm localized Lagrangian bounds at (x, y).  kty may be null (computed).
+LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProblem& p, const double* x, const double* y, const double* kty_or_null,
+                                                 double primal_weight, double radius, bool use_diagonal_qp_solver, double diagonal_qp_tolerance,
+                                                 int* tr_passes);
+
+}  // namespace pdlp_b200
+#endif  // PDLP_B200_OPS_CUH_

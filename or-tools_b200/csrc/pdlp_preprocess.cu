@@ -1,0 +1,420 @@
+// PreprocessSolver: upload, bound clean-up, statistics, input screening, rescaling, the
+// initial step size / primal weight, termination checks and result construction.
+//   follows ortools/pdlp/primal_dual_hybrid_gradient.cc:711-1105, 1204-1286, 1414-1643.
+// Glop presolve (:1107-1202) is host-only and not part of this path.
+#include <random>
+
+#include "pdlp_driver.h"
+
+namespace pdlp_b200 {
+
+namespace {
+
+std::string SixDigits(double v) {
+  char b[64];
+  std::snprintf(b, sizeof b, "%g", v);
+  return b;
+}
+
+// pdhg.cc:731-897 (the log warnings are dropped; every rejection is kept).
+std::optional<SolverResult> CheckProblemStats(const QuadraticProgramStats& s, bool check_excessively_small_values) {
+  const double kBig = 1e50, kSmall = 1e-50;
+  auto err = [](const std::string& m) { return ErrorSolverResult(TERMINATION_REASON_INVALID_PROBLEM, m); };
+  if (std::isnan(s.constraint_matrix_l2_norm.get())) return err("Constraint matrix has a NAN.");
+  if (s.constraint_matrix_abs_max > kBig)
+    return err("Constraint matrix has a non-zero with absolute value " + SixDigits(s.constraint_matrix_abs_max) + " which exceeds limit of " + SixDigits(kBig) + ".");
+  if (s.constraint_matrix_col_min_l_inf_norm > 0 && s.constraint_matrix_col_min_l_inf_norm < kSmall)
+    return err("Constraint matrix has a column with Linf norm " + SixDigits(s.constraint_matrix_col_min_l_inf_norm) + " which is less than limit of " + SixDigits(kSmall) + ".");
+  if (s.constraint_matrix_row_min_l_inf_norm > 0 && s.constraint_matrix_row_min_l_inf_norm < kSmall)
+    return err("Constraint matrix has a row with Linf norm " + SixDigits(s.constraint_matrix_row_min_l_inf_norm) + " which is less than limit of " + SixDigits(kSmall) + ".");
+  if (std::isnan(s.combined_bounds_l2_norm.get())) return err("Constraint bounds vector has a NAN.");
+  if (s.combined_bounds_max > kBig)
+    return err("Combined constraint bounds vector has a non-zero with absolute value " + SixDigits(s.combined_bounds_max) + " which exceeds limit of " + SixDigits(kBig) + ".");
+  if (check_excessively_small_values && s.combined_bounds_min > 0 && s.combined_bounds_min < kSmall)
+    return err("Combined constraint bounds vector has a non-zero with absolute value " + SixDigits(s.combined_bounds_min) + " which is less than the limit of " + SixDigits(kSmall) + ".");
+  if (std::isnan(s.combined_variable_bounds_l2_norm.get())) return err("Variable bounds vector has a NAN.");
+  if (s.combined_variable_bounds_max > kBig)
+    return err("Combined variable bounds vector has a non-zero with absolute value " + SixDigits(s.combined_variable_bounds_max) + " which exceeds limit of " + SixDigits(kBig) + ".");
+  if (check_excessively_small_values && s.combined_variable_bounds_min > 0 && s.combined_variable_bounds_min < kSmall)
+    return err("Combined variable bounds vector has a non-zero with absolute value " + SixDigits(s.combined_variable_bounds_min) + " which is less than the limit of " + SixDigits(kSmall) + ".");
+  if (std::isnan(s.objective_vector_l2_norm.get())) return err("Objective vector has a NAN.");
+  if (s.objective_vector_abs_max > kBig)
+    return err("Objective vector has a non-zero with absolute value " + SixDigits(s.objective_vector_abs_max) + " which exceeds limit of " + SixDigits(kBig) + ".");
+  if (check_excessively_small_values && s.objective_vector_abs_min > 0 && s.objective_vector_abs_min < kSmall)
+    return err("Objective vector has a non-zero with absolute value " + SixDigits(s.objective_vector_abs_min) + " which is less than the limit of " + SixDigits(kSmall) + ".");
+  if (std::isnan(s.objective_matrix_l2_norm.get())) return err("Objective matrix has a NAN.");
+  if (s.objective_matrix_abs_max > kBig)
+    return err("Objective matrix has a non-zero with absolute value " + SixDigits(s.objective_matrix_abs_max) + " which exceeds limit of " + SixDigits(kBig) + ".");
+  return std::nullopt;
+}
+
+}  // namespace
+
+SolverResult ErrorSolverResult(int reason, const std::string& message) {
+  SolverResult r;
+  r.solve_log.termination_reason = reason;
+  r.solve_log.termination_string = message;
+  return r;
+}
+
+PreprocessSolver::PreprocessSolver(const QpView& qp, const PrimalDualHybridGradientParams& params) : view_(qp) {
+  // num_threads / num_shards (pdhg.cc:71-96) configure the reference's CPU thread pool;
+  // the device path accepts and ignores them.
+  ws_.Init(qp.n, qp.m);
+  problem_.n = qp.n;
+  problem_.m = qp.m;
+  problem_.is_lp = qp.q == nullptr;
+  problem_.objective_offset = qp.objective_offset;
+  problem_.objective_scaling_factor = qp.objective_scaling_factor;
+  BuildDeviceMatrix(qp.n, qp.m, qp.nnz, qp.col_ptr, qp.row_idx, qp.val, ws_.stream, &problem_.K);
+  auto up = [&](DVec& d, const double* h, int64_t count) {
+    d.Resize(count > 0 ? count : 1);
+    d.Upload(h, count, ws_.stream);
+  };
+  up(problem_.c, qp.c, qp.n);
+  if (!problem_.is_lp) up(problem_.q, qp.q, qp.n);
+  up(problem_.vlb, qp.vlb, qp.n);
+  up(problem_.vub, qp.vub, qp.n);
+  up(problem_.clb, qp.clb, qp.m);
+  up(problem_.cub, qp.cub, qp.m);
+  problem_.col_scale.Resize(qp.n > 0 ? qp.n : 1);
+  problem_.row_scale.Resize(qp.m > 0 ? qp.m : 1);
+  FillVector(ws_, problem_.col_scale.get(), qp.n, 1.0);
+  FillVector(ws_, problem_.row_scale.get(), qp.m, 1.0);
+  seeds_ = params.random_projection_seeds.v;
+  ws_.Sync();
+}
+
+PreprocessSolver::~PreprocessSolver() { ws_.Destroy(); }
+
+// sharded_optimization_utils.cc:270-343.
+QuadraticProgramStats PreprocessSolver::ComputeStats() {
+  DeviceProblem& p = problem_;
+  QuadraticProgramStats s;
+  // Row / column Linf norms with unit scaling (ones live in scratch).
+  double* ones_n = ws_.scratch_n[1].get();
+  double* ones_m = ws_.scratch_m[1].get();
+  FillVector(ws_, ones_n, p.n, 1.0);
+  FillVector(ws_, ones_m, p.m, 1.0);
+  double* row_norms = ws_.scratch_m[2].get();
+  double* col_norms = ws_.scratch_n[2].get();
+  ScaledRowNorms(ws_, p.K.by_row, ones_n, ones_m, false, row_norms);
+  ScaledRowNorms(ws_, p.K.by_col, ones_m, ones_n, false, col_norms);
+  const VectorInfo rn = ComputeVectorInfo(ws_, InfoKind::kPlain, row_norms, nullptr, p.m);
+  const VectorInfo cn = ComputeVectorInfo(ws_, InfoKind::kPlain, col_norms, nullptr, p.n);
+  const VectorInfo mat = ComputeVectorInfo(ws_, InfoKind::kPlain, p.K.by_col.val.get(), nullptr, p.K.by_col.nnz);
+  const VectorInfo cb = ComputeVectorInfo(ws_, InfoKind::kCombinedBounds, p.cub.get(), p.clb.get(), p.m);
+  const VectorInfo vb = ComputeVectorInfo(ws_, InfoKind::kCombinedBounds, p.vub.get(), p.vlb.get(), p.n);
+  const VectorInfo ov = ComputeVectorInfo(ws_, InfoKind::kPlain, p.c.get(), nullptr, p.n);
+  const VectorInfo gaps = ComputeVectorInfo(ws_, InfoKind::kGap, p.vlb.get(), p.vub.get(), p.n);
+  s.num_variables = p.n;
+  s.num_constraints = p.m;
+  s.constraint_matrix_col_min_l_inf_norm = cn.smallest;
+  s.constraint_matrix_row_min_l_inf_norm = rn.smallest;
+  s.constraint_matrix_num_nonzeros = mat.num_finite_nonzero;
+  s.constraint_matrix_abs_max = mat.largest;
+  s.constraint_matrix_abs_min = mat.smallest;
+  s.constraint_matrix_abs_avg = mat.average;
+  s.constraint_matrix_l2_norm = mat.l2_norm;
+  s.combined_bounds_max = cb.largest;
+  s.combined_bounds_min = cb.smallest;
+  s.combined_bounds_avg = cb.average;
+  s.combined_bounds_l2_norm = cb.l2_norm;
+  s.combined_variable_bounds_max = vb.largest;
+  s.combined_variable_bounds_min = vb.smallest;
+  s.combined_variable_bounds_avg = vb.average;
+  s.combined_variable_bounds_l2_norm = vb.l2_norm;
+  s.variable_bound_gaps_num_finite = gaps.num_finite_nonzero + gaps.num_zero;
+  s.variable_bound_gaps_max = gaps.largest;
+  s.variable_bound_gaps_min = gaps.smallest;
+  s.variable_bound_gaps_avg = gaps.average;
+  s.variable_bound_gaps_l2_norm = gaps.l2_norm;
+  s.objective_vector_abs_max = ov.largest;
+  s.objective_vector_abs_min = ov.smallest;
+  s.objective_vector_abs_avg = ov.average;
+  s.objective_vector_l2_norm = ov.l2_norm;
+  if (p.is_lp) {
+    s.objective_matrix_num_nonzeros = 0;
+    s.objective_matrix_abs_max = 0;
+    s.objective_matrix_abs_min = 0;
+    s.objective_matrix_abs_avg = std::numeric_limits<double>::quiet_NaN();
+    s.objective_matrix_l2_norm = 0;
+  } else {
+    const VectorInfo om = ComputeVectorInfo(ws_, InfoKind::kPlain, p.q.get(), nullptr, p.n);
+    s.objective_matrix_num_nonzeros = om.num_finite_nonzero;
+    s.objective_matrix_abs_max = om.largest;
+    s.objective_matrix_abs_min = om.smallest;
+    s.objective_matrix_abs_avg = om.average;
+    s.objective_matrix_l2_norm = om.l2_norm;
+  }
+  return s;
+}
+
+// sharded_optimization_utils.cc:367-444 + sharded_quadratic_program.cc:134-167.
+void PreprocessSolver::ApplyRescaling(const PrimalDualHybridGradientParams& params) {
+  DeviceProblem& p = problem_;
+  double* row = p.row_scale.get();
+  double* col = p.col_scale.get();
+  double* col_norm = ws_.scratch_n[2].get();
+  double* row_norm = ws_.scratch_m[2].get();
+  auto iteration = [&](bool l2) {
+    ScaledRowNorms(ws_, p.K.by_col, row, col, l2, col_norm);
+    ScaledRowNorms(ws_, p.K.by_row, col, row, l2, row_norm);
+    DivideBySqrtOfDivisor(ws_, col_norm, col, p.n);
+    DivideBySqrtOfDivisor(ws_, row_norm, row, p.m);
+  };
+  bool any = false;
+  for (int i = 0; i < params.l_inf_ruiz_iterations; ++i) { iteration(false); any = true; }
+  if (params.l2_norm_rescaling) { iteration(true); any = true; }
+  if (any) {
+    ScaleProblemVectors(ws_, p, col, row);
+    ScaleMatrixValues(ws_, p.K.by_col, row, col);
+    ScaleMatrixValues(ws_, p.K.by_row, col, row);
+  }
+}
+
+// pdhg.cc:949-1105.
+SolverResult PreprocessSolver::PreprocessAndSolve(const PrimalDualHybridGradientParams& params, const double* x0, const double* y0,
+                                                  const InterruptFlag* interrupt, IterationCallback callback) {
+  WallTimer timer;
+  timer.Start();
+  SolveLog log;
+  if (view_.name != nullptr) log.instance_name = std::string(view_.name);
+  log.params.mut() = params;
+  DeviceProblem& p = problem_;
+  ReplaceLargeBoundsWithInfinity(ws_, p.clb.get(), p.cub.get(), p.m, params.infinite_constraint_bound_threshold);
+  log.original_problem_stats.mut() = ComputeStats();
+  if (auto r = CheckProblemStats(log.original_problem_stats.get(), params.presolve_options->use_glop); r.has_value()) return *r;
+
+  // Starting point (pdhg.cc:1035-1048).  The size checks of CheckInitialSolution
+  // (:899-947) happen at the API boundary where the sizes are known.
+  DVec x_start(p.n > 0 ? p.n : 1), y_start(p.m > 0 ? p.m : 1);
+  if (x0 != nullptr && y0 != nullptr) {
+    x_start.Upload(x0, p.n, ws_.stream);
+    y_start.Upload(y0, p.m, ws_.stream);
+    const double kBig = 1e50;
+    double l2 = 0, linf = 0;
+    NormAndMax(ws_, x_start.get(), p.n, &l2, &linf);
+    if (std::isnan(l2)) return ErrorSolverResult(TERMINATION_REASON_INVALID_INITIAL_SOLUTION, "Initial primal solution has a NAN.");
+    if (linf > kBig)
+      return ErrorSolverResult(TERMINATION_REASON_INVALID_INITIAL_SOLUTION,
+                               "Initial primal solution has an entry with absolute value " + SixDigits(linf) + " which exceeds limit of " + SixDigits(kBig));
+    NormAndMax(ws_, y_start.get(), p.m, &l2, &linf);
+    if (std::isnan(l2)) return ErrorSolverResult(TERMINATION_REASON_INVALID_INITIAL_SOLUTION, "Initial dual solution has a NAN.");
+    if (linf > kBig)
+      return ErrorSolverResult(TERMINATION_REASON_INVALID_INITIAL_SOLUTION,
+                               "Initial dual solution has an entry with absolute value " + SixDigits(linf) + " which exceeds limit of " + SixDigits(kBig));
+  } else {
+    x_start.Zero(ws_.stream);
+    y_start.Zero(ws_.stream);
+  }
+  original_bound_norms_ = BoundNormsFromProblemStats(log.original_problem_stats.get());
+  callback_ = std::move(callback);
+
+  ProjectToPrimalBounds(ws_, p, x_start.get());
+  ProjectToDualBounds(ws_, p, y_start.get());
+
+  ApplyRescaling(params);  // pdhg.cc:1204-1218
+  DivideInPlace(ws_, x_start.get(), p.col_scale.get(), p.n);
+  DivideInPlace(ws_, y_start.get(), p.row_scale.get(), p.m);
+  log.preprocessed_problem_stats.mut() = ComputeStats();
+
+  double step_size = 0.0;
+  if (params.linesearch_rule == CONSTANT_STEP_SIZE_RULE) {
+    // pdhg.cc:1060-1076 + sou.cc:536-699 (power method on K^T K, 2 SpMV per round).
+    // parity unpinned for the exact estimate: the reference draws its start vector with
+    // absl::Gaussian(mt19937(1)), whose algorithm is not in the reference tree.
+    const double desired_relative_error = 0.2, failure_probability = 0.0005;
+    std::mt19937 random(1);
+    std::normal_distribution<double> gauss(0.0, 1.0);
+    std::vector<double> start(p.n);
+    for (double& v : start) v = gauss(random);
+    double* ev = ws_.scratch_n[0].get();
+    double* next = ws_.scratch_n[1].get();
+    double* dual_ev = ws_.scratch_m[0].get();
+    ws_.scratch_n[0].Upload(start.data(), p.n, ws_.stream);
+    auto normalize = [&](double* v) {
+      double l2 = 0, linf = 0;
+      NormAndMax(ws_, v, p.n, &l2, &linf);
+      if (l2 != 0.0) {
+        FillVector(ws_, ws_.scratch_n[2].get(), p.n, l2);
+        DivideInPlace(ws_, v, ws_.scratch_n[2].get(), p.n);
+      }
+    };
+    normalize(ev);
+    const double eps = 1.0 - (1.0 - desired_relative_error) * (1.0 - desired_relative_error);
+    auto fail_prob = [&](int k) {
+      if (k < 2 || eps <= 0.0) return 1.0;
+      return std::min(0.824, 0.354 / std::sqrt(eps * (k - 1))) * std::sqrt(static_cast<double>(p.n)) * std::pow(1.0 - eps, k - 0.5);
+    };
+    double estimate = 0.0;
+    int iters = 0;
+    while (fail_prob(iters) > failure_probability) {
+      RowDot(ws_, p.K.by_row, ev, dual_ev);
+      RowDot(ws_, p.K.by_col, dual_ev, next);
+      // estimate = ev . next = |K ev|^2
+      double l2 = 0, linf = 0;
+      NormAndMax(ws_, dual_ev, p.m, &l2, &linf);
+      estimate = l2 * l2;
+      CopyVector(ws_, ev, next, p.n);
+      ++iters;
+      normalize(ev);
+    }
+    const double singular_value = std::sqrt(estimate);
+    const double inverse_step_lower_bound = singular_value / (1.0 - desired_relative_error);
+    step_size = inverse_step_lower_bound > 0.0 ? 1.0 / inverse_step_lower_bound : 1.0;
+  } else {
+    step_size = 1.0 / std::max(1.0e-20, log.preprocessed_problem_stats->constraint_matrix_abs_max.get());
+  }
+  step_size *= params.initial_step_size_scaling;
+
+  // InitialPrimalWeight, pdhg.cc:1268-1286.
+  double primal_weight = 1.0;
+  const double c_norm = log.preprocessed_problem_stats->objective_vector_l2_norm;
+  const double b_norm = log.preprocessed_problem_stats->combined_bounds_l2_norm;
+  if (params.initial_primal_weight.has) primal_weight = params.initial_primal_weight;
+  else if (c_norm > 0.0 && b_norm > 0.0) primal_weight = c_norm / b_norm;
+
+  Solver solver(params, x_start.get(), y_start.get(), step_size, primal_weight, this);
+  log.preprocessing_time_sec = timer.Get();
+  Solver::Outcome outcome = solver.Solve(IterationType::kNormal, interrupt, std::move(log));
+  SolverResult result = ConstructOriginalSolverResult(params, outcome.x, outcome.y, std::move(outcome.log));
+  // Counters for benchmarks.
+  g_last_counters.kernel_launches = ws_.launches;
+  g_last_counters.trial_steps = solver.TrialSteps();
+  g_last_counters.device_loop_seconds = solver.DeviceLoopSeconds();
+  g_last_counters.setup_seconds = result.solve_log.preprocessing_time_sec;
+  g_last_counters.loop_seconds = result.solve_log.solve_time_sec - result.solve_log.preprocessing_time_sec;
+  return result;
+}
+
+// pdhg.cc:1520-1564 + iteration_stats.cc:349-518, assembled from the fused totals.
+void PreprocessSolver::ComputeConvergenceAndInfeasibility(const PrimalDualHybridGradientParams& params, const double* x, const double* y,
+                                                          const double* x_start, const double* y_start, int candidate_type,
+                                                          ConvergenceInformation* ci, InfeasibilityInformation* ii, PointMetadata* md) {
+  const DetailedOptimalityCriteria oc = EffectiveOptimalityCriteria(params.termination_criteria.get());
+  const double primal_ratio = EpsilonRatio(oc.eps_optimal_primal_residual_absolute, oc.eps_optimal_primal_residual_relative);
+  const double dual_ratio = EpsilonRatio(oc.eps_optimal_dual_residual_absolute, oc.eps_optimal_dual_residual_relative);
+  const KktTotals t = ComputeKktTotals(ws_, problem_, x, y, x_start, y_start, primal_ratio, dual_ratio,
+                                       params.handle_some_primal_gradients_on_finite_bounds_as_residuals);
+  auto apply = [&](double v) { return problem_.objective_scaling_factor * (v + problem_.objective_offset); };
+  if (ci != nullptr) {
+    ci->l_inf_primal_residual = t.primal_res_linf;
+    ci->l2_primal_residual = std::sqrt(t.primal_res_sumsq);
+    ci->l_inf_componentwise_primal_residual = t.primal_res_cw;
+    ci->l_inf_primal_variable = t.x_linf;
+    ci->l2_primal_variable = std::sqrt(t.x_sumsq);
+    ci->l_inf_dual_variable = t.y_linf;
+    ci->l2_dual_variable = std::sqrt(t.y_sumsq);
+    const double quad = problem_.is_lp ? 0.0 : 0.5 * t.x_q_x;
+    ci->primal_objective = apply(quad + t.c_dot_x);
+    const double dual_piece = -quad + t.dual_bounds_term;
+    ci->dual_objective = apply(dual_piece + t.correction);
+    ci->corrected_dual_objective = apply(dual_piece + t.full_correction);
+    ci->l_inf_dual_residual = t.dual_res_linf;
+    ci->l2_dual_residual = std::sqrt(t.dual_res_sumsq);
+    ci->l_inf_componentwise_dual_residual = t.dual_res_cw;
+    ci->candidate_type = candidate_type;
+  }
+  if (ii != nullptr) {
+    const double linf_primal = t.x_linf, linf_dual = t.y_linf;
+    ii->max_primal_ray_infeasibility = 0.0; ii->primal_ray_linear_objective = 0.0; ii->primal_ray_quadratic_norm = 0.0;
+    ii->max_dual_ray_infeasibility = 0.0; ii->dual_ray_objective = 0.0;
+    const double dual_ray_objective = t.dual_bounds_term + t.ray_correction;
+    if (linf_dual > 0) {
+      ii->dual_ray_objective = dual_ray_objective / linf_dual;
+      ii->max_dual_ray_infeasibility = t.ray_dual_res_linf / linf_dual;
+    }
+    if (linf_primal > 0.0) {
+      ii->primal_ray_quadratic_norm = t.qx_linf / linf_primal;
+      ii->max_primal_ray_infeasibility = std::max(t.primal_res_linf_homogeneous, t.sign_violation) / linf_primal;
+      ii->primal_ray_linear_objective = t.c_dot_x / linf_primal;
+    }
+    ii->candidate_type = candidate_type;
+  }
+  if (md != nullptr) {
+    md->point_type = candidate_type;
+    if (candidate_type != POINT_TYPE_ITERATE_DIFFERENCE) {  // pdhg.cc:1343-1412
+      md->active_primal_variable_count = static_cast<int64_t>(t.active_primal_count);
+      md->active_dual_variable_count = static_cast<int64_t>(t.active_dual_count);
+      md->active_primal_variable_change = static_cast<int64_t>(t.active_primal_change);
+      md->active_dual_variable_change = static_cast<int64_t>(t.active_dual_change);
+    }
+    if (!seeds_.empty()) AddRandomProjections(x, y, md);
+  }
+}
+
+// iteration_stats.cc:321-346,598-610.  Rarely used diagnostics: computed on the host
+// from a copy of the point.  parity unpinned (absl::Gaussian; depends on the shard count
+// by design, solvers.proto:397-403): one shard is used here.
+void PreprocessSolver::AddRandomProjections(const double* x, const double* y, PointMetadata* md) {
+  std::vector<double> hx(problem_.n), hy(problem_.m);
+  if (problem_.n > 0) PDLP_CUDA_CHECK(cudaMemcpyAsync(hx.data(), x, problem_.n * sizeof(double), cudaMemcpyDeviceToHost, ws_.stream));
+  if (problem_.m > 0) PDLP_CUDA_CHECK(cudaMemcpyAsync(hy.data(), y, problem_.m * sizeof(double), cudaMemcpyDeviceToHost, ws_.stream));
+  ws_.Sync();
+  auto project = [](const std::vector<double>& v, std::mt19937& seed_gen) {
+    std::mt19937 rnd(seed_gen());
+    std::normal_distribution<double> gauss(0.0, 1.0);
+    double d = 0, n2 = 0;
+    for (double e : v) { const double g = gauss(rnd); d += g * e; n2 += g * g; }
+    return d / std::sqrt(n2);
+  };
+  for (int32_t seed : seeds_) {
+    std::mt19937 gen(seed);
+    md->random_primal_projections.v.push_back(project(hx, gen));
+    md->random_dual_projections.v.push_back(project(hy, gen));
+  }
+}
+
+// pdhg.cc:1434-1518 (text logging not restated).
+std::optional<TerminationReasonAndPointType> PreprocessSolver::UpdateIterationStatsAndCheckTermination(
+    const PrimalDualHybridGradientParams& params, bool force_numerical_termination, const double* x_cur, const double* y_cur, const double* x_avg,
+    const double* y_avg, const double* dx, const double* dy, const double* x_start, const double* y_start, const InterruptFlag* interrupt,
+    IterationType type, const IterationStats& full_stats, IterationStats& stats) {
+  auto add_point = [&](const double* x, const double* y, int point_type, bool convergence) {
+    ConvergenceInformation ci;
+    InfeasibilityInformation ii;
+    PointMetadata md;
+    ComputeConvergenceAndInfeasibility(params, x, y, x_start, y_start, point_type, convergence ? &ci : nullptr, &ii, &md);
+    if (convergence) stats.convergence_information.push_back(ci);
+    stats.infeasibility_information.push_back(ii);
+    stats.point_metadata.push_back(md);
+  };
+  add_point(x_cur, y_cur, POINT_TYPE_CURRENT_ITERATE, true);
+  if (x_avg != nullptr && y_avg != nullptr) add_point(x_avg, y_avg, POINT_TYPE_AVERAGE_ITERATE, true);
+  if (dx != nullptr && dy != nullptr) add_point(dx, dy, POINT_TYPE_ITERATE_DIFFERENCE, false);
+  if (callback_) callback_(IterationCallbackInfo{type, params.termination_criteria.get(), stats, original_bound_norms_});
+  if (auto t = CheckIterateTerminationCriteria(params.termination_criteria.get(), stats, original_bound_norms_, force_numerical_termination); t.has_value()) return t;
+  return CheckSimpleTerminationCriteria(params.termination_criteria.get(), full_stats, interrupt);
+}
+
+// pdhg.cc:1568-1643.
+SolverResult PreprocessSolver::ConstructOriginalSolverResult(const PrimalDualHybridGradientParams& params, const double* x, const double* y, SolveLog log) {
+  DeviceProblem& p = problem_;
+  SolverResult result;
+  const bool zero_objective = log.termination_reason == TERMINATION_REASON_PRIMAL_INFEASIBLE;
+  double* out_x = ws_.scratch_n[0].get();
+  double* out_rc = ws_.scratch_n[1].get();
+  double* out_y = ws_.scratch_m[0].get();
+  ComputeReducedCosts(ws_, p, x, y, zero_objective, params.handle_some_primal_gradients_on_finite_bounds_as_residuals, out_rc);
+  CopyVector(ws_, out_x, x, p.n);
+  CopyVector(ws_, out_y, y, p.m);
+  MultiplyInPlace(ws_, out_x, p.col_scale.get(), p.n);
+  MultiplyInPlace(ws_, out_y, p.row_scale.get(), p.m);
+  DivideInPlace(ws_, out_rc, p.col_scale.get(), p.n);
+  result.primal_solution.resize(p.n);
+  result.dual_solution.resize(p.m);
+  result.reduced_costs.resize(p.n);
+  if (p.n > 0) PDLP_CUDA_CHECK(cudaMemcpyAsync(result.primal_solution.data(), out_x, p.n * sizeof(double), cudaMemcpyDeviceToHost, ws_.stream));
+  if (p.n > 0) PDLP_CUDA_CHECK(cudaMemcpyAsync(result.reduced_costs.data(), out_rc, p.n * sizeof(double), cudaMemcpyDeviceToHost, ws_.stream));
+  if (p.m > 0) PDLP_CUDA_CHECK(cudaMemcpyAsync(result.dual_solution.data(), out_y, p.m * sizeof(double), cudaMemcpyDeviceToHost, ws_.stream));
+  ws_.Sync();
+  IterationType type = IterationType::kNormalTermination;
+  if (log.solution_type == POINT_TYPE_FEASIBILITY_POLISHING_SOLUTION) type = IterationType::kFeasibilityPolishingTermination;
+  else if (log.solution_type == POINT_TYPE_PRESOLVER_SOLUTION) type = IterationType::kPresolveTermination;
+  if (callback_) callback_(IterationCallbackInfo{type, params.termination_criteria.get(), log.solution_stats.get(), original_bound_norms_});
+  result.solve_log = std::move(log);
+  return result;
+}
+
+}  // namespace pdlp_b200

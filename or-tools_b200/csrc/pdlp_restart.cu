@@ -1,0 +1,261 @@
+// Restart-decision numerics on the device: Lagrangian gradients
+// (ortools/pdlp/sharded_optimization_utils.cc:446-527) and the Euclidean-norm localized
+// Lagrangian bounds (ortools/pdlp/trust_region.cc:886-1016) with the joint primal-dual
+// bound-constrained trust-region solve (trust_region.cc:332-449, trust_region.h:193-337).
+//
+// The reference finds the trust-region step by repeated median pivoting over shrinking
+// index lists.  That is sequential in nature; here the same step (it is the unique root
+// of a monotone function) is found by a monotone Newton iteration: with s = delta^2,
+//   g(s) = sum_i a_i min(s, s_i),  a_i = obj_i^2 / w_i,  s_i = (critical step)_i^2
+// is concave, increasing and piecewise linear, so Newton from the left never overshoots
+// and lands exactly on the root once no further breakpoint is crossed.  Each Newton step
+// is one deterministic reduction pass over the n + m critical step sizes.
+#include <cfloat>
+
+#include "pdlp_launch.cuh"
+
+namespace pdlp_b200 {
+
+namespace {
+
+// The joint problem of trust_region.cc:886-974 (JointTrustRegionProblem).
+struct JointView {
+  const double* gx; const double* gy; const double* x; const double* y;
+  const double* vlb; const double* vub; const double* clb; const double* cub; const double* q;
+  int64_t n; double w_primal, w_dual;
+  __device__ double Objective(int64_t i) const { return i < n ? gx[i] : -gy[i - n]; }
+  __device__ double LowerBound(int64_t i) const { return i < n ? vlb[i] : (isfinite(cub[i - n]) ? -INFINITY : 0.0); }
+  __device__ double UpperBound(int64_t i) const { return i < n ? vub[i] : (isfinite(clb[i - n]) ? INFINITY : 0.0); }
+  __device__ double Center(int64_t i) const { return i < n ? x[i] : y[i - n]; }
+  __device__ double Weight(int64_t i) const { return i < n ? w_primal : w_dual; }
+  __device__ double Diagonal(int64_t i) const { return (q != nullptr && i < n) ? q[i] : 0.0; }
+  // trust_region.h:193-228.
+  __device__ double ProjectedValue(int64_t i, double step) const {
+    const double full = Center(i) - step * Objective(i) / Weight(i);
+    return fmin(fmax(full, LowerBound(i)), UpperBound(i));
+  }
+};
+
+// sou.cc:476-500.
+__device__ __forceinline__ double DualSubgradientCoefficient(double lb, double ub, double dual, double primal_product) {
+  if (dual < 0.0) return ub;
+  if (dual > 0.0) return lb;
+  if (isfinite(lb) && isfinite(ub)) {
+    if (primal_product < lb) return lb;
+    if (primal_product > ub) return ub;
+    return primal_product;
+  }
+  if (isfinite(lb)) return lb;
+  if (isfinite(ub)) return ub;
+  return 0.0;
+}
+
+struct OneSumSlot {
+  static constexpr int kNumSlots = 1;
+  __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
+};
+
+// ComputeDualGradient (sou.cc:502-527) fused with K x.
+struct DualGradOp : AlwaysActive, OneSumSlot {
+  const double* val; const int* idx; const double* x;
+  const double* y; const double* clb; const double* cub; double* gy;
+  __device__ double Load(int64_t k) const { return val[k] * x[idx[k]]; }
+  __device__ double RowInit() const { return 0.0; }
+  __device__ double RowAdd(double acc, double staged, int) const { return acc + staged; }
+  __device__ double RowMerge(double a, double b) const { return a + b; }
+  __device__ void RowFinish(int i, double kx, Slots<1>& r) const {
+    const double coeff = DualSubgradientCoefficient(clb[i], cub[i], y[i], kx);
+    r.v[0] += coeff * y[i];
+    gy[i] = coeff - kx;
+  }
+};
+
+// ComputePrimalGradient (sou.cc:446-474).
+__device__ __forceinline__ double PrimalGradAt(double xj, double cj, const double* q, int64_t j, double kty, double* value) {
+  if (q == nullptr) {
+    const double g = cj - kty;
+    *value = xj * g;
+    return g;
+  }
+  const double qx = q[j] * xj;
+  const double g = cj + qx - kty;
+  *value = xj * (g - 0.5 * qx);
+  return g;
+}
+struct PrimalGradRowsOp : AlwaysActive, OneSumSlot {  // K^T y computed here
+  const double* val; const int* idx; const double* y;
+  const double* x; const double* c; const double* q; double* gx;
+  __device__ double Load(int64_t k) const { return val[k] * y[idx[k]]; }
+  __device__ double RowInit() const { return 0.0; }
+  __device__ double RowAdd(double acc, double staged, int) const { return acc + staged; }
+  __device__ double RowMerge(double a, double b) const { return a + b; }
+  __device__ void RowFinish(int j, double kty, Slots<1>& r) const {
+    double v;
+    gx[j] = PrimalGradAt(x[j], c[j], q, j, kty, &v);
+    r.v[0] += v;
+  }
+};
+struct PrimalGradMapOp : AlwaysActive, OneSumSlot {  // K^T y cached
+  const double* kty; const double* x; const double* c; const double* q; double* gx;
+  __device__ void Apply(int64_t j, Slots<1>& r) const {
+    double v;
+    gx[j] = PrimalGradAt(x[j], c[j], q, j, kty[j], &v);
+    r.v[0] += v;
+  }
+};
+
+// Critical step sizes and radius coefficients.  Slots: max |objective| (any nonzero?).
+struct CriticalOp : AlwaysActive {
+  static constexpr int kNumSlots = 1;
+  __host__ __device__ static constexpr int SlotKindOf(int) { return kMax; }
+  JointView p; double* crit; double* coef;
+  __device__ void Apply(int64_t i, Slots<1>& r) const {
+    const double obj = p.Objective(i), w = p.Weight(i);
+    double cs = INFINITY;
+    if (obj != 0.0) {
+      const double dist = obj > 0.0 ? p.LowerBound(i) - p.Center(i) : p.UpperBound(i) - p.Center(i);
+      cs = -w * dist / obj;
+    }
+    crit[i] = cs;
+    coef[i] = obj * obj / w;
+    r.v[0] = fmax(r.v[0], fabs(obj));
+  }
+};
+
+// One Newton pass at step `delta`: fixed radius^2, free coefficient, number fixed.
+struct RadiusPassOp : AlwaysActive {
+  static constexpr int kNumSlots = 3;
+  __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
+  const double* crit; const double* coef; double delta;
+  __device__ void Apply(int64_t i, Slots<3>& r) const {
+    const double cs = crit[i], a = coef[i];
+    if (cs <= delta) { r.v[0] += a * (cs * cs); r.v[2] += 1.0; }
+    else r.v[1] += a;
+  }
+};
+
+// primal_delta / dual_delta of trust_region.cc:951-973 for the linear solver.
+struct BoundsDeltaOp : AlwaysActive {
+  static constexpr int kNumSlots = 2;
+  __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
+  JointView p; double step;
+  __device__ void Apply(int64_t i, Slots<2>& r) const {
+    const double sol = p.ProjectedValue(i, step);
+    if (i < p.n) r.v[0] += p.gx[i] * (sol - p.x[i]);
+    else r.v[1] += p.gy[i - p.n] * (sol - p.y[i - p.n]);
+  }
+};
+
+// Diagonal-QP solver pieces (trust_region.cc:615-753).
+__device__ __forceinline__ double ProjectedScaledDifference(const JointView& p, int64_t i, double scaling) {
+  const double w = p.Weight(i);
+  return fmin(fmax((-p.Objective(i) / sqrt(w)) / (p.Diagonal(i) / w + scaling), sqrt(w) * (p.LowerBound(i) - p.Center(i))),
+              sqrt(w) * (p.UpperBound(i) - p.Center(i)));
+}
+struct DeltaNormOp : AlwaysActive, OneSumSlot {
+  JointView p; double scaling;
+  __device__ void Apply(int64_t i, Slots<1>& r) const {
+    const double v = ProjectedScaledDifference(p, i, scaling);
+    r.v[0] += v * v;
+  }
+};
+struct DiagonalBoundsDeltaOp : AlwaysActive {
+  static constexpr int kNumSlots = 3;
+  __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
+  JointView p; double scaling; int at_center;
+  __device__ void Apply(int64_t i, Slots<3>& r) const {
+    const double c = p.Center(i);
+    const double sol = at_center ? c : c + sqrt(1.0 / p.Weight(i)) * ProjectedScaledDifference(p, i, scaling);
+    const double d = sol - c;
+    if (i < p.n) {
+      r.v[0] += p.gx[i] * d;
+      if (p.q != nullptr) r.v[2] += 0.5 * p.q[i] * (d * d);
+    } else {
+      r.v[1] += p.gy[i - p.n] * d;
+    }
+  }
+};
+
+}  // namespace
+
+LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProblem& p, const double* x, const double* y, const double* kty_or_null,
+                                                 double primal_weight, double radius, bool use_diagonal_qp_solver, double diagonal_qp_tolerance,
+                                                 int* tr_passes) {
+  const SparseRows& csr = p.K.by_row;
+  const SparseRows& csc = p.K.by_col;
+  double* gx = ws.scratch_n[0].get();
+  double* gy = ws.scratch_m[0].get();
+  double primal_value = 0.0, dual_value = 0.0;
+  if (p.m > 0) dual_value = RunRows(ws, DualGradOp{{}, {}, csr.val.get(), csr.idx.get(), x, y, p.clb.get(), p.cub.get(), gy}, csr)[0];
+  if (p.n > 0) {
+    if (kty_or_null != nullptr) primal_value = RunMap(ws, PrimalGradMapOp{{}, {}, kty_or_null, x, p.c.get(), p.q_or_null(), gx}, p.n)[0];
+    else primal_value = RunRows(ws, PrimalGradRowsOp{{}, {}, csc.val.get(), csc.idx.get(), y, x, p.c.get(), p.q_or_null(), gx}, csc)[0];
+  }
+  const double lagrangian = primal_value + dual_value;
+  const int64_t total = p.n + p.m;
+  JointView view{gx, gy, x, y, p.vlb.get(), p.vub.get(), p.clb.get(), p.cub.get(), p.q_or_null(), p.n, 0.5 * primal_weight, 0.5 / primal_weight};
+  int passes = 0;
+  LocalizedBounds out{lagrangian, lagrangian, lagrangian, radius};
+  if (total == 0) { if (tr_passes) *tr_passes = 0; return out; }
+
+  if (use_diagonal_qp_solver) {
+    double primal_delta = 0.0, dual_delta = 0.0;
+    if (radius == 0.0) {
+      // Solution is the centre point: both deltas are exactly zero.
+    } else {
+      auto norm_at = [&](double scaling) { ++passes; return std::sqrt(RunMap(ws, DeltaNormOp{{}, {}, view, scaling}, total)[0]); };
+      double lo = 0.0, hi = 1.0;  // FindScalingFactor, trust_region.cc:683-706
+      while (norm_at(hi) >= radius) { lo = hi; hi *= 2; }
+      while ((hi - lo) >= diagonal_qp_tolerance * std::max(1.0, lo)) {
+        const double mid = (lo + hi) / 2.0;
+        if (norm_at(mid) <= radius) hi = mid; else lo = mid;
+      }
+      const double scaling = (hi + lo) / 2.0;
+      const double* h = RunMap(ws, DiagonalBoundsDeltaOp{{}, view, scaling, 0}, total);
+      primal_delta = h[0] + (p.is_lp ? 0.0 : h[2]);
+      dual_delta = h[1];
+    }
+    out.lower_bound = lagrangian + primal_delta;
+    out.upper_bound = lagrangian + dual_delta;
+    if (tr_passes) *tr_passes = passes;
+    return out;
+  }
+
+  // SolveTrustRegionStepSize.
+  double step = 0.0;
+  if (radius > 0.0) {
+    double* crit = ws.scratch_nm[0].get();
+    double* coef = ws.scratch_nm[1].get();
+    const double max_obj = RunMap(ws, CriticalOp{{}, view, crit, coef}, total)[0];
+    if (max_obj > 0.0) {  // otherwise every objective entry is zero: step 0 (trust_region.cc:349-358)
+      const double r2 = radius * radius;
+      double delta = 0.0;
+      double prev_fixed = -1.0;
+      for (;;) {
+        const double* h = RunMap(ws, RadiusPassOp{{}, crit, coef, delta}, total);
+        ++passes;
+        const double fixed_r2 = h[0], free_coef = h[1], num_fixed = h[2];
+        if (!(free_coef > 0.0)) { step = DBL_MAX; break; }  // trust_region.cc:438-446
+        // No breakpoint crossed since the last pass: delta is the exact root.
+        if (num_fixed == prev_fixed) { step = delta; break; }
+        const double next = std::sqrt(std::max(0.0, r2 - fixed_r2) / free_coef);
+        if (!(next > delta)) { step = delta; break; }  // already at the root up to rounding
+        if (passes >= 200) { step = next; break; }
+        prev_fixed = num_fixed;
+        delta = next;
+      }
+    }
+  }
+  double primal_delta = 0.0, dual_delta = 0.0;
+  {
+    const double* h = RunMap(ws, BoundsDeltaOp{{}, view, step}, total);
+    primal_delta = h[0];
+    dual_delta = h[1];
+  }
+  out.lower_bound = lagrangian + primal_delta;
+  out.upper_bound = lagrangian + dual_delta;
+  if (tr_passes) *tr_passes = passes;
+  return out;
+}
+
+}  // namespace pdlp_b200

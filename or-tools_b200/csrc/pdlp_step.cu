@@ -1,0 +1,377 @@
+// The PDHG trial step on the device: the replacement of Solver::TakeAdaptiveStep,
+// TakeConstantSizeStep and TakeMalitskyPockStep and the helpers they call
+//   ortools/pdlp/primal_dual_hybrid_gradient.cc:1659-1771 (next primal / dual, movement,
+//   nonlinearity), :2211-2406 (the three step rules), sharded_optimization_utils.cc:54-66
+//   (weighted average).
+//
+// One trial of the adaptive rule is five launches, none of which returns to the host:
+//   K1 primal_step   x' = proj(x - tau (c - K^T y)) [/ (1 + tau Q)], xbar = 2x' - x, |dx|^2
+//   K2 dual_step     CSR rows: (K xbar)_i fused with the dual prox, writes y', |dy|^2
+//   K3 kty_step      CSC cols: (K^T y')_j, fused with dx_j (K^T y' - K^T y)_j
+//   K4 decide        movement / nonlinearity / accept / next step size, on one CTA
+//   K5 average       on accept: avg += w/(W+w) (z - avg) for x and y
+// All kernels read their scalars (step size, primal weight, which buffer is current)
+// from the device-resident StepState and exit early once the state says stop, so the
+// host can enqueue a whole major iteration's worth of trials and sync once.
+#include "pdlp_launch.cuh"
+
+namespace pdlp_b200 {
+
+namespace {
+
+constexpr double kDivergentMovement = 1.0e100;  // primal_dual_hybrid_gradient.cc:553
+constexpr int kMaxInnerTrials = 60;             // :2231, :2299
+
+struct OneSum {
+  static constexpr int kNumSlots = 1;
+  __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
+};
+
+// K1.  ComputeNextPrimalSolution (:1659-1705) + the extrapolation of :1716-1722.
+struct PrimalStepOp : OneSum {
+  const StepState* st;
+  double* x0; double* x1;            // the two x buffers
+  const double* kty0; const double* kty1;
+  const double* c; const double* q;  // q null for an LP
+  const double* lb; const double* ub;
+  double* xbar;
+  int write_xbar;                    // Malitsky-Pock extrapolates per dual trial instead
+  // resolved by Begin()
+  const double* x; double* xn; const double* kty; double tau;
+  __device__ bool Begin() {
+    if (st->active == 0) return false;
+    const int cur = st->cur;
+    tau = (st->mp_tau > 0.0) ? st->mp_tau : st->step_size / st->primal_weight;
+    x = cur ? x1 : x0;
+    xn = cur ? x0 : x1;
+    kty = cur ? kty1 : kty0;
+    return true;
+  }
+  __device__ void Apply(int64_t j, Slots<1>& acc) const {
+    const double xj = x[j];
+    double t = xj - tau * (c[j] - kty[j]);
+    if (q != nullptr) t = t / (tau * q[j] + 1.0);
+    const double v = fmax(fmin(t, ub[j]), lb[j]);
+    const double d = v - xj;
+    xn[j] = v;
+    if (write_xbar) xbar[j] = v + 1.0 * d;
+    acc.v[0] += d * d;
+  }
+};
+
+// Malitsky-Pock: xbar = x' + theta (x' - x) for the current dual trial (:1716-1722).
+struct ExtrapolateOp : NoSlots {
+  const StepState* st;
+  const double* x0; const double* x1; double* xbar;
+  const double* x; const double* xn; double theta;
+  __device__ bool Begin() {
+    if (st->active == 0) return false;
+    const int cur = st->cur;
+    x = cur ? x1 : x0;
+    xn = cur ? x0 : x1;
+    theta = st->mp_new_tau / st->mp_tau;
+    return true;
+  }
+  __device__ void Apply(int64_t j, Slots<0>&) const {
+    const double v = xn[j];
+    xbar[j] = v + theta * (v - x[j]);
+  }
+};
+
+// K2.  ComputeNextDualSolution (:1726-1746) on the CSR copy.
+struct DualStepOp : OneSum {
+  const StepState* st;
+  const double* val; const int* idx; const double* xbar;
+  double* y0; double* y1;
+  const double* clb; const double* cub;
+  const double* y; double* yn; double sigma;
+  __device__ bool Begin() {
+    if (st->active == 0) return false;
+    const int cur = st->cur;
+    sigma = (st->mp_tau > 0.0) ? (st->primal_weight * st->primal_weight) * st->mp_new_tau : st->step_size * st->primal_weight;
+    y = cur ? y1 : y0;
+    yn = cur ? y0 : y1;
+    return true;
+  }
+  __device__ double Load(int64_t k) const { return val[k] * xbar[idx[k]]; }
+  __device__ double RowInit() const { return 0.0; }
+  __device__ double RowAdd(double acc, double staged, int) const { return acc + staged; }
+  __device__ double RowMerge(double a, double b) const { return a + b; }
+  __device__ void RowFinish(int i, double kx, Slots<1>& red) const {
+    const double yi = y[i];
+    const double temp = yi - sigma * kx;
+    const double v = fmax(fmin(0.0, temp + sigma * cub[i]), temp + sigma * clb[i]);
+    yn[i] = v;
+    const double d = v - yi;
+    red.v[0] += d * d;
+  }
+};
+
+// K3.  K^T y' on the CSC copy (:2323-2325) fused with ComputeNonlinearity (:1761-1771)
+// and, for Malitsky-Pock, |K^T y' - K^T y|^2 (:2247-2250).
+struct KtyStepOp {
+  static constexpr int kNumSlots = 2;
+  __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
+  const StepState* st;
+  const double* val; const int* idx;
+  const double* y0; const double* y1;
+  const double* x0; const double* x1;
+  double* kty0; double* kty1;
+  const double* yn; const double* x; const double* xn; const double* kty; double* ktyn;
+  __device__ bool Begin() {
+    if (st->active == 0) return false;
+    const int cur = st->cur;
+    yn = cur ? y0 : y1;
+    x = cur ? x1 : x0;
+    xn = cur ? x0 : x1;
+    kty = cur ? kty1 : kty0;
+    ktyn = cur ? kty0 : kty1;
+    return true;
+  }
+  __device__ double Load(int64_t k) const { return val[k] * yn[idx[k]]; }
+  __device__ double RowInit() const { return 0.0; }
+  __device__ double RowAdd(double acc, double staged, int) const { return acc + staged; }
+  __device__ double RowMerge(double a, double b) const { return a + b; }
+  __device__ void RowFinish(int j, double v, Slots<2>& red) const {
+    ktyn[j] = v;
+    const double dk = v - kty[j];
+    red.v[0] += (xn[j] - x[j]) * dk;
+    red.v[1] += dk * dk;
+  }
+};
+
+// K4 for the adaptive and constant rules.  One CTA; thread 0 carries the scalar logic
+// of :2305-2374 (adaptive) or :2382-2405 (constant).
+__global__ void __launch_bounds__(kBlock) decide_adaptive_kernel(StepState* st, const double* p1, int g1, const double* p2, int g2, const double* p3, int g3,
+                                                                int constant_step) {
+  __shared__ double buf[kBlock];
+  if (st->active == 0) {
+    if (threadIdx.x == 0) { st->accepted_last = 0; st->reset_average = 0; }
+    return;
+  }
+  const double dx2 = ReducePartialsSum(p1, g1, 1, 0, buf);
+  const double dy2 = ReducePartialsSum(p2, g2, 1, 0, buf);
+  const double dot = ReducePartialsSum(p3, g3, 2, 0, buf);
+  if (threadIdx.x != 0) return;
+  StepState s = *st;
+  s.total_trials += 1;
+  s.accepted_last = 0;
+  const double movement = (0.5 * s.primal_weight) * dx2 + (0.5 / s.primal_weight) * dy2;
+  const double nonlinearity = -dot;
+  s.last_movement = movement;
+  s.last_nonlinearity = nonlinearity;
+  if (movement == 0.0 || movement > kDivergentMovement) {
+    // :2313-2322 / :2387-2395.  The inner loop breaks without counting this trial.
+    if (movement == 0.0) { s.reset_average = 1; s.avg_weight_sum = 1.0; s.avg_weight_sum_dual = 1.0; s.avg_num_terms = 1; }
+    s.force_numerical = 1;
+    s.active = 0;
+    if (!constant_step) s.num_rejected_steps += s.inner - 1;
+    s.inner = 0;
+    *st = s;
+    return;
+  }
+  if (constant_step) {
+    s.cur ^= 1;
+    s.avg_ratio = s.step_size / (s.avg_weight_sum + s.step_size);
+    s.avg_weight_sum += s.step_size;
+    s.avg_ratio_dual = s.step_size / (s.avg_weight_sum_dual + s.step_size);
+    s.avg_weight_sum_dual += s.step_size;
+    s.avg_num_terms += 1;
+    s.accepted_last = 1;
+    s.iterations_completed += 1;
+  } else {
+    const double limit = nonlinearity > 0.0 ? movement / nonlinearity : INFINITY;
+    const bool accept = s.step_size <= limit;
+    const double total_steps_attempted = static_cast<double>(s.num_rejected_steps + s.inner + s.iterations_completed + 1);
+    if (accept) {
+      s.cur ^= 1;
+      s.avg_ratio = s.step_size / (s.avg_weight_sum + s.step_size);
+      s.avg_weight_sum += s.step_size;
+      s.avg_ratio_dual = s.step_size / (s.avg_weight_sum_dual + s.step_size);
+      s.avg_weight_sum_dual += s.step_size;
+      s.avg_num_terms += 1;
+      s.accepted_last = 1;
+    }
+    const double first = isinf(limit) ? limit : (1.0 - pow(total_steps_attempted + 1.0, -s.reduction_exponent)) * limit;
+    const double second = (1.0 + pow(total_steps_attempted + 1.0, -s.growth_exponent)) * s.step_size;
+    s.step_size = fmin(first, second);
+    if (accept) {
+      s.num_rejected_steps += s.inner;
+      s.inner = 0;
+      s.iterations_completed += 1;
+    } else {
+      s.inner += 1;
+      if (s.inner >= kMaxInnerTrials) {  // :2299-2304
+        s.reset_average = 1; s.avg_weight_sum = 1.0; s.avg_weight_sum_dual = 1.0; s.avg_num_terms = 1;
+        s.force_numerical = 1;
+        s.active = 0;
+        s.num_rejected_steps += s.inner - 1;
+        s.inner = 0;
+      }
+    }
+  }
+  if (s.accepted_last) {
+    if (s.iterations_completed >= s.target_iteration) s.active = 0;
+    const double passes = s.iterations_completed + s.passes_per_rejected_step * s.num_rejected_steps;
+    if (passes >= s.kkt_pass_limit) s.active = 0;
+  }
+  *st = s;
+}
+
+// K5.  ShardedWeightedAverage::Add for x and y in one launch over n + m elements
+// (sou.cc:54-66), plus ResetAverageToCurrent (:2192-2197) when requested.
+struct AverageOp : NoSlots {
+  const StepState* st;
+  const double* x0; const double* x1; const double* y0; const double* y1;
+  double* avg_x; double* avg_y; int64_t n;
+  const double* xs; const double* xold; const double* ys;
+  double ratio_x, ratio_y, ratio_old_x; int reset, first_mp;
+  __device__ bool Begin() {
+    reset = st->reset_average;
+    first_mp = st->first_mp_add_pending;
+    if (st->accepted_last == 0 && reset == 0) return false;
+    const int cur = st->cur;
+    xs = cur ? x1 : x0;
+    xold = cur ? x0 : x1;
+    ys = cur ? y1 : y0;
+    ratio_x = st->avg_ratio;
+    ratio_y = st->avg_ratio_dual;
+    ratio_old_x = st->avg_ratio_old_x;
+    return true;
+  }
+  __device__ void Apply(int64_t i, Slots<0>&) const {
+    if (i < n) {
+      if (reset) { avg_x[i] = xs[i]; return; }
+      double a = avg_x[i];
+      // Malitsky-Pock first accepted step (:2260-2264): the old x enters the empty
+      // average first; after the flip it sits in the other buffer.
+      if (first_mp) a += ratio_old_x * (xold[i] - a);
+      a += ratio_x * (xs[i] - a);
+      avg_x[i] = a;
+    } else {
+      const int64_t k = i - n;
+      if (reset) { avg_y[k] = ys[k]; return; }
+      const double a = avg_y[k];
+      avg_y[k] = a + ratio_y * (ys[k] - a);
+    }
+  }
+};
+
+// K4 for Malitsky-Pock (:2237-2291).
+__global__ void __launch_bounds__(kBlock) decide_mp_kernel(StepState* st, const double* p1, int g1, const double* p2, int g2, const double* p3, int g3) {
+  __shared__ double buf[kBlock];
+  if (st->active == 0) {
+    if (threadIdx.x == 0) { st->accepted_last = 0; st->reset_average = 0; st->first_mp_add_pending = 0; }
+    return;
+  }
+  const double dx2 = ReducePartialsSum(p1, g1, 1, 0, buf);
+  const double dy2 = ReducePartialsSum(p2, g2, 1, 0, buf);
+  const double dkty2 = ReducePartialsSum(p3, g3, 2, 1, buf);
+  if (threadIdx.x != 0) return;
+  StepState s = *st;
+  s.total_trials += 1;
+  s.accepted_last = 0;
+  s.first_mp_add_pending = 0;
+  const double new_ratio = s.mp_new_tau / s.mp_tau;
+  const double dy_norm = sqrt(dy2), dkty_norm = sqrt(dkty2);
+  if (s.primal_weight * s.mp_new_tau * dkty_norm <= s.mp_contraction * dy_norm) {
+    s.step_size = s.mp_new_tau * s.primal_weight;
+    s.ratio_last_two_step_sizes = new_ratio;
+    if (!(s.avg_weight_sum > 0.0)) {
+      // x_avg_.Add(old x, new_tau * ratio) into the empty average: ratio w/(0+w) = 1.
+      const double w0 = s.mp_new_tau * new_ratio;
+      if (w0 > 0.0) { s.first_mp_add_pending = 1; s.avg_ratio_old_x = w0 / (0.0 + w0); s.avg_weight_sum = w0; }
+      // num_terms of the primal average counts this add too; the restart logic reads
+      // the primal counter (:1911), so it is the one mirrored here.
+      s.avg_num_terms += 1;
+    }
+    s.cur ^= 1;
+    s.avg_ratio = s.mp_new_tau / (s.avg_weight_sum + s.mp_new_tau);
+    s.avg_weight_sum += s.mp_new_tau;
+    s.avg_ratio_dual = s.mp_new_tau / (s.avg_weight_sum_dual + s.mp_new_tau);
+    s.avg_weight_sum_dual += s.mp_new_tau;
+    s.avg_num_terms += 1;
+    s.accepted_last = 1;
+    const double movement = (0.5 * s.primal_weight) * dx2 + (0.5 / s.primal_weight) * dy2;
+    s.last_movement = movement;
+    if (movement == 0.0) { s.reset_average = 1; s.avg_weight_sum = 1.0; s.avg_weight_sum_dual = 1.0; s.avg_num_terms = 1; s.force_numerical = 1; s.active = 0; }
+    else if (movement > kDivergentMovement) { s.force_numerical = 1; s.active = 0; }
+    s.num_rejected_steps += s.inner;
+    s.inner = 0;
+    s.iterations_completed += 1;
+    s.mp_tau = -1.0;  // next launch of K1 starts a new outer iteration
+    if (s.iterations_completed >= s.target_iteration) s.active = 0;
+    const double passes = s.iterations_completed + s.passes_per_rejected_step * s.num_rejected_steps;
+    if (passes >= s.kkt_pass_limit) s.active = 0;
+  } else {
+    s.mp_new_tau = s.mp_downscaling * s.mp_new_tau;
+    s.inner += 1;
+    if (s.inner >= kMaxInnerTrials) {  // :2231-2236
+      s.reset_average = 1; s.avg_weight_sum = 1.0; s.avg_weight_sum_dual = 1.0; s.avg_num_terms = 1;
+      s.force_numerical = 1;
+      s.active = 0;
+      s.num_rejected_steps += s.inner;
+      s.inner = 0;
+      s.mp_tau = -1.0;
+    }
+  }
+  *st = s;
+}
+
+// Malitsky-Pock: starts an outer iteration when none is in flight (:2213-2222).
+__global__ void mp_begin_kernel(StepState* st) {
+  if (st->active == 0 || st->mp_tau > 0.0) return;
+  const double tau = st->step_size / st->primal_weight;
+  const double dilating = 1.0 + (st->mp_interpolation * (sqrt(1.0 + st->ratio_last_two_step_sizes) - 1.0));
+  st->mp_tau = tau;
+  st->mp_new_tau = tau * dilating;
+}
+
+}  // namespace
+
+void EnqueueAdaptiveTrials(Workspace& ws, const DeviceProblem& p, Iterate& it, int trials, bool constant_step) {
+  StepState* st = it.state.get();
+  const SparseRows& csr = p.K.by_row;
+  const SparseRows& csc = p.K.by_col;
+  PrimalStepOp k1{{}, st, it.x[0].get(), it.x[1].get(), it.kty[0].get(), it.kty[1].get(), p.c.get(), p.q_or_null(), p.vlb.get(), p.vub.get(), it.xbar.get(), 1};
+  DualStepOp k2{{}, st, csr.val.get(), csr.idx.get(), it.xbar.get(), it.y[0].get(), it.y[1].get(), p.clb.get(), p.cub.get()};
+  KtyStepOp k3{st, csc.val.get(), csc.idx.get(), it.y[0].get(), it.y[1].get(), it.x[0].get(), it.x[1].get(), it.kty[0].get(), it.kty[1].get()};
+  AverageOp k5{{}, st, it.x[0].get(), it.x[1].get(), it.y[0].get(), it.y[1].get(), it.avg_x.get(), it.avg_y.get(), p.n};
+  for (int t = 0; t < trials; ++t) {
+    const int g1 = EnqueueMap(ws, k1, p.n, 0);
+    const int g2 = EnqueueRows(ws, k2, csr, 1);
+    const int g3 = EnqueueRows(ws, k3, csc, 2);
+    decide_adaptive_kernel<<<1, kBlock, 0, ws.stream>>>(st, ws.partials[0].get(), g1, ws.partials[1].get(), g2, ws.partials[2].get(), g3, constant_step ? 1 : 0);
+    ++ws.launches;
+    EnqueueMap(ws, k5, p.n + p.m, 0);
+  }
+  PDLP_CUDA_CHECK(cudaGetLastError());
+}
+
+void EnqueueMalitskyPockTrials(Workspace& ws, const DeviceProblem& p, Iterate& it, int trials) {
+  StepState* st = it.state.get();
+  const SparseRows& csr = p.K.by_row;
+  const SparseRows& csc = p.K.by_col;
+  PrimalStepOp k1{{}, st, it.x[0].get(), it.x[1].get(), it.kty[0].get(), it.kty[1].get(), p.c.get(), p.q_or_null(), p.vlb.get(), p.vub.get(), it.xbar.get(), 0};
+  ExtrapolateOp kx{{}, st, it.x[0].get(), it.x[1].get(), it.xbar.get()};
+  DualStepOp k2{{}, st, csr.val.get(), csr.idx.get(), it.xbar.get(), it.y[0].get(), it.y[1].get(), p.clb.get(), p.cub.get()};
+  KtyStepOp k3{st, csc.val.get(), csc.idx.get(), it.y[0].get(), it.y[1].get(), it.x[0].get(), it.x[1].get(), it.kty[0].get(), it.kty[1].get()};
+  AverageOp k5{{}, st, it.x[0].get(), it.x[1].get(), it.y[0].get(), it.y[1].get(), it.avg_x.get(), it.avg_y.get(), p.n};
+  for (int t = 0; t < trials; ++t) {
+    mp_begin_kernel<<<1, 1, 0, ws.stream>>>(st);
+    ++ws.launches;
+    // The primal step is recomputed per dual trial (same tau, same result): keeping it
+    // inside the trial keeps every trial the same launch sequence; its |dx|^2 partials
+    // land in region 0 and are read by the decision kernel.
+    const int g1 = EnqueueMap(ws, k1, p.n, 0);
+    EnqueueMap(ws, kx, p.n, 1);
+    const int g2 = EnqueueRows(ws, k2, csr, 1);
+    const int g3 = EnqueueRows(ws, k3, csc, 2);
+    decide_mp_kernel<<<1, kBlock, 0, ws.stream>>>(st, ws.partials[0].get(), g1, ws.partials[1].get(), g2, ws.partials[2].get(), g3);
+    ++ws.launches;
+    EnqueueMap(ws, k5, p.n + p.m, 0);
+  }
+  PDLP_CUDA_CHECK(cudaGetLastError());
+}
+
+}  // namespace pdlp_b200

@@ -1,0 +1,121 @@
+// The C++ entry point of the B200 PDLP solver.  Same names, argument order, ownership
+// and error convention as the reference's public header
+//   ortools/pdlp/primal_dual_hybrid_gradient.h:30-156 and quadratic_program.h:53-143,
+// with std::vector / a plain CSC struct where the reference uses Eigen (Eigen is not in
+// this image; the CSC arrays are layout-compatible with a compressed
+// Eigen::SparseMatrix<double, ColMajor, int64_t>: valuePtr / innerIndexPtr / outerIndexPtr).
+//
+// Every failure is reported the reference's way: a normal return whose
+// solve_log.termination_reason is INVALID_PROBLEM / INVALID_PARAMETER /
+// INVALID_INITIAL_SOLUTION with termination_string set.  Only CUDA-level failures
+// (no device, out of memory) throw std::runtime_error: there is no CPU fallback.
+#ifndef PDLP_B200_PRIMAL_DUAL_HYBRID_GRADIENT_H_
+#define PDLP_B200_PRIMAL_DUAL_HYBRID_GRADIENT_H_
+
+#include <atomic>
+#include <cstdint>
+#include <functional>
+#include <limits>
+#include <optional>
+#include <string>
+#include <vector>
+
+#include "pdlp_schema.h"
+#include "pdlp_termination.h"
+
+namespace pdlp_b200 {
+
+using VectorXd = std::vector<double>;
+
+// Compressed sparse column matrix, rows x cols.
+struct SparseMatrixCsc {
+  int64_t rows = 0, cols = 0;
+  std::vector<int64_t> outer_index{0};  // cols + 1
+  std::vector<int64_t> inner_index;     // row of every nonzero
+  std::vector<double> values;
+  int64_t nonZeros() const { return static_cast<int64_t>(values.size()); }
+};
+
+// quadratic_program.h:53-143.
+struct QuadraticProgram {
+  VectorXd objective_vector;
+  std::optional<VectorXd> objective_matrix;  // diagonal; the 1/2 is implicit
+  SparseMatrixCsc constraint_matrix;
+  VectorXd constraint_lower_bounds, constraint_upper_bounds;
+  VectorXd variable_lower_bounds, variable_upper_bounds;
+  std::optional<std::string> problem_name;
+  std::optional<std::vector<std::string>> variable_names, constraint_names;
+  double objective_offset = 0.0;
+  double objective_scaling_factor = 1.0;
+  double ApplyObjectiveScalingAndOffset(double objective) const { return objective_scaling_factor * (objective + objective_offset); }
+  void ResizeAndInitialize(int64_t num_variables, int64_t num_constraints) {
+    const double inf = std::numeric_limits<double>::infinity();
+    objective_vector.assign(num_variables, 0.0);
+    variable_lower_bounds.assign(num_variables, -inf);
+    variable_upper_bounds.assign(num_variables, inf);
+    constraint_lower_bounds.assign(num_constraints, -inf);
+    constraint_upper_bounds.assign(num_constraints, inf);
+    constraint_matrix = SparseMatrixCsc();
+    constraint_matrix.rows = num_constraints;
+    constraint_matrix.cols = num_variables;
+    constraint_matrix.outer_index.assign(num_variables + 1, 0);
+  }
+};
+inline bool IsLinearProgram(const QuadraticProgram& qp) { return !qp.objective_matrix.has_value(); }
+// quadratic_program.cc:37-80; "" when consistent.
+std::string ValidateQuadraticProgramDimensions(const QuadraticProgram& qp);
+// quadratic_program.cc:82-90.
+bool HasValidBounds(const QuadraticProgram& qp);
+
+// primal_dual_hybrid_gradient.h:30-93.
+struct PrimalAndDualSolution {
+  VectorXd primal_solution;
+  VectorXd dual_solution;
+};
+struct SolverResult {
+  VectorXd primal_solution;
+  VectorXd dual_solution;
+  VectorXd reduced_costs;
+  SolveLog solve_log;
+};
+enum class IterationType {
+  kNormal = 0,
+  kPrimalFeasibility = 1,
+  kDualFeasibility = 2,
+  kNormalTermination = 3,
+  kFeasibilityPolishingTermination = 4,
+  kPresolveTermination = 5,
+};
+struct IterationCallbackInfo {
+  IterationType iteration_type;
+  TerminationCriteria termination_criteria;
+  IterationStats iteration_stats;
+  QuadraticProgramBoundNorms bound_norms;
+};
+
+// Device placement; not part of the reference API (defaults reproduce it).
+struct DeviceOptions {
+  int device = -1;  // -1: the calling thread's current CUDA device
+};
+
+// Counters of the last solve on the calling thread, for benchmarks and tests.
+struct SolveCounters {
+  long long kernel_launches = 0;
+  long long trial_steps = 0;
+  double loop_seconds = 0.0;         // host wall time of Solver::Solve
+  double device_loop_seconds = 0.0;  // CUDA-event time of the iteration loop
+  double setup_seconds = 0.0;
+};
+const SolveCounters& LastSolveCounters();
+
+// primal_dual_hybrid_gradient.h:140-156.
+SolverResult PrimalDualHybridGradient(QuadraticProgram qp, const PrimalDualHybridGradientParams& params,
+                                      const std::atomic<bool>* interrupt_solve = nullptr,
+                                      std::function<void(const IterationCallbackInfo&)> iteration_stats_callback = nullptr);
+SolverResult PrimalDualHybridGradient(QuadraticProgram qp, const PrimalDualHybridGradientParams& params,
+                                      std::optional<PrimalAndDualSolution> initial_solution,
+                                      const std::atomic<bool>* interrupt_solve = nullptr,
+                                      std::function<void(const IterationCallbackInfo&)> iteration_stats_callback = nullptr);
+
+}  // namespace pdlp_b200
+#endif  // PDLP_B200_PRIMAL_DUAL_HYBRID_GRADIENT_H_
