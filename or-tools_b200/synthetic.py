@@ -1,0 +1,188 @@
+"""Synthetic problem generators for the benchmark configurations of BASELINE.json
+(SURVEY.md 8d).  Host-side numpy; all take a seed and return a QuadraticProgram whose
+optimum exists by construction (a primal-dual optimal pair is planted for the random
+LP / QP; the network problems are feasible and bounded by positive costs)."""
+import numpy as np
+import scipy.sparse as sp
+
+from ._api import QuadraticProgram
+
+INF = np.inf
+
+
+def _csc_from_columns(m, n, rows, vals, per_col):
+    """rows/vals: (n, per_col) arrays, rows sorted inside each column."""
+    indptr = np.arange(0, n * per_col + 1, per_col, dtype=np.int64)
+    return sp.csc_matrix((vals.reshape(-1), rows.reshape(-1).astype(np.int64), indptr), shape=(m, n))
+
+
+def random_sparse_lp(m, n, nnz_per_col=5, seed=0, equality_fraction=0.5, qp_diagonal=False):
+    """Config C2 (m = 1e6, n = 2e6, 5 per column) and, with qp_diagonal, C4.
+
+    K has exactly nnz_per_col distinct uniform rows per column, N(0,1) values; variables
+    live in [0, U(1,10)]; half the rows are equalities, the rest `<=` rows.  A planted
+    pair (x*, y*) satisfies the KKT conditions, so the optimum is known."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    k = min(nnz_per_col, m)
+    rows = rng.integers(0, m, size=(n, k), dtype=np.int64)
+    rows.sort(axis=1)
+    for _ in range(64):  # resample duplicates inside a column
+        dup = np.zeros_like(rows, dtype=bool)
+        dup[:, 1:] = rows[:, 1:] == rows[:, :-1]
+        bad = dup.any(axis=1)
+        if not bad.any():
+            break
+        rows[bad] = rng.integers(0, m, size=(int(bad.sum()), k), dtype=np.int64)
+        rows[bad] = np.sort(rows[bad], axis=1)
+    vals = rng.standard_normal((n, k))
+    K = _csc_from_columns(m, n, rows, vals, k)
+
+    ub = rng.uniform(1.0, 10.0, n)
+    lb = np.zeros(n)
+    where = rng.integers(0, 3, n)  # 0: at lower, 1: at upper, 2: interior
+    x_star = np.where(where == 0, lb, np.where(where == 1, ub, rng.uniform(0.0, 1.0, n) * ub))
+    activity = K @ x_star
+    is_eq = rng.uniform(size=m) < equality_fraction
+    active_ineq = (~is_eq) & (rng.uniform(size=m) < 0.5)
+    slack = np.where(is_eq | active_ineq, 0.0, rng.uniform(0.0, 1.0, m))
+    cub = activity + slack
+    clb = np.where(is_eq, activity, -INF)
+    # Dual: free sign on equalities, <= 0 on active `<=` rows, 0 on slack rows.
+    y_star = np.where(is_eq, rng.standard_normal(m), np.where(active_ineq, -np.abs(rng.standard_normal(m)), 0.0))
+    reduced = np.where(where == 0, np.abs(rng.standard_normal(n)), np.where(where == 1, -np.abs(rng.standard_normal(n)), 0.0))
+    c = K.T @ y_star + reduced
+    qp = QuadraticProgram()
+    qp.constraint_matrix = K
+    qp.constraint_lower_bounds = clb
+    qp.constraint_upper_bounds = cub
+    qp.variable_lower_bounds = lb
+    qp.variable_upper_bounds = ub
+    if qp_diagonal:
+        q = rng.uniform(0.1, 10.0, n)
+        c = c - q * x_star  # gradient c + Q x* - K^T y* keeps the planted reduced costs
+        qp.set_objective_matrix_diagonal(q)
+    qp.objective_vector = c
+    qp.problem_name = f"random_sparse_{'qp' if qp_diagonal else 'lp'}_{m}x{n}_seed{seed}"
+    qp.planted_primal = x_star
+    qp.planted_dual = y_star
+    return qp
+
+
+def multicommodity_flow_lp(num_commodities=64, grid_side=256, num_arcs=520000, pairs_per_commodity=16, seed=0):
+    """Config C3: K commodities on a directed grid with random shortcut arcs.
+
+    Variables x[a, k] (arc-major, so contiguous column blocks are arc blocks), one
+    conservation row per (node, commodity) with +1 / -1 entries and one joint capacity
+    row per arc with K ones: nnz = 3 K A.  Capacities are 1.3 x a feasible Manhattan
+    routing, so the LP is feasible; costs are positive so it is bounded."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    side = grid_side
+    N = side * side
+    node = lambda r, c: r * side + c
+    rr, cc = np.meshgrid(np.arange(side), np.arange(side), indexing="ij")
+    tails, heads = [], []
+    # grid arcs in 4 directions (no wrap)
+    for dr, dc in ((0, 1), (0, -1), (1, 0), (-1, 0)):
+        ok = (rr + dr >= 0) & (rr + dr < side) & (cc + dc >= 0) & (cc + dc < side)
+        tails.append(node(rr[ok], cc[ok]))
+        heads.append(node(rr[ok] + dr, cc[ok] + dc))
+    tails = np.concatenate(tails)
+    heads = np.concatenate(heads)
+    grid_arcs = tails.size
+    extra = max(0, num_arcs - grid_arcs)
+    et = rng.integers(0, N, extra)
+    eh = rng.integers(0, N, extra)
+    eh = np.where(eh == et, (eh + 1) % N, eh)
+    tails = np.concatenate([tails, et])  # all grid arcs are kept: the planted routing uses them
+    heads = np.concatenate([heads, eh])
+    A = tails.size
+    Kc = num_commodities
+    # arc id lookup for grid moves: (node, direction) -> arc index
+    arc_of = {}
+    dirs = ((0, 1), (0, -1), (1, 0), (-1, 0))
+    start = 0
+    lookup = np.full((4, N), -1, dtype=np.int64)
+    for d, (dr, dc) in enumerate(dirs):
+        ok = (rr + dr >= 0) & (rr + dr < side) & (cc + dc >= 0) & (cc + dc < side)
+        cnt = int(ok.sum())
+        lookup[d, node(rr[ok], cc[ok])] = np.arange(start, start + cnt)
+        start += cnt
+    del arc_of
+    # demands and a feasible routing
+    demand = np.zeros((N, Kc))
+    load = np.zeros(A)
+    for k in range(Kc):
+        for _ in range(pairs_per_commodity):
+            s, t = rng.integers(0, N, 2)
+            if s == t:
+                continue
+            d = rng.uniform(1.0, 10.0)
+            demand[s, k] += d
+            demand[t, k] -= d
+            r, c = divmod(int(s), side)
+            tr, tc = divmod(int(t), side)
+            while c != tc:
+                dirn = 0 if tc > c else 1
+                load[lookup[dirn, node(r, c)]] += d
+                c += 1 if tc > c else -1
+            while r != tr:
+                dirn = 2 if tr > r else 3
+                load[lookup[dirn, node(r, c)]] += d
+                r += 1 if tr > r else -1
+    capacity = 1.3 * load + 1.0
+    n = A * Kc
+    m = N * Kc + A
+    # column j = a * Kc + k: rows (tail, k) -> +1, (head, k) -> -1, capacity row -> +1
+    a_idx = np.repeat(np.arange(A, dtype=np.int64), Kc)
+    k_idx = np.tile(np.arange(Kc, dtype=np.int64), A)
+    r_tail = tails[a_idx] * Kc + k_idx
+    r_head = heads[a_idx] * Kc + k_idx
+    r_cap = N * Kc + a_idx
+    rows = np.stack([r_tail, r_head, r_cap], axis=1)
+    vals = np.stack([np.ones(n), -np.ones(n), np.ones(n)], axis=1)
+    order = np.argsort(rows, axis=1, kind="stable")
+    rows = np.take_along_axis(rows, order, axis=1)
+    vals = np.take_along_axis(vals, order, axis=1)
+    K = _csc_from_columns(m, n, rows, vals, 3)
+    qp = QuadraticProgram()
+    qp.constraint_matrix = K
+    rhs = demand.reshape(-1)
+    qp.constraint_lower_bounds = np.concatenate([rhs, np.full(A, -INF)])
+    qp.constraint_upper_bounds = np.concatenate([rhs, capacity])
+    qp.variable_lower_bounds = np.zeros(n)
+    qp.variable_upper_bounds = np.full(n, INF)
+    qp.objective_vector = rng.uniform(1.0, 10.0, n)
+    qp.problem_name = f"multicommodity_flow_K{Kc}_N{N}_A{A}_seed{seed}"
+    return qp
+
+
+def transportation_lp(num_sources, num_sinks, seed=0, first_source=0, last_source=None):
+    """Config C5: dense bipartite transportation problem; x[s, d] at column s * D + d.
+
+    Rows: supply s (sum_d x <= supply_s), then demand S + d (sum_s x = demand_d); every
+    entry of K is 1 and nnz = 2 n.  `first_source` / `last_source` restrict the columns to
+    a block of sources (the per-GPU column shard); rows are never restricted."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    S, D = num_sources, num_sinks
+    demand = rng.uniform(1.0, 100.0, D)
+    supply = rng.uniform(1.0, 100.0, S)
+    supply *= 1.05 * demand.sum() / supply.sum()
+    last_source = S if last_source is None else last_source
+    block = last_source - first_source
+    n = block * D
+    s_idx = np.repeat(np.arange(first_source, last_source, dtype=np.int64), D)
+    d_idx = np.tile(np.arange(D, dtype=np.int64), block)
+    rows = np.stack([s_idx, S + d_idx], axis=1)
+    vals = np.ones((n, 2))
+    K = _csc_from_columns(S + D, n, rows, vals, 2)
+    cost_rng = np.random.Generator(np.random.PCG64([seed, 1]))
+    cost = cost_rng.uniform(1.0, 100.0, S * D)[first_source * D: last_source * D] if block * D < 5e7 else cost_rng.uniform(1.0, 100.0, n)
+    qp = QuadraticProgram()
+    qp.constraint_matrix = K
+    qp.constraint_lower_bounds = np.concatenate([np.full(S, -INF), demand])
+    qp.constraint_upper_bounds = np.concatenate([supply, demand])
+    qp.variable_lower_bounds = np.zeros(n)
+    qp.variable_upper_bounds = np.full(n, INF)
+    qp.objective_vector = cost
+    qp.problem_name = f"transportation_{S}x{D}_seed{seed}"
+    return qp

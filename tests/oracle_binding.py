@@ -1,0 +1,222 @@
+"""ctypes driver of the CPU oracle (oracle/oracle_capi.cc).  TEST INFRASTRUCTURE ONLY:
+imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / reference leg."""
+import ctypes
+import json
+import os
+import subprocess
+
+import numpy as np
+import scipy.sparse as sp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+ORACLE_LIB = os.path.join(ORACLE_DIR, "_build", "libpdlp_oracle.so")
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", ORACLE_DIR])
+
+
+def load():
+    if not os.path.exists(ORACLE_LIB):
+        build()
+    lib = ctypes.CDLL(ORACLE_LIB)
+    lib.oracle_sigma_max.restype = ctypes.c_double
+    lib.oracle_problem_create.restype = ctypes.c_void_p
+    return lib
+
+
+def flatten_params(msg, prefix=""):
+    """protobuf message -> 'a.b=value' lines holding exactly the explicitly set fields."""
+    lines = []
+    if msg is None:
+        return ""
+    for fd, value in msg.ListFields():
+        name = prefix + fd.name
+        if fd.type == fd.TYPE_MESSAGE:
+            if fd.name == "glop_parameters":
+                continue
+            lines.append(name + "=")
+            sub = flatten_params(value, name + ".")
+            if sub:
+                lines.append(sub)
+        elif fd.is_repeated if hasattr(fd, "is_repeated") else fd.label == fd.LABEL_REPEATED:
+            lines.append(name + "=" + ",".join(str(v) for v in value))
+        elif fd.type == fd.TYPE_BOOL:
+            lines.append(name + "=" + ("1" if value else "0"))
+        elif fd.type == fd.TYPE_DOUBLE:
+            lines.append(name + "=" + repr(float(value)))
+        else:
+            lines.append(name + "=" + str(int(value)))
+    return "\n".join(lines)
+
+
+def _p(a):
+    return ctypes.c_void_p(a.ctypes.data) if a is not None and a.size else ctypes.c_void_p(None)
+
+
+class Marshalled:
+    def __init__(self, qp):
+        K = sp.csc_matrix(qp.constraint_matrix)
+        K.sum_duplicates()
+        self.m, self.n = K.shape
+        self.cp = np.ascontiguousarray(K.indptr, dtype=np.int64)
+        self.ri = np.ascontiguousarray(K.indices, dtype=np.int64)
+        self.v = np.ascontiguousarray(K.data, dtype=np.float64)
+        f = lambda a: np.ascontiguousarray(np.asarray(a, dtype=np.float64).reshape(-1))
+        self.c = f(qp.objective_vector)
+        self.q = None if qp.objective_matrix is None else f(qp.objective_matrix)
+        self.vlb, self.vub = f(qp.variable_lower_bounds), f(qp.variable_upper_bounds)
+        self.clb, self.cub = f(qp.constraint_lower_bounds), f(qp.constraint_upper_bounds)
+        self.offset, self.scale = float(qp.objective_offset), float(qp.objective_scaling_factor)
+
+    def args(self):
+        return [ctypes.c_int64(self.n), ctypes.c_int64(self.m), ctypes.c_int64(self.v.size), _p(self.cp), _p(self.ri), _p(self.v), _p(self.c),
+                _p(self.q), _p(self.vlb), _p(self.vub), _p(self.clb), _p(self.cub), ctypes.c_double(self.offset), ctypes.c_double(self.scale)]
+
+
+CALLBACK = ctypes.CFUNCTYPE(None, ctypes.c_int, ctypes.c_char_p, ctypes.c_void_p)
+
+
+class OracleResult:
+    pass
+
+
+def solve(qp, params=None, initial_solution=None, callback=None, interrupt=None):
+    lib = load()
+    mar = Marshalled(qp)
+    text = flatten_params(params).encode()
+    x = np.zeros(max(mar.n, 1)); y = np.zeros(max(mar.m, 1)); rc = np.zeros(max(mar.n, 1))
+    sizes = np.zeros(3, dtype=np.int64)
+    log = ctypes.c_char_p()
+    x0 = y0 = None
+    if initial_solution is not None:
+        x0 = np.ascontiguousarray(initial_solution[0], dtype=np.float64)
+        y0 = np.ascontiguousarray(initial_solution[1], dtype=np.float64)
+        if x0.size == 0: x0 = np.zeros(1)
+        if y0.size == 0: y0 = np.zeros(1)
+    cb = None
+    if callback is not None:
+        cb = CALLBACK(lambda t, s, u: callback(t, json.loads(s)))
+    lib.oracle_solve(*mar.args(), text, _p(x0), _p(y0), _p(interrupt) if interrupt is not None else None, cb, None, _p(x), _p(y), _p(rc), _p(sizes),
+                     ctypes.byref(log))
+    r = OracleResult()
+    r.solve_log = json.loads(log.value)
+    r.primal_solution = x[: sizes[0]].copy()
+    r.dual_solution = y[: sizes[1]].copy()
+    r.reduced_costs = rc[: sizes[2]].copy()
+    return r
+
+
+class Problem:
+    """Handle on an oracle ShardedQp for the unit entry points."""
+
+    def __init__(self, qp, num_threads=1, num_shards=1):
+        self.lib = load()
+        self.mar = Marshalled(qp)
+        self.h = ctypes.c_void_p(self.lib.oracle_problem_create(*self.mar.args(), num_threads, num_shards))
+        self.n, self.m = self.mar.n, self.mar.m
+
+    def __del__(self):
+        try:
+            self.lib.oracle_problem_destroy(self.h)
+        except Exception:
+            pass
+
+    def matvec(self, which, v):
+        v = np.ascontiguousarray(v, dtype=np.float64)
+        out = np.zeros(max(self.n if which == 0 else self.m, 1))
+        self.lib.oracle_matvec(self.h, which, _p(v), _p(out))
+        return out[: self.n if which == 0 else self.m]
+
+    def col_norms(self, l2, row_scale, col_scale):
+        rs = np.ascontiguousarray(row_scale, dtype=np.float64); cs = np.ascontiguousarray(col_scale, dtype=np.float64)
+        out = np.zeros(max(self.n, 1))
+        self.lib.oracle_col_norms(self.h, int(l2), _p(rs), _p(cs), _p(out))
+        return out[: self.n]
+
+    def stats(self):
+        s = ctypes.c_char_p()
+        self.lib.oracle_stats(self.h, ctypes.byref(s))
+        return json.loads(s.value)
+
+    def rescale(self, ruiz, l2):
+        rs = np.zeros(max(self.m, 1)); cs = np.zeros(max(self.n, 1))
+        self.lib.oracle_rescale(self.h, int(ruiz), int(l2), _p(rs), _p(cs))
+        return rs[: self.m], cs[: self.n]
+
+    def scaling_vectors(self, which, iters, row_scale, col_scale):
+        rs = np.ascontiguousarray(row_scale, dtype=np.float64).copy(); cs = np.ascontiguousarray(col_scale, dtype=np.float64).copy()
+        self.lib.oracle_scaling_vectors(self.h, int(which), int(iters), _p(rs), _p(cs))
+        return rs, cs
+
+    def get(self):
+        nnz = self.mar.v.size
+        out = dict(val=np.zeros(max(nnz, 1)), c=np.zeros(max(self.n, 1)), q=np.zeros(max(self.n, 1)), vlb=np.zeros(max(self.n, 1)),
+                   vub=np.zeros(max(self.n, 1)), clb=np.zeros(max(self.m, 1)), cub=np.zeros(max(self.m, 1)))
+        self.lib.oracle_problem_get(self.h, _p(out["val"]), _p(out["c"]), _p(out["q"]), _p(out["vlb"]), _p(out["vub"]), _p(out["clb"]), _p(out["cub"]))
+        sizes = dict(val=nnz, c=self.n, q=self.n, vlb=self.n, vub=self.n, clb=self.m, cub=self.m)
+        return {k: v[: sizes[k]] for k, v in out.items()}
+
+    def convergence_info(self, params, col_scale, row_scale, x, y, cw_primal_offset=1.0, cw_dual_offset=1.0, candidate_type=1):
+        f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        s = ctypes.c_char_p()
+        self.lib.oracle_convergence_info(self.h, flatten_params(params).encode(), _p(f(col_scale)), _p(f(row_scale)), _p(f(x)), _p(f(y)),
+                                         ctypes.c_double(cw_primal_offset), ctypes.c_double(cw_dual_offset), candidate_type, ctypes.byref(s))
+        return json.loads(s.value)
+
+    def infeasibility_info(self, params, col_scale, row_scale, x, y, candidate_type=1):
+        f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        s = ctypes.c_char_p()
+        self.lib.oracle_infeasibility_info(self.h, flatten_params(params).encode(), _p(f(col_scale)), _p(f(row_scale)), _p(f(x)), _p(f(y)), candidate_type,
+                                           ctypes.byref(s))
+        return json.loads(s.value)
+
+    def reduced_costs(self, params, x, y, zero_objective=False):
+        f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        rc = np.zeros(max(self.n, 1))
+        self.lib.oracle_reduced_costs(self.h, flatten_params(params).encode(), _p(f(x)), _p(f(y)), int(zero_objective), _p(rc))
+        return rc[: self.n]
+
+    def lagrangian_gradients(self, x, y):
+        f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        pg = np.zeros(max(self.n, 1)); dg = np.zeros(max(self.m, 1)); vals = np.zeros(2)
+        self.lib.oracle_lagrangian_gradients(self.h, _p(f(x)), _p(f(y)), _p(pg), _p(dg), _p(vals))
+        return pg[: self.n], dg[: self.m], vals
+
+    def localized_bounds(self, x, y, norm, primal_weight, radius, use_diagonal=False, tol=1e-8):
+        f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        out = np.zeros(4)
+        self.lib.oracle_localized_bounds(self.h, _p(f(x)), _p(f(y)), int(norm), ctypes.c_double(primal_weight), ctypes.c_double(radius), int(use_diagonal),
+                                         ctypes.c_double(tol), _p(out))
+        return dict(lagrangian_value=out[0], lower_bound=out[1], upper_bound=out[2], radius=out[3])
+
+    def sigma_max(self, rel_err=0.2, fail_prob=0.0005, seed=1):
+        it = ctypes.c_int(0)
+        v = self.lib.oracle_sigma_max(self.h, ctypes.c_double(rel_err), ctypes.c_double(fail_prob), int(seed), ctypes.byref(it))
+        return v, it.value
+
+
+def trust_region(obj, lb, ub, center, w, radius, diag=None, num_shards=1, tol=1e-8):
+    lib = load()
+    f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+    obj, lb, ub, center, w = map(f, (obj, lb, ub, center, w))
+    sol = np.zeros(max(obj.size, 1)); out = np.zeros(2)
+    lib.oracle_trust_region(ctypes.c_int64(obj.size), _p(obj), _p(f(diag)) if diag is not None else None, _p(lb), _p(ub), _p(center), _p(w),
+                            ctypes.c_double(radius), int(num_shards), ctypes.c_double(tol), _p(sol), _p(out))
+    return sol[: obj.size], out[0], out[1]
+
+
+def shard_starts(n, num_shards, masses=None):
+    lib = load()
+    starts = np.zeros(num_shards + 2 + n, dtype=np.int64)
+    ms = None if masses is None else np.ascontiguousarray(masses, dtype=np.int64)
+    k = lib.oracle_shard_starts(ctypes.c_int64(n), int(num_shards), _p(ms) if ms is not None else None, _p(starts))
+    return starts[: k + 1]
+
+
+def validate_params(params):
+    lib = load()
+    s = ctypes.c_char_p()
+    lib.oracle_validate_params(flatten_params(params).encode(), ctypes.byref(s))
+    return s.value.decode()
