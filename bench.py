@@ -1,0 +1,305 @@
+#!/usr/bin/env python
+"""Benchmark of the PDLP hot path (BASELINE.json metric): PDHG iterations/sec, time to
+1e-4 relative KKT, achieved HBM GB/s.
+
+    python bench.py --gpus N --steps K --warmup W [--workload c2|c3|c4|c5] [--impl reference]
+
+A "step" is one PDHG trial step (primal step, K x fused with the dual step, K^T y fused
+with the step-size test, decision, averaging) on the resident problem.
+  value     trial steps / second, problem and iterate resident in HBM, CUDA-event timed
+  e2e       iterations / second of a full solve to eps = 1e-4 through the public API
+            with HOST buffers (upload, transpose, rescaling, checks, download included)
+  roofline  algorithmic bytes per step / measured step time vs the
+            measured HBM copy bandwidth in MEASURED_PEAKS.json, plus a per-kernel table
+  cpu_baseline  the CPU oracle (a restatement of the reference's threaded Sharder path)
+            timed on a bounded number of iterations of the same workload
+`--impl reference` times that CPU path alone.  Multi-GPU (N > 1): independent replicas of
+the per-GPU workload, one process per GPU, no data-path collective yet.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name: (description, generator kwargs at scale 1.0)
+    "c2": "synthetic random sparse LP 1M rows x 2M cols, 1e7 nnz, box bounds, eps=1e-4",
+    "c3": "synthetic multi-commodity network-flow LP, 64 commodities x 65536 nodes x 520000 arcs, ~1e8 nnz, eps=1e-4",
+    "c4": "synthetic diagonal-objective convex QP 5M rows x 10M cols, 5e7 nnz, eps=1e-6",
+    "c5": "synthetic transportation LP (dense bipartite), per-GPU block of 1.25e8 nnz, eps=1e-4",
+}
+
+
+def make_problem(name, scale, seed=0):
+    from pdlp_b200 import synthetic
+    if name == "c2":
+        return synthetic.random_sparse_lp(int(1_000_000 * scale), int(2_000_000 * scale), 5, seed)
+    if name == "c3":
+        side = max(8, int(round(256 * scale ** 0.5)))
+        return synthetic.multicommodity_flow_lp(64, side, int(520000 * scale), 16, seed)
+    if name == "c4":
+        return synthetic.random_sparse_lp(int(5_000_000 * scale), int(10_000_000 * scale), 5, seed, qp_diagonal=True)
+    if name == "c5":
+        s = max(8, int(round(7906 * scale ** 0.5)))  # 7906^2 * 2 = 1.25e8 nnz: one GPU's share of config 5
+        return synthetic.transportation_lp(s, s, seed)
+    raise ValueError(name)
+
+
+def solve_params(name, threads=1, iteration_limit=None):
+    import pdlp_b200
+    p = pdlp_b200.PrimalDualHybridGradientParams()
+    eps = 1e-6 if name == "c4" else 1e-4
+    p.termination_criteria.simple_optimality_criteria.eps_optimal_absolute = eps
+    p.termination_criteria.simple_optimality_criteria.eps_optimal_relative = eps
+    p.num_threads = threads
+    if iteration_limit is not None:
+        p.termination_criteria.iteration_limit = iteration_limit
+    return p
+
+
+def bytes_per_step(n, m, nnz, is_qp):
+    """B_step = 24 nnz + 4 (n + m) + 8 (15 n + 8 m)  [+ 8 n for a QP]."""
+    return 24 * nnz + 4 * (n + m) + 8 * (15 * n + 8 * m) + (8 * n if is_qp else 0)
+
+
+def kernel_bytes(n, m, nnz, is_qp):
+    """Algorithmic bytes of each kernel of one accepted trial step."""
+    return {
+        "primal_step": 8 * (7 * n) + (8 * n if is_qp else 0),
+        "dual_step_Kx": 12 * nnz + 4 * m + 8 * (n + 4 * m),
+        "kty_step_KTy": 12 * nnz + 4 * n + 8 * (4 * n + m),
+        "decide": 0,
+        "average": 8 * (3 * n + 3 * m),
+    }
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device = device
+        self.samples = []
+        self.stop = threading.Event()
+        self.thread = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self.stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-i", str(self.device)],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([t.strip() for t in out.splitlines()[0].split(",")])
+            except Exception:  # noqa: BLE001
+                pass
+            self.stop.wait(0.1)
+
+    def __enter__(self):
+        self.thread.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.thread.join(timeout=6)
+
+    def summary(self):
+        sm = [float(s[1]) for s in self.samples if len(s) >= 8 and s[1].replace(".", "").isdigit()]
+        mx = [float(s[2]) for s in self.samples if len(s) >= 8 and s[2].replace(".", "").isdigit()]
+        reasons = set()
+        for s in self.samples:
+            if len(s) >= 8:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), s[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def cpu_reference_leg(qp, name, threads, iterations):
+    """Times `iterations` PDHG iterations of the CPU oracle (threaded Sharder structure,
+    num_shards = 4 x threads) on the workload; returns iterations / loop second."""
+    import oracle_binding as ob
+    p = solve_params(name, threads=threads, iteration_limit=iterations)
+    t0 = time.time()
+    r = ob.solve(qp, p)
+    wall = time.time() - t0
+    log = r.solve_log
+    loop = max(1e-9, log["solve_time_sec"] - log["preprocessing_time_sec"])
+    its = max(1, log["iteration_count"])
+    return {"value": its / loop, "iterations": its, "loop_seconds": loop, "wall_seconds": wall, "preprocessing_seconds": log["preprocessing_time_sec"]}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=os.environ.get("PDLP_BENCH_WORKLOAD", "c3"), choices=sorted(WORKLOADS))
+    ap.add_argument("--scale", type=float, default=float(os.environ.get("PDLP_BENCH_SCALE", "1.0")), help="shrinks the workload (development only)")
+    ap.add_argument("--cpu-iterations", type=int, default=0, help="iterations of the CPU baseline sample (0 = pick by workload)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    name = args.workload
+    threads = os.cpu_count() or 1
+    cpu_its = args.cpu_iterations or {"c2": 48, "c3": 8, "c4": 12, "c5": 8}[name]
+    config = {"workload": name + ": " + WORKLOADS[name], "scale": args.scale, "seed": 0,
+              "l2_policy": "inputs larger than L2 (matrix + vectors >> 126 MB); no flush between steps"}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        qp = make_problem(name, args.scale)
+        K = qp.constraint_matrix
+        # K steps of the reference-structured CPU path (bounded sample: `steps` capped by cpu_its * (warmup+1)).
+        its = min(args.steps, cpu_its)
+        for _ in range(min(args.warmup, 1)):
+            cpu_reference_leg(qp, name, threads, 2)
+        res = cpu_reference_leg(qp, name, threads, its)
+        line = {
+            "impl": "reference", "metric": "pdhg_iterations_per_sec", "value": res["value"], "unit": "iterations/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 / res["value"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": config,
+            "cpu_baseline": {"value": res["value"], "unit": "iterations/s", "cores": threads, "kind": "port",
+                             "sample": f"{res['iterations']} PDHG iterations of the full workload (n={K.shape[1]}, m={K.shape[0]}, nnz={K.nnz}), loop time only"},
+            "e2e": {"value": res["value"], "unit": "iterations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        }
+        print(json.dumps(line))
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    import pdlp_b200
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    qp = make_problem(name, args.scale, seed=0)
+    K = qp.constraint_matrix
+    m, n = K.shape
+    nnz = K.nnz
+    is_qp = qp.objective_matrix is not None
+    b_step = bytes_per_step(n, m, nnz, is_qp)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- resident kernel-path timing ----
+    dp = pdlp_b200.DeviceProblem(qp, device=local_rank)
+    dp.rescale(5, True)  # the solver iterates on the rescaled problem
+    stats = dp.stats()
+    step0 = 1.0 / max(1e-20, stats.constraint_matrix_abs_max)
+    w0 = stats.objective_vector_l2_norm / stats.combined_bounds_l2_norm if stats.objective_vector_l2_norm > 0 and stats.combined_bounds_l2_norm > 0 else 1.0
+    x, y, st, _, _ = dp.trial_steps(args.warmup, step0, w0)
+    barrier()
+    with ClockSampler(local_rank) as clocks:
+        # keep sampling for at least ~0.5 s so the clocks line has data
+        t_begin = time.time()
+        x2, y2, st2, seconds, launches = dp.trial_steps(args.steps, st["step_size"], w0, x, y)
+        barrier()
+        extra_runs = 0
+        while time.time() - t_begin < 0.6:
+            dp.trial_steps(args.steps, st["step_size"], w0, x, y)
+            extra_runs += 1
+    t = torch.tensor([seconds], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    seconds_max = float(t.item())
+    steps_per_sec = world * args.steps / seconds_max
+    # per-kernel breakdown (second pass with CUDA events around every launch)
+    breakdown = dp.trial_steps_profiled(args.steps, st["step_size"], w0, x, y)
+    kb = kernel_bytes(n, m, nnz, is_qp)
+    peak, peak_kind = measured_peak()
+    kernels = []
+    for kname, sec in breakdown.items():
+        kernels.append({"kernel": kname, "us_per_launch": sec * 1e6, "algorithmic_bytes": kb[kname],
+                        "achieved_gbs": kb[kname] / sec / 1e9 if sec > 0 else None, "share": None})
+    total_k = sum(k["us_per_launch"] for k in kernels)
+    for k in kernels:
+        k["share"] = k["us_per_launch"] / total_k if total_k > 0 else None
+    dominant = max(kernels, key=lambda k: k["us_per_launch"])
+    step_gbs = b_step * args.steps / seconds / 1e9
+
+    # ---- end-to-end solve from host buffers ----
+    e2e = None
+    solve_info = {}
+    if not args.no_e2e:
+        p = solve_params(name)
+        barrier()
+        t0 = time.time()
+        result = pdlp_b200.primal_dual_hybrid_gradient(qp, p, device=local_rank)
+        torch.cuda.synchronize()
+        wall = time.time() - t0
+        tw = torch.tensor([wall], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tw, op=dist.ReduceOp.MAX)
+        wall_max = float(tw.item())
+        its = result.solve_log.iteration_count
+        counters = pdlp_b200.last_solve_counters()
+        h2d = 16 * nnz + 8 * (n + 1) + 8 * (3 * n + 2 * m) + (8 * n if is_qp else 0)
+        d2h = 8 * (2 * n + m)
+        ci = result.solve_log.solution_stats.convergence_information
+        e2e = {"value": world * its / wall_max, "unit": "iterations/s", "h2d_bytes_per_step": h2d / max(1, its), "d2h_bytes_per_step": d2h / max(1, its),
+               "time_to_tolerance_sec": wall_max, "iterations": its, "termination_reason": int(result.solve_log.termination_reason),
+               "h2d_bytes_per_solve": h2d, "d2h_bytes_per_solve": d2h}
+        solve_info = {"solve_iterations": its, "solve_trial_steps": counters.get("trial_steps"), "solve_wall_sec": wall_max,
+                      "solve_setup_sec": counters.get("setup_seconds"), "solve_loop_sec": counters.get("loop_seconds"),
+                      "solve_device_loop_sec": counters.get("device_loop_seconds"), "solve_kernel_launches": counters.get("kernel_launches"),
+                      "primal_objective": ci[0].primal_objective if len(ci) else None,
+                      "relative_kkt_eps": 1e-6 if name == "c4" else 1e-4}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        res = cpu_reference_leg(qp, name, threads, cpu_its)
+        cpu = {"value": res["value"], "unit": "iterations/s", "cores": threads, "kind": "port",
+               "sample": f"{res['iterations']} PDHG iterations of the same workload by the CPU oracle (reference's threaded Sharder structure, "
+                         f"num_shards = 4 x {threads}); loop time {res['loop_seconds']:.2f} s, preprocessing {res['preprocessing_seconds']:.2f} s excluded"}
+
+    if rank == 0:
+        line = {
+            "metric": "pdhg_iterations_per_sec", "value": steps_per_sec, "unit": "iterations/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * seconds_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": dict(config, n=n, m=m, nnz=int(nnz), parallelism="1 GPU" if world == 1 else f"{world} independent replicas"),
+            "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": step_gbs, "peak": peak, "unit": "GB/s", "frac": step_gbs / peak, "traffic": None,
+                         "peak_kind": peak_kind, "unit_of_work": "one PDHG trial step (5 kernels)", "algorithmic_bytes_per_step": b_step,
+                         "dominant_kernel": dominant["kernel"], "dominant_kernel_achieved": dominant["achieved_gbs"],
+                         "dominant_kernel_frac": (dominant["achieved_gbs"] or 0) / peak, "kernels": kernels},
+            "cpu_baseline": cpu,
+            "accepted_steps_in_timed_region": st2["iterations_completed"], "rejected_steps_in_timed_region": st2["num_rejected_steps"],
+        }
+        line.update(solve_info)
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

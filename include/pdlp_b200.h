@@ -153,6 +153,12 @@ pdlp_b200_status pdlp_b200_localized_bounds(pdlp_b200_device_problem* h, const d
 pdlp_b200_status pdlp_b200_trial_steps(pdlp_b200_device_problem* h, int steps, double step_size, double primal_weight, double* x /*n, in-out*/,
                                        double* y /*m, in-out*/, double* state_out /*5*/, double* seconds, long long* launches);
 
+/* Same as pdlp_b200_trial_steps with a CUDA event recorded around every launch:
+ * kernel_seconds = average duration of {primal_step, dual_step (K x), kty_step (K^T y),
+ * decide, average}.  For the per-kernel roofline table of bench.py. */
+pdlp_b200_status pdlp_b200_trial_steps_profiled(pdlp_b200_device_problem* h, int steps, double step_size, double primal_weight, const double* x,
+                                                const double* y, double* kernel_seconds /*5*/);
+
 #ifdef __cplusplus
 }
 #endif

@@ -473,8 +473,27 @@ pdlp_b200_status pdlp_b200_localized_bounds(pdlp_b200_device_problem* h, const d
   });
 }
 
+static pdlp_b200_status TrialStepsImpl(pdlp_b200_device_problem* h, int steps, double step_size, double primal_weight, double* x, double* y,
+                                       double* state_out, double* seconds, long long* launches, double* kernel_seconds);
+
 pdlp_b200_status pdlp_b200_trial_steps(pdlp_b200_device_problem* h, int steps, double step_size, double primal_weight, double* x, double* y,
                                        double* state_out, double* seconds, long long* launches) {
+  return TrialStepsImpl(h, steps, step_size, primal_weight, x, y, state_out, seconds, launches, nullptr);
+}
+
+pdlp_b200_status pdlp_b200_trial_steps_profiled(pdlp_b200_device_problem* h, int steps, double step_size, double primal_weight, const double* x,
+                                                const double* y, double* kernel_seconds) {
+  if (kernel_seconds == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "kernel_seconds is null");
+  std::vector<double> xs, ys;
+  double* xp = nullptr;
+  double* yp = nullptr;
+  if (h != nullptr && x != nullptr) { xs.assign(x, x + h->pre->problem().n); xp = xs.data(); }
+  if (h != nullptr && y != nullptr) { ys.assign(y, y + h->pre->problem().m); yp = ys.data(); }
+  return TrialStepsImpl(h, steps, step_size, primal_weight, xp, yp, nullptr, nullptr, nullptr, kernel_seconds);
+}
+
+static pdlp_b200_status TrialStepsImpl(pdlp_b200_device_problem* h, int steps, double step_size, double primal_weight, double* x, double* y,
+                                       double* state_out, double* seconds, long long* launches, double* kernel_seconds) {
   return Guard([&]() -> pdlp_b200_status {
     if (h == nullptr || steps < 0) return Fail(PDLP_B200_BAD_ARGUMENT, "bad argument");
     PDLP_CUDA_CHECK(cudaSetDevice(h->device));
@@ -508,9 +527,12 @@ pdlp_b200_status pdlp_b200_trial_steps(pdlp_b200_device_problem* h, int steps, d
     PDLP_CUDA_CHECK(cudaEventCreate(&e0));
     PDLP_CUDA_CHECK(cudaEventCreate(&e1));
     const long long before = ws.launches;
+    std::vector<cudaEvent_t> marks;
+    if (kernel_seconds != nullptr) ws.profile = &marks;
     PDLP_CUDA_CHECK(cudaEventRecord(e0, ws.stream));
     EnqueueAdaptiveTrials(ws, p, it, steps, false);
     PDLP_CUDA_CHECK(cudaEventRecord(e1, ws.stream));
+    ws.profile = nullptr;
     PDLP_CUDA_CHECK(cudaMemcpyAsync(&st, it.state.get(), sizeof(st), cudaMemcpyDeviceToHost, ws.stream));
     ws.Sync();
     float ms = 0;
@@ -519,6 +541,19 @@ pdlp_b200_status pdlp_b200_trial_steps(pdlp_b200_device_problem* h, int steps, d
     cudaEventDestroy(e1);
     if (seconds != nullptr) *seconds = ms * 1e-3;
     if (launches != nullptr) *launches = ws.launches - before;
+    if (kernel_seconds != nullptr) {
+      // 6 marks per trial: before K1, after K1, K2, K3, K4, K5.
+      for (int k = 0; k < 5; ++k) kernel_seconds[k] = 0.0;
+      const int trials = static_cast<int>(marks.size() / 6);
+      for (int t = 0; t < trials; ++t)
+        for (int k = 0; k < 5; ++k) {
+          float kms = 0;
+          PDLP_CUDA_CHECK(cudaEventElapsedTime(&kms, marks[6 * t + k], marks[6 * t + k + 1]));
+          kernel_seconds[k] += kms * 1e-3;
+        }
+      for (int k = 0; k < 5; ++k) kernel_seconds[k] /= (trials > 0 ? trials : 1);
+      for (cudaEvent_t e : marks) cudaEventDestroy(e);
+    }
     if (x != nullptr) it.x[st.cur].Download(x, p.n, ws.stream);
     if (y != nullptr) it.y[st.cur].Download(y, p.m, ws.stream);
     ws.Sync();

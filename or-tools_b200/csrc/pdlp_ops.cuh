@@ -33,6 +33,7 @@ struct Workspace {
   DVec scratch_n[3], scratch_m[3], scratch_nm[2];  // sized n, m, n+m on demand
   int64_t n = 0, m = 0;
   long long launches = 0;    // kernels launched (bench "gpu_launches")
+  std::vector<cudaEvent_t>* profile = nullptr;  // when set, the trial-step launcher records an event around every kernel
   void Init(int64_t n_, int64_t m_);
   void Destroy();
   void Sync() { PDLP_CUDA_CHECK(cudaStreamSynchronize(stream)); }

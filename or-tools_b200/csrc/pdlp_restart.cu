@@ -82,20 +82,7 @@ __device__ __forceinline__ double PrimalGradAt(double xj, double cj, const doubl
   *value = xj * (g - 0.5 * qx);
   return g;
 }
-struct PrimalGradRowsOp : AlwaysActive, OneSumSlot {  // K^T y computed here
-  const double* val; const int* idx; const double* y;
-  const double* x; const double* c; const double* q; double* gx;
-  __device__ double Load(int64_t k) const { return val[k] * y[idx[k]]; }
-  __device__ double RowInit() const { return 0.0; }
-  __device__ double RowAdd(double acc, double staged, int) const { return acc + staged; }
-  __device__ double RowMerge(double a, double b) const { return a + b; }
-  __device__ void RowFinish(int j, double kty, Slots<1>& r) const {
-    double v;
-    gx[j] = PrimalGradAt(x[j], c[j], q, j, kty, &v);
-    r.v[0] += v;
-  }
-};
-struct PrimalGradMapOp : AlwaysActive, OneSumSlot {  // K^T y cached
+struct PrimalGradMapOp : AlwaysActive, OneSumSlot {
   const double* kty; const double* x; const double* c; const double* q; double* gx;
   __device__ void Apply(int64_t j, Slots<1>& r) const {
     double v;
@@ -188,8 +175,16 @@ LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProb
   double primal_value = 0.0, dual_value = 0.0;
   if (p.m > 0) dual_value = RunRows(ws, DualGradOp{{}, {}, csr.val.get(), csr.idx.get(), x, y, p.clb.get(), p.cub.get(), gy}, csr)[0];
   if (p.n > 0) {
-    if (kty_or_null != nullptr) primal_value = RunMap(ws, PrimalGradMapOp{{}, {}, kty_or_null, x, p.c.get(), p.q_or_null(), gx}, p.n)[0];
-    else primal_value = RunRows(ws, PrimalGradRowsOp{{}, {}, csc.val.get(), csc.idx.get(), y, x, p.c.get(), p.q_or_null(), gx}, csc)[0];
+    // When K^T y is not cached it is computed first; the gradient and its value then come
+    // from the same kernel either way, so "bounds at the average" and "bounds at the
+    // current point" are bit-identical whenever the two points are (the reference's
+    // strict-inequality tie-break in AverageHasBetterPotential relies on that).
+    const double* kty = kty_or_null;
+    if (kty == nullptr) {
+      RowDot(ws, csc, y, ws.scratch_n[1].get());
+      kty = ws.scratch_n[1].get();
+    }
+    primal_value = RunMap(ws, PrimalGradMapOp{{}, {}, kty, x, p.c.get(), p.q_or_null(), gx}, p.n)[0];
   }
   const double lagrangian = primal_value + dual_value;
   const int64_t total = p.n + p.m;

@@ -337,13 +337,26 @@ void EnqueueAdaptiveTrials(Workspace& ws, const DeviceProblem& p, Iterate& it, i
   DualStepOp k2{{}, st, csr.val.get(), csr.idx.get(), it.xbar.get(), it.y[0].get(), it.y[1].get(), p.clb.get(), p.cub.get()};
   KtyStepOp k3{st, csc.val.get(), csc.idx.get(), it.y[0].get(), it.y[1].get(), it.x[0].get(), it.x[1].get(), it.kty[0].get(), it.kty[1].get()};
   AverageOp k5{{}, st, it.x[0].get(), it.x[1].get(), it.y[0].get(), it.y[1].get(), it.avg_x.get(), it.avg_y.get(), p.n};
+  auto mark = [&]() {
+    if (ws.profile == nullptr) return;
+    cudaEvent_t e;
+    PDLP_CUDA_CHECK(cudaEventCreate(&e));
+    PDLP_CUDA_CHECK(cudaEventRecord(e, ws.stream));
+    ws.profile->push_back(e);
+  };
   for (int t = 0; t < trials; ++t) {
+    mark();
     const int g1 = EnqueueMap(ws, k1, p.n, 0);
+    mark();
     const int g2 = EnqueueRows(ws, k2, csr, 1);
+    mark();
     const int g3 = EnqueueRows(ws, k3, csc, 2);
+    mark();
     decide_adaptive_kernel<<<1, kBlock, 0, ws.stream>>>(st, ws.partials[0].get(), g1, ws.partials[1].get(), g2, ws.partials[2].get(), g3, constant_step ? 1 : 0);
     ++ws.launches;
+    mark();
     EnqueueMap(ws, k5, p.n + p.m, 0);
+    mark();
   }
   PDLP_CUDA_CHECK(cudaGetLastError());
 }

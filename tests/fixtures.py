@@ -39,7 +39,7 @@ def tiny_lp():
 
 
 def correlation_clustering_lp():
-    # optimum 1: x = [1, 1, 0, 1, 0, 1] (test_util.h:80-88)
+    # optimum 1: x = [1, 1, 0, 1, 0, 0], multiple optimal duals (test_util.h:70-88)
     return _qp(6, 3, [(0, 1, -1), (0, 2, 1), (0, 5, -1), (1, 3, -1), (1, 4, 1), (1, 5, -1), (2, 0, -1), (2, 1, -1), (2, 3, 1)],
                [-1, -1, 1, -1, 1, -1], [-1, -1, -1], [INF] * 3, [0] * 6, [1] * 6, offset=4)
 
