@@ -82,7 +82,7 @@ EXPORTED_SYMBOLS = [
     "pdlp_b200_solve", "pdlp_b200_validate_params", "pdlp_b200_default_params", "pdlp_b200_describe_schema",
     "pdlp_b200_last_error", "pdlp_b200_free", "pdlp_b200_problem_create", "pdlp_b200_problem_destroy",
     "pdlp_b200_matvec", "pdlp_b200_scaled_norms", "pdlp_b200_stats", "pdlp_b200_rescale", "pdlp_b200_kkt_stats",
-    "pdlp_b200_reduced_costs", "pdlp_b200_localized_bounds", "pdlp_b200_trial_steps",
+    "pdlp_b200_reduced_costs", "pdlp_b200_localized_bounds", "pdlp_b200_trial_steps", "pdlp_b200_trial_steps_profiled",
 ]
 
 

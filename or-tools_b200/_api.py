@@ -349,3 +349,11 @@ class DeviceProblem:
                                           ctypes.byref(sec), ctypes.byref(launches)))
         state = dict(step_size=st[0], iterations_completed=int(st[1]), num_rejected_steps=int(st[2]), last_movement=st[3], last_nonlinearity=st[4])
         return x[: self.n], y[: self.m], state, sec.value, launches.value
+
+    def trial_steps_profiled(self, steps, step_size, primal_weight, x=None, y=None):
+        """Average seconds per launch of the five kernels of a trial step (CUDA events around each)."""
+        x = np.zeros(max(self.n, 1)) if x is None else _f64(x)
+        y = np.zeros(max(self.m, 1)) if y is None else _f64(y)
+        ks = np.zeros(5)
+        _check(_lib.pdlp_b200_trial_steps_profiled(self._h, int(steps), ctypes.c_double(step_size), ctypes.c_double(primal_weight), _vptr(x), _vptr(y), _vptr(ks)))
+        return dict(zip(("primal_step", "dual_step_Kx", "kty_step_KTy", "decide", "average"), ks.tolist()))
