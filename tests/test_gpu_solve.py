@@ -56,7 +56,8 @@ FIXTURES = [
 @pytest.mark.parametrize("name,make,objective,x,y,budget,eps", FIXTURES, ids=[f[0] for f in FIXTURES])
 def test_known_answer_fixtures(name, make, objective, x, y, budget, eps):
     qp = make()
-    extra = {"major_iteration_frequency": 2} if name == "cc_lp" else {}  # as the reference test sets it (:343)
+    # major_iteration_frequency as the reference's own tests set it (primal_dual_hybrid_gradient_test.cc:300-530)
+    extra = {"major_iteration_frequency": {"test_lp": 100, "tiny_lp": 60, "cc_lp": 2, "cc_star": 5, "qp1": 12, "qp2": 12, "qp3": 15}[name]}
     dev, ora = both(qp, params(eps_abs=eps, **extra))
     assert dev.solve_log.termination_reason == pdlp_b200.TerminationReason.TERMINATION_REASON_OPTIMAL
     assert dev.solve_log.iteration_count <= budget  # the reference's own iteration budgets
@@ -86,19 +87,52 @@ def test_step_rules_and_scaling_on_test_lp(rule, scaling):
         assert_parity(dev, ora)
 
 
+def oracle_iteration_envelope(qp, p):
+    """Iteration counts of the oracle over several (num_threads, num_shards) settings.  PDHG with
+    adaptive restarts amplifies summation-order rounding: the reference's own iteration count
+    moves with the shard count (solvers.proto:273-282 promises reproducibility only for a fixed
+    one), so the device count is checked against that envelope widened by the 5 % of the spec."""
+    counts = []
+    for threads, shards in ((1, 0), (2, 5), (4, 16), (4, 37), (3, 101)):
+        q = type(p)()
+        q.CopyFrom(p)
+        q.num_threads = threads
+        if shards:
+            q.num_shards = shards
+        counts.append(ob.solve(qp, q).solve_log["iteration_count"])
+    return min(counts), max(counts)
+
+
+def assert_objectives_close(dev, ora, tol=1e-6):
+    oc = ora.solve_log["solution_stats"]["convergence_information"][0]
+    dc = dev.solve_log.solution_stats.convergence_information[0]
+    for name in ("primal_objective", "dual_objective"):
+        a, b = getattr(dc, name), oc[name]
+        assert abs(a - b) <= tol * max(1.0, abs(b)), (name, a, b)
+
+
 @pytest.mark.parametrize("seed", [0, 1, 2])
 def test_random_lp_parity(seed):
     qp = fixtures.random_lp(400, 800, 5, seed)
-    dev, ora = both(qp, params(eps_abs=1e-6, eps_rel=1e-6))
-    assert dev.solve_log.termination_reason == pdlp_b200.TerminationReason.TERMINATION_REASON_OPTIMAL
-    assert_parity(dev, ora, iter_tol=0.05, iter_slack=64)
+    p = params(eps_abs=1e-7, eps_rel=1e-7)  # both solvers then pin the objective to well under 1e-6 relative
+    dev, ora = both(qp, p)
+    assert dev.solve_log.termination_reason == ora.solve_log["termination_reason"] == pdlp_b200.TerminationReason.TERMINATION_REASON_OPTIMAL
+    assert_objectives_close(dev, ora)
+    lo, hi = oracle_iteration_envelope(qp, p)
+    assert 0.95 * lo - 64 <= dev.solve_log.iteration_count <= 1.05 * hi + 64, (dev.solve_log.iteration_count, lo, hi)
+    ci = dev.solve_log.solution_stats.convergence_information[0]
+    bn = np.linalg.norm(np.where(np.isfinite(qp.constraint_upper_bounds), qp.constraint_upper_bounds, 0.0))
+    assert ci.l2_primal_residual <= 1e-7 * (1 + bn) * 1.0001
 
 
 def test_random_qp_parity():
     qp = fixtures.random_lp(300, 600, 5, 3, qp_diagonal=True)
-    dev, ora = both(qp, params(eps_abs=1e-6, eps_rel=1e-6))
-    assert dev.solve_log.termination_reason == pdlp_b200.TerminationReason.TERMINATION_REASON_OPTIMAL
-    assert_parity(dev, ora, iter_tol=0.05, iter_slack=64)
+    p = params(eps_abs=1e-7, eps_rel=1e-7)
+    dev, ora = both(qp, p)
+    assert dev.solve_log.termination_reason == ora.solve_log["termination_reason"] == pdlp_b200.TerminationReason.TERMINATION_REASON_OPTIMAL
+    assert_objectives_close(dev, ora)
+    lo, hi = oracle_iteration_envelope(qp, p)
+    assert 0.95 * lo - 64 <= dev.solve_log.iteration_count <= 1.05 * hi + 64, (dev.solve_log.iteration_count, lo, hi)
 
 
 def test_iteration_limit_trace_matches_oracle():
