@@ -142,7 +142,7 @@ def cpu_reference_leg(qp, name, threads, iterations):
     t0 = time.time()
     r = ob.solve(qp, p)
     wall = time.time() - t0
-    log = r.solve_log
+    log = r.solve_log_dict
     loop = max(1e-9, log["solve_time_sec"] - log["preprocessing_time_sec"])
     its = max(1, log["iteration_count"])
     return {"value": its / loop, "iterations": its, "loop_seconds": loop, "wall_seconds": wall, "preprocessing_seconds": log["preprocessing_time_sec"]}

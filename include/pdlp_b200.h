@@ -57,7 +57,9 @@ typedef struct {
 } pdlp_b200_problem;
 
 /* IterationCallbackInfo (primal_dual_hybrid_gradient.h:62-93): iteration_type is the
- * IterationType enum value; iteration_stats is a serialized IterationStats message;
+ * IterationType enum value in the reference's order (:70-83: 0 kNormal, 1 kPrimalFeasibility,
+ * 2 kDualFeasibility, 3 kPresolveTermination, 4 kNormalTermination,
+ * 5 kFeasibilityPolishingTermination); iteration_stats is a serialized IterationStats message;
  * bound_norms = {l2_norm_primal_linear_objective, l2_norm_constraint_bounds,
  * l_inf_norm_primal_linear_objective, l_inf_norm_constraint_bounds}.  Runs synchronously
  * on the calling thread at every termination check and once at exit; it may set the

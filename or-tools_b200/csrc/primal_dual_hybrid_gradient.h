@@ -82,10 +82,10 @@ enum class IterationType {
   kNormal = 0,
   kPrimalFeasibility = 1,
   kDualFeasibility = 2,
-  kNormalTermination = 3,
-  kFeasibilityPolishingTermination = 4,
-  kPresolveTermination = 5,
-};
+  kPresolveTermination = 3,  // never produced here: Glop presolve is outside the device path
+  kNormalTermination = 4,
+  kFeasibilityPolishingTermination = 5,
+};  // enumerator order = the reference's (primal_dual_hybrid_gradient.h:70-83)
 struct IterationCallbackInfo {
   IterationType iteration_type;
   TerminationCriteria termination_criteria;

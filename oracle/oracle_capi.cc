@@ -89,7 +89,14 @@ std::string J(const QpStats& s) {
       .num("objective_matrix_abs_min", s.objective_matrix_abs_min).num("objective_matrix_abs_avg", s.objective_matrix_abs_avg).num("objective_matrix_l2_norm", s.objective_matrix_l2_norm).done();
 }
 std::string J(const FeasibilityPolishingDetails& d) {
-  return Obj().i64("polishing_phase_type", d.polishing_phase_type).i64("main_iteration_count", d.main_iteration_count).i64("termination_reason", d.termination_reason)
+  const DetailedCriteria& c = d.detailed_criteria;
+  const std::string detailed = Obj().num("eps_optimal_primal_residual_absolute", c.eps_optimal_primal_residual_absolute)
+      .num("eps_optimal_primal_residual_relative", c.eps_optimal_primal_residual_relative).num("eps_optimal_dual_residual_absolute", c.eps_optimal_dual_residual_absolute)
+      .num("eps_optimal_dual_residual_relative", c.eps_optimal_dual_residual_relative).num("eps_optimal_objective_gap_absolute", c.eps_optimal_objective_gap_absolute)
+      .num("eps_optimal_objective_gap_relative", c.eps_optimal_objective_gap_relative).done();
+  const std::string criteria = Obj().raw("detailed_optimality_criteria", detailed).i64("iteration_limit", d.iteration_limit).done();
+  return Obj().i64("polishing_phase_type", d.polishing_phase_type).i64("main_iteration_count", d.main_iteration_count)
+      .raw("params", Obj().raw("termination_criteria", criteria).done()).i64("termination_reason", d.termination_reason)
       .i64("iteration_count", d.iteration_count).num("solve_time_sec", d.solve_time_sec).raw("solution_stats", J(d.solution_stats)).i64("solution_type", d.solution_type)
       .raw("iteration_stats", Arr(d.iteration_stats, [](const IterationStats& s) { return J(s); })).done();
 }

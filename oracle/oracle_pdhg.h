@@ -17,7 +17,8 @@
 
 namespace oracle {
 
-enum class IterationType { kNormal = 0, kPrimalFeasibility = 1, kDualFeasibility = 2, kNormalTermination = 3, kFeasibilityPolishingTermination = 4, kPresolveTermination = 5 };
+// primal_dual_hybrid_gradient.h:70-83 (same enumerator order).
+enum class IterationType { kNormal = 0, kPrimalFeasibility = 1, kDualFeasibility = 2, kPresolveTermination = 3, kNormalTermination = 4, kFeasibilityPolishingTermination = 5 };
 
 struct SolverResult { Vec primal_solution, dual_solution, reduced_costs; SolveLog solve_log; };
 struct IterationCallbackInfo { IterationType iteration_type; const TerminationCriteria* termination_criteria; const IterationStats* iteration_stats; const BoundNorms* bound_norms; };

@@ -243,10 +243,12 @@ inline IterationStats Solver::TotalWorkSoFar(const SolveLog& log) const {  // :2
   return AddWorkStats(CreateSimpleIterationStats(RESTART_CHOICE_NO_RESTART), WorkFromFeasibilityPolishing(log));
 }
 
-inline FeasibilityPolishingDetails BuildFeasibilityPolishingDetails(int phase, int main_iterations, const SolveLog& log) {  // :2415-2431
+inline FeasibilityPolishingDetails BuildFeasibilityPolishingDetails(int phase, int main_iterations, const Params& params, const SolveLog& log) {  // :2415-2431
   FeasibilityPolishingDetails d;
   d.polishing_phase_type = phase;
   d.main_iteration_count = main_iterations;
+  d.detailed_criteria = params.termination_criteria.detailed;  // the part of `params` the phase changes
+  d.iteration_limit = params.termination_criteria.iteration_limit;
   d.termination_reason = log.termination_reason;
   d.iteration_count = log.iteration_count;
   d.solve_time_sec = log.solve_time_sec;
@@ -307,7 +309,7 @@ inline SolverResult Solver::TryPrimalPolishing(Vec x_start, int iteration_limit,
   SolverResult r = sub.Solve(IterationType::kPrimalFeasibility, interrupt, sub_log);
   timer_.Start();
   pre_->sq().SwapObjectiveVector(objective);
-  log.feasibility_polishing_details.push_back(BuildFeasibilityPolishingDetails(POLISHING_PHASE_TYPE_PRIMAL_FEASIBILITY, iterations_completed_, r.solve_log));
+  log.feasibility_polishing_details.push_back(BuildFeasibilityPolishingDetails(POLISHING_PHASE_TYPE_PRIMAL_FEASIBILITY, iterations_completed_, p, r.solve_log));
   return r;
 }
 
@@ -332,7 +334,7 @@ inline SolverResult Solver::TryDualPolishing(Vec y_start, int iteration_limit, c
   timer_.Start();
   pre_->sq().SwapConstraintBounds(clb, cub);
   pre_->sq().SwapVariableBounds(vlb, vub);
-  log.feasibility_polishing_details.push_back(BuildFeasibilityPolishingDetails(POLISHING_PHASE_TYPE_DUAL_FEASIBILITY, iterations_completed_, r.solve_log));
+  log.feasibility_polishing_details.push_back(BuildFeasibilityPolishingDetails(POLISHING_PHASE_TYPE_DUAL_FEASIBILITY, iterations_completed_, p, r.solve_log));
   return r;
 }
 

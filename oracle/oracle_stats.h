@@ -104,6 +104,8 @@ struct IterationStats {
 struct SolveLog;
 struct FeasibilityPolishingDetails {
   int polishing_phase_type = 0, main_iteration_count = 0;
+  DetailedCriteria detailed_criteria;  // params.termination_criteria.detailed_optimality_criteria of the phase
+  int32_t iteration_limit = 0;         // params.termination_criteria.iteration_limit of the phase
   int termination_reason = 0, iteration_count = 0;
   double solve_time_sec = 0;
   IterationStats solution_stats;

@@ -17,8 +17,8 @@ p.record_iteration_stats = True
 qp = fixtures.random_lp(400, 800, 5, seed) if which == "random" else getattr(fixtures, which)()
 dev = pdlp_b200.primal_dual_hybrid_gradient(qp, p)
 ora = ob.solve(qp, p)
-ds, os_ = dev.solve_log.iteration_stats, ora.solve_log["iteration_stats"]
-print("dev", dev.solve_log.termination_reason, dev.solve_log.iteration_count, "ora", ora.solve_log["termination_reason"], ora.solve_log["iteration_count"])
+ds, os_ = dev.solve_log.iteration_stats, ora.solve_log_dict["iteration_stats"]
+print("dev", dev.solve_log.termination_reason, dev.solve_log.iteration_count, "ora", ora.solve_log_dict["termination_reason"], ora.solve_log_dict["iteration_count"])
 shown = 0
 for d, o in zip(ds, os_):
     rel = abs(d.step_size - o["step_size"]) / o["step_size"]

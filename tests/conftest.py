@@ -11,3 +11,11 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+@pytest.fixture(params=["oracle", pytest.param("device", marks=pytest.mark.gpu)])
+def backend(request):
+    """The reference's test cases run against both drivers: the CPU oracle here, the CUDA
+    path on the GPU box (tests/backends.py)."""
+    import backends
+    return backends.make(request.param)

@@ -51,6 +51,10 @@ def flatten_params(msg, prefix=""):
     return "\n".join(lines)
 
 
+def _f(a):
+    return np.ascontiguousarray(np.asarray(a, dtype=np.float64).reshape(-1))
+
+
 def _p(a):
     return ctypes.c_void_p(a.ctypes.data) if a is not None and a.size else ctypes.c_void_p(None)
 
@@ -82,6 +86,37 @@ class OracleResult:
     pass
 
 
+def to_proto(d, msg):
+    """JSON dict printed by the oracle (proto field names as keys) -> protobuf message."""
+    fields = msg.DESCRIPTOR.fields_by_name
+    for k, v in d.items():
+        fd = fields[k]
+        rep = fd.is_repeated if hasattr(fd, "is_repeated") else fd.label == fd.LABEL_REPEATED
+        if fd.type == fd.TYPE_MESSAGE:
+            if rep:
+                for item in v:
+                    to_proto(item, getattr(msg, k).add())
+            else:
+                sub = getattr(msg, k)
+                sub.SetInParent()
+                to_proto(v, sub)
+        elif rep:
+            getattr(msg, k).extend(v)
+        elif fd.type == fd.TYPE_STRING and v == "" and k == "instance_name":
+            continue  # unnamed problems leave the field unset (primal_dual_hybrid_gradient_test.cc:746)
+        else:
+            setattr(msg, k, v)
+    return msg
+
+
+def _solve_log_proto(d, params):
+    import pdlp_b200
+    log = to_proto(d, pdlp_b200.SolveLog())
+    if params is not None and log.termination_reason not in (9, 10, 13):
+        log.params.CopyFrom(params)  # the oracle echoes nothing; SolverResult.solve_log.params is the caller's
+    return log
+
+
 def solve(qp, params=None, initial_solution=None, callback=None, interrupt=None):
     lib = load()
     mar = Marshalled(qp)
@@ -101,7 +136,8 @@ def solve(qp, params=None, initial_solution=None, callback=None, interrupt=None)
     lib.oracle_solve(*mar.args(), text, _p(x0), _p(y0), _p(interrupt) if interrupt is not None else None, cb, None, _p(x), _p(y), _p(rc), _p(sizes),
                      ctypes.byref(log))
     r = OracleResult()
-    r.solve_log = json.loads(log.value)
+    r.solve_log_dict = json.loads(log.value)
+    r.solve_log = _solve_log_proto(r.solve_log_dict, params)
     r.primal_solution = x[: sizes[0]].copy()
     r.dual_solution = y[: sizes[1]].copy()
     r.reduced_costs = rc[: sizes[2]].copy()
@@ -159,35 +195,35 @@ class Problem:
         return {k: v[: sizes[k]] for k, v in out.items()}
 
     def convergence_info(self, params, col_scale, row_scale, x, y, cw_primal_offset=1.0, cw_dual_offset=1.0, candidate_type=1):
-        f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        col_scale, row_scale, x, y = map(_f, (col_scale, row_scale, x, y))  # named: the arrays must outlive the call
         s = ctypes.c_char_p()
-        self.lib.oracle_convergence_info(self.h, flatten_params(params).encode(), _p(f(col_scale)), _p(f(row_scale)), _p(f(x)), _p(f(y)),
+        self.lib.oracle_convergence_info(self.h, flatten_params(params).encode(), _p(col_scale), _p(row_scale), _p(x), _p(y),
                                          ctypes.c_double(cw_primal_offset), ctypes.c_double(cw_dual_offset), candidate_type, ctypes.byref(s))
         return json.loads(s.value)
 
     def infeasibility_info(self, params, col_scale, row_scale, x, y, candidate_type=1):
-        f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        col_scale, row_scale, x, y = map(_f, (col_scale, row_scale, x, y))
         s = ctypes.c_char_p()
-        self.lib.oracle_infeasibility_info(self.h, flatten_params(params).encode(), _p(f(col_scale)), _p(f(row_scale)), _p(f(x)), _p(f(y)), candidate_type,
+        self.lib.oracle_infeasibility_info(self.h, flatten_params(params).encode(), _p(col_scale), _p(row_scale), _p(x), _p(y), candidate_type,
                                            ctypes.byref(s))
         return json.loads(s.value)
 
     def reduced_costs(self, params, x, y, zero_objective=False):
-        f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        x, y = _f(x), _f(y)
         rc = np.zeros(max(self.n, 1))
-        self.lib.oracle_reduced_costs(self.h, flatten_params(params).encode(), _p(f(x)), _p(f(y)), int(zero_objective), _p(rc))
+        self.lib.oracle_reduced_costs(self.h, flatten_params(params).encode(), _p(x), _p(y), int(zero_objective), _p(rc))
         return rc[: self.n]
 
     def lagrangian_gradients(self, x, y):
-        f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        x, y = _f(x), _f(y)
         pg = np.zeros(max(self.n, 1)); dg = np.zeros(max(self.m, 1)); vals = np.zeros(2)
-        self.lib.oracle_lagrangian_gradients(self.h, _p(f(x)), _p(f(y)), _p(pg), _p(dg), _p(vals))
+        self.lib.oracle_lagrangian_gradients(self.h, _p(x), _p(y), _p(pg), _p(dg), _p(vals))
         return pg[: self.n], dg[: self.m], vals
 
     def localized_bounds(self, x, y, norm, primal_weight, radius, use_diagonal=False, tol=1e-8):
-        f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        x, y = _f(x), _f(y)
         out = np.zeros(4)
-        self.lib.oracle_localized_bounds(self.h, _p(f(x)), _p(f(y)), int(norm), ctypes.c_double(primal_weight), ctypes.c_double(radius), int(use_diagonal),
+        self.lib.oracle_localized_bounds(self.h, _p(x), _p(y), int(norm), ctypes.c_double(primal_weight), ctypes.c_double(radius), int(use_diagonal),
                                          ctypes.c_double(tol), _p(out))
         return dict(lagrangian_value=out[0], lower_bound=out[1], upper_bound=out[2], radius=out[3])
 
@@ -199,17 +235,17 @@ class Problem:
 
 def trust_region(obj, lb, ub, center, w, radius, diag=None, num_shards=1, tol=1e-8):
     lib = load()
-    f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
-    obj, lb, ub, center, w = map(f, (obj, lb, ub, center, w))
+    obj, lb, ub, center, w = map(_f, (obj, lb, ub, center, w))
+    diag = None if diag is None else _f(diag)
     sol = np.zeros(max(obj.size, 1)); out = np.zeros(2)
-    lib.oracle_trust_region(ctypes.c_int64(obj.size), _p(obj), _p(f(diag)) if diag is not None else None, _p(lb), _p(ub), _p(center), _p(w),
+    lib.oracle_trust_region(ctypes.c_int64(obj.size), _p(obj), _p(diag) if diag is not None else None, _p(lb), _p(ub), _p(center), _p(w),
                             ctypes.c_double(radius), int(num_shards), ctypes.c_double(tol), _p(sol), _p(out))
     return sol[: obj.size], out[0], out[1]
 
 
 def shard_starts(n, num_shards, masses=None):
     lib = load()
-    starts = np.zeros(num_shards + 2 + n, dtype=np.int64)
+    starts = np.zeros(min(num_shards, n) + 2 + n, dtype=np.int64)
     ms = None if masses is None else np.ascontiguousarray(masses, dtype=np.int64)
     k = lib.oracle_shard_starts(ctypes.c_int64(n), int(num_shards), _p(ms) if ms is not None else None, _p(starts))
     return starts[: k + 1]

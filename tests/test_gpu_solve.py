@@ -31,11 +31,11 @@ def both(qp, p, **kw):
 
 
 def assert_parity(dev, ora, obj_tol=1e-6, iter_tol=0.05, iter_slack=2):
-    assert dev.solve_log.termination_reason == ora.solve_log["termination_reason"]
-    di, oi = dev.solve_log.iteration_count, ora.solve_log["iteration_count"]
+    assert dev.solve_log.termination_reason == ora.solve_log_dict["termination_reason"]
+    di, oi = dev.solve_log.iteration_count, ora.solve_log_dict["iteration_count"]
     assert abs(di - oi) <= max(iter_slack, iter_tol * oi), (di, oi)
-    if ora.solve_log["solution_stats"]["convergence_information"]:
-        oc = ora.solve_log["solution_stats"]["convergence_information"][0]
+    if ora.solve_log_dict["solution_stats"]["convergence_information"]:
+        oc = ora.solve_log_dict["solution_stats"]["convergence_information"][0]
         dc = dev.solve_log.solution_stats.convergence_information[0]
         for name in ("primal_objective", "dual_objective"):
             a, b = getattr(dc, name), oc[name]
@@ -99,12 +99,12 @@ def oracle_iteration_envelope(qp, p):
         q.num_threads = threads
         if shards:
             q.num_shards = shards
-        counts.append(ob.solve(qp, q).solve_log["iteration_count"])
+        counts.append(ob.solve(qp, q).solve_log_dict["iteration_count"])
     return min(counts), max(counts)
 
 
 def assert_objectives_close(dev, ora, tol=1e-6):
-    oc = ora.solve_log["solution_stats"]["convergence_information"][0]
+    oc = ora.solve_log_dict["solution_stats"]["convergence_information"][0]
     dc = dev.solve_log.solution_stats.convergence_information[0]
     for name in ("primal_objective", "dual_objective"):
         a, b = getattr(dc, name), oc[name]
@@ -116,7 +116,7 @@ def test_random_lp_parity(seed):
     qp = fixtures.random_lp(400, 800, 5, seed)
     p = params(eps_abs=1e-7, eps_rel=1e-7)  # both solvers then pin the objective to well under 1e-6 relative
     dev, ora = both(qp, p)
-    assert dev.solve_log.termination_reason == ora.solve_log["termination_reason"] == pdlp_b200.TerminationReason.TERMINATION_REASON_OPTIMAL
+    assert dev.solve_log.termination_reason == ora.solve_log_dict["termination_reason"] == pdlp_b200.TerminationReason.TERMINATION_REASON_OPTIMAL
     assert_objectives_close(dev, ora)
     lo, hi = oracle_iteration_envelope(qp, p)
     assert 0.95 * lo - 64 <= dev.solve_log.iteration_count <= 1.05 * hi + 64, (dev.solve_log.iteration_count, lo, hi)
@@ -129,7 +129,7 @@ def test_random_qp_parity():
     qp = fixtures.random_lp(300, 600, 5, 3, qp_diagonal=True)
     p = params(eps_abs=1e-7, eps_rel=1e-7)
     dev, ora = both(qp, p)
-    assert dev.solve_log.termination_reason == ora.solve_log["termination_reason"] == pdlp_b200.TerminationReason.TERMINATION_REASON_OPTIMAL
+    assert dev.solve_log.termination_reason == ora.solve_log_dict["termination_reason"] == pdlp_b200.TerminationReason.TERMINATION_REASON_OPTIMAL
     assert_objectives_close(dev, ora)
     lo, hi = oracle_iteration_envelope(qp, p)
     assert 0.95 * lo - 64 <= dev.solve_log.iteration_count <= 1.05 * hi + 64, (dev.solve_log.iteration_count, lo, hi)
@@ -142,7 +142,7 @@ def test_iteration_limit_trace_matches_oracle():
     p.termination_criteria.iteration_limit = 60
     dev, ora = both(fixtures.make_test_lp(), p)
     assert dev.solve_log.termination_reason == pdlp_b200.TerminationReason.TERMINATION_REASON_ITERATION_LIMIT
-    ds, os_ = dev.solve_log.iteration_stats, ora.solve_log["iteration_stats"]
+    ds, os_ = dev.solve_log.iteration_stats, ora.solve_log_dict["iteration_stats"]
     assert len(ds) == len(os_)
     for d, o in zip(ds, os_):
         assert d.iteration_number == o["iteration_number"]

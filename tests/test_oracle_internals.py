@@ -1,0 +1,174 @@
+"""Pins the oracle's internal building blocks (the ones with no device-side twin) against
+the reference's golden values: Sharder (sharder_test.cc:86-190), the linear-time and
+diagonal trust-region solvers (trust_region_test.cc:53-500,963-1066), one-iteration Ruiz/L2
+rescaling (sharded_optimization_utils_test.cc:303-357), the Lagrangian gradients
+(:402-510) and the singular-value estimate (:517-592)."""
+import math
+
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+import fixtures
+import oracle_binding as ob
+import pdlp_b200
+
+INF = np.inf
+
+
+# ---- Sharder ----
+def verify_sharder(starts, target, masses):
+    starts = list(starts)
+    n = len(masses)
+    assert starts[0] == 0 and starts[-1] == n
+    num_shards = len(starts) - 1
+    assert 1 <= num_shards <= 2 * target
+    shard_mass = [sum(masses[starts[s]:starts[s + 1]]) for s in range(num_shards)]
+    for s in range(num_shards):
+        assert starts[s + 1] - starts[s] >= 1 and shard_mass[s] >= 1
+    total, mx = sum(masses), max(masses)
+    upper = max(mx, -(-mx // 2) + -(-total // target))
+    lower = total // target - -(-mx // 2)
+    for s in range(num_shards):
+        assert shard_mass[s] <= upper
+        if s + 1 < num_shards:
+            assert shard_mass[s] >= lower
+
+
+def test_sharder_from_matrix():
+    # column masses of TestSparseMatrix are nnz+1 = [4, 2, 2, 3] (sharder.cc:72-76)
+    verify_sharder(ob.shard_starts(4, 2, [4, 2, 2, 3]), 2, [4, 2, 2, 3])
+
+
+@pytest.mark.parametrize("n,shards,want", [(10, 3, None), (5, 7, [0, 1, 2, 3, 4, 5]), (5, 1_000_000_000, [0, 1, 2, 3, 4, 5]), (5, 1, [0, 5]), (1, 5, [0, 1])])
+def test_uniform_sharder(n, shards, want):
+    starts = ob.shard_starts(n, shards)
+    if want is not None:
+        assert list(starts) == want
+    verify_sharder(starts, min(shards, 7), [1] * n)
+
+
+def test_uniform_sharder_zero_elements():
+    assert list(ob.shard_starts(0, 3)) == [0]
+
+
+# ---- trust region ----
+TR_CASES = [
+    # name, lb, ub, center, objective, weights, radius, solution, objective value, tol on objective for the diagonal solver
+    ("no_bounds", [-INF, -INF], [INF, INF], [2.0, -5.0], [1.0, 1.0], [1, 1], math.sqrt(2.0), [1.0, -6.0], -2.0, 1e-6),
+    ("with_bounds", [2.0, -INF, -INF], [INF, INF, INF], [2.0, -5.0, 1.0], [1.0, -1.0, 1.0], [1, 1, 1], math.sqrt(2.0), [2.0, -4.0, 0.0], -2.0, 1e-6),
+    ("at_bounds", [2.0, -INF], [INF, -5.0], [2.0, -5.0], [1.0, -1.0], [1, 1], 1.0, [2.0, -5.0], 0.0, 1e-6),
+    ("inactive_radius", [2.0, -INF, 0.5], [INF, -5.0, INF], [2.0, -5.0, 1.0], [1.0, -1.0, 1.0], [1, 1, 1], 1.0, [2.0, -5.0, 0.5], -0.5, 1e-6),
+    ("zero_radius", [2.0, -INF, 0.5], [INF, -5.0, INF], [2.0, -5.0, 1.0], [1.0, -1.0, 1.0], [1, 1, 1], 0.0, [2.0, -5.0, 1.0], 0.0, 1e-6),
+    ("infinite_radius", [2.0, -INF, 0.5], [INF, -5.0, INF], [2.0, -5.0, 1.0], [1.0, -1.0, 1.0], [1, 1, 1], INF, [2.0, -5.0, 0.5], -0.5, 1e-6),
+    ("mixed_objective", [1.0, 0.0], [INF, INF], [2.0, 1.0], [2.0, 1.0], [1, 1], math.sqrt(1.25), [1.0, 0.5], -2.5, 2e-6),
+    ("zero_objective", [-INF], [INF], [2.0], [0.0], [1], 1.0, [2.0], 0.0, 1e-6),
+    ("weights_no_bounds", [-INF, -INF], [INF, INF], [2.0, -5.0], [1.0, 2.0], [1.0, 2.0], math.sqrt(3.0), [1.0, -6.0], -3.0, 1e-5),
+    ("weights_with_bounds", [2.0, -INF, -INF], [INF, INF, INF], [2.0, -5.0, 1.0], [0.5, -2.0, 3.0], [0.5, 2.0, 3.0], math.sqrt(5.0), [2.0, -4.0, 0.0], -5.0, 1e-5),
+    ("weights_hits_bound", [1.0, 0.0], [INF, INF], [2.0, 1.0], [1.0, 2.0], [0.5, 2.0], 1.0, [1.0, 0.5], -2.0, 1e-6),
+    ("weights_large", [1.0, 0.0], [INF, INF], [2.0, 1.0], [1000.0, 2.0], [500.0, 2.0], math.sqrt(500.5), [1.0, 0.5], -1001.0, 1e-6),
+]
+
+
+@pytest.mark.parametrize("case", TR_CASES, ids=[c[0] for c in TR_CASES])
+@pytest.mark.parametrize("shards", [1, 2])
+def test_linear_time_trust_region(case, shards):
+    _, lb, ub, center, obj, w, radius, want, want_obj, _ = case
+    sol, _, value = ob.trust_region(obj, lb, ub, center, w, radius, num_shards=shards)
+    np.testing.assert_allclose(sol, want, rtol=0, atol=1e-13)
+    assert abs(value - want_obj) <= 4 * np.spacing(max(abs(want_obj), 1.0))
+
+
+@pytest.mark.parametrize("case", TR_CASES, ids=[c[0] for c in TR_CASES])
+def test_diagonal_trust_region_on_lps(case):
+    _, lb, ub, center, obj, w, radius, want, want_obj, obj_tol = case
+    sol, _, value = ob.trust_region(obj, lb, ub, center, w, radius, diag=np.zeros(len(obj)), num_shards=2, tol=1e-8 if case[0] == "no_bounds" else 1e-6)
+    np.testing.assert_allclose(sol, want, rtol=0, atol=1e-6)
+    assert abs(value - want_obj) <= obj_tol
+
+
+def one_dim_qp_data(primal_weight):
+    # GenerateTestQpProblemData (trust_region_test.cc:859-878)
+    return dict(obj=[2.0, -1.0], diag=[2.0, 0.0], center=[0.0, -1.0], lb=[-INF, -INF], ub=[INF, INF], w=[0.5 * primal_weight, 0.5 / primal_weight])
+
+
+def test_diagonal_trust_region_one_dim_qp():
+    d = one_dim_qp_data(1.0)
+    sol, step, value = ob.trust_region(d["obj"], d["lb"], d["ub"], d["center"], d["w"], 0.5, diag=d["diag"], num_shards=2, tol=1e-6)
+    np.testing.assert_allclose(sol, [-0.5, -0.5], atol=1e-6)
+    assert abs(step - 4.0) <= 4e-6 and abs(value + 1.25) <= 1e-6
+    d = one_dim_qp_data(100.0)
+    _, step, _ = ob.trust_region(d["obj"], d["lb"], d["ub"], d["center"], d["w"], math.sqrt(2705.0 / 2) * (5.0 / 13), diag=d["diag"], num_shards=2, tol=1e-6)
+    assert abs(step - 1.0) <= 1e-6
+    d = one_dim_qp_data(0.01)
+    sol, step, value = ob.trust_region(d["obj"], d["lb"], d["ub"], d["center"], d["w"], 0.71063, diag=d["diag"], num_shards=2, tol=1e-6)
+    np.testing.assert_allclose(sol, [-0.99950025, -0.9], atol=1e-6)
+    assert abs(step - 0.2) <= 1e-6 and abs(value + 1.0999996) <= 1e-6
+
+
+# ---- one-iteration rescaling goldens ----
+def test_linf_ruiz_one_iteration():
+    p = ob.Problem(fixtures.make_test_lp(), 2, 2)
+    rs, cs = p.scaling_vectors(0, 1, [1, 2, 1, 3.0], [0, 1, 2, -1.0])
+    np.testing.assert_array_equal(rs, [1 / math.sqrt(2), 1.0, 1.0, 1.0])
+    np.testing.assert_array_equal(cs, [0.0, 1.0, 2.0 / 3.0, -1.0 / math.sqrt(3.0)])
+
+
+def test_l2_rescaling_one_iteration():
+    p = ob.Problem(fixtures.make_test_lp(), 2, 2)
+    rs, cs = p.scaling_vectors(1, 1, [1, 2, 1, 3.0], [0, 1, 2, -1.0])
+    np.testing.assert_allclose(rs, [1.0 / 3.0 ** 0.5, 1.0, 1.0, 3.0 / 90.0 ** 0.25], rtol=4e-16)
+    np.testing.assert_allclose(cs, [0.0, 1.0, 2.0 / 101 ** 0.25, -1.0 / 13.0 ** 0.25], rtol=4e-16)
+
+
+def test_l2_rescaling_non_square():
+    qp = pdlp_b200.QuadraticProgram()
+    qp.resize_and_initialize(2, 1)
+    qp.constraint_matrix = sp.csc_matrix(np.array([[2.0, 3.0]]))
+    rs, cs = ob.Problem(qp, 2, 2).scaling_vectors(1, 1, [1.0], [1.0, 1.0])
+    np.testing.assert_allclose(rs, [1.0 / 13.0 ** 0.25], rtol=4e-16)
+    np.testing.assert_allclose(cs, [1.0 / math.sqrt(2.0), 1.0 / math.sqrt(3.0)], rtol=4e-16)
+
+
+# ---- Lagrangian gradients ----
+def test_lagrangian_gradients_lp():
+    p = ob.Problem(fixtures.make_test_lp(), 2, 2)
+    pg, dg, vals = p.lagrangian_gradients([0.0, 0.0, 0.0, 3.0], [-1.0, 0.0, 1.0, 1.0])
+    np.testing.assert_array_equal(pg, [5.5 - 2.0, -2.0 + 1.0, -1.0 - 0.5, 1.0 + 3.0])
+    assert vals[0] == 3.0 + 9.0
+    np.testing.assert_array_equal(dg, [12.0 - 6.0, 7.0, -4.0, -1.0 + 3.0])
+    assert vals[1] == 12.0 * -1.0 + -4.0 * 1.0 + -1.0 * 1.0
+
+
+def test_dual_gradient_two_sided_constraints():
+    qp = fixtures.make_test_lp()
+    qp.constraint_lower_bounds[0] = 4
+    qp.constraint_lower_bounds[1] = 5
+    qp.constraint_upper_bounds[2] = -1
+    _, dg, vals = ob.Problem(qp, 2, 2).lagrangian_gradients([0.0, 0.0, 0.0, 3.0], [0.0, 0.0, 0.0, -1.0])
+    np.testing.assert_array_equal(dg, [0.0, 5.0, -1.0, 4.0])
+    assert vals[1] == -1.0
+
+
+def test_lagrangian_gradients_qp():
+    p = ob.Problem(fixtures.diagonal_qp1(), 2, 2)
+    pg, dg, vals = p.lagrangian_gradients([1.0, 2.0], [-2.0])
+    np.testing.assert_array_equal(pg, [5.0, 3.0])
+    assert vals[0] == 4.0 - 3.0 + 2.0 * 3.0
+    np.testing.assert_array_equal(dg, [1.0 - 3.0])
+    assert vals[1] == -2.0
+
+
+# ---- power method ----
+def test_sigma_max_test_lp():
+    # the exact value; the reference's mt19937/absl::Gaussian start vector is not
+    # reproducible outside abseil ("parity unpinned"), the estimate's accuracy is.
+    v, iters = ob.Problem(fixtures.make_test_lp(), 2, 2).sigma_max(0.01, 0.001, 1)
+    assert abs(v - 4.76945) < 0.01 and iters < 300
+
+
+def test_sigma_max_diagonal():
+    qp = fixtures.make_test_lp()
+    qp.constraint_matrix = sp.csc_matrix(np.diag([2.0, 1.0, -3.0, -1.0]))
+    v, iters = ob.Problem(qp, 2, 2).sigma_max(0.01, 0.001, 1)
+    assert abs(v - 3.0) < 1e-4 and iters < 300
