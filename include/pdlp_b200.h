@@ -95,6 +95,19 @@ pdlp_b200_status pdlp_b200_solve(const pdlp_b200_problem* problem, const uint8_t
  * PDLP_B200_OK and *message = NULL when valid, else *message = malloc'ed status text. */
 pdlp_b200_status pdlp_b200_validate_params(const uint8_t* params, size_t params_len, char** message);
 
+/* The termination predicates (termination.cc:161-219,239-271), host code, no device needed.
+ *   which = 0: CheckIterateTerminationCriteria(params.termination_criteria, stats, bound_norms,
+ *              force_numerical_termination); which = 1: CheckSimpleTerminationCriteria(criteria,
+ *              stats, interrupt).
+ *   stats: serialized IterationStats; bound_norms as in pdlp_b200_callback.
+ *   *reason / *point_type: TerminationReason / PointType numbers, both 0 (UNSPECIFIED) when the
+ *   reference would return std::nullopt.
+ *   relative_residuals (optional, 5): ComputeRelativeResiduals of stats.convergence_information(0):
+ *   {l_inf primal, l2 primal, l_inf dual, l2 dual, optimality gap}. */
+pdlp_b200_status pdlp_b200_check_termination(const uint8_t* params, size_t params_len, const uint8_t* stats, size_t stats_len,
+                                             const double* bound_norms /*4*/, int which, int force_numerical_termination,
+                                             const volatile int* interrupt, int* reason, int* point_type, double* relative_residuals);
+
 /* Serialized PrimalDualHybridGradientParams holding every schema default. */
 pdlp_b200_status pdlp_b200_default_params(uint8_t** params, size_t* params_len);
 

@@ -83,6 +83,7 @@ EXPORTED_SYMBOLS = [
     "pdlp_b200_last_error", "pdlp_b200_free", "pdlp_b200_problem_create", "pdlp_b200_problem_destroy",
     "pdlp_b200_matvec", "pdlp_b200_scaled_norms", "pdlp_b200_stats", "pdlp_b200_rescale", "pdlp_b200_kkt_stats",
     "pdlp_b200_reduced_costs", "pdlp_b200_localized_bounds", "pdlp_b200_trial_steps", "pdlp_b200_trial_steps_profiled",
+    "pdlp_b200_check_termination",
 ]
 
 
@@ -142,6 +143,7 @@ from ._api import (  # noqa: E402
     PrimalAndDualSolution,
     QuadraticProgram,
     SolverResult,
+    check_termination,
     is_linear_program,
     last_solve_counters,
     primal_dual_hybrid_gradient,

@@ -172,6 +172,20 @@ def validate_params(params):
     return text
 
 
+def check_termination(params, stats, bound_norms, which="iterate", force_numerical_termination=False, interrupt=None):
+    """termination.cc:161-219 through the C ABI.  Returns (reason, point_type, relative_residuals) with
+    reason = point_type = 0 when the reference would return nullopt.  `which`: "iterate" or "simple"."""
+    pb = _params_bytes(params)
+    sb = stats.SerializeToString() if stats is not None else b""
+    norms = _f64(bound_norms)
+    reason, ptype = ctypes.c_int(0), ctypes.c_int(0)
+    rel = np.zeros(5)
+    flag = ctypes.c_void_p(interrupt.ctypes.data) if interrupt is not None else ctypes.c_void_p(None)
+    _check(_lib.pdlp_b200_check_termination(pb, len(pb), sb, len(sb), _vptr(norms), 0 if which == "iterate" else 1, int(force_numerical_termination), flag,
+                                            ctypes.byref(reason), ctypes.byref(ptype), _vptr(rel)))
+    return reason.value, ptype.value, rel
+
+
 _last_counters = {}
 
 

@@ -285,6 +285,40 @@ pdlp_b200_status pdlp_b200_validate_params(const uint8_t* params_bytes, size_t p
   });
 }
 
+pdlp_b200_status pdlp_b200_check_termination(const uint8_t* params_bytes, size_t params_len, const uint8_t* stats_bytes, size_t stats_len,
+                                             const double* bound_norms, int which, int force_numerical_termination, const volatile int* interrupt,
+                                             int* reason, int* point_type, double* relative_residuals) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (reason == nullptr || point_type == nullptr || bound_norms == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "null argument");
+    PrimalDualHybridGradientParams params;
+    if (!ParseParams(params_bytes, params_len, &params)) return Fail(PDLP_B200_BAD_ARGUMENT, "params is not a serialized PrimalDualHybridGradientParams");
+    IterationStats stats;
+    if (stats_len > 0 && !Parse(stats_bytes, stats_len, &stats)) return Fail(PDLP_B200_BAD_ARGUMENT, "stats is not a serialized IterationStats");
+    const TerminationCriteria& criteria = params.termination_criteria.get();
+    const QuadraticProgramBoundNorms norms{bound_norms[0], bound_norms[1], bound_norms[2], bound_norms[3]};
+    std::optional<TerminationReasonAndPointType> r;
+    if (which == 0) {
+      r = CheckIterateTerminationCriteria(criteria, stats, norms, force_numerical_termination != 0);
+    } else {
+      InterruptFlag flag;
+      flag.int_flag = interrupt;
+      r = CheckSimpleTerminationCriteria(criteria, stats, &flag);
+    }
+    *reason = r.has_value() ? r->reason : TERMINATION_REASON_UNSPECIFIED;
+    *point_type = r.has_value() ? r->type : POINT_TYPE_UNSPECIFIED;
+    if (relative_residuals != nullptr) {
+      for (int k = 0; k < 5; ++k) relative_residuals[k] = 0.0;
+      if (!stats.convergence_information.empty()) {
+        const RelativeConvergenceInformation rel = ComputeRelativeResiduals(EffectiveOptimalityCriteria(criteria), stats.convergence_information[0], norms);
+        relative_residuals[0] = rel.relative_l_inf_primal_residual; relative_residuals[1] = rel.relative_l2_primal_residual;
+        relative_residuals[2] = rel.relative_l_inf_dual_residual; relative_residuals[3] = rel.relative_l2_dual_residual;
+        relative_residuals[4] = rel.relative_optimality_gap;
+      }
+    }
+    return PDLP_B200_OK;
+  });
+}
+
 pdlp_b200_status pdlp_b200_default_params(uint8_t** params, size_t* params_len) {
   return Guard([&]() -> pdlp_b200_status {
     if (params == nullptr || params_len == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "null output");

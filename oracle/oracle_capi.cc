@@ -236,6 +236,46 @@ int oracle_solve(int64_t n, int64_t m, int64_t nnz, const int64_t* col_ptr, cons
 // ---- unit entry points for the golden tests ----
 void oracle_validate_params(const char* params_text, char** message) { *message = Dup(ValidateParams(ParseParams(params_text))); }
 
+// Termination predicates (termination.cc:161-219,239-271) on flat records.
+//   conv: n_conv rows of {candidate_type, primal_objective, dual_objective, l_inf_primal_residual, l2_primal_residual,
+//         l_inf_componentwise_primal_residual, l_inf_dual_residual, l2_dual_residual, l_inf_componentwise_dual_residual}
+//   inf:  n_inf rows of {candidate_type, max_primal_ray_infeasibility, primal_ray_linear_objective, primal_ray_quadratic_norm,
+//         max_dual_ray_infeasibility, dual_ray_objective}
+//   work: {iteration_number, cumulative_kkt_matrix_passes, cumulative_time_sec};  out: {reason, point_type} (0, 0 = nullopt)
+void oracle_check_termination(const char* params_text, int which, int force_numerical, const volatile int* interrupt, const double* norms, int n_conv,
+                              const double* conv, int n_inf, const double* inf, const double* work, int* out, double* relative_residuals) {
+  const Params params = ParseParams(params_text);
+  IterationStats s;
+  for (int i = 0; i < n_conv; ++i) {
+    const double* r = conv + 9 * i;
+    ConvergenceInformation c;
+    c.candidate_type = static_cast<int>(r[0]); c.primal_objective = r[1]; c.dual_objective = r[2];
+    c.l_inf_primal_residual = r[3]; c.l2_primal_residual = r[4]; c.l_inf_componentwise_primal_residual = r[5];
+    c.l_inf_dual_residual = r[6]; c.l2_dual_residual = r[7]; c.l_inf_componentwise_dual_residual = r[8];
+    s.convergence_information.push_back(c);
+  }
+  for (int i = 0; i < n_inf; ++i) {
+    const double* r = inf + 6 * i;
+    InfeasibilityInformation c;
+    c.candidate_type = static_cast<int>(r[0]); c.max_primal_ray_infeasibility = r[1]; c.primal_ray_linear_objective = r[2];
+    c.primal_ray_quadratic_norm = r[3]; c.max_dual_ray_infeasibility = r[4]; c.dual_ray_objective = r[5];
+    s.infeasibility_information.push_back(c);
+  }
+  s.iteration_number = static_cast<int>(work[0]); s.cumulative_kkt_matrix_passes = work[1]; s.cumulative_time_sec = work[2];
+  const BoundNorms bn{norms[0], norms[1], norms[2], norms[3]};
+  std::optional<TerminationReasonAndPointType> r;
+  if (which == 0) r = CheckIterateTerminationCriteria(params.termination_criteria, s, bn, force_numerical != 0);
+  else r = CheckSimpleTerminationCriteria(params.termination_criteria, s, interrupt);
+  out[0] = r.has_value() ? r->reason : 0;
+  out[1] = r.has_value() ? r->type : 0;
+  if (relative_residuals != nullptr && n_conv > 0) {
+    const RelativeConvergenceInformation rel = ComputeRelativeResiduals(EffectiveOptimalityCriteria(params.termination_criteria), s.convergence_information[0], bn);
+    relative_residuals[0] = rel.relative_l_inf_primal_residual; relative_residuals[1] = rel.relative_l2_primal_residual;
+    relative_residuals[2] = rel.relative_l_inf_dual_residual; relative_residuals[3] = rel.relative_l2_dual_residual;
+    relative_residuals[4] = rel.relative_optimality_gap;
+  }
+}
+
 int oracle_shard_starts(int64_t n, int num_shards, const int64_t* masses /*nullable: uniform*/, int64_t* starts_out /*<= num_shards+1*/) {
   std::unique_ptr<Sharder> sh;
   if (masses) sh = std::make_unique<Sharder>(n, num_shards, nullptr, [&](int64_t i) { return masses[i]; });

@@ -256,3 +256,21 @@ def validate_params(params):
     s = ctypes.c_char_p()
     lib.oracle_validate_params(flatten_params(params).encode(), ctypes.byref(s))
     return s.value.decode()
+
+
+def check_termination(params, stats, bound_norms, which="iterate", force_numerical_termination=False, interrupt=None):
+    """Same contract as pdlp_b200.check_termination, on the oracle."""
+    lib = load()
+    conv = np.array([[c.candidate_type, c.primal_objective, c.dual_objective, c.l_inf_primal_residual, c.l2_primal_residual,
+                      c.l_inf_componentwise_primal_residual, c.l_inf_dual_residual, c.l2_dual_residual, c.l_inf_componentwise_dual_residual]
+                     for c in stats.convergence_information], dtype=np.float64).reshape(-1)
+    inf = np.array([[c.candidate_type, c.max_primal_ray_infeasibility, c.primal_ray_linear_objective, c.primal_ray_quadratic_norm,
+                     c.max_dual_ray_infeasibility, c.dual_ray_objective] for c in stats.infeasibility_information], dtype=np.float64).reshape(-1)
+    work = np.array([stats.iteration_number, stats.cumulative_kkt_matrix_passes, stats.cumulative_time_sec], dtype=np.float64)
+    norms = _f(bound_norms)
+    out = np.zeros(2, dtype=np.int32)
+    rel = np.zeros(5)
+    lib.oracle_check_termination(flatten_params(params).encode(), 0 if which == "iterate" else 1, int(force_numerical_termination),
+                                 _p(interrupt) if interrupt is not None else None, _p(norms), len(stats.convergence_information), _p(conv),
+                                 len(stats.infeasibility_information), _p(inf), _p(work), _p(out), _p(rel))
+    return int(out[0]), int(out[1]), rel
