@@ -13,8 +13,10 @@ with the step-size test, decision, averaging) on the resident problem.
             measured HBM copy bandwidth in MEASURED_PEAKS.json, plus a per-kernel table
   cpu_baseline  the CPU oracle (a restatement of the reference's threaded Sharder path)
             timed on a bounded number of iterations of the same workload
-`--impl reference` times that CPU path alone.  Multi-GPU (N > 1): independent replicas of
-the per-GPU workload, one process per GPU, no data-path collective yet.
+`--impl reference` times that CPU path alone.  Multi-GPU (N > 1): the SAME problem column-sharded
+over the N ranks (strong scaling): one process per GPU, each owning a column block
+of K, one NCCL all-reduce of the partial K x (m doubles) plus scalar all-reduces per trial step.
+`--replicas` runs N independent copies instead (no collective).
 """
 import argparse
 import json
@@ -50,9 +52,29 @@ def make_problem(name, scale, seed=0):
     if name == "c4":
         return synthetic.random_sparse_lp(int(5_000_000 * scale), int(10_000_000 * scale), 5, seed, qp_diagonal=True)
     if name == "c5":
-        s = max(8, int(round(7906 * scale ** 0.5)))  # 7906^2 * 2 = 1.25e8 nnz: one GPU's share of config 5
+        s = c5_side(scale)
         return synthetic.transportation_lp(s, s, seed)
     raise ValueError(name)
+
+
+def c5_side(scale):
+    return max(8, int(round(7906 * scale ** 0.5)))  # 7906^2 * 2 = 1.25e8 nnz at scale 1; scale 8 is the 1e9-nnz LP of config 5
+
+
+def make_block(name, scale, rank, world, seed=0):
+    """This rank's column block of the workload: (block qp, starts).  c5 is generated block by
+    block (whole sources, so the 1e9-nnz problem never exists on one host); the others are
+    generated whole on every rank (same seed) and cut by the mass rule."""
+    import pdlp_b200
+    from pdlp_b200 import synthetic
+    if name == "c5":
+        s = c5_side(scale)
+        cuts = [(s * r) // world for r in range(world + 1)]
+        block = synthetic.transportation_lp(s, s, seed, cuts[rank], cuts[rank + 1])
+        return block, np.array([c * s for c in cuts], dtype=np.int64)
+    qp = make_problem(name, scale, seed)
+    starts = pdlp_b200.column_partition(qp.constraint_matrix.indptr, world)
+    return pdlp_b200.take_columns(qp, int(starts[rank]), int(starts[rank + 1])), starts
 
 
 def solve_params(name, threads=1, iteration_limit=None):
@@ -67,9 +89,11 @@ def solve_params(name, threads=1, iteration_limit=None):
     return p
 
 
-def bytes_per_step(n, m, nnz, is_qp):
-    """B_step = 24 nnz + 4 (n + m) + 8 (15 n + 8 m)  [+ 8 n for a QP]."""
-    return 24 * nnz + 4 * (n + m) + 8 * (15 * n + 8 * m) + (8 * n if is_qp else 0)
+def bytes_per_step(n, m, nnz, is_qp, sharded=False):
+    """B_step = 24 nnz + 4 (n + m) + 8 (15 n + 8 m)  [+ 8 n for a QP].
+    Sharded: the same for one rank's block (n, nnz of the block; all m rows) plus the partial row
+    sums written before and read after the all-reduce (16 m); NCCL's own traffic is not counted."""
+    return 24 * nnz + 4 * (n + m) + 8 * (15 * n + 8 * m) + (8 * n if is_qp else 0) + (16 * m if sharded else 0)
 
 
 def kernel_bytes(n, m, nnz, is_qp):
@@ -159,6 +183,7 @@ def main():
     ap.add_argument("--cpu-iterations", type=int, default=0, help="iterations of the CPU baseline sample (0 = pick by workload)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--replicas", action="store_true", help="N > 1: independent replicas instead of one column-sharded problem")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -198,13 +223,24 @@ def main():
 
     torch.cuda.set_device(local_rank)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    qp = make_problem(name, args.scale, seed=0)
+        dist.init_process_group("cpu:gloo,cuda:nccl", device_id=torch.device("cuda", local_rank))
+    sharded = world > 1 and not args.replicas
+    shard = starts = None
+    if sharded:
+        qp, starts = make_block(name, args.scale, rank, world)
+        shard = pdlp_b200.ColumnShard(rank, world, int(starts[-1]), int(starts[rank]), pdlp_b200.sharding.broadcast_unique_id())
+    else:
+        qp = make_problem(name, args.scale, seed=0)
     K = qp.constraint_matrix
     m, n = K.shape
     nnz = K.nnz
     is_qp = qp.objective_matrix is not None
-    b_step = bytes_per_step(n, m, nnz, is_qp)
+    b_step = bytes_per_step(n, m, nnz, is_qp, sharded)  # this rank's
+    n_global, nnz_global, b_step_all = n, nnz, b_step
+    if sharded:
+        tot = torch.tensor([nnz, b_step], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tot)
+        n_global, nnz_global, b_step_all = int(starts[-1]), int(tot[0].item()), float(tot[1].item())
 
     def barrier():
         if world > 1:
@@ -212,7 +248,7 @@ def main():
         torch.cuda.synchronize()
 
     # ---- resident kernel-path timing ----
-    dp = pdlp_b200.DeviceProblem(qp, device=local_rank)
+    dp = pdlp_b200.DeviceProblem(qp, device=local_rank, shard=shard)
     dp.rescale(5, True)  # the solver iterates on the rescaled problem
     stats = dp.stats()
     step0 = 1.0 / max(1e-20, stats.constraint_matrix_abs_max)
@@ -232,7 +268,7 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     seconds_max = float(t.item())
-    steps_per_sec = world * args.steps / seconds_max
+    steps_per_sec = (1 if sharded else world) * args.steps / seconds_max
     # per-kernel breakdown (second pass with CUDA events around every launch)
     breakdown = dp.trial_steps_profiled(args.steps, st["step_size"], w0, x, y)
     kb = kernel_bytes(n, m, nnz, is_qp)
@@ -245,7 +281,9 @@ def main():
     for k in kernels:
         k["share"] = k["us_per_launch"] / total_k if total_k > 0 else None
     dominant = max(kernels, key=lambda k: k["us_per_launch"])
-    step_gbs = b_step * args.steps / seconds / 1e9
+    step_gbs = b_step_all * args.steps / seconds_max / 1e9  # all ranks' algorithmic bytes over the slowest rank's time
+    if not sharded:
+        step_gbs = b_step * args.steps / seconds / 1e9
 
     # ---- end-to-end solve from host buffers ----
     e2e = None
@@ -254,7 +292,10 @@ def main():
         p = solve_params(name)
         barrier()
         t0 = time.time()
-        result = pdlp_b200.primal_dual_hybrid_gradient(qp, p, device=local_rank)
+        if sharded:
+            result = pdlp_b200.primal_dual_hybrid_gradient_sharded(qp, p, device=local_rank, starts=starts, gather=False)
+        else:
+            result = pdlp_b200.primal_dual_hybrid_gradient(qp, p, device=local_rank)
         torch.cuda.synchronize()
         wall = time.time() - t0
         tw = torch.tensor([wall], dtype=torch.float64, device="cuda")
@@ -266,12 +307,13 @@ def main():
         h2d = 16 * nnz + 8 * (n + 1) + 8 * (3 * n + 2 * m) + (8 * n if is_qp else 0)
         d2h = 8 * (2 * n + m)
         ci = result.solve_log.solution_stats.convergence_information
-        e2e = {"value": world * its / wall_max, "unit": "iterations/s", "h2d_bytes_per_step": h2d / max(1, its), "d2h_bytes_per_step": d2h / max(1, its),
+        e2e = {"value": (1 if sharded else world) * its / wall_max, "unit": "iterations/s", "h2d_bytes_per_step": h2d / max(1, its), "d2h_bytes_per_step": d2h / max(1, its),
                "time_to_tolerance_sec": wall_max, "iterations": its, "termination_reason": int(result.solve_log.termination_reason),
                "h2d_bytes_per_solve": h2d, "d2h_bytes_per_solve": d2h}
         solve_info = {"solve_iterations": its, "solve_trial_steps": counters.get("trial_steps"), "solve_wall_sec": wall_max,
                       "solve_setup_sec": counters.get("setup_seconds"), "solve_loop_sec": counters.get("loop_seconds"),
                       "solve_device_loop_sec": counters.get("device_loop_seconds"), "solve_kernel_launches": counters.get("kernel_launches"),
+                      "solve_collectives": counters.get("collectives"),
                       "primal_objective": ci[0].primal_objective if len(ci) else None,
                       "relative_kkt_eps": 1e-6 if name == "c4" else 1e-4}
 
@@ -285,11 +327,16 @@ def main():
     if rank == 0:
         line = {
             "metric": "pdhg_iterations_per_sec", "value": steps_per_sec, "unit": "iterations/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": 1e3 * seconds_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": dict(config, n=n, m=m, nnz=int(nnz), parallelism="1 GPU" if world == 1 else f"{world} independent replicas"),
+            "ms_per_step": 1e3 * seconds_max / args.steps, "higher_is_better": True, "scaling": "strong" if sharded else "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": dict(config, n=int(n_global), m=m, nnz=int(nnz_global),
+                           parallelism="1 GPU" if world == 1 else (f"column-sharded over {world} GPUs, NCCL all-reduce of K x" if sharded else f"{world} independent replicas")),
             "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "achieved": step_gbs, "peak": peak, "unit": "GB/s", "frac": step_gbs / peak, "traffic": None,
-                         "peak_kind": peak_kind, "unit_of_work": "one PDHG trial step (5 kernels)", "algorithmic_bytes_per_step": b_step,
+            "nvlink": {"allreduce_bytes_per_step_per_rank": 8 * m + 8 * 3, "collectives_per_step": 2} if sharded else None,
+            "roofline": {"bound": "hbm", "achieved": step_gbs, "peak": peak * (world if sharded else 1), "unit": "GB/s",
+                         "frac": step_gbs / (peak * (world if sharded else 1)), "traffic": None,
+                         "peak_kind": peak_kind + (f" x {world} GPUs" if sharded else ""), "unit_of_work": "one PDHG trial step (5 kernels)",
+                         "algorithmic_bytes_per_step": b_step_all,
                          "dominant_kernel": dominant["kernel"], "dominant_kernel_achieved": dominant["achieved_gbs"],
                          "dominant_kernel_frac": (dominant["achieved_gbs"] or 0) / peak, "kernels": kernels},
             "cpu_baseline": cpu,

@@ -73,6 +73,7 @@ typedef struct {
   double setup_seconds;         /* upload + transpose + stats + rescaling */
   double loop_seconds;          /* host wall time of the iteration loop */
   double device_loop_seconds;   /* CUDA-event time of the iteration loop */
+  long long collectives;        /* NCCL all-reduces enqueued (0 on one GPU) */
 } pdlp_b200_counters;
 
 /* Solves `problem`.
@@ -90,6 +91,38 @@ pdlp_b200_status pdlp_b200_solve(const pdlp_b200_problem* problem, const uint8_t
                                  const volatile int* interrupt, pdlp_b200_callback callback, void* callback_user, int device,
                                  double* primal_solution, double* dual_solution, double* reduced_costs, int* has_solution,
                                  uint8_t** solve_log, size_t* solve_log_len, pdlp_b200_counters* counters);
+
+/* ---- column-sharded solve over several GPUs (one process per GPU) ----
+ * The reference shards every pass over K by columns across CPU threads (ShardedQuadraticProgram,
+ * sharded_quadratic_program.h:38-60; Sharder mass rule sharder.cc:94-138).  Here rank r of `world`
+ * owns the contiguous column block [column_offset, column_offset + block.num_variables) of the
+ * global problem: `block` holds those columns of K (row indices stay global, num_constraints = m)
+ * and the matching slices of the objective vector / diagonal and the variable bounds; the
+ * constraint bounds are given in full on every rank.  The data path has one exchange step per
+ * trial step (an NCCL all-reduce of the partial K x, m doubles) plus scalar all-reduces.
+ * nccl_unique_id: PDLP_B200_UNIQUE_ID_BYTES bytes from pdlp_b200_unique_id() on ONE rank,
+ * distributed to the others by the caller (any channel: MPI, torch.distributed, a file).
+ * world == 1 or shard == NULL: a plain single-GPU solve. */
+#define PDLP_B200_UNIQUE_ID_BYTES 128
+typedef struct {
+  int rank, world;
+  int64_t global_num_variables;
+  int64_t column_offset;
+  const uint8_t* nccl_unique_id;
+} pdlp_b200_shard;
+
+pdlp_b200_status pdlp_b200_unique_id(uint8_t* out /*PDLP_B200_UNIQUE_ID_BYTES*/);
+
+/* Same contract as pdlp_b200_solve; every rank must call it with the same params and the same
+ * presence of initial solution / interrupt / callback.  initial_primal_solution, primal_solution
+ * and reduced_costs are this rank's block (block.num_variables entries); the dual vectors are
+ * whole (m) and identical on all ranks, as is the SolveLog (up to wall-clock fields).  The
+ * interrupt flag may be raised on any rank: all ranks stop at the same iteration. */
+pdlp_b200_status pdlp_b200_solve_sharded(const pdlp_b200_problem* block, const pdlp_b200_shard* shard, const uint8_t* params, size_t params_len,
+                                         const double* initial_primal_solution, const double* initial_dual_solution,
+                                         const volatile int* interrupt, pdlp_b200_callback callback, void* callback_user, int device,
+                                         double* primal_solution, double* dual_solution, double* reduced_costs, int* has_solution,
+                                         uint8_t** solve_log, size_t* solve_log_len, pdlp_b200_counters* counters);
 
 /* ValidatePrimalDualHybridGradientParams (solvers_proto_validation.cc:171-298): returns
  * PDLP_B200_OK and *message = NULL when valid, else *message = malloc'ed status text. */
@@ -125,6 +158,10 @@ void pdlp_b200_free(void* p);
 typedef struct pdlp_b200_device_problem pdlp_b200_device_problem;
 
 pdlp_b200_status pdlp_b200_problem_create(const pdlp_b200_problem* problem, int device, pdlp_b200_device_problem** out);
+/* The handle of one rank's column block: every kernel-level entry point below then works on the
+ * block (primal-side arguments have block.num_variables entries) and is collective. */
+pdlp_b200_status pdlp_b200_problem_create_sharded(const pdlp_b200_problem* block, const pdlp_b200_shard* shard, int device,
+                                                  pdlp_b200_device_problem** out);
 void pdlp_b200_problem_destroy(pdlp_b200_device_problem* h);
 
 /* TransposedMatrixVectorProduct (sharder.cc:163-176): which = 0 -> out[n] = K^T v[m],

@@ -29,6 +29,28 @@ if not os.path.exists(LIBRARY_PATH):
     )
 _lib = ctypes.CDLL(LIBRARY_PATH)
 
+
+def _prefer_bundled_nccl():
+    """The library resolves NCCL with dlopen at the first sharded call.  In a Python process torch
+    may be imported later and needs ITS NCCL build under the soname libnccl.so.2, so point the
+    library at the copy torch ships (the nvidia-nccl wheel) instead of a system-wide one."""
+    if os.environ.get("PDLP_B200_NCCL_LIBRARY"):
+        return
+    try:
+        import importlib.util
+
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for root in (spec.submodule_search_locations if spec is not None else []):
+            path = os.path.join(root, "lib", "libnccl.so.2")
+            if os.path.exists(path):
+                os.environ["PDLP_B200_NCCL_LIBRARY"] = path
+                return
+    except (ImportError, ValueError):
+        pass
+
+
+_prefer_bundled_nccl()
+
 _c_double_p = ctypes.POINTER(ctypes.c_double)
 _c_int64_p = ctypes.POINTER(ctypes.c_int64)
 _c_uint8_p = ctypes.POINTER(ctypes.c_uint8)
@@ -61,6 +83,20 @@ class _CCounters(ctypes.Structure):
         ("setup_seconds", ctypes.c_double),
         ("loop_seconds", ctypes.c_double),
         ("device_loop_seconds", ctypes.c_double),
+        ("collectives", ctypes.c_longlong),
+    ]
+
+
+UNIQUE_ID_BYTES = 128
+
+
+class _CShard(ctypes.Structure):
+    _fields_ = [
+        ("rank", ctypes.c_int),
+        ("world", ctypes.c_int),
+        ("global_num_variables", ctypes.c_int64),
+        ("column_offset", ctypes.c_int64),
+        ("nccl_unique_id", ctypes.c_void_p),
     ]
 
 
@@ -75,6 +111,9 @@ _lib.pdlp_b200_solve.argtypes = [
     ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
     ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_size_t), ctypes.POINTER(_CCounters),
 ]
+_lib.pdlp_b200_solve_sharded.argtypes = [ctypes.POINTER(_CProblem), ctypes.POINTER(_CShard)] + _lib.pdlp_b200_solve.argtypes[1:]
+_lib.pdlp_b200_problem_create_sharded.argtypes = [ctypes.POINTER(_CProblem), ctypes.POINTER(_CShard), ctypes.c_int, ctypes.POINTER(ctypes.c_void_p)]
+_lib.pdlp_b200_unique_id.argtypes = [ctypes.c_void_p]
 _lib.pdlp_b200_validate_params.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_void_p)]
 _lib.pdlp_b200_default_params.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_size_t)]
 
@@ -83,7 +122,7 @@ EXPORTED_SYMBOLS = [
     "pdlp_b200_last_error", "pdlp_b200_free", "pdlp_b200_problem_create", "pdlp_b200_problem_destroy",
     "pdlp_b200_matvec", "pdlp_b200_scaled_norms", "pdlp_b200_stats", "pdlp_b200_rescale", "pdlp_b200_kkt_stats",
     "pdlp_b200_reduced_costs", "pdlp_b200_localized_bounds", "pdlp_b200_trial_steps", "pdlp_b200_trial_steps_profiled",
-    "pdlp_b200_check_termination",
+    "pdlp_b200_check_termination", "pdlp_b200_unique_id", "pdlp_b200_solve_sharded", "pdlp_b200_problem_create_sharded",
 ]
 
 
@@ -149,4 +188,11 @@ from ._api import (  # noqa: E402
     primal_dual_hybrid_gradient,
     validate_params,
     validate_quadratic_program_dimensions,
+)
+from .sharding import (  # noqa: E402
+    ColumnShard,
+    column_partition,
+    primal_dual_hybrid_gradient_sharded,
+    take_columns,
+    unique_id,
 )

@@ -194,8 +194,8 @@ def last_solve_counters():
     return dict(_last_counters)
 
 
-def primal_dual_hybrid_gradient(qp, params, initial_solution=None, interrupt_solve=None, iteration_stats_callback=None, device=-1):
-    """primal_dual_hybrid_gradient.h:140-156.  `interrupt_solve`, if given, is a
+def primal_dual_hybrid_gradient(qp, params, initial_solution=None, interrupt_solve=None, iteration_stats_callback=None, device=-1, shard=None):
+    """primal_dual_hybrid_gradient.h:140-156.  `shard` (sharding.ColumnShard): `qp` is this rank's column block.  `interrupt_solve`, if given, is a
     numpy int32 array of one element (non-zero = stop); `iteration_stats_callback`
     receives an IterationCallbackInfo."""
     dim_error = _dimension_error(qp)
@@ -254,8 +254,8 @@ def primal_dual_hybrid_gradient(qp, params, initial_solution=None, interrupt_sol
     if interrupt_solve is not None:
         assert interrupt_solve.dtype == np.int32 and interrupt_solve.size >= 1
         interrupt_ptr = ctypes.c_void_p(interrupt_solve.ctypes.data)
-    status = _lib.pdlp_b200_solve(
-        ctypes.byref(mar.c_problem), pbytes, len(pbytes), _vptr(x0), _vptr(y0), interrupt_ptr,
+    status = _lib.pdlp_b200_solve_sharded(
+        ctypes.byref(mar.c_problem), ctypes.byref(shard.c_shard) if shard is not None else None, pbytes, len(pbytes), _vptr(x0), _vptr(y0), interrupt_ptr,
         ctypes.cast(cb, ctypes.c_void_p) if cb is not None else None, None, int(device),
         _vptr(primal), _vptr(dual), _vptr(reduced), ctypes.byref(has_solution), ctypes.byref(log_ptr), ctypes.byref(log_len),
         ctypes.byref(counters),
@@ -271,7 +271,7 @@ def primal_dual_hybrid_gradient(qp, params, initial_solution=None, interrupt_sol
     _last_counters.clear()
     _last_counters.update(
         kernel_launches=counters.kernel_launches, trial_steps=counters.trial_steps, setup_seconds=counters.setup_seconds,
-        loop_seconds=counters.loop_seconds, device_loop_seconds=counters.device_loop_seconds,
+        loop_seconds=counters.loop_seconds, device_loop_seconds=counters.device_loop_seconds, collectives=counters.collectives,
     )
     return result
 
@@ -280,12 +280,14 @@ class DeviceProblem:
     """Kernel-level handle (pdlp_b200_problem_create and friends): a problem resident on
     the device in both matrix orientations, for unit parity tests and profiling."""
 
-    def __init__(self, qp, device=-1):
+    def __init__(self, qp, device=-1, shard=None):
         self._mar = _Marshalled(qp)
         self.n, self.m = self._mar.n, self._mar.m
         self.nnz = self._mar.values.size
         self._h = ctypes.c_void_p()
-        _check(_lib.pdlp_b200_problem_create(ctypes.byref(self._mar.c_problem), int(device), ctypes.byref(self._h)))
+        self._shard = shard
+        _check(_lib.pdlp_b200_problem_create_sharded(ctypes.byref(self._mar.c_problem), ctypes.byref(shard.c_shard) if shard is not None else None,
+                                                     int(device), ctypes.byref(self._h)))
 
     def close(self):
         if self._h:

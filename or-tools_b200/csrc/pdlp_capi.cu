@@ -44,20 +44,31 @@ bool BoundsAreValid(const double* lb, const double* ub, int64_t count) {
 // The checks of pdhg.cc:2787-2826 that need the data (not the dimensions), then the solve.
 SolverResult SolveView(const QpView& qp, const PrimalDualHybridGradientParams& params, const double* x0, const double* y0,
                        const InterruptFlag* interrupt, IterationCallback callback) {
-  if (!BoundsAreValid(qp.clb, qp.cub, qp.m) || !BoundsAreValid(qp.vlb, qp.vub, qp.n))
-    return ErrorSolverResult(TERMINATION_REASON_INVALID_PROBLEM, "The input problem has inconsistent bounds.");
-  if (qp.objective_scaling_factor == 0) return ErrorSolverResult(TERMINATION_REASON_INVALID_PROBLEM, "The objective scaling factor cannot be zero.");
-  if (qp.q != nullptr) {
-    for (int64_t j = 0; j < qp.n; ++j)
-      if (qp.q[j] < 0.0)
-        return ErrorSolverResult(TERMINATION_REASON_INVALID_PROBLEM, "The objective is not convex (i.e., the objective matrix contains negative entries).");
-  }
+  // Data checks in the reference's order; the first that fails wins (smallest code).
+  auto data_error = [&]() -> int {
+    if (!BoundsAreValid(qp.clb, qp.cub, qp.m) || !BoundsAreValid(qp.vlb, qp.vub, qp.n)) return 3;
+    if (qp.objective_scaling_factor == 0) return 2;
+    if (qp.q != nullptr)
+      for (int64_t j = 0; j < qp.n; ++j)
+        if (qp.q[j] < 0.0) return 1;
+    return 0;
+  };
+  auto describe = [](int code) {
+    return ErrorSolverResult(TERMINATION_REASON_INVALID_PROBLEM,
+                             code == 3   ? "The input problem has inconsistent bounds."
+                             : code == 2 ? "The objective scaling factor cannot be zero."
+                                         : "The objective is not convex (i.e., the objective matrix contains negative entries).");
+  };
+  int code = data_error();
+  if (qp.world <= 1 && code != 0) return describe(code);
   if (params.use_feasibility_polishing && qp.q != nullptr)
     return ErrorSolverResult(TERMINATION_REASON_INVALID_PARAMETER, "use_feasibility_polishing is only implemented for linear programs.");
   if (params.presolve_options->use_glop)
     return ErrorSolverResult(TERMINATION_REASON_INVALID_PARAMETER,
                              "presolve_options.use_glop is not supported by the device path: Glop presolve is host-only (run it before the call).");
   PreprocessSolver solver(qp, params);
+  // Sharded: a rank whose block is fine must fail with the rank whose block is not.
+  if (qp.world > 1 && (code = solver.AgreeOnCode(code)) != 0) return describe(code);
   return solver.PreprocessAndSolve(params, x0, y0, interrupt, std::move(callback));
 }
 
@@ -199,6 +210,22 @@ QpView ViewOfC(const pdlp_b200_problem* p) {
   return v;
 }
 
+// Adds the shard description; returns an error text when it is unusable.
+std::string ApplyShard(const pdlp_b200_shard* s, QpView* v) {
+  if (s == nullptr) return "";
+  if (s->world < 1 || s->rank < 0 || s->rank >= s->world) return "shard: rank / world out of range";
+  if (s->world == 1) return "";
+  if (s->nccl_unique_id == nullptr) return "shard: nccl_unique_id is null";
+  if (s->column_offset < 0 || s->global_num_variables < s->column_offset + v->n) return "shard: column block lies outside the global problem";
+  if (v->n < 1 || v->m < 1) return "shard: every rank needs at least one column, and the problem one constraint";
+  v->global_n = s->global_num_variables;
+  v->col_offset = s->column_offset;
+  v->rank = s->rank;
+  v->world = s->world;
+  v->nccl_unique_id = s->nccl_unique_id;
+  return "";
+}
+
 }  // namespace
 
 struct pdlp_b200_device_problem {
@@ -216,9 +243,33 @@ pdlp_b200_status pdlp_b200_solve(const pdlp_b200_problem* problem, const uint8_t
                                  const volatile int* interrupt, pdlp_b200_callback callback, void* callback_user, int device, double* primal,
                                  double* dual, double* reduced, int* has_solution, uint8_t** solve_log, size_t* solve_log_len,
                                  pdlp_b200_counters* counters) {
+  return pdlp_b200_solve_sharded(problem, nullptr, params_bytes, params_len, x0, y0, interrupt, callback, callback_user, device, primal, dual, reduced,
+                                 has_solution, solve_log, solve_log_len, counters);
+}
+
+pdlp_b200_status pdlp_b200_unique_id(uint8_t* out) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (out == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "out is null");
+    NcclApi& api = NcclApi::Get();
+    if (!api.ok()) return Fail(PDLP_B200_INTERNAL_ERROR, "NCCL could not be loaded: " + api.error());
+    ncclUniqueId id;
+    const ncclResult_t r = api.GetUniqueId(&id);
+    if (r != ncclSuccess) return Fail(PDLP_B200_INTERNAL_ERROR, std::string("ncclGetUniqueId failed: ") + api.GetErrorString(r));
+    static_assert(NCCL_UNIQUE_ID_BYTES == PDLP_B200_UNIQUE_ID_BYTES, "unique id size");
+    std::memcpy(out, id.internal, NCCL_UNIQUE_ID_BYTES);
+    return PDLP_B200_OK;
+  });
+}
+
+pdlp_b200_status pdlp_b200_solve_sharded(const pdlp_b200_problem* problem, const pdlp_b200_shard* shard, const uint8_t* params_bytes, size_t params_len,
+                                         const double* x0, const double* y0, const volatile int* interrupt, pdlp_b200_callback callback,
+                                         void* callback_user, int device, double* primal, double* dual, double* reduced, int* has_solution,
+                                         uint8_t** solve_log, size_t* solve_log_len, pdlp_b200_counters* counters) {
   return Guard([&]() -> pdlp_b200_status {
     if (!ProblemPointersOk(problem) || solve_log == nullptr || solve_log_len == nullptr || has_solution == nullptr)
       return Fail(PDLP_B200_BAD_ARGUMENT, "null or negative-sized argument");
+    QpView view = ViewOfC(problem);
+    if (const std::string e = ApplyShard(shard, &view); !e.empty()) return Fail(PDLP_B200_BAD_ARGUMENT, e);
     if ((x0 == nullptr) != (y0 == nullptr)) {
       // A zero-length side may legitimately be null when the other is given.
       if (!((x0 == nullptr && problem->num_variables == 0) || (y0 == nullptr && problem->num_constraints == 0)))
@@ -246,7 +297,7 @@ pdlp_b200_status pdlp_b200_solve(const pdlp_b200_problem* problem, const uint8_t
       }
       static const double kEmpty = 0.0;
       const bool warm = x0 != nullptr || y0 != nullptr;
-      result = SolveView(ViewOfC(problem), params, warm ? (x0 ? x0 : &kEmpty) : nullptr, warm ? (y0 ? y0 : &kEmpty) : nullptr,
+      result = SolveView(view, params, warm ? (x0 ? x0 : &kEmpty) : nullptr, warm ? (y0 ? y0 : &kEmpty) : nullptr,
                          interrupt != nullptr ? &flag : nullptr, std::move(cb));
     }
     if (static_cast<int64_t>(result.primal_solution.size()) == problem->num_variables &&
@@ -269,6 +320,7 @@ pdlp_b200_status pdlp_b200_solve(const pdlp_b200_problem* problem, const uint8_t
       counters->setup_seconds = c.setup_seconds;
       counters->loop_seconds = c.loop_seconds;
       counters->device_loop_seconds = c.device_loop_seconds;
+      counters->collectives = c.collectives;
     }
     return PDLP_B200_OK;
   });
@@ -338,12 +390,18 @@ pdlp_b200_status pdlp_b200_describe_schema(char** text) {
 }
 
 pdlp_b200_status pdlp_b200_problem_create(const pdlp_b200_problem* problem, int device, pdlp_b200_device_problem** out) {
+  return pdlp_b200_problem_create_sharded(problem, nullptr, device, out);
+}
+
+pdlp_b200_status pdlp_b200_problem_create_sharded(const pdlp_b200_problem* problem, const pdlp_b200_shard* shard, int device,
+                                                  pdlp_b200_device_problem** out) {
   return Guard([&]() -> pdlp_b200_status {
     if (!ProblemPointersOk(problem) || out == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "null or negative-sized argument");
+    QpView v = ViewOfC(problem);
+    if (const std::string e = ApplyShard(shard, &v); !e.empty()) return Fail(PDLP_B200_BAD_ARGUMENT, e);
     SelectDevice(device);
     auto h = std::make_unique<pdlp_b200_device_problem>();
     PDLP_CUDA_CHECK(cudaGetDevice(&h->device));
-    QpView v = ViewOfC(problem);
     v.name = nullptr;
     h->pre = std::make_unique<PreprocessSolver>(v, PrimalDualHybridGradientParams());
     *out = h.release();

@@ -25,6 +25,13 @@ struct QpView {
   const double* clb = nullptr; const double* cub = nullptr;
   double objective_offset = 0.0, objective_scaling_factor = 1.0;
   const char* name = nullptr;
+  // Column-sharded solve: this view is the block of columns
+  // [col_offset, col_offset + n) of a problem with global_n columns; rank / world / unique_id
+  // identify the NCCL communicator.  world == 1: the whole problem, no communicator.
+  int64_t global_n = -1, col_offset = 0;
+  int rank = 0, world = 1;
+  const void* nccl_unique_id = nullptr;  // 128 bytes
+  int64_t GlobalN() const { return global_n >= 0 ? global_n : n; }
 };
 
 using IterationCallback = std::function<void(const IterationCallbackInfo&)>;
@@ -68,6 +75,11 @@ class PreprocessSolver {
   SolverResult ConstructOriginalSolverResult(const PrimalDualHybridGradientParams& params, const double* x, const double* y, SolveLog log);
 
   QuadraticProgramStats ComputeStats();
+  // Sharded solves: the largest `code` over all ranks (every rank must call it).
+  int AgreeOnCode(int code);
+  // Max over ranks of each of `count` (<= 8) non-negative values, in place.
+  void AgreeOnMax(double* values, int count);
+  bool sharded() const { return comm_.sharded(); }
   // Kernel-level entry (pdlp_b200_rescale): ApplyRescaling on the resident problem.
   void RescaleForTest(const PrimalDualHybridGradientParams& params) { ApplyRescaling(params); }
   Workspace& ws() { return ws_; }
@@ -80,6 +92,7 @@ class PreprocessSolver {
   void AddRandomProjections(const double* x, const double* y, PointMetadata* md);
 
   QpView view_;
+  Comm comm_;
   Workspace ws_;
   DeviceProblem problem_;
   QuadraticProgramBoundNorms original_bound_norms_;
@@ -150,6 +163,13 @@ class Solver {
   struct { double distance_moved_last_restart_period = std::numeric_limits<double>::infinity(); int length_of_last_restart_period = 1; } distance_info_;
   int poll_iterations_ = 8;
   bool poll_always_ = false;
+  // Sharded solves: host decisions must be identical on every rank, so the two rank-local
+  // inputs (wall clock, interrupt flag) are agreed on (max over ranks) once per host event.
+  void AgreeOnClockAndInterrupt(const InterruptFlag* interrupt);
+  double Seconds() const { return pre_->sharded() ? agreed_seconds_ : preprocessing_time_sec_ + timer_.Get(); }
+  double agreed_seconds_ = 0.0;
+  int agreed_seconds_iteration_ = 0;
+  InterruptFlag agreed_interrupt_;
   double device_loop_seconds_ = 0.0;
   // Holders for the result of feasibility polishing (device vectors must outlive Solve()).
   DVec polished_x_, polished_y_;

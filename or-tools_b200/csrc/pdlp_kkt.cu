@@ -145,12 +145,12 @@ KktTotals ComputeKktTotals(Workspace& ws, const DeviceProblem& p, const double* 
   int g_row = 0, g_col = 0;
   if (p.m > 0) {
     g_row = EnqueueRows(ws, KktRowOp{{}, csr.val.get(), csr.idx.get(), x, y, y_start, p.row_scale.get(), p.clb.get(), p.cub.get(), cw_primal_offset}, csr, 0);
-    EnqueueFinalize<KktRowOp>(ws, g_row, 0, 0);
+    EnqueueFinalize<KktRowOp>(ws, g_row, 0, 0, SideOfRows(csr));
   }
   if (p.n > 0) {
     g_col = EnqueueRows(ws, KktColOp{{}, csc.val.get(), csc.idx.get(), y, x, x_start, p.col_scale.get(), p.c.get(), p.q_or_null(), p.vlb.get(), p.vub.get(),
                                      cw_dual_offset, flag ? 1 : 0}, csc, 1);
-    EnqueueFinalize<KktColOp>(ws, g_col, 1, kMaxSlots);
+    EnqueueFinalize<KktColOp>(ws, g_col, 1, kMaxSlots, SideOfRows(csc));
   }
   if (p.m == 0 && p.n == 0) return t;
   const double* h = FetchTotals(ws, 2 * kMaxSlots);

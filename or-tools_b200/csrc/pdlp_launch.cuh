@@ -1,6 +1,16 @@
 // Internal launch helpers shared by the op translation units.
+//
+// Column-sharded solves: every reduction names the SIDE its index range lives on.
+//   kReplicated  dual-side (length m) data: identical on every rank, nothing to combine
+//   kSharded     primal-side (length n_r) data: per-rank partials, all-reduced after finalize
+//   kJoint       the concatenated (n_r + m) range of the trust-region ops: the op itself skips the
+//                replicated tail on ranks != 0, then combined like kSharded
+// and a row-stream launch over the CSR block (`SparseRows::partial_sums`) runs in two phases
+// around an all-reduce of the row sums: the only O(m) collective of the path.
 #ifndef PDLP_B200_LAUNCH_CUH_
 #define PDLP_B200_LAUNCH_CUH_
+
+#include <type_traits>
 
 #include "pdlp_ops.cuh"
 
@@ -15,6 +25,44 @@ struct NoSlots {
   __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
 };
 
+// An op whose row accumulator combines with max instead of + declares `bool RowCombineMax() const`.
+template <class Op, class = void>
+struct HasRowCombineMax : std::false_type {};
+template <class Op>
+struct HasRowCombineMax<Op, std::void_t<decltype(std::declval<const Op&>().RowCombineMax())>> : std::true_type {};
+template <class Op>
+inline bool RowCombineIsMax(const Op& op) {
+  if constexpr (HasRowCombineMax<Op>::value) return op.RowCombineMax();
+  else return false;
+}
+
+// Phase 1 of a sharded CSR pass: this rank's part of every row sum, stored.
+template <class Op>
+struct PartialRowOp {
+  static constexpr int kNumSlots = 0;
+  __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
+  Op op;
+  double* out;
+  __device__ bool Begin() { return op.Begin(); }
+  __device__ double Load(int64_t k) const { return op.Load(k); }
+  __device__ double RowInit() const { return op.RowInit(); }
+  __device__ double RowAdd(double acc, double staged, int row) const { return op.RowAdd(acc, staged, row); }
+  __device__ double RowMerge(double a, double b) const { return op.RowMerge(a, b); }
+  __device__ void RowFinish(int row, double acc, Slots<0>&) const { out[row] = acc; }
+};
+// Phase 2: the op's epilogue on the all-reduced row sums.
+template <class Op>
+struct FinishRowOp {
+  static constexpr int kNumSlots = Op::kNumSlots;
+  __host__ __device__ static constexpr int SlotKindOf(int s) { return Op::SlotKindOf(s); }
+  Op op;
+  const double* sums;
+  __device__ bool Begin() { return op.Begin(); }
+  __device__ void Apply(int64_t i, Slots<Op::kNumSlots>& acc) const { op.RowFinish(static_cast<int>(i), sums[i], acc); }
+};
+
+inline bool IsSharded(const Workspace& ws) { return ws.comm != nullptr && ws.comm->sharded(); }
+
 // Enqueue only (no finalize, no sync): partial sums land in ws.partials[region].
 template <class Op>
 inline int EnqueueMap(Workspace& ws, const Op& op, int64_t count, int region = 0) {
@@ -25,18 +73,53 @@ inline int EnqueueMap(Workspace& ws, const Op& op, int64_t count, int region = 0
 }
 template <class Op>
 inline int EnqueueRows(Workspace& ws, const Op& op, const SparseRows& s, int region = 0) {
+  if (s.partial_sums && IsSharded(ws)) {
+    double* sums = ws.partial_rows.get();
+    rowstream_kernel<PartialRowOp<Op>><<<s.Grid(), kBlock, 0, ws.stream>>>(PartialRowOp<Op>{op, sums}, s.View(), ws.partials[region].get());
+    ws.comm->AllReduce(sums, static_cast<size_t>(s.rows), RowCombineIsMax(op), ws.stream);
+    const int grid = GridFor(s.rows);
+    map_reduce_kernel<FinishRowOp<Op>><<<grid, kBlock, 0, ws.stream>>>(FinishRowOp<Op>{op, sums}, s.rows, ws.partials[region].get());
+    ws.launches += 2;
+    return grid;
+  }
   const int grid = s.Grid();
   rowstream_kernel<Op><<<grid, kBlock, 0, ws.stream>>>(op, s.View(), ws.partials[region].get());
   ++ws.launches;
   return grid;
 }
+// Side of the reduction slots of a row-stream launch: the CSC block's "rows" are this rank's
+// columns of K (sharded); the CSR block's rows are all of K's rows (replicated after phase 2).
+inline Side SideOfRows(const SparseRows& s) { return s.sharded_rows ? Side::kSharded : Side::kReplicated; }
 
-// Finalize `region` into ws.totals[offset ...] (device), no sync.
 template <class Op>
-inline void EnqueueFinalize(Workspace& ws, int grid, int region, int offset) {
+__global__ void select_max_slots_kernel(double* totals, const double* max_reduced) {
+  const int s = threadIdx.x;
+  if (s < Op::kNumSlots && Op::SlotKindOf(s) == kMax) totals[s] = max_reduced[s];
+}
+
+// Finalize `region` into ws.totals[offset ...] (device) and, for sharded sides, combine the
+// per-rank totals in place; no sync.
+template <class Op>
+inline void EnqueueFinalize(Workspace& ws, int grid, int region, int offset, Side side) {
   if (Op::kNumSlots == 0) return;
-  finalize_kernel<Op><<<1, kBlock, 0, ws.stream>>>(ws.partials[region].get(), grid, ws.totals.get() + offset);
+  double* totals = ws.totals.get() + offset;
+  finalize_kernel<Op><<<1, kBlock, 0, ws.stream>>>(ws.partials[region].get(), grid, totals);
   ++ws.launches;
+  if (side == Side::kReplicated || !IsSharded(ws)) return;
+  bool any_max = false, any_sum = false;
+  for (int s = 0; s < Op::kNumSlots; ++s) (Op::SlotKindOf(s) == kMax ? any_max : any_sum) = true;
+  if (!any_max) {
+    ws.comm->AllReduce(totals, Op::kNumSlots, false, ws.stream);
+  } else if (!any_sum) {
+    ws.comm->AllReduce(totals, Op::kNumSlots, true, ws.stream);
+  } else {
+    double* tmp = ws.combine_tmp.get();
+    PDLP_CUDA_CHECK(cudaMemcpyAsync(tmp, totals, Op::kNumSlots * sizeof(double), cudaMemcpyDeviceToDevice, ws.stream));
+    ws.comm->AllReduce(totals, Op::kNumSlots, false, ws.stream);
+    ws.comm->AllReduce(tmp, Op::kNumSlots, true, ws.stream);
+    select_max_slots_kernel<Op><<<1, 32, 0, ws.stream>>>(totals, tmp);
+    ++ws.launches;
+  }
 }
 
 // Copies `count` totals to the pinned host buffer and waits.
@@ -49,16 +132,16 @@ inline const double* FetchTotals(Workspace& ws, int count) {
 
 // Run + reduce + read back.
 template <class Op>
-inline const double* RunMap(Workspace& ws, const Op& op, int64_t count) {
+inline const double* RunMap(Workspace& ws, const Op& op, int64_t count, Side side) {
   const int grid = EnqueueMap(ws, op, count, 0);
-  EnqueueFinalize<Op>(ws, grid, 0, 0);
+  EnqueueFinalize<Op>(ws, grid, 0, 0, side);
   if (Op::kNumSlots == 0) return nullptr;
   return FetchTotals(ws, Op::kNumSlots);
 }
 template <class Op>
 inline const double* RunRows(Workspace& ws, const Op& op, const SparseRows& s) {
   const int grid = EnqueueRows(ws, op, s, 0);
-  EnqueueFinalize<Op>(ws, grid, 0, 0);
+  EnqueueFinalize<Op>(ws, grid, 0, 0, SideOfRows(s));
   if (Op::kNumSlots == 0) return nullptr;
   return FetchTotals(ws, Op::kNumSlots);
 }

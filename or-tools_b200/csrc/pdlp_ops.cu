@@ -16,6 +16,8 @@ void Workspace::Init(int64_t n_, int64_t m_) {
   for (auto& v : scratch_n) v.Resize(n > 0 ? n : 1);
   for (auto& v : scratch_m) v.Resize(m > 0 ? m : 1);
   for (auto& v : scratch_nm) v.Resize(n + m > 0 ? n + m : 1);
+  partial_rows.Resize(m > 0 ? m : 1);
+  combine_tmp.Resize(kMaxSlots);
 }
 
 void Workspace::Destroy() {
@@ -91,6 +93,7 @@ struct RowNormOp : AlwaysActive, NoSlots {
   __device__ double RowAdd(double acc, double staged, int) const { return l2 ? acc + staged * staged : fmax(acc, fabs(staged)); }
   __device__ double RowMerge(double a, double b) const { return l2 ? a + b : fmax(a, b); }
   __device__ void RowFinish(int row, double acc, Slots<0>&) const { out[row] = (l2 ? sqrt(acc) : acc) * fabs(row_scale[row]); }
+  __host__ __device__ bool RowCombineMax() const { return l2 == 0; }
 };
 
 struct DivSqrtOp : AlwaysActive, NoSlots {
@@ -194,11 +197,11 @@ struct RowDotOp : AlwaysActive, NoSlots {
 
 }  // namespace
 
-VectorInfo ComputeVectorInfo(Workspace& ws, InfoKind kind, const double* a, const double* b, int64_t count) {
+VectorInfo ComputeVectorInfo(Workspace& ws, InfoKind kind, const double* a, const double* b, int64_t count, Side side) {
   VectorInfo r;
   double t[7] = {0, 0, 0, -INFINITY, -INFINITY, 0, 0};
   if (count > 0) {
-    const double* h = RunMap(ws, InfoOp{{}, a, b, static_cast<int>(kind)}, count);
+    const double* h = RunMap(ws, InfoOp{{}, a, b, static_cast<int>(kind)}, count, side);
     for (int i = 0; i < 7; ++i) t[i] = h[i];
   }
   r.num_infinite = static_cast<int64_t>(t[0]);
@@ -260,16 +263,16 @@ void CopyVector(Workspace& ws, double* dst, const double* src, int64_t count) {
 void SubtractVectors(Workspace& ws, double* dst, const double* a, const double* b, int64_t count) {
   if (count > 0) EnqueueMap(ws, SubOp{{}, {}, dst, a, b}, count);
 }
-void NormAndMax(Workspace& ws, const double* v, int64_t count, double* l2, double* linf) {
+void NormAndMax(Workspace& ws, const double* v, int64_t count, double* l2, double* linf, Side side) {
   *l2 = 0.0; *linf = 0.0;
   if (count == 0) return;
-  const double* h = RunMap(ws, NormMaxOp{{}, v}, count);
+  const double* h = RunMap(ws, NormMaxOp{{}, v}, count, side);
   *l2 = std::sqrt(h[0]);
   *linf = h[1] < 0 ? 0.0 : h[1];
 }
-double SquaredDistance(Workspace& ws, const double* a, const double* b, int64_t count) {
+double SquaredDistance(Workspace& ws, const double* a, const double* b, int64_t count, Side side) {
   if (count == 0) return 0.0;
-  return RunMap(ws, SqDistOp{{}, a, b}, count)[0];
+  return RunMap(ws, SqDistOp{{}, a, b}, count, side)[0];
 }
 
 void RowDot(Workspace& ws, const SparseRows& s, const double* v, double* out) {

@@ -7,6 +7,7 @@
 #include <cmath>
 #include <limits>
 
+#include "pdlp_comm.h"
 #include "pdlp_matrix.cuh"
 
 namespace pdlp_b200 {
@@ -24,6 +25,9 @@ struct DeviceProblem {
   const double* q_or_null() const { return is_lp ? nullptr : q.get(); }
 };
 
+// Which side of a column-sharded solve a reduction's index range lives on (pdlp_launch.cuh).
+enum class Side { kReplicated, kSharded, kJoint };
+
 // Launch context: stream, per-kernel partial buffers, totals, pinned read-back.
 struct Workspace {
   cudaStream_t stream = nullptr;
@@ -34,6 +38,9 @@ struct Workspace {
   int64_t n = 0, m = 0;
   long long launches = 0;    // kernels launched (bench "gpu_launches")
   std::vector<cudaEvent_t>* profile = nullptr;  // when set, the trial-step launcher records an event around every kernel
+  Comm* comm = nullptr;      // null or world 1: single GPU.  Otherwise this rank owns a column block of K
+  DVec partial_rows;         // m: per-rank row sums of a sharded CSR pass, all-reduced in place
+  DVec combine_tmp;          // kMaxSlots: max-reduced copy of mixed sum/max totals
   void Init(int64_t n_, int64_t m_);
   void Destroy();
   void Sync() { PDLP_CUDA_CHECK(cudaStreamSynchronize(stream)); }
@@ -86,7 +93,7 @@ struct VectorInfo {  // sharded_optimization_utils.cc:117-177 VectorInfoAccumula
 };
 enum class InfoKind { kPlain, kCombinedBounds, kGap };
 // kPlain: a[i]; kCombinedBounds: CombineBounds(a[i], b[i]) (sou.cc:83-92); kGap: b[i]-a[i].
-VectorInfo ComputeVectorInfo(Workspace& ws, InfoKind kind, const double* a, const double* b, int64_t count);
+VectorInfo ComputeVectorInfo(Workspace& ws, InfoKind kind, const double* a, const double* b, int64_t count, Side side);
 
 // sharded_quadratic_program.cc:119-130,169-175.
 void ReplaceLargeBoundsWithInfinity(Workspace& ws, double* clb, double* cub, int64_t m, double threshold);
@@ -110,7 +117,7 @@ void CopyVector(Workspace& ws, double* dst, const double* src, int64_t count);
 // dst = a - b.
 void SubtractVectors(Workspace& ws, double* dst, const double* a, const double* b, int64_t count);
 // NaN / magnitude screen of an initial solution: out = {sum of squares, max |v|}.
-void NormAndMax(Workspace& ws, const double* v, int64_t count, double* l2, double* linf);
+void NormAndMax(Workspace& ws, const double* v, int64_t count, double* l2, double* linf, Side side);
 
 // out = M v by rows (K^T y with the CSC copy, K x with the CSR copy); sharder.cc:163-176.
 void RowDot(Workspace& ws, const SparseRows& s, const double* v, double* out);
@@ -139,7 +146,7 @@ void ComputeReducedCosts(Workspace& ws, const DeviceProblem& p, const double* x,
                          bool handle_some_primal_gradients_on_finite_bounds_as_residuals, double* rc);
 
 // ---- restarts (trust_region.cc:886-1016, sou.cc:446-527) ----
-double SquaredDistance(Workspace& ws, const double* a, const double* b, int64_t count);
+double SquaredDistance(Workspace& ws, const double* a, const double* b, int64_t count, Side side);
 struct LocalizedBounds { double lagrangian_value, lower_bound, upper_bound, radius; };
 // Euclidean-norm localized Lagrangian bounds at (x, y).  kty may be null (computed).
 LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProblem& p, const double* x, const double* y, const double* kty_or_null,

@@ -5,6 +5,7 @@
 #include <random>
 
 #include "pdlp_driver.h"
+#include "pdlp_launch.cuh"
 
 namespace pdlp_b200 {
 
@@ -61,12 +62,19 @@ PreprocessSolver::PreprocessSolver(const QpView& qp, const PrimalDualHybridGradi
   // num_threads / num_shards (pdhg.cc:71-96) configure the reference's CPU thread pool;
   // the device path accepts and ignores them.
   ws_.Init(qp.n, qp.m);
+  if (qp.world > 1) {
+    if (qp.n < 1 || qp.m < 1) throw std::invalid_argument("pdlp_b200: a sharded solve needs at least one column per rank and one constraint");
+    comm_.Init(qp.rank, qp.world, qp.nccl_unique_id);
+    ws_.comm = &comm_;
+  }
   problem_.n = qp.n;
   problem_.m = qp.m;
   problem_.is_lp = qp.q == nullptr;
   problem_.objective_offset = qp.objective_offset;
   problem_.objective_scaling_factor = qp.objective_scaling_factor;
   BuildDeviceMatrix(qp.n, qp.m, qp.nnz, qp.col_ptr, qp.row_idx, qp.val, ws_.stream, &problem_.K);
+  problem_.K.by_col.sharded_rows = comm_.sharded();
+  problem_.K.by_row.partial_sums = comm_.sharded();
   auto up = [&](DVec& d, const double* h, int64_t count) {
     d.Resize(count > 0 ? count : 1);
     d.Upload(h, count, ws_.stream);
@@ -85,7 +93,23 @@ PreprocessSolver::PreprocessSolver(const QpView& qp, const PrimalDualHybridGradi
   ws_.Sync();
 }
 
-PreprocessSolver::~PreprocessSolver() { ws_.Destroy(); }
+PreprocessSolver::~PreprocessSolver() {
+  comm_.Destroy();
+  ws_.Destroy();
+}
+
+void PreprocessSolver::AgreeOnMax(double* values, int count) {
+  if (!comm_.sharded()) return;
+  PDLP_CUDA_CHECK(cudaMemcpyAsync(ws_.totals.get(), values, count * sizeof(double), cudaMemcpyHostToDevice, ws_.stream));
+  comm_.AllReduce(ws_.totals.get(), count, true, ws_.stream);
+  const double* agreed = FetchTotals(ws_, count);
+  for (int i = 0; i < count; ++i) values[i] = agreed[i];
+}
+int PreprocessSolver::AgreeOnCode(int code) {
+  double v = code;
+  AgreeOnMax(&v, 1);
+  return static_cast<int>(v);
+}
 
 // sharded_optimization_utils.cc:270-343.
 QuadraticProgramStats PreprocessSolver::ComputeStats() {
@@ -100,14 +124,14 @@ QuadraticProgramStats PreprocessSolver::ComputeStats() {
   double* col_norms = ws_.scratch_n[2].get();
   ScaledRowNorms(ws_, p.K.by_row, ones_n, ones_m, false, row_norms);
   ScaledRowNorms(ws_, p.K.by_col, ones_m, ones_n, false, col_norms);
-  const VectorInfo rn = ComputeVectorInfo(ws_, InfoKind::kPlain, row_norms, nullptr, p.m);
-  const VectorInfo cn = ComputeVectorInfo(ws_, InfoKind::kPlain, col_norms, nullptr, p.n);
-  const VectorInfo mat = ComputeVectorInfo(ws_, InfoKind::kPlain, p.K.by_col.val.get(), nullptr, p.K.by_col.nnz);
-  const VectorInfo cb = ComputeVectorInfo(ws_, InfoKind::kCombinedBounds, p.cub.get(), p.clb.get(), p.m);
-  const VectorInfo vb = ComputeVectorInfo(ws_, InfoKind::kCombinedBounds, p.vub.get(), p.vlb.get(), p.n);
-  const VectorInfo ov = ComputeVectorInfo(ws_, InfoKind::kPlain, p.c.get(), nullptr, p.n);
-  const VectorInfo gaps = ComputeVectorInfo(ws_, InfoKind::kGap, p.vlb.get(), p.vub.get(), p.n);
-  s.num_variables = p.n;
+  const VectorInfo rn = ComputeVectorInfo(ws_, InfoKind::kPlain, row_norms, nullptr, p.m, Side::kReplicated);
+  const VectorInfo cn = ComputeVectorInfo(ws_, InfoKind::kPlain, col_norms, nullptr, p.n, Side::kSharded);
+  const VectorInfo mat = ComputeVectorInfo(ws_, InfoKind::kPlain, p.K.by_col.val.get(), nullptr, p.K.by_col.nnz, Side::kSharded);
+  const VectorInfo cb = ComputeVectorInfo(ws_, InfoKind::kCombinedBounds, p.cub.get(), p.clb.get(), p.m, Side::kReplicated);
+  const VectorInfo vb = ComputeVectorInfo(ws_, InfoKind::kCombinedBounds, p.vub.get(), p.vlb.get(), p.n, Side::kSharded);
+  const VectorInfo ov = ComputeVectorInfo(ws_, InfoKind::kPlain, p.c.get(), nullptr, p.n, Side::kSharded);
+  const VectorInfo gaps = ComputeVectorInfo(ws_, InfoKind::kGap, p.vlb.get(), p.vub.get(), p.n, Side::kSharded);
+  s.num_variables = comm_.sharded() ? ov.num_finite_nonzero + ov.num_zero + ov.num_infinite : p.n;  // global count
   s.num_constraints = p.m;
   s.constraint_matrix_col_min_l_inf_norm = cn.smallest;
   s.constraint_matrix_row_min_l_inf_norm = rn.smallest;
@@ -140,7 +164,7 @@ QuadraticProgramStats PreprocessSolver::ComputeStats() {
     s.objective_matrix_abs_avg = std::numeric_limits<double>::quiet_NaN();
     s.objective_matrix_l2_norm = 0;
   } else {
-    const VectorInfo om = ComputeVectorInfo(ws_, InfoKind::kPlain, p.q.get(), nullptr, p.n);
+    const VectorInfo om = ComputeVectorInfo(ws_, InfoKind::kPlain, p.q.get(), nullptr, p.n, Side::kSharded);
     s.objective_matrix_num_nonzeros = om.num_finite_nonzero;
     s.objective_matrix_abs_max = om.largest;
     s.objective_matrix_abs_min = om.smallest;
@@ -194,12 +218,12 @@ SolverResult PreprocessSolver::PreprocessAndSolve(const PrimalDualHybridGradient
     y_start.Upload(y0, p.m, ws_.stream);
     const double kBig = 1e50;
     double l2 = 0, linf = 0;
-    NormAndMax(ws_, x_start.get(), p.n, &l2, &linf);
+    NormAndMax(ws_, x_start.get(), p.n, &l2, &linf, Side::kSharded);
     if (std::isnan(l2)) return ErrorSolverResult(TERMINATION_REASON_INVALID_INITIAL_SOLUTION, "Initial primal solution has a NAN.");
     if (linf > kBig)
       return ErrorSolverResult(TERMINATION_REASON_INVALID_INITIAL_SOLUTION,
                                "Initial primal solution has an entry with absolute value " + SixDigits(linf) + " which exceeds limit of " + SixDigits(kBig));
-    NormAndMax(ws_, y_start.get(), p.m, &l2, &linf);
+    NormAndMax(ws_, y_start.get(), p.m, &l2, &linf, Side::kReplicated);
     if (std::isnan(l2)) return ErrorSolverResult(TERMINATION_REASON_INVALID_INITIAL_SOLUTION, "Initial dual solution has a NAN.");
     if (linf > kBig)
       return ErrorSolverResult(TERMINATION_REASON_INVALID_INITIAL_SOLUTION,
@@ -227,7 +251,9 @@ SolverResult PreprocessSolver::PreprocessAndSolve(const PrimalDualHybridGradient
     const double desired_relative_error = 0.2, failure_probability = 0.0005;
     std::mt19937 random(1);
     std::normal_distribution<double> gauss(0.0, 1.0);
+    // One global sequence; a sharded rank keeps its own slice of it.
     std::vector<double> start(p.n);
+    for (int64_t j = 0; j < view_.col_offset; ++j) (void)gauss(random);
     for (double& v : start) v = gauss(random);
     double* ev = ws_.scratch_n[0].get();
     double* next = ws_.scratch_n[1].get();
@@ -235,7 +261,7 @@ SolverResult PreprocessSolver::PreprocessAndSolve(const PrimalDualHybridGradient
     ws_.scratch_n[0].Upload(start.data(), p.n, ws_.stream);
     auto normalize = [&](double* v) {
       double l2 = 0, linf = 0;
-      NormAndMax(ws_, v, p.n, &l2, &linf);
+      NormAndMax(ws_, v, p.n, &l2, &linf, Side::kSharded);
       if (l2 != 0.0) {
         FillVector(ws_, ws_.scratch_n[2].get(), p.n, l2);
         DivideInPlace(ws_, v, ws_.scratch_n[2].get(), p.n);
@@ -245,7 +271,7 @@ SolverResult PreprocessSolver::PreprocessAndSolve(const PrimalDualHybridGradient
     const double eps = 1.0 - (1.0 - desired_relative_error) * (1.0 - desired_relative_error);
     auto fail_prob = [&](int k) {
       if (k < 2 || eps <= 0.0) return 1.0;
-      return std::min(0.824, 0.354 / std::sqrt(eps * (k - 1))) * std::sqrt(static_cast<double>(p.n)) * std::pow(1.0 - eps, k - 0.5);
+      return std::min(0.824, 0.354 / std::sqrt(eps * (k - 1))) * std::sqrt(static_cast<double>(view_.GlobalN())) * std::pow(1.0 - eps, k - 0.5);
     };
     double estimate = 0.0;
     int iters = 0;
@@ -254,7 +280,7 @@ SolverResult PreprocessSolver::PreprocessAndSolve(const PrimalDualHybridGradient
       RowDot(ws_, p.K.by_col, dual_ev, next);
       // estimate = ev . next = |K ev|^2
       double l2 = 0, linf = 0;
-      NormAndMax(ws_, dual_ev, p.m, &l2, &linf);
+      NormAndMax(ws_, dual_ev, p.m, &l2, &linf, Side::kReplicated);
       estimate = l2 * l2;
       CopyVector(ws_, ev, next, p.n);
       ++iters;
@@ -281,6 +307,7 @@ SolverResult PreprocessSolver::PreprocessAndSolve(const PrimalDualHybridGradient
   SolverResult result = ConstructOriginalSolverResult(params, outcome.x, outcome.y, std::move(outcome.log));
   // Counters for benchmarks.
   g_last_counters.kernel_launches = ws_.launches;
+  g_last_counters.collectives = comm_.collectives();
   g_last_counters.trial_steps = solver.TrialSteps();
   g_last_counters.device_loop_seconds = solver.DeviceLoopSeconds();
   g_last_counters.setup_seconds = result.solve_log.preprocessing_time_sec;
@@ -340,7 +367,7 @@ void PreprocessSolver::ComputeConvergenceAndInfeasibility(const PrimalDualHybrid
       md->active_primal_variable_change = static_cast<int64_t>(t.active_primal_change);
       md->active_dual_variable_change = static_cast<int64_t>(t.active_dual_change);
     }
-    if (!seeds_.empty()) AddRandomProjections(x, y, md);
+    if (!seeds_.empty() && !comm_.sharded()) AddRandomProjections(x, y, md);  // host-side diagnostic of the whole vector: single GPU only
   }
 }
 

@@ -23,6 +23,8 @@ struct JointView {
   const double* gx; const double* gy; const double* x; const double* y;
   const double* vlb; const double* vub; const double* clb; const double* cub; const double* q;
   int64_t n; double w_primal, w_dual;
+  int dual_owner;  // column-sharded solve: only rank 0 accounts for the replicated dual tail of a sum
+  __device__ bool Counts(int64_t i) const { return i < n || dual_owner != 0; }
   __device__ double Objective(int64_t i) const { return i < n ? gx[i] : -gy[i - n]; }
   __device__ double LowerBound(int64_t i) const { return i < n ? vlb[i] : (isfinite(cub[i - n]) ? -INFINITY : 0.0); }
   __device__ double UpperBound(int64_t i) const { return i < n ? vub[i] : (isfinite(clb[i - n]) ? INFINITY : 0.0); }
@@ -113,8 +115,9 @@ struct CriticalOp : AlwaysActive {
 struct RadiusPassOp : AlwaysActive {
   static constexpr int kNumSlots = 3;
   __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
-  const double* crit; const double* coef; double delta;
+  const double* crit; const double* coef; double delta; int64_t n; int dual_owner;
   __device__ void Apply(int64_t i, Slots<3>& r) const {
+    if (i >= n && dual_owner == 0) return;
     const double cs = crit[i], a = coef[i];
     if (cs <= delta) { r.v[0] += a * (cs * cs); r.v[2] += 1.0; }
     else r.v[1] += a;
@@ -127,6 +130,7 @@ struct BoundsDeltaOp : AlwaysActive {
   __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
   JointView p; double step;
   __device__ void Apply(int64_t i, Slots<2>& r) const {
+    if (!p.Counts(i)) return;
     const double sol = p.ProjectedValue(i, step);
     if (i < p.n) r.v[0] += p.gx[i] * (sol - p.x[i]);
     else r.v[1] += p.gy[i - p.n] * (sol - p.y[i - p.n]);
@@ -142,6 +146,7 @@ __device__ __forceinline__ double ProjectedScaledDifference(const JointView& p, 
 struct DeltaNormOp : AlwaysActive, OneSumSlot {
   JointView p; double scaling;
   __device__ void Apply(int64_t i, Slots<1>& r) const {
+    if (!p.Counts(i)) return;
     const double v = ProjectedScaledDifference(p, i, scaling);
     r.v[0] += v * v;
   }
@@ -151,6 +156,7 @@ struct DiagonalBoundsDeltaOp : AlwaysActive {
   __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
   JointView p; double scaling; int at_center;
   __device__ void Apply(int64_t i, Slots<3>& r) const {
+    if (!p.Counts(i)) return;
     const double c = p.Center(i);
     const double sol = at_center ? c : c + sqrt(1.0 / p.Weight(i)) * ProjectedScaledDifference(p, i, scaling);
     const double d = sol - c;
@@ -184,11 +190,12 @@ LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProb
       RowDot(ws, csc, y, ws.scratch_n[1].get());
       kty = ws.scratch_n[1].get();
     }
-    primal_value = RunMap(ws, PrimalGradMapOp{{}, {}, kty, x, p.c.get(), p.q_or_null(), gx}, p.n)[0];
+    primal_value = RunMap(ws, PrimalGradMapOp{{}, {}, kty, x, p.c.get(), p.q_or_null(), gx}, p.n, Side::kSharded)[0];
   }
   const double lagrangian = primal_value + dual_value;
   const int64_t total = p.n + p.m;
-  JointView view{gx, gy, x, y, p.vlb.get(), p.vub.get(), p.clb.get(), p.cub.get(), p.q_or_null(), p.n, 0.5 * primal_weight, 0.5 / primal_weight};
+  JointView view{gx, gy, x, y, p.vlb.get(), p.vub.get(), p.clb.get(), p.cub.get(), p.q_or_null(), p.n, 0.5 * primal_weight, 0.5 / primal_weight,
+                 (!IsSharded(ws) || ws.comm->rank() == 0) ? 1 : 0};
   int passes = 0;
   LocalizedBounds out{lagrangian, lagrangian, lagrangian, radius};
   if (total == 0) { if (tr_passes) *tr_passes = 0; return out; }
@@ -198,7 +205,7 @@ LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProb
     if (radius == 0.0) {
       // Solution is the centre point: both deltas are exactly zero.
     } else {
-      auto norm_at = [&](double scaling) { ++passes; return std::sqrt(RunMap(ws, DeltaNormOp{{}, {}, view, scaling}, total)[0]); };
+      auto norm_at = [&](double scaling) { ++passes; return std::sqrt(RunMap(ws, DeltaNormOp{{}, {}, view, scaling}, total, Side::kJoint)[0]); };
       double lo = 0.0, hi = 1.0;  // FindScalingFactor, trust_region.cc:683-706
       while (norm_at(hi) >= radius) { lo = hi; hi *= 2; }
       while ((hi - lo) >= diagonal_qp_tolerance * std::max(1.0, lo)) {
@@ -206,7 +213,7 @@ LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProb
         if (norm_at(mid) <= radius) hi = mid; else lo = mid;
       }
       const double scaling = (hi + lo) / 2.0;
-      const double* h = RunMap(ws, DiagonalBoundsDeltaOp{{}, view, scaling, 0}, total);
+      const double* h = RunMap(ws, DiagonalBoundsDeltaOp{{}, view, scaling, 0}, total, Side::kJoint);
       primal_delta = h[0] + (p.is_lp ? 0.0 : h[2]);
       dual_delta = h[1];
     }
@@ -221,13 +228,13 @@ LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProb
   if (radius > 0.0) {
     double* crit = ws.scratch_nm[0].get();
     double* coef = ws.scratch_nm[1].get();
-    const double max_obj = RunMap(ws, CriticalOp{{}, view, crit, coef}, total)[0];
+    const double max_obj = RunMap(ws, CriticalOp{{}, view, crit, coef}, total, Side::kJoint)[0];
     if (max_obj > 0.0) {  // otherwise every objective entry is zero: step 0 (trust_region.cc:349-358)
       const double r2 = radius * radius;
       double delta = 0.0;
       double prev_fixed = -1.0;
       for (;;) {
-        const double* h = RunMap(ws, RadiusPassOp{{}, crit, coef, delta}, total);
+        const double* h = RunMap(ws, RadiusPassOp{{}, crit, coef, delta, p.n, view.dual_owner}, total, Side::kJoint);
         ++passes;
         const double fixed_r2 = h[0], free_coef = h[1], num_fixed = h[2];
         if (!(free_coef > 0.0)) { step = DBL_MAX; break; }  // trust_region.cc:438-446
@@ -243,7 +250,7 @@ LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProb
   }
   double primal_delta = 0.0, dual_delta = 0.0;
   {
-    const double* h = RunMap(ws, BoundsDeltaOp{{}, view, step}, total);
+    const double* h = RunMap(ws, BoundsDeltaOp{{}, view, step}, total, Side::kJoint);
     primal_delta = h[0];
     dual_delta = h[1];
   }

@@ -126,7 +126,7 @@ IterationStats Solver::CreateSimpleIterationStats(int restart_used) const {  // 
   s.iteration_number = iterations_completed_;
   s.cumulative_rejected_steps = host_.num_rejected_steps;
   s.cumulative_kkt_matrix_passes = iterations_completed_ + host_.passes_per_rejected_step * host_.num_rejected_steps;
-  s.cumulative_time_sec = preprocessing_time_sec_ + timer_.Get();
+  s.cumulative_time_sec = Seconds();
   s.restart_used = restart_used;
   s.step_size = host_.step_size;
   s.primal_weight = host_.primal_weight;
@@ -134,8 +134,8 @@ IterationStats Solver::CreateSimpleIterationStats(int restart_used) const {  // 
 }
 
 double Solver::DistanceTraveledFromLastStart(const double* x, const double* y) {  // pdhg.cc:1795-1804
-  const double dp = SquaredDistance(ws_, x, it_.x_start.get(), problem_.n);
-  const double dd = SquaredDistance(ws_, y, it_.y_start.get(), problem_.m);
+  const double dp = SquaredDistance(ws_, x, it_.x_start.get(), problem_.n, Side::kSharded);
+  const double dd = SquaredDistance(ws_, y, it_.y_start.get(), problem_.m, Side::kReplicated);
   return std::sqrt((0.5 * host_.primal_weight) * dp + (0.5 / host_.primal_weight) * dd);
 }
 
@@ -219,8 +219,8 @@ int Solver::ChooseRestartToApply(bool is_major_iteration) {  // pdhg.cc:1904-196
 }
 
 double Solver::ComputeNewPrimalWeight() {  // pdhg.cc:1983-2010
-  const double primal_distance = std::sqrt(SquaredDistance(ws_, X(), it_.x_start.get(), problem_.n));
-  const double dual_distance = std::sqrt(SquaredDistance(ws_, Y(), it_.y_start.get(), problem_.m));
+  const double primal_distance = std::sqrt(SquaredDistance(ws_, X(), it_.x_start.get(), problem_.n, Side::kSharded));
+  const double dual_distance = std::sqrt(SquaredDistance(ws_, Y(), it_.y_start.get(), problem_.m, Side::kReplicated));
   constexpr double kNonzeroTol = 1.0e-10;
   if (primal_distance <= kNonzeroTol || primal_distance >= 1.0 / kNonzeroTol || dual_distance <= kNonzeroTol || dual_distance >= 1.0 / kNonzeroTol) {
     return host_.primal_weight;
@@ -296,6 +296,10 @@ Solver::Outcome Solver::PickSolutionAndConstructOutcome(const IterationStats& st
 std::optional<Solver::Outcome> Solver::MajorIterationAndTerminationCheck(IterationType type, bool force_numerical_termination,
                                                                          const InterruptFlag* interrupt,
                                                                          const IterationStats& work_from_feasibility_polishing, SolveLog& log) {  // pdhg.cc:2128-2190
+  if (pre_->sharded()) {
+    AgreeOnClockAndInterrupt(interrupt);
+    interrupt = &agreed_interrupt_;
+  }
   const int major_iteration_cycle = iterations_completed_ % params_.major_iteration_frequency;
   const bool is_major_iteration = major_iteration_cycle == 0 && iterations_completed_ > 0;
   const int restart = force_numerical_termination ? static_cast<int>(RESTART_CHOICE_NO_RESTART) : ChooseRestartToApply(is_major_iteration);
@@ -330,6 +334,19 @@ std::optional<Solver::Outcome> Solver::MajorIterationAndTerminationCheck(Iterati
   return std::nullopt;
 }
 
+void Solver::AgreeOnClockAndInterrupt(const InterruptFlag* interrupt) {
+  double v[2] = {preprocessing_time_sec_ + timer_.Get(), (interrupt != nullptr && interrupt->IsSet()) ? 1.0 : 0.0};
+  pre_->AgreeOnMax(v, 2);
+  const int done = iterations_completed_ - agreed_seconds_iteration_;
+  if (done > 0 && v[0] > agreed_seconds_) {
+    const double per_iteration = (v[0] - agreed_seconds_) / done;
+    poll_iterations_ = static_cast<int>(std::min(4096.0, std::max(1.0, 0.02 / per_iteration)));
+  }
+  agreed_seconds_ = std::max(agreed_seconds_, v[0]);
+  agreed_seconds_iteration_ = iterations_completed_;
+  agreed_interrupt_.agreed = v[1] != 0.0 ? 1 : 0;
+}
+
 IterationStats Solver::TotalWorkSoFar(const SolveLog& log) const {  // pdhg.cc:2408-2413
   return AddWorkStats(CreateSimpleIterationStats(RESTART_CHOICE_NO_RESTART), WorkFromFeasibilityPolishing(log));
 }
@@ -339,6 +356,13 @@ Solver::Outcome Solver::Solve(IterationType type, const InterruptFlag* interrupt
   preprocessing_time_sec_ = log.preprocessing_time_sec;
   timer_.Start();
   poll_always_ = interrupt != nullptr;
+  if (pre_->sharded()) {
+    double v = poll_always_ ? 1.0 : 0.0;
+    pre_->AgreeOnMax(&v, 1);
+    poll_always_ = v != 0.0;
+    agreed_seconds_ = 0.0;
+    agreed_seconds_iteration_ = 0;
+  }
   CopyVector(ws_, it_.x_start.get(), X(), problem_.n);
   CopyVector(ws_, it_.y_start.get(), Y(), problem_.m);
   host_.ratio_last_two_step_sizes = 1.0;
@@ -379,7 +403,7 @@ Solver::Outcome Solver::Solve(IterationType type, const InterruptFlag* interrupt
     // Keep the polling interval near 20 ms of work when a time limit or interrupt is live.
     const double dt = timer_.Get() - t0;
     const int done = iterations_completed_ - before;
-    if (done > 0 && dt > 0.0) {
+    if (done > 0 && dt > 0.0 && !pre_->sharded()) {
       const double per_iteration = dt / done;
       poll_iterations_ = static_cast<int>(std::min(4096.0, std::max(1.0, 0.02 / per_iteration)));
     }

@@ -327,6 +327,21 @@ __global__ void mp_begin_kernel(StepState* st) {
   st->mp_new_tau = tau * dilating;
 }
 
+// Column-sharded solve: |dx|^2 (K1) and the two K3 sums are per-rank partials.  They are folded to
+// three doubles and all-reduced (the second, tiny collective of a trial step; the first is the
+// row-sum all-reduce inside K2); the decision kernel then reads them as one-block "tables".  Every
+// rank takes the same decision from the same numbers.
+struct StepSums { const double* p1; int g1; const double* p3; int g3; };
+StepSums CombineStepPartials(Workspace& ws, int g1, int g3) {
+  if (!IsSharded(ws)) return {ws.partials[0].get(), g1, ws.partials[2].get(), g3};
+  double* t = ws.totals.get() + 3 * kMaxSlots;
+  finalize_kernel<PrimalStepOp><<<1, kBlock, 0, ws.stream>>>(ws.partials[0].get(), g1, t);
+  finalize_kernel<KtyStepOp><<<1, kBlock, 0, ws.stream>>>(ws.partials[2].get(), g3, t + 1);
+  ws.launches += 2;
+  ws.comm->AllReduce(t, 3, false, ws.stream);
+  return {t, 1, t + 1, 1};
+}
+
 }  // namespace
 
 void EnqueueAdaptiveTrials(Workspace& ws, const DeviceProblem& p, Iterate& it, int trials, bool constant_step) {
@@ -352,7 +367,8 @@ void EnqueueAdaptiveTrials(Workspace& ws, const DeviceProblem& p, Iterate& it, i
     mark();
     const int g3 = EnqueueRows(ws, k3, csc, 2);
     mark();
-    decide_adaptive_kernel<<<1, kBlock, 0, ws.stream>>>(st, ws.partials[0].get(), g1, ws.partials[1].get(), g2, ws.partials[2].get(), g3, constant_step ? 1 : 0);
+    const StepSums sums = CombineStepPartials(ws, g1, g3);
+    decide_adaptive_kernel<<<1, kBlock, 0, ws.stream>>>(st, sums.p1, sums.g1, ws.partials[1].get(), g2, sums.p3, sums.g3, constant_step ? 1 : 0);
     ++ws.launches;
     mark();
     EnqueueMap(ws, k5, p.n + p.m, 0);
@@ -380,7 +396,8 @@ void EnqueueMalitskyPockTrials(Workspace& ws, const DeviceProblem& p, Iterate& i
     EnqueueMap(ws, kx, p.n, 1);
     const int g2 = EnqueueRows(ws, k2, csr, 1);
     const int g3 = EnqueueRows(ws, k3, csc, 2);
-    decide_mp_kernel<<<1, kBlock, 0, ws.stream>>>(st, ws.partials[0].get(), g1, ws.partials[1].get(), g2, ws.partials[2].get(), g3);
+    const StepSums sums = CombineStepPartials(ws, g1, g3);
+    decide_mp_kernel<<<1, kBlock, 0, ws.stream>>>(st, sums.p1, sums.g1, ws.partials[1].get(), g2, sums.p3, sums.g3);
     ++ws.launches;
     EnqueueMap(ws, k5, p.n + p.m, 0);
   }

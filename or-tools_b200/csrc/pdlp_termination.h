@@ -26,7 +26,11 @@ struct TerminationReasonAndPointType { int reason; int type; };
 struct InterruptFlag {
   const std::atomic<bool>* atomic_flag = nullptr;
   const volatile int* int_flag = nullptr;
-  bool IsSet() const { return (atomic_flag != nullptr && atomic_flag->load()) || (int_flag != nullptr && *int_flag != 0); }
+  int agreed = -1;  // sharded solves: the value all ranks agreed on at this host event (>= 0 overrides the flags)
+  bool IsSet() const {
+    if (agreed >= 0) return agreed != 0;
+    return (atomic_flag != nullptr && atomic_flag->load()) || (int_flag != nullptr && *int_flag != 0);
+  }
 };
 struct RelativeConvergenceInformation {
   double relative_l_inf_primal_residual = 0, relative_l2_primal_residual = 0;

@@ -105,6 +105,7 @@ struct SolveCounters {
   double loop_seconds = 0.0;         // host wall time of Solver::Solve
   double device_loop_seconds = 0.0;  // CUDA-event time of the iteration loop
   double setup_seconds = 0.0;
+  long long collectives = 0;         // NCCL all-reduces enqueued (0 on one GPU)
 };
 const SolveCounters& LastSolveCounters();
 

@@ -1,0 +1,298 @@
+"""Column-sharded solve on 2 GPUs against the single-GPU path and the CPU oracle.
+
+One process per GPU (spawned here; torch.distributed over gloo carries only the NCCL unique id),
+each calling pdlp_b200_solve_sharded / the sharded kernel-level handle through the C ABI.
+Needs a box with >= 2 GPUs (`gpurun --gpus 2`); skipped on the 1-GPU box.
+"""
+import json
+import os
+import socket
+
+import numpy as np
+import pytest
+
+import backends
+import fixtures
+import oracle_binding as ob
+import pdlp_b200
+
+pytestmark = pytest.mark.gpu
+
+P = pdlp_b200.PrimalDualHybridGradientParams
+TR = pdlp_b200.TerminationReason
+
+
+def _gpu_count():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:  # noqa: BLE001
+        return 0
+
+
+needs_two = pytest.mark.skipif(_gpu_count() < 2, reason="needs 2 GPUs")
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def params(eps=1e-7, **kw):
+    p = P()
+    p.termination_criteria.simple_optimality_criteria.eps_optimal_absolute = eps
+    p.termination_criteria.simple_optimality_criteria.eps_optimal_relative = eps
+    for k, v in kw.items():
+        setattr(p, k, v)
+    return p
+
+
+def cases():
+    """name -> (qp, params).  Same seeds in every process."""
+    out = {}
+    out["lp"] = (fixtures.random_lp(400, 800, 5, 1), params())
+    out["lp_wide"] = (fixtures.random_lp(300, 3000, 4, 3), params(1e-6))
+    out["qp"] = (fixtures.random_lp(300, 600, 5, 4, qp_diagonal=True), params())
+    out["lp_mp"] = (fixtures.random_lp(200, 500, 5, 5), params(1e-6, linesearch_rule=P.MALITSKY_POCK_LINESEARCH_RULE))
+    out["lp_const"] = (fixtures.random_lp(200, 500, 5, 6), params(1e-6, linesearch_rule=P.CONSTANT_STEP_SIZE_RULE))
+    out["lp_distance"] = (fixtures.random_lp(200, 500, 5, 7), params(1e-6, restart_strategy=P.ADAPTIVE_DISTANCE_BASED))
+    pol = params(1e-6, use_feasibility_polishing=True)
+    out["lp_polish"] = (fixtures.random_lp(200, 500, 5, 8), pol)
+    out["test_lp"] = (fixtures.make_test_lp(), params(1e-8))
+    lim = params(1e-12)
+    lim.termination_criteria.iteration_limit = 300
+    lim.record_iteration_stats = True
+    out["lp_limit"] = (fixtures.random_lp(200, 500, 5, 9), lim)
+    return out
+
+
+def _log_summary(r):
+    log = r.solve_log
+    ci = [c for c in log.solution_stats.convergence_information if c.candidate_type == log.solution_type]
+    return dict(reason=int(log.termination_reason), iterations=int(log.iteration_count), solution_type=int(log.solution_type),
+                primal_objective=ci[0].primal_objective if ci else None, dual_objective=ci[0].dual_objective if ci else None,
+                l2_primal_residual=ci[0].l2_primal_residual if ci else None, l2_dual_residual=ci[0].l2_dual_residual if ci else None,
+                message=log.termination_string, num_variables=int(log.original_problem_stats.num_variables),
+                nnz=int(log.original_problem_stats.constraint_matrix_num_nonzeros),
+                trace=[(int(s.iteration_number), s.step_size, s.primal_weight, int(s.restart_used)) for s in log.iteration_stats])
+
+
+def _worker(rank, world, port, out_dir):
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    res = {}
+    arrays = {}
+    try:
+        for name, (qp, p) in cases().items():
+            r = pdlp_b200.primal_dual_hybrid_gradient_sharded(qp, p, device=rank)
+            res[name] = _log_summary(r)
+            res[name]["collectives"] = pdlp_b200.last_solve_counters()["collectives"]
+            arrays[name + "_x"] = r.primal_solution
+            arrays[name + "_y"] = r.dual_solution
+            arrays[name + "_rc"] = r.reduced_costs
+
+        # Warm start: the whole-vector initial solution is sliced per rank.
+        qp, p = cases()["lp"]
+        init = pdlp_b200.PrimalAndDualSolution(arrays["lp_x"], arrays["lp_y"])
+        res["warm"] = _log_summary(pdlp_b200.primal_dual_hybrid_gradient_sharded(qp, p, initial_solution=init, device=rank))
+
+        # An interrupt raised on rank 1 only, from its callback at iteration >= 128, stops both ranks
+        # at the same iteration.
+        flag = np.zeros(1, dtype=np.int32)
+        seen = []
+
+        def cb(info):
+            seen.append(int(info.iteration_stats.iteration_number))
+            if rank == 1 and info.iteration_stats.iteration_number >= 128:
+                flag[0] = 1
+        slow = params(1e-13)
+        r = pdlp_b200.primal_dual_hybrid_gradient_sharded(qp, slow, interrupt_solve=flag, iteration_stats_callback=cb, device=rank)
+        res["interrupt"] = _log_summary(r)
+        res["interrupt"]["callbacks"] = seen
+
+        # A time limit: every rank stops at the same iteration although their clocks differ.
+        timed = params(1e-13)
+        timed.termination_criteria.time_sec_limit = 0.05
+        res["time_limit"] = _log_summary(pdlp_b200.primal_dual_hybrid_gradient_sharded(qp, timed, device=rank))
+
+        # A bad block on one rank only: all ranks report INVALID_PROBLEM.
+        bad = fixtures.random_lp(50, 100, 4, 2)
+        bad.variable_lower_bounds = bad.variable_lower_bounds.copy()
+        bad.variable_upper_bounds = bad.variable_upper_bounds.copy()
+        bad.variable_lower_bounds[99] = 2.0
+        bad.variable_upper_bounds[99] = 1.0
+        res["bad_bounds"] = _log_summary(pdlp_b200.primal_dual_hybrid_gradient_sharded(bad, params(), device=rank))
+        huge = fixtures.random_lp(50, 100, 4, 2)
+        huge.objective_vector = huge.objective_vector.copy()
+        huge.objective_vector[99] = 1e60
+        res["huge_objective"] = _log_summary(pdlp_b200.primal_dual_hybrid_gradient_sharded(huge, params(), device=rank))
+
+        # Kernel-level handle on this rank's block.
+        qp = fixtures.random_lp(300, 700, 5, 12, qp_diagonal=True)
+        K = qp.constraint_matrix
+        starts = pdlp_b200.column_partition(K.indptr, world)
+        lo, hi = int(starts[rank]), int(starts[rank + 1])
+        shard = pdlp_b200.ColumnShard(rank, world, 700, lo, pdlp_b200.sharding.broadcast_unique_id())
+        h = pdlp_b200.DeviceProblem(pdlp_b200.take_columns(qp, lo, hi), device=rank, shard=shard)
+        rng = np.random.default_rng(3)
+        x, y = rng.normal(size=700), rng.normal(size=300)
+        arrays["h_kx"] = h.matvec(1, x[lo:hi])[0]
+        arrays["h_kty"] = h.matvec(0, y)[0]
+        arrays["h_rownorm_inf"] = h.scaled_norms(1, 0, np.ones(300), np.ones(hi - lo))
+        arrays["h_rownorm_l2"] = h.scaled_norms(1, 1, np.ones(300), np.ones(hi - lo))
+        arrays["h_colnorm_l2"] = h.scaled_norms(0, 1, np.ones(300), np.ones(hi - lo))
+        st = h.stats()
+        res["h_stats"] = {f.name: getattr(st, f.name) for f in st.DESCRIPTOR.fields}
+        k = h.kkt_stats(params(), x[lo:hi], y)
+        c, i = k.convergence_information[0], k.infeasibility_information[0]
+        res["h_kkt"] = dict(**{f.name: getattr(c, f.name) for f in c.DESCRIPTOR.fields}, **{"inf_" + f.name: getattr(i, f.name) for f in i.DESCRIPTOR.fields})
+        arrays["h_rc"] = h.reduced_costs(params(), x[lo:hi], y)
+        xb = np.clip(x, qp.variable_lower_bounds, qp.variable_upper_bounds)
+        res["h_bounds"] = h.localized_bounds(xb[lo:hi], np.zeros(300), 1.0, 0.75)
+        res["h_bounds_diag"] = h.localized_bounds(xb[lo:hi], np.zeros(300), 2.0, 0.5, use_diagonal_qp_trust_region_solver=True)
+        rs, cs, vals = h.rescale(4, True)
+        arrays["h_row_scale"], arrays["h_col_scale"], arrays["h_scaled_vals"] = rs, cs, vals
+        res["h_block"] = [lo, hi]
+        h.close()
+    finally:
+        dist.destroy_process_group()
+    with open(os.path.join(out_dir, f"rank{rank}.json"), "w") as f:
+        json.dump(res, f)
+    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), **arrays)
+
+
+@pytest.fixture(scope="module")
+def two_rank_run(tmp_path_factory):
+    import torch.multiprocessing as mp
+
+    out = tmp_path_factory.mktemp("sharded")
+    mp.spawn(_worker, args=(2, _free_port(), str(out)), nprocs=2, join=True)
+    res = [json.load(open(out / f"rank{k}.json")) for k in range(2)]
+    arr = [np.load(out / f"rank{k}.npz") for k in range(2)]
+    return res, arr
+
+
+def _strip_clock(d):
+    return {k: v for k, v in d.items() if k not in ("message",)}
+
+
+@needs_two
+def test_every_rank_reports_the_same_result(two_rank_run):
+    res, arr = two_rank_run
+    for name in res[0]:
+        if name.startswith("h_"):
+            continue
+        assert _strip_clock(res[0][name]) == _strip_clock(res[1][name]), name
+    for key in arr[0].files:
+        if key.startswith("h_") and key not in ("h_kx", "h_rownorm_inf", "h_rownorm_l2", "h_row_scale"):
+            continue  # block-local outputs
+        np.testing.assert_array_equal(arr[0][key], arr[1][key], err_msg=key)
+
+
+@needs_two
+@pytest.mark.parametrize("name", ["lp", "lp_wide", "qp", "lp_mp", "lp_const", "lp_distance", "lp_polish", "test_lp"])
+def test_sharded_solve_matches_single_gpu_and_oracle(two_rank_run, name):
+    res, arr = two_rank_run
+    qp, p = cases()[name]
+    got = res[0][name]
+    single = pdlp_b200.primal_dual_hybrid_gradient(qp, p)
+    ora = ob.solve(qp, p)
+    assert got["reason"] == single.solve_log.termination_reason == ora.solve_log_dict["termination_reason"] == TR.TERMINATION_REASON_OPTIMAL
+    assert got["num_variables"] == qp.constraint_matrix.shape[1] and got["nnz"] == qp.constraint_matrix.nnz
+    s = _log_summary(single)
+    for key in ("primal_objective", "dual_objective"):
+        assert abs(got[key] - s[key]) <= 1e-6 * max(1.0, abs(s[key])), (key, got[key], s[key])
+    # Summation order differs between world sizes exactly as between the reference's shard counts:
+    # iteration counts agree within the chaos envelope, not exactly.
+    lo, hi = sorted((s["iterations"], ora.solve_log_dict["iteration_count"]))
+    assert 0.6 * lo - 64 <= got["iterations"] <= 1.5 * hi + 64, (got["iterations"], s["iterations"], ora.solve_log_dict["iteration_count"])
+    assert got["collectives"] > got["iterations"]  # at least one all-reduce per trial step
+    # The gathered point is a KKT point of the WHOLE problem by the oracle's own measure.
+    x, y = arr[0][name + "_x"], arr[0][name + "_y"]
+    assert x.size == qp.constraint_matrix.shape[1] and y.size == qp.constraint_matrix.shape[0]
+    whole = backends.make("oracle").problem(qp)
+    c = whole.kkt_stats(p, x, y).convergence_information[0]
+    eps = p.termination_criteria.simple_optimality_criteria.eps_optimal_absolute
+    norms = whole.stats()
+    if name != "lp_polish":  # polishing returns a primal from one phase and a dual from another
+        assert c.l2_primal_residual <= 1.01 * eps * (1 + norms.combined_bounds_l2_norm)
+        assert c.l2_dual_residual <= 1.01 * eps * (1 + norms.objective_vector_l2_norm)
+        assert abs(c.primal_objective - c.dual_objective) <= 1.01 * eps * (1 + abs(c.primal_objective) + abs(c.dual_objective))
+        np.testing.assert_allclose(c.primal_objective, got["primal_objective"], rtol=1e-9, atol=1e-9)
+
+
+@needs_two
+def test_sharded_trace_follows_single_gpu_until_rounding_takes_over(two_rank_run):
+    res, _ = two_rank_run
+    qp, p = cases()["lp_limit"]
+    single = _log_summary(pdlp_b200.primal_dual_hybrid_gradient(qp, p))
+    got = res[0]["lp_limit"]
+    assert got["reason"] == single["reason"] == TR.TERMINATION_REASON_ITERATION_LIMIT
+    assert got["iterations"] == single["iterations"] == 300
+    agree = 0
+    for a, b in zip(got["trace"], single["trace"]):
+        if a[0] != b[0] or a[3] != b[3] or abs(a[1] - b[1]) > 1e-9 * abs(b[1]) or abs(a[2] - b[2]) > 1e-9 * abs(b[2]):
+            break
+        agree += 1
+    assert agree >= 64, (agree, got["trace"][agree:agree + 2], single["trace"][agree:agree + 2])
+
+
+@needs_two
+def test_warm_start_interrupt_time_limit_and_errors_are_collective(two_rank_run):
+    res, _ = two_rank_run
+    assert res[0]["warm"]["reason"] == TR.TERMINATION_REASON_OPTIMAL
+    assert res[0]["warm"]["iterations"] <= max(64, res[0]["lp"]["iterations"] // 4)
+    for k in range(2):
+        assert res[k]["interrupt"]["reason"] == TR.TERMINATION_REASON_INTERRUPTED_BY_USER
+        assert res[k]["time_limit"]["reason"] == TR.TERMINATION_REASON_TIME_LIMIT
+        assert res[k]["bad_bounds"]["reason"] == TR.TERMINATION_REASON_INVALID_PROBLEM
+        assert "inconsistent bounds" in res[k]["bad_bounds"]["message"]
+        assert res[k]["huge_objective"]["reason"] == TR.TERMINATION_REASON_INVALID_PROBLEM
+        assert "Objective vector" in res[k]["huge_objective"]["message"]
+    assert res[0]["interrupt"]["iterations"] == res[1]["interrupt"]["iterations"] >= 128
+    assert res[0]["interrupt"]["callbacks"] == res[1]["interrupt"]["callbacks"]
+    assert res[0]["time_limit"]["iterations"] == res[1]["time_limit"]["iterations"]
+
+
+@needs_two
+def test_sharded_kernels_match_the_oracle(two_rank_run):
+    res, arr = two_rank_run
+    qp = fixtures.random_lp(300, 700, 5, 12, qp_diagonal=True)
+    K = qp.constraint_matrix
+    rng = np.random.default_rng(3)
+    x, y = rng.normal(size=700), rng.normal(size=300)
+    op = backends.make("oracle").problem(qp)
+    cat = lambda key: np.concatenate([arr[0][key], arr[1][key]])  # noqa: E731
+    assert res[0]["h_block"][1] == res[1]["h_block"][0] and res[1]["h_block"][1] == 700
+    np.testing.assert_allclose(arr[0]["h_kx"], K @ x, rtol=0, atol=1e-12)
+    np.testing.assert_array_equal(cat("h_kty"), op.matvec(0, y))  # K^T y is local to a column block: bit-exact
+    np.testing.assert_array_equal(arr[0]["h_rownorm_inf"], np.abs(K).max(axis=1).toarray().ravel())  # max is exact
+    np.testing.assert_allclose(arr[0]["h_rownorm_l2"], np.sqrt(np.asarray(K.multiply(K).sum(axis=1)).ravel()), rtol=1e-14)
+    np.testing.assert_array_equal(cat("h_colnorm_l2"), op.col_norms(True, np.ones(300), np.ones(700)))
+    ref = op.stats()
+    for key, v in res[0]["h_stats"].items():
+        want = getattr(ref, key)
+        if isinstance(want, float) and np.isnan(want):
+            assert np.isnan(v), key
+        else:
+            np.testing.assert_allclose(v, want, rtol=1e-13, err_msg=key)
+    k = op.kkt_stats(params(), x, y)
+    c, i = k.convergence_information[0], k.infeasibility_information[0]
+    for key, v in res[0]["h_kkt"].items():
+        want = getattr(i, key[4:]) if key.startswith("inf_") else getattr(c, key)
+        np.testing.assert_allclose(v, want, rtol=1e-11, atol=1e-11, err_msg=key)
+    np.testing.assert_allclose(cat("h_rc"), op.reduced_costs(params(), x, y), rtol=1e-13, atol=1e-13)
+    xb = np.clip(x, qp.variable_lower_bounds, qp.variable_upper_bounds)
+    for key, args in (("h_bounds", (1.0, 0.75, False)), ("h_bounds_diag", (2.0, 0.5, True))):
+        want = op.localized_bounds(xb, np.zeros(300), args[0], args[1], args[2], 1e-8)
+        for f in ("lagrangian_value", "lower_bound", "upper_bound", "radius"):
+            np.testing.assert_allclose(res[0][key][f], want[f], rtol=1e-7 if args[2] else 1e-10, atol=1e-9, err_msg=f"{key}.{f}")
+            assert res[0][key][f] == res[1][key][f]
+    rs, cs, vals = backends.make("oracle").problem(qp).rescale(4, True)
+    np.testing.assert_allclose(arr[0]["h_row_scale"], rs, rtol=1e-12)
+    np.testing.assert_allclose(cat("h_col_scale"), cs, rtol=1e-12)
+    np.testing.assert_allclose(cat("h_scaled_vals"), vals, rtol=1e-12)
