@@ -20,7 +20,7 @@ import numpy as np
 from . import _schema
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIBRARY_PATH = os.path.join(_HERE, "lib", "libpdlp_b200.so")
+LIBRARY_PATH = os.environ.get("PDLP_B200_LIBRARY") or os.path.join(_HERE, "lib", "libpdlp_b200.so")  # override: kernel-variant experiments
 
 if not os.path.exists(LIBRARY_PATH):
     raise ImportError(

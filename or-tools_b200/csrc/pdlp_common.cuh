@@ -21,6 +21,7 @@
 #include <cstdio>
 #include <stdexcept>
 #include <string>
+#include <type_traits>
 #include <utility>
 
 namespace pdlp_b200 {
@@ -150,9 +151,22 @@ __global__ void __launch_bounds__(kBlock) map_reduce_kernel(const Op op_in, int6
 // The matrix is cut at setup into "work blocks" of consecutive rows holding at most
 // kStreamChunk nonzeros (a row longer than that is a work block of its own).  A CTA
 // streams its block's nonzeros with fully coalesced loads into shared memory as
-// products Load(k), then sub-warps of T threads reduce each row out of shared memory
-// (T = 1 for short rows: a sequential, reference-ordered sum).  Long rows are reduced
+// products LoadAt(k, Index(k)), then sub-warps of T threads reduce each row out of shared
+// memory (T = 1 for short rows: a sequential, reference-ordered sum).  Long rows are reduced
 // straight from global memory by the whole CTA.
+//
+// The pass is latency-bound, not bandwidth-bound (profiles/r01_ncu_rowstream_c3_v0.md: DRAM at
+// 51-57 % with full occupancy, stalls on the block_start -> row_ptr -> idx -> gather -> barrier
+// -> row_ptr -> epilogue-operand chain of six dependent memory latencies per work block).  The
+// kernel therefore software-pipelines everything that does not depend on the gather:
+//   * work-block metadata (first row, first nonzero) two blocks ahead, from two flat arrays;
+//   * the column indices of the NEXT block into shared memory (cp.async) while the current block
+//     reduces, and the block's row offsets likewise;
+//   * the epilogue operands of each thread's row(s) (Op::RowPrefetch) into registers, issued
+//     BEFORE the gather so that the in-order warp does not stall in front of them;
+// leaving idx (prefetched) -> gather -> barrier -> reduce from shared memory on the critical path.
+// Shared-memory products are stored with a 1-in-16 skew so that sub-warps reading rows of 16, 32,
+// 64 ... nonzeros do not collide on the same banks.
 //
 // Op interface (in addition to kNumSlots / SlotKindOf / Begin):
 //   __device__ double Load(int64_t k) const;              // value staged for nonzero k
@@ -160,28 +174,119 @@ __global__ void __launch_bounds__(kBlock) map_reduce_kernel(const Op op_in, int6
 //   __device__ double RowAdd(double acc, double staged, int row) const;
 //   __device__ double RowMerge(double a, double b) const;
 //   __device__ void RowFinish(int row, double acc, Slots<kNumSlots>& red) const;
+// Optional (the hot ops have them):
+//   __device__ const int* IndexAddress(int64_t k) const;  __device__ const double* ValueAddress(int64_t k) const;
+//   __device__ double Gather(int index) const;  __device__ double Product(double value, double gathered) const;
+//       split of Load (= Product(*ValueAddress(k), Gather(*IndexAddress(k)))) so that indices travel one
+//       block ahead and values by asynchronous copy
+//   struct Pre;  __device__ Pre RowPrefetch(int row) const;
+//   __device__ void RowFinish(int row, double acc, const Pre& pre, Slots<kNumSlots>& red) const;
+//       epilogue operands fetched before the reduction instead of after it
 struct RowBlocks {
   const int* row_ptr;      // rows + 1
   const int* block_start;  // num_blocks + 1 (row index where each work block starts)
+  const int* block_nz;     // num_blocks + 1 (row_ptr[block_start[b]]: first nonzero of each work block)
   int num_blocks;
   int rows;
 };
 
+constexpr int kMaxRowsPerBlock = 4 * kBlock;
+#ifndef PDLP_ROWSTREAM_MIN_CTAS
+#define PDLP_ROWSTREAM_MIN_CTAS 4  // resident CTAs per SM the register allocation must allow
+#endif
+constexpr int kPerThread = kStreamChunk / kBlock;             // nonzeros per thread per work block
+constexpr int kStagedSize = kStreamChunk + kStreamChunk / 16;  // with the bank skew
+__device__ __forceinline__ int Skew(int k) { return k + (k >> 4); }
+
+template <class Op, class = void>
+struct HasSplitLoad : std::false_type {};
 template <class Op>
-__global__ void __launch_bounds__(kBlock) rowstream_kernel(const Op op_in, RowBlocks rb, double* partials) {
-  __shared__ double staged[kStreamChunk];
+struct HasSplitLoad<Op, std::void_t<decltype(std::declval<const Op&>().IndexAddress(int64_t{0}))>> : std::true_type {};
+template <class Op, class = void>
+struct HasRowPrefetch : std::false_type {};
+template <class Op>
+struct HasRowPrefetch<Op, std::void_t<typename Op::Pre>> : std::true_type {};
+
+struct NoPre {};
+template <class Op, bool = HasRowPrefetch<Op>::value>
+struct PreOf { using type = NoPre; };
+template <class Op>
+struct PreOf<Op, true> { using type = typename Op::Pre; };
+
+template <class Op>
+__device__ __forceinline__ typename PreOf<Op>::type OpRowPrefetch(const Op& op, int row) {
+  if constexpr (HasRowPrefetch<Op>::value) return op.RowPrefetch(row);
+  else return NoPre{};
+}
+template <class Op>
+__device__ __forceinline__ void OpRowFinish(const Op& op, int row, double acc, const typename PreOf<Op>::type& pre, Slots<Op::kNumSlots>& red) {
+  if constexpr (HasRowPrefetch<Op>::value) op.RowFinish(row, acc, pre, red);
+  else op.RowFinish(row, acc, red);
+}
+
+// Ampere-style asynchronous 4-byte copies global -> shared: the row offsets of the current work
+// block and the column indices of the next one travel without occupying registers or stalling
+// the issuing warp.
+__device__ __forceinline__ void CpAsync4(void* smem_dst, const void* global_src) {
+  const unsigned dst = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(global_src));
+}
+__device__ __forceinline__ void CpAsync8(void* smem_dst, const void* global_src) {
+  const unsigned dst = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(dst), "l"(global_src));
+}
+__device__ __forceinline__ void CpAsyncCommit() { asm volatile("cp.async.commit_group;\n" ::); }
+__device__ __forceinline__ void CpAsyncWaitAll() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
+
+template <class Op>
+__device__ __forceinline__ void PrefetchIndices(const Op& op, int* idx_buf, int first_nz, int nz) {
+  if constexpr (HasSplitLoad<Op>::value) {
+    if (nz <= kStreamChunk) {
+#pragma unroll
+      for (int i = 0; i < kPerThread; ++i) {
+        const int k = threadIdx.x + i * kBlock;
+        if (k < nz) CpAsync4(idx_buf + k, op.IndexAddress(first_nz + k));
+      }
+    }
+  }
+  CpAsyncCommit();
+}
+
+template <class Op>
+__global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_kernel(const Op op_in, RowBlocks rb, double* partials) {
+  __shared__ double staged[kStagedSize];
+  __shared__ int row_raw[kMaxRowsPerBlock + 1];  // row_ptr[r0 ...] of the current work block
+  __shared__ int idx_buf[2][HasSplitLoad<Op>::value ? kStreamChunk : 1];
   __shared__ double long_row_buf[kBlock / 32];
+  using Pre = typename PreOf<Op>::type;
+  constexpr int kPreRows = sizeof(Pre) > 16 ? 2 : 4;  // rows per thread whose epilogue operands are fetched before the barrier
   Slots<Op::kNumSlots> red;
 #pragma unroll
   for (int s = 0; s < Op::kNumSlots; ++s) red.v[s] = SlotIdentity(Op::SlotKindOf(s));
   Op op = op_in;
   if (op.Begin()) {
-    for (int b = blockIdx.x; b < rb.num_blocks; b += gridDim.x) {
-      const int r0 = rb.block_start[b], r1 = rb.block_start[b + 1];
-      const int p0 = rb.row_ptr[r0], p1 = rb.row_ptr[r1];
+    const int stride = gridDim.x;
+    int b = blockIdx.x;
+    // Metadata of the current work block and of the next one (b + stride).
+    int r0 = 0, r1 = 0, p0 = 0, p1 = 0, nr0 = 0, nr1 = 0, np0 = 0, np1 = 0;
+    if (b < rb.num_blocks) { r0 = rb.block_start[b]; r1 = rb.block_start[b + 1]; p0 = rb.block_nz[b]; p1 = rb.block_nz[b + 1]; }
+    if (b + stride < rb.num_blocks) {
+      nr0 = rb.block_start[b + stride]; nr1 = rb.block_start[b + stride + 1];
+      np0 = rb.block_nz[b + stride]; np1 = rb.block_nz[b + stride + 1];
+    }
+    int parity = 0;
+    PrefetchIndices(op, idx_buf[0], p0, p1 - p0);
+    while (b < rb.num_blocks) {
       const int nz = p1 - p0;
+      // Metadata two blocks ahead: in flight for a whole block before it is needed.
+      const int b2 = b + 2 * stride;
+      int fr0 = 0, fr1 = 0, fp0 = 0, fp1 = 0;
+      if (b2 < rb.num_blocks) { fr0 = rb.block_start[b2]; fr1 = rb.block_start[b2 + 1]; fp0 = rb.block_nz[b2]; fp1 = rb.block_nz[b2 + 1]; }
+      const int next_nz = np1 - np0;  // 0 when there is no next block
       if (nz > kStreamChunk) {
         // One long row (r1 == r0 + 1 by construction): CTA-wide strided reduce.
+        PrefetchIndices(op, idx_buf[parity ^ 1], np0, next_nz);
+        const Pre pre = OpRowPrefetch(op, r0);
         double a = op.RowInit();
         for (int k = p0 + threadIdx.x; k < p1; k += kBlock) a = op.RowAdd(a, op.Load(k), r0);
 #pragma unroll
@@ -191,34 +296,103 @@ __global__ void __launch_bounds__(kBlock) rowstream_kernel(const Op op_in, RowBl
         if (threadIdx.x == 0) {
           double t = long_row_buf[0];
           for (int w = 1; w < kBlock / 32; ++w) t = op.RowMerge(t, long_row_buf[w]);
-          op.RowFinish(r0, t, red);
+          OpRowFinish(op, r0, t, pre, red);
+        }
+        CpAsyncWaitAll();
+        __syncthreads();
+      } else {
+        // This block's column indices were copied to shared memory a block ago (own positions).
+        CpAsyncWaitAll();
+        int jx[kPerThread];
+        if constexpr (HasSplitLoad<Op>::value) {
+#pragma unroll
+          for (int i = 0; i < kPerThread; ++i) {
+            const int k = threadIdx.x + i * kBlock;
+            jx[i] = k < nz ? idx_buf[parity][k] : 0;
+          }
+        }
+        // Issue order matters (warps issue in order, and ptxas places the cp.async wait directly
+        // behind the last copy): epilogue operands and gathers first - their addresses are known -
+        // then the asynchronous copies of this block's values and row offsets and of the next
+        // block's indices.  All of them are in flight together; the wait then covers one latency.
+        const int nrows = r1 - r0;
+        // Threads per row: largest power of two <= min(32, kBlock / nrows), at least 1.
+        int log_t = 0;
+        while (log_t < 5 && (2 << log_t) * nrows <= kBlock) ++log_t;
+        const int t = 1 << log_t;
+        const int sub = threadIdx.x >> log_t, lane = threadIdx.x & (t - 1);
+        const int groups = kBlock >> log_t;
+        Pre pre[kPreRows];
+#pragma unroll
+        for (int u = 0; u < kPreRows; ++u) {
+          const int rr = sub + u * groups;
+          if (lane == 0 && rr < nrows) pre[u] = OpRowPrefetch(op, r0 + rr);
+        }
+        if constexpr (HasSplitLoad<Op>::value) {
+          double g[kPerThread];
+#pragma unroll
+          for (int i = 0; i < kPerThread; ++i) {
+            const int k = threadIdx.x + i * kBlock;
+            g[i] = k < nz ? op.Gather(jx[i]) : 0.0;
+          }
+#pragma unroll
+          for (int i = 0; i < kPerThread; ++i) {
+            const int k = threadIdx.x + i * kBlock;
+            if (k < nz) CpAsync8(staged + Skew(k), op.ValueAddress(p0 + k));
+          }
+          for (int i = threadIdx.x; i <= nrows; i += kBlock) CpAsync4(row_raw + i, rb.row_ptr + r0 + i);
+          PrefetchIndices(op, idx_buf[parity ^ 1], np0, next_nz);
+          CpAsyncWaitAll();
+          // Each thread multiplies its own positions in place.
+#pragma unroll
+          for (int i = 0; i < kPerThread; ++i) {
+            const int k = threadIdx.x + i * kBlock;
+            if (k < nz) staged[Skew(k)] = op.Product(staged[Skew(k)], g[i]);
+          }
+        } else {
+          for (int i = threadIdx.x; i <= nrows; i += kBlock) CpAsync4(row_raw + i, rb.row_ptr + r0 + i);
+          CpAsyncCommit();
+#pragma unroll
+          for (int i = 0; i < kPerThread; ++i) {
+            const int k = threadIdx.x + i * kBlock;
+            if (k < nz) staged[Skew(k)] = op.Load(p0 + k);
+          }
+          CpAsyncWaitAll();
         }
         __syncthreads();
-        continue;
-      }
-      // Stage: coalesced, 8 independent loads in flight per thread.
-#pragma unroll 8
-      for (int k = threadIdx.x; k < nz; k += kBlock) staged[k] = op.Load(p0 + k);
-      __syncthreads();
-      const int nrows = r1 - r0;
-      // Threads per row: largest power of two <= min(32, kBlock / nrows), at least 1.
-      int t = 1;
-      while (t < 32 && t * 2 * nrows <= kBlock) t *= 2;
-      const int sub = threadIdx.x / t, lane = threadIdx.x % t;
-      const int groups = kBlock / t;
-      for (int base = 0; base < nrows; base += groups) {
-        const int r = r0 + base + sub;
-        double a = op.RowInit();
-        if (base + sub < nrows) {
-          const int q0 = rb.row_ptr[r] - p0, q1 = rb.row_ptr[r + 1] - p0;
-          for (int q = q0 + lane; q < q1; q += t) a = op.RowAdd(a, staged[q], r);
+#pragma unroll
+        for (int u = 0; u < kPreRows; ++u) {
+          const int rr = sub + u * groups;
+          if (u * groups < nrows) {  // uniform across the CTA
+            double a = op.RowInit();
+            if (rr < nrows) {
+              const int q1 = row_raw[rr + 1] - p0;
+              for (int q = row_raw[rr] - p0 + lane; q < q1; q += t) a = op.RowAdd(a, staged[Skew(q)], r0 + rr);
+            }
+            // All 32 lanes take part in the shuffles (t divides 32).
+            for (int off = t >> 1; off > 0; off >>= 1) a = op.RowMerge(a, __shfl_xor_sync(0xffffffffu, a, off));
+            if (lane == 0 && rr < nrows) OpRowFinish(op, r0 + rr, a, pre[u], red);
+          }
         }
-        // All 32 lanes take part in the shuffles (t divides 32).
-        for (int off = t >> 1; off > 0; off >>= 1) a = op.RowMerge(a, __shfl_xor_sync(0xffffffffu, a, off));
-        if (lane == 0 && base + sub < nrows) op.RowFinish(r, a, red);
+        // Rows beyond the prefetched ones (only when a block has more than kPreRows * groups rows).
+        for (int base = kPreRows * groups; base < nrows; base += groups) {
+          const int rr = base + sub;
+          double a = op.RowInit();
+          if (rr < nrows) {
+            const int q1 = row_raw[rr + 1] - p0;
+            for (int q = row_raw[rr] - p0 + lane; q < q1; q += t) a = op.RowAdd(a, staged[Skew(q)], r0 + rr);
+          }
+          for (int off = t >> 1; off > 0; off >>= 1) a = op.RowMerge(a, __shfl_xor_sync(0xffffffffu, a, off));
+          if (lane == 0 && rr < nrows) OpRowFinish(op, r0 + rr, a, OpRowPrefetch(op, r0 + rr), red);
+        }
+        __syncthreads();
       }
-      __syncthreads();
+      parity ^= 1;
+      b += stride;
+      r0 = nr0; r1 = nr1; p0 = np0; p1 = np1;
+      nr0 = fr0; nr1 = fr1; np0 = fp0; np1 = fp1;
     }
+    CpAsyncWaitAll();
   }
   BlockReduceAndStore<Op>(red, partials);
 }

@@ -45,6 +45,14 @@ struct PartialRowOp {
   double* out;
   __device__ bool Begin() { return op.Begin(); }
   __device__ double Load(int64_t k) const { return op.Load(k); }
+  template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
+  __device__ const int* IndexAddress(int64_t k) const { return op.IndexAddress(k); }
+  template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
+  __device__ const double* ValueAddress(int64_t k) const { return op.ValueAddress(k); }
+  template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
+  __device__ double Gather(int index) const { return op.Gather(index); }
+  template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
+  __device__ double Product(double value, double gathered) const { return op.Product(value, gathered); }
   __device__ double RowInit() const { return op.RowInit(); }
   __device__ double RowAdd(double acc, double staged, int row) const { return op.RowAdd(acc, staged, row); }
   __device__ double RowMerge(double a, double b) const { return op.RowMerge(a, b); }
@@ -58,10 +66,27 @@ struct FinishRowOp {
   Op op;
   const double* sums;
   __device__ bool Begin() { return op.Begin(); }
-  __device__ void Apply(int64_t i, Slots<Op::kNumSlots>& acc) const { op.RowFinish(static_cast<int>(i), sums[i], acc); }
+  __device__ void Apply(int64_t i, Slots<Op::kNumSlots>& acc) const {
+    const int row = static_cast<int>(i);
+    OpRowFinish(op, row, sums[i], OpRowPrefetch(op, row), acc);
+  }
 };
 
 inline bool IsSharded(const Workspace& ws) { return ws.comm != nullptr && ws.comm->sharded(); }
+
+// Persistent grid of a row-stream launch: one wave of resident CTAs (SMs x occupancy of this
+// instantiation, asked from the runtime once), never more CTAs than work blocks.
+template <class Op>
+inline int RowStreamGrid(const SparseRows& s) {
+  static const int resident = [] {
+    int device = 0, sms = 148, per_sm = PDLP_ROWSTREAM_MIN_CTAS;
+    if (cudaGetDevice(&device) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rowstream_kernel<Op>, kBlock, 0) != cudaSuccess || per_sm < 1) per_sm = PDLP_ROWSTREAM_MIN_CTAS;
+    const int g = sms * per_sm;
+    return g > kMaxGrid ? kMaxGrid : g;
+  }();
+  return s.num_blocks < 1 ? 1 : (s.num_blocks > resident ? resident : s.num_blocks);
+}
 
 // Enqueue only (no finalize, no sync): partial sums land in ws.partials[region].
 template <class Op>
@@ -75,14 +100,14 @@ template <class Op>
 inline int EnqueueRows(Workspace& ws, const Op& op, const SparseRows& s, int region = 0) {
   if (s.partial_sums && IsSharded(ws)) {
     double* sums = ws.partial_rows.get();
-    rowstream_kernel<PartialRowOp<Op>><<<s.Grid(), kBlock, 0, ws.stream>>>(PartialRowOp<Op>{op, sums}, s.View(), ws.partials[region].get());
+    rowstream_kernel<PartialRowOp<Op>><<<RowStreamGrid<PartialRowOp<Op>>(s), kBlock, 0, ws.stream>>>(PartialRowOp<Op>{op, sums}, s.View(), ws.partials[region].get());
     ws.comm->AllReduce(sums, static_cast<size_t>(s.rows), RowCombineIsMax(op), ws.stream);
     const int grid = GridFor(s.rows);
     map_reduce_kernel<FinishRowOp<Op>><<<grid, kBlock, 0, ws.stream>>>(FinishRowOp<Op>{op, sums}, s.rows, ws.partials[region].get());
     ws.launches += 2;
     return grid;
   }
-  const int grid = s.Grid();
+  const int grid = RowStreamGrid<Op>(s);
   rowstream_kernel<Op><<<grid, kBlock, 0, ws.stream>>>(op, s.View(), ws.partials[region].get());
   ++ws.launches;
   return grid;

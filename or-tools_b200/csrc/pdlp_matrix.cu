@@ -63,13 +63,16 @@ void SetBlocks(SparseRows* s, const std::vector<int>& host_ptr, cudaStream_t str
   s->num_blocks = static_cast<int>(blocks.size()) - 1;
   s->block_start.Resize(blocks.size());
   s->block_start.Upload(blocks.data(), blocks.size(), stream);
+  std::vector<int> first_nz(blocks.size());
+  for (size_t b = 0; b < blocks.size(); ++b) first_nz[b] = host_ptr[blocks[b]];
+  s->block_nz.Resize(blocks.size());
+  s->block_nz.Upload(first_nz.data(), first_nz.size(), stream);
   PDLP_CUDA_CHECK(cudaStreamSynchronize(stream));
 }
 
 }  // namespace
 
 std::vector<int> PartitionRows(const int* ptr, int rows, int* max_row_nnz) {
-  constexpr int kMaxRowsPerBlock = 4 * kBlock;
   std::vector<int> starts;
   starts.push_back(0);
   int mx = 0;

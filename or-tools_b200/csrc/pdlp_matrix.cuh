@@ -20,13 +20,13 @@ struct SparseRows {
   DeviceArray<int> idx;  // nnz
   DVec val;              // nnz
   DeviceArray<int> block_start;  // num_blocks + 1
+  DeviceArray<int> block_nz;     // num_blocks + 1: ptr[block_start[b]]
   int num_blocks = 0;
   int max_row_nnz = 0;
   // Column-sharded solve: the CSC block's compressed "rows" are this rank's columns (their
   // reductions are per-rank partials); the CSR block holds only this rank's part of every row sum.
   bool sharded_rows = false, partial_sums = false;
-  RowBlocks View() const { return RowBlocks{ptr.get(), block_start.get(), num_blocks, rows}; }
-  int Grid() const { return num_blocks < 1 ? 1 : (num_blocks > kMaxGrid ? kMaxGrid : num_blocks); }
+  RowBlocks View() const { return RowBlocks{ptr.get(), block_start.get(), block_nz.get(), num_blocks, rows}; }
 };
 
 struct DeviceMatrix {

@@ -93,14 +93,20 @@ struct DualStepOp : OneSum {
     yn = cur ? y0 : y1;
     return true;
   }
+  __device__ const int* IndexAddress(int64_t k) const { return idx + k; }
+  __device__ const double* ValueAddress(int64_t k) const { return val + k; }
+  __device__ double Gather(int j) const { return xbar[j]; }
+  __device__ double Product(double v, double g) const { return v * g; }
   __device__ double Load(int64_t k) const { return val[k] * xbar[idx[k]]; }
   __device__ double RowInit() const { return 0.0; }
   __device__ double RowAdd(double acc, double staged, int) const { return acc + staged; }
   __device__ double RowMerge(double a, double b) const { return a + b; }
-  __device__ void RowFinish(int i, double kx, Slots<1>& red) const {
-    const double yi = y[i];
+  struct Pre { double y, lb, ub; };
+  __device__ Pre RowPrefetch(int i) const { return Pre{y[i], clb[i], cub[i]}; }
+  __device__ void RowFinish(int i, double kx, const Pre& pre, Slots<1>& red) const {
+    const double yi = pre.y;
     const double temp = yi - sigma * kx;
-    const double v = fmax(fmin(0.0, temp + sigma * cub[i]), temp + sigma * clb[i]);
+    const double v = fmax(fmin(0.0, temp + sigma * pre.ub), temp + sigma * pre.lb);
     yn[i] = v;
     const double d = v - yi;
     red.v[0] += d * d;
@@ -128,14 +134,20 @@ struct KtyStepOp {
     ktyn = cur ? kty0 : kty1;
     return true;
   }
+  __device__ const int* IndexAddress(int64_t k) const { return idx + k; }
+  __device__ const double* ValueAddress(int64_t k) const { return val + k; }
+  __device__ double Gather(int i) const { return yn[i]; }
+  __device__ double Product(double v, double g) const { return v * g; }
   __device__ double Load(int64_t k) const { return val[k] * yn[idx[k]]; }
   __device__ double RowInit() const { return 0.0; }
   __device__ double RowAdd(double acc, double staged, int) const { return acc + staged; }
   __device__ double RowMerge(double a, double b) const { return a + b; }
-  __device__ void RowFinish(int j, double v, Slots<2>& red) const {
+  struct Pre { double kty, dx; };
+  __device__ Pre RowPrefetch(int j) const { return Pre{kty[j], xn[j] - x[j]}; }
+  __device__ void RowFinish(int j, double v, const Pre& pre, Slots<2>& red) const {
     ktyn[j] = v;
-    const double dk = v - kty[j];
-    red.v[0] += (xn[j] - x[j]) * dk;
+    const double dk = v - pre.kty;
+    red.v[0] += pre.dx * dk;
     red.v[1] += dk * dk;
   }
 };
