@@ -36,7 +36,8 @@ import numpy as np  # noqa: E402
 WORKLOADS = {
     # name: (description, generator kwargs at scale 1.0)
     "c2": "synthetic random sparse LP 1M rows x 2M cols, 1e7 nnz, box bounds, eps=1e-4",
-    "c3": "synthetic multi-commodity network-flow LP, 64 commodities x 65536 nodes x 520000 arcs, ~1e8 nnz, eps=1e-4",
+    "c3": "synthetic multi-commodity network-flow LP, 64 commodities x 65536 nodes x 520000 arcs, ~1e8 nnz, block-angular (commodity-major) order, eps=1e-4",
+    "c3a": "the c3 LP in arc-major variable order (a contiguous column block is a set of arcs), eps=1e-4",
     "c4": "synthetic diagonal-objective convex QP 5M rows x 10M cols, 5e7 nnz, eps=1e-6",
     "c5": "synthetic transportation LP (dense bipartite), per-GPU block of 1.25e8 nnz, eps=1e-4",
 }
@@ -46,9 +47,9 @@ def make_problem(name, scale, seed=0):
     from pdlp_b200 import synthetic
     if name == "c2":
         return synthetic.random_sparse_lp(int(1_000_000 * scale), int(2_000_000 * scale), 5, seed)
-    if name == "c3":
+    if name in ("c3", "c3a"):
         side = max(8, int(round(256 * scale ** 0.5)))
-        return synthetic.multicommodity_flow_lp(64, side, int(520000 * scale), 16, seed)
+        return synthetic.multicommodity_flow_lp(64, side, int(520000 * scale), 16, seed, order="commodity" if name == "c3" else "arc")
     if name == "c4":
         return synthetic.random_sparse_lp(int(5_000_000 * scale), int(10_000_000 * scale), 5, seed, qp_diagonal=True)
     if name == "c5":
@@ -62,19 +63,23 @@ def c5_side(scale):
 
 
 def make_block(name, scale, rank, world, seed=0):
-    """This rank's column block of the workload: (block qp, starts).  c5 is generated block by
-    block (whole sources, so the 1e9-nnz problem never exists on one host); the others are
-    generated whole on every rank (same seed) and cut by the mass rule."""
+    """This rank's column block of the workload in the sharded solver's local constraint order:
+    (block qp, column starts, number of shared constraints, global constraint count).  c5 is
+    generated block by block (whole sources, so the 1e9-nnz problem never exists on one host); the
+    others are generated whole on every rank (same seed) and cut by the mass rule."""
     import pdlp_b200
     from pdlp_b200 import synthetic
     if name == "c5":
         s = c5_side(scale)
         cuts = [(s * r) // world for r in range(world + 1)]
-        block = synthetic.transportation_lp(s, s, seed, cuts[rank], cuts[rank + 1])
-        return block, np.array([c * s for c in cuts], dtype=np.int64)
+        block = synthetic.transportation_lp(s, s, seed, cuts[rank], cuts[rank + 1], local_rows=True)
+        return block, np.array([c * s for c in cuts], dtype=np.int64), s, 2 * s
     qp = make_problem(name, scale, seed)
-    starts = pdlp_b200.column_partition(qp.constraint_matrix.indptr, world)
-    return pdlp_b200.take_columns(qp, int(starts[rank]), int(starts[rank + 1])), starts
+    K = qp.constraint_matrix
+    starts = pdlp_b200.column_partition(K.indptr, world)
+    sharing = pdlp_b200.RowSharing.from_matrix(K, starts)
+    block = pdlp_b200.take_columns(qp, int(starts[rank]), int(starts[rank + 1]), sharing.local_rows(rank))
+    return block, starts, int(sharing.shared.size), K.shape[0]
 
 
 def solve_params(name, threads=1, iteration_limit=None):
@@ -91,8 +96,9 @@ def solve_params(name, threads=1, iteration_limit=None):
 
 def bytes_per_step(n, m, nnz, is_qp, sharded=False):
     """B_step = 24 nnz + 4 (n + m) + 8 (15 n + 8 m)  [+ 8 n for a QP].
-    Sharded: the same for one rank's block (n, nnz of the block; all m rows) plus the partial row
-    sums written before and read after the all-reduce (16 m); NCCL's own traffic is not counted."""
+    Sharded: the same for one rank's block (n, nnz and m of the block: its shared + private
+    constraints) plus the partial row sums written before and read after the all-reduce (16 m);
+    NCCL's own traffic is not counted."""
     return 24 * nnz + 4 * (n + m) + 8 * (15 * n + 8 * m) + (8 * n if is_qp else 0) + (16 * m if sharded else 0)
 
 
@@ -191,7 +197,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     name = args.workload
     threads = os.cpu_count() or 1
-    cpu_its = args.cpu_iterations or {"c2": 48, "c3": 8, "c4": 12, "c5": 8}[name]
+    cpu_its = args.cpu_iterations or {"c2": 48, "c3": 8, "c3a": 8, "c4": 12, "c5": 8}[name]
     config = {"workload": name + ": " + WORKLOADS[name], "scale": args.scale, "seed": 0,
               "l2_policy": "inputs larger than L2 (matrix + vectors >> 126 MB); no flush between steps"}
 
@@ -226,9 +232,10 @@ def main():
         dist.init_process_group("cpu:gloo,cuda:nccl", device_id=torch.device("cuda", local_rank))
     sharded = world > 1 and not args.replicas
     shard = starts = None
+    num_shared = m_global = None
     if sharded:
-        qp, starts = make_block(name, args.scale, rank, world)
-        shard = pdlp_b200.ColumnShard(rank, world, int(starts[-1]), int(starts[rank]), pdlp_b200.sharding.broadcast_unique_id())
+        qp, starts, num_shared, m_global = make_block(name, args.scale, rank, world)
+        shard = pdlp_b200.ColumnShard(rank, world, int(starts[-1]), int(starts[rank]), pdlp_b200.sharding.broadcast_unique_id(), num_shared)
     else:
         qp = make_problem(name, args.scale, seed=0)
     K = qp.constraint_matrix
@@ -293,7 +300,7 @@ def main():
         barrier()
         t0 = time.time()
         if sharded:
-            result = pdlp_b200.primal_dual_hybrid_gradient_sharded(qp, p, device=local_rank, starts=starts, gather=False)
+            result = pdlp_b200.primal_dual_hybrid_gradient_sharded(qp, p, device=local_rank, starts=starts, gather=False, num_shared_constraints=num_shared)
         else:
             result = pdlp_b200.primal_dual_hybrid_gradient(qp, p, device=local_rank)
         torch.cuda.synchronize()
@@ -329,10 +336,11 @@ def main():
             "metric": "pdhg_iterations_per_sec", "value": steps_per_sec, "unit": "iterations/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * seconds_max / args.steps, "higher_is_better": True, "scaling": "strong" if sharded else "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": dict(config, n=int(n_global), m=m, nnz=int(nnz_global),
+            "config": dict(config, n=int(n_global), m=int(m_global if sharded else m), nnz=int(nnz_global),
                            parallelism="1 GPU" if world == 1 else (f"column-sharded over {world} GPUs, NCCL all-reduce of K x" if sharded else f"{world} independent replicas")),
             "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": int(launches),
-            "nvlink": {"allreduce_bytes_per_step_per_rank": 8 * m + 8 * 3, "collectives_per_step": 2} if sharded else None,
+            "nvlink": {"allreduce_bytes_per_step_per_rank": 8 * num_shared + 8 * 4, "collectives_per_step": 2, "shared_constraints": num_shared,
+                       "constraints_on_rank0": m} if sharded else None,
             "roofline": {"bound": "hbm", "achieved": step_gbs, "peak": peak * (world if sharded else 1), "unit": "GB/s",
                          "frac": step_gbs / (peak * (world if sharded else 1)), "traffic": None,
                          "peak_kind": peak_kind + (f" x {world} GPUs" if sharded else ""), "unit_of_work": "one PDHG trial step (5 kernels)",

@@ -102,21 +102,33 @@ pdlp_b200_status pdlp_b200_solve(const pdlp_b200_problem* problem, const uint8_t
  * trial step (an NCCL all-reduce of the partial K x, m doubles) plus scalar all-reduces.
  * nccl_unique_id: PDLP_B200_UNIQUE_ID_BYTES bytes from pdlp_b200_unique_id() on ONE rank,
  * distributed to the others by the caller (any channel: MPI, torch.distributed, a file).
- * world == 1 or shard == NULL: a plain single-GPU solve. */
+ * world == 1 or shard == NULL: a plain single-GPU solve.
+ *
+ * Private constraints.  A constraint whose row of K has nonzeros in ONE rank's columns only needs
+ * no exchange at all.  The caller may therefore give each rank just the constraints its columns
+ * touch, renumbered locally: first the num_shared_constraints constraints that several ranks touch
+ * (the same ones, in the same order, on every rank), then the rank's private ones;
+ * block.num_constraints = shared + private, row indices of `block` are these local numbers, and the
+ * constraint bounds / dual vectors of the call have that length and order.  Only the shared rows'
+ * sums are all-reduced (8 * num_shared_constraints bytes per trial step).  A constraint no rank
+ * touches may be given to any one rank as a private one.  num_shared_constraints < 0: every rank
+ * holds all constraints (all of them shared). */
 #define PDLP_B200_UNIQUE_ID_BYTES 128
 typedef struct {
   int rank, world;
   int64_t global_num_variables;
   int64_t column_offset;
   const uint8_t* nccl_unique_id;
+  int64_t num_shared_constraints;
 } pdlp_b200_shard;
 
 pdlp_b200_status pdlp_b200_unique_id(uint8_t* out /*PDLP_B200_UNIQUE_ID_BYTES*/);
 
 /* Same contract as pdlp_b200_solve; every rank must call it with the same params and the same
  * presence of initial solution / interrupt / callback.  initial_primal_solution, primal_solution
- * and reduced_costs are this rank's block (block.num_variables entries); the dual vectors are
- * whole (m) and identical on all ranks, as is the SolveLog (up to wall-clock fields).  The
+ * and reduced_costs are this rank's block (block.num_variables entries); the dual vectors have
+ * block.num_constraints entries (shared part identical on all ranks); the SolveLog is the whole
+ * problem's and identical on all ranks (up to wall-clock fields).  The
  * interrupt flag may be raised on any rank: all ranks stop at the same iteration. */
 pdlp_b200_status pdlp_b200_solve_sharded(const pdlp_b200_problem* block, const pdlp_b200_shard* shard, const uint8_t* params, size_t params_len,
                                          const double* initial_primal_solution, const double* initial_dual_solution,

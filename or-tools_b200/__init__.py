@@ -97,6 +97,7 @@ class _CShard(ctypes.Structure):
         ("global_num_variables", ctypes.c_int64),
         ("column_offset", ctypes.c_int64),
         ("nccl_unique_id", ctypes.c_void_p),
+        ("num_shared_constraints", ctypes.c_int64),
     ]
 
 
@@ -191,6 +192,7 @@ from ._api import (  # noqa: E402
 )
 from .sharding import (  # noqa: E402
     ColumnShard,
+    RowSharing,
     column_partition,
     primal_dual_hybrid_gradient_sharded,
     take_columns,

@@ -223,6 +223,8 @@ std::string ApplyShard(const pdlp_b200_shard* s, QpView* v) {
   v->rank = s->rank;
   v->world = s->world;
   v->nccl_unique_id = s->nccl_unique_id;
+  if (s->num_shared_constraints > v->m) return "shard: num_shared_constraints exceeds the block's constraint count";
+  v->num_shared_rows = s->num_shared_constraints < 0 ? v->m : s->num_shared_constraints;
   return "";
 }
 

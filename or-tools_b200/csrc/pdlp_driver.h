@@ -28,7 +28,9 @@ struct QpView {
   // Column-sharded solve: this view is the block of columns
   // [col_offset, col_offset + n) of a problem with global_n columns; rank / world / unique_id
   // identify the NCCL communicator.  world == 1: the whole problem, no communicator.
-  int64_t global_n = -1, col_offset = 0;
+  // m is then this rank's row count: rows [0, num_shared_rows) are shared by all ranks in the same
+  // order, the rest touch this rank's columns only (num_shared_rows < 0: all m rows are shared).
+  int64_t global_n = -1, col_offset = 0, num_shared_rows = -1;
   int rank = 0, world = 1;
   const void* nccl_unique_id = nullptr;  // 128 bytes
   int64_t GlobalN() const { return global_n >= 0 ? global_n : n; }

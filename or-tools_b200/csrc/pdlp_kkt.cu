@@ -27,11 +27,13 @@ struct KktRowOp : AlwaysActive {
   const double* val; const int* idx; const double* x;
   const double* y; const double* y_start; const double* row_scale; const double* clb; const double* cub;
   double cw_offset;
+  int skip_below;  // sharded: rows below it are shared with other ranks and counted on rank 0 only
   __device__ double Load(int64_t k) const { return val[k] * x[idx[k]]; }
   __device__ double RowInit() const { return 0.0; }
   __device__ double RowAdd(double acc, double staged, int) const { return acc + staged; }
   __device__ double RowMerge(double a, double b) const { return a + b; }
   __device__ void RowFinish(int i, double kx, Slots<9>& r) const {
+    if (i < skip_below) return;
     const double lb = clb[i], ub = cub[i], rs = row_scale[i], yi = y[i];
     {
       double scaled_res = 0.0, res_bound = 0.0;
@@ -144,7 +146,7 @@ KktTotals ComputeKktTotals(Workspace& ws, const DeviceProblem& p, const double* 
   const SparseRows& csc = p.K.by_col;
   int g_row = 0, g_col = 0;
   if (p.m > 0) {
-    g_row = EnqueueRows(ws, KktRowOp{{}, csr.val.get(), csr.idx.get(), x, y, y_start, p.row_scale.get(), p.clb.get(), p.cub.get(), cw_primal_offset}, csr, 0);
+    g_row = EnqueueRows(ws, KktRowOp{{}, csr.val.get(), csr.idx.get(), x, y, y_start, p.row_scale.get(), p.clb.get(), p.cub.get(), cw_primal_offset, static_cast<int>(ws.dual_skip_below)}, csr, 0);
     EnqueueFinalize<KktRowOp>(ws, g_row, 0, 0, SideOfRows(csr));
   }
   if (p.n > 0) {

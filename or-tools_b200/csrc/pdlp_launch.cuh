@@ -1,12 +1,10 @@
 // Internal launch helpers shared by the op translation units.
 //
-// Column-sharded solves: every reduction names the SIDE its index range lives on.
-//   kReplicated  dual-side (length m) data: identical on every rank, nothing to combine
-//   kSharded     primal-side (length n_r) data: per-rank partials, all-reduced after finalize
-//   kJoint       the concatenated (n_r + m) range of the trust-region ops: the op itself skips the
-//                replicated tail on ranks != 0, then combined like kSharded
-// and a row-stream launch over the CSR block (`SparseRows::partial_sums`) runs in two phases
-// around an all-reduce of the row sums: the only O(m) collective of the path.
+// Column-sharded solves: every reduction names the SIDE its index range lives on
+// (pdlp_ops.cuh).  Each rank accumulates only the terms it owns - all of its columns, its private
+// rows, and on rank 0 the rows shared by several ranks - and every finalize is followed by an
+// all-reduce of the totals.  A row-stream launch over the CSR block (`SparseRows::partial_sums`)
+// runs in two phases around an all-reduce of the SHARED rows' sums: the only O(rows) collective.
 #ifndef PDLP_B200_LAUNCH_CUH_
 #define PDLP_B200_LAUNCH_CUH_
 
@@ -101,7 +99,7 @@ inline int EnqueueRows(Workspace& ws, const Op& op, const SparseRows& s, int reg
   if (s.partial_sums && IsSharded(ws)) {
     double* sums = ws.partial_rows.get();
     rowstream_kernel<PartialRowOp<Op>><<<RowStreamGrid<PartialRowOp<Op>>(s), kBlock, 0, ws.stream>>>(PartialRowOp<Op>{op, sums}, s.View(), ws.partials[region].get());
-    ws.comm->AllReduce(sums, static_cast<size_t>(s.rows), RowCombineIsMax(op), ws.stream);
+    ws.comm->AllReduce(sums, static_cast<size_t>(ws.shared_rows), RowCombineIsMax(op), ws.stream);
     const int grid = GridFor(s.rows);
     map_reduce_kernel<FinishRowOp<Op>><<<grid, kBlock, 0, ws.stream>>>(FinishRowOp<Op>{op, sums}, s.rows, ws.partials[region].get());
     ws.launches += 2;
@@ -113,8 +111,8 @@ inline int EnqueueRows(Workspace& ws, const Op& op, const SparseRows& s, int reg
   return grid;
 }
 // Side of the reduction slots of a row-stream launch: the CSC block's "rows" are this rank's
-// columns of K (sharded); the CSR block's rows are all of K's rows (replicated after phase 2).
-inline Side SideOfRows(const SparseRows& s) { return s.sharded_rows ? Side::kSharded : Side::kReplicated; }
+// columns of K, the CSR block's rows its dual side.
+inline Side SideOfRows(const SparseRows& s) { return s.sharded_rows ? Side::kSharded : Side::kDual; }
 
 template <class Op>
 __global__ void select_max_slots_kernel(double* totals, const double* max_reduced) {
@@ -130,7 +128,8 @@ inline void EnqueueFinalize(Workspace& ws, int grid, int region, int offset, Sid
   double* totals = ws.totals.get() + offset;
   finalize_kernel<Op><<<1, kBlock, 0, ws.stream>>>(ws.partials[region].get(), grid, totals);
   ++ws.launches;
-  if (side == Side::kReplicated || !IsSharded(ws)) return;
+  (void)side;
+  if (!IsSharded(ws)) return;
   bool any_max = false, any_sum = false;
   for (int s = 0; s < Op::kNumSlots; ++s) (Op::SlotKindOf(s) == kMax ? any_max : any_sum) = true;
   if (!any_max) {

@@ -2,6 +2,8 @@
 // projections, plain SpMV.  Device replacements for
 //   ortools/pdlp/sharded_optimization_utils.cc:83-444,701-750,
 //   ortools/pdlp/sharded_quadratic_program.cc:97-175, ortools/pdlp/sharder.cc:163-335.
+#include <algorithm>
+
 #include "pdlp_launch.cuh"
 
 namespace pdlp_b200 {
@@ -200,8 +202,10 @@ struct RowDotOp : AlwaysActive, NoSlots {
 VectorInfo ComputeVectorInfo(Workspace& ws, InfoKind kind, const double* a, const double* b, int64_t count, Side side) {
   VectorInfo r;
   double t[7] = {0, 0, 0, -INFINITY, -INFINITY, 0, 0};
-  if (count > 0) {
-    const double* h = RunMap(ws, InfoOp{{}, a, b, static_cast<int>(kind)}, count, side);
+  if (count > 0 || IsSharded(ws)) {
+    // Terms this rank owns: [skip, count) (pdlp_ops.cuh Side).
+    const int64_t skip = std::min(ws.SkipBelow(side), count);
+    const double* h = RunMap(ws, InfoOp{{}, a + skip, b != nullptr ? b + skip : nullptr, static_cast<int>(kind)}, count - skip, side);
     for (int i = 0; i < 7; ++i) t[i] = h[i];
   }
   r.num_infinite = static_cast<int64_t>(t[0]);
@@ -265,14 +269,16 @@ void SubtractVectors(Workspace& ws, double* dst, const double* a, const double* 
 }
 void NormAndMax(Workspace& ws, const double* v, int64_t count, double* l2, double* linf, Side side) {
   *l2 = 0.0; *linf = 0.0;
-  if (count == 0) return;
-  const double* h = RunMap(ws, NormMaxOp{{}, v}, count, side);
+  if (count == 0 && !IsSharded(ws)) return;
+  const int64_t skip = std::min(ws.SkipBelow(side), count);
+  const double* h = RunMap(ws, NormMaxOp{{}, v + skip}, count - skip, side);
   *l2 = std::sqrt(h[0]);
   *linf = h[1] < 0 ? 0.0 : h[1];
 }
 double SquaredDistance(Workspace& ws, const double* a, const double* b, int64_t count, Side side) {
-  if (count == 0) return 0.0;
-  return RunMap(ws, SqDistOp{{}, a, b}, count, side)[0];
+  if (count == 0 && !IsSharded(ws)) return 0.0;
+  const int64_t skip = std::min(ws.SkipBelow(side), count);
+  return RunMap(ws, SqDistOp{{}, a + skip, b + skip}, count - skip, side)[0];
 }
 
 void RowDot(Workspace& ws, const SparseRows& s, const double* v, double* out) {

@@ -25,8 +25,12 @@ struct DeviceProblem {
   const double* q_or_null() const { return is_lp ? nullptr : q.get(); }
 };
 
-// Which side of a column-sharded solve a reduction's index range lives on (pdlp_launch.cuh).
-enum class Side { kReplicated, kSharded, kJoint };
+// Which side of a column-sharded solve a reduction's index range lives on (pdlp_launch.cuh):
+//   kSharded  primal-side (this rank's columns): every entry counts, totals are all-reduced
+//   kDual     dual-side (this rank's rows): the leading `shared_rows` rows exist on every rank and
+//             count on rank 0 only, the rest are private to the rank; totals are all-reduced
+//   kJoint    the concatenation (primal block, dual rows) of the trust-region ops
+enum class Side { kDual, kSharded, kJoint };
 
 // Launch context: stream, per-kernel partial buffers, totals, pinned read-back.
 struct Workspace {
@@ -41,6 +45,12 @@ struct Workspace {
   Comm* comm = nullptr;      // null or world 1: single GPU.  Otherwise this rank owns a column block of K
   DVec partial_rows;         // m: per-rank row sums of a sharded CSR pass, all-reduced in place
   DVec combine_tmp;          // kMaxSlots: max-reduced copy of mixed sum/max totals
+  // Sharded solves: rows [0, shared_rows) of this rank's dual side are shared with other ranks
+  // (their row sums are all-reduced, their values replicated), the rest touch this rank's columns
+  // only.  dual_skip_below = first dual row whose reduction terms count on this rank (0 on rank 0
+  // and on a single GPU, shared_rows elsewhere).
+  int64_t shared_rows = 0, dual_skip_below = 0;
+  int64_t SkipBelow(Side side) const { return side == Side::kDual ? dual_skip_below : 0; }
   void Init(int64_t n_, int64_t m_);
   void Destroy();
   void Sync() { PDLP_CUDA_CHECK(cudaStreamSynchronize(stream)); }

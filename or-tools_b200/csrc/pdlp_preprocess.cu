@@ -66,6 +66,8 @@ PreprocessSolver::PreprocessSolver(const QpView& qp, const PrimalDualHybridGradi
     if (qp.n < 1 || qp.m < 1) throw std::invalid_argument("pdlp_b200: a sharded solve needs at least one column per rank and one constraint");
     comm_.Init(qp.rank, qp.world, qp.nccl_unique_id);
     ws_.comm = &comm_;
+    ws_.shared_rows = qp.num_shared_rows < 0 ? qp.m : qp.num_shared_rows;
+    ws_.dual_skip_below = qp.rank == 0 ? 0 : ws_.shared_rows;
   }
   problem_.n = qp.n;
   problem_.m = qp.m;
@@ -124,15 +126,15 @@ QuadraticProgramStats PreprocessSolver::ComputeStats() {
   double* col_norms = ws_.scratch_n[2].get();
   ScaledRowNorms(ws_, p.K.by_row, ones_n, ones_m, false, row_norms);
   ScaledRowNorms(ws_, p.K.by_col, ones_m, ones_n, false, col_norms);
-  const VectorInfo rn = ComputeVectorInfo(ws_, InfoKind::kPlain, row_norms, nullptr, p.m, Side::kReplicated);
+  const VectorInfo rn = ComputeVectorInfo(ws_, InfoKind::kPlain, row_norms, nullptr, p.m, Side::kDual);
   const VectorInfo cn = ComputeVectorInfo(ws_, InfoKind::kPlain, col_norms, nullptr, p.n, Side::kSharded);
   const VectorInfo mat = ComputeVectorInfo(ws_, InfoKind::kPlain, p.K.by_col.val.get(), nullptr, p.K.by_col.nnz, Side::kSharded);
-  const VectorInfo cb = ComputeVectorInfo(ws_, InfoKind::kCombinedBounds, p.cub.get(), p.clb.get(), p.m, Side::kReplicated);
+  const VectorInfo cb = ComputeVectorInfo(ws_, InfoKind::kCombinedBounds, p.cub.get(), p.clb.get(), p.m, Side::kDual);
   const VectorInfo vb = ComputeVectorInfo(ws_, InfoKind::kCombinedBounds, p.vub.get(), p.vlb.get(), p.n, Side::kSharded);
   const VectorInfo ov = ComputeVectorInfo(ws_, InfoKind::kPlain, p.c.get(), nullptr, p.n, Side::kSharded);
   const VectorInfo gaps = ComputeVectorInfo(ws_, InfoKind::kGap, p.vlb.get(), p.vub.get(), p.n, Side::kSharded);
   s.num_variables = comm_.sharded() ? ov.num_finite_nonzero + ov.num_zero + ov.num_infinite : p.n;  // global count
-  s.num_constraints = p.m;
+  s.num_constraints = comm_.sharded() ? cb.num_finite_nonzero + cb.num_zero + cb.num_infinite : p.m;  // global count
   s.constraint_matrix_col_min_l_inf_norm = cn.smallest;
   s.constraint_matrix_row_min_l_inf_norm = rn.smallest;
   s.constraint_matrix_num_nonzeros = mat.num_finite_nonzero;
@@ -223,7 +225,7 @@ SolverResult PreprocessSolver::PreprocessAndSolve(const PrimalDualHybridGradient
     if (linf > kBig)
       return ErrorSolverResult(TERMINATION_REASON_INVALID_INITIAL_SOLUTION,
                                "Initial primal solution has an entry with absolute value " + SixDigits(linf) + " which exceeds limit of " + SixDigits(kBig));
-    NormAndMax(ws_, y_start.get(), p.m, &l2, &linf, Side::kReplicated);
+    NormAndMax(ws_, y_start.get(), p.m, &l2, &linf, Side::kDual);
     if (std::isnan(l2)) return ErrorSolverResult(TERMINATION_REASON_INVALID_INITIAL_SOLUTION, "Initial dual solution has a NAN.");
     if (linf > kBig)
       return ErrorSolverResult(TERMINATION_REASON_INVALID_INITIAL_SOLUTION,
@@ -280,7 +282,7 @@ SolverResult PreprocessSolver::PreprocessAndSolve(const PrimalDualHybridGradient
       RowDot(ws_, p.K.by_col, dual_ev, next);
       // estimate = ev . next = |K ev|^2
       double l2 = 0, linf = 0;
-      NormAndMax(ws_, dual_ev, p.m, &l2, &linf, Side::kReplicated);
+      NormAndMax(ws_, dual_ev, p.m, &l2, &linf, Side::kDual);
       estimate = l2 * l2;
       CopyVector(ws_, ev, next, p.n);
       ++iters;

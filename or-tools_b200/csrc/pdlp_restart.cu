@@ -23,8 +23,8 @@ struct JointView {
   const double* gx; const double* gy; const double* x; const double* y;
   const double* vlb; const double* vub; const double* clb; const double* cub; const double* q;
   int64_t n; double w_primal, w_dual;
-  int dual_owner;  // column-sharded solve: only rank 0 accounts for the replicated dual tail of a sum
-  __device__ bool Counts(int64_t i) const { return i < n || dual_owner != 0; }
+  int64_t dual_skip_below;  // sharded solve: dual rows below it are shared and counted on rank 0 only
+  __device__ bool Counts(int64_t i) const { return i < n || i - n >= dual_skip_below; }
   __device__ double Objective(int64_t i) const { return i < n ? gx[i] : -gy[i - n]; }
   __device__ double LowerBound(int64_t i) const { return i < n ? vlb[i] : (isfinite(cub[i - n]) ? -INFINITY : 0.0); }
   __device__ double UpperBound(int64_t i) const { return i < n ? vub[i] : (isfinite(clb[i - n]) ? INFINITY : 0.0); }
@@ -61,13 +61,14 @@ struct OneSumSlot {
 struct DualGradOp : AlwaysActive, OneSumSlot {
   const double* val; const int* idx; const double* x;
   const double* y; const double* clb; const double* cub; double* gy;
+  int skip_below;
   __device__ double Load(int64_t k) const { return val[k] * x[idx[k]]; }
   __device__ double RowInit() const { return 0.0; }
   __device__ double RowAdd(double acc, double staged, int) const { return acc + staged; }
   __device__ double RowMerge(double a, double b) const { return a + b; }
   __device__ void RowFinish(int i, double kx, Slots<1>& r) const {
     const double coeff = DualSubgradientCoefficient(clb[i], cub[i], y[i], kx);
-    r.v[0] += coeff * y[i];
+    if (i >= skip_below) r.v[0] += coeff * y[i];
     gy[i] = coeff - kx;
   }
 };
@@ -115,9 +116,9 @@ struct CriticalOp : AlwaysActive {
 struct RadiusPassOp : AlwaysActive {
   static constexpr int kNumSlots = 3;
   __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
-  const double* crit; const double* coef; double delta; int64_t n; int dual_owner;
+  const double* crit; const double* coef; double delta; int64_t n; int64_t dual_skip_below;
   __device__ void Apply(int64_t i, Slots<3>& r) const {
-    if (i >= n && dual_owner == 0) return;
+    if (i >= n && i - n < dual_skip_below) return;
     const double cs = crit[i], a = coef[i];
     if (cs <= delta) { r.v[0] += a * (cs * cs); r.v[2] += 1.0; }
     else r.v[1] += a;
@@ -179,7 +180,7 @@ LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProb
   double* gx = ws.scratch_n[0].get();
   double* gy = ws.scratch_m[0].get();
   double primal_value = 0.0, dual_value = 0.0;
-  if (p.m > 0) dual_value = RunRows(ws, DualGradOp{{}, {}, csr.val.get(), csr.idx.get(), x, y, p.clb.get(), p.cub.get(), gy}, csr)[0];
+  if (p.m > 0) dual_value = RunRows(ws, DualGradOp{{}, {}, csr.val.get(), csr.idx.get(), x, y, p.clb.get(), p.cub.get(), gy, static_cast<int>(ws.dual_skip_below)}, csr)[0];
   if (p.n > 0) {
     // When K^T y is not cached it is computed first; the gradient and its value then come
     // from the same kernel either way, so "bounds at the average" and "bounds at the
@@ -195,7 +196,7 @@ LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProb
   const double lagrangian = primal_value + dual_value;
   const int64_t total = p.n + p.m;
   JointView view{gx, gy, x, y, p.vlb.get(), p.vub.get(), p.clb.get(), p.cub.get(), p.q_or_null(), p.n, 0.5 * primal_weight, 0.5 / primal_weight,
-                 (!IsSharded(ws) || ws.comm->rank() == 0) ? 1 : 0};
+                 ws.dual_skip_below};
   int passes = 0;
   LocalizedBounds out{lagrangian, lagrangian, lagrangian, radius};
   if (total == 0) { if (tr_passes) *tr_passes = 0; return out; }
@@ -234,7 +235,7 @@ LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProb
       double delta = 0.0;
       double prev_fixed = -1.0;
       for (;;) {
-        const double* h = RunMap(ws, RadiusPassOp{{}, crit, coef, delta, p.n, view.dual_owner}, total, Side::kJoint);
+        const double* h = RunMap(ws, RadiusPassOp{{}, crit, coef, delta, p.n, view.dual_skip_below}, total, Side::kJoint);
         ++passes;
         const double fixed_r2 = h[0], free_coef = h[1], num_fixed = h[2];
         if (!(free_coef > 0.0)) { step = DBL_MAX; break; }  // trust_region.cc:438-446

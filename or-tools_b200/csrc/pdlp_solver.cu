@@ -135,7 +135,7 @@ IterationStats Solver::CreateSimpleIterationStats(int restart_used) const {  // 
 
 double Solver::DistanceTraveledFromLastStart(const double* x, const double* y) {  // pdhg.cc:1795-1804
   const double dp = SquaredDistance(ws_, x, it_.x_start.get(), problem_.n, Side::kSharded);
-  const double dd = SquaredDistance(ws_, y, it_.y_start.get(), problem_.m, Side::kReplicated);
+  const double dd = SquaredDistance(ws_, y, it_.y_start.get(), problem_.m, Side::kDual);
   return std::sqrt((0.5 * host_.primal_weight) * dp + (0.5 / host_.primal_weight) * dd);
 }
 
@@ -220,7 +220,7 @@ int Solver::ChooseRestartToApply(bool is_major_iteration) {  // pdhg.cc:1904-196
 
 double Solver::ComputeNewPrimalWeight() {  // pdhg.cc:1983-2010
   const double primal_distance = std::sqrt(SquaredDistance(ws_, X(), it_.x_start.get(), problem_.n, Side::kSharded));
-  const double dual_distance = std::sqrt(SquaredDistance(ws_, Y(), it_.y_start.get(), problem_.m, Side::kReplicated));
+  const double dual_distance = std::sqrt(SquaredDistance(ws_, Y(), it_.y_start.get(), problem_.m, Side::kDual));
   constexpr double kNonzeroTol = 1.0e-10;
   if (primal_distance <= kNonzeroTol || primal_distance >= 1.0 / kNonzeroTol || dual_distance <= kNonzeroTol || dual_distance >= 1.0 / kNonzeroTol) {
     return host_.primal_weight;

@@ -84,6 +84,7 @@ struct DualStepOp : OneSum {
   const double* val; const int* idx; const double* xbar;
   double* y0; double* y1;
   const double* clb; const double* cub;
+  int skip_below;  // rows below it are shared with other ranks and counted on rank 0 only
   const double* y; double* yn; double sigma;
   __device__ bool Begin() {
     if (st->active == 0) return false;
@@ -109,7 +110,7 @@ struct DualStepOp : OneSum {
     const double v = fmax(fmin(0.0, temp + sigma * pre.ub), temp + sigma * pre.lb);
     yn[i] = v;
     const double d = v - yi;
-    red.v[0] += d * d;
+    if (i >= skip_below) red.v[0] += d * d;
   }
 };
 
@@ -339,19 +340,20 @@ __global__ void mp_begin_kernel(StepState* st) {
   st->mp_new_tau = tau * dilating;
 }
 
-// Column-sharded solve: |dx|^2 (K1) and the two K3 sums are per-rank partials.  They are folded to
-// three doubles and all-reduced (the second, tiny collective of a trial step; the first is the
+// Column-sharded solve: |dx|^2 (K1), |dy|^2 over the rows this rank owns (K2) and the two K3 sums are
+// per-rank partials.  They are folded to four doubles and all-reduced (the second, tiny collective of a trial step; the first is the
 // row-sum all-reduce inside K2); the decision kernel then reads them as one-block "tables".  Every
 // rank takes the same decision from the same numbers.
-struct StepSums { const double* p1; int g1; const double* p3; int g3; };
-StepSums CombineStepPartials(Workspace& ws, int g1, int g3) {
-  if (!IsSharded(ws)) return {ws.partials[0].get(), g1, ws.partials[2].get(), g3};
+struct StepSums { const double* p1; int g1; const double* p2; int g2; const double* p3; int g3; };
+StepSums CombineStepPartials(Workspace& ws, int g1, int g2, int g3) {
+  if (!IsSharded(ws)) return {ws.partials[0].get(), g1, ws.partials[1].get(), g2, ws.partials[2].get(), g3};
   double* t = ws.totals.get() + 3 * kMaxSlots;
   finalize_kernel<PrimalStepOp><<<1, kBlock, 0, ws.stream>>>(ws.partials[0].get(), g1, t);
-  finalize_kernel<KtyStepOp><<<1, kBlock, 0, ws.stream>>>(ws.partials[2].get(), g3, t + 1);
-  ws.launches += 2;
-  ws.comm->AllReduce(t, 3, false, ws.stream);
-  return {t, 1, t + 1, 1};
+  finalize_kernel<DualStepOp><<<1, kBlock, 0, ws.stream>>>(ws.partials[1].get(), g2, t + 1);
+  finalize_kernel<KtyStepOp><<<1, kBlock, 0, ws.stream>>>(ws.partials[2].get(), g3, t + 2);
+  ws.launches += 3;
+  ws.comm->AllReduce(t, 4, false, ws.stream);
+  return {t, 1, t + 1, 1, t + 2, 1};
 }
 
 }  // namespace
@@ -361,7 +363,7 @@ void EnqueueAdaptiveTrials(Workspace& ws, const DeviceProblem& p, Iterate& it, i
   const SparseRows& csr = p.K.by_row;
   const SparseRows& csc = p.K.by_col;
   PrimalStepOp k1{{}, st, it.x[0].get(), it.x[1].get(), it.kty[0].get(), it.kty[1].get(), p.c.get(), p.q_or_null(), p.vlb.get(), p.vub.get(), it.xbar.get(), 1};
-  DualStepOp k2{{}, st, csr.val.get(), csr.idx.get(), it.xbar.get(), it.y[0].get(), it.y[1].get(), p.clb.get(), p.cub.get()};
+  DualStepOp k2{{}, st, csr.val.get(), csr.idx.get(), it.xbar.get(), it.y[0].get(), it.y[1].get(), p.clb.get(), p.cub.get(), static_cast<int>(ws.dual_skip_below)};
   KtyStepOp k3{st, csc.val.get(), csc.idx.get(), it.y[0].get(), it.y[1].get(), it.x[0].get(), it.x[1].get(), it.kty[0].get(), it.kty[1].get()};
   AverageOp k5{{}, st, it.x[0].get(), it.x[1].get(), it.y[0].get(), it.y[1].get(), it.avg_x.get(), it.avg_y.get(), p.n};
   auto mark = [&]() {
@@ -379,8 +381,8 @@ void EnqueueAdaptiveTrials(Workspace& ws, const DeviceProblem& p, Iterate& it, i
     mark();
     const int g3 = EnqueueRows(ws, k3, csc, 2);
     mark();
-    const StepSums sums = CombineStepPartials(ws, g1, g3);
-    decide_adaptive_kernel<<<1, kBlock, 0, ws.stream>>>(st, sums.p1, sums.g1, ws.partials[1].get(), g2, sums.p3, sums.g3, constant_step ? 1 : 0);
+    const StepSums sums = CombineStepPartials(ws, g1, g2, g3);
+    decide_adaptive_kernel<<<1, kBlock, 0, ws.stream>>>(st, sums.p1, sums.g1, sums.p2, sums.g2, sums.p3, sums.g3, constant_step ? 1 : 0);
     ++ws.launches;
     mark();
     EnqueueMap(ws, k5, p.n + p.m, 0);
@@ -395,7 +397,7 @@ void EnqueueMalitskyPockTrials(Workspace& ws, const DeviceProblem& p, Iterate& i
   const SparseRows& csc = p.K.by_col;
   PrimalStepOp k1{{}, st, it.x[0].get(), it.x[1].get(), it.kty[0].get(), it.kty[1].get(), p.c.get(), p.q_or_null(), p.vlb.get(), p.vub.get(), it.xbar.get(), 0};
   ExtrapolateOp kx{{}, st, it.x[0].get(), it.x[1].get(), it.xbar.get()};
-  DualStepOp k2{{}, st, csr.val.get(), csr.idx.get(), it.xbar.get(), it.y[0].get(), it.y[1].get(), p.clb.get(), p.cub.get()};
+  DualStepOp k2{{}, st, csr.val.get(), csr.idx.get(), it.xbar.get(), it.y[0].get(), it.y[1].get(), p.clb.get(), p.cub.get(), static_cast<int>(ws.dual_skip_below)};
   KtyStepOp k3{st, csc.val.get(), csc.idx.get(), it.y[0].get(), it.y[1].get(), it.x[0].get(), it.x[1].get(), it.kty[0].get(), it.kty[1].get()};
   AverageOp k5{{}, st, it.x[0].get(), it.x[1].get(), it.y[0].get(), it.y[1].get(), it.avg_x.get(), it.avg_y.get(), p.n};
   for (int t = 0; t < trials; ++t) {
@@ -408,8 +410,8 @@ void EnqueueMalitskyPockTrials(Workspace& ws, const DeviceProblem& p, Iterate& i
     EnqueueMap(ws, kx, p.n, 1);
     const int g2 = EnqueueRows(ws, k2, csr, 1);
     const int g3 = EnqueueRows(ws, k3, csc, 2);
-    const StepSums sums = CombineStepPartials(ws, g1, g3);
-    decide_mp_kernel<<<1, kBlock, 0, ws.stream>>>(st, sums.p1, sums.g1, ws.partials[1].get(), g2, sums.p3, sums.g3);
+    const StepSums sums = CombineStepPartials(ws, g1, g2, g3);
+    decide_mp_kernel<<<1, kBlock, 0, ws.stream>>>(st, sums.p1, sums.g1, sums.p2, sums.g2, sums.p3, sums.g3);
     ++ws.launches;
     EnqueueMap(ws, k5, p.n + p.m, 0);
   }

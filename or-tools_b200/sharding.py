@@ -4,8 +4,10 @@ The reference shards every pass over the constraint matrix by contiguous column 
 balanced mass `1 + nnz(column)` across CPU threads (ShardedQuadraticProgram,
 /root/reference/ortools/pdlp/sharded_quadratic_program.h:38-60; Sharder's mass constructor,
 sharder.cc:36-70, and the matrix overload sharder.h:161-165).  The same ranges, one per
-rank, are the unit of multi-GPU work here: rank r keeps columns [starts[r], starts[r+1]) of K,
-the matching slices of the primal-side vectors, and all dual-side vectors.
+rank, are the unit of multi-GPU work here: rank r keeps columns [starts[r], starts[r+1]) of K and
+the matching slices of the primal-side vectors.  Of the dual side it keeps only the constraints
+its columns touch: those touched by several ranks ("shared", exchanged by all-reduce every step)
+first, then those touched by this rank alone ("private", no exchange at all).
 
 Host-side only (numpy / scipy); the numeric work is pdlp_b200_solve_sharded in the C ABI.
 """
@@ -14,7 +16,7 @@ import ctypes
 import numpy as np
 
 from . import UNIQUE_ID_BYTES, _check, _CShard, _lib
-from ._api import QuadraticProgram, primal_dual_hybrid_gradient
+from ._api import PrimalAndDualSolution, QuadraticProgram, primal_dual_hybrid_gradient
 
 try:
     import scipy.sparse as _sp
@@ -49,20 +51,91 @@ def column_partition(col_ptr, world):
     return starts
 
 
-def take_columns(qp, lo, hi):
-    """The column block [lo, hi) of `qp` as a QuadraticProgram: those columns of K (all m rows),
-    the slices of objective vector / diagonal / variable bounds, and the whole constraint bounds.
+class RowSharing:
+    """Which constraints each rank keeps, from which ranks' columns touch them.
+
+    shared        global ids (ascending) of constraints touched by >= 2 ranks: on every rank, first
+    private[r]    global ids (ascending) of constraints touched by rank r only; constraints no rank
+                  touches (empty rows of K) go to rank 0
+    local_rows(r) = concat(shared, private[r]): the rank's constraints in its local order
+    """
+
+    def __init__(self, shared, private, num_constraints):
+        self.shared = np.asarray(shared, dtype=np.int64)
+        self.private = [np.asarray(p, dtype=np.int64) for p in private]
+        self.num_constraints = int(num_constraints)
+
+    @classmethod
+    def from_touch_counts(cls, touched_by_rank, num_constraints):
+        """touched_by_rank[r]: bool array (m) or index array of the constraints rank r's columns touch."""
+        world = len(touched_by_rank)
+        count = np.zeros(num_constraints, dtype=np.int32)
+        owner = np.zeros(num_constraints, dtype=np.int32)  # rank 0 owns what nobody touches
+        for r, t in enumerate(touched_by_rank):
+            t = np.asarray(t)
+            idx = np.flatnonzero(t) if t.dtype == np.bool_ else t.astype(np.int64)
+            count[idx] += 1
+            owner[idx] = r
+        shared = np.flatnonzero(count >= 2)
+        single = count <= 1
+        private = [np.flatnonzero(single & (owner == r)) for r in range(world)]
+        return cls(shared, private, num_constraints)
+
+    @classmethod
+    def from_matrix(cls, K, starts):
+        """K: the whole constraint matrix (CSC); starts: column_partition boundaries."""
+        m = K.shape[0]
+        touched = []
+        for r in range(len(starts) - 1):
+            rows = K.indices[K.indptr[starts[r]]:K.indptr[starts[r + 1]]]
+            t = np.zeros(m, dtype=np.bool_)
+            t[rows] = True
+            touched.append(t)
+        return cls.from_touch_counts(touched, m)
+
+    @classmethod
+    def replicated(cls, num_constraints, world):
+        """Every rank keeps every constraint (all shared): the plain layout."""
+        return cls(np.arange(num_constraints, dtype=np.int64), [np.zeros(0, dtype=np.int64)] * world, num_constraints)
+
+    def local_rows(self, rank):
+        return np.concatenate([self.shared, self.private[rank]])
+
+    def scatter(self, rank, dual_vector):
+        """Whole (m) dual-side vector -> this rank's local order."""
+        return np.asarray(dual_vector, dtype=np.float64)[self.local_rows(rank)]
+
+    def gather(self, local_vectors):
+        """Per-rank local dual-side vectors -> whole (m) vector (the shared part from rank 0)."""
+        out = np.zeros(self.num_constraints)
+        out[self.shared] = local_vectors[0][: self.shared.size]
+        for r, v in enumerate(local_vectors):
+            out[self.private[r]] = v[self.shared.size:]
+        return out
+
+
+def take_columns(qp, lo, hi, rows=None):
+    """The column block [lo, hi) of `qp` as a QuadraticProgram: those columns of K, the slices of
+    objective vector / diagonal / variable bounds.  `rows` (global constraint ids in the rank's
+    local order, RowSharing.local_rows) restricts and renumbers the constraints; None keeps all.
     The objective offset stays whole on every rank (it is added once, after the reductions)."""
     K = qp.constraint_matrix
     if _sp is not None and not _sp.isspmatrix_csc(K):
         K = _sp.csc_matrix(K)
+    block = K[:, lo:hi]
+    clb = np.asarray(qp.constraint_lower_bounds, dtype=np.float64)
+    cub = np.asarray(qp.constraint_upper_bounds, dtype=np.float64)
+    if rows is not None:
+        rows = np.asarray(rows, dtype=np.int64)
+        block = _sp.csc_matrix(block.tocsr()[rows, :])  # every nonzero of the block lies in `rows`
+        clb, cub = clb[rows], cub[rows]
     out = QuadraticProgram()
-    out.constraint_matrix = K[:, lo:hi]
+    out.constraint_matrix = block
     out.objective_vector = np.asarray(qp.objective_vector, dtype=np.float64)[lo:hi].copy()
     out.variable_lower_bounds = np.asarray(qp.variable_lower_bounds, dtype=np.float64)[lo:hi].copy()
     out.variable_upper_bounds = np.asarray(qp.variable_upper_bounds, dtype=np.float64)[lo:hi].copy()
-    out.constraint_lower_bounds = np.asarray(qp.constraint_lower_bounds, dtype=np.float64).copy()
-    out.constraint_upper_bounds = np.asarray(qp.constraint_upper_bounds, dtype=np.float64).copy()
+    out.constraint_lower_bounds = clb.copy()
+    out.constraint_upper_bounds = cub.copy()
     if qp.objective_matrix is not None:
         out.set_objective_matrix_diagonal(np.asarray(qp.objective_matrix, dtype=np.float64)[lo:hi].copy())
     out.objective_offset = qp.objective_offset
@@ -79,62 +152,68 @@ def unique_id():
 
 
 class ColumnShard:
-    """What pdlp_b200_shard carries: which block of the global columns this rank holds."""
+    """What pdlp_b200_shard carries: which block of the global columns this rank holds and how many
+    of its leading constraints are shared with other ranks (None: all of them)."""
 
-    def __init__(self, rank, world, global_num_variables, column_offset, nccl_unique_id):
+    def __init__(self, rank, world, global_num_variables, column_offset, nccl_unique_id, num_shared_constraints=None):
         if world > 1 and (nccl_unique_id is None or len(nccl_unique_id) != UNIQUE_ID_BYTES):
             raise ValueError(f"nccl_unique_id must be {UNIQUE_ID_BYTES} bytes")
         self.rank, self.world = int(rank), int(world)
         self.global_num_variables, self.column_offset = int(global_num_variables), int(column_offset)
+        self.num_shared_constraints = -1 if num_shared_constraints is None else int(num_shared_constraints)
         self._id = (ctypes.c_uint8 * UNIQUE_ID_BYTES).from_buffer_copy(nccl_unique_id) if nccl_unique_id is not None else None
         self.c_shard = _CShard(self.rank, self.world, self.global_num_variables, self.column_offset,
-                               ctypes.cast(self._id, ctypes.c_void_p) if self._id is not None else None)
+                               ctypes.cast(self._id, ctypes.c_void_p) if self._id is not None else None, self.num_shared_constraints)
 
 
 def broadcast_unique_id(group=None):
     """Rank 0 of the torch.distributed group draws the id; everybody returns the same bytes."""
-    import torch
     import torch.distributed as dist
 
     rank = dist.get_rank(group)
     payload = [unique_id() if rank == 0 else None]
     dist.broadcast_object_list(payload, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
-    del torch
     return payload[0]
 
 
 def primal_dual_hybrid_gradient_sharded(qp, params, initial_solution=None, interrupt_solve=None, iteration_stats_callback=None, device=-1,
-                                        group=None, starts=None, gather=True):
+                                        group=None, starts=None, sharing=None, gather=True, private_rows=True, num_shared_constraints=None):
     """PrimalDualHybridGradient over the ranks of a torch.distributed group, one GPU each.
 
-    Every rank passes the same whole `qp` (or `starts` plus a qp that is already its own block --
-    then `qp.global_num_variables` is not needed: starts[-1] is the global count) and receives the
-    same SolverResult: with gather=True the primal solution and reduced costs are all-gathered to
-    full length, otherwise they are this rank's block."""
+    Whole-problem mode (starts is None): every rank passes the same whole `qp` and, with gather=True,
+    receives the same whole SolverResult.  Block mode: `qp` is already this rank's block in its local
+    row order, `starts` the column boundaries and `sharing` the RowSharing that produced the local
+    order (None: every rank holds all constraints, or give num_shared_constraints when only the count
+    is known); results stay local unless gather=True (which needs `sharing` for the dual vector).
+    private_rows=False keeps every constraint on every rank (one all-reduce of all m row sums)."""
     import torch.distributed as dist
 
     rank, world = dist.get_rank(group), dist.get_world_size(group)
     if world == 1:
         return primal_dual_hybrid_gradient(qp, params, initial_solution, interrupt_solve, iteration_stats_callback, device)
-    K = qp.constraint_matrix
     whole = starts is None
     if whole:
+        K = qp.constraint_matrix
         if _sp is not None and not _sp.isspmatrix_csc(K):
             K = _sp.csc_matrix(K)
         starts = column_partition(K.indptr, world)
-        block = take_columns(qp, int(starts[rank]), int(starts[rank + 1]))
+        sharing = RowSharing.from_matrix(K, starts) if private_rows else RowSharing.replicated(K.shape[0], world)
+        lo, hi = int(starts[rank]), int(starts[rank + 1])
+        block = take_columns(qp, lo, hi, sharing.local_rows(rank))
+        if initial_solution is not None:
+            initial_solution = PrimalAndDualSolution(np.asarray(initial_solution.primal_solution, dtype=np.float64)[lo:hi],
+                                                     sharing.scatter(rank, initial_solution.dual_solution))
     else:
         block = qp
-    lo, hi = int(starts[rank]), int(starts[rank + 1])
-    if initial_solution is not None and whole:
-        from ._api import PrimalAndDualSolution
-
-        initial_solution = PrimalAndDualSolution(np.asarray(initial_solution.primal_solution)[lo:hi], initial_solution.dual_solution)
-    shard = ColumnShard(rank, world, int(starts[-1]), lo, broadcast_unique_id(group))
+        lo = int(starts[rank])
+    num_shared = num_shared_constraints if sharing is None else int(sharing.shared.size)
+    shard = ColumnShard(rank, world, int(starts[-1]), lo, broadcast_unique_id(group), num_shared)
     result = primal_dual_hybrid_gradient(block, params, initial_solution, interrupt_solve, iteration_stats_callback, device, shard=shard)
     if gather and result.primal_solution.size:
         parts = [None] * world
-        dist.all_gather_object(parts, (result.primal_solution, result.reduced_costs), group=group)
+        dist.all_gather_object(parts, (result.primal_solution, result.reduced_costs, result.dual_solution), group=group)
         result.primal_solution = np.concatenate([p[0] for p in parts])
         result.reduced_costs = np.concatenate([p[1] for p in parts])
+        if sharing is not None:
+            result.dual_solution = sharing.gather([p[2] for p in parts])
     return result

@@ -68,13 +68,18 @@ def random_sparse_lp(m, n, nnz_per_col=5, seed=0, equality_fraction=0.5, qp_diag
     return qp
 
 
-def multicommodity_flow_lp(num_commodities=64, grid_side=256, num_arcs=520000, pairs_per_commodity=16, seed=0):
+def multicommodity_flow_lp(num_commodities=64, grid_side=256, num_arcs=520000, pairs_per_commodity=16, seed=0, order="commodity"):
     """Config C3: K commodities on a directed grid with random shortcut arcs.
 
-    Variables x[a, k] (arc-major, so contiguous column blocks are arc blocks), one
-    conservation row per (node, commodity) with +1 / -1 entries and one joint capacity
-    row per arc with K ones: nnz = 3 K A.  Capacities are 1.3 x a feasible Manhattan
-    routing, so the LP is feasible; costs are positive so it is bounded."""
+    One conservation row per (commodity, node) with +1 / -1 entries and one joint capacity row per
+    arc with K ones: nnz = 3 K A.  Capacities are 1.3 x a feasible Manhattan routing, so the LP is
+    feasible; costs are positive so it is bounded.
+
+    order="commodity" (default): the textbook block-angular layout - variables x[k, a] at column
+    k A + a, conservation rows at k N + node, then the A linking capacity rows.  A contiguous column
+    block is a set of commodities: its conservation rows are private to it and only the capacity
+    rows link blocks.  order="arc": the same LP with variables at a K + k and conservation rows at
+    node K + k (a contiguous column block is a set of arcs and touches nearly every row)."""
     rng = np.random.Generator(np.random.PCG64(seed))
     side = grid_side
     N = side * side
@@ -132,36 +137,46 @@ def multicommodity_flow_lp(num_commodities=64, grid_side=256, num_arcs=520000, p
     capacity = 1.3 * load + 1.0
     n = A * Kc
     m = N * Kc + A
-    # column j = a * Kc + k: rows (tail, k) -> +1, (head, k) -> -1, capacity row -> +1
-    a_idx = np.repeat(np.arange(A, dtype=np.int64), Kc)
-    k_idx = np.tile(np.arange(Kc, dtype=np.int64), A)
-    r_tail = tails[a_idx] * Kc + k_idx
-    r_head = heads[a_idx] * Kc + k_idx
+    # column of (a, k): rows (tail, k) -> +1, (head, k) -> -1, capacity row of a -> +1
+    if order == "arc":
+        a_idx = np.repeat(np.arange(A, dtype=np.int64), Kc)
+        k_idx = np.tile(np.arange(Kc, dtype=np.int64), A)
+        r_tail = tails[a_idx] * Kc + k_idx
+        r_head = heads[a_idx] * Kc + k_idx
+    elif order == "commodity":
+        k_idx = np.repeat(np.arange(Kc, dtype=np.int64), A)
+        a_idx = np.tile(np.arange(A, dtype=np.int64), Kc)
+        r_tail = k_idx * N + tails[a_idx]
+        r_head = k_idx * N + heads[a_idx]
+    else:
+        raise ValueError(order)
     r_cap = N * Kc + a_idx
     rows = np.stack([r_tail, r_head, r_cap], axis=1)
     vals = np.stack([np.ones(n), -np.ones(n), np.ones(n)], axis=1)
-    order = np.argsort(rows, axis=1, kind="stable")
-    rows = np.take_along_axis(rows, order, axis=1)
-    vals = np.take_along_axis(vals, order, axis=1)
+    by_row = np.argsort(rows, axis=1, kind="stable")
+    rows = np.take_along_axis(rows, by_row, axis=1)
+    vals = np.take_along_axis(vals, by_row, axis=1)
     K = _csc_from_columns(m, n, rows, vals, 3)
     qp = QuadraticProgram()
     qp.constraint_matrix = K
-    rhs = demand.reshape(-1)
+    rhs = demand.reshape(-1) if order == "arc" else demand.T.reshape(-1)
     qp.constraint_lower_bounds = np.concatenate([rhs, np.full(A, -INF)])
     qp.constraint_upper_bounds = np.concatenate([rhs, capacity])
     qp.variable_lower_bounds = np.zeros(n)
     qp.variable_upper_bounds = np.full(n, INF)
     qp.objective_vector = rng.uniform(1.0, 10.0, n)
-    qp.problem_name = f"multicommodity_flow_K{Kc}_N{N}_A{A}_seed{seed}"
+    qp.problem_name = f"multicommodity_flow_K{Kc}_N{N}_A{A}_seed{seed}_{order}"
     return qp
 
 
-def transportation_lp(num_sources, num_sinks, seed=0, first_source=0, last_source=None):
+def transportation_lp(num_sources, num_sinks, seed=0, first_source=0, last_source=None, local_rows=False):
     """Config C5: dense bipartite transportation problem; x[s, d] at column s * D + d.
 
     Rows: supply s (sum_d x <= supply_s), then demand S + d (sum_s x = demand_d); every
     entry of K is 1 and nnz = 2 n.  `first_source` / `last_source` restrict the columns to
-    a block of sources (the per-GPU column shard); rows are never restricted."""
+    a block of sources (the per-GPU column shard).  local_rows=False keeps all S + D rows;
+    local_rows=True keeps only the rows the block touches, in the sharded solver's local order:
+    the D demand rows (shared by every block) first, then the block's own supply rows (private)."""
     rng = np.random.Generator(np.random.PCG64(seed))
     S, D = num_sources, num_sinks
     demand = rng.uniform(1.0, 100.0, D)
@@ -172,15 +187,24 @@ def transportation_lp(num_sources, num_sinks, seed=0, first_source=0, last_sourc
     n = block * D
     s_idx = np.repeat(np.arange(first_source, last_source, dtype=np.int64), D)
     d_idx = np.tile(np.arange(D, dtype=np.int64), block)
-    rows = np.stack([s_idx, S + d_idx], axis=1)
+    if local_rows:
+        rows = np.stack([d_idx, D + (s_idx - first_source)], axis=1)
+        num_rows = D + block
+    else:
+        rows = np.stack([s_idx, S + d_idx], axis=1)
+        num_rows = S + D
     vals = np.ones((n, 2))
-    K = _csc_from_columns(S + D, n, rows, vals, 2)
+    K = _csc_from_columns(num_rows, n, rows, vals, 2)
     cost_rng = np.random.Generator(np.random.PCG64([seed, 1]))
     cost = cost_rng.uniform(1.0, 100.0, S * D)[first_source * D: last_source * D] if block * D < 5e7 else cost_rng.uniform(1.0, 100.0, n)
     qp = QuadraticProgram()
     qp.constraint_matrix = K
-    qp.constraint_lower_bounds = np.concatenate([np.full(S, -INF), demand])
-    qp.constraint_upper_bounds = np.concatenate([supply, demand])
+    if local_rows:
+        qp.constraint_lower_bounds = np.concatenate([demand, np.full(block, -INF)])
+        qp.constraint_upper_bounds = np.concatenate([demand, supply[first_source:last_source]])
+    else:
+        qp.constraint_lower_bounds = np.concatenate([np.full(S, -INF), demand])
+        qp.constraint_upper_bounds = np.concatenate([supply, demand])
     qp.variable_lower_bounds = np.zeros(n)
     qp.variable_upper_bounds = np.full(n, INF)
     qp.objective_vector = cost

@@ -57,8 +57,12 @@ def cases():
     out["lp_mp"] = (fixtures.random_lp(200, 500, 5, 5), params(1e-6, linesearch_rule=P.MALITSKY_POCK_LINESEARCH_RULE))
     out["lp_const"] = (fixtures.random_lp(200, 500, 5, 6), params(1e-6, linesearch_rule=P.CONSTANT_STEP_SIZE_RULE))
     out["lp_distance"] = (fixtures.random_lp(200, 500, 5, 7), params(1e-6, restart_strategy=P.ADAPTIVE_DISTANCE_BASED))
-    pol = params(1e-6, use_feasibility_polishing=True)
+    pol = params(1e-6, use_feasibility_polishing=True, handle_some_primal_gradients_on_finite_bounds_as_residuals=False)
     out["lp_polish"] = (fixtures.random_lp(200, 500, 5, 8), pol)
+    # Block-structured problems: most constraints are private to one rank.
+    from pdlp_b200 import synthetic
+    out["transport"] = (synthetic.transportation_lp(24, 30, seed=3), params(1e-6))
+    out["flow"] = (synthetic.multicommodity_flow_lp(4, 8, 220, 4, seed=2), params(1e-6))
     out["test_lp"] = (fixtures.make_test_lp(), params(1e-8))
     lim = params(1e-12)
     lim.termination_criteria.iteration_limit = 300
@@ -67,9 +71,22 @@ def cases():
     return out
 
 
+def handle_qp():
+    return fixtures.random_lp(300, 700, 5, 12, qp_diagonal=True)
+
+
+def handle_qp_blocked():
+    from pdlp_b200 import synthetic
+    qp = synthetic.transportation_lp(16, 40, seed=5)
+    n = qp.constraint_matrix.shape[1]
+    qp.set_objective_matrix_diagonal(np.random.default_rng(8).random(n))
+    qp.variable_upper_bounds = np.full(n, 50.0)
+    return qp
+
+
 def _log_summary(r):
     log = r.solve_log
-    ci = [c for c in log.solution_stats.convergence_information if c.candidate_type == log.solution_type]
+    ci = [c for c in log.solution_stats.convergence_information if c.candidate_type == log.solution_type] or list(log.solution_stats.convergence_information)
     return dict(reason=int(log.termination_reason), iterations=int(log.iteration_count), solution_type=int(log.solution_type),
                 primal_objective=ci[0].primal_objective if ci else None, dual_objective=ci[0].dual_objective if ci else None,
                 l2_primal_residual=ci[0].l2_primal_residual if ci else None, l2_dual_residual=ci[0].l2_dual_residual if ci else None,
@@ -91,9 +108,13 @@ def _worker(rank, world, port, out_dir):
             r = pdlp_b200.primal_dual_hybrid_gradient_sharded(qp, p, device=rank)
             res[name] = _log_summary(r)
             res[name]["collectives"] = pdlp_b200.last_solve_counters()["collectives"]
+            res[name]["num_constraints"] = int(r.solve_log.original_problem_stats.num_constraints)
             arrays[name + "_x"] = r.primal_solution
             arrays[name + "_y"] = r.dual_solution
             arrays[name + "_rc"] = r.reduced_costs
+        # The same solve with every constraint held by every rank (no private rows).
+        qp, p = cases()["transport"]
+        res["transport_replicated"] = _log_summary(pdlp_b200.primal_dual_hybrid_gradient_sharded(qp, p, device=rank, private_rows=False))
 
         # Warm start: the whole-vector initial solution is sliced per rank.
         qp, p = cases()["lp"]
@@ -131,33 +152,38 @@ def _worker(rank, world, port, out_dir):
         huge.objective_vector[99] = 1e60
         res["huge_objective"] = _log_summary(pdlp_b200.primal_dual_hybrid_gradient_sharded(huge, params(), device=rank))
 
-        # Kernel-level handle on this rank's block.
-        qp = fixtures.random_lp(300, 700, 5, 12, qp_diagonal=True)
-        K = qp.constraint_matrix
-        starts = pdlp_b200.column_partition(K.indptr, world)
-        lo, hi = int(starts[rank]), int(starts[rank + 1])
-        shard = pdlp_b200.ColumnShard(rank, world, 700, lo, pdlp_b200.sharding.broadcast_unique_id())
-        h = pdlp_b200.DeviceProblem(pdlp_b200.take_columns(qp, lo, hi), device=rank, shard=shard)
-        rng = np.random.default_rng(3)
-        x, y = rng.normal(size=700), rng.normal(size=300)
-        arrays["h_kx"] = h.matvec(1, x[lo:hi])[0]
-        arrays["h_kty"] = h.matvec(0, y)[0]
-        arrays["h_rownorm_inf"] = h.scaled_norms(1, 0, np.ones(300), np.ones(hi - lo))
-        arrays["h_rownorm_l2"] = h.scaled_norms(1, 1, np.ones(300), np.ones(hi - lo))
-        arrays["h_colnorm_l2"] = h.scaled_norms(0, 1, np.ones(300), np.ones(hi - lo))
-        st = h.stats()
-        res["h_stats"] = {f.name: getattr(st, f.name) for f in st.DESCRIPTOR.fields}
-        k = h.kkt_stats(params(), x[lo:hi], y)
-        c, i = k.convergence_information[0], k.infeasibility_information[0]
-        res["h_kkt"] = dict(**{f.name: getattr(c, f.name) for f in c.DESCRIPTOR.fields}, **{"inf_" + f.name: getattr(i, f.name) for f in i.DESCRIPTOR.fields})
-        arrays["h_rc"] = h.reduced_costs(params(), x[lo:hi], y)
-        xb = np.clip(x, qp.variable_lower_bounds, qp.variable_upper_bounds)
-        res["h_bounds"] = h.localized_bounds(xb[lo:hi], np.zeros(300), 1.0, 0.75)
-        res["h_bounds_diag"] = h.localized_bounds(xb[lo:hi], np.zeros(300), 2.0, 0.5, use_diagonal_qp_trust_region_solver=True)
-        rs, cs, vals = h.rescale(4, True)
-        arrays["h_row_scale"], arrays["h_col_scale"], arrays["h_scaled_vals"] = rs, cs, vals
-        res["h_block"] = [lo, hi]
-        h.close()
+        # Kernel-level handle on this rank's block, in both constraint layouts.
+        for tag, qp, private in (("h", handle_qp(), False), ("hp", handle_qp_blocked(), True)):
+            K = qp.constraint_matrix
+            m, n = K.shape
+            starts = pdlp_b200.column_partition(K.indptr, world)
+            sharing = pdlp_b200.RowSharing.from_matrix(K, starts) if private else pdlp_b200.RowSharing.replicated(m, world)
+            lo, hi = int(starts[rank]), int(starts[rank + 1])
+            local = sharing.local_rows(rank)
+            shard = pdlp_b200.ColumnShard(rank, world, n, lo, pdlp_b200.sharding.broadcast_unique_id(), sharing.shared.size)
+            h = pdlp_b200.DeviceProblem(pdlp_b200.take_columns(qp, lo, hi, local), device=rank, shard=shard)
+            rng = np.random.default_rng(3)
+            x, y = rng.normal(size=n), rng.normal(size=m)
+            ones_m, ones_n = np.ones(local.size), np.ones(hi - lo)
+            arrays[tag + "_kx"] = h.matvec(1, x[lo:hi])[0]
+            arrays[tag + "_kty"] = h.matvec(0, y[local])[0]
+            arrays[tag + "_rownorm_inf"] = h.scaled_norms(1, 0, ones_m, ones_n)
+            arrays[tag + "_rownorm_l2"] = h.scaled_norms(1, 1, ones_m, ones_n)
+            arrays[tag + "_colnorm_l2"] = h.scaled_norms(0, 1, ones_m, ones_n)
+            st = h.stats()
+            res[tag + "_stats"] = {f.name: getattr(st, f.name) for f in st.DESCRIPTOR.fields}
+            k = h.kkt_stats(params(), x[lo:hi], y[local])
+            c, i = k.convergence_information[0], k.infeasibility_information[0]
+            res[tag + "_kkt"] = dict(**{f.name: getattr(c, f.name) for f in c.DESCRIPTOR.fields},
+                                     **{"inf_" + f.name: getattr(i, f.name) for f in i.DESCRIPTOR.fields})
+            arrays[tag + "_rc"] = h.reduced_costs(params(), x[lo:hi], y[local])
+            xb = np.clip(x, qp.variable_lower_bounds, qp.variable_upper_bounds)
+            res[tag + "_bounds"] = h.localized_bounds(xb[lo:hi], np.zeros(local.size), 1.0, 0.75)
+            res[tag + "_bounds_diag"] = h.localized_bounds(xb[lo:hi], np.zeros(local.size), 2.0, 0.5, use_diagonal_qp_trust_region_solver=True)
+            rs, cs, vals = h.rescale(4, True)
+            arrays[tag + "_row_scale"], arrays[tag + "_col_scale"], arrays[tag + "_scaled_vals"] = rs, cs, vals
+            res[tag + "_block"] = [lo, hi]
+            h.close()
     finally:
         dist.destroy_process_group()
     with open(os.path.join(out_dir, f"rank{rank}.json"), "w") as f:
@@ -188,13 +214,13 @@ def test_every_rank_reports_the_same_result(two_rank_run):
             continue
         assert _strip_clock(res[0][name]) == _strip_clock(res[1][name]), name
     for key in arr[0].files:
-        if key.startswith("h_") and key not in ("h_kx", "h_rownorm_inf", "h_rownorm_l2", "h_row_scale"):
-            continue  # block-local outputs
+        if key.startswith(("h_", "hp_")):
+            continue  # block-local outputs, checked in test_sharded_kernels_match_the_oracle
         np.testing.assert_array_equal(arr[0][key], arr[1][key], err_msg=key)
 
 
 @needs_two
-@pytest.mark.parametrize("name", ["lp", "lp_wide", "qp", "lp_mp", "lp_const", "lp_distance", "lp_polish", "test_lp"])
+@pytest.mark.parametrize("name", ["lp", "lp_wide", "qp", "lp_mp", "lp_const", "lp_distance", "lp_polish", "test_lp", "transport", "flow"])
 def test_sharded_solve_matches_single_gpu_and_oracle(two_rank_run, name):
     res, arr = two_rank_run
     qp, p = cases()[name]
@@ -203,6 +229,7 @@ def test_sharded_solve_matches_single_gpu_and_oracle(two_rank_run, name):
     ora = ob.solve(qp, p)
     assert got["reason"] == single.solve_log.termination_reason == ora.solve_log_dict["termination_reason"] == TR.TERMINATION_REASON_OPTIMAL
     assert got["num_variables"] == qp.constraint_matrix.shape[1] and got["nnz"] == qp.constraint_matrix.nnz
+    assert got["num_constraints"] == qp.constraint_matrix.shape[0]
     s = _log_summary(single)
     for key in ("primal_objective", "dual_objective"):
         assert abs(got[key] - s[key]) <= 1e-6 * max(1.0, abs(s[key])), (key, got[key], s[key])
@@ -259,40 +286,66 @@ def test_warm_start_interrupt_time_limit_and_errors_are_collective(two_rank_run)
 
 
 @needs_two
-def test_sharded_kernels_match_the_oracle(two_rank_run):
-    res, arr = two_rank_run
-    qp = fixtures.random_lp(300, 700, 5, 12, qp_diagonal=True)
+def test_private_rows_shrink_the_exchange_and_change_nothing_else(two_rank_run):
+    res, _ = two_rank_run
+    a, b = res[0]["transport"], res[0]["transport_replicated"]
+    assert a["reason"] == b["reason"] == TR.TERMINATION_REASON_OPTIMAL
+    for key in ("primal_objective", "dual_objective"):
+        assert abs(a[key] - b[key]) <= 1e-6 * max(1.0, abs(b[key]))
+    qp, _ = cases()["transport"]
     K = qp.constraint_matrix
+    sh = pdlp_b200.RowSharing.from_matrix(K, pdlp_b200.column_partition(K.indptr, 2))
+    assert sh.shared.size == 30 and sh.private[0].size + sh.private[1].size == 24  # demand rows shared, supply rows private
+
+
+@needs_two
+@pytest.mark.parametrize("tag,make,private", [("h", handle_qp, False), ("hp", handle_qp_blocked, True)], ids=["replicated", "private_rows"])
+def test_sharded_kernels_match_the_oracle(two_rank_run, tag, make, private):
+    res, arr = two_rank_run
+    qp = make()
+    K = qp.constraint_matrix
+    m, n = K.shape
+    starts = pdlp_b200.column_partition(K.indptr, 2)
+    sh = pdlp_b200.RowSharing.from_matrix(K, starts) if private else pdlp_b200.RowSharing.replicated(m, 2)
+    if private:
+        assert 0 < sh.shared.size < m
     rng = np.random.default_rng(3)
-    x, y = rng.normal(size=700), rng.normal(size=300)
+    x, y = rng.normal(size=n), rng.normal(size=m)
     op = backends.make("oracle").problem(qp)
-    cat = lambda key: np.concatenate([arr[0][key], arr[1][key]])  # noqa: E731
-    assert res[0]["h_block"][1] == res[1]["h_block"][0] and res[1]["h_block"][1] == 700
-    np.testing.assert_allclose(arr[0]["h_kx"], K @ x, rtol=0, atol=1e-12)
-    np.testing.assert_array_equal(cat("h_kty"), op.matvec(0, y))  # K^T y is local to a column block: bit-exact
-    np.testing.assert_array_equal(arr[0]["h_rownorm_inf"], np.abs(K).max(axis=1).toarray().ravel())  # max is exact
-    np.testing.assert_allclose(arr[0]["h_rownorm_l2"], np.sqrt(np.asarray(K.multiply(K).sum(axis=1)).ravel()), rtol=1e-14)
-    np.testing.assert_array_equal(cat("h_colnorm_l2"), op.col_norms(True, np.ones(300), np.ones(700)))
+    cat = lambda key: np.concatenate([arr[0][tag + key], arr[1][tag + key]])  # noqa: E731
+    rows = lambda key: sh.gather([arr[0][tag + key], arr[1][tag + key]])  # noqa: E731
+    ns = sh.shared.size
+    for key in ("_kx", "_rownorm_inf", "_rownorm_l2", "_row_scale"):  # the shared part is identical on both ranks
+        np.testing.assert_array_equal(arr[0][tag + key][:ns], arr[1][tag + key][:ns], err_msg=key)
+    assert res[0][tag + "_block"][1] == res[1][tag + "_block"][0] and res[1][tag + "_block"][1] == n
+    np.testing.assert_allclose(rows("_kx"), K @ x, rtol=0, atol=1e-12)
+    np.testing.assert_allclose(cat("_kty"), op.matvec(0, y), rtol=0, atol=1e-13)  # local to a column block (row order inside a column may differ)
+    np.testing.assert_array_equal(rows("_rownorm_inf"), np.abs(K).max(axis=1).toarray().ravel())  # max is exact
+    np.testing.assert_allclose(rows("_rownorm_l2"), np.sqrt(np.asarray(K.multiply(K).sum(axis=1)).ravel()), rtol=1e-14)
+    np.testing.assert_allclose(cat("_colnorm_l2"), op.col_norms(True, np.ones(m), np.ones(n)), rtol=1e-15)
     ref = op.stats()
-    for key, v in res[0]["h_stats"].items():
+    for key, v in res[0][tag + "_stats"].items():
         want = getattr(ref, key)
+        assert v == res[1][tag + "_stats"][key] or (np.isnan(v) and np.isnan(res[1][tag + "_stats"][key])), key
         if isinstance(want, float) and np.isnan(want):
             assert np.isnan(v), key
         else:
             np.testing.assert_allclose(v, want, rtol=1e-13, err_msg=key)
     k = op.kkt_stats(params(), x, y)
     c, i = k.convergence_information[0], k.infeasibility_information[0]
-    for key, v in res[0]["h_kkt"].items():
+    for key, v in res[0][tag + "_kkt"].items():
         want = getattr(i, key[4:]) if key.startswith("inf_") else getattr(c, key)
         np.testing.assert_allclose(v, want, rtol=1e-11, atol=1e-11, err_msg=key)
-    np.testing.assert_allclose(cat("h_rc"), op.reduced_costs(params(), x, y), rtol=1e-13, atol=1e-13)
+        assert v == res[1][tag + "_kkt"][key], key
+    np.testing.assert_allclose(cat("_rc"), op.reduced_costs(params(), x, y), rtol=1e-13, atol=1e-13)
     xb = np.clip(x, qp.variable_lower_bounds, qp.variable_upper_bounds)
-    for key, args in (("h_bounds", (1.0, 0.75, False)), ("h_bounds_diag", (2.0, 0.5, True))):
-        want = op.localized_bounds(xb, np.zeros(300), args[0], args[1], args[2], 1e-8)
+    for key, args in (("_bounds", (1.0, 0.75, False)), ("_bounds_diag", (2.0, 0.5, True))):
+        want = op.localized_bounds(xb, np.zeros(m), args[0], args[1], args[2], 1e-8)
         for f in ("lagrangian_value", "lower_bound", "upper_bound", "radius"):
-            np.testing.assert_allclose(res[0][key][f], want[f], rtol=1e-7 if args[2] else 1e-10, atol=1e-9, err_msg=f"{key}.{f}")
-            assert res[0][key][f] == res[1][key][f]
+            np.testing.assert_allclose(res[0][tag + key][f], want[f], rtol=1e-7 if args[2] else 1e-10, atol=1e-9, err_msg=f"{key}.{f}")
+            assert res[0][tag + key][f] == res[1][tag + key][f]
     rs, cs, vals = backends.make("oracle").problem(qp).rescale(4, True)
-    np.testing.assert_allclose(arr[0]["h_row_scale"], rs, rtol=1e-12)
-    np.testing.assert_allclose(cat("h_col_scale"), cs, rtol=1e-12)
-    np.testing.assert_allclose(cat("h_scaled_vals"), vals, rtol=1e-12)
+    np.testing.assert_allclose(rows("_row_scale"), rs, rtol=1e-12)
+    np.testing.assert_allclose(cat("_col_scale"), cs, rtol=1e-12)
+    # Scaled values come back in each block's local CSC order; compare as sorted multisets per column block.
+    np.testing.assert_allclose(np.sort(cat("_scaled_vals")), np.sort(vals), rtol=1e-12)

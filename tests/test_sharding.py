@@ -101,12 +101,70 @@ def test_blocks_reassemble_the_problem(quadratic):
         assert pdlp._api._dimension_error(b) == ""
 
 
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_row_sharing_splits_constraints_into_shared_and_private(world):
+    # Block-structured matrix plus a few linking rows and one empty row: most rows are private.
+    rng = np.random.default_rng(world)
+    n, m = 240, 90
+    rows, cols, vals = [], [], []
+    for j in range(n):
+        blk = j * world // n
+        for i in rng.choice(np.arange(blk * 10, blk * 10 + 10), size=3, replace=False):
+            rows.append(i); cols.append(j); vals.append(rng.normal())
+        if j % 7 == 0:
+            rows.append(85 + j % 4); cols.append(j); vals.append(1.0)  # linking rows 85..88
+    K = sp.csc_matrix((vals, (rows, cols)), shape=(m, n))  # row 89 and rows beyond the blocks stay empty
+    starts = pdlp.column_partition(K.indptr, world)
+    sh = pdlp.RowSharing.from_matrix(K, starts)
+    everything = np.concatenate([sh.shared] + sh.private)
+    assert sorted(everything.tolist()) == list(range(m))  # disjoint and complete
+    assert set(sh.shared.tolist()) >= {85, 86, 87, 88} or world == 1
+    assert 89 in sh.private[0].tolist()  # untouched constraints go to rank 0
+    x = rng.normal(size=n)
+    y = rng.normal(size=m)
+    total = np.zeros(m)
+    for r in range(world):
+        lo, hi = int(starts[r]), int(starts[r + 1])
+        local = sh.local_rows(r)
+        blockK = K[:, lo:hi]
+        # every nonzero of the block lies in the rank's local rows ...
+        outside = np.setdiff1d(np.arange(m), local)
+        assert blockK[outside, :].nnz == 0
+        # ... so shared partial sums + private sums reproduce K x, and K^T y needs only local y.
+        part = blockK[local, :] @ x[lo:hi]
+        total[local] += part
+        np.testing.assert_array_equal(blockK[local, :].T @ y[local], blockK.T @ y)
+    np.testing.assert_allclose(total, K @ x, rtol=0, atol=1e-12)
+    v = rng.normal(size=m)
+    np.testing.assert_array_equal(sh.gather([sh.scatter(r, v) for r in range(world)]), v)
+
+
+def test_privatised_blocks_carry_local_rows():
+    qp = random_qp(120, 60, 0.03, 5)
+    K = qp.constraint_matrix
+    starts = pdlp.column_partition(K.indptr, 3)
+    sh = pdlp.RowSharing.from_matrix(K, starts)
+    for r in range(3):
+        lo, hi = int(starts[r]), int(starts[r + 1])
+        local = sh.local_rows(r)
+        b = pdlp.take_columns(qp, lo, hi, local)
+        assert b.constraint_matrix.shape == (local.size, hi - lo)
+        assert (b.constraint_matrix != K[local, lo:hi]).nnz == 0
+        np.testing.assert_array_equal(b.constraint_lower_bounds, qp.constraint_lower_bounds[local])
+        np.testing.assert_array_equal(b.constraint_upper_bounds, qp.constraint_upper_bounds[local])
+        assert pdlp._api._dimension_error(b) == ""
+    rep = pdlp.RowSharing.replicated(60, 3)
+    assert rep.shared.size == 60 and all(p.size == 0 for p in rep.private)
+
+
 def test_shard_descriptor_validation():
     with pytest.raises(ValueError):
         pdlp.ColumnShard(0, 2, 10, 0, b"short")
     s = pdlp.ColumnShard(1, 2, 10, 5, bytes(range(128)))
     assert (s.c_shard.rank, s.c_shard.world, s.c_shard.global_num_variables, s.c_shard.column_offset) == (1, 2, 10, 5)
     assert pdlp.ColumnShard(0, 1, 10, 0, None).c_shard.nccl_unique_id is None
+    assert s.c_shard.num_shared_constraints == -1
+    assert pdlp.ColumnShard(1, 2, 10, 5, bytes(128), 7).c_shard.num_shared_constraints == 7
 
 
 def test_unique_id_is_fresh_each_call():
@@ -147,9 +205,14 @@ def _worker(rank, world, port, out_dir):
         block = pdlp.take_columns(qp, lo, hi)
         x = np.random.default_rng(5).normal(size=300)
         y = np.random.default_rng(6).normal(size=120)
-        # The one O(m) exchange of a trial step: partial K x, summed over ranks.
+        # The one O(rows) exchange of a trial step: partial K x, summed over ranks.
         partial = torch.from_numpy(block.constraint_matrix @ x[lo:hi])
         dist.all_reduce(partial)
+        # With private constraints only the shared prefix is exchanged.
+        sh = pdlp.RowSharing.from_matrix(K, starts)
+        local_block = pdlp.take_columns(qp, lo, hi, sh.local_rows(rank))
+        local_kx = torch.from_numpy(local_block.constraint_matrix @ x[lo:hi])
+        dist.all_reduce(local_kx[: sh.shared.size])
         # The scalar exchange: per-rank partial sums of a primal-side reduction.
         scalars = torch.tensor([float(np.dot(x[lo:hi], x[lo:hi])), float(np.abs(x[lo:hi]).max())], dtype=torch.float64)
         sums = scalars.clone()
@@ -164,7 +227,7 @@ def _worker(rank, world, port, out_dir):
             solve_error = "no error"
         except RuntimeError as e:
             solve_error = str(e)
-        np.savez(os.path.join(out_dir, f"rank{rank}.npz"), kx=partial.numpy(), sums=sums.numpy(), maxes=maxes.numpy(), kty=kty_block, lo=lo, hi=hi,
+        np.savez(os.path.join(out_dir, f"rank{rank}.npz"), kx=partial.numpy(), sums=sums.numpy(), maxes=maxes.numpy(), kty=kty_block, lo=lo, hi=hi, local_kx=local_kx.numpy(), num_shared=sh.shared.size,
                  uid=np.frombuffer(uid, dtype=np.uint8), solve_error=solve_error)
     finally:
         dist.destroy_process_group()
@@ -188,6 +251,13 @@ def test_two_ranks_over_gloo(tmp_path):
     # ... which is K x up to the reassociation of the row sums (the documented source of
     # iteration-count drift between world sizes).
     np.testing.assert_allclose(r[0]["kx"], K @ x, rtol=0, atol=1e-12)
+    # Private-constraint layout: shared prefix identical after the exchange, whole K x after the gather.
+    starts = pdlp.column_partition(K.indptr, world)
+    sh = pdlp.RowSharing.from_matrix(K, starts)
+    ns = int(r[0]["num_shared"])
+    assert ns == sh.shared.size and 0 < ns <= K.shape[0]
+    np.testing.assert_array_equal(r[0]["local_kx"][:ns], r[1]["local_kx"][:ns])
+    np.testing.assert_allclose(sh.gather([r[0]["local_kx"], r[1]["local_kx"]]), K @ x, rtol=0, atol=1e-12)
     np.testing.assert_allclose(r[0]["sums"][0], np.dot(x, x), rtol=1e-15)
     assert r[0]["maxes"][1] == np.abs(x).max() == r[1]["maxes"][1]
     np.testing.assert_array_equal(np.concatenate([r[0]["kty"], r[1]["kty"]]), K.T @ y)
