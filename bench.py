@@ -31,6 +31,9 @@ for _p in (ROOT, os.path.join(ROOT, "tests")):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
+if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+    os.environ["NCCL_DEBUG"] = "WARN"  # NCCL's version banner goes to stdout, which carries the one JSON line
+
 import numpy as np  # noqa: E402
 
 WORKLOADS = {
