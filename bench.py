@@ -39,8 +39,9 @@ import numpy as np  # noqa: E402
 WORKLOADS = {
     # name: (description, generator kwargs at scale 1.0)
     "c2": "synthetic random sparse LP 1M rows x 2M cols, 1e7 nnz, box bounds, eps=1e-4",
-    "c3": "synthetic multi-commodity network-flow LP, 64 commodities x 65536 nodes x 520000 arcs, ~1e8 nnz, block-angular (commodity-major) order, eps=1e-4",
-    "c3a": "the c3 LP in arc-major variable order (a contiguous column block is a set of arcs), eps=1e-4",
+    "c3": "synthetic multi-commodity network-flow LP, 64 commodities x 65536 nodes x 520000 arcs, ~1e8 nnz, block-angular order (8 blocks of 8 commodities, arc-major inside a block), eps=1e-4",
+    "c3a": "the c3 LP in arc-major order (a contiguous column block is a set of arcs and touches nearly every row), eps=1e-4",
+    "c3k": "the c3 LP in commodity-major order (textbook block-angular, strided capacity rows), eps=1e-4",
     "c4": "synthetic diagonal-objective convex QP 5M rows x 10M cols, 5e7 nnz, eps=1e-6",
     "c5": "synthetic transportation LP (dense bipartite), per-GPU block of 1.25e8 nnz, eps=1e-4",
 }
@@ -50,9 +51,9 @@ def make_problem(name, scale, seed=0):
     from pdlp_b200 import synthetic
     if name == "c2":
         return synthetic.random_sparse_lp(int(1_000_000 * scale), int(2_000_000 * scale), 5, seed)
-    if name in ("c3", "c3a"):
+    if name in ("c3", "c3a", "c3k"):
         side = max(8, int(round(256 * scale ** 0.5)))
-        return synthetic.multicommodity_flow_lp(64, side, int(520000 * scale), 16, seed, order="commodity" if name == "c3" else "arc")
+        return synthetic.multicommodity_flow_lp(64, side, int(520000 * scale), 16, seed, order={"c3": "block", "c3a": "arc", "c3k": "commodity"}[name])
     if name == "c4":
         return synthetic.random_sparse_lp(int(5_000_000 * scale), int(10_000_000 * scale), 5, seed, qp_diagonal=True)
     if name == "c5":
@@ -200,7 +201,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     name = args.workload
     threads = os.cpu_count() or 1
-    cpu_its = args.cpu_iterations or {"c2": 48, "c3": 8, "c3a": 8, "c4": 12, "c5": 8}[name]
+    cpu_its = args.cpu_iterations or {"c2": 48, "c3": 8, "c3a": 8, "c3k": 8, "c4": 12, "c5": 8}[name]
     config = {"workload": name + ": " + WORKLOADS[name], "scale": args.scale, "seed": 0,
               "l2_policy": "inputs larger than L2 (matrix + vectors >> 126 MB); no flush between steps"}
 
@@ -323,7 +324,7 @@ def main():
         solve_info = {"solve_iterations": its, "solve_trial_steps": counters.get("trial_steps"), "solve_wall_sec": wall_max,
                       "solve_setup_sec": counters.get("setup_seconds"), "solve_loop_sec": counters.get("loop_seconds"),
                       "solve_device_loop_sec": counters.get("device_loop_seconds"), "solve_kernel_launches": counters.get("kernel_launches"),
-                      "solve_collectives": counters.get("collectives"),
+                      "solve_collectives": counters.get("collectives"), "solve_upload_sec": counters.get("upload_seconds"),
                       "primal_objective": ci[0].primal_objective if len(ci) else None,
                       "relative_kkt_eps": 1e-6 if name == "c4" else 1e-4}
 

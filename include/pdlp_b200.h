@@ -74,6 +74,7 @@ typedef struct {
   double loop_seconds;          /* host wall time of the iteration loop */
   double device_loop_seconds;   /* CUDA-event time of the iteration loop */
   long long collectives;        /* NCCL all-reduces enqueued (0 on one GPU) */
+  double upload_seconds;        /* host->device copies, CSR build, communicator set-up */
 } pdlp_b200_counters;
 
 /* Solves `problem`.
@@ -123,6 +124,12 @@ typedef struct {
 } pdlp_b200_shard;
 
 pdlp_b200_status pdlp_b200_unique_id(uint8_t* out /*PDLP_B200_UNIQUE_ID_BYTES*/);
+
+/* The communicator behind a unique id is created by the first sharded call that presents the id
+ * (collective: all ranks must make that call) and then kept for the life of the process: later
+ * solves with the same id / rank / world reuse it.  This destroys every kept communicator (collective;
+ * no solve may be running); *released (optional) = how many. */
+pdlp_b200_status pdlp_b200_release_communicators(int* released);
 
 /* Same contract as pdlp_b200_solve; every rank must call it with the same params and the same
  * presence of initial solution / interrupt / callback.  initial_primal_solution, primal_solution

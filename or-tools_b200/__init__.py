@@ -84,6 +84,7 @@ class _CCounters(ctypes.Structure):
         ("loop_seconds", ctypes.c_double),
         ("device_loop_seconds", ctypes.c_double),
         ("collectives", ctypes.c_longlong),
+        ("upload_seconds", ctypes.c_double),
     ]
 
 
@@ -123,7 +124,7 @@ EXPORTED_SYMBOLS = [
     "pdlp_b200_last_error", "pdlp_b200_free", "pdlp_b200_problem_create", "pdlp_b200_problem_destroy",
     "pdlp_b200_matvec", "pdlp_b200_scaled_norms", "pdlp_b200_stats", "pdlp_b200_rescale", "pdlp_b200_kkt_stats",
     "pdlp_b200_reduced_costs", "pdlp_b200_localized_bounds", "pdlp_b200_trial_steps", "pdlp_b200_trial_steps_profiled",
-    "pdlp_b200_check_termination", "pdlp_b200_unique_id", "pdlp_b200_solve_sharded", "pdlp_b200_problem_create_sharded",
+    "pdlp_b200_check_termination", "pdlp_b200_unique_id", "pdlp_b200_solve_sharded", "pdlp_b200_problem_create_sharded", "pdlp_b200_release_communicators",
 ]
 
 
@@ -195,6 +196,7 @@ from .sharding import (  # noqa: E402
     RowSharing,
     column_partition,
     primal_dual_hybrid_gradient_sharded,
+    release_communicators,
     take_columns,
     unique_id,
 )

@@ -66,10 +66,15 @@ SolverResult SolveView(const QpView& qp, const PrimalDualHybridGradientParams& p
   if (params.presolve_options->use_glop)
     return ErrorSolverResult(TERMINATION_REASON_INVALID_PARAMETER,
                              "presolve_options.use_glop is not supported by the device path: Glop presolve is host-only (run it before the call).");
+  WallTimer upload;
+  upload.Start();
   PreprocessSolver solver(qp, params);
   // Sharded: a rank whose block is fine must fail with the rank whose block is not.
   if (qp.world > 1 && (code = solver.AgreeOnCode(code)) != 0) return describe(code);
-  return solver.PreprocessAndSolve(params, x0, y0, interrupt, std::move(callback));
+  const double upload_seconds = upload.Get();
+  SolverResult result = solver.PreprocessAndSolve(params, x0, y0, interrupt, std::move(callback));
+  g_last_counters.upload_seconds = upload_seconds;
+  return result;
 }
 
 QpView ViewOf(const QuadraticProgram& qp) {
@@ -263,6 +268,14 @@ pdlp_b200_status pdlp_b200_unique_id(uint8_t* out) {
   });
 }
 
+pdlp_b200_status pdlp_b200_release_communicators(int* released) {
+  return Guard([&]() -> pdlp_b200_status {
+    const int count = CommCache::Get().Release();
+    if (released != nullptr) *released = count;
+    return PDLP_B200_OK;
+  });
+}
+
 pdlp_b200_status pdlp_b200_solve_sharded(const pdlp_b200_problem* problem, const pdlp_b200_shard* shard, const uint8_t* params_bytes, size_t params_len,
                                          const double* x0, const double* y0, const volatile int* interrupt, pdlp_b200_callback callback,
                                          void* callback_user, int device, double* primal, double* dual, double* reduced, int* has_solution,
@@ -323,6 +336,7 @@ pdlp_b200_status pdlp_b200_solve_sharded(const pdlp_b200_problem* problem, const
       counters->loop_seconds = c.loop_seconds;
       counters->device_loop_seconds = c.device_loop_seconds;
       counters->collectives = c.collectives;
+      counters->upload_seconds = c.upload_seconds;
     }
     return PDLP_B200_OK;
   });

@@ -10,6 +10,8 @@
 #include <nccl.h>  // types and enumerators only; no link dependency
 
 #include <cstring>
+#include <map>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 
@@ -57,6 +59,36 @@ class NcclApi {
   std::string error_;
 };
 
+// Communicators are expensive to create (hundreds of milliseconds): they are kept per process,
+// keyed by (unique id, rank, world), and reused by every later solve that presents the same id.
+class CommCache {
+ public:
+  static CommCache& Get() {
+    static CommCache cache;
+    return cache;
+  }
+  ncclComm_t Find(const std::string& key) {
+    std::lock_guard<std::mutex> lock(mu_);
+    auto it = comms_.find(key);
+    return it == comms_.end() ? nullptr : it->second;
+  }
+  void Insert(const std::string& key, ncclComm_t comm) {
+    std::lock_guard<std::mutex> lock(mu_);
+    comms_[key] = comm;
+  }
+  int Release() {  // destroys every cached communicator; no solve may be running
+    std::lock_guard<std::mutex> lock(mu_);
+    const int count = static_cast<int>(comms_.size());
+    for (auto& kv : comms_) NcclApi::Get().CommDestroy(kv.second);
+    comms_.clear();
+    return count;
+  }
+
+ private:
+  std::mutex mu_;
+  std::map<std::string, ncclComm_t> comms_;
+};
+
 // rank / world / communicator of one solve.  world == 1: every method is a no-op.
 class Comm {
  public:
@@ -71,12 +103,16 @@ class Comm {
     if (world <= 1) return;
     NcclApi& api = NcclApi::Get();
     if (!api.ok()) throw std::runtime_error("pdlp_b200: NCCL is required for a sharded solve but could not be loaded: " + api.error());
+    std::string key(static_cast<const char*>(unique_id_128), NCCL_UNIQUE_ID_BYTES);
+    key += ":" + std::to_string(rank) + "/" + std::to_string(world);
+    comm_ = CommCache::Get().Find(key);
+    if (comm_ != nullptr) return;
     ncclUniqueId id;
     std::memcpy(id.internal, unique_id_128, NCCL_UNIQUE_ID_BYTES);
     Check(api.CommInitRank(&comm_, world, id, rank), "ncclCommInitRank");
+    CommCache::Get().Insert(key, comm_);
   }
-  void Destroy() {
-    if (comm_ != nullptr) NcclApi::Get().CommDestroy(comm_);
+  void Destroy() {  // the communicator stays in the cache
     comm_ = nullptr;
     world_ = 1;
     rank_ = 0;

@@ -106,6 +106,7 @@ struct SolveCounters {
   double device_loop_seconds = 0.0;  // CUDA-event time of the iteration loop
   double setup_seconds = 0.0;
   long long collectives = 0;         // NCCL all-reduces enqueued (0 on one GPU)
+  double upload_seconds = 0.0;       // host -> device copies, CSR build, communicator set-up (before preprocessing)
 };
 const SolveCounters& LastSolveCounters();
 

@@ -166,14 +166,31 @@ class ColumnShard:
                                ctypes.cast(self._id, ctypes.c_void_p) if self._id is not None else None, self.num_shared_constraints)
 
 
-def broadcast_unique_id(group=None):
-    """Rank 0 of the torch.distributed group draws the id; everybody returns the same bytes."""
+_group_ids = {}
+
+
+def broadcast_unique_id(group=None, fresh=False):
+    """Rank 0 of the torch.distributed group draws the id; everybody returns the same bytes.  The id
+    is drawn once per group and process (the library keeps the communicator behind it, so later
+    solves skip NCCL's set-up); fresh=True draws a new one (all ranks must pass the same flag)."""
     import torch.distributed as dist
 
+    key = id(group) if group is not None else None
+    if not fresh and key in _group_ids:
+        return _group_ids[key]
     rank = dist.get_rank(group)
     payload = [unique_id() if rank == 0 else None]
     dist.broadcast_object_list(payload, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    _group_ids[key] = payload[0]
     return payload[0]
+
+
+def release_communicators():
+    """Destroys the NCCL communicators the library kept (collective; e.g. before the process group goes away)."""
+    released = ctypes.c_int(0)
+    _check(_lib.pdlp_b200_release_communicators(ctypes.byref(released)))
+    _group_ids.clear()
+    return released.value
 
 
 def primal_dual_hybrid_gradient_sharded(qp, params, initial_solution=None, interrupt_solve=None, iteration_stats_callback=None, device=-1,

@@ -68,18 +68,25 @@ def random_sparse_lp(m, n, nnz_per_col=5, seed=0, equality_fraction=0.5, qp_diag
     return qp
 
 
-def multicommodity_flow_lp(num_commodities=64, grid_side=256, num_arcs=520000, pairs_per_commodity=16, seed=0, order="commodity"):
+def multicommodity_flow_lp(num_commodities=64, grid_side=256, num_arcs=520000, pairs_per_commodity=16, seed=0, order="block", commodity_block=8):
     """Config C3: K commodities on a directed grid with random shortcut arcs.
 
     One conservation row per (commodity, node) with +1 / -1 entries and one joint capacity row per
     arc with K ones: nnz = 3 K A.  Capacities are 1.3 x a feasible Manhattan routing, so the LP is
     feasible; costs are positive so it is bounded.
 
-    order="commodity" (default): the textbook block-angular layout - variables x[k, a] at column
-    k A + a, conservation rows at k N + node, then the A linking capacity rows.  A contiguous column
-    block is a set of commodities: its conservation rows are private to it and only the capacity
-    rows link blocks.  order="arc": the same LP with variables at a K + k and conservation rows at
-    node K + k (a contiguous column block is a set of arcs and touches nearly every row)."""
+    The same LP in three variable / constraint orders (a permutation; costs are drawn per (arc,
+    commodity) so the instance is identical):
+    order="commodity": the textbook block-angular layout - x[k, a] at column k A + a, conservation
+      rows at k N + node, then the A linking capacity rows.  A contiguous column block is a set of
+      commodities: its conservation rows are private to it and only the capacity rows link blocks.
+    order="arc": x at a K + k, conservation rows at node K + k.  A capacity row's K entries and the
+      K conservation rows of a node then sit in K consecutive positions (coalesced gathers), but a
+      contiguous column block is a set of arcs and touches nearly every row.
+    order="block" (default): block-angular with blocks of `commodity_block` commodities, arc-major
+      inside a block: block b holds commodities [b B, (b+1) B), x[k, a] at column b A B + a B + (k - b B),
+      its conservation rows at b N B + node B + (k - b B), then the capacity rows.  Keeps runs of B
+      consecutive entries (B = 8: one 64-byte run) and shards into K / B independent blocks."""
     rng = np.random.Generator(np.random.PCG64(seed))
     side = grid_side
     N = side * side
@@ -148,6 +155,16 @@ def multicommodity_flow_lp(num_commodities=64, grid_side=256, num_arcs=520000, p
         a_idx = np.tile(np.arange(A, dtype=np.int64), Kc)
         r_tail = k_idx * N + tails[a_idx]
         r_head = k_idx * N + heads[a_idx]
+    elif order == "block":
+        B = commodity_block
+        if Kc % B != 0:
+            raise ValueError("commodity_block must divide num_commodities")
+        b_idx = np.repeat(np.arange(Kc // B, dtype=np.int64), A * B)
+        a_idx = np.tile(np.repeat(np.arange(A, dtype=np.int64), B), Kc // B)
+        l_idx = np.tile(np.arange(B, dtype=np.int64), A * (Kc // B))
+        k_idx = b_idx * B + l_idx
+        r_tail = b_idx * (N * B) + tails[a_idx] * B + l_idx
+        r_head = b_idx * (N * B) + heads[a_idx] * B + l_idx
     else:
         raise ValueError(order)
     r_cap = N * Kc + a_idx
@@ -159,12 +176,18 @@ def multicommodity_flow_lp(num_commodities=64, grid_side=256, num_arcs=520000, p
     K = _csc_from_columns(m, n, rows, vals, 3)
     qp = QuadraticProgram()
     qp.constraint_matrix = K
-    rhs = demand.reshape(-1) if order == "arc" else demand.T.reshape(-1)
+    if order == "arc":
+        rhs = demand.reshape(-1)  # (node, k)
+    elif order == "commodity":
+        rhs = demand.T.reshape(-1)  # (k, node)
+    else:
+        rhs = demand.reshape(N, Kc // commodity_block, commodity_block).transpose(1, 0, 2).reshape(-1)  # (block, node, k in block)
     qp.constraint_lower_bounds = np.concatenate([rhs, np.full(A, -INF)])
     qp.constraint_upper_bounds = np.concatenate([rhs, capacity])
     qp.variable_lower_bounds = np.zeros(n)
     qp.variable_upper_bounds = np.full(n, INF)
-    qp.objective_vector = rng.uniform(1.0, 10.0, n)
+    cost = rng.uniform(1.0, 10.0, (A, Kc))  # per (arc, commodity): the same instance in every order
+    qp.objective_vector = cost[a_idx, k_idx]
     qp.problem_name = f"multicommodity_flow_K{Kc}_N{N}_A{A}_seed{seed}_{order}"
     return qp
 

@@ -62,7 +62,7 @@ def cases():
     # Block-structured problems: most constraints are private to one rank.
     from pdlp_b200 import synthetic
     out["transport"] = (synthetic.transportation_lp(24, 30, seed=3), params(1e-6))
-    out["flow"] = (synthetic.multicommodity_flow_lp(4, 8, 220, 4, seed=2), params(1e-6))
+    out["flow"] = (synthetic.multicommodity_flow_lp(4, 8, 220, 4, seed=2, commodity_block=2), params(1e-6))
     out["test_lp"] = (fixtures.make_test_lp(), params(1e-8))
     lim = params(1e-12)
     lim.termination_criteria.iteration_limit = 300
