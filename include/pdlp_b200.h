@@ -54,6 +54,10 @@ typedef struct {
   double objective_offset;
   double objective_scaling_factor;          /* -1 encodes maximisation */
   const char* problem_name;                 /* NULL if unnamed */
+  /* Optional 32-bit form of the offsets / indices (what scipy and most CSC producers hold below 2^31
+   * nonzeros): when col_ptr32 is non-NULL the pair replaces col_ptr / row_idx, which may then be NULL. */
+  const int32_t* col_ptr32;                 /* n + 1 */
+  const int32_t* row_idx32;                 /* num_nonzeros */
 } pdlp_b200_problem;
 
 /* IterationCallbackInfo (primal_dual_hybrid_gradient.h:62-93): iteration_type is the

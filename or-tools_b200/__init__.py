@@ -73,6 +73,8 @@ class _CProblem(ctypes.Structure):
         ("objective_offset", ctypes.c_double),
         ("objective_scaling_factor", ctypes.c_double),
         ("problem_name", ctypes.c_char_p),
+        ("col_ptr32", ctypes.POINTER(ctypes.c_int32)),
+        ("row_idx32", ctypes.POINTER(ctypes.c_int32)),
     ]
 
 

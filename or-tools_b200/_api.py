@@ -134,8 +134,11 @@ class _Marshalled:
             K = K.copy()
             K.sum_duplicates()
         m, n = K.shape
-        self.col_ptr = np.ascontiguousarray(K.indptr, dtype=np.int64)
-        self.row_idx = np.ascontiguousarray(K.indices, dtype=np.int64)
+        # scipy keeps 32-bit offsets / indices below 2^31 nonzeros: hand them over as they are.
+        narrow = K.indptr.dtype == np.int32 and K.indices.dtype == np.int32
+        itype = np.int32 if narrow else np.int64
+        self.col_ptr = np.ascontiguousarray(K.indptr, dtype=itype)
+        self.row_idx = np.ascontiguousarray(K.indices, dtype=itype)
         self.values = np.ascontiguousarray(K.data, dtype=np.float64)
         self.c = _f64(qp.objective_vector)
         self.q = None if qp.objective_matrix is None else _f64(qp.objective_matrix)
@@ -145,10 +148,15 @@ class _Marshalled:
         self.cub = _f64(qp.constraint_upper_bounds)
         self.name = qp.problem_name.encode() if qp.problem_name else None
         self.n, self.m = n, m
+        i32 = ctypes.POINTER(ctypes.c_int32)
         self.c_problem = _CProblem(
-            n, m, self.values.size, _ptr(self.col_ptr, _c_int64_p), _ptr(self.row_idx, _c_int64_p), _ptr(self.values),
+            n, m, self.values.size,
+            ctypes.cast(None, _c_int64_p) if narrow else self.col_ptr.ctypes.data_as(_c_int64_p),
+            ctypes.cast(None, _c_int64_p) if narrow else _ptr(self.row_idx, _c_int64_p), _ptr(self.values),
             _ptr(self.c), _ptr(self.q), _ptr(self.vlb), _ptr(self.vub), _ptr(self.clb), _ptr(self.cub),
             float(qp.objective_offset), float(qp.objective_scaling_factor), self.name,
+            self.col_ptr.ctypes.data_as(i32) if narrow else ctypes.cast(None, i32),
+            (self.row_idx.ctypes.data_as(i32) if self.row_idx.size else ctypes.cast(None, i32)) if narrow else ctypes.cast(None, i32),
         )
 
 

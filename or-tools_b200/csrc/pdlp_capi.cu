@@ -196,8 +196,9 @@ bool ParseParams(const uint8_t* bytes, size_t len, PrimalDualHybridGradientParam
 
 bool ProblemPointersOk(const pdlp_b200_problem* p) {
   if (p == nullptr || p->num_variables < 0 || p->num_constraints < 0 || p->num_nonzeros < 0) return false;
-  if (p->col_ptr == nullptr) return false;
-  if (p->num_nonzeros > 0 && (p->row_idx == nullptr || p->values == nullptr)) return false;
+  if (p->col_ptr == nullptr && p->col_ptr32 == nullptr) return false;
+  if (p->num_nonzeros > 0 && p->values == nullptr) return false;
+  if (p->num_nonzeros > 0 && (p->col_ptr32 != nullptr ? p->row_idx32 == nullptr : p->row_idx == nullptr)) return false;
   if (p->num_variables > 0 && (p->objective_vector == nullptr || p->variable_lower_bounds == nullptr || p->variable_upper_bounds == nullptr)) return false;
   if (p->num_constraints > 0 && (p->constraint_lower_bounds == nullptr || p->constraint_upper_bounds == nullptr)) return false;
   return true;
@@ -207,6 +208,7 @@ QpView ViewOfC(const pdlp_b200_problem* p) {
   QpView v;
   v.n = p->num_variables; v.m = p->num_constraints; v.nnz = p->num_nonzeros;
   v.col_ptr = p->col_ptr; v.row_idx = p->row_idx; v.val = p->values;
+  v.col_ptr32 = p->col_ptr32; v.row_idx32 = p->row_idx32;
   v.c = p->objective_vector; v.q = p->objective_matrix_diagonal;
   v.vlb = p->variable_lower_bounds; v.vub = p->variable_upper_bounds;
   v.clb = p->constraint_lower_bounds; v.cub = p->constraint_upper_bounds;

@@ -18,6 +18,8 @@ struct QpView {
   int64_t n = 0, m = 0, nnz = 0;
   const int64_t* col_ptr = nullptr;
   const int64_t* row_idx = nullptr;
+  const int32_t* col_ptr32 = nullptr;  // when set, the 32-bit pair replaces col_ptr / row_idx
+  const int32_t* row_idx32 = nullptr;
   const double* val = nullptr;
   const double* c = nullptr;
   const double* q = nullptr;  // null for an LP

@@ -10,7 +10,8 @@ namespace pdlp_b200 {
 
 namespace {
 
-__global__ void narrow_offsets_kernel(const int64_t* in, int* out, int64_t count, int64_t nnz, int* bad) {
+template <class I>
+__global__ void narrow_offsets_kernel(const I* in, int* out, int64_t count, int64_t nnz, int* bad) {
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < count; i += stride) {
     const int64_t v = in[i];
@@ -19,7 +20,8 @@ __global__ void narrow_offsets_kernel(const int64_t* in, int* out, int64_t count
   }
 }
 
-__global__ void narrow_indices_kernel(const int64_t* in, int* out, int* iota, int64_t count, int64_t limit, int* bad) {
+template <class I>
+__global__ void narrow_indices_kernel(const I* in, int* out, int* iota, int64_t count, int64_t limit, int* bad) {
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < count; i += stride) {
     const int64_t v = in[i];
@@ -97,8 +99,10 @@ std::vector<int> PartitionRows(const int* ptr, int rows, int* max_row_nnz) {
   return starts;
 }
 
-void BuildDeviceMatrix(int64_t n, int64_t m, int64_t nnz, const int64_t* col_ptr, const int64_t* row_idx, const double* val,
-                       cudaStream_t stream, DeviceMatrix* out) {
+namespace {
+template <class I>
+void BuildDeviceMatrixT(int64_t n, int64_t m, int64_t nnz, const I* col_ptr, const I* row_idx, const double* val, cudaStream_t stream,
+                        DeviceMatrix* out) {
   if (nnz >= (int64_t{1} << 31) - 1 || n >= (int64_t{1} << 31) - 1 || m >= (int64_t{1} << 31) - 1) {
     throw std::runtime_error("pdlp_b200: one device block must have fewer than 2^31 rows, columns and nonzeros");
   }
@@ -113,12 +117,12 @@ void BuildDeviceMatrix(int64_t n, int64_t m, int64_t nnz, const int64_t* col_ptr
   bad.Zero(stream);
   DeviceArray<int> iota(nnz);
   {
-    DeviceArray<int64_t> wide_ptr(n + 1), wide_idx(nnz);
+    DeviceArray<I> wide_ptr(n + 1), wide_idx(nnz);
     wide_ptr.Upload(col_ptr, n + 1, stream);
     wide_idx.Upload(row_idx, nnz, stream);
     csc.val.Upload(val, nnz, stream);
-    narrow_offsets_kernel<<<GridFor(n + 1), kBlock, 0, stream>>>(wide_ptr.get(), csc.ptr.get(), n + 1, nnz, bad.get());
-    narrow_indices_kernel<<<GridFor(nnz), kBlock, 0, stream>>>(wide_idx.get(), csc.idx.get(), iota.get(), nnz, m, bad.get());
+    narrow_offsets_kernel<I><<<GridFor(n + 1), kBlock, 0, stream>>>(wide_ptr.get(), csc.ptr.get(), n + 1, nnz, bad.get());
+    narrow_indices_kernel<I><<<GridFor(nnz), kBlock, 0, stream>>>(wide_idx.get(), csc.idx.get(), iota.get(), nnz, m, bad.get());
     PDLP_CUDA_CHECK(cudaGetLastError());
     int host_bad = 0;
     bad.Download(&host_bad, 1, stream);
@@ -154,6 +158,16 @@ void BuildDeviceMatrix(int64_t n, int64_t m, int64_t nnz, const int64_t* col_ptr
   csr.ptr.Download(host_ptr.data(), m + 1, stream);
   PDLP_CUDA_CHECK(cudaStreamSynchronize(stream));
   SetBlocks(&csr, host_ptr, stream);
+}
+}  // namespace
+
+void BuildDeviceMatrix(int64_t n, int64_t m, int64_t nnz, const int64_t* col_ptr, const int64_t* row_idx, const double* val,
+                       cudaStream_t stream, DeviceMatrix* out) {
+  BuildDeviceMatrixT(n, m, nnz, col_ptr, row_idx, val, stream, out);
+}
+void BuildDeviceMatrix(int64_t n, int64_t m, int64_t nnz, const int32_t* col_ptr, const int32_t* row_idx, const double* val,
+                       cudaStream_t stream, DeviceMatrix* out) {
+  BuildDeviceMatrixT(n, m, nnz, col_ptr, row_idx, val, stream, out);
 }
 
 }  // namespace pdlp_b200

@@ -42,6 +42,9 @@ std::vector<int> PartitionRows(const int* ptr, int rows, int* max_row_nnz);
 // `.transpose()` materialisation).  Throws std::runtime_error on CUDA failure.
 void BuildDeviceMatrix(int64_t n, int64_t m, int64_t nnz, const int64_t* col_ptr, const int64_t* row_idx, const double* val,
                        cudaStream_t stream, DeviceMatrix* out);
+// The same from 32-bit offsets / indices (what scipy holds below 2^31 nonzeros): half the index upload.
+void BuildDeviceMatrix(int64_t n, int64_t m, int64_t nnz, const int32_t* col_ptr, const int32_t* row_idx, const double* val,
+                       cudaStream_t stream, DeviceMatrix* out);
 
 }  // namespace pdlp_b200
 #endif  // PDLP_B200_MATRIX_CUH_

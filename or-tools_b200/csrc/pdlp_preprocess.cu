@@ -74,7 +74,8 @@ PreprocessSolver::PreprocessSolver(const QpView& qp, const PrimalDualHybridGradi
   problem_.is_lp = qp.q == nullptr;
   problem_.objective_offset = qp.objective_offset;
   problem_.objective_scaling_factor = qp.objective_scaling_factor;
-  BuildDeviceMatrix(qp.n, qp.m, qp.nnz, qp.col_ptr, qp.row_idx, qp.val, ws_.stream, &problem_.K);
+  if (qp.col_ptr32 != nullptr) BuildDeviceMatrix(qp.n, qp.m, qp.nnz, qp.col_ptr32, qp.row_idx32, qp.val, ws_.stream, &problem_.K);
+  else BuildDeviceMatrix(qp.n, qp.m, qp.nnz, qp.col_ptr, qp.row_idx, qp.val, ws_.stream, &problem_.K);
   problem_.K.by_col.sharded_rows = comm_.sharded();
   problem_.K.by_row.partial_sums = comm_.sharded();
   auto up = [&](DVec& d, const double* h, int64_t count) {
