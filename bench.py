@@ -32,7 +32,7 @@ for _p in (ROOT, os.path.join(ROOT, "tests")):
         sys.path.insert(0, _p)
 
 if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-    os.environ["NCCL_DEBUG"] = "WARN"  # NCCL's version banner goes to stdout, which carries the one JSON line
+    os.environ["NCCL_DEBUG"] = "NONE"  # NCCL's version banner (level VERSION, e.g. from /etc/nccl.conf) goes to stdout, which carries the one JSON line
 
 import numpy as np  # noqa: E402
 

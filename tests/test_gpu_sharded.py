@@ -291,7 +291,7 @@ def test_private_rows_shrink_the_exchange_and_change_nothing_else(two_rank_run):
     a, b = res[0]["transport"], res[0]["transport_replicated"]
     assert a["reason"] == b["reason"] == TR.TERMINATION_REASON_OPTIMAL
     for key in ("primal_objective", "dual_objective"):
-        assert abs(a[key] - b[key]) <= 1e-6 * max(1.0, abs(b[key]))
+        assert abs(a[key] - b[key]) <= 1e-5 * max(1.0, abs(b[key]))  # both are eps = 1e-6 optimal
     qp, _ = cases()["transport"]
     K = qp.constraint_matrix
     sh = pdlp_b200.RowSharing.from_matrix(K, pdlp_b200.column_partition(K.indptr, 2))
