@@ -296,6 +296,8 @@ def main():
     if not sharded:
         step_gbs = b_step * args.steps / seconds / 1e9
 
+    dp.close()  # the resident copy goes away before the end-to-end solve uploads its own
+
     # ---- end-to-end solve from host buffers ----
     e2e = None
     solve_info = {}
