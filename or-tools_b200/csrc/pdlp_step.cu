@@ -344,14 +344,23 @@ __global__ void mp_begin_kernel(StepState* st) {
 // per-rank partials.  They are folded to four doubles and all-reduced (the second, tiny collective of a trial step; the first is the
 // row-sum all-reduce inside K2); the decision kernel then reads them as one-block "tables".  Every
 // rank takes the same decision from the same numbers.
+// The four step-test sums of this rank, reduced in the same fixed order the decision kernel uses.
+__global__ void __launch_bounds__(kBlock) fold_step_partials_kernel(const double* p1, int g1, const double* p2, int g2, const double* p3, int g3,
+                                                                   double* out) {
+  __shared__ double buf[kBlock];
+  const double a = ReducePartialsSum(p1, g1, 1, 0, buf);
+  const double b = ReducePartialsSum(p2, g2, 1, 0, buf);
+  const double c = ReducePartialsSum(p3, g3, 2, 0, buf);
+  const double d = ReducePartialsSum(p3, g3, 2, 1, buf);
+  if (threadIdx.x == 0) { out[0] = a; out[1] = b; out[2] = c; out[3] = d; }
+}
+
 struct StepSums { const double* p1; int g1; const double* p2; int g2; const double* p3; int g3; };
 StepSums CombineStepPartials(Workspace& ws, int g1, int g2, int g3) {
   if (!IsSharded(ws)) return {ws.partials[0].get(), g1, ws.partials[1].get(), g2, ws.partials[2].get(), g3};
   double* t = ws.totals.get() + 3 * kMaxSlots;
-  finalize_kernel<PrimalStepOp><<<1, kBlock, 0, ws.stream>>>(ws.partials[0].get(), g1, t);
-  finalize_kernel<DualStepOp><<<1, kBlock, 0, ws.stream>>>(ws.partials[1].get(), g2, t + 1);
-  finalize_kernel<KtyStepOp><<<1, kBlock, 0, ws.stream>>>(ws.partials[2].get(), g3, t + 2);
-  ws.launches += 3;
+  fold_step_partials_kernel<<<1, kBlock, 0, ws.stream>>>(ws.partials[0].get(), g1, ws.partials[1].get(), g2, ws.partials[2].get(), g3, t);
+  ++ws.launches;
   ws.comm->AllReduce(t, 4, false, ws.stream);
   return {t, 1, t + 1, 1, t + 2, 1};
 }
