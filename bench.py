@@ -326,7 +326,7 @@ def main():
         solve_info = {"solve_iterations": its, "solve_trial_steps": counters.get("trial_steps"), "solve_wall_sec": wall_max,
                       "solve_setup_sec": counters.get("setup_seconds"), "solve_loop_sec": counters.get("loop_seconds"),
                       "solve_device_loop_sec": counters.get("device_loop_seconds"), "solve_kernel_launches": counters.get("kernel_launches"),
-                      "solve_collectives": counters.get("collectives"), "solve_upload_sec": counters.get("upload_seconds"),
+                      "solve_collectives": counters.get("collectives"), "solve_upload_sec": counters.get("upload_seconds"), "solve_nccl_symmetric_buffers": counters.get("symmetric_buffers"),
                       "primal_objective": ci[0].primal_objective if len(ci) else None,
                       "relative_kkt_eps": 1e-6 if name == "c4" else 1e-4}
 

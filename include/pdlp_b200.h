@@ -79,6 +79,7 @@ typedef struct {
   double device_loop_seconds;   /* CUDA-event time of the iteration loop */
   long long collectives;        /* NCCL all-reduces enqueued (0 on one GPU) */
   double upload_seconds;        /* host->device copies, CSR build, communicator set-up */
+  int symmetric_buffers;        /* exchange buffers NCCL registered as symmetric windows (0: plain all-reduce) */
 } pdlp_b200_counters;
 
 /* Solves `problem`.

@@ -87,6 +87,7 @@ class _CCounters(ctypes.Structure):
         ("device_loop_seconds", ctypes.c_double),
         ("collectives", ctypes.c_longlong),
         ("upload_seconds", ctypes.c_double),
+        ("symmetric_buffers", ctypes.c_int),
     ]
 
 

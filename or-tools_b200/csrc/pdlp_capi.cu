@@ -339,6 +339,7 @@ pdlp_b200_status pdlp_b200_solve_sharded(const pdlp_b200_problem* problem, const
       counters->device_loop_seconds = c.device_loop_seconds;
       counters->collectives = c.collectives;
       counters->upload_seconds = c.upload_seconds;
+      counters->symmetric_buffers = c.symmetric_buffers;
     }
     return PDLP_B200_OK;
   });

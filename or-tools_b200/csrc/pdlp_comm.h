@@ -14,6 +14,7 @@
 #include <mutex>
 #include <stdexcept>
 #include <string>
+#include <vector>
 
 namespace pdlp_b200 {
 
@@ -28,7 +29,13 @@ class NcclApi {
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
   ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  // Symmetric-memory registration (NCCL >= 2.27); optional: null when the library lacks it.
+  ncclResult_t (*MemAlloc)(void**, size_t) = nullptr;
+  ncclResult_t (*MemFree)(void*) = nullptr;
+  ncclResult_t (*CommWindowRegister)(ncclComm_t, void*, size_t, ncclWindow_t*, int) = nullptr;
+  ncclResult_t (*CommWindowDeregister)(ncclComm_t, ncclWindow_t) = nullptr;
   bool ok() const { return handle_ != nullptr; }
+  bool has_symmetric() const { return MemAlloc != nullptr && MemFree != nullptr && CommWindowRegister != nullptr && CommWindowDeregister != nullptr; }
   const std::string& error() const { return error_; }
 
  private:
@@ -46,6 +53,12 @@ class NcclApi {
     Load(CommDestroy, "ncclCommDestroy");
     Load(AllReduce, "ncclAllReduce");
     Load(GetErrorString, "ncclGetErrorString");
+    if (handle_ != nullptr) {
+      MemAlloc = reinterpret_cast<decltype(MemAlloc)>(dlsym(handle_, "ncclMemAlloc"));
+      MemFree = reinterpret_cast<decltype(MemFree)>(dlsym(handle_, "ncclMemFree"));
+      CommWindowRegister = reinterpret_cast<decltype(CommWindowRegister)>(dlsym(handle_, "ncclCommWindowRegister"));
+      CommWindowDeregister = reinterpret_cast<decltype(CommWindowDeregister)>(dlsym(handle_, "ncclCommWindowDeregister"));
+    }
   }
   template <class F>
   void Load(F& f, const char* symbol) {
@@ -112,7 +125,40 @@ class Comm {
     Check(api.CommInitRank(&comm_, world, id, rank), "ncclCommInitRank");
     CommCache::Get().Insert(key, comm_);
   }
+  // A device buffer of `bytes` (the same on every rank; collective) for all-reduces in place.  With
+  // NCCL's symmetric-memory support (ncclMemAlloc + ncclCommWindowRegister, NCCL_WIN_COLL_SYMMETRIC)
+  // the library then uses its low-latency NVLink kernels on it; without it (older NCCL, no NVLink
+  // fabric, PDLP_B200_NCCL_SYMMETRIC=0) this is plain device memory and the call is the usual one.
+  double* AllocateExchangeBuffer(size_t bytes) {
+    Exchange e;
+    NcclApi& api = NcclApi::Get();
+    const char* env = std::getenv("PDLP_B200_NCCL_SYMMETRIC");
+    const bool wanted = world_ > 1 && api.has_symmetric() && !(env != nullptr && env[0] == '0');
+    if (wanted && api.MemAlloc(&e.ptr, bytes) == ncclSuccess) {
+      e.nccl_memory = true;
+      if (api.CommWindowRegister(comm_, e.ptr, bytes, &e.window, NCCL_WIN_COLL_SYMMETRIC) == ncclSuccess && e.window != nullptr) {
+        e.registered = true;
+        ++symmetric_buffers_;
+      }
+    } else {
+      e.ptr = nullptr;
+      cudaError_t err = cudaMalloc(&e.ptr, bytes);
+      if (err != cudaSuccess) throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(err) + " allocating an exchange buffer");
+    }
+    cudaMemset(e.ptr, 0, bytes);
+    exchange_.push_back(e);
+    return static_cast<double*>(e.ptr);
+  }
+  int symmetric_buffers() const { return symmetric_buffers_; }
+
   void Destroy() {  // the communicator stays in the cache
+    for (Exchange& e : exchange_) {
+      if (e.registered) NcclApi::Get().CommWindowDeregister(comm_, e.window);
+      if (e.nccl_memory) NcclApi::Get().MemFree(e.ptr);
+      else if (e.ptr != nullptr) cudaFree(e.ptr);
+    }
+    exchange_.clear();
+    symmetric_buffers_ = 0;
     comm_ = nullptr;
     world_ = 1;
     rank_ = 0;
@@ -133,6 +179,9 @@ class Comm {
   void Check(ncclResult_t r, const char* what) {
     if (r != ncclSuccess) throw std::runtime_error(std::string("pdlp_b200: ") + what + " failed: " + NcclApi::Get().GetErrorString(r));
   }
+  struct Exchange { void* ptr = nullptr; ncclWindow_t window = nullptr; bool nccl_memory = false, registered = false; };
+  std::vector<Exchange> exchange_;
+  int symmetric_buffers_ = 0;
   int rank_ = 0, world_ = 1;
   ncclComm_t comm_ = nullptr;
   long long collectives_ = 0;

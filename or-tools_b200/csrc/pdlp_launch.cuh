@@ -97,7 +97,7 @@ inline int EnqueueMap(Workspace& ws, const Op& op, int64_t count, int region = 0
 template <class Op>
 inline int EnqueueRows(Workspace& ws, const Op& op, const SparseRows& s, int region = 0) {
   if (s.partial_sums && IsSharded(ws)) {
-    double* sums = ws.partial_rows.get();
+    double* sums = ws.exchange_rows;
     rowstream_kernel<PartialRowOp<Op>><<<RowStreamGrid<PartialRowOp<Op>>(s), kBlock, 0, ws.stream>>>(PartialRowOp<Op>{op, sums}, s.View(), ws.partials[region].get());
     ws.comm->AllReduce(sums, static_cast<size_t>(ws.shared_rows), RowCombineIsMax(op), ws.stream);
     const int grid = GridFor(s.rows);

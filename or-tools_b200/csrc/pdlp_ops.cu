@@ -18,7 +18,6 @@ void Workspace::Init(int64_t n_, int64_t m_) {
   for (auto& v : scratch_n) v.Resize(n > 0 ? n : 1);
   for (auto& v : scratch_m) v.Resize(m > 0 ? m : 1);
   for (auto& v : scratch_nm) v.Resize(n + m > 0 ? n + m : 1);
-  partial_rows.Resize(m > 0 ? m : 1);
   combine_tmp.Resize(kMaxSlots);
 }
 

@@ -43,7 +43,8 @@ struct Workspace {
   long long launches = 0;    // kernels launched (bench "gpu_launches")
   std::vector<cudaEvent_t>* profile = nullptr;  // when set, the trial-step launcher records an event around every kernel
   Comm* comm = nullptr;      // null or world 1: single GPU.  Otherwise this rank owns a column block of K
-  DVec partial_rows;         // m: per-rank row sums of a sharded CSR pass, all-reduced in place
+  double* exchange_rows = nullptr;  // sharded: the buffer the row sums are written to and all-reduced in (Comm::AllocateExchangeBuffer)
+  double* exchange_sums = nullptr;  // sharded: 16 doubles for the step-test sums
   DVec combine_tmp;          // kMaxSlots: max-reduced copy of mixed sum/max totals
   // Sharded solves: rows [0, shared_rows) of this rank's dual side are shared with other ranks
   // (their row sums are all-reduced, their values replicated), the rest touch this rank's columns

@@ -68,6 +68,11 @@ PreprocessSolver::PreprocessSolver(const QpView& qp, const PrimalDualHybridGradi
     ws_.comm = &comm_;
     ws_.shared_rows = qp.num_shared_rows < 0 ? qp.m : qp.num_shared_rows;
     ws_.dual_skip_below = qp.rank == 0 ? 0 : ws_.shared_rows;
+    // Exchange buffers have the same size on every rank (NCCL symmetric registration needs that).
+    double most_rows = static_cast<double>(qp.m);
+    AgreeOnMax(&most_rows, 1);
+    ws_.exchange_rows = comm_.AllocateExchangeBuffer(static_cast<size_t>(most_rows) * sizeof(double));
+    ws_.exchange_sums = comm_.AllocateExchangeBuffer(16 * sizeof(double));
   }
   problem_.n = qp.n;
   problem_.m = qp.m;
@@ -97,6 +102,7 @@ PreprocessSolver::PreprocessSolver(const QpView& qp, const PrimalDualHybridGradi
 }
 
 PreprocessSolver::~PreprocessSolver() {
+  if (ws_.stream != nullptr) cudaStreamSynchronize(ws_.stream);
   comm_.Destroy();
   ws_.Destroy();
 }
@@ -311,6 +317,7 @@ SolverResult PreprocessSolver::PreprocessAndSolve(const PrimalDualHybridGradient
   // Counters for benchmarks.
   g_last_counters.kernel_launches = ws_.launches;
   g_last_counters.collectives = comm_.collectives();
+  g_last_counters.symmetric_buffers = comm_.symmetric_buffers();
   g_last_counters.trial_steps = solver.TrialSteps();
   g_last_counters.device_loop_seconds = solver.DeviceLoopSeconds();
   g_last_counters.setup_seconds = result.solve_log.preprocessing_time_sec;

@@ -358,7 +358,7 @@ __global__ void __launch_bounds__(kBlock) fold_step_partials_kernel(const double
 struct StepSums { const double* p1; int g1; const double* p2; int g2; const double* p3; int g3; };
 StepSums CombineStepPartials(Workspace& ws, int g1, int g2, int g3) {
   if (!IsSharded(ws)) return {ws.partials[0].get(), g1, ws.partials[1].get(), g2, ws.partials[2].get(), g3};
-  double* t = ws.totals.get() + 3 * kMaxSlots;
+  double* t = ws.exchange_sums;
   fold_step_partials_kernel<<<1, kBlock, 0, ws.stream>>>(ws.partials[0].get(), g1, ws.partials[1].get(), g2, ws.partials[2].get(), g3, t);
   ++ws.launches;
   ws.comm->AllReduce(t, 4, false, ws.stream);

@@ -106,6 +106,7 @@ struct SolveCounters {
   double device_loop_seconds = 0.0;  // CUDA-event time of the iteration loop
   double setup_seconds = 0.0;
   long long collectives = 0;         // NCCL all-reduces enqueued (0 on one GPU)
+  int symmetric_buffers = 0;         // exchange buffers NCCL accepted as symmetric windows (0: plain all-reduce path)
   double upload_seconds = 0.0;       // host -> device copies, CSR build, communicator set-up (before preprocessing)
 };
 const SolveCounters& LastSolveCounters();
