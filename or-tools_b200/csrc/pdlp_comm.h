@@ -72,34 +72,52 @@ class NcclApi {
   std::string error_;
 };
 
-// Communicators are expensive to create (hundreds of milliseconds): they are kept per process,
-// keyed by (unique id, rank, world), and reused by every later solve that presents the same id.
+// Communicators are expensive to create (hundreds of milliseconds), and so is registering an
+// exchange buffer with them: both are kept per process, keyed by (unique id, rank, world), and
+// reused by every later solve that presents the same id.
+struct ExchangeBuffer { void* ptr = nullptr; size_t bytes = 0; ncclWindow_t window = nullptr; bool nccl_memory = false, registered = false; };
+struct CachedComm {
+  ncclComm_t comm = nullptr;
+  std::vector<ExchangeBuffer> buffers;  // by slot
+  int users = 0;                        // live solvers / problem handles on this communicator
+};
 class CommCache {
  public:
   static CommCache& Get() {
     static CommCache cache;
     return cache;
   }
-  ncclComm_t Find(const std::string& key) {
+  CachedComm* Find(const std::string& key) {
     std::lock_guard<std::mutex> lock(mu_);
     auto it = comms_.find(key);
-    return it == comms_.end() ? nullptr : it->second;
+    return it == comms_.end() ? nullptr : &it->second;
   }
-  void Insert(const std::string& key, ncclComm_t comm) {
+  CachedComm* Insert(const std::string& key, ncclComm_t comm) {
     std::lock_guard<std::mutex> lock(mu_);
-    comms_[key] = comm;
+    CachedComm& c = comms_[key];
+    c.comm = comm;
+    return &c;
   }
-  int Release() {  // destroys every cached communicator; no solve may be running
+  static void FreeBuffer(ncclComm_t comm, ExchangeBuffer& e) {
+    if (e.registered) NcclApi::Get().CommWindowDeregister(comm, e.window);
+    if (e.nccl_memory) NcclApi::Get().MemFree(e.ptr);
+    else if (e.ptr != nullptr) cudaFree(e.ptr);
+    e = ExchangeBuffer();
+  }
+  int Release() {  // destroys every cached communicator and its buffers; no solve may be running
     std::lock_guard<std::mutex> lock(mu_);
     const int count = static_cast<int>(comms_.size());
-    for (auto& kv : comms_) NcclApi::Get().CommDestroy(kv.second);
+    for (auto& kv : comms_) {
+      for (ExchangeBuffer& e : kv.second.buffers) FreeBuffer(kv.second.comm, e);
+      NcclApi::Get().CommDestroy(kv.second.comm);
+    }
     comms_.clear();
     return count;
   }
 
  private:
   std::mutex mu_;
-  std::map<std::string, ncclComm_t> comms_;
+  std::map<std::string, CachedComm> comms_;  // node-based: pointers to entries stay valid
 };
 
 // rank / world / communicator of one solve.  world == 1: every method is a no-op.
@@ -118,47 +136,57 @@ class Comm {
     if (!api.ok()) throw std::runtime_error("pdlp_b200: NCCL is required for a sharded solve but could not be loaded: " + api.error());
     std::string key(static_cast<const char*>(unique_id_128), NCCL_UNIQUE_ID_BYTES);
     key += ":" + std::to_string(rank) + "/" + std::to_string(world);
-    comm_ = CommCache::Get().Find(key);
-    if (comm_ != nullptr) return;
+    cached_ = CommCache::Get().Find(key);
+    if (cached_ != nullptr) {
+      comm_ = cached_->comm;
+      ++cached_->users;
+      return;
+    }
     ncclUniqueId id;
     std::memcpy(id.internal, unique_id_128, NCCL_UNIQUE_ID_BYTES);
     Check(api.CommInitRank(&comm_, world, id, rank), "ncclCommInitRank");
-    CommCache::Get().Insert(key, comm_);
+    cached_ = CommCache::Get().Insert(key, comm_);
+    ++cached_->users;
   }
-  // A device buffer of `bytes` (the same on every rank; collective) for all-reduces in place.  With
-  // NCCL's symmetric-memory support (ncclMemAlloc + ncclCommWindowRegister, NCCL_WIN_COLL_SYMMETRIC)
-  // the library then uses its low-latency NVLink kernels on it; without it (older NCCL, no NVLink
-  // fabric, PDLP_B200_NCCL_SYMMETRIC=0) this is plain device memory and the call is the usual one.
-  double* AllocateExchangeBuffer(size_t bytes) {
-    Exchange e;
+  // Exchange buffer number `slot`, at least `bytes` long (the same request on every rank;
+  // collective), for all-reduces in place.  With NCCL's symmetric-memory support (ncclMemAlloc +
+  // ncclCommWindowRegister, NCCL_WIN_COLL_SYMMETRIC) the library then uses its low-latency NVLink
+  // kernels on it; without it (older NCCL, no NVLink fabric, PDLP_B200_NCCL_SYMMETRIC=0) this is
+  // plain device memory and the call is the usual one.  Buffers stay with the cached communicator
+  // and are reused by later solves (registration costs ~0.1 s).
+  double* ExchangeBufferFor(int slot, size_t bytes) {
+    if (cached_->buffers.size() <= static_cast<size_t>(slot)) cached_->buffers.resize(slot + 1);
+    ExchangeBuffer& e = cached_->buffers[slot];
+    if (e.ptr != nullptr && e.bytes >= bytes) {
+      symmetric_buffers_ += e.registered ? 1 : 0;
+      return static_cast<double*>(e.ptr);
+    }
+    if (e.ptr != nullptr) {
+      if (cached_->users > 1) throw std::runtime_error("pdlp_b200: a larger sharded problem cannot be created while another one is alive on the same communicator");
+      CommCache::FreeBuffer(comm_, e);
+    }
     NcclApi& api = NcclApi::Get();
     const char* env = std::getenv("PDLP_B200_NCCL_SYMMETRIC");
-    const bool wanted = world_ > 1 && api.has_symmetric() && !(env != nullptr && env[0] == '0');
+    const bool wanted = api.has_symmetric() && !(env != nullptr && env[0] == '0');
     if (wanted && api.MemAlloc(&e.ptr, bytes) == ncclSuccess) {
       e.nccl_memory = true;
-      if (api.CommWindowRegister(comm_, e.ptr, bytes, &e.window, NCCL_WIN_COLL_SYMMETRIC) == ncclSuccess && e.window != nullptr) {
-        e.registered = true;
-        ++symmetric_buffers_;
-      }
+      e.registered = api.CommWindowRegister(comm_, e.ptr, bytes, &e.window, NCCL_WIN_COLL_SYMMETRIC) == ncclSuccess && e.window != nullptr;
     } else {
       e.ptr = nullptr;
-      cudaError_t err = cudaMalloc(&e.ptr, bytes);
+      const cudaError_t err = cudaMalloc(&e.ptr, bytes);
       if (err != cudaSuccess) throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(err) + " allocating an exchange buffer");
     }
+    e.bytes = bytes;
     cudaMemset(e.ptr, 0, bytes);
-    exchange_.push_back(e);
+    symmetric_buffers_ += e.registered ? 1 : 0;
     return static_cast<double*>(e.ptr);
   }
   int symmetric_buffers() const { return symmetric_buffers_; }
 
-  void Destroy() {  // the communicator stays in the cache
-    for (Exchange& e : exchange_) {
-      if (e.registered) NcclApi::Get().CommWindowDeregister(comm_, e.window);
-      if (e.nccl_memory) NcclApi::Get().MemFree(e.ptr);
-      else if (e.ptr != nullptr) cudaFree(e.ptr);
-    }
-    exchange_.clear();
+  void Destroy() {  // the communicator and its exchange buffers stay in the cache
     symmetric_buffers_ = 0;
+    if (cached_ != nullptr) --cached_->users;
+    cached_ = nullptr;
     comm_ = nullptr;
     world_ = 1;
     rank_ = 0;
@@ -179,8 +207,7 @@ class Comm {
   void Check(ncclResult_t r, const char* what) {
     if (r != ncclSuccess) throw std::runtime_error(std::string("pdlp_b200: ") + what + " failed: " + NcclApi::Get().GetErrorString(r));
   }
-  struct Exchange { void* ptr = nullptr; ncclWindow_t window = nullptr; bool nccl_memory = false, registered = false; };
-  std::vector<Exchange> exchange_;
+  CachedComm* cached_ = nullptr;
   int symmetric_buffers_ = 0;
   int rank_ = 0, world_ = 1;
   ncclComm_t comm_ = nullptr;

@@ -71,8 +71,8 @@ PreprocessSolver::PreprocessSolver(const QpView& qp, const PrimalDualHybridGradi
     // Exchange buffers have the same size on every rank (NCCL symmetric registration needs that).
     double most_rows = static_cast<double>(qp.m);
     AgreeOnMax(&most_rows, 1);
-    ws_.exchange_rows = comm_.AllocateExchangeBuffer(static_cast<size_t>(most_rows) * sizeof(double));
-    ws_.exchange_sums = comm_.AllocateExchangeBuffer(16 * sizeof(double));
+    ws_.exchange_rows = comm_.ExchangeBufferFor(0, static_cast<size_t>(most_rows) * sizeof(double));
+    ws_.exchange_sums = comm_.ExchangeBufferFor(1, 16 * sizeof(double));
   }
   problem_.n = qp.n;
   problem_.m = qp.m;
