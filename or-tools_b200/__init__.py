@@ -194,6 +194,15 @@ from ._api import (  # noqa: E402
     validate_params,
     validate_quadratic_program_dimensions,
 )
+from . import mp_model  # noqa: E402
+from .mp_model import (  # noqa: E402
+    MPModelProto,
+    MPModelRequest,
+    MPSolutionResponse,
+    pdlp_solve_proto,
+    qp_from_mpmodel_proto,
+    qp_to_mpmodel_proto,
+)
 from .sharding import (  # noqa: E402
     ColumnShard,
     RowSharing,

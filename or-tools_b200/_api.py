@@ -240,9 +240,10 @@ def primal_dual_hybrid_gradient(qp, params, initial_solution=None, interrupt_sol
             x0 = np.zeros(1)
         if y0.size == 0:
             y0 = np.zeros(1)
-    primal = np.zeros(max(n, 1))
-    dual = np.zeros(max(m, 1))
-    reduced = np.zeros(max(n, 1))
+    # Filled by the library straight from the device (no zero-fill, no copies on the way out).
+    primal = np.empty(max(n, 1))
+    dual = np.empty(max(m, 1))
+    reduced = np.empty(max(n, 1))
     has_solution = ctypes.c_int(0)
     log_ptr = ctypes.c_void_p()
     log_len = ctypes.c_size_t(0)
@@ -273,9 +274,9 @@ def primal_dual_hybrid_gradient(qp, params, initial_solution=None, interrupt_sol
         raise cb_error[0]
     result.solve_log.ParseFromString(_take_bytes(log_ptr, log_len.value))
     if has_solution.value:
-        result.primal_solution = primal[:n].copy()
-        result.dual_solution = dual[:m].copy()
-        result.reduced_costs = reduced[:n].copy()
+        result.primal_solution = primal[:n]
+        result.dual_solution = dual[:m]
+        result.reduced_costs = reduced[:n]
     _last_counters.clear()
     _last_counters.update(
         kernel_launches=counters.kernel_launches, trial_steps=counters.trial_steps, setup_seconds=counters.setup_seconds,

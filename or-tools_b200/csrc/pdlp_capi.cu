@@ -1,8 +1,11 @@
 // The C++ entry points (primal_dual_hybrid_gradient.h) and the C ABI (include/pdlp_b200.h).
 //   follows ortools/pdlp/primal_dual_hybrid_gradient.cc:2778-2831 (entry checks),
 //           ortools/pdlp/quadratic_program.cc:37-90 (dimension / bound validation).
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <thread>
+#include <vector>
 
 #include "pdlp_b200.h"
 #include "pdlp_driver.h"
@@ -36,21 +39,49 @@ std::string ValidateQuadraticProgramDimensions(const QuadraticProgram& qp) {  //
 
 namespace {
 
-bool BoundsAreValid(const double* lb, const double* ub, int64_t count) {
-  for (int64_t i = 0; i < count; ++i) if (!(lb[i] <= ub[i])) return false;
+// Runs pred over [0, count) in slices on several host threads (the data checks scan every bound
+// and diagonal entry once: 1 GB of reads on the 1e8-nonzero LP).  True iff every slice is true.
+template <class SlicePred>
+bool AllSlices(int64_t count, SlicePred pred) {
+  constexpr int64_t kSerialBelow = int64_t{1} << 20;
+  const unsigned hw = std::thread::hardware_concurrency();
+  const int threads = count < kSerialBelow ? 1 : static_cast<int>(std::max(1u, std::min(8u, hw / 2)));
+  if (threads == 1) return pred(int64_t{0}, count);
+  std::vector<char> ok(threads, 1);
+  std::vector<std::thread> pool;
+  const int64_t per = (count + threads - 1) / threads;
+  for (int t = 0; t < threads; ++t) {
+    pool.emplace_back([&, t]() {
+      const int64_t lo = std::min<int64_t>(count, t * per), hi = std::min<int64_t>(count, lo + per);
+      ok[t] = pred(lo, hi) ? 1 : 0;
+    });
+  }
+  for (std::thread& th : pool) th.join();
+  for (char c : ok) if (!c) return false;
   return true;
+}
+
+bool BoundsAreValid(const double* lb, const double* ub, int64_t count) {
+  return AllSlices(count, [&](int64_t lo, int64_t hi) {
+    for (int64_t i = lo; i < hi; ++i) if (!(lb[i] <= ub[i])) return false;
+    return true;
+  });
 }
 
 // The checks of pdhg.cc:2787-2826 that need the data (not the dimensions), then the solve.
 SolverResult SolveView(const QpView& qp, const PrimalDualHybridGradientParams& params, const double* x0, const double* y0,
-                       const InterruptFlag* interrupt, IterationCallback callback) {
+                       const InterruptFlag* interrupt, IterationCallback callback, SolutionSink* sink = nullptr) {
   // Data checks in the reference's order; the first that fails wins (smallest code).
   auto data_error = [&]() -> int {
     if (!BoundsAreValid(qp.clb, qp.cub, qp.m) || !BoundsAreValid(qp.vlb, qp.vub, qp.n)) return 3;
     if (qp.objective_scaling_factor == 0) return 2;
-    if (qp.q != nullptr)
-      for (int64_t j = 0; j < qp.n; ++j)
-        if (qp.q[j] < 0.0) return 1;
+    if (qp.q != nullptr) {
+      const bool convex = AllSlices(qp.n, [&](int64_t lo, int64_t hi) {
+        for (int64_t j = lo; j < hi; ++j) if (qp.q[j] < 0.0) return false;
+        return true;
+      });
+      if (!convex) return 1;
+    }
     return 0;
   };
   auto describe = [](int code) {
@@ -69,6 +100,7 @@ SolverResult SolveView(const QpView& qp, const PrimalDualHybridGradientParams& p
   WallTimer upload;
   upload.Start();
   PreprocessSolver solver(qp, params);
+  solver.set_solution_sink(sink);
   // Sharded: a rank whose block is fine must fail with the rank whose block is not.
   if (qp.world > 1 && (code = solver.AgreeOnCode(code)) != 0) return describe(code);
   const double upload_seconds = upload.Get();
@@ -296,6 +328,8 @@ pdlp_b200_status pdlp_b200_solve_sharded(const pdlp_b200_problem* problem, const
     if (!ParseParams(params_bytes, params_len, &params)) return Fail(PDLP_B200_BAD_ARGUMENT, "params is not a serialized PrimalDualHybridGradientParams");
     *has_solution = 0;
     SolverResult result;
+    SolutionSink sink;
+    sink.primal = primal; sink.dual = dual; sink.reduced_costs = reduced;
     const std::string perr = ValidatePrimalDualHybridGradientParams(params);
     if (!perr.empty()) {
       result = ErrorSolverResult(TERMINATION_REASON_INVALID_PARAMETER, perr);
@@ -315,17 +349,13 @@ pdlp_b200_status pdlp_b200_solve_sharded(const pdlp_b200_problem* problem, const
       static const double kEmpty = 0.0;
       const bool warm = x0 != nullptr || y0 != nullptr;
       result = SolveView(view, params, warm ? (x0 ? x0 : &kEmpty) : nullptr, warm ? (y0 ? y0 : &kEmpty) : nullptr,
-                         interrupt != nullptr ? &flag : nullptr, std::move(cb));
+                         interrupt != nullptr ? &flag : nullptr, std::move(cb), &sink);
     }
-    if (static_cast<int64_t>(result.primal_solution.size()) == problem->num_variables &&
-        static_cast<int64_t>(result.dual_solution.size()) == problem->num_constraints &&
-        result.solve_log.termination_reason != TERMINATION_REASON_INVALID_PROBLEM &&
+    // The solver wrote the solution straight into primal / dual / reduced (SolutionSink).
+    if (sink.filled && result.solve_log.termination_reason != TERMINATION_REASON_INVALID_PROBLEM &&
         result.solve_log.termination_reason != TERMINATION_REASON_INVALID_PARAMETER &&
         result.solve_log.termination_reason != TERMINATION_REASON_INVALID_INITIAL_SOLUTION) {
       *has_solution = 1;
-      if (primal != nullptr) std::copy(result.primal_solution.begin(), result.primal_solution.end(), primal);
-      if (dual != nullptr) std::copy(result.dual_solution.begin(), result.dual_solution.end(), dual);
-      if (reduced != nullptr) std::copy(result.reduced_costs.begin(), result.reduced_costs.end(), reduced);
     }
     const std::string bytes = Serialize(result.solve_log);
     *solve_log = DupBytes(bytes);

@@ -24,6 +24,8 @@
 #include <type_traits>
 #include <utility>
 
+#include "pdlp_stager.h"
+
 namespace pdlp_b200 {
 
 #define PDLP_CUDA_CHECK(expr)                                                              \
@@ -62,11 +64,17 @@ class DeviceArray {
   }
   T* get() const { return p_; }
   size_t size() const { return n_; }
+  // Large arrays travel through the multi-threaded pinned stager (pdlp_stager.h); small ones and
+  // the fallback through a plain stream-ordered copy.
   void Upload(const T* host, size_t n, cudaStream_t s) {
-    if (n > 0) PDLP_CUDA_CHECK(cudaMemcpyAsync(p_, host, n * sizeof(T), cudaMemcpyHostToDevice, s));
+    if (n == 0) return;
+    if (n * sizeof(T) >= HostStager::kMinBytes && HostStager::Get().Upload(p_, host, n * sizeof(T), s)) return;
+    PDLP_CUDA_CHECK(cudaMemcpyAsync(p_, host, n * sizeof(T), cudaMemcpyHostToDevice, s));
   }
   void Download(T* host, size_t n, cudaStream_t s) const {
-    if (n > 0) PDLP_CUDA_CHECK(cudaMemcpyAsync(host, p_, n * sizeof(T), cudaMemcpyDeviceToHost, s));
+    if (n == 0) return;
+    if (n * sizeof(T) >= HostStager::kMinBytes && HostStager::Get().Download(host, p_, n * sizeof(T), s)) return;
+    PDLP_CUDA_CHECK(cudaMemcpyAsync(host, p_, n * sizeof(T), cudaMemcpyDeviceToHost, s));
   }
   void Zero(cudaStream_t s) {
     if (n_ > 0) PDLP_CUDA_CHECK(cudaMemsetAsync(p_, 0, n_ * sizeof(T), s));

@@ -40,6 +40,16 @@ struct QpView {
 
 using IterationCallback = std::function<void(const IterationCallbackInfo&)>;
 
+// Caller-owned destinations for the solution (the C ABI's output arrays): when given, the three
+// vectors are copied from the device straight into them and SolverResult's own vectors stay empty,
+// instead of device -> SolverResult -> caller.  A null member is skipped.
+struct SolutionSink {
+  double* primal = nullptr;
+  double* dual = nullptr;
+  double* reduced_costs = nullptr;
+  bool filled = false;
+};
+
 class WallTimer {
  public:
   void Start() { running_ = true; t0_ = Clock::now(); }
@@ -65,6 +75,7 @@ class PreprocessSolver {
   ~PreprocessSolver();
   SolverResult PreprocessAndSolve(const PrimalDualHybridGradientParams& params, const double* x0, const double* y0,
                                   const InterruptFlag* interrupt, IterationCallback callback);
+  void set_solution_sink(SolutionSink* sink) { sink_ = sink; }
 
   // pdhg.cc:1434-1518.  Points are device pointers; avg / delta may be null.
   std::optional<TerminationReasonAndPointType> UpdateIterationStatsAndCheckTermination(
@@ -102,6 +113,7 @@ class PreprocessSolver {
   QuadraticProgramBoundNorms original_bound_norms_;
   IterationCallback callback_;
   std::vector<int32_t> seeds_;
+  SolutionSink* sink_ = nullptr;
 };
 
 enum class InnerStepOutcome { kSuccessful, kForceNumericalTermination };

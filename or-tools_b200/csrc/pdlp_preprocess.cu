@@ -439,13 +439,24 @@ SolverResult PreprocessSolver::ConstructOriginalSolverResult(const PrimalDualHyb
   MultiplyInPlace(ws_, out_x, p.col_scale.get(), p.n);
   MultiplyInPlace(ws_, out_y, p.row_scale.get(), p.m);
   DivideInPlace(ws_, out_rc, p.col_scale.get(), p.n);
-  result.primal_solution.resize(p.n);
-  result.dual_solution.resize(p.m);
-  result.reduced_costs.resize(p.n);
-  if (p.n > 0) PDLP_CUDA_CHECK(cudaMemcpyAsync(result.primal_solution.data(), out_x, p.n * sizeof(double), cudaMemcpyDeviceToHost, ws_.stream));
-  if (p.n > 0) PDLP_CUDA_CHECK(cudaMemcpyAsync(result.reduced_costs.data(), out_rc, p.n * sizeof(double), cudaMemcpyDeviceToHost, ws_.stream));
-  if (p.m > 0) PDLP_CUDA_CHECK(cudaMemcpyAsync(result.dual_solution.data(), out_y, p.m * sizeof(double), cudaMemcpyDeviceToHost, ws_.stream));
+  // Straight into the caller's arrays when there is a sink (C ABI), else into the result's vectors.
+  auto download = [&](const double* device, int64_t count, std::vector<double>* own, double* sink, bool use_sink) {
+    double* host = sink;
+    if (!use_sink) {
+      own->resize(count);
+      host = own->data();
+    }
+    if (count == 0 || host == nullptr) return;
+    const size_t bytes = static_cast<size_t>(count) * sizeof(double);
+    if (bytes >= HostStager::kMinBytes && HostStager::Get().Download(host, device, bytes, ws_.stream)) return;
+    PDLP_CUDA_CHECK(cudaMemcpyAsync(host, device, bytes, cudaMemcpyDeviceToHost, ws_.stream));
+  };
+  const bool use_sink = sink_ != nullptr;
+  download(out_x, p.n, &result.primal_solution, use_sink ? sink_->primal : nullptr, use_sink);
+  download(out_rc, p.n, &result.reduced_costs, use_sink ? sink_->reduced_costs : nullptr, use_sink);
+  download(out_y, p.m, &result.dual_solution, use_sink ? sink_->dual : nullptr, use_sink);
   ws_.Sync();
+  if (use_sink) sink_->filled = true;
   IterationType type = IterationType::kNormalTermination;
   if (log.solution_type == POINT_TYPE_FEASIBILITY_POLISHING_SOLUTION) type = IterationType::kFeasibilityPolishingTermination;
   else if (log.solution_type == POINT_TYPE_PRESOLVER_SOLUTION) type = IterationType::kPresolveTermination;
