@@ -203,6 +203,8 @@ from .mp_model import (  # noqa: E402
     qp_from_mpmodel_proto,
     qp_to_mpmodel_proto,
 )
+from . import qp_io  # noqa: E402
+from .qp_io import read_quadratic_program_or_die  # noqa: E402
 from .sharding import (  # noqa: E402
     ColumnShard,
     RowSharing,

@@ -73,7 +73,7 @@ struct StepState {
   int accepted_last;         // last trial accepted (consumed by the averaging kernel)
   int avg_num_terms;
   int first_mp_add_pending;  // Malitsky-Pock: old x must be added to the empty average
-  int reserved;
+  int avg_pending;           // adaptive / constant rule: the accepted iterate has not entered the average yet (applied by the next K1 / K2 or the batch-end flush)
   long long total_trials;
   double step_size, primal_weight;
   double avg_weight_sum, avg_weight_sum_dual;  // differ only under Malitsky-Pock (:2260-2272)

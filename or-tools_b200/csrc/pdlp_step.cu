@@ -10,6 +10,10 @@
 //   K3 kty_step      CSC cols: (K^T y')_j, fused with dx_j (K^T y' - K^T y)_j
 //   K4 decide        movement / nonlinearity / accept / next step size, on one CTA
 //   K5 average       on accept: avg += w/(W+w) (z - avg) for x and y
+// Under the adaptive and constant rules K5 is folded into the NEXT trial's K1 and K2, which read the
+// accepted x and y anyway (8 (n + m) bytes and one launch less per step): the decision kernel marks
+// the update pending, K1 / K2 apply it with the same arithmetic, and a flush at the end of every
+// enqueued batch applies what is still pending, so the host always sees complete averages.
 // All kernels read their scalars (step size, primal weight, which buffer is current)
 // from the device-resident StepState and exit early once the state says stop, so the
 // host can enqueue a whole major iteration's worth of trials and sync once.
@@ -36,11 +40,15 @@ struct PrimalStepOp : OneSum {
   const double* lb; const double* ub;
   double* xbar;
   int write_xbar;                    // Malitsky-Pock extrapolates per dual trial instead
+  double* avg_x;                     // deferred averaging (null: K5 does it)
   // resolved by Begin()
   const double* x; double* xn; const double* kty; double tau;
+  int avg_pending; double avg_ratio;
   __device__ bool Begin() {
     if (st->active == 0) return false;
     const int cur = st->cur;
+    avg_pending = avg_x != nullptr ? st->avg_pending : 0;
+    avg_ratio = st->avg_ratio;
     tau = (st->mp_tau > 0.0) ? st->mp_tau : st->step_size / st->primal_weight;
     x = cur ? x1 : x0;
     xn = cur ? x0 : x1;
@@ -49,6 +57,10 @@ struct PrimalStepOp : OneSum {
   }
   __device__ void Apply(int64_t j, Slots<1>& acc) const {
     const double xj = x[j];
+    if (avg_pending) {  // ShardedWeightedAverage::Add of the iterate accepted by the previous trial (sou.cc:54-66)
+      const double a = avg_x[j];
+      avg_x[j] = a + avg_ratio * (xj - a);
+    }
     double t = xj - tau * (c[j] - kty[j]);
     if (q != nullptr) t = t / (tau * q[j] + 1.0);
     const double v = fmax(fmin(t, ub[j]), lb[j]);
@@ -85,10 +97,14 @@ struct DualStepOp : OneSum {
   double* y0; double* y1;
   const double* clb; const double* cub;
   int skip_below;  // rows below it are shared with other ranks and counted on rank 0 only
+  double* avg_y;   // deferred averaging (null: K5 does it)
   const double* y; double* yn; double sigma;
+  int avg_pending; double avg_ratio;
   __device__ bool Begin() {
     if (st->active == 0) return false;
     const int cur = st->cur;
+    avg_pending = avg_y != nullptr ? st->avg_pending : 0;
+    avg_ratio = st->avg_ratio_dual;
     sigma = (st->mp_tau > 0.0) ? (st->primal_weight * st->primal_weight) * st->mp_new_tau : st->step_size * st->primal_weight;
     y = cur ? y1 : y0;
     yn = cur ? y0 : y1;
@@ -102,10 +118,11 @@ struct DualStepOp : OneSum {
   __device__ double RowInit() const { return 0.0; }
   __device__ double RowAdd(double acc, double staged, int) const { return acc + staged; }
   __device__ double RowMerge(double a, double b) const { return a + b; }
-  struct Pre { double y, lb, ub; };
-  __device__ Pre RowPrefetch(int i) const { return Pre{y[i], clb[i], cub[i]}; }
+  struct Pre { double y, lb, ub, avg; };
+  __device__ Pre RowPrefetch(int i) const { return Pre{y[i], clb[i], cub[i], avg_pending ? avg_y[i] : 0.0}; }
   __device__ void RowFinish(int i, double kx, const Pre& pre, Slots<1>& red) const {
     const double yi = pre.y;
+    if (avg_pending) avg_y[i] = pre.avg + avg_ratio * (yi - pre.avg);
     const double temp = yi - sigma * kx;
     const double v = fmax(fmin(0.0, temp + sigma * pre.ub), temp + sigma * pre.lb);
     yn[i] = v;
@@ -159,7 +176,8 @@ __global__ void __launch_bounds__(kBlock) decide_adaptive_kernel(StepState* st, 
                                                                 int constant_step) {
   __shared__ double buf[kBlock];
   if (st->active == 0) {
-    if (threadIdx.x == 0) { st->accepted_last = 0; st->reset_average = 0; }
+    // avg_pending and reset_average stay as they are: the batch-end flush consumes them.
+    if (threadIdx.x == 0) st->accepted_last = 0;
     return;
   }
   const double dx2 = ReducePartialsSum(p1, g1, 1, 0, buf);
@@ -169,6 +187,7 @@ __global__ void __launch_bounds__(kBlock) decide_adaptive_kernel(StepState* st, 
   StepState s = *st;
   s.total_trials += 1;
   s.accepted_last = 0;
+  s.avg_pending = 0;  // this trial's K1 / K2 applied the previous accepted iterate
   const double movement = (0.5 * s.primal_weight) * dx2 + (0.5 / s.primal_weight) * dy2;
   const double nonlinearity = -dot;
   s.last_movement = movement;
@@ -191,6 +210,7 @@ __global__ void __launch_bounds__(kBlock) decide_adaptive_kernel(StepState* st, 
     s.avg_weight_sum_dual += s.step_size;
     s.avg_num_terms += 1;
     s.accepted_last = 1;
+    s.avg_pending = 1;
     s.iterations_completed += 1;
   } else {
     const double limit = nonlinearity > 0.0 ? movement / nonlinearity : INFINITY;
@@ -204,6 +224,7 @@ __global__ void __launch_bounds__(kBlock) decide_adaptive_kernel(StepState* st, 
       s.avg_weight_sum_dual += s.step_size;
       s.avg_num_terms += 1;
       s.accepted_last = 1;
+      s.avg_pending = 1;
     }
     const double first = isinf(limit) ? limit : (1.0 - pow(total_steps_attempted + 1.0, -s.reduction_exponent)) * limit;
     const double second = (1.0 + pow(total_steps_attempted + 1.0, -s.growth_exponent)) * s.step_size;
@@ -237,12 +258,13 @@ struct AverageOp : NoSlots {
   const StepState* st;
   const double* x0; const double* x1; const double* y0; const double* y1;
   double* avg_x; double* avg_y; int64_t n;
+  int deferred;  // 1: the batch-end flush of the adaptive / constant rules (keyed on avg_pending)
   const double* xs; const double* xold; const double* ys;
   double ratio_x, ratio_y, ratio_old_x; int reset, first_mp;
   __device__ bool Begin() {
     reset = st->reset_average;
     first_mp = st->first_mp_add_pending;
-    if (st->accepted_last == 0 && reset == 0) return false;
+    if ((deferred ? st->avg_pending : st->accepted_last) == 0 && reset == 0) return false;
     const int cur = st->cur;
     xs = cur ? x1 : x0;
     xold = cur ? x0 : x1;
@@ -269,6 +291,12 @@ struct AverageOp : NoSlots {
     }
   }
 };
+
+// After the batch-end flush: nothing is pending any more.
+__global__ void finish_average_kernel(StepState* st) {
+  st->avg_pending = 0;
+  st->reset_average = 0;
+}
 
 // K4 for Malitsky-Pock (:2237-2291).
 __global__ void __launch_bounds__(kBlock) decide_mp_kernel(StepState* st, const double* p1, int g1, const double* p2, int g2, const double* p3, int g3) {
@@ -371,10 +399,12 @@ void EnqueueAdaptiveTrials(Workspace& ws, const DeviceProblem& p, Iterate& it, i
   StepState* st = it.state.get();
   const SparseRows& csr = p.K.by_row;
   const SparseRows& csc = p.K.by_col;
-  PrimalStepOp k1{{}, st, it.x[0].get(), it.x[1].get(), it.kty[0].get(), it.kty[1].get(), p.c.get(), p.q_or_null(), p.vlb.get(), p.vub.get(), it.xbar.get(), 1};
-  DualStepOp k2{{}, st, csr.val.get(), csr.idx.get(), it.xbar.get(), it.y[0].get(), it.y[1].get(), p.clb.get(), p.cub.get(), static_cast<int>(ws.dual_skip_below)};
+  PrimalStepOp k1{{}, st, it.x[0].get(), it.x[1].get(), it.kty[0].get(), it.kty[1].get(), p.c.get(), p.q_or_null(), p.vlb.get(), p.vub.get(), it.xbar.get(), 1,
+                  it.avg_x.get()};
+  DualStepOp k2{{}, st, csr.val.get(), csr.idx.get(), it.xbar.get(), it.y[0].get(), it.y[1].get(), p.clb.get(), p.cub.get(), static_cast<int>(ws.dual_skip_below),
+                it.avg_y.get()};
   KtyStepOp k3{st, csc.val.get(), csc.idx.get(), it.y[0].get(), it.y[1].get(), it.x[0].get(), it.x[1].get(), it.kty[0].get(), it.kty[1].get()};
-  AverageOp k5{{}, st, it.x[0].get(), it.x[1].get(), it.y[0].get(), it.y[1].get(), it.avg_x.get(), it.avg_y.get(), p.n};
+  AverageOp flush{{}, st, it.x[0].get(), it.x[1].get(), it.y[0].get(), it.y[1].get(), it.avg_x.get(), it.avg_y.get(), p.n, 1};
   auto mark = [&]() {
     if (ws.profile == nullptr) return;
     cudaEvent_t e;
@@ -394,8 +424,13 @@ void EnqueueAdaptiveTrials(Workspace& ws, const DeviceProblem& p, Iterate& it, i
     decide_adaptive_kernel<<<1, kBlock, 0, ws.stream>>>(st, sums.p1, sums.g1, sums.p2, sums.g2, sums.p3, sums.g3, constant_step ? 1 : 0);
     ++ws.launches;
     mark();
-    EnqueueMap(ws, k5, p.n + p.m, 0);
-    mark();
+    mark();  // (the averaging slot of the per-kernel profile: folded into the next K1 / K2)
+  }
+  // The last accepted iterate (or a requested reset) enters the average here.
+  if (trials > 0) {
+    EnqueueMap(ws, flush, p.n + p.m, 0);
+    finish_average_kernel<<<1, 1, 0, ws.stream>>>(st);
+    ++ws.launches;
   }
   PDLP_CUDA_CHECK(cudaGetLastError());
 }
@@ -404,11 +439,12 @@ void EnqueueMalitskyPockTrials(Workspace& ws, const DeviceProblem& p, Iterate& i
   StepState* st = it.state.get();
   const SparseRows& csr = p.K.by_row;
   const SparseRows& csc = p.K.by_col;
-  PrimalStepOp k1{{}, st, it.x[0].get(), it.x[1].get(), it.kty[0].get(), it.kty[1].get(), p.c.get(), p.q_or_null(), p.vlb.get(), p.vub.get(), it.xbar.get(), 0};
+  PrimalStepOp k1{{}, st, it.x[0].get(), it.x[1].get(), it.kty[0].get(), it.kty[1].get(), p.c.get(), p.q_or_null(), p.vlb.get(), p.vub.get(), it.xbar.get(), 0, nullptr};
   ExtrapolateOp kx{{}, st, it.x[0].get(), it.x[1].get(), it.xbar.get()};
-  DualStepOp k2{{}, st, csr.val.get(), csr.idx.get(), it.xbar.get(), it.y[0].get(), it.y[1].get(), p.clb.get(), p.cub.get(), static_cast<int>(ws.dual_skip_below)};
+  DualStepOp k2{{}, st, csr.val.get(), csr.idx.get(), it.xbar.get(), it.y[0].get(), it.y[1].get(), p.clb.get(), p.cub.get(), static_cast<int>(ws.dual_skip_below),
+                nullptr};
   KtyStepOp k3{st, csc.val.get(), csc.idx.get(), it.y[0].get(), it.y[1].get(), it.x[0].get(), it.x[1].get(), it.kty[0].get(), it.kty[1].get()};
-  AverageOp k5{{}, st, it.x[0].get(), it.x[1].get(), it.y[0].get(), it.y[1].get(), it.avg_x.get(), it.avg_y.get(), p.n};
+  AverageOp k5{{}, st, it.x[0].get(), it.x[1].get(), it.y[0].get(), it.y[1].get(), it.avg_x.get(), it.avg_y.get(), p.n, 0};
   for (int t = 0; t < trials; ++t) {
     mp_begin_kernel<<<1, 1, 0, ws.stream>>>(st);
     ++ws.launches;
