@@ -171,6 +171,16 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def recorded_traffic(workload, kernel):
+    """DRAM bytes per launch of `kernel` from the committed ncu capture (profiles/traffic.json), or None."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(path) as f:
+            return json.load(f).get(workload, {}).get(kernel)
+    except (OSError, ValueError):
+        return None
+
+
 def cpu_reference_leg(qp, name, threads, iterations):
     """Times `iterations` PDHG iterations of the CPU oracle (threaded Sharder structure,
     num_shards = 4 x threads) on the workload; returns iterations / loop second."""
@@ -351,7 +361,9 @@ def main():
             "nvlink": {"allreduce_bytes_per_step_per_rank": 8 * num_shared + 8 * 4, "collectives_per_step": 2, "shared_constraints": num_shared,
                        "constraints_on_rank0": m} if sharded else None,
             "roofline": {"bound": "hbm", "achieved": step_gbs, "peak": peak * (world if sharded else 1), "unit": "GB/s",
-                         "frac": step_gbs / (peak * (world if sharded else 1)), "traffic": None,
+                         "frac": step_gbs / (peak * (world if sharded else 1)),
+                         "traffic": None if sharded or args.scale != 1.0 else recorded_traffic(name, dominant["kernel"]),
+                         "traffic_note": "dram bytes read + written per launch of the dominant kernel, from the committed ncu --set full capture (profiles/traffic.json); compare with that kernel's algorithmic_bytes",
                          "peak_kind": peak_kind + (f" x {world} GPUs" if sharded else ""), "unit_of_work": "one PDHG trial step (4 kernels: primal step + x average, K x + dual step + y average, K^T y + step test, decision)",
                          "algorithmic_bytes_per_step": b_step_all,
                          "dominant_kernel": dominant["kernel"], "dominant_kernel_achieved": dominant["achieved_gbs"],

@@ -89,7 +89,10 @@ using DVec = DeviceArray<double>;
 
 constexpr int kBlock = 256;          // threads per CTA for every kernel here
 constexpr int kMaxSlots = 16;        // reduction slots an op may use
-constexpr int kStreamChunk = 2048;   // nonzeros staged in shared memory per work block
+#ifndef PDLP_STREAM_CHUNK
+#define PDLP_STREAM_CHUNK 2048
+#endif
+constexpr int kStreamChunk = PDLP_STREAM_CHUNK;   // nonzeros staged in shared memory per work block
 constexpr int kMaxGrid = 148 * 8;    // 148 SMs x 8 resident CTAs: persistent grid-stride launches
 
 // Reduction slot kinds.  kMax slots must only ever receive values >= 0 or be
@@ -143,7 +146,7 @@ __device__ __forceinline__ void BlockReduceAndStore(Slots<Op::kNumSlots>& acc, d
 //                                // loop control)
 //   __device__ void Apply(int64_t i, Slots<kNumSlots>& acc) const;
 template <class Op>
-__global__ void __launch_bounds__(kBlock) map_reduce_kernel(const Op op_in, int64_t count, double* partials) {
+__global__ void __launch_bounds__(kBlock, 4) map_reduce_kernel(const Op op_in, int64_t count, double* partials) {
   Slots<Op::kNumSlots> acc;
 #pragma unroll
   for (int s = 0; s < Op::kNumSlots; ++s) acc.v[s] = SlotIdentity(Op::SlotKindOf(s));
@@ -173,8 +176,8 @@ __global__ void __launch_bounds__(kBlock) map_reduce_kernel(const Op op_in, int6
 //   * the epilogue operands of each thread's row(s) (Op::RowPrefetch) into registers, issued
 //     BEFORE the gather so that the in-order warp does not stall in front of them;
 // leaving idx (prefetched) -> gather -> barrier -> reduce from shared memory on the critical path.
-// Shared-memory products are stored with a 1-in-16 skew so that sub-warps reading rows of 16, 32,
-// 64 ... nonzeros do not collide on the same banks.
+// Shared-memory products are stored with a 1-in-8 pad so that sub-warps reading rows of 8, 16, 32,
+// 64 ... nonzeros do not collide on the same banks (see Skew below).
 //
 // Op interface (in addition to kNumSlots / SlotKindOf / Begin):
 //   __device__ double Load(int64_t k) const;              // value staged for nonzero k
@@ -203,8 +206,20 @@ constexpr int kMaxRowsPerBlock = 4 * kBlock;
 #define PDLP_ROWSTREAM_MIN_CTAS 4  // resident CTAs per SM the register allocation must allow
 #endif
 constexpr int kPerThread = kStreamChunk / kBlock;             // nonzeros per thread per work block
-constexpr int kStagedSize = kStreamChunk + kStreamChunk / 16;  // with the bank skew
-__device__ __forceinline__ int Skew(int k) { return k + (k >> 4); }
+constexpr int kStagedSize = kStreamChunk + kStreamChunk / 8;  // with the bank skew
+// Position of staged product k: one pad slot every 8 products (shift 3), or none (shift 31).  With
+// 8-byte products a half-warp reads 16 bank pairs; rows of 8, 16, 32, 64 ... products read by 1, 2,
+// 4, 8 ... threads each land on the same pair without the pad (8-way conflicts) and on distinct
+// pairs with it.  Rows of one odd length (3 or 5 nonzeros per column in the CSC copies of the bench
+// LPs) are conflict-free unpadded and 2-way conflicted padded, so a work block whose rows all have
+// the same odd length - told by nz == nrows * (nz / nrows), odd quotient - is staged unpadded.
+// (Measured before this rule, pad every 16: 24 % of the shared-memory wavefronts of both SpMV
+// kernels on C3 were bank conflicts, profiles/r01_ncu_rowstream_c3_v6.md.)
+__device__ __forceinline__ int Skew(int k, int shift) { return k + (k >> shift); }
+__device__ __forceinline__ int SkewShiftFor(int nz, int nrows) {
+  const int len = nz / nrows;
+  return (len * nrows == nz && (len & 1)) ? 31 : 3;
+}
 
 template <class Op, class = void>
 struct HasSplitLoad : std::false_type {};
@@ -324,6 +339,7 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
         // then the asynchronous copies of this block's values and row offsets and of the next
         // block's indices.  All of them are in flight together; the wait then covers one latency.
         const int nrows = r1 - r0;
+        const int shift = SkewShiftFor(nz, nrows);
         // Threads per row: largest power of two <= min(32, kBlock / nrows), at least 1.
         int log_t = 0;
         while (log_t < 5 && (2 << log_t) * nrows <= kBlock) ++log_t;
@@ -346,7 +362,7 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
 #pragma unroll
           for (int i = 0; i < kPerThread; ++i) {
             const int k = threadIdx.x + i * kBlock;
-            if (k < nz) CpAsync8(staged + Skew(k), op.ValueAddress(p0 + k));
+            if (k < nz) CpAsync8(staged + Skew(k, shift), op.ValueAddress(p0 + k));
           }
           for (int i = threadIdx.x; i <= nrows; i += kBlock) CpAsync4(row_raw + i, rb.row_ptr + r0 + i);
           PrefetchIndices(op, idx_buf[parity ^ 1], np0, next_nz);
@@ -355,7 +371,7 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
 #pragma unroll
           for (int i = 0; i < kPerThread; ++i) {
             const int k = threadIdx.x + i * kBlock;
-            if (k < nz) staged[Skew(k)] = op.Product(staged[Skew(k)], g[i]);
+            if (k < nz) staged[Skew(k, shift)] = op.Product(staged[Skew(k, shift)], g[i]);
           }
         } else {
           for (int i = threadIdx.x; i <= nrows; i += kBlock) CpAsync4(row_raw + i, rb.row_ptr + r0 + i);
@@ -363,7 +379,7 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
 #pragma unroll
           for (int i = 0; i < kPerThread; ++i) {
             const int k = threadIdx.x + i * kBlock;
-            if (k < nz) staged[Skew(k)] = op.Load(p0 + k);
+            if (k < nz) staged[Skew(k, shift)] = op.Load(p0 + k);
           }
           CpAsyncWaitAll();
         }
@@ -375,7 +391,7 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
             double a = op.RowInit();
             if (rr < nrows) {
               const int q1 = row_raw[rr + 1] - p0;
-              for (int q = row_raw[rr] - p0 + lane; q < q1; q += t) a = op.RowAdd(a, staged[Skew(q)], r0 + rr);
+              for (int q = row_raw[rr] - p0 + lane; q < q1; q += t) a = op.RowAdd(a, staged[Skew(q, shift)], r0 + rr);
             }
             // All 32 lanes take part in the shuffles (t divides 32).
             for (int off = t >> 1; off > 0; off >>= 1) a = op.RowMerge(a, __shfl_xor_sync(0xffffffffu, a, off));
@@ -388,7 +404,7 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
           double a = op.RowInit();
           if (rr < nrows) {
             const int q1 = row_raw[rr + 1] - p0;
-            for (int q = row_raw[rr] - p0 + lane; q < q1; q += t) a = op.RowAdd(a, staged[Skew(q)], r0 + rr);
+            for (int q = row_raw[rr] - p0 + lane; q < q1; q += t) a = op.RowAdd(a, staged[Skew(q, shift)], r0 + rr);
           }
           for (int off = t >> 1; off > 0; off >>= 1) a = op.RowMerge(a, __shfl_xor_sync(0xffffffffu, a, off));
           if (lane == 0 && rr < nrows) OpRowFinish(op, r0 + rr, a, OpRowPrefetch(op, r0 + rr), red);

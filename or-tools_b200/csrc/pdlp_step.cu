@@ -56,17 +56,20 @@ struct PrimalStepOp : OneSum {
     return true;
   }
   __device__ void Apply(int64_t j, Slots<1>& acc) const {
+    // Every load first, every store last: the stores may alias the loads as far as the compiler
+    // knows, and a store between them would split the element into two dependent memory round trips.
     const double xj = x[j];
-    if (avg_pending) {  // ShardedWeightedAverage::Add of the iterate accepted by the previous trial (sou.cc:54-66)
-      const double a = avg_x[j];
-      avg_x[j] = a + avg_ratio * (xj - a);
-    }
-    double t = xj - tau * (c[j] - kty[j]);
-    if (q != nullptr) t = t / (tau * q[j] + 1.0);
-    const double v = fmax(fmin(t, ub[j]), lb[j]);
+    const double cj = c[j], kj = kty[j], uj = ub[j], lj = lb[j];
+    const double qj = q != nullptr ? q[j] : 0.0;
+    const double aj = avg_pending ? avg_x[j] : 0.0;
+    double t = xj - tau * (cj - kj);
+    if (q != nullptr) t = t / (tau * qj + 1.0);
+    const double v = fmax(fmin(t, uj), lj);
     const double d = v - xj;
     xn[j] = v;
     if (write_xbar) xbar[j] = v + 1.0 * d;
+    // ShardedWeightedAverage::Add of the iterate accepted by the previous trial (sou.cc:54-66)
+    if (avg_pending) avg_x[j] = aj + avg_ratio * (xj - aj);
     acc.v[0] += d * d;
   }
 };
