@@ -176,8 +176,8 @@ __global__ void __launch_bounds__(kBlock, 4) map_reduce_kernel(const Op op_in, i
 //   * the epilogue operands of each thread's row(s) (Op::RowPrefetch) into registers, issued
 //     BEFORE the gather so that the in-order warp does not stall in front of them;
 // leaving idx (prefetched) -> gather -> barrier -> reduce from shared memory on the critical path.
-// Shared-memory products are stored with a 1-in-8 pad so that sub-warps reading rows of 8, 16, 32,
-// 64 ... nonzeros do not collide on the same banks (see Skew below).
+// Shared-memory products are stored with a per-block bank pad so that the threads reducing rows of
+// 8, 16, 32, 64 ... nonzeros do not collide on the same banks (see Skew below).
 //
 // Op interface (in addition to kNumSlots / SlotKindOf / Begin):
 //   __device__ double Load(int64_t k) const;              // value staged for nonzero k
@@ -206,19 +206,26 @@ constexpr int kMaxRowsPerBlock = 4 * kBlock;
 #define PDLP_ROWSTREAM_MIN_CTAS 4  // resident CTAs per SM the register allocation must allow
 #endif
 constexpr int kPerThread = kStreamChunk / kBlock;             // nonzeros per thread per work block
-constexpr int kStagedSize = kStreamChunk + kStreamChunk / 8;  // with the bank skew
-// Position of staged product k: one pad slot every 8 products (shift 3), or none (shift 31).  With
-// 8-byte products a half-warp reads 16 bank pairs; rows of 8, 16, 32, 64 ... products read by 1, 2,
-// 4, 8 ... threads each land on the same pair without the pad (8-way conflicts) and on distinct
-// pairs with it.  Rows of one odd length (3 or 5 nonzeros per column in the CSC copies of the bench
-// LPs) are conflict-free unpadded and 2-way conflicted padded, so a work block whose rows all have
-// the same odd length - told by nz == nrows * (nz / nrows), odd quotient - is staged unpadded.
-// (Measured before this rule, pad every 16: 24 % of the shared-memory wavefronts of both SpMV
-// kernels on C3 were bank conflicts, profiles/r01_ncu_rowstream_c3_v6.md.)
-__device__ __forceinline__ int Skew(int k, int shift) { return k + (k >> shift); }
-__device__ __forceinline__ int SkewShiftFor(int nz, int nrows) {
+constexpr int kStagedSize = kStreamChunk + 3 * (kStreamChunk / 16);  // with the largest bank pad
+// Position of staged product k: c pad slots after every 16 products, c = 0 .. 3 chosen per work
+// block.  With 8-byte products a half-warp touches 16 bank pairs.  The three coalesced passes over
+// the products (asynchronous copy in, multiply in place) walk 16 consecutive k that start at a multiple of 16, so a
+// pad that only falls between such groups keeps them conflict-free (a pad every 8 products does
+// not: measured +6 % on K x).  The row reduction reads T threads per row; simulated conflict
+// degrees (scripts/bank_pad_sim.py, wavefronts per 16 products, 1.0 = none):
+//   rows of one odd length (3, 5: CSC copies of the bench LPs)    c=0: 1.0   c=1: 3-5   c=2,3: 2.0
+//   rows of one length that is a multiple of 16 (16, 32, 64)       c=0: 2-8   c=1: 2.0   c=2: 1.0   c=3: 2.0
+//   rows of one other even length (2, 4, 8, 10, 12, 24)            c=0: 2-8   c=1: 1-5   c=2: 2-3   c=3: 1.0-2.0
+//   irregular rows (Poisson lengths around 10 or 16)               c=0: 3.6   c=1: 3.5   c=2: 3.1-3.6   c=3: 3.0-3.6
+// A block is "of one length" when nz == nrows * (nz / nrows).  (Before this rule, c = 1 everywhere:
+// 24 % of the shared-memory wavefronts of both SpMV kernels on C3 were bank conflicts,
+// profiles/r01_ncu_step_kernels_c3_v6.md.)
+__device__ __forceinline__ int Skew(int k, int pad) { return k + pad * (k >> 4); }
+__device__ __forceinline__ int BankPadFor(int nz, int nrows) {
   const int len = nz / nrows;
-  return (len * nrows == nz && (len & 1)) ? 31 : 3;
+  if (len * nrows != nz) return 3;
+  if (len & 1) return 0;
+  return (len & 15) == 0 ? 2 : 3;
 }
 
 template <class Op, class = void>
@@ -279,7 +286,9 @@ template <class Op>
 __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_kernel(const Op op_in, RowBlocks rb, double* partials) {
   __shared__ double staged[kStagedSize];
   __shared__ int row_raw[kMaxRowsPerBlock + 1];  // row_ptr[r0 ...] of the current work block
-  __shared__ int idx_buf[2][HasSplitLoad<Op>::value ? kStreamChunk : 1];
+  // One buffer is enough for "this block's indices" and "the next block's indices": a thread copies
+  // the next block's indices into exactly the positions it has already read this block's from.
+  __shared__ int idx_buf[HasSplitLoad<Op>::value ? kStreamChunk : 1];
   __shared__ double long_row_buf[kBlock / 32];
   using Pre = typename PreOf<Op>::type;
   constexpr int kPreRows = sizeof(Pre) > 16 ? 2 : 4;  // rows per thread whose epilogue operands are fetched before the barrier
@@ -297,8 +306,7 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
       nr0 = rb.block_start[b + stride]; nr1 = rb.block_start[b + stride + 1];
       np0 = rb.block_nz[b + stride]; np1 = rb.block_nz[b + stride + 1];
     }
-    int parity = 0;
-    PrefetchIndices(op, idx_buf[0], p0, p1 - p0);
+    PrefetchIndices(op, idx_buf, p0, p1 - p0);
     while (b < rb.num_blocks) {
       const int nz = p1 - p0;
       // Metadata two blocks ahead: in flight for a whole block before it is needed.
@@ -308,7 +316,7 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
       const int next_nz = np1 - np0;  // 0 when there is no next block
       if (nz > kStreamChunk) {
         // One long row (r1 == r0 + 1 by construction): CTA-wide strided reduce.
-        PrefetchIndices(op, idx_buf[parity ^ 1], np0, next_nz);
+        PrefetchIndices(op, idx_buf, np0, next_nz);
         const Pre pre = OpRowPrefetch(op, r0);
         double a = op.RowInit();
         for (int k = p0 + threadIdx.x; k < p1; k += kBlock) a = op.RowAdd(a, op.Load(k), r0);
@@ -331,7 +339,7 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
 #pragma unroll
           for (int i = 0; i < kPerThread; ++i) {
             const int k = threadIdx.x + i * kBlock;
-            jx[i] = k < nz ? idx_buf[parity][k] : 0;
+            jx[i] = k < nz ? idx_buf[k] : 0;
           }
         }
         // Issue order matters (warps issue in order, and ptxas places the cp.async wait directly
@@ -339,7 +347,7 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
         // then the asynchronous copies of this block's values and row offsets and of the next
         // block's indices.  All of them are in flight together; the wait then covers one latency.
         const int nrows = r1 - r0;
-        const int shift = SkewShiftFor(nz, nrows);
+        const int shift = BankPadFor(nz, nrows);
         // Threads per row: largest power of two <= min(32, kBlock / nrows), at least 1.
         int log_t = 0;
         while (log_t < 5 && (2 << log_t) * nrows <= kBlock) ++log_t;
@@ -365,7 +373,7 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
             if (k < nz) CpAsync8(staged + Skew(k, shift), op.ValueAddress(p0 + k));
           }
           for (int i = threadIdx.x; i <= nrows; i += kBlock) CpAsync4(row_raw + i, rb.row_ptr + r0 + i);
-          PrefetchIndices(op, idx_buf[parity ^ 1], np0, next_nz);
+          PrefetchIndices(op, idx_buf, np0, next_nz);
           CpAsyncWaitAll();
           // Each thread multiplies its own positions in place.
 #pragma unroll
@@ -411,7 +419,6 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
         }
         __syncthreads();
       }
-      parity ^= 1;
       b += stride;
       r0 = nr0; r1 = nr1; p0 = np0; p1 = np1;
       nr0 = fr0; nr1 = fr1; np0 = fp0; np1 = fp1;

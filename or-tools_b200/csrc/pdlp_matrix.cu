@@ -6,6 +6,10 @@
 
 #include <cub/device/device_radix_sort.cuh>
 
+#include <cstdlib>
+#include <future>
+#include <vector>
+
 namespace pdlp_b200 {
 
 namespace {
@@ -60,43 +64,56 @@ __global__ void row_offsets_kernel(const int* sorted_rows, int64_t nnz, int m, i
   }
 }
 
-void SetBlocks(SparseRows* s, const std::vector<int>& host_ptr, cudaStream_t stream) {
-  std::vector<int> blocks = PartitionRows(host_ptr.data(), s->rows, &s->max_row_nnz);
-  s->num_blocks = static_cast<int>(blocks.size()) - 1;
-  s->block_start.Resize(blocks.size());
-  s->block_start.Upload(blocks.data(), blocks.size(), stream);
-  std::vector<int> first_nz(blocks.size());
-  for (size_t b = 0; b < blocks.size(); ++b) first_nz[b] = host_ptr[blocks[b]];
-  s->block_nz.Resize(blocks.size());
-  s->block_nz.Upload(first_nz.data(), first_nz.size(), stream);
+// Work-block partition of one orientation, computed on the host from its offsets.
+struct HostBlocks {
+  std::vector<int> starts, first_nz;
+  int max_row_nnz = 0;
+};
+
+template <class P>
+HostBlocks ComputeBlocks(const P* ptr, int rows) {
+  HostBlocks out;
+  out.starts.push_back(0);
+  int mx = 0;
+  int r = 0;
+  while (r < rows) {
+    const int begin = r;
+    int64_t nz = static_cast<int64_t>(ptr[r + 1]) - static_cast<int64_t>(ptr[r]);
+    mx = nz > mx ? static_cast<int>(nz) : mx;
+    ++r;
+    if (nz <= kStreamChunk) {
+      while (r < rows && r - begin < kMaxRowsPerBlock) {
+        const int64_t next = static_cast<int64_t>(ptr[r + 1]) - static_cast<int64_t>(ptr[r]);
+        if (nz + next > kStreamChunk) break;
+        nz += next;
+        mx = next > mx ? static_cast<int>(next) : mx;
+        ++r;
+      }
+    }
+    out.starts.push_back(r);
+  }
+  out.max_row_nnz = mx;
+  out.first_nz.resize(out.starts.size());
+  for (size_t b = 0; b < out.starts.size(); ++b) out.first_nz[b] = static_cast<int>(ptr[out.starts[b]]);
+  return out;
+}
+
+void UploadBlocks(SparseRows* s, const HostBlocks& hb, cudaStream_t stream) {
+  s->max_row_nnz = hb.max_row_nnz;
+  s->num_blocks = static_cast<int>(hb.starts.size()) - 1;
+  s->block_start.Resize(hb.starts.size());
+  s->block_start.Upload(hb.starts.data(), hb.starts.size(), stream);
+  s->block_nz.Resize(hb.first_nz.size());
+  s->block_nz.Upload(hb.first_nz.data(), hb.first_nz.size(), stream);
   PDLP_CUDA_CHECK(cudaStreamSynchronize(stream));
 }
 
 }  // namespace
 
 std::vector<int> PartitionRows(const int* ptr, int rows, int* max_row_nnz) {
-  std::vector<int> starts;
-  starts.push_back(0);
-  int mx = 0;
-  int r = 0;
-  while (r < rows) {
-    const int begin = r;
-    int nz = ptr[r + 1] - ptr[r];
-    mx = nz > mx ? nz : mx;
-    ++r;
-    if (nz <= kStreamChunk) {
-      while (r < rows && r - begin < kMaxRowsPerBlock) {
-        const int next = ptr[r + 1] - ptr[r];
-        if (nz + next > kStreamChunk) break;
-        nz += next;
-        mx = next > mx ? next : mx;
-        ++r;
-      }
-    }
-    starts.push_back(r);
-  }
-  if (max_row_nnz != nullptr) *max_row_nnz = mx;
-  return starts;
+  HostBlocks hb = ComputeBlocks(ptr, rows);
+  if (max_row_nnz != nullptr) *max_row_nnz = hb.max_row_nnz;
+  return std::move(hb.starts);
 }
 
 namespace {
@@ -112,6 +129,14 @@ void BuildDeviceMatrixT(int64_t n, int64_t m, int64_t nnz, const I* col_ptr, con
   csr.rows = static_cast<int>(m); csr.cols = static_cast<int>(n); csr.nnz = nnz;
   csc.ptr.Resize(n + 1); csc.idx.Resize(nnz); csc.val.Resize(nnz);
   csr.ptr.Resize(m + 1); csr.idx.Resize(nnz); csr.val.Resize(nnz);
+
+  // The CSC work-block partition only needs the host offsets: it runs on a host thread while the
+  // matrix is uploaded and transposed (a sequential scan of n offsets, ~0.1 s at n = 3.3e7).  Offsets
+  // that fail the device-side validity check below never reach a kernel: the partition only reads
+  // ptr[0 .. n] and its result is dropped with the exception.
+  const bool overlap_partition = std::getenv("PDLP_B200_SYNC_PARTITION") == nullptr;  // (timing experiments)
+  std::future<HostBlocks> csc_blocks = std::async(overlap_partition ? std::launch::async : std::launch::deferred,
+                                                  [col_ptr, n]() { return ComputeBlocks(col_ptr, static_cast<int>(n)); });
 
   DeviceArray<int> bad(1);
   bad.Zero(stream);
@@ -151,13 +176,11 @@ void BuildDeviceMatrixT(int64_t n, int64_t m, int64_t nnz, const I* col_ptr, con
   }
 
   // Work-block partitions (host, from the offsets).
-  std::vector<int> host_ptr(n + 1);
-  for (int64_t j = 0; j <= n; ++j) host_ptr[j] = static_cast<int>(col_ptr[j]);
-  SetBlocks(&csc, host_ptr, stream);
-  host_ptr.assign(m + 1, 0);
+  UploadBlocks(&csc, csc_blocks.get(), stream);
+  std::vector<int> host_ptr(m + 1, 0);
   csr.ptr.Download(host_ptr.data(), m + 1, stream);
   PDLP_CUDA_CHECK(cudaStreamSynchronize(stream));
-  SetBlocks(&csr, host_ptr, stream);
+  UploadBlocks(&csr, ComputeBlocks(host_ptr.data(), static_cast<int>(m)), stream);
 }
 }  // namespace
 
