@@ -112,16 +112,22 @@ struct CriticalOp : AlwaysActive {
   }
 };
 
-// One Newton pass at step `delta`: fixed radius^2, free coefficient, number fixed.
+// One Newton pass evaluated at kRadiusCandidates step sizes at once (ascending): for each, the
+// fixed radius^2, the free coefficient and the number of fixed entries.  Slot 3 k + {0, 1, 2}.
+constexpr int kRadiusCandidates = 5;
 struct RadiusPassOp : AlwaysActive {
-  static constexpr int kNumSlots = 3;
+  static constexpr int kNumSlots = 3 * kRadiusCandidates;
   __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
-  const double* crit; const double* coef; double delta; int64_t n; int64_t dual_skip_below;
-  __device__ void Apply(int64_t i, Slots<3>& r) const {
+  const double* crit; const double* coef; double delta[kRadiusCandidates]; int64_t n; int64_t dual_skip_below;
+  __device__ void Apply(int64_t i, Slots<kNumSlots>& r) const {
     if (i >= n && i - n < dual_skip_below) return;
     const double cs = crit[i], a = coef[i];
-    if (cs <= delta) { r.v[0] += a * (cs * cs); r.v[2] += 1.0; }
-    else r.v[1] += a;
+    const double fixed = a * (cs * cs);
+#pragma unroll
+    for (int k = 0; k < kRadiusCandidates; ++k) {
+      if (cs <= delta[k]) { r.v[3 * k] += fixed; r.v[3 * k + 2] += 1.0; }
+      else r.v[3 * k + 1] += a;
+    }
   }
 };
 
@@ -231,20 +237,39 @@ LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProb
     double* coef = ws.scratch_nm[1].get();
     const double max_obj = RunMap(ws, CriticalOp{{}, view, crit, coef}, total, Side::kJoint)[0];
     if (max_obj > 0.0) {  // otherwise every objective entry is zero: step 0 (trust_region.cc:349-358)
+      // Root of phi(d) = fixed_r2(d) + d^2 free_coef(d) - r^2 (concave piecewise in d^2) by Newton from
+      // the left: from a point left of the root the Newton step lands left of the root again, and
+      // once a step crosses no breakpoint it is the exact root of the final segment.  Each pass also
+      // evaluates phi at four points further right (the Newton point plus 1, 3, 7, 15 times the
+      // last increment); the iteration continues from the rightmost one that is still left of the
+      // root.  The final value depends only on the final segment's sums, so it is the same root, bit
+      // for bit, as plain Newton's - in a third of the passes where the active set changes slowly.
       const double r2 = radius * radius;
-      double delta = 0.0;
+      double delta = 0.0, increment = 0.0;
       double prev_fixed = -1.0;
       for (;;) {
-        const double* h = RunMap(ws, RadiusPassOp{{}, crit, coef, delta, p.n, view.dual_skip_below}, total, Side::kJoint);
+        RadiusPassOp op{{}, crit, coef, {}, p.n, view.dual_skip_below};
+        static const double kAhead[kRadiusCandidates] = {0.0, 1.0, 3.0, 7.0, 15.0};
+        for (int k = 0; k < kRadiusCandidates; ++k) op.delta[k] = delta + kAhead[k] * increment;
+        const double* h = RunMap(ws, op, total, Side::kJoint);
         ++passes;
-        const double fixed_r2 = h[0], free_coef = h[1], num_fixed = h[2];
+        // Rightmost candidate that is not right of the root (candidate 0 never is).
+        int pick = 0;
+        for (int k = 1; k < kRadiusCandidates && increment > 0.0; ++k) {
+          const double d = op.delta[k];
+          const double phi = h[3 * k] + (d * d) * h[3 * k + 1] - r2;
+          if (phi <= 0.0 && d > op.delta[pick]) pick = k;
+        }
+        const double at = op.delta[pick];
+        const double fixed_r2 = h[3 * pick], free_coef = h[3 * pick + 1], num_fixed = h[3 * pick + 2];
         if (!(free_coef > 0.0)) { step = DBL_MAX; break; }  // trust_region.cc:438-446
-        // No breakpoint crossed since the last pass: delta is the exact root.
-        if (num_fixed == prev_fixed) { step = delta; break; }
+        // No breakpoint crossed since the last pass: the Newton point is the exact root.
+        if (pick == 0 && num_fixed == prev_fixed) { step = at; break; }
         const double next = std::sqrt(std::max(0.0, r2 - fixed_r2) / free_coef);
-        if (!(next > delta)) { step = delta; break; }  // already at the root up to rounding
+        if (!(next > at)) { step = at; break; }  // already at the root up to rounding
         if (passes >= 200) { step = next; break; }
         prev_fixed = num_fixed;
+        increment = next - delta;
         delta = next;
       }
     }
