@@ -1,6 +1,6 @@
 // Host <-> device copies of large pageable arrays through pinned staging slots filled by several
 // host threads.  A plain cudaMemcpyAsync from pageable memory is staged by the driver on one thread
-// (~10 GB/s measured on the C3 upload: 2.7 GB in 0.28 s); here T threads each own two pinned slots
+// (~10 GB/s measured on the C3 upload: 2.7 GB in 0.28 s); here T threads (up to 12) each own two 4 MB pinned slots
 // and a stream, copy their chunks into a slot and queue the DMA, so that the host-side copies run in
 // parallel and overlap the transfers.  The problem upload and the solution download are the only
 // host <-> device traffic of a solve, so this is what the end-to-end time sees of PCIe.
@@ -24,7 +24,7 @@ namespace pdlp_b200 {
 
 class HostStager {
  public:
-  static constexpr size_t kChunkBytes = size_t{8} << 20;
+  static constexpr size_t kChunkBytes = size_t{4} << 20;
   static constexpr size_t kMinBytes = size_t{4} << 20;  // smaller copies take the plain path
   static constexpr int kSlots = 2;
 
@@ -46,7 +46,8 @@ class HostStager {
 
   HostStager() {
     const unsigned hw = std::thread::hardware_concurrency();
-    const int lanes = static_cast<int>(std::max(1u, std::min(6u, hw / 2)));
+    // One host thread per lane; leave two cores to the caller (2 x 4 MB pinned per lane, <= 96 MB).
+    const int lanes = static_cast<int>(std::max(1u, std::min(12u, hw > 2 ? hw - 2 : 1u)));
     lanes_.resize(lanes);
   }
   ~HostStager() = default;  // pinned memory and streams live for the process (the context may be gone at exit)
