@@ -8,6 +8,7 @@
 #ifndef PDLP_B200_LAUNCH_CUH_
 #define PDLP_B200_LAUNCH_CUH_
 
+#include <algorithm>
 #include <type_traits>
 
 #include "pdlp_ops.cuh"
@@ -98,6 +99,36 @@ template <class Op>
 inline int EnqueueRows(Workspace& ws, const Op& op, const SparseRows& s, int region = 0) {
   if (s.partial_sums && IsSharded(ws)) {
     double* sums = ws.exchange_rows;
+    double* partials = ws.partials[region].get();
+    if (s.cut_block >= 0) {
+      // The block's rows are cut into shared rows [0, cut_row) and rows private to this rank.  Only the
+      // shared rows need the exchange: their partial sums are stored and all-reduced, then finished by a
+      // map kernel over cut_row rows; the private rows run the op's own epilogue inside the row-stream
+      // kernel, exactly as on a single GPU (no partial-sum round trip, no second pass over their vectors).
+      // Reduction partials of the two finishing launches sit behind one another in the region's table.
+      const int shared_blocks = s.cut_block, private_blocks = s.num_blocks - s.cut_block;
+      if (shared_blocks > 0) {
+        const RowBlocks v = s.ViewOfBlocks(0, shared_blocks);
+        const int g = std::min(shared_blocks, RowStreamGrid<PartialRowOp<Op>>(s));
+        rowstream_kernel<PartialRowOp<Op>><<<g, kBlock, 0, ws.stream>>>(PartialRowOp<Op>{op, sums}, v, partials);
+        ++ws.launches;
+        ws.comm->AllReduce(sums, static_cast<size_t>(s.cut_row), RowCombineIsMax(op), ws.stream);
+      }
+      int grid = 0;
+      if (private_blocks > 0) {
+        const RowBlocks v = s.ViewOfBlocks(s.cut_block, private_blocks);
+        grid = std::min(private_blocks, RowStreamGrid<Op>(s));
+        rowstream_kernel<Op><<<grid, kBlock, 0, ws.stream>>>(op, v, partials);
+        ++ws.launches;
+      }
+      if (s.cut_row > 0) {
+        const int g = GridFor(s.cut_row);
+        map_reduce_kernel<FinishRowOp<Op>><<<g, kBlock, 0, ws.stream>>>(FinishRowOp<Op>{op, sums}, s.cut_row, partials + static_cast<size_t>(grid) * Op::kNumSlots);
+        ++ws.launches;
+        grid += g;
+      }
+      return grid > 0 ? grid : 1;
+    }
     rowstream_kernel<PartialRowOp<Op>><<<RowStreamGrid<PartialRowOp<Op>>(s), kBlock, 0, ws.stream>>>(PartialRowOp<Op>{op, sums}, s.View(), ws.partials[region].get());
     ws.comm->AllReduce(sums, static_cast<size_t>(ws.shared_rows), RowCombineIsMax(op), ws.stream);
     const int grid = GridFor(s.rows);

@@ -6,6 +6,7 @@
 
 #include <cub/device/device_radix_sort.cuh>
 
+#include <algorithm>
 #include <cstdlib>
 #include <future>
 #include <vector>
@@ -68,21 +69,25 @@ __global__ void row_offsets_kernel(const int* sorted_rows, int64_t nnz, int m, i
 struct HostBlocks {
   std::vector<int> starts, first_nz;
   int max_row_nnz = 0;
+  int cut_block = -1;
 };
 
+// `cut` in (0, rows): no work block straddles that row; out.cut_block = the block starting there.
 template <class P>
-HostBlocks ComputeBlocks(const P* ptr, int rows) {
+HostBlocks ComputeBlocks(const P* ptr, int rows, int cut = -1) {
   HostBlocks out;
   out.starts.push_back(0);
   int mx = 0;
   int r = 0;
   while (r < rows) {
     const int begin = r;
+    if (r == cut) out.cut_block = static_cast<int>(out.starts.size()) - 1;
+    const int limit = (cut > r) ? cut : rows;
     int64_t nz = static_cast<int64_t>(ptr[r + 1]) - static_cast<int64_t>(ptr[r]);
     mx = nz > mx ? static_cast<int>(nz) : mx;
     ++r;
     if (nz <= kStreamChunk) {
-      while (r < rows && r - begin < kMaxRowsPerBlock) {
+      while (r < limit && r - begin < kMaxRowsPerBlock) {
         const int64_t next = static_cast<int64_t>(ptr[r + 1]) - static_cast<int64_t>(ptr[r]);
         if (nz + next > kStreamChunk) break;
         nz += next;
@@ -119,7 +124,7 @@ std::vector<int> PartitionRows(const int* ptr, int rows, int* max_row_nnz) {
 namespace {
 template <class I>
 void BuildDeviceMatrixT(int64_t n, int64_t m, int64_t nnz, const I* col_ptr, const I* row_idx, const double* val, cudaStream_t stream,
-                        DeviceMatrix* out) {
+                        DeviceMatrix* out, int64_t row_cut) {
   if (nnz >= (int64_t{1} << 31) - 1 || n >= (int64_t{1} << 31) - 1 || m >= (int64_t{1} << 31) - 1) {
     throw std::runtime_error("pdlp_b200: one device block must have fewer than 2^31 rows, columns and nonzeros");
   }
@@ -180,17 +185,22 @@ void BuildDeviceMatrixT(int64_t n, int64_t m, int64_t nnz, const I* col_ptr, con
   std::vector<int> host_ptr(m + 1, 0);
   csr.ptr.Download(host_ptr.data(), m + 1, stream);
   PDLP_CUDA_CHECK(cudaStreamSynchronize(stream));
-  UploadBlocks(&csr, ComputeBlocks(host_ptr.data(), static_cast<int>(m)), stream);
+  const int cut = (row_cut > 0 && row_cut < m) ? static_cast<int>(row_cut) : -1;
+  const HostBlocks csr_blocks = ComputeBlocks(host_ptr.data(), static_cast<int>(m), cut);
+  UploadBlocks(&csr, csr_blocks, stream);
+  // All rows shared (cut at m) or none (cut at 0) are expressed with the block counts alone.
+  csr.cut_row = row_cut < 0 ? 0 : static_cast<int>(std::min<int64_t>(row_cut, m));
+  csr.cut_block = row_cut < 0 ? -1 : (row_cut >= m ? csr.num_blocks : (row_cut == 0 ? 0 : csr_blocks.cut_block));
 }
 }  // namespace
 
 void BuildDeviceMatrix(int64_t n, int64_t m, int64_t nnz, const int64_t* col_ptr, const int64_t* row_idx, const double* val,
-                       cudaStream_t stream, DeviceMatrix* out) {
-  BuildDeviceMatrixT(n, m, nnz, col_ptr, row_idx, val, stream, out);
+                       cudaStream_t stream, DeviceMatrix* out, int64_t row_cut) {
+  BuildDeviceMatrixT(n, m, nnz, col_ptr, row_idx, val, stream, out, row_cut);
 }
 void BuildDeviceMatrix(int64_t n, int64_t m, int64_t nnz, const int32_t* col_ptr, const int32_t* row_idx, const double* val,
-                       cudaStream_t stream, DeviceMatrix* out) {
-  BuildDeviceMatrixT(n, m, nnz, col_ptr, row_idx, val, stream, out);
+                       cudaStream_t stream, DeviceMatrix* out, int64_t row_cut) {
+  BuildDeviceMatrixT(n, m, nnz, col_ptr, row_idx, val, stream, out, row_cut);
 }
 
 }  // namespace pdlp_b200

@@ -26,7 +26,12 @@ struct SparseRows {
   // Column-sharded solve: the CSC block's compressed "rows" are this rank's columns (their
   // reductions are per-rank partials); the CSR block holds only this rank's part of every row sum.
   bool sharded_rows = false, partial_sums = false;
+  // Column-sharded CSR block: work blocks [0, cut_block) hold exactly the rows shared with other
+  // ranks (rows [0, cut_row)), the rest the rows private to this rank.  -1: no cut.
+  int cut_block = -1, cut_row = 0;
   RowBlocks View() const { return RowBlocks{ptr.get(), block_start.get(), block_nz.get(), num_blocks, rows}; }
+  // Work blocks [first, first + count): same row / nonzero numbering, so ops index rows as usual.
+  RowBlocks ViewOfBlocks(int first, int count) const { return RowBlocks{ptr.get(), block_start.get() + first, block_nz.get() + first, count, rows}; }
 };
 
 struct DeviceMatrix {
@@ -40,11 +45,13 @@ std::vector<int> PartitionRows(const int* ptr, int rows, int* max_row_nnz);
 // Uploads CSC(K) given with int64 offsets/indices and builds CSR(K) on the device
 // (stable: columns ascending inside every row, exactly the order of Eigen's
 // `.transpose()` materialisation).  Throws std::runtime_error on CUDA failure.
+// `row_cut` >= 0 forces a work-block boundary of the CSR copy at that row (the shared / private split of
+// a column-sharded block).
 void BuildDeviceMatrix(int64_t n, int64_t m, int64_t nnz, const int64_t* col_ptr, const int64_t* row_idx, const double* val,
-                       cudaStream_t stream, DeviceMatrix* out);
+                       cudaStream_t stream, DeviceMatrix* out, int64_t row_cut = -1);
 // The same from 32-bit offsets / indices (what scipy holds below 2^31 nonzeros): half the index upload.
 void BuildDeviceMatrix(int64_t n, int64_t m, int64_t nnz, const int32_t* col_ptr, const int32_t* row_idx, const double* val,
-                       cudaStream_t stream, DeviceMatrix* out);
+                       cudaStream_t stream, DeviceMatrix* out, int64_t row_cut = -1);
 
 }  // namespace pdlp_b200
 #endif  // PDLP_B200_MATRIX_CUH_

@@ -11,7 +11,8 @@ namespace pdlp_b200 {
 void Workspace::Init(int64_t n_, int64_t m_) {
   n = n_; m = m_;
   PDLP_CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
-  for (auto& p : partials) { p.Resize(static_cast<size_t>(kMaxGrid) * kMaxSlots); p.Zero(stream); }
+  // Two launches may share a region's table (sharded CSR pass: private rows, then shared rows).
+  for (auto& p : partials) { p.Resize(static_cast<size_t>(2 * kMaxGrid) * kMaxSlots); p.Zero(stream); }
   totals.Resize(kMaxSlots * 4);
   totals.Zero(stream);
   PDLP_CUDA_CHECK(cudaMallocHost(&host_totals, kMaxSlots * 4 * sizeof(double)));

@@ -35,7 +35,7 @@ enum class Side { kDual, kSharded, kJoint };
 // Launch context: stream, per-kernel partial buffers, totals, pinned read-back.
 struct Workspace {
   cudaStream_t stream = nullptr;
-  DVec partials[3];          // kMaxGrid * kMaxSlots each
+  DVec partials[3];          // 2 * kMaxGrid * kMaxSlots each
   DVec totals;               // kMaxSlots * 4
   double* host_totals = nullptr;  // pinned, kMaxSlots * 4
   DVec scratch_n[3], scratch_m[3], scratch_nm[2];  // sized n, m, n+m on demand

@@ -79,8 +79,10 @@ PreprocessSolver::PreprocessSolver(const QpView& qp, const PrimalDualHybridGradi
   problem_.is_lp = qp.q == nullptr;
   problem_.objective_offset = qp.objective_offset;
   problem_.objective_scaling_factor = qp.objective_scaling_factor;
-  if (qp.col_ptr32 != nullptr) BuildDeviceMatrix(qp.n, qp.m, qp.nnz, qp.col_ptr32, qp.row_idx32, qp.val, ws_.stream, &problem_.K);
-  else BuildDeviceMatrix(qp.n, qp.m, qp.nnz, qp.col_ptr, qp.row_idx, qp.val, ws_.stream, &problem_.K);
+  // Sharded: the CSR copy's work blocks are cut at the shared / private row boundary (pdlp_launch.cuh:EnqueueRows).
+  const int64_t row_cut = comm_.sharded() ? ws_.shared_rows : -1;
+  if (qp.col_ptr32 != nullptr) BuildDeviceMatrix(qp.n, qp.m, qp.nnz, qp.col_ptr32, qp.row_idx32, qp.val, ws_.stream, &problem_.K, row_cut);
+  else BuildDeviceMatrix(qp.n, qp.m, qp.nnz, qp.col_ptr, qp.row_idx, qp.val, ws_.stream, &problem_.K, row_cut);
   problem_.K.by_col.sharded_rows = comm_.sharded();
   problem_.K.by_row.partial_sums = comm_.sharded();
   auto up = [&](DVec& d, const double* h, int64_t count) {
