@@ -95,6 +95,11 @@ def solve_params(name, threads=1, iteration_limit=None):
     p.num_threads = threads
     if iteration_limit is not None:
         p.termination_criteria.iteration_limit = iteration_limit
+    else:
+        # Guard rail of the end-to-end leg only (a solve that reaches eps never sees it; the reason it
+        # stopped for is reported in e2e.termination_reason): the reference's default is unlimited.  No
+        # time limit: a finite one makes the host poll the clock every ~20 ms instead of every 64 iterations.
+        p.termination_criteria.iteration_limit = 100000
     return p
 
 
