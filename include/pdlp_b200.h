@@ -235,6 +235,15 @@ pdlp_b200_status pdlp_b200_trial_steps(pdlp_b200_device_problem* h, int steps, d
 pdlp_b200_status pdlp_b200_trial_steps_profiled(pdlp_b200_device_problem* h, int steps, double step_size, double primal_weight, const double* x,
                                                 const double* y, double* kernel_seconds /*5*/);
 
+/* Host only (no device needed): the work-block partition the row-stream kernels run on
+ * (at most 2048 nonzeros and 1024 rows per block, a longer row alone in its block),
+ * from `rows + 1` compressed offsets.  cut in (0, rows): no block straddles that row (the
+ * shared / private split of a sharded block), *cut_block = the block starting there;
+ * cut < 0: none, *cut_block = -1.  block_start has room for rows + 1 entries; the first
+ * *num_blocks + 1 are written.  For the CPU-side tests of the invariants the kernels rely on. */
+pdlp_b200_status pdlp_b200_work_blocks(const int64_t* offsets, int64_t rows, int64_t cut, int32_t* block_start, int64_t* num_blocks,
+                                       int32_t* cut_block, int32_t* max_row_nnz);
+
 #ifdef __cplusplus
 }
 #endif

@@ -194,6 +194,20 @@ def check_termination(params, stats, bound_norms, which="iterate", force_numeric
     return reason.value, ptype.value, rel
 
 
+def work_blocks(offsets, cut=-1):
+    """The work-block partition the row-stream kernels run on (host only, pdlp_b200_work_blocks):
+    returns (block_start, cut_block, max_row_nnz) for `rows + 1` compressed offsets."""
+    off = np.ascontiguousarray(offsets, dtype=np.int64)
+    rows = off.size - 1
+    if rows < 0:
+        raise ValueError("offsets must have rows + 1 entries")
+    starts = np.zeros(rows + 1, dtype=np.int32)
+    nb, cb, mx = ctypes.c_int64(0), ctypes.c_int32(-1), ctypes.c_int32(0)
+    _check(_lib.pdlp_b200_work_blocks(ctypes.c_void_p(off.ctypes.data), ctypes.c_int64(rows), ctypes.c_int64(int(cut)), ctypes.c_void_p(starts.ctypes.data),
+                                      ctypes.byref(nb), ctypes.byref(cb), ctypes.byref(mx)))
+    return starts[:nb.value + 1].copy(), cb.value, mx.value
+
+
 _last_counters = {}
 
 

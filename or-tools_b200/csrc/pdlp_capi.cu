@@ -466,6 +466,26 @@ void pdlp_b200_problem_destroy(pdlp_b200_device_problem* h) {
   delete h;
 }
 
+pdlp_b200_status pdlp_b200_work_blocks(const int64_t* offsets, int64_t rows, int64_t cut, int32_t* block_start, int64_t* num_blocks,
+                                       int32_t* cut_block, int32_t* max_row_nnz) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (offsets == nullptr || block_start == nullptr || num_blocks == nullptr || rows < 0 || rows >= (int64_t{1} << 31) - 1 || cut >= rows || cut == 0) {
+      return Fail(PDLP_B200_BAD_ARGUMENT, "bad argument");
+    }
+    for (int64_t r = 0; r < rows; ++r) {
+      if (offsets[r + 1] < offsets[r]) return Fail(PDLP_B200_BAD_ARGUMENT, "offsets must not decrease");
+    }
+    if (offsets[rows] - offsets[0] >= (int64_t{1} << 31) - 1) return Fail(PDLP_B200_BAD_ARGUMENT, "too many nonzeros for one device block");
+    int mx = 0, cb = -1;
+    const std::vector<int> starts = PartitionRowsWithCut(offsets, static_cast<int>(rows), cut < 0 ? -1 : static_cast<int>(cut), &mx, &cb);
+    std::copy(starts.begin(), starts.end(), block_start);
+    *num_blocks = static_cast<int64_t>(starts.size()) - 1;
+    if (cut_block != nullptr) *cut_block = cb;
+    if (max_row_nnz != nullptr) *max_row_nnz = mx;
+    return PDLP_B200_OK;
+  });
+}
+
 pdlp_b200_status pdlp_b200_matvec(pdlp_b200_device_problem* h, int which, const double* v, double* out, int repeat, double* seconds_per_launch) {
   return Guard([&]() -> pdlp_b200_status {
     if (h == nullptr || v == nullptr || out == nullptr || (which != 0 && which != 1)) return Fail(PDLP_B200_BAD_ARGUMENT, "bad argument");

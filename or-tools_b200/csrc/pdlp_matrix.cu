@@ -121,6 +121,13 @@ std::vector<int> PartitionRows(const int* ptr, int rows, int* max_row_nnz) {
   return std::move(hb.starts);
 }
 
+std::vector<int> PartitionRowsWithCut(const int64_t* ptr, int rows, int cut, int* max_row_nnz, int* cut_block) {
+  HostBlocks hb = ComputeBlocks(ptr, rows, cut);
+  if (max_row_nnz != nullptr) *max_row_nnz = hb.max_row_nnz;
+  if (cut_block != nullptr) *cut_block = hb.cut_block;
+  return std::move(hb.starts);
+}
+
 namespace {
 template <class I>
 void BuildDeviceMatrixT(int64_t n, int64_t m, int64_t nnz, const I* col_ptr, const I* row_idx, const double* val, cudaStream_t stream,

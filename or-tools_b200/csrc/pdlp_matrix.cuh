@@ -41,6 +41,9 @@ struct DeviceMatrix {
 
 // Cuts [0, rows) into work blocks for rowstream_kernel from a host copy of the offsets.
 std::vector<int> PartitionRows(const int* ptr, int rows, int* max_row_nnz);
+// Host-only view of the same partition for the unit tests (pdlp_b200_work_blocks): block starts
+// with a cut at row `cut` (-1: none); *cut_block = index of the block that starts there, or -1.
+std::vector<int> PartitionRowsWithCut(const int64_t* ptr, int rows, int cut, int* max_row_nnz, int* cut_block);
 
 // Uploads CSC(K) given with int64 offsets/indices and builds CSR(K) on the device
 // (stable: columns ascending inside every row, exactly the order of Eigen's
