@@ -1,5 +1,6 @@
-// Device plumbing shared by every PDLP kernel file: error checking, RAII device buffers,
-// deterministic block reductions, and the two kernel skeletons every op is an instance of:
+// Device plumbing shared by every PDLP kernel file: error checking, RAII device buffers, and
+// (pdlp_skeletons.cuh) deterministic block reductions and the two kernel skeletons every op is an
+// instance of:
 //
 //   map_reduce_kernel<Op>   one grid-stride pass over a dense index range [0, count)
 //   rowstream_kernel<Op>    one pass over a compressed sparse matrix by rows ("row" = a
@@ -87,462 +88,8 @@ class DeviceArray {
 };
 using DVec = DeviceArray<double>;
 
-constexpr int kBlock = 256;          // threads per CTA for every kernel here
-constexpr int kMaxSlots = 16;        // reduction slots an op may use
-#ifndef PDLP_STREAM_CHUNK
-#define PDLP_STREAM_CHUNK 2048
-#endif
-constexpr int kStreamChunk = PDLP_STREAM_CHUNK;   // nonzeros staged in shared memory per work block
-constexpr int kMaxGrid = 148 * 8;    // 148 SMs x 8 resident CTAs: persistent grid-stride launches
-
-// Reduction slot kinds.  kMax slots must only ever receive values >= 0 or be
-// initialised by the op through Op::Init (we initialise every slot with Identity()).
-enum SlotKind : int { kSum = 0, kMax = 1 };
-
-__device__ __forceinline__ double SlotIdentity(int kind) { return kind == kMax ? -INFINITY : 0.0; }
-__device__ __forceinline__ double SlotCombine(int kind, double a, double b) {
-  return kind == kMax ? fmax(a, b) : a + b;
-}
-// fmax drops NaNs; the stats pass detects NaNs through the sum slots, as the reference
-// does through the l2 norm (primal_dual_hybrid_gradient.cc:737).
-
-template <int NS>
-struct Slots {
-  double v[NS > 0 ? NS : 1];
-};
-
-// Block-wide reduction of NS slots; result valid in thread 0.  Fixed tree: lanes by
-// xor-shuffle, then warps in index order.
-template <class Op>
-__device__ __forceinline__ void BlockReduceAndStore(Slots<Op::kNumSlots>& acc, double* partials) {
-  constexpr int NS = Op::kNumSlots;
-  if constexpr (NS > 0) {
-    __shared__ double warp_buf[NS][kBlock / 32];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-    for (int s = 0; s < NS; ++s) {
-      double x = acc.v[s];
-      const int kind = Op::SlotKindOf(s);
-#pragma unroll
-      for (int off = 16; off > 0; off >>= 1) x = SlotCombine(kind, x, __shfl_xor_sync(0xffffffffu, x, off));
-      if (lane == 0) warp_buf[s][warp] = x;
-    }
-    __syncthreads();
-    if (threadIdx.x < NS) {
-      const int s = threadIdx.x;
-      const int kind = Op::SlotKindOf(s);
-      double x = warp_buf[s][0];
-      for (int w = 1; w < kBlock / 32; ++w) x = SlotCombine(kind, x, warp_buf[s][w]);
-      partials[static_cast<size_t>(blockIdx.x) * NS + s] = x;
-    }
-  }
-}
-
-// ---- skeleton 1: dense index range ----
-// Op interface:
-//   static constexpr int kNumSlots; static __device__ int SlotKindOf(int s);
-//   __device__ bool Begin();     // once per thread: resolve state-dependent pointers and
-//                                // scalars into members; false = early-out (device-side
-//                                // loop control)
-//   __device__ void Apply(int64_t i, Slots<kNumSlots>& acc) const;
-template <class Op>
-__global__ void __launch_bounds__(kBlock, 4) map_reduce_kernel(const Op op_in, int64_t count, double* partials) {
-  Slots<Op::kNumSlots> acc;
-#pragma unroll
-  for (int s = 0; s < Op::kNumSlots; ++s) acc.v[s] = SlotIdentity(Op::SlotKindOf(s));
-  Op op = op_in;
-  if (op.Begin()) {
-    const int64_t stride = static_cast<int64_t>(gridDim.x) * kBlock;
-    for (int64_t i = static_cast<int64_t>(blockIdx.x) * kBlock + threadIdx.x; i < count; i += stride) op.Apply(i, acc);
-  }
-  BlockReduceAndStore<Op>(acc, partials);
-}
-
-// ---- skeleton 2: compressed sparse matrix by rows ----
-// The matrix is cut at setup into "work blocks" of consecutive rows holding at most
-// kStreamChunk nonzeros (a row longer than that is a work block of its own).  A CTA
-// streams its block's nonzeros with fully coalesced loads into shared memory as
-// products LoadAt(k, Index(k)), then sub-warps of T threads reduce each row out of shared
-// memory (T = 1 for short rows: a sequential, reference-ordered sum).  Long rows are reduced
-// straight from global memory by the whole CTA.
-//
-// The pass is latency-bound, not bandwidth-bound (profiles/r01_ncu_rowstream_c3_v0.md: DRAM at
-// 51-57 % with full occupancy, stalls on the block_start -> row_ptr -> idx -> gather -> barrier
-// -> row_ptr -> epilogue-operand chain of six dependent memory latencies per work block).  The
-// kernel therefore software-pipelines everything that does not depend on the gather:
-//   * work-block metadata (first row, first nonzero) two blocks ahead, from two flat arrays;
-//   * the column indices of the NEXT block into shared memory (cp.async) while the current block
-//     reduces, and the block's row offsets likewise;
-//   * the epilogue operands of each thread's row(s) (Op::RowPrefetch) into registers, issued
-//     BEFORE the gather so that the in-order warp does not stall in front of them;
-// leaving idx (prefetched) -> gather -> barrier -> reduce from shared memory on the critical path.
-// Shared-memory products are stored with a per-block bank pad so that the threads reducing rows of
-// 8, 16, 32, 64 ... nonzeros do not collide on the same banks (see Skew below).
-//
-// Op interface (in addition to kNumSlots / SlotKindOf / Begin):
-//   __device__ double Load(int64_t k) const;              // value staged for nonzero k
-//   __device__ double RowInit() const;
-//   __device__ double RowAdd(double acc, double staged, int row) const;
-//   __device__ double RowMerge(double a, double b) const;
-//   __device__ void RowFinish(int row, double acc, Slots<kNumSlots>& red) const;
-// Optional (the hot ops have them):
-//   __device__ const int* IndexAddress(int64_t k) const;  __device__ const double* ValueAddress(int64_t k) const;
-//   __device__ double Gather(int index) const;  __device__ double Product(double value, double gathered) const;
-//       split of Load (= Product(*ValueAddress(k), Gather(*IndexAddress(k)))) so that indices travel one
-//       block ahead and values by asynchronous copy
-//   struct Pre;  __device__ Pre RowPrefetch(int row) const;
-//   __device__ void RowFinish(int row, double acc, const Pre& pre, Slots<kNumSlots>& red) const;
-//       epilogue operands fetched before the reduction instead of after it
-struct RowBlocks {
-  const int* row_ptr;      // rows + 1
-  const int* block_start;  // num_blocks + 1 (row index where each work block starts)
-  const int* block_nz;     // num_blocks + 1 (row_ptr[block_start[b]]: first nonzero of each work block)
-  int num_blocks;
-  int rows;
-};
-
-constexpr int kMaxRowsPerBlock = 4 * kBlock;
-#ifndef PDLP_ROWSTREAM_MIN_CTAS
-#define PDLP_ROWSTREAM_MIN_CTAS 4  // resident CTAs per SM the register allocation must allow
-#endif
-constexpr int kPerThread = kStreamChunk / kBlock;             // nonzeros per thread per work block
-constexpr int kStagedSize = kStreamChunk + 3 * (kStreamChunk / 16);  // with the largest bank pad
-// Position of staged product k: c pad slots after every 16 products, c = 0 .. 3 chosen per work
-// block.  With 8-byte products a half-warp touches 16 bank pairs.  The three coalesced passes over
-// the products (asynchronous copy in, multiply in place) walk 16 consecutive k that start at a multiple of 16, so a
-// pad that only falls between such groups keeps them conflict-free (a pad every 8 products does
-// not: measured +6 % on K x).  The row reduction reads T threads per row; simulated conflict
-// degrees (scripts/bank_pad_sim.py, wavefronts per 16 products, 1.0 = none):
-//   rows of one odd length (3, 5: CSC copies of the bench LPs)    c=0: 1.0   c=1: 3-5   c=2,3: 2.0
-//   rows of one length that is a multiple of 16 (16, 32, 64)       c=0: 2-8   c=1: 2.0   c=2: 1.0   c=3: 2.0
-//   rows of one other even length (2, 4, 8, 10, 12, 24)            c=0: 2-8   c=1: 1-5   c=2: 2-3   c=3: 1.0-2.0
-//   irregular rows (Poisson lengths around 10 or 16)               c=0: 3.6   c=1: 3.5   c=2: 3.1-3.6   c=3: 3.0-3.6
-// A block is "of one length" when nz == nrows * (nz / nrows).  (Before this rule, c = 1 everywhere:
-// 24 % of the shared-memory wavefronts of both SpMV kernels on C3 were bank conflicts,
-// profiles/r01_ncu_step_kernels_c3_v6.md.)
-__device__ __forceinline__ int Skew(int k, int pad) { return k + pad * (k >> 4); }
-// PDLP_ROWSTREAM_LEAN=1 selects a staging path with fewer issued instructions per nonzero (the
-// row-stream kernels are issue-bound): work blocks that fill all but the last of a
-// thread's kPerThread positions run without per-position predicates, staged positions advance by
-// one stride per position instead of being recomputed, and the bank-pad rule avoids the integer
-// division.  Same arithmetic, same staged layout, same results.  Off by default until it has been
-// timed on the device (build with EXTRA_NVCCFLAGS=-DPDLP_ROWSTREAM_LEAN=1).
-#ifndef PDLP_ROWSTREAM_LEAN
-#define PDLP_ROWSTREAM_LEAN 0
-#endif
-__device__ __forceinline__ int BankPadFor(int nz, int nrows) {
-#if PDLP_ROWSTREAM_LEAN
-  // nz <= kStreamChunk and nrows <= kMaxRowsPerBlock are exact in fp32; when nrows divides nz the
-  // approximate quotient is within 2 ulp of the integer and rounds to it, otherwise no integer
-  // passes the multiplication test.
-  const int len = __float2int_rn(__fdividef(static_cast<float>(nz), static_cast<float>(nrows)));
-#else
-  const int len = nz / nrows;
-#endif
-  if (len * nrows != nz) return 3;
-  if (len & 1) return 0;
-  return (len & 15) == 0 ? 2 : 3;
-}
-
-template <class Op, class = void>
-struct HasSplitLoad : std::false_type {};
-template <class Op>
-struct HasSplitLoad<Op, std::void_t<decltype(std::declval<const Op&>().IndexAddress(int64_t{0}))>> : std::true_type {};
-template <class Op, class = void>
-struct HasRowPrefetch : std::false_type {};
-template <class Op>
-struct HasRowPrefetch<Op, std::void_t<typename Op::Pre>> : std::true_type {};
-
-struct NoPre {};
-template <class Op, bool = HasRowPrefetch<Op>::value>
-struct PreOf { using type = NoPre; };
-template <class Op>
-struct PreOf<Op, true> { using type = typename Op::Pre; };
-
-template <class Op>
-__device__ __forceinline__ typename PreOf<Op>::type OpRowPrefetch(const Op& op, int row) {
-  if constexpr (HasRowPrefetch<Op>::value) return op.RowPrefetch(row);
-  else return NoPre{};
-}
-template <class Op>
-__device__ __forceinline__ void OpRowFinish(const Op& op, int row, double acc, const typename PreOf<Op>::type& pre, Slots<Op::kNumSlots>& red) {
-  if constexpr (HasRowPrefetch<Op>::value) op.RowFinish(row, acc, pre, red);
-  else op.RowFinish(row, acc, red);
-}
-
-// Ampere-style asynchronous 4-byte copies global -> shared: the row offsets of the current work
-// block and the column indices of the next one travel without occupying registers or stalling
-// the issuing warp.
-__device__ __forceinline__ void CpAsync4(void* smem_dst, const void* global_src) {
-  const unsigned dst = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(global_src));
-}
-__device__ __forceinline__ void CpAsync8(void* smem_dst, const void* global_src) {
-  const unsigned dst = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(dst), "l"(global_src));
-}
-__device__ __forceinline__ void CpAsyncCommit() { asm volatile("cp.async.commit_group;\n" ::); }
-__device__ __forceinline__ void CpAsyncWaitAll() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
-
-template <class Op>
-__device__ __forceinline__ void PrefetchIndices(const Op& op, int* idx_buf, int first_nz, int nz) {
-  if constexpr (HasSplitLoad<Op>::value) {
-    if (nz <= kStreamChunk) {
-#if PDLP_ROWSTREAM_LEAN
-      if (nz > (kPerThread - 1) * kBlock) {
-        // Only the last position of a thread can fall outside the block.
-        const int* src = op.IndexAddress(first_nz + static_cast<int>(threadIdx.x));
-        int* dst = idx_buf + threadIdx.x;
-#pragma unroll
-        for (int i = 0; i < kPerThread - 1; ++i) CpAsync4(dst + i * kBlock, src + i * kBlock);
-        if (static_cast<int>(threadIdx.x) + (kPerThread - 1) * kBlock < nz) CpAsync4(dst + (kPerThread - 1) * kBlock, src + (kPerThread - 1) * kBlock);
-      } else
-#endif
-      {
-#pragma unroll
-        for (int i = 0; i < kPerThread; ++i) {
-          const int k = threadIdx.x + i * kBlock;
-          if (k < nz) CpAsync4(idx_buf + k, op.IndexAddress(first_nz + k));
-        }
-      }
-    }
-  }
-  CpAsyncCommit();
-}
-
-// Staging of one work block of a split-load op (indices already in idx_buf): gathers, asynchronous
-// copies of the values, the row offsets and the next block's indices, then the products in place.
-// kDense: every position but a thread's last is inside the block, so only that one is predicated.
-template <bool kDense, class Op>
-__device__ __forceinline__ void StageSplitLean(const Op& op, double* staged, int* idx_buf, int* row_raw, const RowBlocks& rb, int p0, int nz, int r0, int nrows,
-                                               int pad, int np0, int next_nz) {
-  const int tid = threadIdx.x;
-  const bool last_live = tid + (kPerThread - 1) * kBlock < nz;
-  auto live = [&](int i) { return kDense ? (i < kPerThread - 1 || last_live) : (tid + i * kBlock < nz); };
-  // Position of nonzero tid + i * kBlock: Skew(tid, pad) + i * (kBlock + pad * kBlock / 16).
-  double* mine = staged + Skew(tid, pad);
-  const int step = kBlock + pad * (kBlock >> 4);
-  double g[kPerThread];
-#pragma unroll
-  for (int i = 0; i < kPerThread; ++i) g[i] = live(i) ? op.Gather(idx_buf[tid + i * kBlock]) : 0.0;
-  // The index reads above stay ahead of the asynchronous copies that overwrite idx_buf below.
-  asm volatile("" ::: "memory");
-  const double* values = op.ValueAddress(p0 + tid);
-#pragma unroll
-  for (int i = 0; i < kPerThread; ++i) {
-    if (live(i)) CpAsync8(mine + i * step, values + i * kBlock);
-  }
-#pragma unroll 1
-  for (int i = tid; i <= nrows; i += kBlock) CpAsync4(row_raw + i, rb.row_ptr + r0 + i);
-  PrefetchIndices(op, idx_buf, np0, next_nz);
-  CpAsyncWaitAll();
-#pragma unroll
-  for (int i = 0; i < kPerThread; ++i) {
-    if (live(i)) mine[i * step] = op.Product(mine[i * step], g[i]);
-  }
-}
-
-template <class Op>
-__global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_kernel(const Op op_in, RowBlocks rb, double* partials) {
-  __shared__ double staged[kStagedSize];
-  __shared__ int row_raw[kMaxRowsPerBlock + 1];  // row_ptr[r0 ...] of the current work block
-  // One buffer is enough for "this block's indices" and "the next block's indices": a thread copies
-  // the next block's indices into exactly the positions it has already read this block's from.
-  __shared__ int idx_buf[HasSplitLoad<Op>::value ? kStreamChunk : 1];
-  __shared__ double long_row_buf[kBlock / 32];
-  using Pre = typename PreOf<Op>::type;
-  constexpr int kPreRows = sizeof(Pre) > 16 ? 2 : 4;  // rows per thread whose epilogue operands are fetched before the barrier
-  Slots<Op::kNumSlots> red;
-#pragma unroll
-  for (int s = 0; s < Op::kNumSlots; ++s) red.v[s] = SlotIdentity(Op::SlotKindOf(s));
-  Op op = op_in;
-  if (op.Begin()) {
-    const int stride = gridDim.x;
-    int b = blockIdx.x;
-    // Metadata of the current work block and of the next one (b + stride).
-    int r0 = 0, r1 = 0, p0 = 0, p1 = 0, nr0 = 0, nr1 = 0, np0 = 0, np1 = 0;
-    if (b < rb.num_blocks) { r0 = rb.block_start[b]; r1 = rb.block_start[b + 1]; p0 = rb.block_nz[b]; p1 = rb.block_nz[b + 1]; }
-    if (b + stride < rb.num_blocks) {
-      nr0 = rb.block_start[b + stride]; nr1 = rb.block_start[b + stride + 1];
-      np0 = rb.block_nz[b + stride]; np1 = rb.block_nz[b + stride + 1];
-    }
-    PrefetchIndices(op, idx_buf, p0, p1 - p0);
-    while (b < rb.num_blocks) {
-      const int nz = p1 - p0;
-      // Metadata two blocks ahead: in flight for a whole block before it is needed.
-      const int b2 = b + 2 * stride;
-      int fr0 = 0, fr1 = 0, fp0 = 0, fp1 = 0;
-      if (b2 < rb.num_blocks) { fr0 = rb.block_start[b2]; fr1 = rb.block_start[b2 + 1]; fp0 = rb.block_nz[b2]; fp1 = rb.block_nz[b2 + 1]; }
-      const int next_nz = np1 - np0;  // 0 when there is no next block
-      if (nz > kStreamChunk) {
-        // One long row (r1 == r0 + 1 by construction): CTA-wide strided reduce.
-        PrefetchIndices(op, idx_buf, np0, next_nz);
-        const Pre pre = OpRowPrefetch(op, r0);
-        double a = op.RowInit();
-        for (int k = p0 + threadIdx.x; k < p1; k += kBlock) a = op.RowAdd(a, op.Load(k), r0);
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) a = op.RowMerge(a, __shfl_xor_sync(0xffffffffu, a, off));
-        if ((threadIdx.x & 31) == 0) long_row_buf[threadIdx.x >> 5] = a;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-          double t = long_row_buf[0];
-          for (int w = 1; w < kBlock / 32; ++w) t = op.RowMerge(t, long_row_buf[w]);
-          OpRowFinish(op, r0, t, pre, red);
-        }
-        CpAsyncWaitAll();
-        __syncthreads();
-      } else {
-        // This block's column indices were copied to shared memory a block ago (own positions).
-        CpAsyncWaitAll();
-#if !PDLP_ROWSTREAM_LEAN
-        int jx[kPerThread];
-        if constexpr (HasSplitLoad<Op>::value) {
-#pragma unroll
-          for (int i = 0; i < kPerThread; ++i) {
-            const int k = threadIdx.x + i * kBlock;
-            jx[i] = k < nz ? idx_buf[k] : 0;
-          }
-        }
-#endif
-        // Issue order matters (warps issue in order, and ptxas places the cp.async wait directly
-        // behind the last copy): epilogue operands and gathers first - their addresses are known -
-        // then the asynchronous copies of this block's values and row offsets and of the next
-        // block's indices.  All of them are in flight together; the wait then covers one latency.
-        const int nrows = r1 - r0;
-        const int shift = BankPadFor(nz, nrows);
-        // Threads per row: largest power of two <= min(32, kBlock / nrows), at least 1.
-#if PDLP_ROWSTREAM_LEAN
-        // 2^l * nrows <= kBlock = 2^8  <=>  l <= 8 - ceil(log2(nrows)),  ceil(log2(n)) = 32 - clz(n - 1).
-        static_assert(kBlock == 256, "log_t below assumes kBlock == 256");
-        const int log_t = min(5, max(0, __clz(nrows - 1) - 24));
-#else
-        int log_t = 0;
-        while (log_t < 5 && (2 << log_t) * nrows <= kBlock) ++log_t;
-#endif
-        const int t = 1 << log_t;
-        const int sub = threadIdx.x >> log_t, lane = threadIdx.x & (t - 1);
-        const int groups = kBlock >> log_t;
-        Pre pre[kPreRows];
-#pragma unroll
-        for (int u = 0; u < kPreRows; ++u) {
-          const int rr = sub + u * groups;
-          if (lane == 0 && rr < nrows) pre[u] = OpRowPrefetch(op, r0 + rr);
-        }
-        if constexpr (HasSplitLoad<Op>::value) {
-#if PDLP_ROWSTREAM_LEAN
-          if (nz > (kPerThread - 1) * kBlock) StageSplitLean<true>(op, staged, idx_buf, row_raw, rb, p0, nz, r0, nrows, shift, np0, next_nz);
-          else StageSplitLean<false>(op, staged, idx_buf, row_raw, rb, p0, nz, r0, nrows, shift, np0, next_nz);
-#else
-          double g[kPerThread];
-#pragma unroll
-          for (int i = 0; i < kPerThread; ++i) {
-            const int k = threadIdx.x + i * kBlock;
-            g[i] = k < nz ? op.Gather(jx[i]) : 0.0;
-          }
-#pragma unroll
-          for (int i = 0; i < kPerThread; ++i) {
-            const int k = threadIdx.x + i * kBlock;
-            if (k < nz) CpAsync8(staged + Skew(k, shift), op.ValueAddress(p0 + k));
-          }
-          for (int i = threadIdx.x; i <= nrows; i += kBlock) CpAsync4(row_raw + i, rb.row_ptr + r0 + i);
-          PrefetchIndices(op, idx_buf, np0, next_nz);
-          CpAsyncWaitAll();
-          // Each thread multiplies its own positions in place.
-#pragma unroll
-          for (int i = 0; i < kPerThread; ++i) {
-            const int k = threadIdx.x + i * kBlock;
-            if (k < nz) staged[Skew(k, shift)] = op.Product(staged[Skew(k, shift)], g[i]);
-          }
-#endif
-        } else {
-          for (int i = threadIdx.x; i <= nrows; i += kBlock) CpAsync4(row_raw + i, rb.row_ptr + r0 + i);
-          CpAsyncCommit();
-#pragma unroll
-          for (int i = 0; i < kPerThread; ++i) {
-            const int k = threadIdx.x + i * kBlock;
-            if (k < nz) staged[Skew(k, shift)] = op.Load(p0 + k);
-          }
-          CpAsyncWaitAll();
-        }
-        __syncthreads();
-#pragma unroll
-        for (int u = 0; u < kPreRows; ++u) {
-          const int rr = sub + u * groups;
-          if (u * groups < nrows) {  // uniform across the CTA
-            double a = op.RowInit();
-            if (rr < nrows) {
-              const int q1 = row_raw[rr + 1] - p0;
-              for (int q = row_raw[rr] - p0 + lane; q < q1; q += t) a = op.RowAdd(a, staged[Skew(q, shift)], r0 + rr);
-            }
-            // All 32 lanes take part in the shuffles (t divides 32).
-            for (int off = t >> 1; off > 0; off >>= 1) a = op.RowMerge(a, __shfl_xor_sync(0xffffffffu, a, off));
-            if (lane == 0 && rr < nrows) OpRowFinish(op, r0 + rr, a, pre[u], red);
-          }
-        }
-        // Rows beyond the prefetched ones (only when a block has more than kPreRows * groups rows).
-        for (int base = kPreRows * groups; base < nrows; base += groups) {
-          const int rr = base + sub;
-          double a = op.RowInit();
-          if (rr < nrows) {
-            const int q1 = row_raw[rr + 1] - p0;
-            for (int q = row_raw[rr] - p0 + lane; q < q1; q += t) a = op.RowAdd(a, staged[Skew(q, shift)], r0 + rr);
-          }
-          for (int off = t >> 1; off > 0; off >>= 1) a = op.RowMerge(a, __shfl_xor_sync(0xffffffffu, a, off));
-          if (lane == 0 && rr < nrows) OpRowFinish(op, r0 + rr, a, OpRowPrefetch(op, r0 + rr), red);
-        }
-        __syncthreads();
-      }
-      b += stride;
-      r0 = nr0; r1 = nr1; p0 = np0; p1 = np1;
-      nr0 = fr0; nr1 = fr1; np0 = fp0; np1 = fp1;
-    }
-    CpAsyncWaitAll();
-  }
-  BlockReduceAndStore<Op>(red, partials);
-}
-
-// ---- finalize: partials[num_blocks][NS] -> totals[NS], fixed order, one CTA ----
-template <class Op>
-__global__ void __launch_bounds__(kBlock) finalize_kernel(const double* partials, int num_blocks, double* totals) {
-  constexpr int NS = Op::kNumSlots;
-  __shared__ double buf[kBlock];
-  for (int s = 0; s < NS; ++s) {
-    const int kind = Op::SlotKindOf(s);
-    double x = SlotIdentity(kind);
-    for (int b = threadIdx.x; b < num_blocks; b += kBlock) x = SlotCombine(kind, x, partials[static_cast<size_t>(b) * NS + s]);
-    buf[threadIdx.x] = x;
-    __syncthreads();
-    for (int off = kBlock / 2; off > 0; off >>= 1) {
-      if (threadIdx.x < off) buf[threadIdx.x] = SlotCombine(kind, buf[threadIdx.x], buf[threadIdx.x + off]);
-      __syncthreads();
-    }
-    if (threadIdx.x == 0) totals[s] = buf[0];
-    __syncthreads();
-  }
-}
-
-// Same reduction as a device function, for kernels that consume the totals themselves
-// (the step-decision kernel).  Must be called by all kBlock threads of a single CTA.
-__device__ __forceinline__ double ReducePartialsSum(const double* partials, int num_blocks, int stride, int slot, double* buf) {
-  double x = 0.0;
-  for (int b = threadIdx.x; b < num_blocks; b += kBlock) x += partials[static_cast<size_t>(b) * stride + slot];
-  buf[threadIdx.x] = x;
-  __syncthreads();
-  for (int off = kBlock / 2; off > 0; off >>= 1) {
-    if (threadIdx.x < off) buf[threadIdx.x] += buf[threadIdx.x + off];
-    __syncthreads();
-  }
-  const double r = buf[0];
-  __syncthreads();
-  return r;
-}
-
-inline int GridFor(int64_t count) {
-  int64_t g = (count + kBlock - 1) / kBlock;
-  if (g < 1) g = 1;
-  if (g > kMaxGrid) g = kMaxGrid;
-  return static_cast<int>(g);
-}
-
 }  // namespace pdlp_b200
+
+#include "pdlp_skeletons.cuh"
+
 #endif  // PDLP_B200_COMMON_CUH_
