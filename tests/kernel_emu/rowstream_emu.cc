@@ -81,6 +81,37 @@ void Run(const Op& op, const RowBlocks& rb, int grid, double* totals) {
 }
 }  // namespace
 
+// Dense skeleton: sum, max and a written vector over [0, count), then finalize_kernel and
+// ReducePartialsSum over the per-CTA partials.
+namespace {
+struct AxpyOp {
+  static constexpr int kNumSlots = 2;
+  static constexpr int SlotKindOf(int s) { return s == 0 ? kSum : kMax; }
+  const double* a; double* b; double scale; bool run;
+  bool Begin() { return run; }
+  void Apply(int64_t i, Slots<2>& acc) const {
+    b[i] = b[i] + scale * a[i];
+    acc.v[0] += b[i];
+    acc.v[1] = fmax(acc.v[1], fabs(b[i]));
+  }
+};
+}  // namespace
+
+// totals[0..1] from finalize_kernel, totals[2] = slot 0 again through ReducePartialsSum.
+extern "C" int emu_map_reduce(const double* a, double* b, long long count, double scale, int run, int grid, double* totals) {
+  std::vector<double> partials(static_cast<size_t>(grid) * 2, -1.0);
+  double* p = partials.data();
+  const AxpyOp op{a, b, scale, run != 0};
+  cuda_emu::Launch(grid, pdlp_b200::kBlock, [=]() { pdlp_b200::map_reduce_kernel<AxpyOp>(op, count, p); });
+  cuda_emu::Launch(1, pdlp_b200::kBlock, [=]() { pdlp_b200::finalize_kernel<AxpyOp>(p, grid, totals); });
+  cuda_emu::Launch(1, pdlp_b200::kBlock, [=]() {
+    __shared__ double buf[pdlp_b200::kBlock];
+    const double r = pdlp_b200::ReducePartialsSum(p, grid, 2, 0, buf);
+    if (threadIdx.x == 0) totals[2] = r;
+  });
+  return 0;
+}
+
 extern "C" int emu_is_lean() { return PDLP_ROWSTREAM_LEAN; }
 extern "C" int emu_stream_chunk() { return pdlp_b200::kStreamChunk; }
 extern "C" int emu_max_rows_per_block() { return pdlp_b200::kMaxRowsPerBlock; }

@@ -132,3 +132,24 @@ def test_lean_bank_pad_rule_tolerates_the_fast_division_error(libs, ulps):
         want_out, _ = reference(0, mat)
         out, _ = run(libs[1], 0, mat, 2, 1, ulps)
         np.testing.assert_array_equal(out, want_out)
+
+
+@pytest.mark.parametrize("count, grid", [(0, 1), (1, 1), (255, 1), (256, 2), (1000, 3), (5000, 7)])
+def test_dense_skeleton_and_its_two_stage_reduction(libs, count, grid):
+    rng = np.random.default_rng(count + grid)
+    a = rng.integers(-5, 6, max(count, 1)).astype(np.float64)
+    b0 = rng.integers(-5, 6, max(count, 1)).astype(np.float64)
+    p = lambda v: ctypes.c_void_p(v.ctypes.data)
+    lib = libs[0]
+    lib.emu_map_reduce.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_longlong, ctypes.c_double, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+    b, totals = b0.copy(), np.zeros(3)
+    assert lib.emu_map_reduce(p(a), p(b), count, 2.0, 1, grid, p(totals)) == 0
+    want = (b0 + 2.0 * a)[:count]
+    np.testing.assert_array_equal(b[:count], want)
+    assert totals[0] == want.sum() and totals[2] == want.sum()
+    assert totals[1] == (np.abs(want).max() if count else -np.inf)
+    # Begin() == false: the device-side early-out leaves the data alone and reduces to the identities
+    b, totals = b0.copy(), np.zeros(3)
+    assert lib.emu_map_reduce(p(a), p(b), count, 2.0, 0, grid, p(totals)) == 0
+    np.testing.assert_array_equal(b, b0)
+    assert totals[0] == 0.0 and totals[1] == -np.inf and totals[2] == 0.0
