@@ -15,15 +15,6 @@
 
 namespace pdlp_b200 {
 
-// Base for ops that are always active and reduce nothing.
-struct AlwaysActive {
-  __device__ bool Begin() { return true; }
-};
-struct NoSlots {
-  static constexpr int kNumSlots = 0;
-  __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
-};
-
 // An op whose row accumulator combines with max instead of + declares `bool RowCombineMax() const`.
 template <class Op, class = void>
 struct HasRowCombineMax : std::false_type {};

@@ -41,6 +41,15 @@ struct Slots {
   double v[NS > 0 ? NS : 1];
 };
 
+// Base for ops that are always active and reduce nothing.
+struct AlwaysActive {
+  __device__ bool Begin() { return true; }
+};
+struct NoSlots {
+  static constexpr int kNumSlots = 0;
+  __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
+};
+
 // Block-wide reduction of NS slots; result valid in thread 0.  Fixed tree: lanes by
 // xor-shuffle, then warps in index order.
 template <class Op>

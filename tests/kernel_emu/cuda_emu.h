@@ -102,6 +102,9 @@ inline float __fdividef(float a, float b) {
   for (int i = 0; i < std::abs(cuda_emu::fdividef_ulps); ++i) q = std::nextafterf(q, cuda_emu::fdividef_ulps > 0 ? INFINITY : -INFINITY);
   return q;
 }
+using std::isfinite;
+using std::isinf;
+using std::isnan;
 inline int min(int a, int b) { return a < b ? a : b; }
 inline int max(int a, int b) { return a > b ? a : b; }
 

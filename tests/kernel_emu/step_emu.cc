@@ -1,0 +1,98 @@
+// CPU run of the adaptive-rule trial step (K1 - K4 and the averaging flush of
+// or-tools_b200/csrc/pdlp_step_kernels.cuh) under the shim in cuda_emu.h, for
+// tests/test_kernel_emulation.py.  The launch sequence and the initial StepState restate
+// EnqueueAdaptiveTrials (pdlp_step.cu) and pdlp_b200_trial_steps (pdlp_capi.cu) for one GPU.
+#define PDLP_EMULATE 1
+#include "cuda_emu.h"
+
+#include "pdlp_step_kernels.cuh"
+
+#include <limits>
+
+namespace {
+using namespace pdlp_b200;
+
+struct HostRows {
+  const int* ptr; const int* idx; const double* val; const int* block_start; int num_blocks; int rows;
+  std::vector<int> block_nz;
+  RowBlocks View() {
+    block_nz.resize(num_blocks + 1);
+    for (int b = 0; b <= num_blocks; ++b) block_nz[b] = ptr[block_start[b]];
+    return RowBlocks{ptr, block_start, block_nz.data(), num_blocks, rows};
+  }
+};
+
+template <class Op>
+int LaunchMap(const Op& op, int64_t count, double* partials) {
+  const int grid = GridFor(count);
+  cuda_emu::Launch(grid, kBlock, [=]() { map_reduce_kernel<Op>(op, count, partials); });
+  return grid;
+}
+template <class Op>
+int LaunchRows(const Op& op, const RowBlocks& rb, int max_grid, double* partials) {
+  const int grid = std::max(1, std::min(rb.num_blocks, max_grid));
+  cuda_emu::Launch(grid, kBlock, [=]() { rowstream_kernel<Op>(op, rb, partials); });
+  return grid;
+}
+}  // namespace
+
+// x, y: in = start point, out = current iterate after the last accepted step.  q may be null (LP).
+// state_out = {step_size, iterations_completed, num_rejected_steps, last_movement, last_nonlinearity,
+//              avg_weight_sum, active, total_trials}.
+extern "C" int emu_adaptive_trials(int n, int m, const int* csr_ptr, const int* csr_idx, const double* csr_val, const int* csr_blocks, int csr_num_blocks,
+                                   const int* csc_ptr, const int* csc_idx, const double* csc_val, const int* csc_blocks, int csc_num_blocks, const double* c,
+                                   const double* q, const double* vlb, const double* vub, const double* clb, const double* cub, double* x, double* y,
+                                   double* avg_x, double* avg_y, double step_size, double primal_weight, int trials, int constant_step, int max_grid,
+                                   int defer_async, double* state_out) {
+  cuda_emu::defer_async = defer_async != 0;
+  HostRows csr{csr_ptr, csr_idx, csr_val, csr_blocks, csr_num_blocks, m, {}};
+  HostRows csc{csc_ptr, csc_idx, csc_val, csc_blocks, csc_num_blocks, n, {}};
+  const RowBlocks by_row = csr.View(), by_col = csc.View();
+  std::vector<double> xb[2] = {std::vector<double>(x, x + n), std::vector<double>(n, 0.0)};
+  std::vector<double> yb[2] = {std::vector<double>(y, y + m), std::vector<double>(m, 0.0)};
+  std::vector<double> kty[2] = {std::vector<double>(n, 0.0), std::vector<double>(n, 0.0)};
+  std::vector<double> xbar(n, 0.0), ax(n, 0.0), ay(m, 0.0);
+  for (int j = 0; j < n; ++j) {  // K^T y of the start point (pdlp_capi.cu: RowDot over the CSC copy)
+    double a = 0.0;
+    for (int k = csc_ptr[j]; k < csc_ptr[j + 1]; ++k) a += csc_val[k] * y[csc_idx[k]];
+    kty[0][j] = a;
+  }
+  StepState state{};
+  state.active = 1;
+  state.target_iteration = 2147483647;
+  state.step_size = step_size;
+  state.primal_weight = primal_weight;
+  state.ratio_last_two_step_sizes = 1.0;
+  state.kkt_pass_limit = std::numeric_limits<double>::infinity();
+  state.passes_per_rejected_step = 1.0;
+  state.reduction_exponent = 0.3;
+  state.growth_exponent = 0.6;
+  state.mp_tau = -1.0;
+  state.mp_new_tau = -1.0;
+  StepState* st = &state;
+
+  std::vector<double> part[3] = {std::vector<double>(kMaxGrid * 2), std::vector<double>(kMaxGrid * 2), std::vector<double>(kMaxGrid * 2)};
+  double* p0 = part[0].data(); double* p1 = part[1].data(); double* p2 = part[2].data();
+  PrimalStepOp k1{{}, st, xb[0].data(), xb[1].data(), kty[0].data(), kty[1].data(), c, q, vlb, vub, xbar.data(), 1, ax.data()};
+  DualStepOp k2{{}, st, csr_val, csr_idx, xbar.data(), yb[0].data(), yb[1].data(), clb, cub, 0, ay.data()};
+  KtyStepOp k3{st, csc_val, csc_idx, yb[0].data(), yb[1].data(), xb[0].data(), xb[1].data(), kty[0].data(), kty[1].data()};
+  AverageOp flush{{}, st, xb[0].data(), xb[1].data(), yb[0].data(), yb[1].data(), ax.data(), ay.data(), n, 1};
+  for (int t = 0; t < trials; ++t) {
+    const int g1 = LaunchMap(k1, n, p0);
+    const int g2 = LaunchRows(k2, by_row, max_grid, p1);
+    const int g3 = LaunchRows(k3, by_col, max_grid, p2);
+    cuda_emu::Launch(1, kBlock, [=]() { decide_adaptive_kernel(st, p0, g1, p1, g2, p2, g3, constant_step ? 1 : 0); });
+  }
+  if (trials > 0) {
+    LaunchMap(flush, static_cast<int64_t>(n) + m, p0);
+    cuda_emu::Launch(1, 1, [=]() { finish_average_kernel(st); });
+  }
+  std::copy(xb[state.cur].begin(), xb[state.cur].end(), x);
+  std::copy(yb[state.cur].begin(), yb[state.cur].end(), y);
+  std::copy(ax.begin(), ax.end(), avg_x);
+  std::copy(ay.begin(), ay.end(), avg_y);
+  state_out[0] = state.step_size; state_out[1] = state.iterations_completed; state_out[2] = state.num_rejected_steps;
+  state_out[3] = state.last_movement; state_out[4] = state.last_nonlinearity; state_out[5] = state.avg_weight_sum;
+  state_out[6] = state.active; state_out[7] = static_cast<double>(state.total_trials);
+  return 0;
+}

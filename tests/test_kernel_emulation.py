@@ -153,3 +153,136 @@ def test_dense_skeleton_and_its_two_stage_reduction(libs, count, grid):
     assert lib.emu_map_reduce(p(a), p(b), count, 2.0, 0, grid, p(totals)) == 0
     np.testing.assert_array_equal(b, b0)
     assert totals[0] == 0.0 and totals[1] == -np.inf and totals[2] == 0.0
+
+
+# ---- the adaptive trial step (K1 - K4 + averaging) against a restatement of the reference ----
+
+def _build_step(lean):
+    out = os.path.join(BUILD, f"step_emu_lean{lean}.so")
+    sources = [os.path.join(EMU, "step_emu.cc"), os.path.join(EMU, "cuda_emu.h"), os.path.join(CSRC, "pdlp_skeletons.cuh"),
+               os.path.join(CSRC, "pdlp_step_kernels.cuh"), os.path.join(CSRC, "pdlp_step_state.h")]
+    os.makedirs(BUILD, exist_ok=True)
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(s) for s in sources):
+        subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-Wno-attributes",
+                        f"-DPDLP_ROWSTREAM_LEAN={lean}", "-I" + EMU, "-I" + CSRC, sources[0], "-o", out], check=True)
+    return ctypes.CDLL(out)
+
+
+@pytest.fixture(scope="module")
+def step_libs():
+    return {0: _build_step(0), 1: _build_step(1)}
+
+
+def reference_adaptive_trials(K, c, q, vlb, vub, clb, cub, x, y, step, w, trials):
+    """Solver::TakeAdaptiveStep (primal_dual_hybrid_gradient.cc:2295-2376) one trial at a time, with
+    ComputeNextPrimalSolution (:1659-1705), ComputeNextDualSolution (:1707-1748), ComputeMovement
+    (:1750-1759), ComputeNonlinearity (:1761-1771) and ShardedWeightedAverage::Add
+    (sharded_optimization_utils.cc:54-66).  Dense numpy; K is a scipy matrix."""
+    x, y = x.copy(), y.copy()
+    kty = K.T @ y
+    avg_x, avg_y, weight_sum = np.zeros_like(x), np.zeros_like(y), 0.0
+    completed = rejected = inner = 0
+    movement = nonlinearity = 0.0
+    for _ in range(trials):
+        tau, sigma = step / w, step * w
+        t = x - tau * (c - kty)
+        if q is not None:
+            t = t / (1.0 + tau * q)
+        xn = np.minimum(np.maximum(t, vlb), vub)
+        dx = xn - x
+        temp = y - sigma * (K @ (xn + dx))
+        yn = np.maximum(np.minimum(0.0, temp + sigma * cub), temp + sigma * clb)
+        dy = yn - y
+        movement = 0.5 * w * (dx @ dx) + 0.5 / w * (dy @ dy)
+        assert 0.0 < movement < 1e100
+        ktyn = K.T @ yn
+        nonlinearity = -(dx @ (ktyn - kty))
+        limit = movement / nonlinearity if nonlinearity > 0 else np.inf
+        accepted = step <= limit
+        total = rejected + inner + completed + 1
+        if accepted:
+            x, y, kty = xn, yn, ktyn
+            ratio = step / (weight_sum + step)
+            avg_x += ratio * (x - avg_x)
+            avg_y += ratio * (y - avg_y)
+            weight_sum += step
+        first = limit if np.isinf(limit) else (1 - (total + 1.0) ** -0.3) * limit
+        second = (1 + (total + 1.0) ** -0.6) * step
+        step = min(first, second)
+        if accepted:
+            rejected += inner  # num_rejected_steps_ += inner_iterations - 1 after the loop
+            inner = 0
+            completed += 1
+        else:
+            inner += 1
+    return dict(x=x, y=y, avg_x=avg_x, avg_y=avg_y, step=step, completed=completed, rejected=rejected + inner, movement=movement,
+                nonlinearity=nonlinearity, weight_sum=weight_sum)
+
+
+def emulated_adaptive_trials(lib, K, c, q, vlb, vub, clb, cub, x, y, step, w, trials, max_grid=3, defer=0):
+    import scipy.sparse as sp
+    csr, csc = sp.csr_matrix(K), sp.csc_matrix(K)
+    csr.sort_indices(); csc.sort_indices()
+    m, n = K.shape
+    i32 = lambda a: np.ascontiguousarray(a, dtype=np.int32)
+    f64 = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+    arrays = dict(rp=i32(csr.indptr), ri=i32(csr.indices), rv=f64(csr.data), cp=i32(csc.indptr), ci=i32(csc.indices), cv=f64(csc.data))
+    rb, _, _ = pdlp_b200.work_blocks(arrays["rp"])
+    cb, _, _ = pdlp_b200.work_blocks(arrays["cp"])
+    rb, cb = i32(rb), i32(cb)
+    xo, yo, ax, ay, st = f64(x).copy(), f64(y).copy(), np.zeros(n), np.zeros(m), np.zeros(8)
+    p = lambda a: ctypes.c_void_p(a.ctypes.data) if a is not None else ctypes.c_void_p(None)
+    vecs = [f64(c), None if q is None else f64(q), f64(vlb), f64(vub), f64(clb), f64(cub)]
+    rc = lib.emu_adaptive_trials(n, m, p(arrays["rp"]), p(arrays["ri"]), p(arrays["rv"]), p(rb), len(rb) - 1, p(arrays["cp"]), p(arrays["ci"]), p(arrays["cv"]),
+                                 p(cb), len(cb) - 1, *[p(v) for v in vecs], p(xo), p(yo), p(ax), p(ay), ctypes.c_double(step), ctypes.c_double(w), trials, 0,
+                                 max_grid, defer, p(st))
+    assert rc == 0
+    return dict(x=xo, y=yo, avg_x=ax, avg_y=ay, step=st[0], completed=int(st[1]), rejected=int(st[2]), movement=st[3], nonlinearity=st[4], weight_sum=st[5],
+                active=int(st[6]), total_trials=int(st[7]))
+
+
+def step_problem(seed, qp):
+    import scipy.sparse as sp
+    rng = np.random.default_rng(seed)
+    n, m = 700, 420
+    K = sp.random(m, n, density=0.02, random_state=seed, data_rvs=lambda k: rng.standard_normal(k)).tocsr()
+    c = rng.standard_normal(n)
+    q = rng.uniform(0.0, 2.0, n) if qp else None
+    vlb = np.where(rng.random(n) < 0.3, -np.inf, rng.uniform(-2, 0, n))
+    vub = np.where(rng.random(n) < 0.3, np.inf, rng.uniform(0, 2, n))
+    mid = rng.standard_normal(m)
+    clb = np.where(rng.random(m) < 0.3, -np.inf, mid - rng.uniform(0, 1, m))
+    cub = np.where(rng.random(m) < 0.3, np.inf, mid + rng.uniform(0, 1, m))
+    eq = rng.random(m) < 0.2
+    clb[eq] = cub[eq] = mid[eq]
+    x0 = np.minimum(np.maximum(rng.standard_normal(n), vlb), vub)
+    y0 = rng.standard_normal(m) * 0.1
+    y0 = np.where(np.isinf(clb), np.minimum(y0, 0.0), y0)
+    y0 = np.where(np.isinf(cub), np.maximum(y0, 0.0), y0)
+    return K, c, q, vlb, vub, clb, cub, x0, y0
+
+
+@pytest.mark.parametrize("lean", [0, 1])
+@pytest.mark.parametrize("qp", [False, True])
+def test_adaptive_trial_steps_follow_the_reference_step_rule(step_libs, qp, lean):
+    prob = step_problem(2 if not qp else 6, qp)
+    # a first step far too long: the rule must reject, shrink, then accept and grow again
+    step, w, trials = 50.0, 0.2, 14
+    want = reference_adaptive_trials(*prob, step, w, trials)
+    assert want["rejected"] >= 2 and want["completed"] >= 8
+    got = emulated_adaptive_trials(step_libs[lean], *prob, step, w, trials, defer=lean)
+    assert (got["completed"], got["rejected"]) == (want["completed"], want["rejected"])
+    assert got["active"] == 1 and got["total_trials"] == trials
+    for key in ("x", "y", "avg_x", "avg_y"):
+        np.testing.assert_allclose(got[key], want[key], rtol=1e-11, atol=1e-12, err_msg=key)
+    for key in ("step", "movement", "nonlinearity", "weight_sum"):
+        np.testing.assert_allclose(got[key], want[key], rtol=1e-10, err_msg=key)
+
+
+def test_lean_and_default_steps_are_bit_identical(step_libs):
+    prob = step_problem(9, False)
+    a = emulated_adaptive_trials(step_libs[0], *prob, 0.5, 1.0, 6)
+    b = emulated_adaptive_trials(step_libs[1], *prob, 0.5, 1.0, 6, defer=1)
+    for key in ("x", "y", "avg_x", "avg_y"):
+        np.testing.assert_array_equal(a[key], b[key])
+    assert a["step"] == b["step"] and a["movement"] == b["movement"]
