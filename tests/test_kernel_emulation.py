@@ -173,11 +173,12 @@ def step_libs():
     return {0: _build_step(0), 1: _build_step(1)}
 
 
-def reference_adaptive_trials(K, c, q, vlb, vub, clb, cub, x, y, step, w, trials):
+def reference_adaptive_trials(K, c, q, vlb, vub, clb, cub, x, y, step, w, trials, constant=False):
     """Solver::TakeAdaptiveStep (primal_dual_hybrid_gradient.cc:2295-2376) one trial at a time, with
     ComputeNextPrimalSolution (:1659-1705), ComputeNextDualSolution (:1707-1748), ComputeMovement
     (:1750-1759), ComputeNonlinearity (:1761-1771) and ShardedWeightedAverage::Add
-    (sharded_optimization_utils.cc:54-66).  Dense numpy; K is a scipy matrix."""
+    (sharded_optimization_utils.cc:54-66).  constant=True: TakeConstantSizeStep (:2378-2406), every
+    step accepted at the same size.  Dense numpy; K is a scipy matrix."""
     x, y = x.copy(), y.copy()
     kty = K.T @ y
     avg_x, avg_y, weight_sum = np.zeros_like(x), np.zeros_like(y), 0.0
@@ -198,7 +199,7 @@ def reference_adaptive_trials(K, c, q, vlb, vub, clb, cub, x, y, step, w, trials
         ktyn = K.T @ yn
         nonlinearity = -(dx @ (ktyn - kty))
         limit = movement / nonlinearity if nonlinearity > 0 else np.inf
-        accepted = step <= limit
+        accepted = constant or step <= limit
         total = rejected + inner + completed + 1
         if accepted:
             x, y, kty = xn, yn, ktyn
@@ -208,7 +209,8 @@ def reference_adaptive_trials(K, c, q, vlb, vub, clb, cub, x, y, step, w, trials
             weight_sum += step
         first = limit if np.isinf(limit) else (1 - (total + 1.0) ** -0.3) * limit
         second = (1 + (total + 1.0) ** -0.6) * step
-        step = min(first, second)
+        if not constant:
+            step = min(first, second)
         if accepted:
             rejected += inner  # num_rejected_steps_ += inner_iterations - 1 after the loop
             inner = 0
@@ -219,7 +221,7 @@ def reference_adaptive_trials(K, c, q, vlb, vub, clb, cub, x, y, step, w, trials
                 nonlinearity=nonlinearity, weight_sum=weight_sum)
 
 
-def emulated_adaptive_trials(lib, K, c, q, vlb, vub, clb, cub, x, y, step, w, trials, max_grid=3, defer=0):
+def emulated_adaptive_trials(lib, K, c, q, vlb, vub, clb, cub, x, y, step, w, trials, max_grid=3, defer=0, constant=False):
     import scipy.sparse as sp
     csr, csc = sp.csr_matrix(K), sp.csc_matrix(K)
     csr.sort_indices(); csc.sort_indices()
@@ -234,7 +236,7 @@ def emulated_adaptive_trials(lib, K, c, q, vlb, vub, clb, cub, x, y, step, w, tr
     p = lambda a: ctypes.c_void_p(a.ctypes.data) if a is not None else ctypes.c_void_p(None)
     vecs = [f64(c), None if q is None else f64(q), f64(vlb), f64(vub), f64(clb), f64(cub)]
     rc = lib.emu_adaptive_trials(n, m, p(arrays["rp"]), p(arrays["ri"]), p(arrays["rv"]), p(rb), len(rb) - 1, p(arrays["cp"]), p(arrays["ci"]), p(arrays["cv"]),
-                                 p(cb), len(cb) - 1, *[p(v) for v in vecs], p(xo), p(yo), p(ax), p(ay), ctypes.c_double(step), ctypes.c_double(w), trials, 0,
+                                 p(cb), len(cb) - 1, *[p(v) for v in vecs], p(xo), p(yo), p(ax), p(ay), ctypes.c_double(step), ctypes.c_double(w), trials, int(constant),
                                  max_grid, defer, p(st))
     assert rc == 0
     return dict(x=xo, y=yo, avg_x=ax, avg_y=ay, step=st[0], completed=int(st[1]), rejected=int(st[2]), movement=st[3], nonlinearity=st[4], weight_sum=st[5],
@@ -286,3 +288,14 @@ def test_lean_and_default_steps_are_bit_identical(step_libs):
     for key in ("x", "y", "avg_x", "avg_y"):
         np.testing.assert_array_equal(a[key], b[key])
     assert a["step"] == b["step"] and a["movement"] == b["movement"]
+
+
+def test_constant_size_steps_follow_the_reference(step_libs):
+    prob = step_problem(3, False)
+    step, w, trials = 0.05, 0.7, 6
+    want = reference_adaptive_trials(*prob, step, w, trials, constant=True)
+    got = emulated_adaptive_trials(step_libs[0], *prob, step, w, trials, constant=True)
+    assert (got["completed"], got["rejected"], got["step"]) == (trials, 0, step)
+    for key in ("x", "y", "avg_x", "avg_y"):
+        np.testing.assert_allclose(got[key], want[key], rtol=1e-11, atol=1e-12, err_msg=key)
+    np.testing.assert_allclose(got["weight_sum"], want["weight_sum"], rtol=1e-12)
