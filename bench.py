@@ -20,6 +20,7 @@ of K, one NCCL all-reduce of the partial K x (m doubles) plus scalar all-reduces
 """
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -289,10 +290,14 @@ def main():
         t_begin = time.time()
         x2, y2, st2, seconds, launches = dp.trial_steps(args.steps, st["step_size"], w0, x, y)
         barrier()
-        extra_runs = 0
-        while time.time() - t_begin < 0.6:
+        # Sharded trial steps are collective: every rank must repeat them the same number of times, so
+        # the count comes from rank 0's clock, not from each rank's own.
+        extra = torch.tensor([max(0, min(50, math.ceil((0.6 - (time.time() - t_begin)) / max(seconds, 1e-3))))], dtype=torch.int64, device="cuda")
+        if world > 1:
+            dist.broadcast(extra, src=0)
+        extra_runs = int(extra.item())
+        for _ in range(extra_runs):
             dp.trial_steps(args.steps, st["step_size"], w0, x, y)
-            extra_runs += 1
     t = torch.tensor([seconds], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
