@@ -299,3 +299,28 @@ def test_constant_size_steps_follow_the_reference(step_libs):
     for key in ("x", "y", "avg_x", "avg_y"):
         np.testing.assert_allclose(got[key], want[key], rtol=1e-11, atol=1e-12, err_msg=key)
     np.testing.assert_allclose(got["weight_sum"], want["weight_sum"], rtol=1e-12)
+
+
+# ---- shared-memory protocol under a race detector ----
+
+@pytest.mark.parametrize("lean", [0, 1])
+def test_rowstream_shared_memory_protocol_is_race_free(lean):
+    """tests/kernel_emu/race_check.cc under ThreadSanitizer: with __syncthreads as the only
+    cross-thread ordering, every conflicting pair of accesses to the staged products, the row offsets
+    and the single index buffer (this block's indices read, the next block's copied into the same
+    positions) must be separated by a barrier, in both cp.async orders.  Removing one barrier from the
+    kernel makes this fail (checked by hand when the test was written)."""
+    exe = os.path.join(BUILD, f"race_check_lean{lean}")
+    src = os.path.join(EMU, "race_check.cc")
+    os.makedirs(BUILD, exist_ok=True)
+    build = subprocess.run(["g++", "-std=c++20", "-O1", "-g", "-fsanitize=thread", "-pthread", "-Wno-unknown-pragmas", "-Wno-attributes",
+                            f"-DPDLP_ROWSTREAM_LEAN={lean}", "-I" + EMU, "-I" + CSRC, src, "-o", exe], capture_output=True, text=True)
+    if build.returncode != 0 and ("tsan" in build.stderr.lower() or "sanitize" in build.stderr.lower()):
+        pytest.skip("ThreadSanitizer runtime not available: " + build.stderr.strip().splitlines()[-1])
+    assert build.returncode == 0, build.stderr
+    run = subprocess.run([exe], capture_output=True, text=True, timeout=600)
+    text = run.stdout + run.stderr
+    if "FATAL: ThreadSanitizer" in text:
+        pytest.skip("ThreadSanitizer cannot run here: " + text.strip().splitlines()[0])
+    assert "ThreadSanitizer" not in text, text[:4000]
+    assert run.returncode == 0 and "wrong rows: 0" in text, text[:2000]
