@@ -96,3 +96,68 @@ extern "C" int emu_adaptive_trials(int n, int m, const int* csr_ptr, const int* 
   state_out[6] = state.active; state_out[7] = static_cast<double>(state.total_trials);
   return 0;
 }
+
+// Malitsky-Pock rule: the launch sequence of EnqueueMalitskyPockTrials (pdlp_step.cu) for one GPU.
+// params = {step_size_downscaling_factor, linesearch_contraction_factor, step_size_interpolation}.
+// state_out as above, with [5] = primal average weight sum, [8] = dual average weight sum,
+// [9] = ratio_last_two_step_sizes.
+extern "C" int emu_malitsky_pock_trials(int n, int m, const int* csr_ptr, const int* csr_idx, const double* csr_val, const int* csr_blocks, int csr_num_blocks,
+                                        const int* csc_ptr, const int* csc_idx, const double* csc_val, const int* csc_blocks, int csc_num_blocks, const double* c,
+                                        const double* q, const double* vlb, const double* vub, const double* clb, const double* cub, double* x, double* y,
+                                        double* avg_x, double* avg_y, double step_size, double primal_weight, const double* params, int trials, int max_grid,
+                                        double* state_out) {
+  cuda_emu::defer_async = false;
+  HostRows csr{csr_ptr, csr_idx, csr_val, csr_blocks, csr_num_blocks, m, {}};
+  HostRows csc{csc_ptr, csc_idx, csc_val, csc_blocks, csc_num_blocks, n, {}};
+  const RowBlocks by_row = csr.View(), by_col = csc.View();
+  std::vector<double> xb[2] = {std::vector<double>(x, x + n), std::vector<double>(n, 0.0)};
+  std::vector<double> yb[2] = {std::vector<double>(y, y + m), std::vector<double>(m, 0.0)};
+  std::vector<double> kty[2] = {std::vector<double>(n, 0.0), std::vector<double>(n, 0.0)};
+  std::vector<double> xbar(n, 0.0), ax(n, 0.0), ay(m, 0.0);
+  for (int j = 0; j < n; ++j) {
+    double a = 0.0;
+    for (int k = csc_ptr[j]; k < csc_ptr[j + 1]; ++k) a += csc_val[k] * y[csc_idx[k]];
+    kty[0][j] = a;
+  }
+  StepState state{};
+  state.active = 1;
+  state.target_iteration = 2147483647;
+  state.step_size = step_size;
+  state.primal_weight = primal_weight;
+  state.ratio_last_two_step_sizes = 1.0;
+  state.kkt_pass_limit = std::numeric_limits<double>::infinity();
+  state.passes_per_rejected_step = 1.0;
+  state.reduction_exponent = 0.3;
+  state.growth_exponent = 0.6;
+  state.mp_downscaling = params[0];
+  state.mp_contraction = params[1];
+  state.mp_interpolation = params[2];
+  state.mp_tau = -1.0;
+  state.mp_new_tau = -1.0;
+  StepState* st = &state;
+  std::vector<double> part[3] = {std::vector<double>(kMaxGrid * 2), std::vector<double>(kMaxGrid * 2), std::vector<double>(kMaxGrid * 2)};
+  double* p0 = part[0].data(); double* p1 = part[1].data(); double* p2 = part[2].data();
+  PrimalStepOp k1{{}, st, xb[0].data(), xb[1].data(), kty[0].data(), kty[1].data(), c, q, vlb, vub, xbar.data(), 0, nullptr};
+  ExtrapolateOp kx{{}, st, xb[0].data(), xb[1].data(), xbar.data()};
+  DualStepOp k2{{}, st, csr_val, csr_idx, xbar.data(), yb[0].data(), yb[1].data(), clb, cub, 0, nullptr};
+  KtyStepOp k3{st, csc_val, csc_idx, yb[0].data(), yb[1].data(), xb[0].data(), xb[1].data(), kty[0].data(), kty[1].data()};
+  AverageOp k5{{}, st, xb[0].data(), xb[1].data(), yb[0].data(), yb[1].data(), ax.data(), ay.data(), n, 0};
+  for (int t = 0; t < trials; ++t) {
+    cuda_emu::Launch(1, 1, [=]() { mp_begin_kernel(st); });
+    const int g1 = LaunchMap(k1, n, p0);
+    LaunchMap(kx, n, p1);
+    const int g2 = LaunchRows(k2, by_row, max_grid, p1);
+    const int g3 = LaunchRows(k3, by_col, max_grid, p2);
+    cuda_emu::Launch(1, kBlock, [=]() { decide_mp_kernel(st, p0, g1, p1, g2, p2, g3); });
+    LaunchMap(k5, static_cast<int64_t>(n) + m, p0);
+  }
+  std::copy(xb[state.cur].begin(), xb[state.cur].end(), x);
+  std::copy(yb[state.cur].begin(), yb[state.cur].end(), y);
+  std::copy(ax.begin(), ax.end(), avg_x);
+  std::copy(ay.begin(), ay.end(), avg_y);
+  state_out[0] = state.step_size; state_out[1] = state.iterations_completed; state_out[2] = state.num_rejected_steps;
+  state_out[3] = state.last_movement; state_out[4] = state.last_nonlinearity; state_out[5] = state.avg_weight_sum;
+  state_out[6] = state.active; state_out[7] = static_cast<double>(state.total_trials);
+  state_out[8] = state.avg_weight_sum_dual; state_out[9] = state.ratio_last_two_step_sizes;
+  return 0;
+}

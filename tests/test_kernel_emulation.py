@@ -301,6 +301,75 @@ def test_constant_size_steps_follow_the_reference(step_libs):
     np.testing.assert_allclose(got["weight_sum"], want["weight_sum"], rtol=1e-12)
 
 
+def reference_malitsky_pock_trials(K, c, q, vlb, vub, clb, cub, x, y, step, w, trials, downscaling=0.7, contraction=0.99, interpolation=1.0):
+    """Solver::TakeMalitskyPockStep (primal_dual_hybrid_gradient.cc:2211-2293), one dual trial at a time."""
+    x, y = x.copy(), y.copy()
+    kty = K.T @ y
+    avg_x, avg_y, wx, wy = np.zeros_like(x), np.zeros_like(y), 0.0, 0.0
+    completed = rejected = 0
+    ratio = 1.0
+    new_tau = None
+    for _ in range(trials):
+        tau = step / w
+        if new_tau is None:  # a new outer iteration
+            t = x - tau * (c - kty)
+            if q is not None:
+                t = t / (1.0 + tau * q)
+            xn = np.minimum(np.maximum(t, vlb), vub)
+            dx = xn - x
+            new_tau = tau * (1 + interpolation * (np.sqrt(1 + ratio) - 1))
+        theta = new_tau / tau
+        sigma = w * w * new_tau
+        temp = y - sigma * (K @ (xn + theta * dx))
+        yn = np.maximum(np.minimum(0.0, temp + sigma * cub), temp + sigma * clb)
+        dy = yn - y
+        ktyn = K.T @ yn
+        if w * new_tau * np.linalg.norm(ktyn - kty) <= contraction * np.linalg.norm(dy):
+            step, ratio = new_tau * w, theta
+            if wx == 0.0:
+                weight = new_tau * theta
+                avg_x += weight / (wx + weight) * (x - avg_x)
+                wx += weight
+            x, y, kty = xn, yn, ktyn
+            avg_x += new_tau / (wx + new_tau) * (x - avg_x)
+            wx += new_tau
+            avg_y += new_tau / (wy + new_tau) * (y - avg_y)
+            wy += new_tau
+            completed += 1
+            new_tau = None
+        else:
+            new_tau = downscaling * new_tau
+            rejected += 1
+    return dict(x=x, y=y, avg_x=avg_x, avg_y=avg_y, step=step, completed=completed, rejected=rejected, wx=wx, wy=wy, ratio=ratio)
+
+
+def test_malitsky_pock_steps_follow_the_reference(step_libs):
+    import scipy.sparse as sp
+    K, c, q, vlb, vub, clb, cub, x0, y0 = prob = step_problem(4, False)
+    step, w, trials = 0.08, 0.8, 16
+    want = reference_malitsky_pock_trials(*prob, step, w, trials)
+    assert want["rejected"] >= 2 and want["completed"] >= 6
+    lib = step_libs[0]
+    csr, csc = sp.csr_matrix(K), sp.csc_matrix(K)
+    csr.sort_indices(); csc.sort_indices()
+    m, n = K.shape
+    i32 = lambda a: np.ascontiguousarray(a, dtype=np.int32)
+    f64 = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+    rp, ri, rv, cp, ci, cv = i32(csr.indptr), i32(csr.indices), f64(csr.data), i32(csc.indptr), i32(csc.indices), f64(csc.data)
+    rb, cb = i32(pdlp_b200.work_blocks(rp)[0]), i32(pdlp_b200.work_blocks(cp)[0])
+    xo, yo, ax, ay, st = f64(x0).copy(), f64(y0).copy(), np.zeros(n), np.zeros(m), np.zeros(10)
+    params = np.array([0.7, 0.99, 1.0])
+    p = lambda a: ctypes.c_void_p(a.ctypes.data) if a is not None else ctypes.c_void_p(None)
+    rc = lib.emu_malitsky_pock_trials(n, m, p(rp), p(ri), p(rv), p(rb), len(rb) - 1, p(cp), p(ci), p(cv), p(cb), len(cb) - 1, p(f64(c)), p(None), p(f64(vlb)),
+                                      p(f64(vub)), p(f64(clb)), p(f64(cub)), p(xo), p(yo), p(ax), p(ay), ctypes.c_double(step), ctypes.c_double(w), p(params),
+                                      trials, 3, p(st))
+    assert rc == 0
+    assert (int(st[1]), int(st[2])) == (want["completed"], want["rejected"])
+    for got, key in ((xo, "x"), (yo, "y"), (ax, "avg_x"), (ay, "avg_y")):
+        np.testing.assert_allclose(got, want[key], rtol=1e-11, atol=1e-12, err_msg=key)
+    np.testing.assert_allclose([st[0], st[5], st[8], st[9]], [want["step"], want["wx"], want["wy"], want["ratio"]], rtol=1e-12)
+
+
 # ---- shared-memory protocol under a race detector ----
 
 @pytest.mark.parametrize("lean", [0, 1])
