@@ -447,6 +447,55 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
   BlockReduceAndStore<Op>(red, partials);
 }
 
+// ---- the two phases of a column-sharded pass over the CSR block (launched by
+// pdlp_launch.cuh:EnqueueRows around the all-reduce of the shared rows' sums) ----
+// An op whose row accumulator combines with max instead of + declares `bool RowCombineMax() const`.
+template <class Op, class = void>
+struct HasRowCombineMax : std::false_type {};
+template <class Op>
+struct HasRowCombineMax<Op, std::void_t<decltype(std::declval<const Op&>().RowCombineMax())>> : std::true_type {};
+template <class Op>
+inline bool RowCombineIsMax(const Op& op) {
+  if constexpr (HasRowCombineMax<Op>::value) return op.RowCombineMax();
+  else return false;
+}
+
+// Phase 1 of a sharded CSR pass: this rank's part of every row sum, stored.
+template <class Op>
+struct PartialRowOp {
+  static constexpr int kNumSlots = 0;
+  __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
+  Op op;
+  double* out;
+  __device__ bool Begin() { return op.Begin(); }
+  __device__ double Load(int64_t k) const { return op.Load(k); }
+  template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
+  __device__ const int* IndexAddress(int64_t k) const { return op.IndexAddress(k); }
+  template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
+  __device__ const double* ValueAddress(int64_t k) const { return op.ValueAddress(k); }
+  template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
+  __device__ double Gather(int index) const { return op.Gather(index); }
+  template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
+  __device__ double Product(double value, double gathered) const { return op.Product(value, gathered); }
+  __device__ double RowInit() const { return op.RowInit(); }
+  __device__ double RowAdd(double acc, double staged, int row) const { return op.RowAdd(acc, staged, row); }
+  __device__ double RowMerge(double a, double b) const { return op.RowMerge(a, b); }
+  __device__ void RowFinish(int row, double acc, Slots<0>&) const { out[row] = acc; }
+};
+// Phase 2: the op's epilogue on the all-reduced row sums.
+template <class Op>
+struct FinishRowOp {
+  static constexpr int kNumSlots = Op::kNumSlots;
+  __host__ __device__ static constexpr int SlotKindOf(int s) { return Op::SlotKindOf(s); }
+  Op op;
+  const double* sums;
+  __device__ bool Begin() { return op.Begin(); }
+  __device__ void Apply(int64_t i, Slots<Op::kNumSlots>& acc) const {
+    const int row = static_cast<int>(i);
+    OpRowFinish(op, row, sums[i], OpRowPrefetch(op, row), acc);
+  }
+};
+
 // ---- finalize: partials[num_blocks][NS] -> totals[NS], fixed order, one CTA ----
 template <class Op>
 __global__ void __launch_bounds__(kBlock) finalize_kernel(const double* partials, int num_blocks, double* totals) {

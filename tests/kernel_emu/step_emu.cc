@@ -161,3 +161,62 @@ extern "C" int emu_malitsky_pock_trials(int n, int m, const int* csr_ptr, const 
   state_out[8] = state.avg_weight_sum_dual; state_out[9] = state.ratio_last_two_step_sizes;
   return 0;
 }
+
+// ---- column-sharded dual step (K2), one rank at a time ----
+// The two device phases of pdlp_launch.cuh:EnqueueRows for a CSR block cut into shared rows
+// [0, cut_row) and private rows; the test sums the ranks' partial row sums in between (the
+// all-reduce).  block_start comes from pdlp_b200.work_blocks(ptr, cut_row); cut_block = number of
+// work blocks before the cut (0: no shared rows, num_blocks: all shared).
+namespace {
+StepState FreshState(double step_size, double primal_weight) {
+  StepState state{};
+  state.active = 1;
+  state.target_iteration = 2147483647;
+  state.step_size = step_size;
+  state.primal_weight = primal_weight;
+  state.ratio_last_two_step_sizes = 1.0;
+  state.mp_tau = -1.0;
+  state.mp_new_tau = -1.0;
+  return state;
+}
+RowBlocks ViewOfBlocks(const RowBlocks& all, int first, int count) {  // pdlp_matrix.cuh: SparseRows::ViewOfBlocks
+  return RowBlocks{all.row_ptr, all.block_start + first, all.block_nz + first, count, all.rows};
+}
+}  // namespace
+
+// Phase 1: this rank's part of the shared rows' sums of K xbar -> sums[cut_row].
+extern "C" int emu_sharded_dual_partial(int m_local, const int* ptr, const int* idx, const double* val, const int* block_start, int num_blocks, int cut_block,
+                                        const double* xbar, double* y0, double* y1, const double* clb, const double* cub, double step_size, double primal_weight,
+                                        int max_grid, double* sums) {
+  cuda_emu::defer_async = false;
+  HostRows csr{ptr, idx, val, block_start, num_blocks, m_local, {}};
+  const RowBlocks all = csr.View();
+  StepState state = FreshState(step_size, primal_weight);
+  if (cut_block > 0) {
+    const DualStepOp op{{}, &state, val, idx, xbar, y0, y1, clb, cub, 0, nullptr};
+    std::vector<double> partials(kMaxGrid, 0.0);
+    LaunchRows(PartialRowOp<DualStepOp>{op, sums}, ViewOfBlocks(all, 0, cut_block), max_grid, partials.data());
+  }
+  return 0;
+}
+
+// Phase 2: private rows through the op's own epilogue inside the row-stream kernel, shared rows
+// through FinishRowOp on the all-reduced sums.  y1 receives y'; *dy2 = this rank's part of |dy|^2
+// (rows below skip_below are counted on rank 0 only).
+extern "C" int emu_sharded_dual_finish(int m_local, const int* ptr, const int* idx, const double* val, const int* block_start, int num_blocks, int cut_block,
+                                       int cut_row, const double* xbar, double* y0, double* y1, const double* clb, const double* cub, double step_size,
+                                       double primal_weight, int skip_below, int max_grid, const double* sums, double* dy2) {
+  cuda_emu::defer_async = false;
+  HostRows csr{ptr, idx, val, block_start, num_blocks, m_local, {}};
+  const RowBlocks all = csr.View();
+  StepState state = FreshState(step_size, primal_weight);
+  const DualStepOp op{{}, &state, val, idx, xbar, y0, y1, clb, cub, skip_below, nullptr};
+  std::vector<double> partials(2 * kMaxGrid, 0.0);
+  int grid = 0;
+  if (num_blocks - cut_block > 0) grid = LaunchRows(op, ViewOfBlocks(all, cut_block, num_blocks - cut_block), max_grid, partials.data());
+  if (cut_row > 0) grid += LaunchMap(FinishRowOp<DualStepOp>{op, sums}, cut_row, partials.data() + grid);
+  double total = 0.0;
+  for (int b = 0; b < grid; ++b) total += partials[b];
+  *dy2 = total;
+  return 0;
+}

@@ -370,6 +370,72 @@ def test_malitsky_pock_steps_follow_the_reference(step_libs):
     np.testing.assert_allclose([st[0], st[5], st[8], st[9]], [want["step"], want["wx"], want["wy"], want["ratio"]], rtol=1e-12)
 
 
+# ---- the column-sharded dual step on emulated ranks ----
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_sharded_dual_step_over_emulated_ranks_matches_one_rank(step_libs, world):
+    """K2 of a column-sharded solve with the real host-side sharding: every rank's block
+    holds the shared constraints first and its private ones after; phase 1 stores the shared rows'
+    partial sums, the test adds them in rank order (the all-reduce), phase 2 finishes private rows
+    inside the row-stream kernel and shared rows through FinishRowOp.  Gathered y' and the summed
+    |dy|^2 must equal the unsharded step."""
+    import scipy.sparse as sp
+    rng = np.random.default_rng(40 + world)
+    m, n = 900, 1600
+    # banded columns (most constraints private to one rank) plus a few dense rows that every rank touches
+    rows = np.concatenate([(np.arange(n * 4) // 4 * m // n + rng.integers(0, 30, n * 4)) % m, rng.integers(0, 12, 800)])
+    cols = np.concatenate([np.arange(n * 4) // 4, rng.integers(0, n, 800)])
+    K = sp.csc_matrix(sp.coo_matrix((rng.standard_normal(rows.size), (rows, cols)), shape=(m, n)))
+    K.sum_duplicates()
+    xbar, y = rng.standard_normal(n), rng.standard_normal(m) * 0.3
+    mid = rng.standard_normal(m)
+    clb = np.where(rng.random(m) < 0.3, -np.inf, mid - 0.5)
+    cub = np.where(rng.random(m) < 0.3, np.inf, mid + 0.5)
+    step, w = 0.4, 1.7
+    sigma = step * w
+    temp = y - sigma * (K @ xbar)
+    want = np.maximum(np.minimum(0.0, temp + sigma * cub), temp + sigma * clb)
+
+    starts = pdlp_b200.column_partition(K.indptr, world)
+    sharing = pdlp_b200.sharding.RowSharing.from_matrix(K, starts)
+    S = int(sharing.shared.size)
+    assert 0 < S < m and all(p.size > 0 for p in sharing.private)
+    lib = step_libs[0]
+    p = lambda a: ctypes.c_void_p(a.ctypes.data)
+    i32 = lambda a: np.ascontiguousarray(a, dtype=np.int32)
+    ranks = []
+    for r in range(world):
+        local = sharing.local_rows(r)
+        block = sp.csr_matrix(K[:, starts[r]:starts[r + 1]].tocsr()[local, :])
+        block.sort_indices()
+        ptr = i32(block.indptr)
+        blocks, cut_block, _ = pdlp_b200.work_blocks(ptr, S if 0 < S < local.size else -1)
+        if S >= local.size:
+            cut_block = len(blocks) - 1
+        ranks.append(dict(m=local.size, ptr=ptr, idx=i32(block.indices), val=np.ascontiguousarray(block.data), blocks=i32(blocks), cut=int(cut_block),
+                          xbar=np.ascontiguousarray(xbar[starts[r]:starts[r + 1]]), y0=sharing.scatter(r, y), y1=np.zeros(local.size),
+                          clb=sharing.scatter(r, clb), cub=sharing.scatter(r, cub)))
+    sums = np.zeros(S)
+    for k in ranks:  # phase 1 + all-reduce in rank order
+        part = np.zeros(S)
+        assert lib.emu_sharded_dual_partial(k["m"], p(k["ptr"]), p(k["idx"]), p(k["val"]), p(k["blocks"]), len(k["blocks"]) - 1, k["cut"], p(k["xbar"]), p(k["y0"]),
+                                            p(k["y1"]), p(k["clb"]), p(k["cub"]), ctypes.c_double(step), ctypes.c_double(w), 3, p(part)) == 0
+        sums += part
+    np.testing.assert_allclose(sums, (K @ xbar)[sharing.shared], rtol=1e-11, atol=1e-12)
+    total = 0.0
+    for r, k in enumerate(ranks):
+        dy2 = ctypes.c_double(0.0)
+        assert lib.emu_sharded_dual_finish(k["m"], p(k["ptr"]), p(k["idx"]), p(k["val"]), p(k["blocks"]), len(k["blocks"]) - 1, k["cut"], S, p(k["xbar"]), p(k["y0"]),
+                                           p(k["y1"]), p(k["clb"]), p(k["cub"]), ctypes.c_double(step), ctypes.c_double(w), 0 if r == 0 else S, 3, p(sums),
+                                           ctypes.byref(dy2)) == 0
+        total += dy2.value
+        if r > 0:  # the shared part is replicated: bit-identical on every rank
+            np.testing.assert_array_equal(k["y1"][:S], ranks[0]["y1"][:S])
+    got = sharing.gather([k["y1"] for k in ranks])
+    np.testing.assert_allclose(got, want, rtol=1e-11, atol=1e-12)
+    np.testing.assert_allclose(total, np.sum((want - y) ** 2), rtol=1e-11)
+
+
 # ---- shared-memory protocol under a race detector ----
 
 @pytest.mark.parametrize("lean", [0, 1])
