@@ -5,6 +5,7 @@
 # then: scripts/gpurun_retry.sh --timeout 1500 -- bash scripts/gpu_call_lean.sh
 # The variant must pass the whole GPU suite before its bench lines mean anything.
 mkdir -p gpurun_out
+( timeout 300 python scripts/check_trial_steps_gpu.py ) > gpurun_out/check_trial_steps.log 2>&1; echo "trial-steps check exit $?" | tee -a gpurun_out/check_trial_steps.log
 lean=$PWD/or-tools_b200/lib_lean/libpdlp_b200.so
 [ -f "$lean" ] || { echo "missing $lean" | tee gpurun_out/lean_missing.txt; exit 1; }
 ( time PDLP_B200_LIBRARY=$lean timeout 1200 python -m pytest tests -m gpu -x -q ) > gpurun_out/pytest_gpu_lean.log 2>&1
