@@ -372,6 +372,9 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
 #pragma unroll
         for (int u = 0; u < kPreRows; ++u) {
           const int rr = sub + u * groups;
+#if PDLP_ROWSTREAM_LEAN
+          if (u * groups >= nrows) break;  // uniform across the CTA: no thread has a row in this or a later round
+#endif
           if (lane == 0 && rr < nrows) pre[u] = OpRowPrefetch(op, r0 + rr);
         }
         if constexpr (HasSplitLoad<Op>::value) {
