@@ -169,6 +169,13 @@ __device__ __forceinline__ int Skew(int k, int pad) { return k + pad * (k >> 4);
 #ifndef PDLP_ROWSTREAM_LEAN
 #define PDLP_ROWSTREAM_LEAN 0
 #endif
+// Unroll factor of the per-row sum out of shared memory (1 = a load -> add chain per nonzero, as
+// shipped; 4 = four shared loads in flight per thread at ~15 % more instructions for short rows; the
+// order of the additions does not change).  A second knob for the same A/B run.
+#ifndef PDLP_ROWSTREAM_REDUCE_UNROLL
+#define PDLP_ROWSTREAM_REDUCE_UNROLL 1
+#endif
+constexpr int kReduceUnroll = PDLP_ROWSTREAM_REDUCE_UNROLL;
 __device__ __forceinline__ int BankPadFor(int nz, int nrows) {
 #if PDLP_ROWSTREAM_LEAN
   // nz <= kStreamChunk and nrows <= kMaxRowsPerBlock are exact in fp32; when nrows divides nz the
@@ -421,6 +428,9 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
             double a = op.RowInit();
             if (rr < nrows) {
               const int q1 = row_raw[rr + 1] - p0;
+#if PDLP_ROWSTREAM_REDUCE_UNROLL > 1
+#pragma unroll kReduceUnroll
+#endif
               for (int q = row_raw[rr] - p0 + lane; q < q1; q += t) a = op.RowAdd(a, staged[Skew(q, shift)], r0 + rr);
             }
             // All 32 lanes take part in the shuffles (t divides 32).
