@@ -4,13 +4,14 @@
 //   nonlinearity), :2211-2406 (the three step rules), sharded_optimization_utils.cc:54-66
 //   (weighted average).
 //
-// One trial of the adaptive rule is five launches, none of which returns to the host:
+// One trial is the launches below, none of which returns to the host (ops and decision kernels:
+// pdlp_step_kernels.cuh; this file holds the launch sequences):
 //   K1 primal_step   x' = proj(x - tau (c - K^T y)) [/ (1 + tau Q)], xbar = 2x' - x, |dx|^2
 //   K2 dual_step     CSR rows: (K xbar)_i fused with the dual prox, writes y', |dy|^2
 //   K3 kty_step      CSC cols: (K^T y')_j, fused with dx_j (K^T y' - K^T y)_j
 //   K4 decide        movement / nonlinearity / accept / next step size, on one CTA
 //   K5 average       on accept: avg += w/(W+w) (z - avg) for x and y
-// Under the adaptive and constant rules K5 is folded into the NEXT trial's K1 and K2, which read the
+// Under the adaptive and constant rules (four launches per trial) K5 is folded into the NEXT trial's K1 and K2, which read the
 // accepted x and y anyway (8 (n + m) bytes and one launch less per step): the decision kernel marks
 // the update pending, K1 / K2 apply it with the same arithmetic, and a flush at the end of every
 // enqueued batch applies what is still pending, so the host always sees complete averages.
