@@ -22,6 +22,7 @@ import argparse
 import json
 import math
 import os
+import signal
 import subprocess
 import sys
 import threading
@@ -213,7 +214,12 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--replicas", action="store_true", help="N > 1: independent replicas instead of one column-sharded problem")
+    ap.add_argument("--watchdog-sec", type=int, default=1500, help="kill this process if the run takes longer (0 = off)")
     args = ap.parse_args()
+    if args.watchdog_sec > 0:
+        # Default SIGALRM action on purpose: it ends the process even inside a native call that never
+        # returns (a collective waiting for a rank that is gone), where a Python handler would not run.
+        signal.alarm(args.watchdog_sec)
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
