@@ -436,6 +436,92 @@ def test_sharded_dual_step_over_emulated_ranks_matches_one_rank(step_libs, world
     np.testing.assert_allclose(total, np.sum((want - y) ** 2), rtol=1e-11)
 
 
+# ---- termination statistics (the two fused KKT passes) against the oracle ----
+
+def _build_kkt():
+    out = os.path.join(BUILD, "kkt_emu.so")
+    sources = [os.path.join(EMU, "kkt_emu.cc"), os.path.join(EMU, "cuda_emu.h"), os.path.join(CSRC, "pdlp_skeletons.cuh"), os.path.join(CSRC, "pdlp_kkt_kernels.cuh")]
+    os.makedirs(BUILD, exist_ok=True)
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(s) for s in sources):
+        subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-Wno-attributes", "-I" + EMU, "-I" + CSRC,
+                        sources[0], "-o", out], check=True)
+    return ctypes.CDLL(out)
+
+
+@pytest.mark.parametrize("qp_case, flag", [(False, True), (False, False), (True, True)])
+def test_kkt_passes_match_the_oracles_convergence_and_infeasibility_information(qp_case, flag):
+    """KktRowOp / KktColOp (pdlp_kkt_kernels.cuh) through the emulated row-stream kernel; the totals are
+    assembled as PreprocessSolver::ComputeConvergenceAndInfeasibility does (pdlp_preprocess.cu) and
+    compared with the oracle's ComputeConvergenceInformation / ComputeInfeasibilityInformation
+    (iteration_stats.cc:349-518) on a point that sits on bounds, off bounds and at zero."""
+    import scipy.sparse as sp
+    import oracle_binding as ob
+    K, c, q, vlb, vub, clb, cub, x, y = step_problem(11 + qp_case, qp_case)
+    rng = np.random.default_rng(3)
+    m, n = K.shape
+    x = x + rng.standard_normal(n) * (rng.random(n) < 0.5)      # half the variables leave their projected start
+    on = rng.random(n) < 0.2
+    x[on & np.isfinite(vlb)] = vlb[on & np.isfinite(vlb)]       # some exactly on a bound
+    x[rng.random(n) < 0.1] = 0.0
+    y = rng.standard_normal(m) * (rng.random(m) < 0.7)          # zeros included
+    row_scale, col_scale = rng.uniform(0.5, 2.0, m), rng.uniform(0.5, 2.0, n)
+    x_start, y_start = np.minimum(np.maximum(np.zeros(n), vlb), vub), np.zeros(m)
+    cw_p, cw_d = 2.5, 0.4
+
+    qp = pdlp_b200.QuadraticProgram()
+    qp.constraint_matrix = sp.csc_matrix(K)
+    qp.objective_vector = c
+    qp.variable_lower_bounds, qp.variable_upper_bounds = vlb, vub
+    qp.constraint_lower_bounds, qp.constraint_upper_bounds = clb, cub
+    if q is not None:
+        qp.set_objective_matrix_diagonal(q)
+    params = pdlp_b200.PrimalDualHybridGradientParams()
+    params.handle_some_primal_gradients_on_finite_bounds_as_residuals = flag
+    oracle = ob.Problem(qp)
+    want_ci = oracle.convergence_info(params, col_scale, row_scale, x, y, cw_p, cw_d)
+    want_ii = oracle.infeasibility_info(params, col_scale, row_scale, x, y)
+
+    lib = _build_kkt()
+    csr, csc = sp.csr_matrix(K), sp.csc_matrix(K)
+    csr.sort_indices(); csc.sort_indices()
+    i32 = lambda a: np.ascontiguousarray(a, dtype=np.int32)
+    f64 = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+    arr = [i32(csr.indptr), i32(csr.indices), f64(csr.data)]
+    rb = i32(pdlp_b200.work_blocks(arr[0])[0])
+    arc = [i32(csc.indptr), i32(csc.indices), f64(csc.data)]
+    cb = i32(pdlp_b200.work_blocks(arc[0])[0])
+    p = lambda a: ctypes.c_void_p(a.ctypes.data) if a is not None else ctypes.c_void_p(None)
+    vec = [f64(v) if v is not None else None for v in (c, q, vlb, vub, clb, cub, row_scale, col_scale, x, y, x_start, y_start)]
+    r, t = np.zeros(9), np.zeros(15)
+    assert lib.emu_kkt_totals(n, m, p(arr[0]), p(arr[1]), p(arr[2]), p(rb), len(rb) - 1, p(arc[0]), p(arc[1]), p(arc[2]), p(cb), len(cb) - 1, *[p(v) for v in vec],
+                              ctypes.c_double(cw_p), ctypes.c_double(cw_d), int(flag), 3, p(r), p(t)) == 0
+    nn = lambda v: max(v, 0.0)  # max slots start at 0 in the reference
+    quad = 0.0 if q is None else 0.5 * t[1]
+    dual_piece = -quad + r[3]
+    got_ci = dict(l_inf_primal_residual=nn(r[1]), l2_primal_residual=np.sqrt(r[0]), l_inf_componentwise_primal_residual=nn(r[2]), l_inf_primal_variable=nn(t[7]),
+                  l2_primal_variable=np.sqrt(t[8]), l_inf_dual_variable=nn(r[4]), l2_dual_variable=np.sqrt(r[5]), primal_objective=quad + t[0],
+                  dual_objective=dual_piece + t[2], corrected_dual_objective=dual_piece + t[3], l_inf_dual_residual=nn(t[4]), l2_dual_residual=np.sqrt(t[5]),
+                  l_inf_componentwise_dual_residual=nn(t[6]))
+    for key, value in got_ci.items():
+        np.testing.assert_allclose(value, want_ci.get(key, 0.0), rtol=1e-11, atol=1e-12, err_msg=key)
+    linf_x, linf_y = nn(t[7]), nn(r[4])
+    got_ii = dict(dual_ray_objective=(r[3] + t[9]) / linf_y, max_dual_ray_infeasibility=nn(t[10]) / linf_y, primal_ray_quadratic_norm=nn(t[12]) / linf_x,
+                  max_primal_ray_infeasibility=max(nn(r[6]), nn(t[11])) / linf_x, primal_ray_linear_objective=t[0] / linf_x)
+    for key, value in got_ii.items():
+        np.testing.assert_allclose(value, want_ii.get(key, 0.0), rtol=1e-11, atol=1e-12, err_msg=key)
+    # active-set counts of SetActiveSetInformation (primal_dual_hybrid_gradient.cc:1343-1412)
+    assert t[13] == np.sum((x > vlb) & (x < vub))
+    free = np.isneginf(clb) & np.isposinf(cub)
+    assert r[7] == np.sum((y != 0) | free)
+
+    # ReducedCosts (iteration_stats.cc:533-565)
+    rc = np.zeros(n)
+    for zero_objective in (0, 1):
+        assert lib.emu_reduced_costs(n, p(arc[0]), p(arc[1]), p(arc[2]), p(cb), len(cb) - 1, p(vec[0]), p(vec[1]), p(vec[2]), p(vec[3]), p(vec[8]), p(vec[9]),
+                                     zero_objective, int(flag), 3, p(rc)) == 0
+        np.testing.assert_allclose(rc, oracle.reduced_costs(params, x, y, bool(zero_objective)), rtol=1e-11, atol=1e-12)
+
+
 # ---- shared-memory protocol under a race detector ----
 
 @pytest.mark.parametrize("lean", [0, 1])
