@@ -9,6 +9,7 @@
 
 #include "pdlp_comm.h"
 #include "pdlp_matrix.cuh"
+#include "pdlp_restart_types.h"
 #include "pdlp_step_state.h"
 
 namespace pdlp_b200 {
@@ -129,7 +130,6 @@ void ComputeReducedCosts(Workspace& ws, const DeviceProblem& p, const double* x,
 
 // ---- restarts (trust_region.cc:886-1016, sou.cc:446-527) ----
 double SquaredDistance(Workspace& ws, const double* a, const double* b, int64_t count, Side side);
-struct LocalizedBounds { double lagrangian_value, lower_bound, upper_bound, radius; };
 // Euclidean-norm localized Lagrangian bounds at (x, y).  kty may be null (computed).
 LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProblem& p, const double* x, const double* y, const double* kty_or_null,
                                                  double primal_weight, double radius, bool use_diagonal_qp_solver, double diagonal_qp_tolerance,

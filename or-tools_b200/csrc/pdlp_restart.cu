@@ -13,277 +13,30 @@
 #include <cfloat>
 
 #include "pdlp_launch.cuh"
+#include "pdlp_restart_kernels.cuh"
 
 namespace pdlp_b200 {
 
 namespace {
-
-// The joint problem of trust_region.cc:886-974 (JointTrustRegionProblem).
-struct JointView {
-  const double* gx; const double* gy; const double* x; const double* y;
-  const double* vlb; const double* vub; const double* clb; const double* cub; const double* q;
-  int64_t n; double w_primal, w_dual;
-  int64_t dual_skip_below;  // sharded solve: dual rows below it are shared and counted on rank 0 only
-  __device__ bool Counts(int64_t i) const { return i < n || i - n >= dual_skip_below; }
-  __device__ double Objective(int64_t i) const { return i < n ? gx[i] : -gy[i - n]; }
-  __device__ double LowerBound(int64_t i) const { return i < n ? vlb[i] : (isfinite(cub[i - n]) ? -INFINITY : 0.0); }
-  __device__ double UpperBound(int64_t i) const { return i < n ? vub[i] : (isfinite(clb[i - n]) ? INFINITY : 0.0); }
-  __device__ double Center(int64_t i) const { return i < n ? x[i] : y[i - n]; }
-  __device__ double Weight(int64_t i) const { return i < n ? w_primal : w_dual; }
-  __device__ double Diagonal(int64_t i) const { return (q != nullptr && i < n) ? q[i] : 0.0; }
-  // trust_region.h:193-228.
-  __device__ double ProjectedValue(int64_t i, double step) const {
-    const double full = Center(i) - step * Objective(i) / Weight(i);
-    return fmin(fmax(full, LowerBound(i)), UpperBound(i));
-  }
+struct DeviceRunner {
+  Workspace& ws;
+  const DeviceProblem& p;
+  template <class Op> const double* CsrRows(const Op& op) { return RunRows(ws, op, p.K.by_row); }
+  void ColumnDot(const double* y, double* out) { RowDot(ws, p.K.by_col, y, out); }
+  template <class Op> const double* Primal(const Op& op, int64_t count) { return RunMap(ws, op, count, Side::kSharded); }
+  template <class Op> const double* Joint(const Op& op, int64_t count) { return RunMap(ws, op, count, Side::kJoint); }
 };
-
-// sou.cc:476-500.
-__device__ __forceinline__ double DualSubgradientCoefficient(double lb, double ub, double dual, double primal_product) {
-  if (dual < 0.0) return ub;
-  if (dual > 0.0) return lb;
-  if (isfinite(lb) && isfinite(ub)) {
-    if (primal_product < lb) return lb;
-    if (primal_product > ub) return ub;
-    return primal_product;
-  }
-  if (isfinite(lb)) return lb;
-  if (isfinite(ub)) return ub;
-  return 0.0;
-}
-
-struct OneSumSlot {
-  static constexpr int kNumSlots = 1;
-  __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
-};
-
-// ComputeDualGradient (sou.cc:502-527) fused with K x.
-struct DualGradOp : AlwaysActive, OneSumSlot {
-  const double* val; const int* idx; const double* x;
-  const double* y; const double* clb; const double* cub; double* gy;
-  int skip_below;
-  __device__ double Load(int64_t k) const { return val[k] * x[idx[k]]; }
-  __device__ double RowInit() const { return 0.0; }
-  __device__ double RowAdd(double acc, double staged, int) const { return acc + staged; }
-  __device__ double RowMerge(double a, double b) const { return a + b; }
-  __device__ void RowFinish(int i, double kx, Slots<1>& r) const {
-    const double coeff = DualSubgradientCoefficient(clb[i], cub[i], y[i], kx);
-    if (i >= skip_below) r.v[0] += coeff * y[i];
-    gy[i] = coeff - kx;
-  }
-};
-
-// ComputePrimalGradient (sou.cc:446-474).
-__device__ __forceinline__ double PrimalGradAt(double xj, double cj, const double* q, int64_t j, double kty, double* value) {
-  if (q == nullptr) {
-    const double g = cj - kty;
-    *value = xj * g;
-    return g;
-  }
-  const double qx = q[j] * xj;
-  const double g = cj + qx - kty;
-  *value = xj * (g - 0.5 * qx);
-  return g;
-}
-struct PrimalGradMapOp : AlwaysActive, OneSumSlot {
-  const double* kty; const double* x; const double* c; const double* q; double* gx;
-  __device__ void Apply(int64_t j, Slots<1>& r) const {
-    double v;
-    gx[j] = PrimalGradAt(x[j], c[j], q, j, kty[j], &v);
-    r.v[0] += v;
-  }
-};
-
-// Critical step sizes and radius coefficients.  Slots: max |objective| (any nonzero?).
-struct CriticalOp : AlwaysActive {
-  static constexpr int kNumSlots = 1;
-  __host__ __device__ static constexpr int SlotKindOf(int) { return kMax; }
-  JointView p; double* crit; double* coef;
-  __device__ void Apply(int64_t i, Slots<1>& r) const {
-    const double obj = p.Objective(i), w = p.Weight(i);
-    double cs = INFINITY;
-    if (obj != 0.0) {
-      const double dist = obj > 0.0 ? p.LowerBound(i) - p.Center(i) : p.UpperBound(i) - p.Center(i);
-      cs = -w * dist / obj;
-    }
-    crit[i] = cs;
-    coef[i] = obj * obj / w;
-    r.v[0] = fmax(r.v[0], fabs(obj));
-  }
-};
-
-// One Newton pass evaluated at kRadiusCandidates step sizes at once (ascending): for each, the
-// fixed radius^2, the free coefficient and the number of fixed entries.  Slot 3 k + {0, 1, 2}.
-constexpr int kRadiusCandidates = 5;
-struct RadiusPassOp : AlwaysActive {
-  static constexpr int kNumSlots = 3 * kRadiusCandidates;
-  __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
-  const double* crit; const double* coef; double delta[kRadiusCandidates]; int64_t n; int64_t dual_skip_below;
-  __device__ void Apply(int64_t i, Slots<kNumSlots>& r) const {
-    if (i >= n && i - n < dual_skip_below) return;
-    const double cs = crit[i], a = coef[i];
-    const double fixed = a * (cs * cs);
-#pragma unroll
-    for (int k = 0; k < kRadiusCandidates; ++k) {
-      if (cs <= delta[k]) { r.v[3 * k] += fixed; r.v[3 * k + 2] += 1.0; }
-      else r.v[3 * k + 1] += a;
-    }
-  }
-};
-
-// primal_delta / dual_delta of trust_region.cc:951-973 for the linear solver.
-struct BoundsDeltaOp : AlwaysActive {
-  static constexpr int kNumSlots = 2;
-  __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
-  JointView p; double step;
-  __device__ void Apply(int64_t i, Slots<2>& r) const {
-    if (!p.Counts(i)) return;
-    const double sol = p.ProjectedValue(i, step);
-    if (i < p.n) r.v[0] += p.gx[i] * (sol - p.x[i]);
-    else r.v[1] += p.gy[i - p.n] * (sol - p.y[i - p.n]);
-  }
-};
-
-// Diagonal-QP solver pieces (trust_region.cc:615-753).
-__device__ __forceinline__ double ProjectedScaledDifference(const JointView& p, int64_t i, double scaling) {
-  const double w = p.Weight(i);
-  return fmin(fmax((-p.Objective(i) / sqrt(w)) / (p.Diagonal(i) / w + scaling), sqrt(w) * (p.LowerBound(i) - p.Center(i))),
-              sqrt(w) * (p.UpperBound(i) - p.Center(i)));
-}
-struct DeltaNormOp : AlwaysActive, OneSumSlot {
-  JointView p; double scaling;
-  __device__ void Apply(int64_t i, Slots<1>& r) const {
-    if (!p.Counts(i)) return;
-    const double v = ProjectedScaledDifference(p, i, scaling);
-    r.v[0] += v * v;
-  }
-};
-struct DiagonalBoundsDeltaOp : AlwaysActive {
-  static constexpr int kNumSlots = 3;
-  __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
-  JointView p; double scaling; int at_center;
-  __device__ void Apply(int64_t i, Slots<3>& r) const {
-    if (!p.Counts(i)) return;
-    const double c = p.Center(i);
-    const double sol = at_center ? c : c + sqrt(1.0 / p.Weight(i)) * ProjectedScaledDifference(p, i, scaling);
-    const double d = sol - c;
-    if (i < p.n) {
-      r.v[0] += p.gx[i] * d;
-      if (p.q != nullptr) r.v[2] += 0.5 * p.q[i] * (d * d);
-    } else {
-      r.v[1] += p.gy[i - p.n] * d;
-    }
-  }
-};
-
 }  // namespace
 
 LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProblem& p, const double* x, const double* y, const double* kty_or_null,
                                                  double primal_weight, double radius, bool use_diagonal_qp_solver, double diagonal_qp_tolerance,
                                                  int* tr_passes) {
   const SparseRows& csr = p.K.by_row;
-  const SparseRows& csc = p.K.by_col;
-  double* gx = ws.scratch_n[0].get();
-  double* gy = ws.scratch_m[0].get();
-  double primal_value = 0.0, dual_value = 0.0;
-  if (p.m > 0) dual_value = RunRows(ws, DualGradOp{{}, {}, csr.val.get(), csr.idx.get(), x, y, p.clb.get(), p.cub.get(), gy, static_cast<int>(ws.dual_skip_below)}, csr)[0];
-  if (p.n > 0) {
-    // When K^T y is not cached it is computed first; the gradient and its value then come
-    // from the same kernel either way, so "bounds at the average" and "bounds at the
-    // current point" are bit-identical whenever the two points are (the reference's
-    // strict-inequality tie-break in AverageHasBetterPotential relies on that).
-    const double* kty = kty_or_null;
-    if (kty == nullptr) {
-      RowDot(ws, csc, y, ws.scratch_n[1].get());
-      kty = ws.scratch_n[1].get();
-    }
-    primal_value = RunMap(ws, PrimalGradMapOp{{}, {}, kty, x, p.c.get(), p.q_or_null(), gx}, p.n, Side::kSharded)[0];
-  }
-  const double lagrangian = primal_value + dual_value;
-  const int64_t total = p.n + p.m;
-  JointView view{gx, gy, x, y, p.vlb.get(), p.vub.get(), p.clb.get(), p.cub.get(), p.q_or_null(), p.n, 0.5 * primal_weight, 0.5 / primal_weight,
-                 ws.dual_skip_below};
-  int passes = 0;
-  LocalizedBounds out{lagrangian, lagrangian, lagrangian, radius};
-  if (total == 0) { if (tr_passes) *tr_passes = 0; return out; }
-
-  if (use_diagonal_qp_solver) {
-    double primal_delta = 0.0, dual_delta = 0.0;
-    if (radius == 0.0) {
-      // Solution is the centre point: both deltas are exactly zero.
-    } else {
-      auto norm_at = [&](double scaling) { ++passes; return std::sqrt(RunMap(ws, DeltaNormOp{{}, {}, view, scaling}, total, Side::kJoint)[0]); };
-      double lo = 0.0, hi = 1.0;  // FindScalingFactor, trust_region.cc:683-706
-      while (norm_at(hi) >= radius) { lo = hi; hi *= 2; }
-      while ((hi - lo) >= diagonal_qp_tolerance * std::max(1.0, lo)) {
-        const double mid = (lo + hi) / 2.0;
-        if (norm_at(mid) <= radius) hi = mid; else lo = mid;
-      }
-      const double scaling = (hi + lo) / 2.0;
-      const double* h = RunMap(ws, DiagonalBoundsDeltaOp{{}, view, scaling, 0}, total, Side::kJoint);
-      primal_delta = h[0] + (p.is_lp ? 0.0 : h[2]);
-      dual_delta = h[1];
-    }
-    out.lower_bound = lagrangian + primal_delta;
-    out.upper_bound = lagrangian + dual_delta;
-    if (tr_passes) *tr_passes = passes;
-    return out;
-  }
-
-  // SolveTrustRegionStepSize.
-  double step = 0.0;
-  if (radius > 0.0) {
-    double* crit = ws.scratch_nm[0].get();
-    double* coef = ws.scratch_nm[1].get();
-    const double max_obj = RunMap(ws, CriticalOp{{}, view, crit, coef}, total, Side::kJoint)[0];
-    if (max_obj > 0.0) {  // otherwise every objective entry is zero: step 0 (trust_region.cc:349-358)
-      // Root of phi(d) = fixed_r2(d) + d^2 free_coef(d) - r^2 (concave piecewise in d^2) by Newton from
-      // the left: from a point left of the root the Newton step lands left of the root again, and
-      // once a step crosses no breakpoint it is the exact root of the final segment.  Each pass also
-      // evaluates phi at four points further right (the Newton point plus 1, 3, 7, 15 times the
-      // last increment); the iteration continues from the rightmost one that is still left of the
-      // root.  The final value depends only on the final segment's sums, so it is the same root, bit
-      // for bit, as plain Newton's - in a third of the passes where the active set changes slowly.
-      const double r2 = radius * radius;
-      double delta = 0.0, increment = 0.0;
-      double prev_fixed = -1.0;
-      for (;;) {
-        RadiusPassOp op{{}, crit, coef, {}, p.n, view.dual_skip_below};
-        static const double kAhead[kRadiusCandidates] = {0.0, 1.0, 3.0, 7.0, 15.0};
-        for (int k = 0; k < kRadiusCandidates; ++k) op.delta[k] = delta + kAhead[k] * increment;
-        const double* h = RunMap(ws, op, total, Side::kJoint);
-        ++passes;
-        // Rightmost candidate that is not right of the root (candidate 0 never is).
-        int pick = 0;
-        for (int k = 1; k < kRadiusCandidates && increment > 0.0; ++k) {
-          const double d = op.delta[k];
-          const double phi = h[3 * k] + (d * d) * h[3 * k + 1] - r2;
-          if (phi <= 0.0 && d > op.delta[pick]) pick = k;
-        }
-        const double at = op.delta[pick];
-        const double fixed_r2 = h[3 * pick], free_coef = h[3 * pick + 1], num_fixed = h[3 * pick + 2];
-        if (!(free_coef > 0.0)) { step = DBL_MAX; break; }  // trust_region.cc:438-446
-        // No breakpoint crossed since the last pass: the Newton point is the exact root.
-        if (pick == 0 && num_fixed == prev_fixed) { step = at; break; }
-        const double next = std::sqrt(std::max(0.0, r2 - fixed_r2) / free_coef);
-        if (!(next > at)) { step = at; break; }  // already at the root up to rounding
-        if (passes >= 200) { step = next; break; }
-        prev_fixed = num_fixed;
-        increment = next - delta;
-        delta = next;
-      }
-    }
-  }
-  double primal_delta = 0.0, dual_delta = 0.0;
-  {
-    const double* h = RunMap(ws, BoundsDeltaOp{{}, view, step}, total, Side::kJoint);
-    primal_delta = h[0];
-    dual_delta = h[1];
-  }
-  out.lower_bound = lagrangian + primal_delta;
-  out.upper_bound = lagrangian + dual_delta;
-  if (tr_passes) *tr_passes = passes;
-  return out;
+  const RestartProblemView view{csr.val.get(), csr.idx.get(), p.c.get(), p.q_or_null(), p.vlb.get(), p.vub.get(), p.clb.get(), p.cub.get(), p.n, p.m, p.is_lp,
+                                ws.dual_skip_below, ws.scratch_n[0].get(), ws.scratch_m[0].get(), ws.scratch_n[1].get(), ws.scratch_nm[0].get(),
+                                ws.scratch_nm[1].get()};
+  DeviceRunner run{ws, p};
+  return LocalizedLagrangianBoundsWith(run, view, x, y, kty_or_null, primal_weight, radius, use_diagonal_qp_solver, diagonal_qp_tolerance, tr_passes);
 }
 
 }  // namespace pdlp_b200

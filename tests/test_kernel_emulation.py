@@ -522,6 +522,63 @@ def test_kkt_passes_match_the_oracles_convergence_and_infeasibility_information(
         np.testing.assert_allclose(rc, oracle.reduced_costs(params, x, y, bool(zero_objective)), rtol=1e-11, atol=1e-12)
 
 
+# ---- restart criteria: localized Lagrangian bounds against the oracle ----
+
+def _build_restart():
+    out = os.path.join(BUILD, "restart_emu.so")
+    sources = [os.path.join(EMU, "restart_emu.cc"), os.path.join(EMU, "cuda_emu.h"), os.path.join(CSRC, "pdlp_skeletons.cuh"),
+               os.path.join(CSRC, "pdlp_restart_kernels.cuh"), os.path.join(CSRC, "pdlp_restart_types.h")]
+    os.makedirs(BUILD, exist_ok=True)
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(s) for s in sources):
+        subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-Wno-attributes", "-I" + EMU, "-I" + CSRC,
+                        sources[0], "-o", out], check=True)
+    return ctypes.CDLL(out)
+
+
+@pytest.mark.parametrize("qp_case, diagonal", [(False, False), (False, True), (True, True)])
+def test_localized_lagrangian_bounds_match_the_oracle(qp_case, diagonal):
+    """ComputeLocalizedLagrangianBounds, Euclidean norm (trust_region.cc:886-1016): the gradient ops,
+    the trust-region ops and the root-finding host loop of pdlp_restart_kernels.cuh - the code the device
+    path runs, driven through the emulated kernels - against the oracle's median-based solver, from
+    radius 0 to a radius that fixes most variables at their bounds."""
+    import scipy.sparse as sp
+    import oracle_binding as ob
+    K, c, q, vlb, vub, clb, cub, x, y = step_problem(21 + qp_case, qp_case)
+    m, n = K.shape
+    qp = pdlp_b200.QuadraticProgram()
+    qp.constraint_matrix = sp.csc_matrix(K)
+    qp.objective_vector = c
+    qp.variable_lower_bounds, qp.variable_upper_bounds = vlb, vub
+    qp.constraint_lower_bounds, qp.constraint_upper_bounds = clb, cub
+    if q is not None:
+        qp.set_objective_matrix_diagonal(q)
+    oracle = ob.Problem(qp)
+    lib = _build_restart()
+    csr, csc = sp.csr_matrix(K), sp.csc_matrix(K)
+    csr.sort_indices(); csc.sort_indices()
+    i32 = lambda a: np.ascontiguousarray(a, dtype=np.int32)
+    f64 = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+    arr = [i32(csr.indptr), i32(csr.indices), f64(csr.data)]
+    rb = i32(pdlp_b200.work_blocks(arr[0])[0])
+    arc = [i32(csc.indptr), i32(csc.indices), f64(csc.data)]
+    cb = i32(pdlp_b200.work_blocks(arc[0])[0])
+    p = lambda a: ctypes.c_void_p(a.ctypes.data) if a is not None else ctypes.c_void_p(None)
+    vec = [f64(v) if v is not None else None for v in (c, q, vlb, vub, clb, cub, x, y)]
+    tol = 1e-6 if diagonal else 1e-10  # (the diagonal solver bisects to `tol`: ~25 passes per radius at 1e-6)
+    passes = []
+    for radius, w in (((0.0, 1.0), (1.0, 0.6), (300.0, 1.0)) if diagonal else ((0.0, 1.0), (0.05, 1.0), (1.0, 0.6), (7.0, 2.0), (300.0, 1.0))):
+        want = oracle.localized_bounds(x, y, 1, w, radius, diagonal, tol)
+        out = np.zeros(5)
+        assert lib.emu_localized_bounds(n, m, p(arr[0]), p(arr[1]), p(arr[2]), p(rb), len(rb) - 1, p(arc[0]), p(arc[1]), p(arc[2]), p(cb), len(cb) - 1,
+                                        *[p(v) for v in vec], ctypes.c_double(w), ctypes.c_double(radius), int(diagonal), ctypes.c_double(tol), 3, p(out)) == 0
+        got = dict(lagrangian_value=out[0], lower_bound=out[1], upper_bound=out[2], radius=out[3])
+        scale = max(1.0, abs(want["lagrangian_value"]))
+        for key in want:
+            assert abs(got[key] - want[key]) <= (1e-5 if diagonal else 1e-10) * scale, (radius, key, got[key], want[key])
+        passes.append(int(out[4]))
+    assert passes[0] == 0 and max(passes) >= 2
+
+
 # ---- shared-memory protocol under a race detector ----
 
 @pytest.mark.parametrize("lean", [0, 1])
