@@ -579,6 +579,55 @@ def test_localized_lagrangian_bounds_match_the_oracle(qp_case, diagonal):
     assert passes[0] == 0 and max(passes) >= 2
 
 
+# ---- setup: Ruiz / L2 rescaling against the oracle ----
+
+@pytest.mark.parametrize("qp_case, ruiz, l2", [(False, 5, True), (True, 3, False), (False, 0, True)])
+def test_rescaling_matches_the_oracle(qp_case, ruiz, l2):
+    """ApplyRescaling (sharded_optimization_utils.cc:367-444) and RescaleQuadraticProgram
+    (sharded_quadratic_program.cc:97-167): scaled column / row norms over both matrix copies, the
+    square-root updates, then the scaling of the vectors and of both copies of K."""
+    import scipy.sparse as sp
+    import oracle_binding as ob
+    K, c, q, vlb, vub, clb, cub, _, _ = step_problem(31 + qp_case, qp_case)
+    m, n = K.shape
+    qp = pdlp_b200.QuadraticProgram()
+    qp.constraint_matrix = sp.csc_matrix(K)
+    qp.objective_vector = c
+    qp.variable_lower_bounds, qp.variable_upper_bounds = vlb, vub
+    qp.constraint_lower_bounds, qp.constraint_upper_bounds = clb, cub
+    if q is not None:
+        qp.set_objective_matrix_diagonal(q)
+    oracle = ob.Problem(qp)
+    want_row, want_col = oracle.rescale(ruiz, l2)
+    want = oracle.get()
+
+    out = os.path.join(BUILD, "setup_emu.so")
+    sources = [os.path.join(EMU, "setup_emu.cc"), os.path.join(EMU, "cuda_emu.h"), os.path.join(CSRC, "pdlp_skeletons.cuh"), os.path.join(CSRC, "pdlp_ops_kernels.cuh")]
+    os.makedirs(BUILD, exist_ok=True)
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(f) for f in sources):
+        subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-Wno-attributes", "-I" + EMU, "-I" + CSRC,
+                        sources[0], "-o", out], check=True)
+    lib = ctypes.CDLL(out)
+    csr, csc = sp.csr_matrix(K), sp.csc_matrix(K)
+    csr.sort_indices(); csc.sort_indices()
+    i32 = lambda a: np.ascontiguousarray(a, dtype=np.int32)
+    f64 = lambda a: np.array(a, dtype=np.float64)
+    rp, ri, rv = i32(csr.indptr), i32(csr.indices), f64(csr.data)
+    cp, ci, cv = i32(csc.indptr), i32(csc.indices), f64(csc.data)
+    rb, cb = i32(pdlp_b200.work_blocks(rp)[0]), i32(pdlp_b200.work_blocks(cp)[0])
+    vec = dict(c=f64(c), q=None if q is None else f64(q), vlb=f64(vlb), vub=f64(vub), clb=f64(clb), cub=f64(cub))
+    row, col = np.ones(m), np.ones(n)
+    p = lambda a: ctypes.c_void_p(a.ctypes.data) if a is not None else ctypes.c_void_p(None)
+    assert lib.emu_rescale(n, m, p(rp), p(ri), p(rv), p(rb), len(rb) - 1, p(cp), p(ci), p(cv), p(cb), len(cb) - 1, p(vec["c"]), p(vec["q"]), p(vec["vlb"]),
+                           p(vec["vub"]), p(vec["clb"]), p(vec["cub"]), ruiz, int(l2), 3, p(row), p(col)) == 0
+    np.testing.assert_allclose(row, want_row, rtol=1e-12)
+    np.testing.assert_allclose(col, want_col, rtol=1e-12)
+    for key in ("c", "vlb", "vub", "clb", "cub") + (("q",) if q is not None else ()):
+        np.testing.assert_allclose(vec[key], want[key], rtol=1e-12, err_msg=key)
+    np.testing.assert_allclose(cv, want["val"], rtol=1e-12)  # the oracle's matrix is the CSC copy
+    np.testing.assert_allclose(sp.csr_matrix((rv, ri, rp), shape=(m, n)).toarray(), sp.csc_matrix((cv, ci, cp), shape=(m, n)).toarray(), rtol=1e-13)
+
+
 # ---- shared-memory protocol under a race detector ----
 
 @pytest.mark.parametrize("lean", [0, 1])
