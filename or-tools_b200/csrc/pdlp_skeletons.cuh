@@ -163,9 +163,12 @@ __device__ __forceinline__ int Skew(int k, int pad) { return k + pad * (k >> 4);
 // PDLP_ROWSTREAM_LEAN=1 selects a staging path with fewer issued instructions per nonzero (the
 // row-stream kernels are issue-bound): work blocks that fill all but the last of a
 // thread's kPerThread positions run without per-position predicates, staged positions advance by
-// one stride per position instead of being recomputed, and the bank-pad rule avoids the integer
-// division.  Same arithmetic, same staged layout, same results.  Off by default until it has been
-// timed on the device (build with EXTRA_NVCCFLAGS=-DPDLP_ROWSTREAM_LEAN=1).
+// one stride per position instead of being recomputed, the bank-pad rule avoids the integer
+// division, the threads per row come from a count of leading zeros instead of a loop, and rounds of
+// the epilogue prefetch that no thread has a row in are skipped.  Same arithmetic, same staged
+// layout, same results (bit-identical under tests/kernel_emu, profiles/r01_sass_rowstream_lean.md
+// for the instruction counts).  Off by default until it has been timed on the device (build with
+// EXTRA_NVCCFLAGS=-DPDLP_ROWSTREAM_LEAN=1; scripts/gpu_call_lean.sh).
 #ifndef PDLP_ROWSTREAM_LEAN
 #define PDLP_ROWSTREAM_LEAN 0
 #endif
