@@ -1,4 +1,4 @@
-"""Shared-memory bank-conflict model of rowstream_kernel's staging buffer (pdlp_common.cuh `Skew`).
+"""Shared-memory bank-conflict model of rowstream_kernel's staging buffer (pdlp_skeletons.cuh `Skew`).
 
 8-byte products, 16 bank pairs per half-warp.  For a work block (<= 2048 nonzeros, 256 threads) it
 counts the wavefronts of (a) the three coalesced passes over the products (thread t handles

@@ -1,5 +1,5 @@
 #!/bin/bash
-# One GPU: A/B of the lean row-stream staging path (PDLP_ROWSTREAM_LEAN=1, pdlp_common.cuh).
+# One GPU: A/B of the lean row-stream staging path (PDLP_ROWSTREAM_LEAN=1, pdlp_skeletons.cuh).
 # Build the variant HERE first (the box only runs prebuilt files):
 #   make -C or-tools_b200/csrc OUT=../lib_lean OBJ=../lib_lean/obj EXTRA_NVCCFLAGS=-DPDLP_ROWSTREAM_LEAN=1
 #   make -C or-tools_b200/csrc OUT=../lib_lean4 OBJ=../lib_lean4/obj EXTRA_NVCCFLAGS="-DPDLP_ROWSTREAM_LEAN=1 -DPDLP_ROWSTREAM_REDUCE_UNROLL=4"
