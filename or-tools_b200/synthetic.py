@@ -5,7 +5,7 @@ LP / QP; the network problems are feasible and bounded by positive costs)."""
 import numpy as np
 import scipy.sparse as sp
 
-from ._api import QuadraticProgram
+from ._qp import QuadraticProgram
 
 INF = np.inf
 

@@ -233,6 +233,22 @@ int oracle_solve(int64_t n, int64_t m, int64_t nnz, const int64_t* col_ptr, cons
   return 0;
 }
 
+// Bench support: seconds of `steps` iterations of the step loop alone after `warmup` untimed ones
+// (no termination checks, no restarts; oracle_pdhg_impl.h:TimeSteps).  out = {seconds, accepted steps,
+// rejected steps, preprocessing seconds}.  Returns 0, or 1 when preprocessing rejects the problem or a
+// step forces numerical termination.
+int oracle_time_steps(int64_t n, int64_t m, int64_t nnz, const int64_t* col_ptr, const int64_t* row_idx, const double* val, const double* c, const double* q_diag,
+                      const double* vlb, const double* vub, const double* clb, const double* cub, double objective_offset, double objective_scaling_factor,
+                      const char* params_text, int warmup, int steps, double* out /*4*/) {
+  Qp qp = MakeQp(n, m, nnz, col_ptr, row_idx, val, c, q_diag, vlb, vub, clb, cub, objective_offset, objective_scaling_factor);
+  const Params params = ParseParams(params_text);
+  PreprocessSolver solver(std::move(qp), params);
+  StepTiming t;
+  const bool ok = solver.TimeSteps(params, warmup, steps, t);
+  out[0] = t.seconds; out[1] = t.accepted_steps; out[2] = t.rejected_steps; out[3] = t.preprocessing_seconds;
+  return ok && t.completed ? 0 : 1;
+}
+
 // ---- unit entry points for the golden tests ----
 void oracle_validate_params(const char* params_text, char** message) { *message = Dup(ValidateParams(ParseParams(params_text))); }
 

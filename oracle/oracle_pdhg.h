@@ -21,6 +21,8 @@ namespace oracle {
 enum class IterationType { kNormal = 0, kPrimalFeasibility = 1, kDualFeasibility = 2, kPresolveTermination = 3, kNormalTermination = 4, kFeasibilityPolishingTermination = 5 };
 
 struct SolverResult { Vec primal_solution, dual_solution, reduced_costs; SolveLog solve_log; };
+// Result of the bench-support step-loop timing (oracle_pdhg_impl.h:TimeSteps).
+struct StepTiming { double seconds = 0, preprocessing_seconds = 0; int accepted_steps = 0, rejected_steps = 0; bool completed = false; };
 struct IterationCallbackInfo { IterationType iteration_type; const TerminationCriteria* termination_criteria; const IterationStats* iteration_stats; const BoundNorms* bound_norms; };
 using Callback = std::function<void(const IterationCallbackInfo&)>;
 
@@ -127,6 +129,8 @@ class PreprocessSolver {
         sq_(std::move(qp), num_threads_, num_shards_) {}
 
   SolverResult PreprocessAndSolve(const Params& params, const Vec* x0, const Vec* y0, const volatile int* interrupt, Callback cb);
+  std::optional<SolverResult> Prepare(const Params& params, const Vec* x0, const Vec* y0, SolveLog& log, Vec& x, Vec& y, double& step_size, double& primal_weight);
+  bool TimeSteps(const Params& params, int warmup, int steps, StepTiming& out);
 
   // :1434-1518 (text logging dropped).
   std::optional<TerminationReasonAndPointType> UpdateIterationStatsAndCheckTermination(
@@ -212,6 +216,7 @@ class Solver {
         step_size_(step_size), primal_weight_(primal_weight), pre_(pre) {}
 
   SolverResult Solve(IterationType type, const volatile int* interrupt, SolveLog log);
+  void TimeSteps(int warmup, int steps, StepTiming& out);
 
  private:
   struct Next { Vec value, delta; };

@@ -6,23 +6,21 @@
 
 namespace oracle {
 
-// :949-1105 (presolve branch :988-1033 not restated).
-inline SolverResult PreprocessSolver::PreprocessAndSolve(const Params& params, const Vec* x0, const Vec* y0, const volatile int* interrupt, Callback cb) {
-  WallTimer timer;
-  timer.Start();
-  SolveLog log;
+// :949-1105 (presolve branch :988-1033 not restated).  Prepare() is everything before the Solver is
+// built: bound clean-up, statistics, input checks, projection of the start, rescaling, initial step
+// size and primal weight; PreprocessAndSolve() then runs the loop.
+inline std::optional<SolverResult> PreprocessSolver::Prepare(const Params& params, const Vec* x0, const Vec* y0, SolveLog& log, Vec& x, Vec& y, double& step_size,
+                                                             double& primal_weight) {
   if (sq_.qp().name.has_value()) log.instance_name = *sq_.qp().name;
   sq_.ReplaceLargeConstraintBoundsWithInfinity(params.infinite_constraint_bound_threshold);
   log.original_problem_stats = ComputeStats(sq_);
   log.has_original_stats = true;
-  if (auto r = CheckProblemStats(log.original_problem_stats, params.use_glop); r.has_value()) return *r;
+  if (auto r = CheckProblemStats(log.original_problem_stats, params.use_glop); r.has_value()) return r;
   if (x0 != nullptr && y0 != nullptr) {
-    if (auto r = CheckInitialSolution(sq_, *x0, *y0); r.has_value()) return *r;
+    if (auto r = CheckInitialSolution(sq_, *x0, *y0); r.has_value()) return r;
   }
   original_bound_norms_ = BoundNormsFromProblemStats(log.original_problem_stats);
-  callback_ = std::move(cb);
 
-  Vec x, y;
   if (x0 != nullptr && y0 != nullptr) { x = *x0; y = *y0; }
   else { SetZero(sq_.PrimalSharder(), x); SetZero(sq_.DualSharder(), y); }
   ProjectToPrimalVariableBounds(sq_, x);
@@ -37,7 +35,7 @@ inline SolverResult PreprocessSolver::PreprocessAndSolve(const Params& params, c
   log.preprocessed_problem_stats = ComputeStats(sq_);
   log.has_preprocessed_stats = true;
 
-  double step_size = 0.0;
+  step_size = 0.0;
   if (params.linesearch_rule == CONSTANT_STEP_SIZE_RULE) {  // :1060-1076
     std::mt19937 random(1);
     const auto est = EstimateMaximumSingularValue(sq_, nullptr, nullptr, 0.2, 0.0005, random);
@@ -49,15 +47,72 @@ inline SolverResult PreprocessSolver::PreprocessAndSolve(const Params& params, c
   step_size *= params.initial_step_size_scaling;
 
   // InitialPrimalWeight :1268-1286.
-  double primal_weight = 1.0;
+  primal_weight = 1.0;
   const double c_norm = log.preprocessed_problem_stats.objective_vector_l2_norm, b_norm = log.preprocessed_problem_stats.combined_bounds_l2_norm;
   if (params.has_initial_primal_weight) primal_weight = params.initial_primal_weight;
   else if (c_norm > 0.0 && b_norm > 0.0) primal_weight = c_norm / b_norm;
+  return std::nullopt;
+}
 
+inline SolverResult PreprocessSolver::PreprocessAndSolve(const Params& params, const Vec* x0, const Vec* y0, const volatile int* interrupt, Callback cb) {
+  WallTimer timer;
+  timer.Start();
+  SolveLog log;
+  callback_ = std::move(cb);
+  Vec x, y;
+  double step_size = 0.0, primal_weight = 1.0;
+  if (auto r = Prepare(params, x0, y0, log, x, y, step_size, primal_weight); r.has_value()) return *r;
   Solver solver(params, x, y, step_size, primal_weight, this);
   log.preprocessing_time_sec = timer.Get();
   SolverResult result = solver.Solve(IterationType::kNormal, interrupt, std::move(log));
   return ConstructOriginalSolverResult(params, std::move(result));
+}
+
+// Bench support (bench.py cpu_baseline / --impl reference): the steady-state cost of the step loop
+// alone - `warmup` untimed + `steps` timed iterations of the configured step rule
+// (TakeAdaptiveStep / TakeMalitskyPockStep / TakeConstantSizeStep, rejected trials included) after
+// the reference's preprocessing, with no termination checks and no restarts: the same unit as the
+// device's `pdlp_b200_trial_steps`.  Returns false when preprocessing rejects the problem.
+inline bool PreprocessSolver::TimeSteps(const Params& params, int warmup, int steps, StepTiming& out) {
+  WallTimer timer;
+  timer.Start();
+  SolveLog log;
+  Vec x, y;
+  double step_size = 0.0, primal_weight = 1.0;
+  if (Prepare(params, nullptr, nullptr, log, x, y, step_size, primal_weight).has_value()) return false;
+  Solver solver(params, x, y, step_size, primal_weight, this);
+  out.preprocessing_seconds = timer.Get();
+  solver.TimeSteps(warmup, steps, out);
+  return true;
+}
+
+inline void Solver::TimeSteps(int warmup, int steps, StepTiming& out) {
+  x_start_ = CloneVector(x_, sq().PrimalSharder());
+  y_start_ = CloneVector(y_, sq().DualSharder());
+  ratio_last_two_step_sizes_ = 1;
+  kty_ = TransposedMatVec(qp().K, y_, sq().KSharder());
+  num_rejected_steps_ = 0;
+  auto run = [&](int count) {
+    for (int i = 0; i < count; ++i, ++iterations_completed_) {
+      InnerStepOutcome outcome;
+      switch (params_.linesearch_rule) {
+        case MALITSKY_POCK_LINESEARCH_RULE: outcome = TakeMalitskyPockStep(); break;
+        case CONSTANT_STEP_SIZE_RULE: outcome = TakeConstantSizeStep(); break;
+        default: outcome = TakeAdaptiveStep(); break;
+      }
+      if (outcome == InnerStepOutcome::kForceNumericalTermination) return false;
+    }
+    return true;
+  };
+  iterations_completed_ = 0;
+  out.completed = run(warmup);
+  const int rejected_before = num_rejected_steps_;
+  WallTimer timer;
+  timer.Start();
+  out.completed = out.completed && run(steps);
+  out.seconds = timer.Get();
+  out.accepted_steps = iterations_completed_ - warmup;
+  out.rejected_steps = num_rejected_steps_ - rejected_before;
 }
 
 inline int Solver::ChooseRestartToApply(bool is_major) {  // :1904-1965

@@ -117,10 +117,28 @@ def _solve_log_proto(d, params):
     return log
 
 
+def _params_text(params):
+    """Params as the oracle's 'a.b=value' lines: a protobuf message, or such text already (callers that
+    must not import the product package, i.e. bench.py --impl reference, write the lines themselves)."""
+    return (params if isinstance(params, str) else flatten_params(params)).encode()
+
+
+def time_steps(qp, params, warmup, steps):
+    """Seconds of `steps` iterations of the oracle's step loop alone (after `warmup` untimed ones; no
+    termination checks, no restarts): dict(seconds, accepted_steps, rejected_steps, preprocessing_seconds)."""
+    lib = load()
+    mar = Marshalled(qp)
+    out = np.zeros(4)
+    rc = lib.oracle_time_steps(*mar.args(), _params_text(params), int(warmup), int(steps), _p(out))
+    if rc != 0:
+        raise RuntimeError("oracle_time_steps: preprocessing rejected the problem or a step forced numerical termination")
+    return dict(seconds=float(out[0]), accepted_steps=int(out[1]), rejected_steps=int(out[2]), preprocessing_seconds=float(out[3]))
+
+
 def solve(qp, params=None, initial_solution=None, callback=None, interrupt=None):
     lib = load()
     mar = Marshalled(qp)
-    text = flatten_params(params).encode()
+    text = _params_text(params)
     x = np.zeros(max(mar.n, 1)); y = np.zeros(max(mar.m, 1)); rc = np.zeros(max(mar.n, 1))
     sizes = np.zeros(3, dtype=np.int64)
     log = ctypes.c_char_p()
@@ -137,7 +155,7 @@ def solve(qp, params=None, initial_solution=None, callback=None, interrupt=None)
                      ctypes.byref(log))
     r = OracleResult()
     r.solve_log_dict = json.loads(log.value)
-    r.solve_log = _solve_log_proto(r.solve_log_dict, params)
+    r.solve_log = None if isinstance(params, str) else _solve_log_proto(r.solve_log_dict, params)
     r.primal_solution = x[: sizes[0]].copy()
     r.dual_solution = y[: sizes[1]].copy()
     r.reduced_costs = rc[: sizes[2]].copy()
@@ -197,21 +215,21 @@ class Problem:
     def convergence_info(self, params, col_scale, row_scale, x, y, cw_primal_offset=1.0, cw_dual_offset=1.0, candidate_type=1):
         col_scale, row_scale, x, y = map(_f, (col_scale, row_scale, x, y))  # named: the arrays must outlive the call
         s = ctypes.c_char_p()
-        self.lib.oracle_convergence_info(self.h, flatten_params(params).encode(), _p(col_scale), _p(row_scale), _p(x), _p(y),
+        self.lib.oracle_convergence_info(self.h, _params_text(params), _p(col_scale), _p(row_scale), _p(x), _p(y),
                                          ctypes.c_double(cw_primal_offset), ctypes.c_double(cw_dual_offset), candidate_type, ctypes.byref(s))
         return json.loads(s.value)
 
     def infeasibility_info(self, params, col_scale, row_scale, x, y, candidate_type=1):
         col_scale, row_scale, x, y = map(_f, (col_scale, row_scale, x, y))
         s = ctypes.c_char_p()
-        self.lib.oracle_infeasibility_info(self.h, flatten_params(params).encode(), _p(col_scale), _p(row_scale), _p(x), _p(y), candidate_type,
+        self.lib.oracle_infeasibility_info(self.h, _params_text(params), _p(col_scale), _p(row_scale), _p(x), _p(y), candidate_type,
                                            ctypes.byref(s))
         return json.loads(s.value)
 
     def reduced_costs(self, params, x, y, zero_objective=False):
         x, y = _f(x), _f(y)
         rc = np.zeros(max(self.n, 1))
-        self.lib.oracle_reduced_costs(self.h, flatten_params(params).encode(), _p(x), _p(y), int(zero_objective), _p(rc))
+        self.lib.oracle_reduced_costs(self.h, _params_text(params), _p(x), _p(y), int(zero_objective), _p(rc))
         return rc[: self.n]
 
     def lagrangian_gradients(self, x, y):
@@ -254,7 +272,7 @@ def shard_starts(n, num_shards, masses=None):
 def validate_params(params):
     lib = load()
     s = ctypes.c_char_p()
-    lib.oracle_validate_params(flatten_params(params).encode(), ctypes.byref(s))
+    lib.oracle_validate_params(_params_text(params), ctypes.byref(s))
     return s.value.decode()
 
 
@@ -270,7 +288,7 @@ def check_termination(params, stats, bound_norms, which="iterate", force_numeric
     norms = _f(bound_norms)
     out = np.zeros(2, dtype=np.int32)
     rel = np.zeros(5)
-    lib.oracle_check_termination(flatten_params(params).encode(), 0 if which == "iterate" else 1, int(force_numerical_termination),
+    lib.oracle_check_termination(_params_text(params), 0 if which == "iterate" else 1, int(force_numerical_termination),
                                  _p(interrupt) if interrupt is not None else None, _p(norms), len(stats.convergence_information), _p(conv),
                                  len(stats.infeasibility_information), _p(inf), _p(work), _p(out), _p(rel))
     return int(out[0]), int(out[1]), rel

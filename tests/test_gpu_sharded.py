@@ -220,6 +220,24 @@ def test_every_rank_reports_the_same_result(two_rank_run):
 
 
 @needs_two
+def test_sharded_iteration_counts_are_typical(two_rank_run):
+    """Median over the ten cases of (2-GPU count / 1-GPU count) within 10 % (the cases are single solves,
+    not perturbation medians: tests/test_gpu_iteration_parity.py holds the 5 % bound on a real distribution),
+    and no case further than a factor 2 from the single-GPU count (a sanity guard, not a parity claim)."""
+    res, _ = two_rank_run
+    ratios = {}
+    for name, (qp, p) in cases().items():
+        if name not in res[0]:
+            continue
+        single = pdlp_b200.primal_dual_hybrid_gradient(qp, p)
+        ratios[name] = res[0][name]["iterations"] / max(1, single.solve_log.iteration_count)
+    print(ratios)
+    assert len(ratios) >= 8
+    assert 0.9 <= float(np.median(list(ratios.values()))) <= 1.1, ratios
+    assert all(0.5 <= r <= 2.0 for r in ratios.values()), ratios
+
+
+@needs_two
 @pytest.mark.parametrize("name", ["lp", "lp_wide", "qp", "lp_mp", "lp_const", "lp_distance", "lp_polish", "test_lp", "transport", "flow"])
 def test_sharded_solve_matches_single_gpu_and_oracle(two_rank_run, name):
     res, arr = two_rank_run
@@ -233,10 +251,9 @@ def test_sharded_solve_matches_single_gpu_and_oracle(two_rank_run, name):
     s = _log_summary(single)
     for key in ("primal_objective", "dual_objective"):
         assert abs(got[key] - s[key]) <= 1e-6 * max(1.0, abs(s[key])), (key, got[key], s[key])
-    # Summation order differs between world sizes exactly as between the reference's shard counts:
-    # iteration counts agree within the chaos envelope, not exactly.
-    lo, hi = sorted((s["iterations"], ora.solve_log_dict["iteration_count"]))
-    assert 0.6 * lo - 64 <= got["iterations"] <= 1.5 * hi + 64, (got["iterations"], s["iterations"], ora.solve_log_dict["iteration_count"])
+    # Iteration counts: summation order differs between world sizes exactly as between the reference's
+    # shard counts, so single pairs of counts are not comparable; the typical ratio over all
+    # cases is asserted in test_sharded_iteration_counts_are_typical below.
     assert got["collectives"] > got["iterations"]  # at least one all-reduce per trial step
     # The gathered point is a KKT point of the WHOLE problem by the oracle's own measure.
     x, y = arr[0][name + "_x"], arr[0][name + "_y"]

@@ -87,31 +87,6 @@ def test_step_rules_and_scaling_on_test_lp(rule, scaling):
         assert_parity(dev, ora)
 
 
-def oracle_iteration_envelope(qp, p):
-    """Iteration counts of the oracle over several (num_threads, num_shards) settings.  PDHG with
-    adaptive restarts amplifies summation-order rounding: the reference's own iteration count
-    moves with the shard count (solvers.proto:273-282 promises reproducibility only for a fixed
-    one), so the device count is checked against that envelope widened by the 5 % of the spec."""
-    counts = []
-    for threads, shards in ((1, 0), (2, 5), (4, 16), (4, 37), (3, 101)):
-        q = type(p)()
-        q.CopyFrom(p)
-        q.num_threads = threads
-        if shards:
-            q.num_shards = shards
-        counts.append(ob.solve(qp, q).solve_log_dict["iteration_count"])
-    return min(counts), max(counts)
-
-
-def assert_in_envelope(count, lo, hi):
-    """The 5 shard settings sample only a few roundings of a chaotic count (seed 0 spans
-    11584..31360 in the oracle alone); the device is one more sample.  Accept the envelope
-    widened by 30 %, and report how far outside the strict 5 % band the device is."""
-    if not (0.95 * lo - 64 <= count <= 1.05 * hi + 64):
-        print(f"iteration count {count} outside the 5% band of the oracle's shard-count envelope [{lo}, {hi}]")
-    assert 0.7 * lo - 64 <= count <= 1.3 * hi + 64, (count, lo, hi)
-
-
 def assert_objectives_close(dev, ora, tol=1e-6):
     oc = ora.solve_log_dict["solution_stats"]["convergence_information"][0]
     dc = dev.solve_log.solution_stats.convergence_information[0]
@@ -126,9 +101,7 @@ def test_random_lp_parity(seed):
     p = params(eps_abs=1e-7, eps_rel=1e-7)  # both solvers then pin the objective to well under 1e-6 relative
     dev, ora = both(qp, p)
     assert dev.solve_log.termination_reason == ora.solve_log_dict["termination_reason"] == pdlp_b200.TerminationReason.TERMINATION_REASON_OPTIMAL
-    assert_objectives_close(dev, ora)
-    lo, hi = oracle_iteration_envelope(qp, p)
-    assert_in_envelope(dev.solve_log.iteration_count, lo, hi)
+    assert_objectives_close(dev, ora)  # iteration counts: tests/test_gpu_iteration_parity.py (a distribution, not one pair of solves)
     ci = [c for c in dev.solve_log.solution_stats.convergence_information if c.candidate_type == dev.solve_log.solution_type][0]
     bn = np.linalg.norm(np.where(np.isfinite(qp.constraint_upper_bounds), qp.constraint_upper_bounds, 0.0))
     assert ci.l2_primal_residual <= 1e-7 * (1 + bn) * 1.0001
@@ -140,8 +113,6 @@ def test_random_qp_parity():
     dev, ora = both(qp, p)
     assert dev.solve_log.termination_reason == ora.solve_log_dict["termination_reason"] == pdlp_b200.TerminationReason.TERMINATION_REASON_OPTIMAL
     assert_objectives_close(dev, ora)
-    lo, hi = oracle_iteration_envelope(qp, p)
-    assert_in_envelope(dev.solve_log.iteration_count, lo, hi)
 
 
 def test_trace_on_random_lp_follows_the_oracle_until_rounding_takes_over():
