@@ -24,6 +24,9 @@ constexpr int kMaxSlots = 16;        // reduction slots an op may use
 #endif
 constexpr int kStreamChunk = PDLP_STREAM_CHUNK;   // nonzeros staged in shared memory per work block
 constexpr int kMaxGrid = 148 * 8;    // 148 SMs x 8 resident CTAs: persistent grid-stride launches
+// Work blocks of several rows hold at most this many nonzeros: the asynchronous row-stream kernel stages a
+// window that starts at a multiple of four nonzeros (128-bit copies), up to three before the block.
+constexpr int kMaxStagedNnz = kStreamChunk - 4;
 
 // Reduction slot kinds.  kMax slots must only ever receive values >= 0 or be
 // initialised by the op through Op::Init (we initialise every slot with Identity()).
@@ -160,34 +163,8 @@ constexpr int kStagedSize = kStreamChunk + 3 * (kStreamChunk / 16);  // with the
 // 24 % of the shared-memory wavefronts of both SpMV kernels on C3 were bank conflicts,
 // profiles/r01_ncu_step_kernels_c3_v6.md.)
 __device__ __forceinline__ int Skew(int k, int pad) { return k + pad * (k >> 4); }
-// PDLP_ROWSTREAM_LEAN=1 selects a staging path with fewer issued instructions per nonzero (the
-// row-stream kernels are issue-bound): work blocks that fill all but the last of a
-// thread's kPerThread positions run without per-position predicates, staged positions advance by
-// one stride per position instead of being recomputed, the bank-pad rule avoids the integer
-// division, the threads per row come from a count of leading zeros instead of a loop, and rounds of
-// the epilogue prefetch that no thread has a row in are skipped.  Same arithmetic, same staged
-// layout, same results (bit-identical under tests/kernel_emu, profiles/r01_sass_rowstream_lean.md
-// for the instruction counts).  Off by default until it has been timed on the device (build with
-// EXTRA_NVCCFLAGS=-DPDLP_ROWSTREAM_LEAN=1; scripts/gpu_call_lean.sh).
-#ifndef PDLP_ROWSTREAM_LEAN
-#define PDLP_ROWSTREAM_LEAN 0
-#endif
-// Unroll factor of the per-row sum out of shared memory (1 = a load -> add chain per nonzero, as
-// shipped; 4 = four shared loads in flight per thread at ~15 % more instructions for short rows; the
-// order of the additions does not change).  A second knob for the same A/B run.
-#ifndef PDLP_ROWSTREAM_REDUCE_UNROLL
-#define PDLP_ROWSTREAM_REDUCE_UNROLL 1
-#endif
-constexpr int kReduceUnroll = PDLP_ROWSTREAM_REDUCE_UNROLL;
 __device__ __forceinline__ int BankPadFor(int nz, int nrows) {
-#if PDLP_ROWSTREAM_LEAN
-  // nz <= kStreamChunk and nrows <= kMaxRowsPerBlock are exact in fp32; when nrows divides nz the
-  // approximate quotient is within 2 ulp of the integer and rounds to it, otherwise no integer
-  // passes the multiplication test.
-  const int len = __float2int_rn(__fdividef(static_cast<float>(nz), static_cast<float>(nrows)));
-#else
   const int len = nz / nrows;
-#endif
   if (len * nrows != nz) return 3;
   if (len & 1) return 0;
   return (len & 15) == 0 ? 2 : 3;
@@ -243,17 +220,7 @@ __device__ __forceinline__ void CpAsyncWaitAll() { asm volatile("cp.async.wait_g
 template <class Op>
 __device__ __forceinline__ void PrefetchIndices(const Op& op, int* idx_buf, int first_nz, int nz) {
   if constexpr (HasSplitLoad<Op>::value) {
-    if (nz <= kStreamChunk) {
-#if PDLP_ROWSTREAM_LEAN
-      if (nz > (kPerThread - 1) * kBlock) {
-        // Only the last position of a thread can fall outside the block.
-        const int* src = op.IndexAddress(first_nz + static_cast<int>(threadIdx.x));
-        int* dst = idx_buf + threadIdx.x;
-#pragma unroll
-        for (int i = 0; i < kPerThread - 1; ++i) CpAsync4(dst + i * kBlock, src + i * kBlock);
-        if (static_cast<int>(threadIdx.x) + (kPerThread - 1) * kBlock < nz) CpAsync4(dst + (kPerThread - 1) * kBlock, src + (kPerThread - 1) * kBlock);
-      } else
-#endif
+    if (nz <= kMaxStagedNnz) {
       {
 #pragma unroll
         for (int i = 0; i < kPerThread; ++i) {
@@ -264,38 +231,6 @@ __device__ __forceinline__ void PrefetchIndices(const Op& op, int* idx_buf, int 
     }
   }
   CpAsyncCommit();
-}
-
-// Staging of one work block of a split-load op (indices already in idx_buf): gathers, asynchronous
-// copies of the values, the row offsets and the next block's indices, then the products in place.
-// kDense: every position but a thread's last is inside the block, so only that one is predicated.
-template <bool kDense, class Op>
-__device__ __forceinline__ void StageSplitLean(const Op& op, double* staged, int* idx_buf, int* row_raw, const RowBlocks& rb, int p0, int nz, int r0, int nrows,
-                                               int pad, int np0, int next_nz) {
-  const int tid = threadIdx.x;
-  const bool last_live = tid + (kPerThread - 1) * kBlock < nz;
-  auto live = [&](int i) { return kDense ? (i < kPerThread - 1 || last_live) : (tid + i * kBlock < nz); };
-  // Position of nonzero tid + i * kBlock: Skew(tid, pad) + i * (kBlock + pad * kBlock / 16).
-  double* mine = staged + Skew(tid, pad);
-  const int step = kBlock + pad * (kBlock >> 4);
-  double g[kPerThread];
-#pragma unroll
-  for (int i = 0; i < kPerThread; ++i) g[i] = live(i) ? op.Gather(idx_buf[tid + i * kBlock]) : 0.0;
-  // The index reads above stay ahead of the asynchronous copies that overwrite idx_buf below.
-  asm volatile("" ::: "memory");
-  const double* values = op.ValueAddress(p0 + tid);
-#pragma unroll
-  for (int i = 0; i < kPerThread; ++i) {
-    if (live(i)) CpAsync8(mine + i * step, values + i * kBlock);
-  }
-#pragma unroll 1
-  for (int i = tid; i <= nrows; i += kBlock) CpAsync4(row_raw + i, rb.row_ptr + r0 + i);
-  PrefetchIndices(op, idx_buf, np0, next_nz);
-  CpAsyncWaitAll();
-#pragma unroll
-  for (int i = 0; i < kPerThread; ++i) {
-    if (live(i)) mine[i * step] = op.Product(mine[i * step], g[i]);
-  }
 }
 
 template <class Op>
@@ -330,7 +265,7 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
       int fr0 = 0, fr1 = 0, fp0 = 0, fp1 = 0;
       if (b2 < rb.num_blocks) { fr0 = rb.block_start[b2]; fr1 = rb.block_start[b2 + 1]; fp0 = rb.block_nz[b2]; fp1 = rb.block_nz[b2 + 1]; }
       const int next_nz = np1 - np0;  // 0 when there is no next block
-      if (nz > kStreamChunk) {
+      if (nz > kMaxStagedNnz) {
         // One long row (r1 == r0 + 1 by construction): CTA-wide strided reduce.
         PrefetchIndices(op, idx_buf, np0, next_nz);
         const Pre pre = OpRowPrefetch(op, r0);
@@ -350,7 +285,6 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
       } else {
         // This block's column indices were copied to shared memory a block ago (own positions).
         CpAsyncWaitAll();
-#if !PDLP_ROWSTREAM_LEAN
         int jx[kPerThread];
         if constexpr (HasSplitLoad<Op>::value) {
 #pragma unroll
@@ -359,7 +293,6 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
             jx[i] = k < nz ? idx_buf[k] : 0;
           }
         }
-#endif
         // Issue order matters (warps issue in order, and ptxas places the cp.async wait directly
         // behind the last copy): epilogue operands and gathers first - their addresses are known -
         // then the asynchronous copies of this block's values and row offsets and of the next
@@ -367,14 +300,8 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
         const int nrows = r1 - r0;
         const int shift = BankPadFor(nz, nrows);
         // Threads per row: largest power of two <= min(32, kBlock / nrows), at least 1.
-#if PDLP_ROWSTREAM_LEAN
-        // 2^l * nrows <= kBlock = 2^8  <=>  l <= 8 - ceil(log2(nrows)),  ceil(log2(n)) = 32 - clz(n - 1).
-        static_assert(kBlock == 256, "log_t below assumes kBlock == 256");
-        const int log_t = min(5, max(0, __clz(nrows - 1) - 24));
-#else
         int log_t = 0;
         while (log_t < 5 && (2 << log_t) * nrows <= kBlock) ++log_t;
-#endif
         const int t = 1 << log_t;
         const int sub = threadIdx.x >> log_t, lane = threadIdx.x & (t - 1);
         const int groups = kBlock >> log_t;
@@ -382,16 +309,9 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
 #pragma unroll
         for (int u = 0; u < kPreRows; ++u) {
           const int rr = sub + u * groups;
-#if PDLP_ROWSTREAM_LEAN
-          if (u * groups >= nrows) break;  // uniform across the CTA: no thread has a row in this or a later round
-#endif
           if (lane == 0 && rr < nrows) pre[u] = OpRowPrefetch(op, r0 + rr);
         }
         if constexpr (HasSplitLoad<Op>::value) {
-#if PDLP_ROWSTREAM_LEAN
-          if (nz > (kPerThread - 1) * kBlock) StageSplitLean<true>(op, staged, idx_buf, row_raw, rb, p0, nz, r0, nrows, shift, np0, next_nz);
-          else StageSplitLean<false>(op, staged, idx_buf, row_raw, rb, p0, nz, r0, nrows, shift, np0, next_nz);
-#else
           double g[kPerThread];
 #pragma unroll
           for (int i = 0; i < kPerThread; ++i) {
@@ -412,7 +332,6 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
             const int k = threadIdx.x + i * kBlock;
             if (k < nz) staged[Skew(k, shift)] = op.Product(staged[Skew(k, shift)], g[i]);
           }
-#endif
         } else {
           for (int i = threadIdx.x; i <= nrows; i += kBlock) CpAsync4(row_raw + i, rb.row_ptr + r0 + i);
           CpAsyncCommit();
@@ -431,9 +350,6 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
             double a = op.RowInit();
             if (rr < nrows) {
               const int q1 = row_raw[rr + 1] - p0;
-#if PDLP_ROWSTREAM_REDUCE_UNROLL > 1
-#pragma unroll kReduceUnroll
-#endif
               for (int q = row_raw[rr] - p0 + lane; q < q1; q += t) a = op.RowAdd(a, staged[Skew(q, shift)], r0 + rr);
             }
             // All 32 lanes take part in the shuffles (t divides 32).
@@ -462,6 +378,10 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
   }
   BlockReduceAndStore<Op>(red, partials);
 }
+
+}  // namespace pdlp_b200
+#include "pdlp_rowstream_async.cuh"
+namespace pdlp_b200 {
 
 // ---- the two phases of a column-sharded pass over the CSR block (launched by
 // pdlp_launch.cuh:EnqueueRows around the all-reduce of the shared rows' sums) ----
@@ -493,6 +413,8 @@ struct PartialRowOp {
   __device__ double Gather(int index) const { return op.Gather(index); }
   template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
   __device__ double Product(double value, double gathered) const { return op.Product(value, gathered); }
+  template <class O = Op, class = std::enable_if_t<HasAsyncGather<O>::value>>
+  __device__ const double* GatherAddress(int index) const { return op.GatherAddress(index); }
   __device__ double RowInit() const { return op.RowInit(); }
   __device__ double RowAdd(double acc, double staged, int row) const { return op.RowAdd(acc, staged, row); }
   __device__ double RowMerge(double a, double b) const { return op.RowMerge(a, b); }
