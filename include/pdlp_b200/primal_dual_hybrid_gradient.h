@@ -1,4 +1,10 @@
-// The C++ entry point of the B200 PDLP solver.  Same names, argument order, ownership
+// The C++ entry point of the B200 PDLP solver (public header: include/pdlp_b200/, next to the two
+// headers it needs, pdlp_schema.h and pdlp_termination.h; link against libpdlp_b200.so).  The
+// declarations live in namespace pdlp_b200 and are also reachable under the reference's own
+// qualified names, operations_research::pdlp::PrimalDualHybridGradient etc. (end of this file), so a
+// caller of ortools/pdlp/primal_dual_hybrid_gradient.h compiles against this header unchanged apart
+// from the container types.  tests/test_cpp_header.py compiles and runs such a caller.
+// Same names, argument order, ownership
 // and error convention as the reference's public header
 //   ortools/pdlp/primal_dual_hybrid_gradient.h:30-156 and quadratic_program.h:53-143,
 // with std::vector / a plain CSC struct where the reference uses Eigen (Eigen is not in
@@ -121,4 +127,9 @@ SolverResult PrimalDualHybridGradient(QuadraticProgram qp, const PrimalDualHybri
                                       std::function<void(const IterationCallbackInfo&)> iteration_stats_callback = nullptr);
 
 }  // namespace pdlp_b200
+
+// The reference's namespace (primal_dual_hybrid_gradient.h:28, quadratic_program.h:30).
+namespace operations_research::pdlp {
+using namespace ::pdlp_b200;  // NOLINT: qualified lookup of operations_research::pdlp::X finds pdlp_b200::X
+}  // namespace operations_research::pdlp
 #endif  // PDLP_B200_PRIMAL_DUAL_HYBRID_GRADIENT_H_

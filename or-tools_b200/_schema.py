@@ -1,6 +1,6 @@
 """Protobuf message classes for the two PDLP schemas, built at import time from the
 schema description exported by the native library (`pdlp_b200_describe_schema`), so the
-C++ structs in csrc/pdlp_schema.h stay the single source of truth.
+C++ structs in include/pdlp_b200/pdlp_schema.h stay the single source of truth.
 
 The classes are wire- and text-format compatible with
 /root/reference/ortools/pdlp/solvers.proto:20-481 and solve_log.proto:24-450 (package

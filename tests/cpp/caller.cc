@@ -1,0 +1,65 @@
+// A caller of the reference's public C++ API, written against include/pdlp_b200/primal_dual_hybrid_gradient.h
+// under the reference's own qualified names (ortools/pdlp/primal_dual_hybrid_gradient.h:140-156).
+// Built and run by tests/test_cpp_header.py.   usage: caller cpu | caller gpu
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+#include "pdlp_b200/primal_dual_hybrid_gradient.h"
+
+namespace pdlp = operations_research::pdlp;
+
+// TestLp of ortools/pdlp/test_util.cc:35-60: optimum -34 at x = [-1, 8, 1, 2.5].
+static pdlp::QuadraticProgram TestLp() {
+  const double inf = std::numeric_limits<double>::infinity();
+  pdlp::QuadraticProgram qp;
+  qp.ResizeAndInitialize(4, 4);
+  qp.constraint_matrix.outer_index = {0, 3, 4, 7, 9};
+  qp.constraint_matrix.inner_index = {0, 1, 2, 0, 0, 1, 3, 0, 3};
+  qp.constraint_matrix.values = {2, 1, 4, 1, 1, 1, 1.5, 2, -1};
+  qp.objective_vector = {5.5, -2, -1, 1};
+  qp.constraint_lower_bounds = {12, -inf, -4, -1};
+  qp.constraint_upper_bounds = {12, 7, inf, 1};
+  qp.variable_lower_bounds = {-inf, -2, -inf, 2.5};
+  qp.variable_upper_bounds = {inf, inf, 6, 3.5};
+  qp.objective_offset = -14;
+  return qp;
+}
+
+int main(int argc, char** argv) {
+  const bool gpu = argc > 1 && std::strcmp(argv[1], "gpu") == 0;
+  pdlp::PrimalDualHybridGradientParams params;
+  params.termination_criteria.mut().simple_optimality_criteria.mut().eps_optimal_absolute = 1.0e-6;
+  params.termination_criteria.mut().simple_optimality_criteria.mut().eps_optimal_relative = 1.0e-6;
+  if (!gpu) {
+    // Errors found before the device is touched come back the reference's way: a normal return with the
+    // reason in the log (primal_dual_hybrid_gradient.cc:717-725, :2787-2831).
+    pdlp::QuadraticProgram bad = TestLp();
+    bad.constraint_lower_bounds.pop_back();
+    const pdlp::SolverResult r1 = pdlp::PrimalDualHybridGradient(bad, params);
+    if (r1.solve_log.termination_reason != pdlp::TERMINATION_REASON_INVALID_PROBLEM) return 1;
+    pdlp::PrimalDualHybridGradientParams bad_params = params;
+    bad_params.major_iteration_frequency = 0;
+    const pdlp::SolverResult r2 = pdlp::PrimalDualHybridGradient(TestLp(), bad_params);
+    if (r2.solve_log.termination_reason != pdlp::TERMINATION_REASON_INVALID_PARAMETER) return 2;
+    pdlp::PrimalAndDualSolution start{{0, 0, 0}, {0, 0, 0, 0}};  // wrong primal size
+    const pdlp::SolverResult r3 = pdlp::PrimalDualHybridGradient(TestLp(), params, start);
+    if (r3.solve_log.termination_reason != pdlp::TERMINATION_REASON_INVALID_INITIAL_SOLUTION) return 3;
+    if (!pdlp::IsLinearProgram(TestLp()) || !pdlp::HasValidBounds(TestLp()) || !pdlp::ValidateQuadraticProgramDimensions(TestLp()).empty()) return 4;
+    std::printf("cpu ok: %s | %s\n", r1.solve_log.termination_string.get().c_str(), r2.solve_log.termination_string.get().c_str());
+    return 0;
+  }
+  int callbacks = 0;
+  std::atomic<bool> interrupt{false};
+  const pdlp::SolverResult r = pdlp::PrimalDualHybridGradient(TestLp(), params, &interrupt, [&](const pdlp::IterationCallbackInfo&) { ++callbacks; });
+  if (r.solve_log.termination_reason != pdlp::TERMINATION_REASON_OPTIMAL) return 10;
+  const double want[4] = {-1, 8, 1, 2.5};
+  for (int j = 0; j < 4; ++j) if (std::fabs(r.primal_solution[j] - want[j]) > 1.0e-4) return 11;
+  double objective = -14;
+  const double c[4] = {5.5, -2, -1, 1};
+  for (int j = 0; j < 4; ++j) objective += c[j] * r.primal_solution[j];
+  if (std::fabs(objective + 34.0) > 1.0e-4 || callbacks < 2) return 12;
+  std::printf("gpu ok: OPTIMAL in %d iterations, objective %.6f, %d callbacks, %lld kernel launches\n", static_cast<int>(r.solve_log.iteration_count), objective,
+              callbacks, pdlp::LastSolveCounters().kernel_launches);
+  return 0;
+}
