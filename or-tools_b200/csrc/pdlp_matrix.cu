@@ -86,10 +86,10 @@ HostBlocks ComputeBlocks(const P* ptr, int rows, int cut = -1) {
     int64_t nz = static_cast<int64_t>(ptr[r + 1]) - static_cast<int64_t>(ptr[r]);
     mx = nz > mx ? static_cast<int>(nz) : mx;
     ++r;
-    if (nz <= kMaxStagedNnz) {
+    if (nz <= kStreamChunk) {
       while (r < limit && r - begin < kMaxRowsPerBlock) {
         const int64_t next = static_cast<int64_t>(ptr[r + 1]) - static_cast<int64_t>(ptr[r]);
-        if (nz + next > kMaxStagedNnz) break;
+        if (nz + next > kStreamChunk) break;
         nz += next;
         mx = next > mx ? static_cast<int>(next) : mx;
         ++r;
@@ -139,16 +139,8 @@ void BuildDeviceMatrixT(int64_t n, int64_t m, int64_t nnz, const I* col_ptr, con
   SparseRows& csr = out->by_row;
   csc.rows = static_cast<int>(n); csc.cols = static_cast<int>(m); csc.nnz = nnz;
   csr.rows = static_cast<int>(m); csr.cols = static_cast<int>(n); csr.nnz = nnz;
-  // Four elements of padding behind the nonzeros: the asynchronous row-stream kernel copies indices four
-  // and values two at a time from windows aligned to four nonzeros (pdlp_rowstream_async.cuh), so its
-  // last copies read up to three elements past the end.  Zeroed: a padded index is a valid one.
-  constexpr int64_t kPadding = 4;
-  csc.ptr.Resize(n + 1); csc.idx.Resize(nnz + kPadding); csc.val.Resize(nnz + kPadding);
-  csr.ptr.Resize(m + 1); csr.idx.Resize(nnz + kPadding); csr.val.Resize(nnz + kPadding);
-  for (SparseRows* s : {&csc, &csr}) {
-    PDLP_CUDA_CHECK(cudaMemsetAsync(s->idx.get() + nnz, 0, kPadding * sizeof(int), stream));
-    PDLP_CUDA_CHECK(cudaMemsetAsync(s->val.get() + nnz, 0, kPadding * sizeof(double), stream));
-  }
+  csc.ptr.Resize(n + 1); csc.idx.Resize(nnz); csc.val.Resize(nnz);
+  csr.ptr.Resize(m + 1); csr.idx.Resize(nnz); csr.val.Resize(nnz);
 
   // The CSC work-block partition only needs the host offsets: it runs on a host thread while the
   // matrix is uploaded and transposed (a sequential scan of n offsets, ~0.1 s at n = 3.3e7).  Offsets

@@ -24,9 +24,6 @@ constexpr int kMaxSlots = 16;        // reduction slots an op may use
 #endif
 constexpr int kStreamChunk = PDLP_STREAM_CHUNK;   // nonzeros staged in shared memory per work block
 constexpr int kMaxGrid = 148 * 8;    // 148 SMs x 8 resident CTAs: persistent grid-stride launches
-// Work blocks of several rows hold at most this many nonzeros: the asynchronous row-stream kernel stages a
-// window that starts at a multiple of four nonzeros (128-bit copies), up to three before the block.
-constexpr int kMaxStagedNnz = kStreamChunk - 4;
 
 // Reduction slot kinds.  kMax slots must only ever receive values >= 0 or be
 // initialised by the op through Op::Init (we initialise every slot with Identity()).
@@ -220,7 +217,7 @@ __device__ __forceinline__ void CpAsyncWaitAll() { asm volatile("cp.async.wait_g
 template <class Op>
 __device__ __forceinline__ void PrefetchIndices(const Op& op, int* idx_buf, int first_nz, int nz) {
   if constexpr (HasSplitLoad<Op>::value) {
-    if (nz <= kMaxStagedNnz) {
+    if (nz <= kStreamChunk) {
       {
 #pragma unroll
         for (int i = 0; i < kPerThread; ++i) {
@@ -265,7 +262,7 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
       int fr0 = 0, fr1 = 0, fp0 = 0, fp1 = 0;
       if (b2 < rb.num_blocks) { fr0 = rb.block_start[b2]; fr1 = rb.block_start[b2 + 1]; fp0 = rb.block_nz[b2]; fp1 = rb.block_nz[b2 + 1]; }
       const int next_nz = np1 - np0;  // 0 when there is no next block
-      if (nz > kMaxStagedNnz) {
+      if (nz > kStreamChunk) {
         // One long row (r1 == r0 + 1 by construction): CTA-wide strided reduce.
         PrefetchIndices(op, idx_buf, np0, next_nz);
         const Pre pre = OpRowPrefetch(op, r0);
@@ -379,10 +376,6 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
   BlockReduceAndStore<Op>(red, partials);
 }
 
-}  // namespace pdlp_b200
-#include "pdlp_rowstream_async.cuh"
-namespace pdlp_b200 {
-
 // ---- the two phases of a column-sharded pass over the CSR block (launched by
 // pdlp_launch.cuh:EnqueueRows around the all-reduce of the shared rows' sums) ----
 // An op whose row accumulator combines with max instead of + declares `bool RowCombineMax() const`.
@@ -413,8 +406,6 @@ struct PartialRowOp {
   __device__ double Gather(int index) const { return op.Gather(index); }
   template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
   __device__ double Product(double value, double gathered) const { return op.Product(value, gathered); }
-  template <class O = Op, class = std::enable_if_t<HasAsyncGather<O>::value>>
-  __device__ const double* GatherAddress(int index) const { return op.GatherAddress(index); }
   __device__ double RowInit() const { return op.RowInit(); }
   __device__ double RowAdd(double acc, double staged, int row) const { return op.RowAdd(acc, staged, row); }
   __device__ double RowMerge(double a, double b) const { return op.RowMerge(a, b); }

@@ -104,7 +104,6 @@ struct DualStepOp : OneSum {
   __device__ const int* IndexAddress(int64_t k) const { return idx + k; }
   __device__ const double* ValueAddress(int64_t k) const { return val + k; }
   __device__ double Gather(int j) const { return xbar[j]; }
-  __device__ const double* GatherAddress(int j) const { return xbar + j; }
   __device__ double Product(double v, double g) const { return v * g; }
   __device__ double Load(int64_t k) const { return val[k] * xbar[idx[k]]; }
   __device__ double RowInit() const { return 0.0; }
@@ -147,7 +146,6 @@ struct KtyStepOp {
   __device__ const int* IndexAddress(int64_t k) const { return idx + k; }
   __device__ const double* ValueAddress(int64_t k) const { return val + k; }
   __device__ double Gather(int i) const { return yn[i]; }
-  __device__ const double* GatherAddress(int i) const { return yn + i; }
   __device__ double Product(double v, double g) const { return v * g; }
   __device__ double Load(int64_t k) const { return val[k] * yn[idx[k]]; }
   __device__ double RowInit() const { return 0.0; }

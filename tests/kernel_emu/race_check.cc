@@ -2,12 +2,8 @@
 // ThreadSanitizer.  Every __syncthreads is a std::barrier, so any pair of conflicting accesses to
 // a __shared__ array that is not separated by a barrier (or by the shuffle exchange) is reported as
 // a data race.  Exit code 0 = no report.  Built and run by tests/test_kernel_emulation.py:
-//   g++ -std=c++20 -O1 -g -fsanitize=thread -pthread -DPDLP_EMU_ASYNC={0,1} race_check.cc
-// (0: the plain skeleton's split-load path; 1: the asynchronous pipeline of pdlp_rowstream_async.cuh)
+//   g++ -std=c++20 -O1 -g -fsanitize=thread -pthread race_check.cc
 #define PDLP_EMULATE 1
-#ifndef PDLP_EMU_ASYNC
-#define PDLP_EMU_ASYNC 1
-#endif
 #include "cuda_emu.h"
 
 #include "pdlp_skeletons.cuh"
@@ -26,7 +22,6 @@ struct SplitOp {
   const int* IndexAddress(int64_t k) const { return idx + k; }
   const double* ValueAddress(int64_t k) const { return val + k; }
   double Gather(int j) const { return x[j]; }
-  const double* GatherAddress(int j) const { return x + j; }
   double Product(double v, double g) const { return v * g; }
   double Load(int64_t k) const { return val[k] * x[idx[k]]; }
   double RowInit() const { return 0.0; }
@@ -46,8 +41,8 @@ std::vector<int> Partition(const std::vector<int>& ptr) {
     const int begin = r;
     long nz = ptr[r + 1] - ptr[r];
     ++r;
-    if (nz <= kMaxStagedNnz) {
-      while (r < rows && r - begin < kMaxRowsPerBlock && nz + (ptr[r + 1] - ptr[r]) <= kMaxStagedNnz) { nz += ptr[r + 1] - ptr[r]; ++r; }
+    if (nz <= kStreamChunk) {
+      while (r < rows && r - begin < kMaxRowsPerBlock && nz + (ptr[r + 1] - ptr[r]) <= kStreamChunk) { nz += ptr[r + 1] - ptr[r]; ++r; }
     }
     starts.push_back(r);
   }
@@ -59,10 +54,10 @@ int RunShape(const std::vector<int>& lengths, int grid, bool defer) {
   for (int l : lengths) ptr.push_back(ptr.back() + l);
   const int rows = static_cast<int>(lengths.size()), nnz = ptr.back(), cols = 97;
   std::mt19937 gen(7);
-  std::vector<int> idx(nnz + 4, 0);        // + the device allocation's padding
-  std::vector<double> val(nnz + 4, 0.0), x(cols), out(rows, 1.0), want(rows, 1.0);
-  for (int k = 0; k < nnz; ++k) idx[k] = static_cast<int>(gen() % cols);
-  for (int k = 0; k < nnz; ++k) val[k] = static_cast<double>(static_cast<int>(gen() % 7) - 3);
+  std::vector<int> idx(nnz);
+  std::vector<double> val(nnz), x(cols), out(rows, 1.0), want(rows, 1.0);
+  for (int& j : idx) j = static_cast<int>(gen() % cols);
+  for (double& v : val) v = static_cast<double>(static_cast<int>(gen() % 7) - 3);
   for (double& v : x) v = static_cast<double>(static_cast<int>(gen() % 9) - 4);
   for (int i = 0; i < rows; ++i) for (int k = ptr[i]; k < ptr[i + 1]; ++k) want[i] += val[k] * x[idx[k]];
   const std::vector<int> starts = Partition(ptr);
@@ -75,8 +70,7 @@ int RunShape(const std::vector<int>& lengths, int grid, bool defer) {
   double* p = partials.data();
   const SplitOp op{val.data(), idx.data(), x.data(), out.data()};
   cuda_emu::defer_async = defer;
-  if (PDLP_EMU_ASYNC != 0) cuda_emu::Launch(grid, kBlock, [=]() { rowstream_async_kernel<SplitOp>(op, rb, p); });
-  else cuda_emu::Launch(grid, kBlock, [=]() { rowstream_kernel<SplitOp>(op, rb, p); });
+  cuda_emu::Launch(grid, kBlock, [=]() { rowstream_kernel<SplitOp>(op, rb, p); });
   int bad = 0;
   for (int i = 0; i < rows; ++i) bad += out[i] != want[i];
   return bad;

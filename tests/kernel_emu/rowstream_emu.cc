@@ -1,13 +1,6 @@
-// CPU run of rowstream_kernel<Op> (or-tools_b200/csrc/pdlp_skeletons.cuh) and of rowstream_async_kernel<Op>
-// (pdlp_rowstream_async.cuh) under the shim in cuda_emu.h, for tests/test_kernel_emulation.py.  Built
-// twice: -DPDLP_EMU_ASYNC=0 (the split-load op runs the plain skeleton) and =1 (it runs the asynchronous
-// pipeline, like the step kernels' ops on the device).  Every input array is placed right before an
-// inaccessible page, so a read past its end faults; the matrix arrays carry the four elements of
-// padding the device allocation gives them (pdlp_matrix.cu) and not one more.
+// CPU run of rowstream_kernel<Op> (or-tools_b200/csrc/pdlp_skeletons.cuh) under the shim in
+// cuda_emu.h, for tests/test_kernel_emulation.py.  // Every input array is placed right before an inaccessible page, so a read past its end faults.
 #define PDLP_EMULATE 1
-#ifndef PDLP_EMU_ASYNC
-#define PDLP_EMU_ASYNC 1
-#endif
 #include "cuda_emu.h"
 
 #include "pdlp_skeletons.cuh"
@@ -27,7 +20,6 @@ struct SplitOp {
   const int* IndexAddress(int64_t k) const { return idx + k; }
   const double* ValueAddress(int64_t k) const { return val + k; }
   double Gather(int j) const { return x[j]; }
-  const double* GatherAddress(int j) const { return x + j; }
   double Product(double v, double g) const { return v * g; }
   double Load(int64_t k) const { return val[k] * x[idx[k]]; }
   double RowInit() const { return 0.0; }
@@ -61,14 +53,11 @@ struct PlainMaxOp {
 // Copy of an input array that ends right before an inaccessible page: a read past the end faults.
 class Guarded {
  public:
-  // `padding` zero bytes follow the copy (still before the guard page); the copy starts 16-byte aligned
-  // like a cudaMalloc'ed array.
-  Guarded(const void* src, size_t bytes, size_t padding = 0) {
+  Guarded(const void* src, size_t bytes) {
     const size_t page = 4096;
-    const size_t total = (bytes + padding + 15) / 16 * 16;
-    body_ = (total + page - 1) / page * page;
+    body_ = (bytes + page - 1) / page * page;
     base_ = static_cast<char*>(mmap(nullptr, body_ + page, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0));
-    data_ = base_ + body_ - total;
+    data_ = base_ + body_ - bytes;
     if (bytes > 0) std::memcpy(data_, src, bytes);
     mprotect(base_ + body_, page, PROT_NONE);
   }
@@ -82,8 +71,7 @@ template <class Op>
 void Run(const Op& op, const RowBlocks& rb, int grid, double* totals) {
   std::vector<double> partials(static_cast<size_t>(grid) * Op::kNumSlots, 0.0);
   double* p = partials.data();
-  if constexpr (PDLP_EMU_ASYNC != 0 && HasAsyncGather<Op>::value) cuda_emu::Launch(grid, kBlock, [=]() { rowstream_async_kernel<Op>(op, rb, p); });
-  else cuda_emu::Launch(grid, kBlock, [=]() { rowstream_kernel<Op>(op, rb, p); });
+  cuda_emu::Launch(grid, kBlock, [=]() { rowstream_kernel<Op>(op, rb, p); });
   for (int s = 0; s < Op::kNumSlots; ++s) {  // finalize_kernel's fixed order
     double t = SlotIdentity(Op::SlotKindOf(s));
     for (int b = 0; b < grid; ++b) t = SlotCombine(Op::SlotKindOf(s), t, partials[static_cast<size_t>(b) * Op::kNumSlots + s]);
@@ -123,8 +111,6 @@ extern "C" int emu_map_reduce(const double* a, double* b, long long count, doubl
   return 0;
 }
 
-extern "C" int emu_is_async() { return PDLP_EMU_ASYNC; }
-extern "C" int emu_max_staged_nnz() { return pdlp_b200::kMaxStagedNnz; }
 extern "C" int emu_stream_chunk() { return pdlp_b200::kStreamChunk; }
 extern "C" int emu_max_rows_per_block() { return pdlp_b200::kMaxRowsPerBlock; }
 
@@ -136,7 +122,7 @@ extern "C" int emu_rowstream(int op_kind, const int* row_ptr, const int* idx, co
   const size_t nnz = static_cast<size_t>(row_ptr[rows]);
   int cols = 0;
   for (size_t k = 0; k < nnz; ++k) cols = std::max(cols, idx[k] + 1);
-  const Guarded g_ptr(row_ptr, (rows + 1) * sizeof(int)), g_idx(idx, nnz * sizeof(int), 4 * sizeof(int)), g_val(val, nnz * sizeof(double), 4 * sizeof(double)), g_x(x, cols * sizeof(double)),
+  const Guarded g_ptr(row_ptr, (rows + 1) * sizeof(int)), g_idx(idx, nnz * sizeof(int)), g_val(val, nnz * sizeof(double)), g_x(x, cols * sizeof(double)),
       g_bias(bias, rows * sizeof(double)), g_start(block_start, (num_blocks + 1) * sizeof(int)), g_nz(block_nz.data(), (num_blocks + 1) * sizeof(int));
   const pdlp_b200::RowBlocks rb{g_ptr.as<int>(), g_start.as<int>(), g_nz.as<int>(), num_blocks, rows};
   cuda_emu::defer_async = defer_async != 0;

@@ -5,9 +5,7 @@ threads, __syncthreads / shuffles = barriers, cp.async landing either at issue o
 runs it on the real work-block partition (pdlp_b200.work_blocks).  What this pins down without a
 GPU: the index arithmetic of the staging and reduction phases (bank-padded positions, threads per
 row, prefetch distances, the long-row path, ragged and empty rows, the per-thread tail positions),
-the placement of waits and barriers, and that the asynchronous software pipeline of the hot ops
-(pdlp_rowstream_async.cuh; build variant 1, "lean" in the parameter names for history) computes
-bit-identical results to the plain skeleton (variant 0).  It says nothing about speed or about the hardware memory model; the
+and the placement of waits and barriers.  It says nothing about speed or about the hardware memory model; the
 GPU parity tests (tests/test_gpu_solve.py) remain the check of the shipped binary."""
 import ctypes
 import os
@@ -24,27 +22,19 @@ BUILD = os.path.join(ROOT, "tests", "_build")
 CSRC = os.path.join(ROOT, "or-tools_b200", "csrc")
 
 
-def padded(a):
-    """Four zero elements behind a matrix index / value array: the padding the device allocation carries
-    for the asynchronous row-stream kernel's aligned 16-byte copies (pdlp_matrix.cu)."""
-    return np.ascontiguousarray(np.concatenate([a, np.zeros(4, dtype=a.dtype)]))
-
-
-def _build(lean):
+def _build():
     os.makedirs(BUILD, exist_ok=True)
-    out = os.path.join(BUILD, f"rowstream_emu_lean{lean}.so")
-    sources = [os.path.join(EMU, "rowstream_emu.cc"), os.path.join(EMU, "cuda_emu.h"), os.path.join(CSRC, "pdlp_skeletons.cuh"), os.path.join(CSRC, "pdlp_rowstream_async.cuh")]
+    out = os.path.join(BUILD, "rowstream_emu.so")
+    sources = [os.path.join(EMU, "rowstream_emu.cc"), os.path.join(EMU, "cuda_emu.h"), os.path.join(CSRC, "pdlp_skeletons.cuh")]
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(s) for s in sources):
         subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-Wno-attributes",
-                        f"-DPDLP_EMU_ASYNC={lean}", "-I" + EMU, "-I" + CSRC, sources[0], "-o", out], check=True)
-    lib = ctypes.CDLL(out)
-    assert lib.emu_is_async() == lean
-    return lib
+                        "-I" + EMU, "-I" + CSRC, sources[0], "-o", out], check=True)
+    return ctypes.CDLL(out)
 
 
 @pytest.fixture(scope="module")
 def libs():
-    return {0: _build(0), 1: _build(1)}
+    return {0: _build()}
 
 
 def make_matrix(lengths, cols, rng, integer=True):
@@ -97,7 +87,7 @@ SHAPES = {
     "poisson10": lambda rng: rng.poisson(10, 900),            # ragged rows, blocks a few short of full
     "empty_rows": lambda rng: rng.integers(0, 2, 5000),       # 1024-row blocks, one thread per row, tail loop
     "wide_rows": lambda rng: rng.integers(300, 2048, 12),     # 1-6 rows per block: 32 threads per row
-    "long_rows": lambda rng: np.array([5, 0, 5000, 7, 2044, 2045, 2048, 1, 9000, 3, 3]),  # CTA-wide path between staged blocks
+    "long_rows": lambda rng: np.array([5, 0, 5000, 7, 2048, 2049, 1, 9000, 3, 3]),  # CTA-wide path between staged blocks
     "short_tail": lambda rng: np.concatenate([np.full(256, 8), [5]]),               # last block of 5 nonzeros
     "one_nonzero": lambda rng: np.array([1]),
     "ends_at_1700": lambda rng: np.full(170, 10),             # last block just below the all-but-last-position-full rule
@@ -105,9 +95,8 @@ SHAPES = {
 }
 
 
-@pytest.mark.parametrize("lean", [0, 1])
 @pytest.mark.parametrize("shape", sorted(SHAPES))
-def test_rowstream_matches_a_serial_product_exactly(libs, shape, lean):
+def test_rowstream_matches_a_serial_product_exactly(libs, shape, lean=0):
     rng = np.random.default_rng(17)
     mat = make_matrix(SHAPES[shape](rng), 333, rng)
     for op in (0, 1):
@@ -116,17 +105,6 @@ def test_rowstream_matches_a_serial_product_exactly(libs, shape, lean):
             out, tot = run(libs[lean], op, mat, grid, defer)
             np.testing.assert_array_equal(out, want_out, err_msg=f"op {op} grid {grid} defer {defer}")
             np.testing.assert_array_equal(tot[:2 if op == 0 else 1], want_tot[:2 if op == 0 else 1])
-
-
-@pytest.mark.parametrize("shape", ["uniform16", "poisson10", "wide_rows", "long_rows", "empty_rows"])
-def test_async_pipeline_is_bit_identical_to_the_plain_skeleton(libs, shape):
-    rng = np.random.default_rng(23)
-    mat = make_matrix(SHAPES[shape](rng), 1000, rng, integer=False)
-    base_out, base_tot = run(libs[0], 0, mat, 2, 0)
-    for defer in (0, 1):
-        out, tot = run(libs[1], 0, mat, 2, defer)
-        np.testing.assert_array_equal(out, base_out)
-        np.testing.assert_array_equal(tot, base_tot)
 
 
 @pytest.mark.parametrize("count, grid", [(0, 1), (1, 1), (255, 1), (256, 2), (1000, 3), (5000, 7)])
@@ -152,20 +130,20 @@ def test_dense_skeleton_and_its_two_stage_reduction(libs, count, grid):
 
 # ---- the adaptive trial step (K1 - K4 + averaging) against a restatement of the reference ----
 
-def _build_step(lean):
-    out = os.path.join(BUILD, f"step_emu_lean{lean}.so")
+def _build_step():
+    out = os.path.join(BUILD, "step_emu.so")
     sources = [os.path.join(EMU, "step_emu.cc"), os.path.join(EMU, "cuda_emu.h"), os.path.join(CSRC, "pdlp_skeletons.cuh"),
-               os.path.join(CSRC, "pdlp_step_kernels.cuh"), os.path.join(CSRC, "pdlp_step_state.h"), os.path.join(CSRC, "pdlp_rowstream_async.cuh")]
+               os.path.join(CSRC, "pdlp_step_kernels.cuh"), os.path.join(CSRC, "pdlp_step_state.h")]
     os.makedirs(BUILD, exist_ok=True)
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(s) for s in sources):
         subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-Wno-attributes",
-                        f"-DPDLP_EMU_ASYNC={lean}", "-I" + EMU, "-I" + CSRC, sources[0], "-o", out], check=True)
+                        "-I" + EMU, "-I" + CSRC, sources[0], "-o", out], check=True)
     return ctypes.CDLL(out)
 
 
 @pytest.fixture(scope="module")
 def step_libs():
-    return {0: _build_step(0), 1: _build_step(1)}
+    return {0: _build_step()}
 
 
 def reference_adaptive_trials(K, c, q, vlb, vub, clb, cub, x, y, step, w, trials, constant=False):
@@ -223,7 +201,7 @@ def emulated_adaptive_trials(lib, K, c, q, vlb, vub, clb, cub, x, y, step, w, tr
     m, n = K.shape
     i32 = lambda a: np.ascontiguousarray(a, dtype=np.int32)
     f64 = lambda a: np.ascontiguousarray(a, dtype=np.float64)
-    arrays = dict(rp=i32(csr.indptr), ri=padded(i32(csr.indices)), rv=padded(f64(csr.data)), cp=i32(csc.indptr), ci=padded(i32(csc.indices)), cv=padded(f64(csc.data)))
+    arrays = dict(rp=i32(csr.indptr), ri=i32(csr.indices), rv=f64(csr.data), cp=i32(csc.indptr), ci=i32(csc.indices), cv=f64(csc.data))
     rb, _, _ = pdlp_b200.work_blocks(arrays["rp"])
     cb, _, _ = pdlp_b200.work_blocks(arrays["cp"])
     rb, cb = i32(rb), i32(cb)
@@ -259,30 +237,21 @@ def step_problem(seed, qp):
     return K, c, q, vlb, vub, clb, cub, x0, y0
 
 
-@pytest.mark.parametrize("lean", [0, 1])
+@pytest.mark.parametrize("defer", [0, 1])
 @pytest.mark.parametrize("qp", [False, True])
-def test_adaptive_trial_steps_follow_the_reference_step_rule(step_libs, qp, lean):
+def test_adaptive_trial_steps_follow_the_reference_step_rule(step_libs, qp, defer):
     prob = step_problem(2 if not qp else 6, qp)
     # a first step far too long: the rule must reject, shrink, then accept and grow again
     step, w, trials = 50.0, 0.2, 14
     want = reference_adaptive_trials(*prob, step, w, trials)
     assert want["rejected"] >= 2 and want["completed"] >= 8
-    got = emulated_adaptive_trials(step_libs[lean], *prob, step, w, trials, defer=lean)
+    got = emulated_adaptive_trials(step_libs[0], *prob, step, w, trials, defer=defer)
     assert (got["completed"], got["rejected"]) == (want["completed"], want["rejected"])
     assert got["active"] == 1 and got["total_trials"] == trials
     for key in ("x", "y", "avg_x", "avg_y"):
         np.testing.assert_allclose(got[key], want[key], rtol=1e-11, atol=1e-12, err_msg=key)
     for key in ("step", "movement", "nonlinearity", "weight_sum"):
         np.testing.assert_allclose(got[key], want[key], rtol=1e-10, err_msg=key)
-
-
-def test_async_and_plain_steps_are_bit_identical(step_libs):
-    prob = step_problem(9, False)
-    a = emulated_adaptive_trials(step_libs[0], *prob, 0.5, 1.0, 6)
-    b = emulated_adaptive_trials(step_libs[1], *prob, 0.5, 1.0, 6, defer=1)
-    for key in ("x", "y", "avg_x", "avg_y"):
-        np.testing.assert_array_equal(a[key], b[key])
-    assert a["step"] == b["step"] and a["movement"] == b["movement"]
 
 
 def test_constant_size_steps_follow_the_reference(step_libs):
@@ -350,7 +319,7 @@ def test_malitsky_pock_steps_follow_the_reference(step_libs):
     m, n = K.shape
     i32 = lambda a: np.ascontiguousarray(a, dtype=np.int32)
     f64 = lambda a: np.ascontiguousarray(a, dtype=np.float64)
-    rp, ri, rv, cp, ci, cv = i32(csr.indptr), padded(i32(csr.indices)), padded(f64(csr.data)), i32(csc.indptr), padded(i32(csc.indices)), padded(f64(csc.data))
+    rp, ri, rv, cp, ci, cv = i32(csr.indptr), i32(csr.indices), f64(csr.data), i32(csc.indptr), i32(csc.indices), f64(csc.data)
     rb, cb = i32(pdlp_b200.work_blocks(rp)[0]), i32(pdlp_b200.work_blocks(cp)[0])
     xo, yo, ax, ay, st = f64(x0).copy(), f64(y0).copy(), np.zeros(n), np.zeros(m), np.zeros(10)
     params = np.array([0.7, 0.99, 1.0])
@@ -407,7 +376,7 @@ def test_sharded_dual_step_over_emulated_ranks_matches_one_rank(step_libs, world
         blocks, cut_block, _ = pdlp_b200.work_blocks(ptr, S if 0 < S < local.size else -1)
         if S >= local.size:
             cut_block = len(blocks) - 1
-        ranks.append(dict(m=local.size, ptr=ptr, idx=padded(i32(block.indices)), val=padded(np.ascontiguousarray(block.data)), blocks=i32(blocks), cut=int(cut_block),
+        ranks.append(dict(m=local.size, ptr=ptr, idx=i32(block.indices), val=np.ascontiguousarray(block.data), blocks=i32(blocks), cut=int(cut_block),
                           xbar=np.ascontiguousarray(xbar[starts[r]:starts[r + 1]]), y0=sharing.scatter(r, y), y1=np.zeros(local.size),
                           clb=sharing.scatter(r, clb), cub=sharing.scatter(r, cub)))
     sums = np.zeros(S)
@@ -625,18 +594,17 @@ def test_rescaling_matches_the_oracle(qp_case, ruiz, l2):
 
 # ---- shared-memory protocol under a race detector ----
 
-@pytest.mark.parametrize("lean", [0, 1])
-def test_rowstream_shared_memory_protocol_is_race_free(lean):
+def test_rowstream_shared_memory_protocol_is_race_free():
     """tests/kernel_emu/race_check.cc under ThreadSanitizer: with __syncthreads as the only
     cross-thread ordering, every conflicting pair of accesses to the staged products, the row offsets
     and the single index buffer (this block's indices read, the next block's copied into the same
     positions) must be separated by a barrier, in both cp.async orders.  Removing one barrier from the
     kernel makes this fail (checked by hand when the test was written)."""
-    exe = os.path.join(BUILD, f"race_check_lean{lean}")
+    exe = os.path.join(BUILD, "race_check")
     src = os.path.join(EMU, "race_check.cc")
     os.makedirs(BUILD, exist_ok=True)
     build = subprocess.run(["g++", "-std=c++20", "-O1", "-g", "-fsanitize=thread", "-pthread", "-Wno-unknown-pragmas", "-Wno-attributes",
-                            f"-DPDLP_EMU_ASYNC={lean}", "-I" + EMU, "-I" + CSRC, src, "-o", exe], capture_output=True, text=True)
+                            "-I" + EMU, "-I" + CSRC, src, "-o", exe], capture_output=True, text=True)
     if build.returncode != 0 and ("tsan" in build.stderr.lower() or "sanitize" in build.stderr.lower()):
         pytest.skip("ThreadSanitizer runtime not available: " + build.stderr.strip().splitlines()[-1])
     assert build.returncode == 0, build.stderr

@@ -1,15 +1,14 @@
 """Host-side invariants of the work-block partition the row-stream kernels run on
 (pdlp_matrix.cu:ComputeBlocks through pdlp_b200_work_blocks).  The kernels stage
 one block in shared memory, so a block that broke these limits would corrupt a solve rather than
-fail: at most 2044 nonzeros unless it is one long row (2048-slot windows that start at a multiple of
-four nonzeros, pdlp_rowstream_async.cuh), at most 1024 rows, no block across the shared / private cut
-of a sharded constraint block."""
+fail: at most 2048 nonzeros unless it is one long row, at most 1024 rows, no block across the
+shared / private cut of a sharded constraint block."""
 import numpy as np
 import pytest
 
 import pdlp_b200
 
-CHUNK, MAX_ROWS = 2044, 1024  # kMaxStagedNnz, kMaxRowsPerBlock
+CHUNK, MAX_ROWS = 2048, 1024
 
 
 def offsets_of(lengths):
@@ -37,8 +36,8 @@ SHAPES = {
     "poisson10": lambda rng: rng.poisson(10, 4000),
     "empty_rows": lambda rng: rng.integers(0, 2, 6000),
     "all_empty": lambda rng: np.zeros(3000, dtype=np.int64),
-    "long_rows": lambda rng: np.where(rng.random(300) < 0.1, rng.integers(2045, 9000, 300), rng.integers(0, 40, 300)),
-    "exactly_chunk": lambda rng: np.array([2044, 2044, 1, 2043, 1, 2045, 2048, 0, 0, 5]),
+    "long_rows": lambda rng: np.where(rng.random(300) < 0.1, rng.integers(2049, 9000, 300), rng.integers(0, 40, 300)),
+    "exactly_chunk": lambda rng: np.array([2048, 2048, 1, 2047, 1, 2049, 0, 0, 5]),
     "one_row": lambda rng: np.array([7]),
 }
 
