@@ -235,6 +235,31 @@ pdlp_b200_status pdlp_b200_trial_steps(pdlp_b200_device_problem* h, int steps, d
 pdlp_b200_status pdlp_b200_trial_steps_profiled(pdlp_b200_device_problem* h, int steps, double step_size, double primal_weight, const double* x,
                                                 const double* y, double* kernel_seconds /*5*/);
 
+/* K v WITHOUT ANY ALLOCATION: out[rows] = K v for a CSR matrix the caller holds in device memory.
+ * No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same kernel as pdlp_b200_matvec(which = 1) (rowstream_kernel<RowDotOp>); the work-block table
+ * that pdlp_b200_problem_create keeps in cudaMalloc'ed arrays is built on the device into a
+ * file-scope static __device__ array of sizeof(int) * 2 * (PDLP_B200_NO_ALLOC_MAX_ROWS + 1) + 64 bytes
+ * (about 2 MB), which every GPU that loads the library holds until the process exits
+ * (or-tools_b200/csrc/pdlp_noalloc.cu).  The call runs no cudaMalloc / cudaFree / allocating library
+ * routine; it enqueues on `stream` (a cudaStream_t, NULL = the default stream) and returns after the
+ * result is complete.
+ *   rows, cols        shape of K; rows > PDLP_B200_NO_ALLOC_MAX_ROWS is rejected with
+ *                     PDLP_B200_BAD_ARGUMENT and a message naming the limit
+ *   row_ptr           rows + 1 ascending int32 offsets, row_ptr[rows] = number of nonzeros (< 2^31)
+ *   col_idx, values   column (int32, in [0, cols)) and value of every nonzero, row by row
+ *   v (cols), out (rows)
+ *   ALL FIVE ARRAYS ARE DEVICE POINTERS on `device` (-1: the current device); host pointers fault.
+ * Rows that several lanes share are summed in a lane order that may differ from pdlp_b200_matvec's
+ * (the table is cut differently): results agree to rounding (1e-12 relative), not bit for bit.
+ * The static array is shared by every call on a GPU and keeps the last call's contents; the call
+ * clears what it needs cleared.  Calls that overlap on the same GPU (other streams, other threads)
+ * race on it: serialise them. */
+#define PDLP_B200_NO_ALLOC_MAX_ROWS 262144
+pdlp_b200_status pdlp_b200_matvec_no_alloc(int64_t rows, int64_t cols, const int32_t* row_ptr, const int32_t* col_idx, const double* values,
+                                           const double* v, double* out, int device, void* stream);
+
 /* Host only (no device needed): the work-block partition the row-stream kernels run on
  * (at most 2048 nonzeros and 1024 rows per block, a longer row alone in its block),
  * from `rows + 1` compressed offsets.  cut in (0, rows): no block straddles that row (the

@@ -122,13 +122,18 @@ _lib.pdlp_b200_unique_id.argtypes = [ctypes.c_void_p]
 _lib.pdlp_b200_validate_params.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_void_p)]
 _lib.pdlp_b200_default_params.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_size_t)]
 
+# Device pointers in, device pointer out, nothing allocated (include/pdlp_b200.h); NO_ALLOC_MAX_ROWS = PDLP_B200_NO_ALLOC_MAX_ROWS.
+_lib.pdlp_b200_matvec_no_alloc.argtypes = [ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                           ctypes.c_int, ctypes.c_void_p]
+NO_ALLOC_MAX_ROWS = 262144
+
 EXPORTED_SYMBOLS = [
     "pdlp_b200_solve", "pdlp_b200_validate_params", "pdlp_b200_default_params", "pdlp_b200_describe_schema",
     "pdlp_b200_last_error", "pdlp_b200_free", "pdlp_b200_problem_create", "pdlp_b200_problem_destroy",
     "pdlp_b200_matvec", "pdlp_b200_scaled_norms", "pdlp_b200_stats", "pdlp_b200_rescale", "pdlp_b200_kkt_stats",
     "pdlp_b200_reduced_costs", "pdlp_b200_localized_bounds", "pdlp_b200_trial_steps", "pdlp_b200_trial_steps_profiled",
     "pdlp_b200_check_termination", "pdlp_b200_unique_id", "pdlp_b200_solve_sharded", "pdlp_b200_problem_create_sharded", "pdlp_b200_release_communicators",
-    "pdlp_b200_work_blocks",
+    "pdlp_b200_work_blocks", "pdlp_b200_matvec_no_alloc",
 ]
 
 

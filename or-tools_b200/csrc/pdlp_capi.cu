@@ -517,6 +517,22 @@ pdlp_b200_status pdlp_b200_matvec(pdlp_b200_device_problem* h, int which, const 
   });
 }
 
+// No counterpart in the reference: K v from caller-owned device arrays with the
+// work-block table in a static device array; kernels and scratch in pdlp_noalloc.cu.
+pdlp_b200_status pdlp_b200_matvec_no_alloc(int64_t rows, int64_t cols, const int32_t* row_ptr, const int32_t* col_idx, const double* values, const double* v,
+                                           double* out, int device, void* stream) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (rows < 0 || cols < 0 || row_ptr == nullptr || (rows > 0 && out == nullptr)) return Fail(PDLP_B200_BAD_ARGUMENT, "pdlp_b200_matvec_no_alloc: bad argument");
+    if (rows > PDLP_B200_NO_ALLOC_MAX_ROWS) {
+      return Fail(PDLP_B200_BAD_ARGUMENT, "pdlp_b200_matvec_no_alloc: " + std::to_string(rows) + " rows exceed the static scratch limit of " +
+                                              std::to_string(PDLP_B200_NO_ALLOC_MAX_ROWS) + " rows (use pdlp_b200_problem_create + pdlp_b200_matvec)");
+    }
+    SelectDevice(device);
+    MatVecNoAlloc(rows, cols, row_ptr, col_idx, values, v, out, static_cast<cudaStream_t>(stream));
+    return PDLP_B200_OK;
+  });
+}
+
 pdlp_b200_status pdlp_b200_scaled_norms(pdlp_b200_device_problem* h, int which, int l2, const double* row_scale, const double* col_scale, double* out) {
   return Guard([&]() -> pdlp_b200_status {
     if (h == nullptr || row_scale == nullptr || col_scale == nullptr || out == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "bad argument");

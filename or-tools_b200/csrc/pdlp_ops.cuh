@@ -135,5 +135,9 @@ LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProb
                                                  double primal_weight, double radius, bool use_diagonal_qp_solver, double diagonal_qp_tolerance,
                                                  int* tr_passes);
 
+// K v from caller-owned device CSR arrays with the work-block table in a static device array
+// (pdlp_noalloc.cu; the kernel side of pdlp_b200_matvec_no_alloc, which has no counterpart in the reference).
+void MatVecNoAlloc(int64_t rows, int64_t cols, const int* row_ptr, const int* col_idx, const double* values, const double* v, double* out, cudaStream_t stream);
+
 }  // namespace pdlp_b200
 #endif  // PDLP_B200_OPS_CUH_
