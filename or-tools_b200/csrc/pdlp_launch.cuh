@@ -17,15 +17,6 @@ namespace pdlp_b200 {
 
 inline bool IsSharded(const Workspace& ws) { return ws.comm != nullptr && ws.comm->sharded(); }
 
-// Which skeleton runs an op's row-stream pass: PDLP_ROWSTREAM_PIPELINED=1 sends the split-load ops (the two
-// SpMV kernels of the trial step and their sharded phase-1 wrappers) through the register-pipelined kernel
-// (pdlp_rowstream_pipelined.cuh); every other op, and every op when it is 0, runs rowstream_kernel.
-#ifndef PDLP_ROWSTREAM_PIPELINED
-#define PDLP_ROWSTREAM_PIPELINED 0
-#endif
-template <class Op>
-constexpr bool UsesPipelinedRowStream() { return PDLP_ROWSTREAM_PIPELINED != 0 && HasSplitLoad<Op>::value; }
-
 // Persistent grid of a row-stream launch: one wave of resident CTAs (SMs x occupancy of this
 // instantiation, asked from the runtime once), never more CTAs than work blocks.
 template <class Op>
@@ -33,22 +24,11 @@ inline int RowStreamGrid(const SparseRows& s) {
   static const int resident = [] {
     int device = 0, sms = 148, per_sm = PDLP_ROWSTREAM_MIN_CTAS;
     if (cudaGetDevice(&device) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-    if constexpr (UsesPipelinedRowStream<Op>()) {
-      PDLP_CUDA_CHECK(cudaFuncSetAttribute(rowstream_pipelined_kernel<Op>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sizeof(PipeSmem))));
-      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rowstream_pipelined_kernel<Op>, kBlock, sizeof(PipeSmem)) != cudaSuccess || per_sm < 1) per_sm = 1;
-    } else {
-      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rowstream_kernel<Op>, kBlock, 0) != cudaSuccess || per_sm < 1) per_sm = PDLP_ROWSTREAM_MIN_CTAS;
-    }
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rowstream_kernel<Op>, kBlock, 0) != cudaSuccess || per_sm < 1) per_sm = PDLP_ROWSTREAM_MIN_CTAS;
     const int g = sms * per_sm;
     return g > kMaxGrid ? kMaxGrid : g;
   }();
   return s.num_blocks < 1 ? 1 : (s.num_blocks > resident ? resident : s.num_blocks);
-}
-// The launch itself (grid from RowStreamGrid<Op>, possibly clipped by the caller).
-template <class Op>
-inline void LaunchRowStream(int grid, cudaStream_t stream, const Op& op, const RowBlocks& view, double* partials) {
-  if constexpr (UsesPipelinedRowStream<Op>()) rowstream_pipelined_kernel<Op><<<grid, kBlock, sizeof(PipeSmem), stream>>>(op, view, partials);
-  else rowstream_kernel<Op><<<grid, kBlock, 0, stream>>>(op, view, partials);
 }
 
 // Enqueue only (no finalize, no sync): partial sums land in ws.partials[region].
@@ -74,7 +54,7 @@ inline int EnqueueRows(Workspace& ws, const Op& op, const SparseRows& s, int reg
       if (shared_blocks > 0) {
         const RowBlocks v = s.ViewOfBlocks(0, shared_blocks);
         const int g = std::min(shared_blocks, RowStreamGrid<PartialRowOp<Op>>(s));
-        LaunchRowStream(g, ws.stream, PartialRowOp<Op>{op, sums}, v, partials);
+        rowstream_kernel<PartialRowOp<Op>><<<g, kBlock, 0, ws.stream>>>(PartialRowOp<Op>{op, sums}, v, partials);
         ++ws.launches;
         ws.comm->AllReduce(sums, static_cast<size_t>(s.cut_row), RowCombineIsMax(op), ws.stream);
       }
@@ -82,7 +62,7 @@ inline int EnqueueRows(Workspace& ws, const Op& op, const SparseRows& s, int reg
       if (private_blocks > 0) {
         const RowBlocks v = s.ViewOfBlocks(s.cut_block, private_blocks);
         grid = std::min(private_blocks, RowStreamGrid<Op>(s));
-        LaunchRowStream(grid, ws.stream, op, v, partials);
+        rowstream_kernel<Op><<<grid, kBlock, 0, ws.stream>>>(op, v, partials);
         ++ws.launches;
       }
       if (s.cut_row > 0) {
@@ -93,7 +73,7 @@ inline int EnqueueRows(Workspace& ws, const Op& op, const SparseRows& s, int reg
       }
       return grid > 0 ? grid : 1;
     }
-    LaunchRowStream(RowStreamGrid<PartialRowOp<Op>>(s), ws.stream, PartialRowOp<Op>{op, sums}, s.View(), ws.partials[region].get());
+    rowstream_kernel<PartialRowOp<Op>><<<RowStreamGrid<PartialRowOp<Op>>(s), kBlock, 0, ws.stream>>>(PartialRowOp<Op>{op, sums}, s.View(), ws.partials[region].get());
     ws.comm->AllReduce(sums, static_cast<size_t>(ws.shared_rows), RowCombineIsMax(op), ws.stream);
     const int grid = GridFor(s.rows);
     map_reduce_kernel<FinishRowOp<Op>><<<grid, kBlock, 0, ws.stream>>>(FinishRowOp<Op>{op, sums}, s.rows, ws.partials[region].get());
@@ -101,7 +81,7 @@ inline int EnqueueRows(Workspace& ws, const Op& op, const SparseRows& s, int reg
     return grid;
   }
   const int grid = RowStreamGrid<Op>(s);
-  LaunchRowStream(grid, ws.stream, op, s.View(), ws.partials[region].get());
+  rowstream_kernel<Op><<<grid, kBlock, 0, ws.stream>>>(op, s.View(), ws.partials[region].get());
   ++ws.launches;
   return grid;
 }

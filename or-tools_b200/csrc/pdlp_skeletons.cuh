@@ -376,10 +376,6 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
   BlockReduceAndStore<Op>(red, partials);
 }
 
-}  // namespace pdlp_b200
-#include "pdlp_rowstream_pipelined.cuh"
-namespace pdlp_b200 {
-
 // ---- the two phases of a column-sharded pass over the CSR block (launched by
 // pdlp_launch.cuh:EnqueueRows around the all-reduce of the shared rows' sums) ----
 // An op whose row accumulator combines with max instead of + declares `bool RowCombineMax() const`.

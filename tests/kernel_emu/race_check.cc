@@ -4,9 +4,6 @@
 // a data race.  Exit code 0 = no report.  Built and run by tests/test_kernel_emulation.py:
 //   g++ -std=c++20 -O1 -g -fsanitize=thread -pthread race_check.cc
 #define PDLP_EMULATE 1
-#ifndef PDLP_EMU_PIPELINED
-#define PDLP_EMU_PIPELINED 0
-#endif
 #include "cuda_emu.h"
 
 #include "pdlp_skeletons.cuh"
@@ -73,8 +70,7 @@ int RunShape(const std::vector<int>& lengths, int grid, bool defer) {
   double* p = partials.data();
   const SplitOp op{val.data(), idx.data(), x.data(), out.data()};
   cuda_emu::defer_async = defer;
-  if (PDLP_EMU_PIPELINED != 0) cuda_emu::Launch(grid, kBlock, [=]() { rowstream_pipelined_kernel<SplitOp>(op, rb, p); });
-  else cuda_emu::Launch(grid, kBlock, [=]() { rowstream_kernel<SplitOp>(op, rb, p); });
+  cuda_emu::Launch(grid, kBlock, [=]() { rowstream_kernel<SplitOp>(op, rb, p); });
   int bad = 0;
   for (int i = 0; i < rows; ++i) bad += out[i] != want[i];
   return bad;

@@ -1,9 +1,6 @@
 // CPU run of rowstream_kernel<Op> (or-tools_b200/csrc/pdlp_skeletons.cuh) under the shim in
 // cuda_emu.h, for tests/test_kernel_emulation.py.  // Every input array is placed right before an inaccessible page, so a read past its end faults.
 #define PDLP_EMULATE 1
-#ifndef PDLP_EMU_PIPELINED
-#define PDLP_EMU_PIPELINED 0  // 1: split-load ops run rowstream_pipelined_kernel (pdlp_rowstream_pipelined.cuh)
-#endif
 #include "cuda_emu.h"
 
 #include "pdlp_skeletons.cuh"
@@ -74,8 +71,7 @@ template <class Op>
 void Run(const Op& op, const RowBlocks& rb, int grid, double* totals) {
   std::vector<double> partials(static_cast<size_t>(grid) * Op::kNumSlots, 0.0);
   double* p = partials.data();
-  if constexpr (PDLP_EMU_PIPELINED != 0 && HasSplitLoad<Op>::value) cuda_emu::Launch(grid, kBlock, [=]() { rowstream_pipelined_kernel<Op>(op, rb, p); });
-  else cuda_emu::Launch(grid, kBlock, [=]() { rowstream_kernel<Op>(op, rb, p); });
+  cuda_emu::Launch(grid, kBlock, [=]() { rowstream_kernel<Op>(op, rb, p); });
   for (int s = 0; s < Op::kNumSlots; ++s) {  // finalize_kernel's fixed order
     double t = SlotIdentity(Op::SlotKindOf(s));
     for (int b = 0; b < grid; ++b) t = SlotCombine(Op::SlotKindOf(s), t, partials[static_cast<size_t>(b) * Op::kNumSlots + s]);
@@ -115,7 +111,6 @@ extern "C" int emu_map_reduce(const double* a, double* b, long long count, doubl
   return 0;
 }
 
-extern "C" int emu_is_pipelined() { return PDLP_EMU_PIPELINED; }
 extern "C" int emu_stream_chunk() { return pdlp_b200::kStreamChunk; }
 extern "C" int emu_max_rows_per_block() { return pdlp_b200::kMaxRowsPerBlock; }
 

@@ -3,9 +3,6 @@
 // tests/test_kernel_emulation.py.  The launch sequence and the initial StepState restate
 // EnqueueAdaptiveTrials (pdlp_step.cu) and pdlp_b200_trial_steps (pdlp_capi.cu) for one GPU.
 #define PDLP_EMULATE 1
-#ifndef PDLP_EMU_PIPELINED
-#define PDLP_EMU_PIPELINED 0
-#endif
 #include "cuda_emu.h"
 
 #include "pdlp_step_kernels.cuh"
@@ -34,8 +31,7 @@ int LaunchMap(const Op& op, int64_t count, double* partials) {
 template <class Op>
 int LaunchRows(const Op& op, const RowBlocks& rb, int max_grid, double* partials) {
   const int grid = std::max(1, std::min(rb.num_blocks, max_grid));
-  if constexpr (PDLP_EMU_PIPELINED != 0 && HasSplitLoad<Op>::value) cuda_emu::Launch(grid, kBlock, [=]() { rowstream_pipelined_kernel<Op>(op, rb, partials); });
-  else cuda_emu::Launch(grid, kBlock, [=]() { rowstream_kernel<Op>(op, rb, partials); });
+  cuda_emu::Launch(grid, kBlock, [=]() { rowstream_kernel<Op>(op, rb, partials); });
   return grid;
 }
 }  // namespace

@@ -22,22 +22,19 @@ BUILD = os.path.join(ROOT, "tests", "_build")
 CSRC = os.path.join(ROOT, "or-tools_b200", "csrc")
 
 
-def _build(pipelined=0):
+def _build():
     os.makedirs(BUILD, exist_ok=True)
-    out = os.path.join(BUILD, f"rowstream_emu_p{pipelined}.so")
-    sources = [os.path.join(EMU, "rowstream_emu.cc"), os.path.join(EMU, "cuda_emu.h"), os.path.join(CSRC, "pdlp_skeletons.cuh"), os.path.join(CSRC, "pdlp_rowstream_pipelined.cuh")]
+    out = os.path.join(BUILD, "rowstream_emu.so")
+    sources = [os.path.join(EMU, "rowstream_emu.cc"), os.path.join(EMU, "cuda_emu.h"), os.path.join(CSRC, "pdlp_skeletons.cuh")]
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(s) for s in sources):
         subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-Wno-attributes",
-                        f"-DPDLP_EMU_PIPELINED={pipelined}", "-I" + EMU, "-I" + CSRC, sources[0], "-o", out], check=True)
-    lib = ctypes.CDLL(out)
-    assert lib.emu_is_pipelined() == pipelined
-    return lib
+                        "-I" + EMU, "-I" + CSRC, sources[0], "-o", out], check=True)
+    return ctypes.CDLL(out)
 
 
 @pytest.fixture(scope="module")
 def libs():
-    """0: rowstream_kernel for every op; 1: the split-load op runs rowstream_pipelined_kernel."""
-    return {0: _build(0), 1: _build(1)}
+    return {0: _build()}
 
 
 def make_matrix(lengths, cols, rng, integer=True):
@@ -98,9 +95,8 @@ SHAPES = {
 }
 
 
-@pytest.mark.parametrize("lean", [0, 1])  # the build variant (name kept from round 1)
 @pytest.mark.parametrize("shape", sorted(SHAPES))
-def test_rowstream_matches_a_serial_product_exactly(libs, shape, lean):
+def test_rowstream_matches_a_serial_product_exactly(libs, shape, lean=0):
     rng = np.random.default_rng(17)
     mat = make_matrix(SHAPES[shape](rng), 333, rng)
     for op in (0, 1):
@@ -109,17 +105,6 @@ def test_rowstream_matches_a_serial_product_exactly(libs, shape, lean):
             out, tot = run(libs[lean], op, mat, grid, defer)
             np.testing.assert_array_equal(out, want_out, err_msg=f"op {op} grid {grid} defer {defer}")
             np.testing.assert_array_equal(tot[:2 if op == 0 else 1], want_tot[:2 if op == 0 else 1])
-
-
-@pytest.mark.parametrize("shape", ["uniform16", "poisson10", "wide_rows", "long_rows", "empty_rows"])
-def test_pipelined_kernel_is_bit_identical_to_the_plain_skeleton(libs, shape):
-    rng = np.random.default_rng(23)
-    mat = make_matrix(SHAPES[shape](rng), 1000, rng, integer=False)
-    base_out, base_tot = run(libs[0], 0, mat, 2, 0)
-    for defer in (0, 1):
-        out, tot = run(libs[1], 0, mat, 2, defer)
-        np.testing.assert_array_equal(out, base_out)
-        np.testing.assert_array_equal(tot, base_tot)
 
 
 @pytest.mark.parametrize("count, grid", [(0, 1), (1, 1), (255, 1), (256, 2), (1000, 3), (5000, 7)])
@@ -145,20 +130,20 @@ def test_dense_skeleton_and_its_two_stage_reduction(libs, count, grid):
 
 # ---- the adaptive trial step (K1 - K4 + averaging) against a restatement of the reference ----
 
-def _build_step(pipelined=0):
-    out = os.path.join(BUILD, f"step_emu_p{pipelined}.so")
+def _build_step():
+    out = os.path.join(BUILD, "step_emu.so")
     sources = [os.path.join(EMU, "step_emu.cc"), os.path.join(EMU, "cuda_emu.h"), os.path.join(CSRC, "pdlp_skeletons.cuh"),
-               os.path.join(CSRC, "pdlp_step_kernels.cuh"), os.path.join(CSRC, "pdlp_step_state.h"), os.path.join(CSRC, "pdlp_rowstream_pipelined.cuh")]
+               os.path.join(CSRC, "pdlp_step_kernels.cuh"), os.path.join(CSRC, "pdlp_step_state.h")]
     os.makedirs(BUILD, exist_ok=True)
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(s) for s in sources):
         subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-Wno-attributes",
-                        f"-DPDLP_EMU_PIPELINED={pipelined}", "-I" + EMU, "-I" + CSRC, sources[0], "-o", out], check=True)
+                        "-I" + EMU, "-I" + CSRC, sources[0], "-o", out], check=True)
     return ctypes.CDLL(out)
 
 
 @pytest.fixture(scope="module")
 def step_libs():
-    return {0: _build_step(0), 1: _build_step(1)}
+    return {0: _build_step()}
 
 
 def reference_adaptive_trials(K, c, q, vlb, vub, clb, cub, x, y, step, w, trials, constant=False):
@@ -267,15 +252,6 @@ def test_adaptive_trial_steps_follow_the_reference_step_rule(step_libs, qp, defe
         np.testing.assert_allclose(got[key], want[key], rtol=1e-11, atol=1e-12, err_msg=key)
     for key in ("step", "movement", "nonlinearity", "weight_sum"):
         np.testing.assert_allclose(got[key], want[key], rtol=1e-10, err_msg=key)
-
-
-def test_pipelined_and_plain_steps_are_bit_identical(step_libs):
-    prob = step_problem(9, False)
-    a = emulated_adaptive_trials(step_libs[0], *prob, 0.5, 1.0, 6)
-    b = emulated_adaptive_trials(step_libs[1], *prob, 0.5, 1.0, 6, defer=1)
-    for key in ("x", "y", "avg_x", "avg_y"):
-        np.testing.assert_array_equal(a[key], b[key])
-    assert a["step"] == b["step"] and a["movement"] == b["movement"]
 
 
 def test_constant_size_steps_follow_the_reference(step_libs):
@@ -618,18 +594,17 @@ def test_rescaling_matches_the_oracle(qp_case, ruiz, l2):
 
 # ---- shared-memory protocol under a race detector ----
 
-@pytest.mark.parametrize("pipelined", [0, 1])
-def test_rowstream_shared_memory_protocol_is_race_free(pipelined):
+def test_rowstream_shared_memory_protocol_is_race_free():
     """tests/kernel_emu/race_check.cc under ThreadSanitizer: with __syncthreads as the only
     cross-thread ordering, every conflicting pair of accesses to the staged products, the row offsets
     and the single index buffer (this block's indices read, the next block's copied into the same
     positions) must be separated by a barrier, in both cp.async orders.  Removing one barrier from the
     kernel makes this fail (checked by hand when the test was written)."""
-    exe = os.path.join(BUILD, f"race_check_p{pipelined}")
+    exe = os.path.join(BUILD, "race_check")
     src = os.path.join(EMU, "race_check.cc")
     os.makedirs(BUILD, exist_ok=True)
     build = subprocess.run(["g++", "-std=c++20", "-O1", "-g", "-fsanitize=thread", "-pthread", "-Wno-unknown-pragmas", "-Wno-attributes",
-                            f"-DPDLP_EMU_PIPELINED={pipelined}", "-I" + EMU, "-I" + CSRC, src, "-o", exe], capture_output=True, text=True)
+                            "-I" + EMU, "-I" + CSRC, src, "-o", exe], capture_output=True, text=True)
     if build.returncode != 0 and ("tsan" in build.stderr.lower() or "sanitize" in build.stderr.lower()):
         pytest.skip("ThreadSanitizer runtime not available: " + build.stderr.strip().splitlines()[-1])
     assert build.returncode == 0, build.stderr
