@@ -501,7 +501,7 @@ def main():
         solve_info = {"solve_iterations": its, "solve_trial_steps": trials, "solve_wall_sec": wall_max,
                       "solve_setup_sec": counters.get("setup_seconds"), "solve_loop_sec": loop_sec,
                       "solve_device_loop_sec": counters.get("device_loop_seconds"), "solve_kernel_launches": counters.get("kernel_launches"),
-                      "solve_collectives": counters.get("collectives"), "solve_upload_sec": counters.get("upload_seconds"), "solve_nccl_symmetric_buffers": counters.get("symmetric_buffers"),
+                      "solve_collectives": counters.get("collectives"), "solve_upload_sec": counters.get("upload_seconds"), "solve_nccl_symmetric_buffers": counters.get("symmetric_buffers"), "solve_peer_exchanges": counters.get("peer_exchanges"),
                       "primal_objective": ci[0].primal_objective if len(ci) else None,
                       "relative_kkt_eps": workload_eps(name),
                       # the solver's own iteration rate (termination checks and restarts inside) and the
@@ -544,7 +544,9 @@ def main():
             "config": make_config(name, args.scale, n_global, m_global if sharded else m, nnz_global, world, sharded),
             "value_unit_note": "trial steps (accepted + rejected) per second of the resident problem, no termination checks; loop_iterations_per_sec is the solver's own iteration rate",
             "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": int(launches), "parity": parity,
-            "nvlink": {"exchange_bytes_per_step_per_rank": 8 * num_shared + 8 * 4, "shared_constraints": num_shared, "constraints_on_rank0": m} if sharded else None,
+            "nvlink": {"exchange": "peer memory (CUDA IPC): every rank stores its partial sums of the shared rows into every peer, then sums its N slots locally in rank order"
+                                   if solve_info.get("solve_peer_exchanges") else "ncclAllReduce",
+                       "pushed_bytes_per_step_per_rank": (world - 1) * (8 * num_shared + 8 * 4), "shared_constraints": num_shared, "constraints_on_rank0": m} if sharded else None,
             "roofline": {"bound": "hbm", "achieved": step_gbs, "peak": peak_all, "unit": "GB/s",
                          "frac": step_gbs / peak_all,
                          "traffic": None if sharded or args.scale != 1.0 else recorded_traffic(name, dominant["kernel"]),

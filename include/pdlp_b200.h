@@ -77,9 +77,10 @@ typedef struct {
   double setup_seconds;         /* upload + transpose + stats + rescaling */
   double loop_seconds;          /* host wall time of the iteration loop */
   double device_loop_seconds;   /* CUDA-event time of the iteration loop */
-  long long collectives;        /* NCCL all-reduces enqueued (0 on one GPU) */
+  long long collectives;        /* exchange steps enqueued: NCCL all-reduces + peer-memory exchanges (0 on one GPU) */
   double upload_seconds;        /* host->device copies, CSR build, communicator set-up */
   int symmetric_buffers;        /* exchange buffers NCCL registered as symmetric windows (0: plain all-reduce) */
+  long long peer_exchanges;     /* exchange steps that went through peer memory instead of ncclAllReduce (counted in `collectives` too) */
 } pdlp_b200_counters;
 
 /* Solves `problem`.

@@ -113,6 +113,7 @@ struct SolveCounters {
   double setup_seconds = 0.0;
   long long collectives = 0;         // NCCL all-reduces enqueued (0 on one GPU)
   int symmetric_buffers = 0;         // exchange buffers NCCL accepted as symmetric windows (0: plain all-reduce path)
+  long long peer_exchanges = 0;      // exchange steps through peer memory (pdlp_peer.cuh) instead of ncclAllReduce
   double upload_seconds = 0.0;       // host -> device copies, CSR build, communicator set-up (before preprocessing)
 };
 const SolveCounters& LastSolveCounters();

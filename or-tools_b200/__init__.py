@@ -88,6 +88,7 @@ class _CCounters(ctypes.Structure):
         ("collectives", ctypes.c_longlong),
         ("upload_seconds", ctypes.c_double),
         ("symmetric_buffers", ctypes.c_int),
+        ("peer_exchanges", ctypes.c_longlong),
     ]
 
 

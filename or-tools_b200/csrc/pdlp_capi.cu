@@ -370,6 +370,7 @@ pdlp_b200_status pdlp_b200_solve_sharded(const pdlp_b200_problem* problem, const
       counters->collectives = c.collectives;
       counters->upload_seconds = c.upload_seconds;
       counters->symmetric_buffers = c.symmetric_buffers;
+      counters->peer_exchanges = c.peer_exchanges;
     }
     return PDLP_B200_OK;
   });

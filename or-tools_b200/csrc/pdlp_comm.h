@@ -9,12 +9,15 @@
 #include <dlfcn.h>
 #include <nccl.h>  // types and enumerators only; no link dependency
 
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
 #include <stdexcept>
 #include <string>
 #include <vector>
+
+#include "pdlp_peer_view.h"
 
 namespace pdlp_b200 {
 
@@ -76,9 +79,21 @@ class NcclApi {
 // exchange buffer with them: both are kept per process, keyed by (unique id, rank, world), and
 // reused by every later solve that presents the same id.
 struct ExchangeBuffer { void* ptr = nullptr; size_t bytes = 0; ncclWindow_t window = nullptr; bool nccl_memory = false, registered = false; };
+// The peer-memory exchange region of this rank and its peers' regions as mapped here (pdlp_peer.cuh).
+// Epochs count the exchanges enqueued so far; they continue across solves on the same communicator
+// because the flags in the regions do.
+struct PeerRegion {
+  bool ok = false;
+  int rank = 0, world = 1;
+  long long cap_rows = 0;
+  void* own = nullptr;
+  void* mapped[kMaxPeers] = {};  // mapped[rank] == own
+  unsigned long long row_epoch = 0, sum_epoch = 0;
+};
 struct CachedComm {
   ncclComm_t comm = nullptr;
   std::vector<ExchangeBuffer> buffers;  // by slot
+  PeerRegion peer;
   int users = 0;                        // live solvers / problem handles on this communicator
 };
 class CommCache {
@@ -104,10 +119,25 @@ class CommCache {
     else if (e.ptr != nullptr) cudaFree(e.ptr);
     e = ExchangeBuffer();
   }
+  // Unmaps the peers' regions, waits until every rank has done so (an exporter must not free memory a
+  // peer still has mapped), then frees this rank's region.  Collective.
+  static void FreePeerRegion(ncclComm_t comm, PeerRegion& p) {
+    if (p.own == nullptr) { p = PeerRegion(); return; }
+    cudaDeviceSynchronize();
+    for (int r = 0; r < p.world; ++r) {
+      if (r != p.rank && p.mapped[r] != nullptr) cudaIpcCloseMemHandle(p.mapped[r]);
+    }
+    // The first 8 bytes of the own region double as the barrier's buffer (its contents no longer matter).
+    NcclApi::Get().AllReduce(p.own, p.own, 1, ncclFloat64, ncclSum, comm, nullptr);
+    cudaDeviceSynchronize();
+    cudaFree(p.own);
+    p = PeerRegion();
+  }
   int Release() {  // destroys every cached communicator and its buffers; no solve may be running
     std::lock_guard<std::mutex> lock(mu_);
     const int count = static_cast<int>(comms_.size());
     for (auto& kv : comms_) {
+      FreePeerRegion(kv.second.comm, kv.second.peer);
       for (ExchangeBuffer& e : kv.second.buffers) FreeBuffer(kv.second.comm, e);
       NcclApi::Get().CommDestroy(kv.second.comm);
     }
@@ -183,6 +213,81 @@ class Comm {
   }
   int symmetric_buffers() const { return symmetric_buffers_; }
 
+  // Sets up (or reuses) the peer-memory exchange for `cap_rows` shared rows: one region per rank, mapped
+  // into every peer with CUDA IPC (the handles travel through one NCCL all-reduce).  Collective: every
+  // rank calls it with the same cap_rows.  Returns false - on EVERY rank - when any rank cannot do it
+  // (more than kMaxPeers ranks, IPC or peer access unavailable, PDLP_B200_PEER_EXCHANGE=0): the caller
+  // then keeps the NCCL all-reduce path.
+  bool SetupPeerExchange(long long cap_rows, cudaStream_t stream) {
+    if (world_ <= 1) return false;
+    PeerRegion& p = cached_->peer;
+    const char* env = std::getenv("PDLP_B200_PEER_EXCHANGE");
+    bool failed = world_ > kMaxPeers || (env != nullptr && env[0] == '0');
+    const bool reuse = !failed && p.ok && p.cap_rows >= cap_rows;
+    if (!failed && !reuse) {
+      if (p.own != nullptr && cached_->users > 1) throw std::runtime_error("pdlp_b200: a larger sharded problem cannot be created while another one is alive on the same communicator");
+      CommCache::FreePeerRegion(comm_, p);
+      p.rank = rank_;
+      p.world = world_;
+      p.cap_rows = cap_rows;
+      const size_t bytes = PeerView::Bytes(world_, cap_rows);
+      cudaIpcMemHandle_t handle;
+      unsigned char* table = nullptr;  // world x sizeof(handle) bytes: zero except this rank's handle
+      const size_t hb = sizeof(cudaIpcMemHandle_t);
+      failed = cudaMalloc(&p.own, bytes) != cudaSuccess;
+      if (failed) { p.own = nullptr; cudaGetLastError(); }
+      if (!failed) failed = cudaMemset(p.own, 0, bytes) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess;
+      if (!failed) failed = cudaIpcGetMemHandle(&handle, p.own) != cudaSuccess;
+      if (cudaMalloc(&table, hb * world_) != cudaSuccess) throw std::runtime_error("CUDA error: allocating the IPC handle table");
+      cudaMemset(table, 0, hb * world_);
+      if (!failed) cudaMemcpy(table + hb * rank_, &handle, hb, cudaMemcpyHostToDevice);
+      // Bytes summed as uint8: one non-zero contribution per position, so the sum is that rank's byte.
+      Check(NcclApi::Get().AllReduce(table, table, hb * world_, ncclUint8, ncclSum, comm_, stream), "ncclAllReduce (IPC handles)");
+      std::vector<unsigned char> host(hb * world_);
+      cudaMemcpyAsync(host.data(), table, hb * world_, cudaMemcpyDeviceToHost, stream);
+      cudaStreamSynchronize(stream);
+      cudaFree(table);
+      for (int r = 0; r < world_ && !failed; ++r) {
+        if (r == rank_) { p.mapped[r] = p.own; continue; }
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, host.data() + hb * r, hb);
+        bool zero = true;
+        for (size_t i = 0; i < hb; ++i) zero = zero && host[hb * r + i] == 0;
+        if (zero || cudaIpcOpenMemHandle(&p.mapped[r], h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+          p.mapped[r] = nullptr;
+          cudaGetLastError();
+          failed = true;
+        }
+      }
+    }
+    // Agree: one failure anywhere switches every rank to the NCCL path.
+    double flag = failed ? 1.0 : 0.0;
+    double* d = ExchangeBufferFor(1, 16 * sizeof(double));
+    cudaMemcpyAsync(d, &flag, sizeof(double), cudaMemcpyHostToDevice, stream);
+    AllReduce(d, 1, true, stream);
+    cudaMemcpyAsync(&flag, d, sizeof(double), cudaMemcpyDeviceToHost, stream);
+    cudaStreamSynchronize(stream);
+    if (flag != 0.0) {
+      CommCache::FreePeerRegion(comm_, p);
+      return false;
+    }
+    p.ok = true;
+    return true;
+  }
+  bool peer_exchange() const { return cached_ != nullptr && cached_->peer.ok; }
+  PeerView peer_view() const {
+    PeerView v;
+    const PeerRegion& p = cached_->peer;
+    v.rank = rank_;
+    v.world = world_;
+    v.cap_rows = p.cap_rows;
+    for (int r = 0; r < world_ && r < kMaxPeers; ++r) v.base[r] = static_cast<char*>(p.mapped[r]);
+    return v;
+  }
+  unsigned long long NextRowEpoch() { ++exchanges_; return ++cached_->peer.row_epoch; }
+  unsigned long long NextSumEpoch() { ++exchanges_; return ++cached_->peer.sum_epoch; }
+  long long peer_exchanges() const { return exchanges_; }
+
   void Destroy() {  // the communicator and its exchange buffers stay in the cache
     symmetric_buffers_ = 0;
     if (cached_ != nullptr) --cached_->users;
@@ -212,6 +317,7 @@ class Comm {
   int rank_ = 0, world_ = 1;
   ncclComm_t comm_ = nullptr;
   long long collectives_ = 0;
+  long long exchanges_ = 0;  // peer-memory exchanges enqueued (each replaces one all-reduce)
 };
 
 }  // namespace pdlp_b200

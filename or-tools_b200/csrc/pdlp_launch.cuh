@@ -39,9 +39,49 @@ inline int EnqueueMap(Workspace& ws, const Op& op, int64_t count, int region = 0
   ++ws.launches;
   return grid;
 }
+// A pass over the column-sharded CSR block with the shared rows' sums exchanged through peer memory
+// (pdlp_peer.cuh): push + signal, then the private rows (which hide the transfer), then wait + finish.
+template <class Op>
+inline int EnqueueRowsPeer(Workspace& ws, const Op& op, const SparseRows& s, int region) {
+  const PeerView view = ws.comm->peer_view();
+  double* partials = ws.partials[region].get();
+  const bool cut = s.cut_block >= 0;
+  const int shared_blocks = cut ? s.cut_block : s.num_blocks;
+  const int private_blocks = cut ? s.num_blocks - s.cut_block : 0;
+  const int64_t shared_rows = cut ? s.cut_row : s.rows;
+  unsigned long long epoch = 0;
+  if (shared_rows > 0) {  // the same on every rank
+    epoch = ws.comm->NextRowEpoch();
+    if (shared_blocks > 0) {
+      const RowBlocks v = s.ViewOfBlocks(0, shared_blocks);
+      const int g = std::min(shared_blocks, RowStreamGrid<PeerPartialRowOp<Op>>(s));
+      rowstream_kernel<PeerPartialRowOp<Op>><<<g, kBlock, 0, ws.stream>>>(PeerPartialRowOp<Op>{op, view, static_cast<int>(epoch & 1)}, v, partials);
+      ++ws.launches;
+    }
+    peer_signal_rows_kernel<<<1, 32, 0, ws.stream>>>(view, epoch);
+    ++ws.launches;
+  }
+  int grid = 0;
+  if (private_blocks > 0) {
+    const RowBlocks v = s.ViewOfBlocks(s.cut_block, private_blocks);
+    grid = std::min(private_blocks, RowStreamGrid<Op>(s));
+    rowstream_kernel<Op><<<grid, kBlock, 0, ws.stream>>>(op, v, partials);
+    ++ws.launches;
+  }
+  if (shared_rows > 0) {
+    const int g = GridFor(shared_rows);
+    map_reduce_kernel<PeerFinishRowOp<Op>><<<g, kBlock, 0, ws.stream>>>(PeerFinishRowOp<Op>{op, view, epoch, RowCombineIsMax(op) ? 1 : 0, nullptr}, shared_rows,
+                                                                      partials + static_cast<size_t>(grid) * Op::kNumSlots);
+    ++ws.launches;
+    grid += g;
+  }
+  return grid > 0 ? grid : 1;
+}
+
 template <class Op>
 inline int EnqueueRows(Workspace& ws, const Op& op, const SparseRows& s, int region = 0) {
   if (s.partial_sums && IsSharded(ws)) {
+    if (ws.peer) return EnqueueRowsPeer(ws, op, s, region);
     double* sums = ws.exchange_rows;
     double* partials = ws.partials[region].get();
     if (s.cut_block >= 0) {

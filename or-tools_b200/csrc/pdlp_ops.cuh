@@ -47,6 +47,7 @@ struct Workspace {
   Comm* comm = nullptr;      // null or world 1: single GPU.  Otherwise this rank owns a column block of K
   double* exchange_rows = nullptr;  // sharded: the buffer the row sums are written to and all-reduced in (Comm::AllocateExchangeBuffer)
   double* exchange_sums = nullptr;  // sharded: 16 doubles for the step-test sums
+  bool peer = false;         // sharded: row sums and step-test sums travel through peer memory (pdlp_peer.cuh) instead of ncclAllReduce
   DVec combine_tmp;          // kMaxSlots: max-reduced copy of mixed sum/max totals
   // Sharded solves: rows [0, shared_rows) of this rank's dual side are shared with other ranks
   // (their row sums are all-reduced, their values replicated), the rest touch this rank's columns

@@ -1,0 +1,147 @@
+// Peer-memory exchange of the column-sharded solve: the replacement of the two
+// ncclAllReduce calls inside a trial step.  Device side; the host side (allocation, CUDA IPC handles,
+// epochs) is PeerExchange in pdlp_comm.h.
+//
+// Every rank owns one region in its own HBM that all its peers have mapped (one process per GPU, CUDA
+// IPC).  A sender PUSHES: its row-stream kernel stores each partial row sum into slot [its rank] of every
+// rank's region (posted NVLink stores, no round trip), then a one-warp kernel publishes "epoch e is
+// complete" into every rank's flag [its rank].  A receiver works on LOCAL memory only: it waits until its
+// N flags have reached the epoch, then adds its N slots in rank order - the same order on every rank, so
+// the replicated dual entries of the shared constraints stay bit-identical across ranks.  No collective
+// kernel is launched, nothing waits for another GPU's kernel boundary, and the private rows' row-stream
+// launch sits between the push and the wait, so the transfer hides behind it.
+//
+// Slots are double-buffered by epoch parity.  Signal and wait are unconditional (a trial step that the
+// device-side loop control has switched off still signals and waits), so two ranks are never more than
+// one epoch apart and a writer of epoch e + 1 cannot touch the half a slow reader of epoch e is using.
+#ifndef PDLP_B200_PEER_CUH_
+#define PDLP_B200_PEER_CUH_
+
+#include "pdlp_peer_view.h"
+
+namespace pdlp_b200 {
+
+#ifdef PDLP_EMULATE
+inline void PeerFenceSystem() {}
+inline unsigned long long PeerLoadFlag(const unsigned long long* p) { return *reinterpret_cast<const volatile unsigned long long*>(p); }
+inline void PeerStoreFlag(unsigned long long* p, unsigned long long v) { *reinterpret_cast<volatile unsigned long long*>(p) = v; }
+inline double PeerLoadSlot(const double* p) { return *p; }
+#else
+__device__ __forceinline__ void PeerFenceSystem() { __threadfence_system(); }
+__device__ __forceinline__ unsigned long long PeerLoadFlag(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void PeerStoreFlag(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// Slots are written by other GPUs: read them from L2, never from a stale L1 line.
+__device__ __forceinline__ double PeerLoadSlot(const double* p) { return __ldcg(p); }
+#endif
+
+// Blocks the calling thread until every rank's flag in MY region has reached `epoch`.
+__device__ __forceinline__ void PeerWait(const unsigned long long* my_flags, int world, unsigned long long epoch) {
+  for (int r = 0; r < world; ++r) {
+    while (PeerLoadFlag(my_flags + r) < epoch) {
+#if !defined(PDLP_EMULATE)
+      __nanosleep(64);
+#endif
+    }
+  }
+}
+
+// Publishes "everything this rank stored for row epoch `epoch` is complete" to every rank.  Launched
+// behind the pushing kernel on the same stream (its stores are complete at the kernel boundary; the fence
+// orders them before the flag for observers on other GPUs).
+static __global__ void peer_signal_rows_kernel(PeerView view, unsigned long long epoch) {
+  PeerFenceSystem();
+  if (threadIdx.x < static_cast<unsigned>(view.world)) PeerStoreFlag(view.RowFlags(threadIdx.x) + view.rank, epoch);
+}
+
+// Scalar exchange, sender: `count` (<= kPeerSumsPerRank) doubles of this rank to every rank, then the flag.
+// One thread; called by the kernel that produced the values.
+__device__ __forceinline__ void PeerPushSums(const PeerView& view, unsigned long long epoch, const double* values, int count) {
+  const int parity = static_cast<int>(epoch & 1);
+  for (int r = 0; r < view.world; ++r) {
+    double* slot = view.SumSlot(r, parity, view.rank);
+    for (int i = 0; i < count; ++i) slot[i] = values[i];
+  }
+  PeerFenceSystem();
+  for (int r = 0; r < view.world; ++r) PeerStoreFlag(view.SumFlags(r) + view.rank, epoch);
+}
+// Scalar exchange, receiver: waits, then out[i] = sum (or max) over ranks, in rank order.  One thread.
+__device__ __forceinline__ void PeerCombineSums(const PeerView& view, unsigned long long epoch, double* out, int count, bool max) {
+  PeerWait(view.SumFlags(view.rank), view.world, epoch);
+  const int parity = static_cast<int>(epoch & 1);
+  for (int i = 0; i < count; ++i) {
+    double a = PeerLoadSlot(view.SumSlot(view.rank, parity, 0) + i);
+    for (int r = 1; r < view.world; ++r) {
+      const double b = PeerLoadSlot(view.SumSlot(view.rank, parity, r) + i);
+      a = max ? fmax(a, b) : a + b;
+    }
+    out[i] = a;
+  }
+}
+static __global__ void peer_combine_sums_kernel(PeerView view, unsigned long long epoch, double* out, int count, int max) {
+  if (threadIdx.x == 0) PeerCombineSums(view, epoch, out, count, max != 0);
+}
+
+// Phase 1 of a sharded CSR pass in peer mode: this rank's part of every shared row sum, pushed into slot
+// [rank] of every rank's region.  Same interface as PartialRowOp (pdlp_skeletons.cuh).
+template <class Op>
+struct PeerPartialRowOp {
+  static constexpr int kNumSlots = 0;
+  __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
+  Op op;
+  PeerView view;
+  int parity;
+  __device__ bool Begin() { return op.Begin(); }
+  __device__ double Load(int64_t k) const { return op.Load(k); }
+  template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
+  __device__ const int* IndexAddress(int64_t k) const { return op.IndexAddress(k); }
+  template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
+  __device__ const double* ValueAddress(int64_t k) const { return op.ValueAddress(k); }
+  template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
+  __device__ double Gather(int index) const { return op.Gather(index); }
+  template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
+  __device__ double Product(double value, double gathered) const { return op.Product(value, gathered); }
+  __device__ double RowInit() const { return op.RowInit(); }
+  __device__ double RowAdd(double acc, double staged, int row) const { return op.RowAdd(acc, staged, row); }
+  __device__ double RowMerge(double a, double b) const { return op.RowMerge(a, b); }
+  __device__ void RowFinish(int row, double acc, Slots<0>&) const {
+#pragma unroll 1
+    for (int r = 0; r < view.world; ++r) view.RowSlot(r, parity, view.rank)[row] = acc;
+  }
+};
+
+// Phase 2 in peer mode: wait for every rank's push, add the N local slots in rank order (or take their
+// maximum), run the op's epilogue.  A map op over the shared rows.  The wait runs even when the op is
+// switched off (Begin() false), so that ranks stay within one epoch of each other.
+template <class Op>
+struct PeerFinishRowOp {
+  static constexpr int kNumSlots = Op::kNumSlots;
+  __host__ __device__ static constexpr int SlotKindOf(int s) { return Op::SlotKindOf(s); }
+  Op op;
+  PeerView view;
+  unsigned long long epoch;
+  int combine_max;
+  const double* slots;  // resolved by Begin(): my region, this epoch's half, source 0
+  __device__ bool Begin() {
+    PeerWait(view.RowFlags(view.rank), view.world, epoch);
+    slots = view.RowSlot(view.rank, static_cast<int>(epoch & 1), 0);
+    return op.Begin();
+  }
+  __device__ void Apply(int64_t i, Slots<Op::kNumSlots>& acc) const {
+    double a = PeerLoadSlot(slots + i);
+    for (int r = 1; r < view.world; ++r) {
+      const double b = PeerLoadSlot(slots + static_cast<size_t>(r) * static_cast<size_t>(view.cap_rows) + i);
+      a = combine_max ? fmax(a, b) : a + b;
+    }
+    const int row = static_cast<int>(i);
+    OpRowFinish(op, row, a, OpRowPrefetch(op, row), acc);
+  }
+};
+
+}  // namespace pdlp_b200
+#endif  // PDLP_B200_PEER_CUH_

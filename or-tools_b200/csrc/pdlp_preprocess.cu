@@ -73,6 +73,12 @@ PreprocessSolver::PreprocessSolver(const QpView& qp, const PrimalDualHybridGradi
     AgreeOnMax(&most_rows, 1);
     ws_.exchange_rows = comm_.ExchangeBufferFor(0, static_cast<size_t>(most_rows) * sizeof(double));
     ws_.exchange_sums = comm_.ExchangeBufferFor(1, 16 * sizeof(double));
+    // The shared constraints are the same ones on every rank (include/pdlp_b200.h); the peer-memory slots
+    // are sized by their number.  A disagreement would corrupt the exchange, so it is checked.
+    double agreed[2] = {static_cast<double>(ws_.shared_rows), -static_cast<double>(ws_.shared_rows)};
+    AgreeOnMax(agreed, 2);
+    if (agreed[0] != -agreed[1]) throw std::invalid_argument("pdlp_b200: num_shared_constraints differs between ranks");
+    ws_.peer = comm_.SetupPeerExchange(ws_.shared_rows, ws_.stream);
   }
   problem_.n = qp.n;
   problem_.m = qp.m;
@@ -318,8 +324,9 @@ SolverResult PreprocessSolver::PreprocessAndSolve(const PrimalDualHybridGradient
   SolverResult result = ConstructOriginalSolverResult(params, outcome.x, outcome.y, std::move(outcome.log));
   // Counters for benchmarks.
   g_last_counters.kernel_launches = ws_.launches;
-  g_last_counters.collectives = comm_.collectives();
+  g_last_counters.collectives = comm_.collectives() + comm_.peer_exchanges();  // exchange steps: NCCL all-reduces + peer-memory exchanges
   g_last_counters.symmetric_buffers = comm_.symmetric_buffers();
+  g_last_counters.peer_exchanges = comm_.peer_exchanges();
   g_last_counters.trial_steps = solver.TrialSteps();
   g_last_counters.device_loop_seconds = solver.DeviceLoopSeconds();
   g_last_counters.setup_seconds = result.solve_log.preprocessing_time_sec;

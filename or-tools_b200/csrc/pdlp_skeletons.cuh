@@ -425,6 +425,10 @@ struct FinishRowOp {
   }
 };
 
+}  // namespace pdlp_b200
+#include "pdlp_peer.cuh"  // the same two phases over peer memory instead of an all-reduce
+namespace pdlp_b200 {
+
 // ---- finalize: partials[num_blocks][NS] -> totals[NS], fixed order, one CTA ----
 template <class Op>
 __global__ void __launch_bounds__(kBlock) finalize_kernel(const double* partials, int num_blocks, double* totals) {

@@ -29,6 +29,15 @@ struct StepSums { const double* p1; int g1; const double* p2; int g2; const doub
 StepSums CombineStepPartials(Workspace& ws, int g1, int g2, int g3) {
   if (!IsSharded(ws)) return {ws.partials[0].get(), g1, ws.partials[1].get(), g2, ws.partials[2].get(), g3};
   double* t = ws.exchange_sums;
+  if (ws.peer) {
+    // Every rank pushes its four sums to all ranks; each then adds the N contributions in rank order.
+    const PeerView view = ws.comm->peer_view();
+    const unsigned long long epoch = ws.comm->NextSumEpoch();
+    fold_and_push_step_partials_kernel<<<1, kBlock, 0, ws.stream>>>(ws.partials[0].get(), g1, ws.partials[1].get(), g2, ws.partials[2].get(), g3, view, epoch);
+    peer_combine_sums_kernel<<<1, 32, 0, ws.stream>>>(view, epoch, t, 4, 0);
+    ws.launches += 2;
+    return {t, 1, t + 1, 1, t + 2, 1};
+  }
   fold_step_partials_kernel<<<1, kBlock, 0, ws.stream>>>(ws.partials[0].get(), g1, ws.partials[1].get(), g2, ws.partials[2].get(), g3, t);
   ++ws.launches;
   ws.comm->AllReduce(t, 4, false, ws.stream);

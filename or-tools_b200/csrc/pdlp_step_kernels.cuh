@@ -374,6 +374,18 @@ __global__ void __launch_bounds__(kBlock) fold_step_partials_kernel(const double
   if (threadIdx.x == 0) { out[0] = a; out[1] = b; out[2] = c; out[3] = d; }
 }
 
+// The same fold in peer mode: the four sums go straight into every rank's scalar slot (pdlp_peer.cuh).
+__global__ void __launch_bounds__(kBlock) fold_and_push_step_partials_kernel(const double* p1, int g1, const double* p2, int g2, const double* p3, int g3,
+                                                                            PeerView view, unsigned long long epoch) {
+  __shared__ double buf[kBlock];
+  double v[4];
+  v[0] = ReducePartialsSum(p1, g1, 1, 0, buf);
+  v[1] = ReducePartialsSum(p2, g2, 1, 0, buf);
+  v[2] = ReducePartialsSum(p3, g3, 2, 0, buf);
+  v[3] = ReducePartialsSum(p3, g3, 2, 1, buf);
+  if (threadIdx.x == 0) PeerPushSums(view, epoch, v, 4);
+}
+
 }  // namespace
 
 }  // namespace pdlp_b200

@@ -220,3 +220,73 @@ extern "C" int emu_sharded_dual_finish(int m_local, const int* ptr, const int* i
   *dy2 = total;
   return 0;
 }
+
+// ---- the same two phases through peer memory (pdlp_peer.cuh): all emulated ranks live in this process,
+// `regions[r]` is rank r's region (PeerView::Bytes(world, cap_rows) bytes, zeroed by the caller once). ----
+namespace {
+PeerView ViewOf(int rank, int world, long long cap_rows, void* const* regions) {
+  PeerView v;
+  v.rank = rank;
+  v.world = world;
+  v.cap_rows = cap_rows;
+  for (int r = 0; r < world; ++r) v.base[r] = static_cast<char*>(regions[r]);
+  return v;
+}
+}  // namespace
+
+extern "C" long long emu_peer_region_bytes(int world, long long cap_rows) { return static_cast<long long>(PeerView::Bytes(world, cap_rows)); }
+
+// Phase 1 + signal of `rank` for row epoch `epoch`: pushes into every rank's region.
+extern "C" int emu_peer_dual_partial(int m_local, const int* ptr, const int* idx, const double* val, const int* block_start, int num_blocks, int cut_block,
+                                     const double* xbar, double* y0, double* y1, const double* clb, const double* cub, double step_size, double primal_weight,
+                                     int max_grid, int rank, int world, long long cap_rows, void* const* regions, unsigned long long epoch) {
+  cuda_emu::defer_async = false;
+  HostRows csr{ptr, idx, val, block_start, num_blocks, m_local, {}};
+  const RowBlocks all = csr.View();
+  StepState state = FreshState(step_size, primal_weight);
+  const PeerView view = ViewOf(rank, world, cap_rows, regions);
+  if (cut_block > 0) {
+    const DualStepOp op{{}, &state, val, idx, xbar, y0, y1, clb, cub, 0, nullptr};
+    std::vector<double> partials(kMaxGrid, 0.0);
+    LaunchRows(PeerPartialRowOp<DualStepOp>{op, view, static_cast<int>(epoch & 1)}, ViewOfBlocks(all, 0, cut_block), max_grid, partials.data());
+  }
+  cuda_emu::Launch(1, 32, [=]() { peer_signal_rows_kernel(view, epoch); });
+  return 0;
+}
+
+// Phase 2 of `rank`: private rows in the row-stream kernel, shared rows by PeerFinishRowOp (wait + rank-order sum).
+extern "C" int emu_peer_dual_finish(int m_local, const int* ptr, const int* idx, const double* val, const int* block_start, int num_blocks, int cut_block,
+                                    int cut_row, const double* xbar, double* y0, double* y1, const double* clb, const double* cub, double step_size,
+                                    double primal_weight, int skip_below, int max_grid, int rank, int world, long long cap_rows, void* const* regions,
+                                    unsigned long long epoch, double* dy2) {
+  cuda_emu::defer_async = false;
+  HostRows csr{ptr, idx, val, block_start, num_blocks, m_local, {}};
+  const RowBlocks all = csr.View();
+  StepState state = FreshState(step_size, primal_weight);
+  const DualStepOp op{{}, &state, val, idx, xbar, y0, y1, clb, cub, skip_below, nullptr};
+  const PeerView view = ViewOf(rank, world, cap_rows, regions);
+  std::vector<double> partials(2 * kMaxGrid, 0.0);
+  int grid = 0;
+  if (num_blocks - cut_block > 0) grid = LaunchRows(op, ViewOfBlocks(all, cut_block, num_blocks - cut_block), max_grid, partials.data());
+  if (cut_row > 0) grid += LaunchMap(PeerFinishRowOp<DualStepOp>{op, view, epoch, 0, nullptr}, cut_row, partials.data() + grid);
+  double total = 0.0;
+  for (int b = 0; b < grid; ++b) total += partials[b];
+  *dy2 = total;
+  return 0;
+}
+
+// The scalar exchange: every rank pushes `count` values for sum epoch `epoch`, then every rank combines.
+// values: world x count in, out: world x count (each rank's combined copy; must be identical rows).
+extern "C" int emu_peer_sums(int world, long long cap_rows, void* const* regions, unsigned long long epoch, int count, int max, const double* values, double* out) {
+  for (int r = 0; r < world; ++r) {
+    const PeerView view = ViewOf(r, world, cap_rows, regions);
+    const double* mine = values + static_cast<size_t>(r) * count;
+    cuda_emu::Launch(1, 1, [=]() { PeerPushSums(view, epoch, mine, count); });
+  }
+  for (int r = 0; r < world; ++r) {
+    const PeerView view = ViewOf(r, world, cap_rows, regions);
+    double* dst = out + static_cast<size_t>(r) * count;
+    cuda_emu::Launch(1, 32, [=]() { peer_combine_sums_kernel(view, epoch, dst, count, max); });
+  }
+  return 0;
+}

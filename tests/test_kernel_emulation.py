@@ -133,7 +133,7 @@ def test_dense_skeleton_and_its_two_stage_reduction(libs, count, grid):
 def _build_step():
     out = os.path.join(BUILD, "step_emu.so")
     sources = [os.path.join(EMU, "step_emu.cc"), os.path.join(EMU, "cuda_emu.h"), os.path.join(CSRC, "pdlp_skeletons.cuh"),
-               os.path.join(CSRC, "pdlp_step_kernels.cuh"), os.path.join(CSRC, "pdlp_step_state.h")]
+               os.path.join(CSRC, "pdlp_step_kernels.cuh"), os.path.join(CSRC, "pdlp_step_state.h"), os.path.join(CSRC, "pdlp_peer.cuh"), os.path.join(CSRC, "pdlp_peer_view.h")]
     os.makedirs(BUILD, exist_ok=True)
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(s) for s in sources):
         subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-Wno-attributes",
@@ -398,6 +398,84 @@ def test_sharded_dual_step_over_emulated_ranks_matches_one_rank(step_libs, world
     got = sharing.gather([k["y1"] for k in ranks])
     np.testing.assert_allclose(got, want, rtol=1e-11, atol=1e-12)
     np.testing.assert_allclose(total, np.sum((want - y) ** 2), rtol=1e-11)
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_peer_memory_exchange_of_the_sharded_dual_step(step_libs, world):
+    """The column-sharded dual step with the shared rows' sums exchanged through peer memory
+    (pdlp_peer.cuh: PeerPartialRowOp pushes into every rank's region, peer_signal_rows_kernel publishes the
+    epoch, PeerFinishRowOp waits and adds the N slots in rank order), all ranks emulated in one process.
+    Three consecutive epochs with different operands: the parity double buffer must never serve an older
+    epoch's sums, the replicated shared part must be bit-identical on every rank, and the result must equal
+    the unsharded step."""
+    import scipy.sparse as sp
+    rng = np.random.default_rng(40 + world)
+    m, n = 700, 1500
+    K = sp.random(m, n, density=0.01, random_state=7, data_rvs=lambda k: rng.standard_normal(k)).tocsc()
+    K = sp.csc_matrix(K)
+    # a band of rows touched by one column block only (private) plus rows touched by all (shared)
+    starts = pdlp_b200.column_partition(K.indptr, world)
+    sharing = pdlp_b200.sharding.RowSharing.from_matrix(K, starts)
+    S = int(sharing.shared.size)
+    assert S > 0
+    y = rng.standard_normal(m)
+    mid = rng.standard_normal(m)
+    clb = np.where(rng.random(m) < 0.3, -np.inf, mid - 0.5)
+    cub = np.where(rng.random(m) < 0.3, np.inf, mid + 0.5)
+    y = np.where(np.isinf(clb), np.minimum(y, 0.0), y)
+    y = np.where(np.isinf(cub), np.maximum(y, 0.0), y)
+    step, w = 0.4, 1.7
+    sigma = step * w
+    lib = step_libs[0]
+    lib.emu_peer_region_bytes.restype = ctypes.c_longlong
+    p = lambda a: ctypes.c_void_p(a.ctypes.data)
+    i32 = lambda a: np.ascontiguousarray(a, dtype=np.int32)
+    nbytes = lib.emu_peer_region_bytes(world, ctypes.c_longlong(S))
+    regions = [np.zeros(nbytes // 8 + 1, dtype=np.float64) for _ in range(world)]
+    table = (ctypes.c_void_p * world)(*[r.ctypes.data for r in regions])
+    blocks_of = []
+    for r in range(world):
+        local = sharing.local_rows(r)
+        block = sp.csr_matrix(K[:, starts[r]:starts[r + 1]].tocsr()[local, :])
+        block.sort_indices()
+        ptr = i32(block.indptr)
+        blocks, cut_block, _ = pdlp_b200.work_blocks(ptr, S if 0 < S < local.size else -1)
+        if S >= local.size:
+            cut_block = len(blocks) - 1
+        blocks_of.append(dict(m=local.size, ptr=ptr, idx=i32(block.indices), val=np.ascontiguousarray(block.data), blocks=i32(blocks), cut=int(cut_block),
+                              y0=sharing.scatter(r, y), clb=sharing.scatter(r, clb), cub=sharing.scatter(r, cub)))
+    for epoch in (1, 2, 3):
+        xbar = rng.standard_normal(n) * epoch
+        temp = y - sigma * (K @ xbar)
+        want = np.maximum(np.minimum(0.0, temp + sigma * cub), temp + sigma * clb)
+        ranks = [dict(k, xbar=np.ascontiguousarray(xbar[starts[r]:starts[r + 1]]), y1=np.zeros(k["m"])) for r, k in enumerate(blocks_of)]
+        for r, k in enumerate(ranks):
+            assert lib.emu_peer_dual_partial(k["m"], p(k["ptr"]), p(k["idx"]), p(k["val"]), p(k["blocks"]), len(k["blocks"]) - 1, k["cut"], p(k["xbar"]), p(k["y0"]),
+                                             p(k["y1"]), p(k["clb"]), p(k["cub"]), ctypes.c_double(step), ctypes.c_double(w), 3, r, world, ctypes.c_longlong(S), table,
+                                             ctypes.c_ulonglong(epoch)) == 0
+        total = 0.0
+        for r, k in enumerate(ranks):
+            dy2 = ctypes.c_double(0.0)
+            assert lib.emu_peer_dual_finish(k["m"], p(k["ptr"]), p(k["idx"]), p(k["val"]), p(k["blocks"]), len(k["blocks"]) - 1, k["cut"], S, p(k["xbar"]), p(k["y0"]),
+                                            p(k["y1"]), p(k["clb"]), p(k["cub"]), ctypes.c_double(step), ctypes.c_double(w), 0 if r == 0 else S, 3, r, world,
+                                            ctypes.c_longlong(S), table, ctypes.c_ulonglong(epoch), ctypes.byref(dy2)) == 0
+            total += dy2.value
+            if r > 0:
+                np.testing.assert_array_equal(k["y1"][:S], ranks[0]["y1"][:S])
+        got = sharing.gather([k["y1"] for k in ranks])
+        np.testing.assert_allclose(got, want, rtol=1e-11, atol=1e-12)
+        np.testing.assert_allclose(total, np.sum((want - y) ** 2), rtol=1e-11)
+    # The scalar exchange: sums and maxima in rank order, identical on every rank, over three epochs.
+    for epoch in (1, 2, 3):
+        values = rng.standard_normal((world, 4))
+        out = np.zeros((world, 4))
+        for mx in (0, 1):
+            assert lib.emu_peer_sums(world, ctypes.c_longlong(S), table, ctypes.c_ulonglong(2 * epoch - 1 + mx), 4, mx, p(values), p(out)) == 0
+            ref = values[0].copy()
+            for r in range(1, world):
+                ref = np.maximum(ref, values[r]) if mx else ref + values[r]
+            for r in range(world):
+                np.testing.assert_array_equal(out[r], ref)
 
 
 # ---- termination statistics (the two fused KKT passes) against the oracle ----
