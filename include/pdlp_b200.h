@@ -166,6 +166,14 @@ pdlp_b200_status pdlp_b200_check_termination(const uint8_t* params, size_t param
                                              const double* bound_norms /*4*/, int which, int force_numerical_termination,
                                              const volatile int* interrupt, int* reason, int* point_type, double* relative_residuals);
 
+/* Host only: the iteration log table of verbosity_level >= 2 (LogIterationStatsHeader / LogIterationStats,
+ * primal_dual_hybrid_gradient.cc:193-287) as text, for one serialized IterationStats: what the solve writes
+ * to stderr at every termination check.  params supplies verbosity_level, use_feasibility_polishing and the
+ * termination criteria; iteration_type / preferred_candidate are IterationType / PointType numbers;
+ * bound_norms as in pdlp_b200_callback.  *header and *line are malloc'ed (pdlp_b200_free). */
+pdlp_b200_status pdlp_b200_format_iteration_stats(const uint8_t* params, size_t params_len, const uint8_t* stats, size_t stats_len, const double* bound_norms /*4*/,
+                                                  int iteration_type, int preferred_candidate, char** header, char** line);
+
 /* Serialized PrimalDualHybridGradientParams holding every schema default. */
 pdlp_b200_status pdlp_b200_default_params(uint8_t** params, size_t* params_len);
 

@@ -9,6 +9,7 @@
 
 #include "pdlp_b200.h"
 #include "pdlp_driver.h"
+#include "pdlp_logging.h"
 
 namespace pdlp_b200 {
 
@@ -417,6 +418,24 @@ pdlp_b200_status pdlp_b200_check_termination(const uint8_t* params_bytes, size_t
         relative_residuals[4] = rel.relative_optimality_gap;
       }
     }
+    return PDLP_B200_OK;
+  });
+}
+
+pdlp_b200_status pdlp_b200_format_iteration_stats(const uint8_t* params, size_t params_len, const uint8_t* stats, size_t stats_len, const double* bound_norms,
+                                                  int iteration_type, int preferred_candidate, char** header, char** line) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (stats == nullptr || bound_norms == nullptr || header == nullptr || line == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "bad argument");
+    PrimalDualHybridGradientParams p;
+    if (!ParseParams(params, params_len, &p)) return Fail(PDLP_B200_BAD_ARGUMENT, "params bytes do not parse as PrimalDualHybridGradientParams");
+    IterationStats s;
+    if (!Parse(stats, stats_len, &s)) return Fail(PDLP_B200_BAD_ARGUMENT, "stats bytes do not parse as IterationStats");
+    QuadraticProgramBoundNorms bn;
+    bn.l2_norm_primal_linear_objective = bound_norms[0]; bn.l2_norm_constraint_bounds = bound_norms[1];
+    bn.l_inf_norm_primal_linear_objective = bound_norms[2]; bn.l_inf_norm_constraint_bounds = bound_norms[3];
+    *header = DupString(IterationStatsHeader(p.verbosity_level, p.use_feasibility_polishing));
+    *line = DupString(IterationStatsLine(p.verbosity_level, p.use_feasibility_polishing, static_cast<IterationType>(iteration_type), s, p.termination_criteria.get(), bn,
+                                         preferred_candidate));
     return PDLP_B200_OK;
   });
 }

@@ -9,6 +9,8 @@
 #include <dlfcn.h>
 #include <nccl.h>  // types and enumerators only; no link dependency
 
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -224,6 +226,10 @@ class Comm {
     const char* env = std::getenv("PDLP_B200_PEER_EXCHANGE");
     bool failed = world_ > kMaxPeers || (env != nullptr && env[0] == '0');
     const bool reuse = !failed && p.ok && p.cap_rows >= cap_rows;
+    const bool timing = std::getenv("PDLP_B200_DEBUG_TIMING") != nullptr;
+    auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t0 = now();
+    double t_alloc = t0, t_handles = t0, t_open = t0;
     if (!failed && !reuse) {
       if (p.own != nullptr && cached_->users > 1) throw std::runtime_error("pdlp_b200: a larger sharded problem cannot be created while another one is alive on the same communicator");
       CommCache::FreePeerRegion(comm_, p);
@@ -238,6 +244,7 @@ class Comm {
       if (failed) { p.own = nullptr; cudaGetLastError(); }
       if (!failed) failed = cudaMemset(p.own, 0, bytes) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess;
       if (!failed) failed = cudaIpcGetMemHandle(&handle, p.own) != cudaSuccess;
+      t_alloc = now();
       if (cudaMalloc(&table, hb * world_) != cudaSuccess) throw std::runtime_error("CUDA error: allocating the IPC handle table");
       cudaMemset(table, 0, hb * world_);
       if (!failed) cudaMemcpy(table + hb * rank_, &handle, hb, cudaMemcpyHostToDevice);
@@ -247,6 +254,7 @@ class Comm {
       cudaMemcpyAsync(host.data(), table, hb * world_, cudaMemcpyDeviceToHost, stream);
       cudaStreamSynchronize(stream);
       cudaFree(table);
+      t_handles = now();
       for (int r = 0; r < world_ && !failed; ++r) {
         if (r == rank_) { p.mapped[r] = p.own; continue; }
         cudaIpcMemHandle_t h;
@@ -260,6 +268,7 @@ class Comm {
         }
       }
     }
+    t_open = now();
     // Agree: one failure anywhere switches every rank to the NCCL path.
     double flag = failed ? 1.0 : 0.0;
     double* d = ExchangeBufferFor(1, 16 * sizeof(double));
@@ -272,6 +281,8 @@ class Comm {
       return false;
     }
     p.ok = true;
+    if (timing) std::fprintf(stderr, "[pdlp_b200] rank %d peer set-up%s: region %.1f ms, handle exchange %.1f ms, open %.1f ms, agree %.1f ms\n", rank_, reuse ? " (reused)" : "",
+                             1e3 * (t_alloc - t0), 1e3 * (t_handles - t_alloc), 1e3 * (t_open - t_handles), 1e3 * (now() - t_open));
     return true;
   }
   bool peer_exchange() const { return cached_ != nullptr && cached_->peer.ok; }

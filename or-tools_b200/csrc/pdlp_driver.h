@@ -114,6 +114,11 @@ class PreprocessSolver {
   IterationCallback callback_;
   std::vector<int32_t> seeds_;
   SolutionSink* sink_ = nullptr;
+  // Text logging (pdlp_logging.h): a table header every 15 lines, lines at most every log_interval_seconds; rank 0 only.
+  int log_counter_ = 0;
+  double time_of_last_log_ = -1.0e300;
+ public:
+  bool Logs(const PrimalDualHybridGradientParams& params, int level) const { return params.verbosity_level >= level && comm_.rank() == 0; }
 };
 
 enum class InnerStepOutcome { kSuccessful, kForceNumericalTermination };

@@ -4,7 +4,10 @@
 // Glop presolve (:1107-1202) is host-only and not part of this path.
 #include <random>
 
+#include <chrono>
+
 #include "pdlp_driver.h"
+#include "pdlp_logging.h"
 #include "pdlp_launch.cuh"
 
 namespace pdlp_b200 {
@@ -250,6 +253,10 @@ SolverResult PreprocessSolver::PreprocessAndSolve(const PrimalDualHybridGradient
     y_start.Zero(ws_.stream);
   }
   original_bound_norms_ = BoundNormsFromProblemStats(log.original_problem_stats.get());
+  if (Logs(params, 1)) {  // pdhg.cc:979-986
+    LogInfoWithoutPrefix("Problem stats before rescaling:");
+    for (const std::string& line : QuadraticProgramStatsLines(log.original_problem_stats.get(), log.original_problem_stats->constraint_matrix_num_nonzeros > 0, problem_.is_lp)) LogInfoWithoutPrefix(line);
+  }
   callback_ = std::move(callback);
 
   ProjectToPrimalBounds(ws_, p, x_start.get());
@@ -259,6 +266,10 @@ SolverResult PreprocessSolver::PreprocessAndSolve(const PrimalDualHybridGradient
   DivideInPlace(ws_, x_start.get(), p.col_scale.get(), p.n);
   DivideInPlace(ws_, y_start.get(), p.row_scale.get(), p.m);
   log.preprocessed_problem_stats.mut() = ComputeStats();
+  if (Logs(params, 1)) {  // pdhg.cc:1053-1057
+    LogInfoWithoutPrefix("Problem stats after rescaling:");
+    for (const std::string& line : QuadraticProgramStatsLines(log.preprocessed_problem_stats.get(), log.preprocessed_problem_stats->constraint_matrix_num_nonzeros > 0, problem_.is_lp)) LogInfoWithoutPrefix(line);
+  }
 
   double step_size = 0.0;
   if (params.linesearch_rule == CONSTANT_STEP_SIZE_RULE) {
@@ -412,7 +423,7 @@ void PreprocessSolver::AddRandomProjections(const double* x, const double* y, Po
   }
 }
 
-// pdhg.cc:1434-1518 (text logging not restated).
+// pdhg.cc:1434-1518.
 std::optional<TerminationReasonAndPointType> PreprocessSolver::UpdateIterationStatsAndCheckTermination(
     const PrimalDualHybridGradientParams& params, bool force_numerical_termination, const double* x_cur, const double* y_cur, const double* x_avg,
     const double* y_avg, const double* dx, const double* dy, const double* x_start, const double* y_start, const InterruptFlag* interrupt,
@@ -429,6 +440,21 @@ std::optional<TerminationReasonAndPointType> PreprocessSolver::UpdateIterationSt
   add_point(x_cur, y_cur, POINT_TYPE_CURRENT_ITERATE, true);
   if (x_avg != nullptr && y_avg != nullptr) add_point(x_avg, y_avg, POINT_TYPE_AVERAGE_ITERATE, true);
   if (dx != nullptr && dy != nullptr) add_point(dx, dy, POINT_TYPE_ITERATE_DIFFERENCE, false);
+  if (Logs(params, 2)) {  // :1471-1501
+    constexpr int kLogEvery = 15;
+    const double now = std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+    if (params.log_interval_seconds == 0.0 || now - time_of_last_log_ >= params.log_interval_seconds) {
+      const int level = params.verbosity_level;
+      if (log_counter_ == 0) LogInfoWithoutPrefix(IterationStatsHeader(level, params.use_feasibility_polishing));
+      LogInfoWithoutPrefix(IterationStatsLine(level, params.use_feasibility_polishing, type, stats, params.termination_criteria.get(), original_bound_norms_, POINT_TYPE_AVERAGE_ITERATE));
+      // When there is no average the line above already shows the current iterate: it is not repeated.
+      if (level >= 4 && GetConvergenceInformationFor(stats, POINT_TYPE_AVERAGE_ITERATE).has_value()) {
+        LogInfoWithoutPrefix(IterationStatsLine(level, params.use_feasibility_polishing, type, stats, params.termination_criteria.get(), original_bound_norms_, POINT_TYPE_CURRENT_ITERATE));
+      }
+      time_of_last_log_ = now;
+      if (++log_counter_ >= kLogEvery) log_counter_ = 0;
+    }
+  }
   if (callback_) callback_(IterationCallbackInfo{type, params.termination_criteria.get(), stats, original_bound_norms_});
   if (auto t = CheckIterateTerminationCriteria(params.termination_criteria.get(), stats, original_bound_norms_, force_numerical_termination); t.has_value()) return t;
   return CheckSimpleTerminationCriteria(params.termination_criteria.get(), full_stats, interrupt);
@@ -470,6 +496,17 @@ SolverResult PreprocessSolver::ConstructOriginalSolverResult(const PrimalDualHyb
   if (log.solution_type == POINT_TYPE_FEASIBILITY_POLISHING_SOLUTION) type = IterationType::kFeasibilityPolishingTermination;
   else if (log.solution_type == POINT_TYPE_PRESOLVER_SOLUTION) type = IterationType::kPresolveTermination;
   if (callback_) callback_(IterationCallbackInfo{type, params.termination_criteria.get(), log.solution_stats.get(), original_bound_norms_});
+  if (Logs(params, 1)) {  // :1617-1641
+    LogInfoWithoutPrefix(std::string("Termination reason: ") + TerminationReasonName(log.termination_reason));
+    LogInfoWithoutPrefix(std::string("Solution point type: ") + PointTypeName(log.solution_type));
+    LogInfoWithoutPrefix("Final solution stats:");
+    LogInfoWithoutPrefix(IterationStatsHeader(params.verbosity_level, params.use_feasibility_polishing));
+    LogInfoWithoutPrefix(IterationStatsLine(params.verbosity_level, params.use_feasibility_polishing, type, log.solution_stats.get(), params.termination_criteria.get(), original_bound_norms_, log.solution_type));
+    const auto info = GetConvergenceInformationFor(log.solution_stats.get(), log.solution_type);
+    if (info.has_value() && std::isfinite(info->corrected_dual_objective.get())) {
+      LogInfoWithoutPrefix(Format("Dual objective after infeasibility correction: %g", info->corrected_dual_objective.get()));
+    }
+  }
   result.solve_log = std::move(log);
   return result;
 }

@@ -7,6 +7,7 @@
 #include <algorithm>
 
 #include "pdlp_driver.h"
+#include "pdlp_logging.h"
 
 namespace pdlp_b200 {
 
@@ -226,7 +227,9 @@ double Solver::ComputeNewPrimalWeight() {  // pdhg.cc:1983-2010
     return host_.primal_weight;
   }
   const double smoothing = params_.primal_weight_update_smoothing;
-  return std::exp(smoothing * std::log(dual_distance / primal_distance) + (1.0 - smoothing) * std::log(host_.primal_weight));
+  const double new_primal_weight = std::exp(smoothing * std::log(dual_distance / primal_distance) + (1.0 - smoothing) * std::log(host_.primal_weight));
+  if (pre_->Logs(params_, 4)) LogInfoWithoutPrefix(Format("New computed primal weight is %g at iteration %d", new_primal_weight, iterations_completed_));  // :2004-2008
+  return new_primal_weight;
 }
 
 void Solver::ApplyRestartChoice(int restart_to_apply) {  // pdhg.cc:2042-2094
@@ -235,8 +238,10 @@ void Solver::ApplyRestartChoice(int restart_to_apply) {  // pdhg.cc:2042-2094
     case RESTART_CHOICE_NO_RESTART:
       return;
     case RESTART_CHOICE_WEIGHTED_AVERAGE_RESET:
+      if (pre_->Logs(params_, 4)) LogInfoWithoutPrefix(Format("Restarted to current on iteration %d after %d iterations", iterations_completed_, host_.avg_num_terms));  // :2048-2052
       break;
     case RESTART_CHOICE_RESTART_TO_AVERAGE:
+      if (pre_->Logs(params_, 4)) LogInfoWithoutPrefix(Format("Restarted to average on iteration %d after %d iterations", iterations_completed_, host_.avg_num_terms));  // :2055-2059
       CopyVector(ws_, it_.x[host_.cur].get(), it_.avg_x.get(), problem_.n);
       CopyVector(ws_, it_.y[host_.cur].get(), it_.avg_y.get(), problem_.m);
       RowDot(ws_, problem_.K.by_col, it_.y[host_.cur].get(), it_.kty[host_.cur].get());
@@ -407,7 +412,10 @@ Solver::Outcome Solver::Solve(IterationType type, const InterruptFlag* interrupt
       const double per_iteration = dt / done;
       poll_iterations_ = static_cast<int>(std::min(4096.0, std::max(1.0, 0.02 / per_iteration)));
     }
-    if (host_.force_numerical != 0) force_numerical_termination = true;
+    if (host_.force_numerical != 0) {
+      if (!force_numerical_termination && pre_->Logs(params_, 2)) LogInfoWithoutPrefix(Format("Forced numerical termination at iteration %d", iterations_completed_));  // :2199-2204
+      force_numerical_termination = true;
+    }
   }
 }
 
@@ -443,7 +451,10 @@ std::optional<Solver::Outcome> Solver::TryFeasibilityPolishing(int iteration_lim
   ConvergenceInformation first_convergence_info;
   pre_->ComputeConvergenceAndInfeasibility(params_, average_primal, average_dual, it_.x_start.get(), it_.y_start.get(), POINT_TYPE_AVERAGE_ITERATE,
                                            &first_convergence_info, nullptr, nullptr);
-  if (!ObjectiveGapMet(optimality_criteria, first_convergence_info)) return std::nullopt;
+  if (!ObjectiveGapMet(optimality_criteria, first_convergence_info)) {
+    if (pre_->Logs(params_, 2)) LogInfoWithoutPrefix("Skipping feasibility polishing because the objective gap is too large.");  // :2457-2461
+    return std::nullopt;
+  }
 
   const int64_t n = problem_.n, m = problem_.m;
   auto run_phase = [&](bool primal_phase, DVec* result_holder) -> int {
@@ -488,6 +499,7 @@ std::optional<Solver::Outcome> Solver::TryFeasibilityPolishing(int iteration_lim
     const double* start_x = primal_phase ? average_primal : zeros.get();
     const double* start_y = primal_phase ? zeros.get() : average_dual;
     int reason;
+    if (pre_->Logs(params_, 2)) LogInfoWithoutPrefix(primal_phase ? "Starting primal feasibility polishing" : "Starting dual feasibility polishing");  // :2465, :2491
     {
       Solver sub(phase_params, start_x, start_y, host_.step_size, host_.primal_weight, pre_);
       SolveLog sub_log;
@@ -496,6 +508,9 @@ std::optional<Solver::Outcome> Solver::TryFeasibilityPolishing(int iteration_lim
       timer_.Start();
       host_.total_trials += sub.TrialSteps();
       reason = r.log.termination_reason;
+      if (pre_->Logs(params_, 2)) {  // :2471-2475, :2497-2501
+        LogInfoWithoutPrefix(std::string(primal_phase ? "Primal" : "Dual") + " feasibility polishing termination reason: " + TerminationReasonName(reason));
+      }
       result_holder->Resize(primal_phase ? (n > 0 ? n : 1) : (m > 0 ? m : 1));
       CopyVector(ws_, result_holder->get(), primal_phase ? r.x : r.y, primal_phase ? n : m);
       ws_.Sync();

@@ -194,7 +194,7 @@ def release_communicators():
 
 
 def primal_dual_hybrid_gradient_sharded(qp, params, initial_solution=None, interrupt_solve=None, iteration_stats_callback=None, device=-1,
-                                        group=None, starts=None, sharing=None, gather=True, private_rows=True, num_shared_constraints=None):
+                                        group=None, starts=None, sharing=None, gather=True, private_rows=True, num_shared_constraints=None, unique_id=None):
     """PrimalDualHybridGradient over the ranks of a torch.distributed group, one GPU each.
 
     Whole-problem mode (starts is None): every rank passes the same whole `qp` and, with gather=True,
@@ -224,7 +224,9 @@ def primal_dual_hybrid_gradient_sharded(qp, params, initial_solution=None, inter
         block = qp
         lo = int(starts[rank])
     num_shared = num_shared_constraints if sharing is None else int(sharing.shared.size)
-    shard = ColumnShard(rank, world, int(starts[-1]), lo, broadcast_unique_id(group), num_shared)
+    # unique_id: the id of an earlier sharded call of this process group; its communicator (and its peer-memory
+    # mappings) are cached per process and reused, so only the first call pays for their creation.
+    shard = ColumnShard(rank, world, int(starts[-1]), lo, unique_id if unique_id is not None else broadcast_unique_id(group), num_shared)
     result = primal_dual_hybrid_gradient(block, params, initial_solution, interrupt_solve, iteration_stats_callback, device, shard=shard)
     if gather and result.primal_solution.size:
         parts = [None] * world
