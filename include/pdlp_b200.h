@@ -230,6 +230,11 @@ pdlp_b200_status pdlp_b200_reduced_costs(pdlp_b200_device_problem* h, const uint
 pdlp_b200_status pdlp_b200_localized_bounds(pdlp_b200_device_problem* h, const double* x, const double* y, double primal_weight, double radius,
                                             int use_diagonal_qp_trust_region_solver, double diagonal_qp_trust_region_solver_tolerance, double* out);
 
+/* ComputeLocalizedLagrangianBounds with PrimalDualNorm::kMaxNorm (trust_region.cc:797-884, dispatcher :1003-1007):
+ * the primal and the dual trust-region problem solved separately with radii sqrt(2) r / sqrt(w) and
+ * sqrt(2) r sqrt(w).  out as above.  (PDHG itself only asks for the Euclidean norm.) */
+pdlp_b200_status pdlp_b200_localized_bounds_max_norm(pdlp_b200_device_problem* h, const double* x, const double* y, double primal_weight, double radius, double* out);
+
 /* `steps` trial steps of the adaptive rule from (x, y) with the given step size and
  * primal weight, nothing else (no restarts, no checks): the timed unit of the
  * benchmark.  Outputs the iterate after the last accepted step and the step state:

@@ -333,9 +333,13 @@ class DeviceProblem:
         _check(_lib.pdlp_b200_reduced_costs(self._h, b, len(b), _vptr(x if x.size else np.zeros(1)), _vptr(y if y.size else np.zeros(1)), int(use_zero_primal_objective), _vptr(rc)))
         return rc[: self.n]
 
-    def localized_bounds(self, x, y, primal_weight, radius, use_diagonal_qp_trust_region_solver=False, tolerance=1e-8):
+    def localized_bounds(self, x, y, primal_weight, radius, use_diagonal_qp_trust_region_solver=False, tolerance=1e-8, max_norm=False):
         x, y = _f64(x), _f64(y)
         out = np.zeros(4)
+        if max_norm:  # PrimalDualNorm::kMaxNorm (trust_region.cc:797-884)
+            _check(_lib.pdlp_b200_localized_bounds_max_norm(self._h, _vptr(x if x.size else np.zeros(1)), _vptr(y if y.size else np.zeros(1)),
+                                                            ctypes.c_double(primal_weight), ctypes.c_double(radius), _vptr(out)))
+            return dict(lagrangian_value=out[0], lower_bound=out[1], upper_bound=out[2], radius=out[3])
         _check(_lib.pdlp_b200_localized_bounds(self._h, _vptr(x if x.size else np.zeros(1)), _vptr(y if y.size else np.zeros(1)), ctypes.c_double(primal_weight),
                                                ctypes.c_double(radius), int(use_diagonal_qp_trust_region_solver), ctypes.c_double(tolerance), _vptr(out)))
         return dict(lagrangian_value=out[0], lower_bound=out[1], upper_bound=out[2], radius=out[3])

@@ -670,6 +670,21 @@ pdlp_b200_status pdlp_b200_localized_bounds(pdlp_b200_device_problem* h, const d
   });
 }
 
+pdlp_b200_status pdlp_b200_localized_bounds_max_norm(pdlp_b200_device_problem* h, const double* x, const double* y, double primal_weight, double radius, double* out) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (h == nullptr || out == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "bad argument");
+    PDLP_CUDA_CHECK(cudaSetDevice(h->device));
+    Workspace& ws = h->pre->ws();
+    DeviceProblem& p = h->pre->problem();
+    DVec dx(p.n > 0 ? p.n : 1), dy(p.m > 0 ? p.m : 1);
+    dx.Upload(x, p.n, ws.stream);
+    dy.Upload(y, p.m, ws.stream);
+    const LocalizedBounds b = ComputeLocalizedLagrangianBounds(ws, p, dx.get(), dy.get(), nullptr, primal_weight, radius, false, 0.0, nullptr, /*max_norm=*/true);
+    out[0] = b.lagrangian_value; out[1] = b.lower_bound; out[2] = b.upper_bound; out[3] = b.radius;
+    return PDLP_B200_OK;
+  });
+}
+
 static pdlp_b200_status TrialStepsImpl(pdlp_b200_device_problem* h, int steps, double step_size, double primal_weight, double* x, double* y,
                                        double* state_out, double* seconds, long long* launches, double* kernel_seconds);
 

@@ -134,7 +134,7 @@ double SquaredDistance(Workspace& ws, const double* a, const double* b, int64_t 
 // Euclidean-norm localized Lagrangian bounds at (x, y).  kty may be null (computed).
 LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProblem& p, const double* x, const double* y, const double* kty_or_null,
                                                  double primal_weight, double radius, bool use_diagonal_qp_solver, double diagonal_qp_tolerance,
-                                                 int* tr_passes);
+                                                 int* tr_passes, bool max_norm = false);
 
 // K v from caller-owned device CSR arrays with the work-block table in a static device array
 // (pdlp_noalloc.cu; the kernel side of pdlp_b200_matvec_no_alloc, which has no counterpart in the reference).

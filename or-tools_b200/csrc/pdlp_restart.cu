@@ -1,6 +1,7 @@
 // Restart-decision numerics on the device: Lagrangian gradients
 // (ortools/pdlp/sharded_optimization_utils.cc:446-527) and the Euclidean-norm localized
-// Lagrangian bounds (ortools/pdlp/trust_region.cc:886-1016) with the joint primal-dual
+// Lagrangian bounds (ortools/pdlp/trust_region.cc:886-1016; the max-norm variant :797-884 as two
+// masked sub-problems of the same code) with the joint primal-dual
 // bound-constrained trust-region solve (trust_region.cc:332-449, trust_region.h:193-337).
 //
 // The reference finds the trust-region step by repeated median pivoting over shrinking
@@ -30,13 +31,13 @@ struct DeviceRunner {
 
 LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProblem& p, const double* x, const double* y, const double* kty_or_null,
                                                  double primal_weight, double radius, bool use_diagonal_qp_solver, double diagonal_qp_tolerance,
-                                                 int* tr_passes) {
+                                                 int* tr_passes, bool max_norm) {
   const SparseRows& csr = p.K.by_row;
   const RestartProblemView view{csr.val.get(), csr.idx.get(), p.c.get(), p.q_or_null(), p.vlb.get(), p.vub.get(), p.clb.get(), p.cub.get(), p.n, p.m, p.is_lp,
                                 ws.dual_skip_below, ws.scratch_n[0].get(), ws.scratch_m[0].get(), ws.scratch_n[1].get(), ws.scratch_nm[0].get(),
                                 ws.scratch_nm[1].get()};
   DeviceRunner run{ws, p};
-  return LocalizedLagrangianBoundsWith(run, view, x, y, kty_or_null, primal_weight, radius, use_diagonal_qp_solver, diagonal_qp_tolerance, tr_passes);
+  return LocalizedLagrangianBoundsWith(run, view, x, y, kty_or_null, primal_weight, radius, use_diagonal_qp_solver, diagonal_qp_tolerance, tr_passes, max_norm);
 }
 
 }  // namespace pdlp_b200

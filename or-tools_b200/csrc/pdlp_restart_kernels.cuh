@@ -21,7 +21,9 @@ struct JointView {
   const double* vlb; const double* vub; const double* clb; const double* cub; const double* q;
   int64_t n; double w_primal, w_dual;
   int64_t dual_skip_below;  // sharded solve: dual rows below it are shared and counted on rank 0 only
-  __device__ bool Counts(int64_t i) const { return i < n || i - n >= dual_skip_below; }
+  int part = 0;             // 0: the joint problem; 1 / 2: only its primal / dual entries (the two max-norm problems, trust_region.cc:797-884)
+  __device__ bool InPart(int64_t i) const { return part == 0 || (part == 1) == (i < n); }
+  __device__ bool Counts(int64_t i) const { return InPart(i) && (i < n || i - n >= dual_skip_below); }
   __device__ double Objective(int64_t i) const { return i < n ? gx[i] : -gy[i - n]; }
   __device__ double LowerBound(int64_t i) const { return i < n ? vlb[i] : (isfinite(cub[i - n]) ? -INFINITY : 0.0); }
   __device__ double UpperBound(int64_t i) const { return i < n ? vub[i] : (isfinite(clb[i - n]) ? INFINITY : 0.0); }
@@ -97,6 +99,11 @@ struct CriticalOp : AlwaysActive {
   __host__ __device__ static constexpr int SlotKindOf(int) { return kMax; }
   JointView p; double* crit; double* coef;
   __device__ void Apply(int64_t i, Slots<1>& r) const {
+    if (!p.InPart(i)) {  // outside the sub-problem: never fixed, no radius coefficient
+      crit[i] = INFINITY;
+      coef[i] = 0.0;
+      return;
+    }
     const double obj = p.Objective(i), w = p.Weight(i);
     double cs = INFINITY;
     if (obj != 0.0) {
@@ -193,7 +200,7 @@ struct RestartProblemView {
 template <class Runner>
 LocalizedBounds LocalizedLagrangianBoundsWith(Runner& run, const RestartProblemView& p, const double* x, const double* y, const double* kty_or_null,
                                               double primal_weight, double radius, bool use_diagonal_qp_solver, double diagonal_qp_tolerance,
-                                              int* tr_passes) {
+                                              int* tr_passes, bool max_norm = false) {
   double* gx = p.gx;
   double* gy = p.gy;
   double primal_value = 0.0, dual_value = 0.0;
@@ -217,7 +224,7 @@ LocalizedBounds LocalizedLagrangianBoundsWith(Runner& run, const RestartProblemV
   LocalizedBounds out{lagrangian, lagrangian, lagrangian, radius};
   if (total == 0) { if (tr_passes) *tr_passes = 0; return out; }
 
-  if (use_diagonal_qp_solver) {
+  if (use_diagonal_qp_solver && !max_norm) {  // the max-norm bounds always use the linear-time solver (trust_region.cc:1003-1007)
     double primal_delta = 0.0, dual_delta = 0.0;
     if (radius == 0.0) {
       // Solution is the centre point: both deltas are exactly zero.
@@ -240,52 +247,69 @@ LocalizedBounds LocalizedLagrangianBoundsWith(Runner& run, const RestartProblemV
     return out;
   }
 
-  // SolveTrustRegionStepSize.
-  double step = 0.0;
-  if (radius > 0.0) {
+  // SolveTrustRegionStepSize (trust_region.cc:332-449) for a view of the joint index range.
+  auto solve_step = [&](const JointView& v, double target_radius) -> double {
+    double step = 0.0;
+    if (!(target_radius > 0.0)) return step;
     double* crit = p.crit;
     double* coef = p.coef;
-    const double max_obj = run.Joint(CriticalOp{{}, view, crit, coef}, total)[0];
-    if (max_obj > 0.0) {  // otherwise every objective entry is zero: step 0 (trust_region.cc:349-358)
-      // Root of phi(d) = fixed_r2(d) + d^2 free_coef(d) - r^2 (concave piecewise in d^2) by Newton from
-      // the left: from a point left of the root the Newton step lands left of the root again, and
-      // once a step crosses no breakpoint it is the exact root of the final segment.  Each pass also
-      // evaluates phi at four points further right (the Newton point plus 1, 3, 7, 15 times the
-      // last increment); the iteration continues from the rightmost one that is still left of the
-      // root.  The final value depends only on the final segment's sums, so it is the same root, bit
-      // for bit, as plain Newton's - in a third of the passes where the active set changes slowly.
-      const double r2 = radius * radius;
-      double delta = 0.0, increment = 0.0;
-      double prev_fixed = -1.0;
-      for (;;) {
-        RadiusPassOp op{{}, crit, coef, {}, p.n, view.dual_skip_below};
-        static const double kAhead[kRadiusCandidates] = {0.0, 1.0, 3.0, 7.0, 15.0};
-        for (int k = 0; k < kRadiusCandidates; ++k) op.delta[k] = delta + kAhead[k] * increment;
-        const double* h = run.Joint(op, total);
-        ++passes;
-        // Rightmost candidate that is not right of the root (candidate 0 never is).
-        int pick = 0;
-        for (int k = 1; k < kRadiusCandidates && increment > 0.0; ++k) {
-          const double d = op.delta[k];
-          const double phi = h[3 * k] + (d * d) * h[3 * k + 1] - r2;
-          if (phi <= 0.0 && d > op.delta[pick]) pick = k;
-        }
-        const double at = op.delta[pick];
-        const double fixed_r2 = h[3 * pick], free_coef = h[3 * pick + 1], num_fixed = h[3 * pick + 2];
-        if (!(free_coef > 0.0)) { step = DBL_MAX; break; }  // trust_region.cc:438-446
-        // No breakpoint crossed since the last pass: the Newton point is the exact root.
-        if (pick == 0 && num_fixed == prev_fixed) { step = at; break; }
-        const double next = std::sqrt(std::max(0.0, r2 - fixed_r2) / free_coef);
-        if (!(next > at)) { step = at; break; }  // already at the root up to rounding
-        if (passes >= 200) { step = next; break; }
-        prev_fixed = num_fixed;
-        increment = next - delta;
-        delta = next;
+    const double max_obj = run.Joint(CriticalOp{{}, v, crit, coef}, total)[0];
+    if (!(max_obj > 0.0)) return step;  // every objective entry is zero: step 0 (trust_region.cc:349-358)
+    // Root of phi(d) = fixed_r2(d) + d^2 free_coef(d) - r^2 (concave piecewise in d^2) by Newton from
+    // the left: from a point left of the root the Newton step lands left of the root again, and
+    // once a step crosses no breakpoint it is the exact root of the final segment.  Each pass also
+    // evaluates phi at four points further right (the Newton point plus 1, 3, 7, 15 times the
+    // last increment); the iteration continues from the rightmost one that is still left of the
+    // root.  The final value depends only on the final segment's sums, so it is the same root, bit
+    // for bit, as plain Newton's - in a third of the passes where the active set changes slowly.
+    const double r2 = target_radius * target_radius;
+    double delta = 0.0, increment = 0.0;
+    double prev_fixed = -1.0;
+    for (;;) {
+      RadiusPassOp op{{}, crit, coef, {}, p.n, v.dual_skip_below};
+      static const double kAhead[kRadiusCandidates] = {0.0, 1.0, 3.0, 7.0, 15.0};
+      for (int k = 0; k < kRadiusCandidates; ++k) op.delta[k] = delta + kAhead[k] * increment;
+      const double* h = run.Joint(op, total);
+      ++passes;
+      // Rightmost candidate that is not right of the root (candidate 0 never is).
+      int pick = 0;
+      for (int k = 1; k < kRadiusCandidates && increment > 0.0; ++k) {
+        const double d = op.delta[k];
+        const double phi = h[3 * k] + (d * d) * h[3 * k + 1] - r2;
+        if (phi <= 0.0 && d > op.delta[pick]) pick = k;
       }
+      const double at = op.delta[pick];
+      const double fixed_r2 = h[3 * pick], free_coef = h[3 * pick + 1], num_fixed = h[3 * pick + 2];
+      if (!(free_coef > 0.0)) { step = DBL_MAX; break; }  // trust_region.cc:438-446
+      // No breakpoint crossed since the last pass: the Newton point is the exact root.
+      if (pick == 0 && num_fixed == prev_fixed) { step = at; break; }
+      const double next = std::sqrt(std::max(0.0, r2 - fixed_r2) / free_coef);
+      if (!(next > at)) { step = at; break; }  // already at the root up to rounding
+      if (passes >= 200) { step = next; break; }
+      prev_fixed = num_fixed;
+      increment = next - delta;
+      delta = next;
     }
-  }
+    return step;
+  };
   double primal_delta = 0.0, dual_delta = 0.0;
-  {
+  if (max_norm) {
+    // ComputeMaxNormLocalizedLagrangianBounds (trust_region.cc:797-884): the primal and the dual problem are
+    // solved separately, each in the unweighted Euclidean norm, with radii sqrt(2) r / sqrt(w) and sqrt(2) r sqrt(w);
+    // lower = L + primal objective value, upper = L - dual objective value (its objective is -gradient).
+    JointView primal_view = view, dual_view = view;
+    primal_view.part = 1; primal_view.w_primal = 1.0; primal_view.w_dual = 1.0;
+    dual_view.part = 2; dual_view.w_primal = 1.0; dual_view.w_dual = 1.0;
+    if (p.n > 0) {
+      const double step = solve_step(primal_view, std::sqrt(2.0) * radius / std::sqrt(primal_weight));
+      primal_delta = run.Joint(BoundsDeltaOp{{}, primal_view, step}, total)[0];
+    }
+    if (p.m > 0) {
+      const double step = solve_step(dual_view, std::sqrt(2.0) * radius * std::sqrt(primal_weight));
+      dual_delta = run.Joint(BoundsDeltaOp{{}, dual_view, step}, total)[1];
+    }
+  } else {
+    const double step = solve_step(view, radius);
     const double* h = run.Joint(BoundsDeltaOp{{}, view, step}, total);
     primal_delta = h[0];
     dual_delta = h[1];

@@ -141,10 +141,7 @@ class _DeviceProblem:
         return self.h.reduced_costs(params, x, y, use_zero_primal_objective)
 
     def localized_bounds(self, x, y, primal_weight, radius, use_diagonal=False, tolerance=1e-8, max_norm=False):
-        if max_norm:  # PDHG only ever asks for the Euclidean norm (primal_dual_hybrid_gradient.cc:1741,1752)
-            import pytest
-            pytest.skip("the device path implements the Euclidean-norm bounds only")
-        return self.h.localized_bounds(x, y, primal_weight, radius, use_diagonal, tolerance)
+        return self.h.localized_bounds(x, y, primal_weight, radius, use_diagonal, tolerance, max_norm=max_norm)
 
 
 def make(name):

@@ -619,6 +619,20 @@ def test_localized_lagrangian_bounds_match_the_oracle(qp_case, diagonal):
             assert abs(got[key] - want[key]) <= (1e-5 if diagonal else 1e-10) * scale, (radius, key, got[key], want[key])
         passes.append(int(out[4]))
     assert passes[0] == 0 and max(passes) >= 2
+    if not diagonal:  # PrimalDualNorm::kMaxNorm: the primal and the dual problem solved separately (trust_region.cc:797-884)
+        lib.emu_set_max_norm(1)
+        try:
+            for radius, w in ((0.0, 1.0), (0.05, 1.0), (1.0, 0.6), (7.0, 2.0), (300.0, 1.0)):
+                want = oracle.localized_bounds(x, y, 0, w, radius, False, tol)
+                out = np.zeros(5)
+                assert lib.emu_localized_bounds(n, m, p(arr[0]), p(arr[1]), p(arr[2]), p(rb), len(rb) - 1, p(arc[0]), p(arc[1]), p(arc[2]), p(cb), len(cb) - 1,
+                                                *[p(v) for v in vec], ctypes.c_double(w), ctypes.c_double(radius), 0, ctypes.c_double(tol), 3, p(out)) == 0
+                got = dict(lagrangian_value=out[0], lower_bound=out[1], upper_bound=out[2], radius=out[3])
+                scale = max(1.0, abs(want["lagrangian_value"]))
+                for key in want:
+                    assert abs(got[key] - want[key]) <= 1e-10 * scale, ("max norm", radius, key, got[key], want[key])
+        finally:
+            lib.emu_set_max_norm(0)
 
 
 # ---- setup: Ruiz / L2 rescaling against the oracle ----
