@@ -50,23 +50,34 @@ inline int EnqueueRowsPeer(Workspace& ws, const Op& op, const SparseRows& s, int
   const int private_blocks = cut ? s.num_blocks - s.cut_block : 0;
   const int64_t shared_rows = cut ? s.cut_row : s.rows;
   unsigned long long epoch = 0;
-  if (shared_rows > 0) {  // the same on every rank
-    epoch = ws.comm->NextRowEpoch();
-    if (shared_blocks > 0) {
-      const RowBlocks v = s.ViewOfBlocks(0, shared_blocks);
-      const int g = std::min(shared_blocks, RowStreamGrid<PeerPartialRowOp<Op>>(s));
-      rowstream_kernel<PeerPartialRowOp<Op>><<<g, kBlock, 0, ws.stream>>>(PeerPartialRowOp<Op>{op, view, static_cast<int>(epoch & 1)}, v, partials);
+  int grid = 0;
+  if (shared_rows > 0) epoch = ws.comm->NextRowEpoch();  // the same on every rank
+  if (shared_rows > 0 && shared_blocks > 0 && private_blocks > 0) {
+    // One launch over the whole block: shared rows push, private rows finish in place (PeerCutRowOp).
+    using Cut = PeerCutRowOp<Op>;
+    Cut cut_op;
+    cut_op.op = op; cut_op.view = view; cut_op.parity = static_cast<int>(epoch & 1); cut_op.cut_row = static_cast<int>(s.cut_row);
+    grid = RowStreamGrid<Cut>(s);
+    rowstream_kernel<Cut><<<grid, kBlock, 0, ws.stream>>>(cut_op, s.View(), partials);
+    peer_signal_rows_kernel<<<1, 32, 0, ws.stream>>>(view, epoch);
+    ws.launches += 2;
+  } else {
+    if (shared_rows > 0) {
+      if (shared_blocks > 0) {
+        const RowBlocks v = s.ViewOfBlocks(0, shared_blocks);
+        const int g = std::min(shared_blocks, RowStreamGrid<PeerPartialRowOp<Op>>(s));
+        rowstream_kernel<PeerPartialRowOp<Op>><<<g, kBlock, 0, ws.stream>>>(PeerPartialRowOp<Op>{op, view, static_cast<int>(epoch & 1)}, v, partials);
+        ++ws.launches;
+      }
+      peer_signal_rows_kernel<<<1, 32, 0, ws.stream>>>(view, epoch);
       ++ws.launches;
     }
-    peer_signal_rows_kernel<<<1, 32, 0, ws.stream>>>(view, epoch);
-    ++ws.launches;
-  }
-  int grid = 0;
-  if (private_blocks > 0) {
-    const RowBlocks v = s.ViewOfBlocks(s.cut_block, private_blocks);
-    grid = std::min(private_blocks, RowStreamGrid<Op>(s));
-    rowstream_kernel<Op><<<grid, kBlock, 0, ws.stream>>>(op, v, partials);
-    ++ws.launches;
+    if (private_blocks > 0) {
+      const RowBlocks v = s.ViewOfBlocks(s.cut_block, private_blocks);
+      grid = std::min(private_blocks, RowStreamGrid<Op>(s));
+      rowstream_kernel<Op><<<grid, kBlock, 0, ws.stream>>>(op, v, partials);
+      ++ws.launches;
+    }
   }
   if (shared_rows > 0) {
     const int g = GridFor(shared_rows);

@@ -115,6 +115,56 @@ struct PeerPartialRowOp {
   }
 };
 
+// Phase 1 and the private rows in ONE row-stream launch (a CSR block cut into shared rows [0, cut_row) and
+// private rows): shared rows push their partial sums like PeerPartialRowOp, private rows run the op's own
+// epilogue.  The persistent grid takes work blocks in index order, shared rows first, so their NVLink stores
+// drain while the same CTAs work through the private rows; as two launches the pushing kernel had to wait
+// for its last store to be acknowledged before the private rows could start.
+template <class Op, bool kHasPre = HasRowPrefetch<Op>::value>
+struct PeerCutRowOp;
+template <class Op>
+struct PeerCutRowOpBase {
+  static constexpr int kNumSlots = Op::kNumSlots;
+  __host__ __device__ static constexpr int SlotKindOf(int s) { return Op::SlotKindOf(s); }
+  Op op;
+  PeerView view;
+  int parity;
+  int cut_row;
+  __device__ bool Begin() { return op.Begin(); }
+  __device__ double Load(int64_t k) const { return op.Load(k); }
+  template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
+  __device__ const int* IndexAddress(int64_t k) const { return op.IndexAddress(k); }
+  template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
+  __device__ const double* ValueAddress(int64_t k) const { return op.ValueAddress(k); }
+  template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
+  __device__ double Gather(int index) const { return op.Gather(index); }
+  template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
+  __device__ double Product(double value, double gathered) const { return op.Product(value, gathered); }
+  __device__ double RowInit() const { return op.RowInit(); }
+  __device__ double RowAdd(double acc, double staged, int row) const { return op.RowAdd(acc, staged, row); }
+  __device__ double RowMerge(double a, double b) const { return op.RowMerge(a, b); }
+  __device__ void Push(int row, double acc) const {
+#pragma unroll 1
+    for (int r = 0; r < view.world; ++r) view.RowSlot(r, parity, view.rank)[row] = acc;
+  }
+};
+template <class Op>
+struct PeerCutRowOp<Op, true> : PeerCutRowOpBase<Op> {
+  using Pre = typename Op::Pre;
+  __device__ Pre RowPrefetch(int row) const { return row >= this->cut_row ? this->op.RowPrefetch(row) : Pre{}; }
+  __device__ void RowFinish(int row, double acc, const Pre& pre, Slots<Op::kNumSlots>& red) const {
+    if (row < this->cut_row) this->Push(row, acc);
+    else this->op.RowFinish(row, acc, pre, red);
+  }
+};
+template <class Op>
+struct PeerCutRowOp<Op, false> : PeerCutRowOpBase<Op> {
+  __device__ void RowFinish(int row, double acc, Slots<Op::kNumSlots>& red) const {
+    if (row < this->cut_row) this->Push(row, acc);
+    else this->op.RowFinish(row, acc, red);
+  }
+};
+
 // Phase 2 in peer mode: wait for every rank's push, add the N local slots in rank order (or take their
 // maximum), run the op's epilogue.  A map op over the shared rows.  The wait runs even when the op is
 // switched off (Begin() false), so that ranks stay within one epoch of each other.

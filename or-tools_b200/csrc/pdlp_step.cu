@@ -25,23 +25,23 @@ namespace pdlp_b200 {
 
 namespace {
 
-struct StepSums { const double* p1; int g1; const double* p2; int g2; const double* p3; int g3; };
+struct StepSums { const double* p1; int g1; const double* p2; int g2; const double* p3; int g3; PeerView peer; unsigned long long peer_epoch; };
 StepSums CombineStepPartials(Workspace& ws, int g1, int g2, int g3) {
-  if (!IsSharded(ws)) return {ws.partials[0].get(), g1, ws.partials[1].get(), g2, ws.partials[2].get(), g3};
+  if (!IsSharded(ws)) return {ws.partials[0].get(), g1, ws.partials[1].get(), g2, ws.partials[2].get(), g3, PeerView{}, 0};
   double* t = ws.exchange_sums;
   if (ws.peer) {
     // Every rank pushes its four sums to all ranks; each then adds the N contributions in rank order.
     const PeerView view = ws.comm->peer_view();
     const unsigned long long epoch = ws.comm->NextSumEpoch();
+    // The decision kernel waits for the N contributions and adds them in rank order itself.
     fold_and_push_step_partials_kernel<<<1, kBlock, 0, ws.stream>>>(ws.partials[0].get(), g1, ws.partials[1].get(), g2, ws.partials[2].get(), g3, view, epoch);
-    peer_combine_sums_kernel<<<1, 32, 0, ws.stream>>>(view, epoch, t, 4, 0);
-    ws.launches += 2;
-    return {t, 1, t + 1, 1, t + 2, 1};
+    ++ws.launches;
+    return {t, 1, t + 1, 1, t + 2, 1, view, epoch};
   }
   fold_step_partials_kernel<<<1, kBlock, 0, ws.stream>>>(ws.partials[0].get(), g1, ws.partials[1].get(), g2, ws.partials[2].get(), g3, t);
   ++ws.launches;
   ws.comm->AllReduce(t, 4, false, ws.stream);
-  return {t, 1, t + 1, 1, t + 2, 1};
+  return {t, 1, t + 1, 1, t + 2, 1, PeerView{}, 0};
 }
 
 }  // namespace
@@ -72,7 +72,7 @@ void EnqueueAdaptiveTrials(Workspace& ws, const DeviceProblem& p, Iterate& it, i
     const int g3 = EnqueueRows(ws, k3, csc, 2);
     mark();
     const StepSums sums = CombineStepPartials(ws, g1, g2, g3);
-    decide_adaptive_kernel<<<1, kBlock, 0, ws.stream>>>(st, sums.p1, sums.g1, sums.p2, sums.g2, sums.p3, sums.g3, constant_step ? 1 : 0);
+    decide_adaptive_kernel<<<1, kBlock, 0, ws.stream>>>(st, sums.p1, sums.g1, sums.p2, sums.g2, sums.p3, sums.g3, constant_step ? 1 : 0, sums.peer, sums.peer_epoch);
     ++ws.launches;
     mark();
     mark();  // (the averaging slot of the per-kernel profile: folded into the next K1 / K2)
@@ -107,7 +107,7 @@ void EnqueueMalitskyPockTrials(Workspace& ws, const DeviceProblem& p, Iterate& i
     const int g2 = EnqueueRows(ws, k2, csr, 1);
     const int g3 = EnqueueRows(ws, k3, csc, 2);
     const StepSums sums = CombineStepPartials(ws, g1, g2, g3);
-    decide_mp_kernel<<<1, kBlock, 0, ws.stream>>>(st, sums.p1, sums.g1, sums.p2, sums.g2, sums.p3, sums.g3);
+    decide_mp_kernel<<<1, kBlock, 0, ws.stream>>>(st, sums.p1, sums.g1, sums.p2, sums.g2, sums.p3, sums.g3, sums.peer, sums.peer_epoch);
     ++ws.launches;
     EnqueueMap(ws, k5, p.n + p.m, 0);
   }

@@ -163,17 +163,25 @@ struct KtyStepOp {
 
 // K4 for the adaptive and constant rules.  One CTA; thread 0 carries the scalar logic
 // of :2305-2374 (adaptive) or :2382-2405 (constant).
+// `peer` (world > 1): a column-sharded solve in peer mode - the four step-test sums of every rank sit in this
+// rank's scalar slots (fold_and_push_step_partials_kernel); the kernel waits for them and adds them in rank
+// order instead of reading the partial tables.  The wait comes first and is unconditional (pdlp_peer.cuh).
 __global__ void __launch_bounds__(kBlock) decide_adaptive_kernel(StepState* st, const double* p1, int g1, const double* p2, int g2, const double* p3, int g3,
-                                                                int constant_step) {
+                                                                int constant_step, PeerView peer, unsigned long long peer_epoch) {
   __shared__ double buf[kBlock];
+  __shared__ double peer_sums[4];
+  if (peer.world > 1) {
+    if (threadIdx.x == 0) PeerCombineSums(peer, peer_epoch, peer_sums, 4, false);
+    __syncthreads();
+  }
   if (st->active == 0) {
     // avg_pending and reset_average stay as they are: the batch-end flush consumes them.
     if (threadIdx.x == 0) st->accepted_last = 0;
     return;
   }
-  const double dx2 = ReducePartialsSum(p1, g1, 1, 0, buf);
-  const double dy2 = ReducePartialsSum(p2, g2, 1, 0, buf);
-  const double dot = ReducePartialsSum(p3, g3, 2, 0, buf);
+  const double dx2 = peer.world > 1 ? peer_sums[0] : ReducePartialsSum(p1, g1, 1, 0, buf);
+  const double dy2 = peer.world > 1 ? peer_sums[1] : ReducePartialsSum(p2, g2, 1, 0, buf);
+  const double dot = peer.world > 1 ? peer_sums[2] : ReducePartialsSum(p3, g3, 2, 0, buf);
   if (threadIdx.x != 0) return;
   StepState s = *st;
   s.total_trials += 1;
@@ -290,15 +298,21 @@ __global__ void finish_average_kernel(StepState* st) {
 }
 
 // K4 for Malitsky-Pock (:2237-2291).
-__global__ void __launch_bounds__(kBlock) decide_mp_kernel(StepState* st, const double* p1, int g1, const double* p2, int g2, const double* p3, int g3) {
+__global__ void __launch_bounds__(kBlock) decide_mp_kernel(StepState* st, const double* p1, int g1, const double* p2, int g2, const double* p3, int g3, PeerView peer,
+                                                          unsigned long long peer_epoch) {
   __shared__ double buf[kBlock];
+  __shared__ double peer_sums[4];
+  if (peer.world > 1) {
+    if (threadIdx.x == 0) PeerCombineSums(peer, peer_epoch, peer_sums, 4, false);
+    __syncthreads();
+  }
   if (st->active == 0) {
     if (threadIdx.x == 0) { st->accepted_last = 0; st->reset_average = 0; st->first_mp_add_pending = 0; }
     return;
   }
-  const double dx2 = ReducePartialsSum(p1, g1, 1, 0, buf);
-  const double dy2 = ReducePartialsSum(p2, g2, 1, 0, buf);
-  const double dkty2 = ReducePartialsSum(p3, g3, 2, 1, buf);
+  const double dx2 = peer.world > 1 ? peer_sums[0] : ReducePartialsSum(p1, g1, 1, 0, buf);
+  const double dy2 = peer.world > 1 ? peer_sums[1] : ReducePartialsSum(p2, g2, 1, 0, buf);
+  const double dkty2 = peer.world > 1 ? peer_sums[3] : ReducePartialsSum(p3, g3, 2, 1, buf);
   if (threadIdx.x != 0) return;
   StepState s = *st;
   s.total_trials += 1;

@@ -1,0 +1,31 @@
+#!/bin/bash
+# Round 2 (8-GPU box), second scaling call: sharded GPU tests on the fused peer path (2 ranks), C3 strong scaling at
+# N = 8, 4, 2 in peer mode, C5 at scale 8 (the 1e9-nnz transportation LP) at N = 8 with the end-to-end solve.
+mkdir -p gpurun_out
+free -g | head -2 > gpurun_out/host_mem_8.txt
+( time timeout 600 python -m pytest tests/test_gpu_sharded.py -m gpu -x -q ) > gpurun_out/pytest_sharded_fused.log 2>&1; echo "pytest sharded exit $?" | tee -a gpurun_out/pytest_sharded_fused.log
+grep -n "passed\|failed\|error" gpurun_out/pytest_sharded_fused.log | tail -2
+show() {
+python - "$1" <<'P'
+import json, sys
+try:
+    d = json.loads([l for l in open(sys.argv[1]) if l.startswith("{")][-1])
+    e = d.get("e2e") or {}
+    print(sys.argv[1], "value", round(d["value"], 1), "ms/step", round(d["ms_per_step"], 4), "frac", round(d["roofline"]["frac"], 3),
+          [(k["kernel"], round(k["us_per_launch"], 1)) for k in d["roofline"]["kernels"]], "e2e", e.get("value"), e.get("time_to_tolerance_sec"), e.get("iterations"), e.get("termination_reason"),
+          "loop", d.get("loop_iterations_per_sec"), "peer", d.get("solve_peer_exchanges"), "parity", d.get("parity"))
+except Exception as e:
+    print(sys.argv[1], "failed", e)
+P
+}
+run() {  # N workload scale port extra...
+  local N=$1 w=$2 scale=$3 port=$4; shift 4
+  local TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $port"
+  timeout 700 $TR bench.py --gpus $N --workload $w --scale $scale --no-cpu "$@" > gpurun_out/r2b_${w}_s${scale}_${N}gpu.json 2> gpurun_out/r2b_${w}_s${scale}_${N}gpu.err
+  show gpurun_out/r2b_${w}_s${scale}_${N}gpu.json
+  tail -c 300 gpurun_out/r2b_${w}_s${scale}_${N}gpu.err | grep -v OMP_NUM | tail -3
+}
+run 8 c3 1.0 29531 --steps 200
+run 4 c3 1.0 29532 --steps 200
+run 2 c3 1.0 29533 --steps 200
+run 8 c5 8 29534 --steps 100

@@ -81,7 +81,7 @@ extern "C" int emu_adaptive_trials(int n, int m, const int* csr_ptr, const int* 
     const int g1 = LaunchMap(k1, n, p0);
     const int g2 = LaunchRows(k2, by_row, max_grid, p1);
     const int g3 = LaunchRows(k3, by_col, max_grid, p2);
-    cuda_emu::Launch(1, kBlock, [=]() { decide_adaptive_kernel(st, p0, g1, p1, g2, p2, g3, constant_step ? 1 : 0); });
+    cuda_emu::Launch(1, kBlock, [=]() { decide_adaptive_kernel(st, p0, g1, p1, g2, p2, g3, constant_step ? 1 : 0, PeerView{}, 0ULL); });
   }
   if (trials > 0) {
     LaunchMap(flush, static_cast<int64_t>(n) + m, p0);
@@ -148,7 +148,7 @@ extern "C" int emu_malitsky_pock_trials(int n, int m, const int* csr_ptr, const 
     LaunchMap(kx, n, p1);
     const int g2 = LaunchRows(k2, by_row, max_grid, p1);
     const int g3 = LaunchRows(k3, by_col, max_grid, p2);
-    cuda_emu::Launch(1, kBlock, [=]() { decide_mp_kernel(st, p0, g1, p1, g2, p2, g3); });
+    cuda_emu::Launch(1, kBlock, [=]() { decide_mp_kernel(st, p0, g1, p1, g2, p2, g3, PeerView{}, 0ULL); });
     LaunchMap(k5, static_cast<int64_t>(n) + m, p0);
   }
   std::copy(xb[state.cur].begin(), xb[state.cur].end(), x);
@@ -288,5 +288,28 @@ extern "C" int emu_peer_sums(int world, long long cap_rows, void* const* regions
     double* dst = out + static_cast<size_t>(r) * count;
     cuda_emu::Launch(1, 32, [=]() { peer_combine_sums_kernel(view, epoch, dst, count, max); });
   }
+  return 0;
+}
+
+// Phase 1 + private rows of `rank` in one launch (PeerCutRowOp), then the signal; `*dy2_private` = the private
+// rows' part of |dy|^2.  emu_peer_dual_finish with cut_block == num_blocks then only runs the shared rows' finish.
+extern "C" int emu_peer_dual_fused(int m_local, const int* ptr, const int* idx, const double* val, const int* block_start, int num_blocks, int cut_row,
+                                   const double* xbar, double* y0, double* y1, const double* clb, const double* cub, double step_size, double primal_weight,
+                                   int skip_below, int max_grid, int rank, int world, long long cap_rows, void* const* regions, unsigned long long epoch,
+                                   double* dy2_private) {
+  cuda_emu::defer_async = false;
+  HostRows csr{ptr, idx, val, block_start, num_blocks, m_local, {}};
+  const RowBlocks all = csr.View();
+  StepState state = FreshState(step_size, primal_weight);
+  const PeerView view = ViewOf(rank, world, cap_rows, regions);
+  PeerCutRowOp<DualStepOp> op;
+  op.op = DualStepOp{{}, &state, val, idx, xbar, y0, y1, clb, cub, skip_below, nullptr};
+  op.view = view; op.parity = static_cast<int>(epoch & 1); op.cut_row = cut_row;
+  std::vector<double> partials(kMaxGrid, 0.0);
+  const int grid = LaunchRows(op, all, max_grid, partials.data());
+  cuda_emu::Launch(1, 32, [=]() { peer_signal_rows_kernel(view, epoch); });
+  double total = 0.0;
+  for (int b = 0; b < grid; ++b) total += partials[b];
+  *dy2_private = total;
   return 0;
 }

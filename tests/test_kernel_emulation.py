@@ -449,14 +449,23 @@ def test_peer_memory_exchange_of_the_sharded_dual_step(step_libs, world):
         temp = y - sigma * (K @ xbar)
         want = np.maximum(np.minimum(0.0, temp + sigma * cub), temp + sigma * clb)
         ranks = [dict(k, xbar=np.ascontiguousarray(xbar[starts[r]:starts[r + 1]]), y1=np.zeros(k["m"])) for r, k in enumerate(blocks_of)]
-        for r, k in enumerate(ranks):
-            assert lib.emu_peer_dual_partial(k["m"], p(k["ptr"]), p(k["idx"]), p(k["val"]), p(k["blocks"]), len(k["blocks"]) - 1, k["cut"], p(k["xbar"]), p(k["y0"]),
-                                             p(k["y1"]), p(k["clb"]), p(k["cub"]), ctypes.c_double(step), ctypes.c_double(w), 3, r, world, ctypes.c_longlong(S), table,
-                                             ctypes.c_ulonglong(epoch)) == 0
+        fused = epoch == 2  # the middle epoch through the one-launch form (PeerCutRowOp), the others as two launches
         total = 0.0
         for r, k in enumerate(ranks):
+            if fused:
+                part = ctypes.c_double(0.0)
+                assert lib.emu_peer_dual_fused(k["m"], p(k["ptr"]), p(k["idx"]), p(k["val"]), p(k["blocks"]), len(k["blocks"]) - 1, S, p(k["xbar"]), p(k["y0"]),
+                                               p(k["y1"]), p(k["clb"]), p(k["cub"]), ctypes.c_double(step), ctypes.c_double(w), 0 if r == 0 else S, 3, r, world,
+                                               ctypes.c_longlong(S), table, ctypes.c_ulonglong(epoch), ctypes.byref(part)) == 0
+                total += part.value
+            else:
+                assert lib.emu_peer_dual_partial(k["m"], p(k["ptr"]), p(k["idx"]), p(k["val"]), p(k["blocks"]), len(k["blocks"]) - 1, k["cut"], p(k["xbar"]), p(k["y0"]),
+                                                 p(k["y1"]), p(k["clb"]), p(k["cub"]), ctypes.c_double(step), ctypes.c_double(w), 3, r, world, ctypes.c_longlong(S), table,
+                                                 ctypes.c_ulonglong(epoch)) == 0
+        for r, k in enumerate(ranks):
             dy2 = ctypes.c_double(0.0)
-            assert lib.emu_peer_dual_finish(k["m"], p(k["ptr"]), p(k["idx"]), p(k["val"]), p(k["blocks"]), len(k["blocks"]) - 1, k["cut"], S, p(k["xbar"]), p(k["y0"]),
+            nb = len(k["blocks"]) - 1
+            assert lib.emu_peer_dual_finish(k["m"], p(k["ptr"]), p(k["idx"]), p(k["val"]), p(k["blocks"]), nb, nb if fused else k["cut"], S, p(k["xbar"]), p(k["y0"]),
                                             p(k["y1"]), p(k["clb"]), p(k["cub"]), ctypes.c_double(step), ctypes.c_double(w), 0 if r == 0 else S, 3, r, world,
                                             ctypes.c_longlong(S), table, ctypes.c_ulonglong(epoch), ctypes.byref(dy2)) == 0
             total += dy2.value
