@@ -444,10 +444,13 @@ def main():
         for _ in range(extra_runs):
             dp.trial_steps(args.steps, st["step_size"], w0, x, y)
     # Every enqueued trial must have run: a trial that forces numerical termination turns the rest of
-    # the batch into no-op launches, which would still count towards steps/s.
-    trials_run = st2["iterations_completed"] + st2["num_rejected_steps"]
-    if trials_run != args.steps:
-        raise SystemExit(f"bench: {trials_run} of {args.steps} timed trial steps executed (the device stopped early: movement {st2['last_movement']}); no line printed")
+    # the batch into no-op launches, which would still count towards steps/s.  (Rejected trials of an
+    # iteration that has not accepted a step yet are in neither iterations_completed nor
+    # num_rejected_steps: count executed trials, not their sum.)
+    if st2["total_trials"] != args.steps or st2["forced_numerical_termination"]:
+        raise SystemExit(f"bench: {st2['total_trials']} of {args.steps} timed trial steps executed ({st2['iterations_completed']} accepted, {st2['num_rejected_steps']} + "
+                         f"{st2['pending_rejected_steps']} rejected; forced numerical termination {st2['forced_numerical_termination']}: movement {st2['last_movement']}, "
+                         f"nonlinearity {st2['last_nonlinearity']}, step size {st2['step_size']}); no line printed")
     t = torch.tensor([seconds], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -562,7 +565,7 @@ def main():
                          "dominant_kernel": dominant["kernel"], "dominant_kernel_achieved": dominant["achieved_gbs"],
                          "dominant_kernel_frac": (dominant["achieved_gbs"] or 0) / peak, "kernels": kernels},
             "cpu_baseline": cpu,
-            "accepted_steps_in_timed_region": st2["iterations_completed"], "rejected_steps_in_timed_region": st2["num_rejected_steps"],
+            "accepted_steps_in_timed_region": st2["iterations_completed"], "rejected_steps_in_timed_region": st2["num_rejected_steps"] + st2["pending_rejected_steps"],
         }
         line.update(solve_info)
         print(json.dumps(line))

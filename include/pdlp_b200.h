@@ -149,6 +149,32 @@ pdlp_b200_status pdlp_b200_solve_sharded(const pdlp_b200_problem* block, const p
                                          double* primal_solution, double* dual_solution, double* reduced_costs, int* has_solution,
                                          uint8_t** solve_log, size_t* solve_log_len, pdlp_b200_counters* counters);
 
+/* ---- presolve hand-off ----
+ * The reference runs Glop's preprocessor inside the solve when presolve_options.use_glop is set
+ * (ApplyPresolveIfEnabled, primal_dual_hybrid_gradient.cc:1145-1202): PDHG iterates on the presolved LP while
+ * convergence / infeasibility statistics, termination tests and the returned solution are those of the ORIGINAL
+ * problem at the point RecoverOriginalSolution (:1288-1341) maps back, and reduced costs are recomputed on the
+ * original (:1571-1585).  Glop is host code outside this library, so the presolver is the caller's:
+ *   original          the problem as given (sizes of primal / dual / reduced outputs, of the statistics)
+ *   presolved         what PDHG iterates on; NULL when the presolver solved the problem by itself - then
+ *                     presolve_status is its verdict as a TerminationReason (GlopStatusToTerminationReason,
+ *                     :1123-1143) and the result is built as in :986-1034 (solution_type
+ *                     POINT_TYPE_PRESOLVER_SOLUTION, callback type kPresolveTermination; OPTIMAL only if the
+ *                     recovered point really meets the optimality criteria, else NUMERICAL_ERROR)
+ *   postsolve         maps an UNSCALED solution of the presolved problem (both vectors, zero-length when
+ *                     presolved is NULL) to a solution of the original; called on the solving thread at every
+ *                     termination check and once at the end; the library then projects onto the original's
+ *                     variable bounds and dual sign constraints, as the reference does
+ *   initial solution  ignored with the reference's warning (:1164-1168)
+ * presolve_options.use_glop in params is not required and not consulted.  Single GPU only.  Everything
+ * else as pdlp_b200_solve. */
+typedef void (*pdlp_b200_postsolve)(const double* presolved_primal, const double* presolved_dual, double* original_primal, double* original_dual, void* user);
+pdlp_b200_status pdlp_b200_solve_presolved(const pdlp_b200_problem* original, const pdlp_b200_problem* presolved, int presolve_status, pdlp_b200_postsolve postsolve,
+                                           void* postsolve_user, const uint8_t* params, size_t params_len, const double* initial_primal_solution,
+                                           const double* initial_dual_solution, const volatile int* interrupt, pdlp_b200_callback callback, void* callback_user,
+                                           int device, double* primal_solution, double* dual_solution, double* reduced_costs, int* has_solution, uint8_t** solve_log,
+                                           size_t* solve_log_len, pdlp_b200_counters* counters);
+
 /* ValidatePrimalDualHybridGradientParams (solvers_proto_validation.cc:171-298): returns
  * PDLP_B200_OK and *message = NULL when valid, else *message = malloc'ed status text. */
 pdlp_b200_status pdlp_b200_validate_params(const uint8_t* params, size_t params_len, char** message);
@@ -239,9 +265,12 @@ pdlp_b200_status pdlp_b200_localized_bounds_max_norm(pdlp_b200_device_problem* h
  * primal weight, nothing else (no restarts, no checks): the timed unit of the
  * benchmark.  Outputs the iterate after the last accepted step and the step state:
  * state_out = {step_size, iterations_completed, num_rejected_steps, last_movement,
- * last_nonlinearity}; *seconds (optional) = CUDA-event time of the whole batch. */
+ * last_nonlinearity, trials executed, rejected trials of the unfinished iteration (counted in
+ * num_rejected_steps only once that iteration accepts a step), 1 if a trial forced numerical
+ * termination and turned the rest of the batch into no-ops}; *seconds (optional) = CUDA-event time
+ * of the whole batch. */
 pdlp_b200_status pdlp_b200_trial_steps(pdlp_b200_device_problem* h, int steps, double step_size, double primal_weight, double* x /*n, in-out*/,
-                                       double* y /*m, in-out*/, double* state_out /*5*/, double* seconds, long long* launches);
+                                       double* y /*m, in-out*/, double* state_out /*8*/, double* seconds, long long* launches);
 
 /* Same as pdlp_b200_trial_steps with a CUDA event recorded around every launch:
  * kernel_seconds = average duration of {primal_step, dual_step (K x), kty_step (K^T y),

@@ -134,7 +134,7 @@ EXPORTED_SYMBOLS = [
     "pdlp_b200_matvec", "pdlp_b200_scaled_norms", "pdlp_b200_stats", "pdlp_b200_rescale", "pdlp_b200_kkt_stats",
     "pdlp_b200_reduced_costs", "pdlp_b200_localized_bounds", "pdlp_b200_trial_steps", "pdlp_b200_trial_steps_profiled",
     "pdlp_b200_check_termination", "pdlp_b200_unique_id", "pdlp_b200_solve_sharded", "pdlp_b200_problem_create_sharded", "pdlp_b200_release_communicators",
-    "pdlp_b200_work_blocks", "pdlp_b200_matvec_no_alloc", "pdlp_b200_format_iteration_stats", "pdlp_b200_localized_bounds_max_norm",
+    "pdlp_b200_work_blocks", "pdlp_b200_matvec_no_alloc", "pdlp_b200_format_iteration_stats", "pdlp_b200_localized_bounds_max_norm", "pdlp_b200_solve_presolved",
 ]
 
 
@@ -199,6 +199,7 @@ from ._api import (  # noqa: E402
     is_linear_program,
     last_solve_counters,
     primal_dual_hybrid_gradient,
+    primal_dual_hybrid_gradient_presolved,
     validate_params,
     validate_quadratic_program_dimensions,
 )

@@ -179,7 +179,7 @@ def last_solve_counters():
     return dict(_last_counters)
 
 
-def primal_dual_hybrid_gradient(qp, params, initial_solution=None, interrupt_solve=None, iteration_stats_callback=None, device=-1, shard=None):
+def primal_dual_hybrid_gradient(qp, params, initial_solution=None, interrupt_solve=None, iteration_stats_callback=None, device=-1, shard=None, _presolve=None):
     """primal_dual_hybrid_gradient.h:140-156.  `shard` (sharding.ColumnShard): `qp` is this rank's column block.  `interrupt_solve`, if given, is a
     numpy int32 array of one element (non-zero = stop); `iteration_stats_callback`
     receives an IterationCallbackInfo."""
@@ -240,12 +240,14 @@ def primal_dual_hybrid_gradient(qp, params, initial_solution=None, interrupt_sol
     if interrupt_solve is not None:
         assert interrupt_solve.dtype == np.int32 and interrupt_solve.size >= 1
         interrupt_ptr = ctypes.c_void_p(interrupt_solve.ctypes.data)
-    status = _lib.pdlp_b200_solve_sharded(
-        ctypes.byref(mar.c_problem), ctypes.byref(shard.c_shard) if shard is not None else None, pbytes, len(pbytes), _vptr(x0), _vptr(y0), interrupt_ptr,
-        ctypes.cast(cb, ctypes.c_void_p) if cb is not None else None, None, int(device),
-        _vptr(primal), _vptr(dual), _vptr(reduced), ctypes.byref(has_solution), ctypes.byref(log_ptr), ctypes.byref(log_len),
-        ctypes.byref(counters),
-    )
+    tail = (pbytes, len(pbytes), _vptr(x0), _vptr(y0), interrupt_ptr, ctypes.cast(cb, ctypes.c_void_p) if cb is not None else None, None, int(device),
+            _vptr(primal), _vptr(dual), _vptr(reduced), ctypes.byref(has_solution), ctypes.byref(log_ptr), ctypes.byref(log_len), ctypes.byref(counters))
+    if _presolve is not None:
+        presolved_mar, presolve_status, post = _presolve
+        status = _lib.pdlp_b200_solve_presolved(ctypes.byref(mar.c_problem), ctypes.byref(presolved_mar.c_problem) if presolved_mar is not None else None,
+                                                int(presolve_status), ctypes.cast(post, ctypes.c_void_p), None, *tail)
+    else:
+        status = _lib.pdlp_b200_solve_sharded(ctypes.byref(mar.c_problem), ctypes.byref(shard.c_shard) if shard is not None else None, *tail)
     _check(status)
     if cb_error:
         raise cb_error[0]
@@ -259,6 +261,51 @@ def primal_dual_hybrid_gradient(qp, params, initial_solution=None, interrupt_sol
         kernel_launches=counters.kernel_launches, trial_steps=counters.trial_steps, setup_seconds=counters.setup_seconds,
         loop_seconds=counters.loop_seconds, device_loop_seconds=counters.device_loop_seconds, collectives=counters.collectives, upload_seconds=counters.upload_seconds, symmetric_buffers=counters.symmetric_buffers, peer_exchanges=counters.peer_exchanges,
     )
+    return result
+
+
+POSTSOLVE_TYPE = ctypes.CFUNCTYPE(None, _c_double_p, _c_double_p, _c_double_p, _c_double_p, ctypes.c_void_p)
+
+
+def primal_dual_hybrid_gradient_presolved(original_qp, presolved_qp, postsolve, params, presolve_status=0, initial_solution=None, interrupt_solve=None,
+                                          iteration_stats_callback=None, device=-1):
+    """The presolve hand-off (include/pdlp_b200.h: pdlp_b200_solve_presolved; the reference's Glop branch,
+    primal_dual_hybrid_gradient.cc:1145-1202, :986-1034, :1288-1341, with the caller's presolver).
+
+    PDHG iterates on `presolved_qp`; statistics, termination tests and the returned vectors are those of
+    `original_qp` at the point `postsolve(x_presolved, y_presolved) -> (x_original, y_original)` recovers (numpy
+    arrays, unscaled).  presolved_qp None: the presolver solved the problem by itself and `presolve_status` is its
+    verdict (a TerminationReason number); postsolve is then called with two empty arrays."""
+    for name, q in (("original", original_qp), ("presolved", presolved_qp)):
+        if q is not None:
+            err = _dimension_error(q)
+            if err:
+                raise ValueError(f"{name} problem: {err}")
+    n_o, m_o = len(original_qp.objective_vector), len(original_qp.constraint_lower_bounds)
+    presolved_mar = _Marshalled(presolved_qp) if presolved_qp is not None else None
+    n_p = presolved_mar.n if presolved_mar is not None else 0
+    m_p = presolved_mar.m if presolved_mar is not None else 0
+    errors = []
+
+    def _post(px, py, ox, oy, _user):
+        try:
+            x = np.ctypeslib.as_array(px, shape=(n_p,)).copy() if n_p else np.zeros(0)
+            y = np.ctypeslib.as_array(py, shape=(m_p,)).copy() if m_p else np.zeros(0)
+            rx, ry = postsolve(x, y)
+            rx, ry = _f64(rx), _f64(ry)
+            if rx.size != n_o or ry.size != m_o:
+                raise ValueError(f"postsolve returned vectors of sizes {rx.size}, {ry.size}; the original problem has {n_o} variables and {m_o} constraints")
+            if n_o:
+                np.ctypeslib.as_array(ox, shape=(n_o,))[:] = rx
+            if m_o:
+                np.ctypeslib.as_array(oy, shape=(m_o,))[:] = ry
+        except BaseException as e:  # noqa: BLE001 - must not unwind through C; the outputs stay as they are
+            errors.append(e)
+
+    result = primal_dual_hybrid_gradient(original_qp, params, initial_solution, interrupt_solve, iteration_stats_callback, device,
+                                         _presolve=(presolved_mar, presolve_status, POSTSOLVE_TYPE(_post)))
+    if errors:
+        raise errors[0]
     return result
 
 
@@ -348,12 +395,13 @@ class DeviceProblem:
         """Runs `steps` adaptive-rule trial steps from (x, y); returns (x, y, state dict, seconds, launches)."""
         x = np.zeros(max(self.n, 1)) if x is None else _f64(x).copy()
         y = np.zeros(max(self.m, 1)) if y is None else _f64(y).copy()
-        st = np.zeros(5)
+        st = np.zeros(8)
         sec = ctypes.c_double(0)
         launches = ctypes.c_longlong(0)
         _check(_lib.pdlp_b200_trial_steps(self._h, int(steps), ctypes.c_double(step_size), ctypes.c_double(primal_weight), _vptr(x), _vptr(y), _vptr(st),
                                           ctypes.byref(sec), ctypes.byref(launches)))
-        state = dict(step_size=st[0], iterations_completed=int(st[1]), num_rejected_steps=int(st[2]), last_movement=st[3], last_nonlinearity=st[4])
+        state = dict(step_size=st[0], iterations_completed=int(st[1]), num_rejected_steps=int(st[2]), last_movement=st[3], last_nonlinearity=st[4],
+                     total_trials=int(st[5]), pending_rejected_steps=int(st[6]), forced_numerical_termination=bool(st[7]))
         return x[: self.n], y[: self.m], state, sec.value, launches.value
 
     def trial_steps_profiled(self, steps, step_size, primal_weight, x=None, y=None):

@@ -97,7 +97,7 @@ SolverResult SolveView(const QpView& qp, const PrimalDualHybridGradientParams& p
     return ErrorSolverResult(TERMINATION_REASON_INVALID_PARAMETER, "use_feasibility_polishing is only implemented for linear programs.");
   if (params.presolve_options->use_glop)
     return ErrorSolverResult(TERMINATION_REASON_INVALID_PARAMETER,
-                             "presolve_options.use_glop is not supported by the device path: Glop presolve is host-only (run it before the call).");
+                             "presolve_options.use_glop is not supported by the device path: Glop presolve is host-only. Presolve on the host and call pdlp_b200_solve_presolved with the presolved problem and a postsolve callback.");
   WallTimer upload;
   upload.Start();
   PreprocessSolver solver(qp, params);
@@ -106,6 +106,45 @@ SolverResult SolveView(const QpView& qp, const PrimalDualHybridGradientParams& p
   if (qp.world > 1 && (code = solver.AgreeOnCode(code)) != 0) return describe(code);
   const double upload_seconds = upload.Get();
   SolverResult result = solver.PreprocessAndSolve(params, x0, y0, interrupt, std::move(callback));
+  g_last_counters.upload_seconds = upload_seconds;
+  return result;
+}
+
+// The presolve hand-off (pdhg.cc:1145-1202, :986-1034, :1288-1341 with the caller's presolver in Glop's place):
+// PDHG runs on `presolved` (null: the presolver solved the problem, `presolve_reason` says how), every
+// statistic, termination test and the result are those of `original` at the point `postsolve` recovers.
+SolverResult SolveViewPresolved(const QpView& original, const QpView* presolved, int presolve_reason,
+                                std::function<void(const double*, const double*, double*, double*)> postsolve, const PrimalDualHybridGradientParams& params,
+                                const double* x0, const double* y0, const InterruptFlag* interrupt, IterationCallback callback, SolutionSink* sink) {
+  auto invalid = [&](const QpView& qp) -> const char* {
+    if (!BoundsAreValid(qp.clb, qp.cub, qp.m) || !BoundsAreValid(qp.vlb, qp.vub, qp.n)) return "The input problem has inconsistent bounds.";
+    if (qp.objective_scaling_factor == 0) return "The objective scaling factor cannot be zero.";
+    if (qp.q != nullptr) {
+      for (int64_t j = 0; j < qp.n; ++j) if (qp.q[j] < 0.0) return "The objective is not convex (i.e., the objective matrix contains negative entries).";
+    }
+    return nullptr;
+  };
+  if (const char* e = invalid(original)) return ErrorSolverResult(TERMINATION_REASON_INVALID_PROBLEM, e);
+  if (presolved != nullptr) {
+    if (const char* e = invalid(*presolved)) return ErrorSolverResult(TERMINATION_REASON_INVALID_PROBLEM, std::string("presolved problem: ") + e);
+  }
+  if (params.use_feasibility_polishing && (original.q != nullptr || (presolved != nullptr && presolved->q != nullptr)))
+    return ErrorSolverResult(TERMINATION_REASON_INVALID_PARAMETER, "use_feasibility_polishing is only implemented for linear programs.");
+  WallTimer upload;
+  upload.Start();
+  PreprocessSolver original_solver(original, params);
+  PresolveHook hook;
+  hook.original = &original_solver;
+  hook.postsolve = std::move(postsolve);
+  static const int64_t kNoColumns[1] = {0};
+  QpView empty;  // zero variables, zero constraints: what PDHG "iterates on" when the presolver solved everything
+  empty.col_ptr = kNoColumns;
+  PreprocessSolver working(presolved != nullptr ? *presolved : empty, params);
+  working.set_presolve(&hook);
+  working.set_solution_sink(sink);
+  const double upload_seconds = upload.Get();
+  SolverResult result = presolved != nullptr ? working.PreprocessAndSolve(params, x0, y0, interrupt, std::move(callback))
+                                             : working.FinishPresolvedOnly(params, presolve_reason, interrupt, std::move(callback));
   g_last_counters.upload_seconds = upload_seconds;
   return result;
 }
@@ -311,13 +350,28 @@ pdlp_b200_status pdlp_b200_release_communicators(int* released) {
   });
 }
 
-pdlp_b200_status pdlp_b200_solve_sharded(const pdlp_b200_problem* problem, const pdlp_b200_shard* shard, const uint8_t* params_bytes, size_t params_len,
-                                         const double* x0, const double* y0, const volatile int* interrupt, pdlp_b200_callback callback,
-                                         void* callback_user, int device, double* primal, double* dual, double* reduced, int* has_solution,
-                                         uint8_t** solve_log, size_t* solve_log_len, pdlp_b200_counters* counters) {
+namespace {
+struct PresolveArgs {
+  const pdlp_b200_problem* presolved;  // null: the presolver solved the problem
+  int presolve_reason;
+  pdlp_b200_postsolve postsolve;
+  void* user;
+};
+}  // namespace
+
+static pdlp_b200_status SolveCommon(const pdlp_b200_problem* problem, const pdlp_b200_shard* shard, const PresolveArgs* pre, const uint8_t* params_bytes,
+                                    size_t params_len, const double* x0, const double* y0, const volatile int* interrupt, pdlp_b200_callback callback,
+                                    void* callback_user, int device, double* primal, double* dual, double* reduced, int* has_solution, uint8_t** solve_log,
+                                    size_t* solve_log_len, pdlp_b200_counters* counters) {
   return Guard([&]() -> pdlp_b200_status {
     if (!ProblemPointersOk(problem) || solve_log == nullptr || solve_log_len == nullptr || has_solution == nullptr)
       return Fail(PDLP_B200_BAD_ARGUMENT, "null or negative-sized argument");
+    if (pre != nullptr) {
+      if (pre->postsolve == nullptr) return Fail(PDLP_B200_BAD_ARGUMENT, "postsolve callback is null");
+      if (pre->presolved != nullptr && !ProblemPointersOk(pre->presolved)) return Fail(PDLP_B200_BAD_ARGUMENT, "presolved problem: null or negative-sized argument");
+      if (pre->presolved == nullptr && (pre->presolve_reason < TERMINATION_REASON_OPTIMAL || pre->presolve_reason > TERMINATION_REASON_INVALID_INITIAL_SOLUTION))
+        return Fail(PDLP_B200_BAD_ARGUMENT, "presolve_status must be a TerminationReason when there is no presolved problem");
+    }
     QpView view = ViewOfC(problem);
     if (const std::string e = ApplyShard(shard, &view); !e.empty()) return Fail(PDLP_B200_BAD_ARGUMENT, e);
     if ((x0 == nullptr) != (y0 == nullptr)) {
@@ -349,8 +403,19 @@ pdlp_b200_status pdlp_b200_solve_sharded(const pdlp_b200_problem* problem, const
       }
       static const double kEmpty = 0.0;
       const bool warm = x0 != nullptr || y0 != nullptr;
-      result = SolveView(view, params, warm ? (x0 ? x0 : &kEmpty) : nullptr, warm ? (y0 ? y0 : &kEmpty) : nullptr,
-                         interrupt != nullptr ? &flag : nullptr, std::move(cb), &sink);
+      if (pre != nullptr) {
+        QpView presolved_view;
+        if (pre->presolved != nullptr) presolved_view = ViewOfC(pre->presolved);
+        pdlp_b200_postsolve fn = pre->postsolve;
+        void* user = pre->user;
+        result = SolveViewPresolved(view, pre->presolved != nullptr ? &presolved_view : nullptr, pre->presolve_reason,
+                                    [fn, user](const double* px, const double* py, double* ox, double* oy) { fn(px, py, ox, oy, user); }, params,
+                                    warm ? (x0 ? x0 : &kEmpty) : nullptr, warm ? (y0 ? y0 : &kEmpty) : nullptr, interrupt != nullptr ? &flag : nullptr, std::move(cb),
+                                    &sink);
+      } else {
+        result = SolveView(view, params, warm ? (x0 ? x0 : &kEmpty) : nullptr, warm ? (y0 ? y0 : &kEmpty) : nullptr,
+                           interrupt != nullptr ? &flag : nullptr, std::move(cb), &sink);
+      }
     }
     // The solver wrote the solution straight into primal / dual / reduced (SolutionSink).
     if (sink.filled && result.solve_log.termination_reason != TERMINATION_REASON_INVALID_PROBLEM &&
@@ -375,6 +440,23 @@ pdlp_b200_status pdlp_b200_solve_sharded(const pdlp_b200_problem* problem, const
     }
     return PDLP_B200_OK;
   });
+}
+
+pdlp_b200_status pdlp_b200_solve_sharded(const pdlp_b200_problem* problem, const pdlp_b200_shard* shard, const uint8_t* params_bytes, size_t params_len,
+                                         const double* x0, const double* y0, const volatile int* interrupt, pdlp_b200_callback callback,
+                                         void* callback_user, int device, double* primal, double* dual, double* reduced, int* has_solution,
+                                         uint8_t** solve_log, size_t* solve_log_len, pdlp_b200_counters* counters) {
+  return SolveCommon(problem, shard, nullptr, params_bytes, params_len, x0, y0, interrupt, callback, callback_user, device, primal, dual, reduced, has_solution, solve_log,
+                     solve_log_len, counters);
+}
+
+pdlp_b200_status pdlp_b200_solve_presolved(const pdlp_b200_problem* original, const pdlp_b200_problem* presolved, int presolve_status, pdlp_b200_postsolve postsolve,
+                                           void* postsolve_user, const uint8_t* params_bytes, size_t params_len, const double* x0, const double* y0,
+                                           const volatile int* interrupt, pdlp_b200_callback callback, void* callback_user, int device, double* primal, double* dual,
+                                           double* reduced, int* has_solution, uint8_t** solve_log, size_t* solve_log_len, pdlp_b200_counters* counters) {
+  const PresolveArgs pre{presolved, presolve_status, postsolve, postsolve_user};
+  return SolveCommon(original, nullptr, &pre, params_bytes, params_len, x0, y0, interrupt, callback, callback_user, device, primal, dual, reduced, has_solution,
+                     solve_log, solve_log_len, counters);
 }
 
 pdlp_b200_status pdlp_b200_validate_params(const uint8_t* params_bytes, size_t params_len, char** message) {
@@ -772,6 +854,7 @@ static pdlp_b200_status TrialStepsImpl(pdlp_b200_device_problem* h, int steps, d
     if (state_out != nullptr) {
       state_out[0] = st.step_size; state_out[1] = st.iterations_completed; state_out[2] = st.num_rejected_steps;
       state_out[3] = st.last_movement; state_out[4] = st.last_nonlinearity;
+      state_out[5] = static_cast<double>(st.total_trials); state_out[6] = st.inner; state_out[7] = st.force_numerical;
     }
     return PDLP_B200_OK;
   });

@@ -67,6 +67,18 @@ SolverResult ErrorSolverResult(int reason, const std::string& message);  // pdhg
 extern thread_local SolveCounters g_last_counters;
 
 class Solver;
+class PreprocessSolver;
+
+// What the reference keeps in PresolveInfo (pdhg.cc:395-417) when Glop presolve ran: the original problem
+// (resident on the device through a PreprocessSolver of its own, never rescaled) and the way back from a
+// solution of the presolved problem.  Here the presolver is the caller's (Glop is host code outside this
+// library): `postsolve` maps UNSCALED presolved (x, y) host vectors to original-space host vectors, the
+// role of glop::MainLpPreprocessor::RecoverSolution in RecoverOriginalSolution (:1288-1341).
+struct PresolveHook {
+  PreprocessSolver* original = nullptr;
+  std::function<void(const double* presolved_x, const double* presolved_y, double* original_x, double* original_y)> postsolve;
+  DVec x, y;  // the recovered point on the device (original sizes)
+};
 
 // pdhg.cc:318-502.
 class PreprocessSolver {
@@ -76,6 +88,12 @@ class PreprocessSolver {
   SolverResult PreprocessAndSolve(const PrimalDualHybridGradientParams& params, const double* x0, const double* y0,
                                   const InterruptFlag* interrupt, IterationCallback callback);
   void set_solution_sink(SolutionSink* sink) { sink_ = sink; }
+  // The solve runs on this (presolved) problem; statistics, termination tests and the result are those of
+  // hook->original at the recovered point (pdhg.cc:1530-1548, :1571-1585).
+  void set_presolve(PresolveHook* hook) { presolve_ = hook; }
+  // The presolver solved the problem by itself (pdhg.cc:986-1034): no iterations, the result is the recovered
+  // empty solution with `presolve_reason` (a TerminationReason) unless the point earns a better one.
+  SolverResult FinishPresolvedOnly(const PrimalDualHybridGradientParams& params, int presolve_reason, const InterruptFlag* interrupt, IterationCallback callback);
 
   // pdhg.cc:1434-1518.  Points are device pointers; avg / delta may be null.
   std::optional<TerminationReasonAndPointType> UpdateIterationStatsAndCheckTermination(
@@ -114,6 +132,10 @@ class PreprocessSolver {
   IterationCallback callback_;
   std::vector<int32_t> seeds_;
   SolutionSink* sink_ = nullptr;
+  PresolveHook* presolve_ = nullptr;
+  // Unscales (x, y) of this problem, runs the postsolve hook and leaves the projected original-space point in
+  // presolve_->x / y (RecoverOriginalSolution, pdhg.cc:1288-1341).
+  void RecoverOriginalOnDevice(const double* x, const double* y);
   // Text logging (pdlp_logging.h): a table header every 15 lines, lines at most every log_interval_seconds; rank 0 only.
   int log_counter_ = 0;
   double time_of_last_log_ = -1.0e300;
@@ -183,6 +205,7 @@ class Solver {
   WallTimer timer_;
   struct { double distance_moved_last_restart_period = std::numeric_limits<double>::infinity(); int length_of_last_restart_period = 1; } distance_info_;
   int poll_iterations_ = 8;
+  double kkt_passes_from_polishing_ = 0.0;  // cumulative_kkt_matrix_passes of the polishing phases so far (counts against kkt_matrix_pass_limit)
   bool poll_always_ = false;
   // Sharded solves: host decisions must be identical on every rank, so the two rank-local
   // inputs (wall clock, interrupt flag) are agreed on (max over ranks) once per host event.

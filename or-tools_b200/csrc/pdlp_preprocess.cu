@@ -227,8 +227,20 @@ SolverResult PreprocessSolver::PreprocessAndSolve(const PrimalDualHybridGradient
   log.params.mut() = params;
   DeviceProblem& p = problem_;
   ReplaceLargeBoundsWithInfinity(ws_, p.clb.get(), p.cub.get(), p.m, params.infinite_constraint_bound_threshold);
-  log.original_problem_stats.mut() = ComputeStats();
-  if (auto r = CheckProblemStats(log.original_problem_stats.get(), params.presolve_options->use_glop); r.has_value()) return *r;
+  if (presolve_ != nullptr) {
+    // The statistics of the ORIGINAL problem (pdhg.cc:962-978 run before ApplyPresolveIfEnabled); a warm start
+    // cannot be mapped into the presolved space and is dropped with the reference's warning (:1164-1168).
+    PreprocessSolver& o = *presolve_->original;
+    ReplaceLargeBoundsWithInfinity(o.ws_, o.problem_.clb.get(), o.problem_.cub.get(), o.problem_.m, params.infinite_constraint_bound_threshold);
+    log.original_problem_stats.mut() = o.ComputeStats();
+    if (x0 != nullptr || y0 != nullptr) {
+      std::fputs("WARNING: Ignoring initial solution. Initial solutions are ignored when presolve is on.\n", stderr);
+      x0 = y0 = nullptr;
+    }
+  } else {
+    log.original_problem_stats.mut() = ComputeStats();
+  }
+  if (auto r = CheckProblemStats(log.original_problem_stats.get(), presolve_ != nullptr || params.presolve_options->use_glop); r.has_value()) return *r;
 
   // Starting point (pdhg.cc:1035-1048).  The size checks of CheckInitialSolution
   // (:899-947) happen at the API boundary where the sizes are known.
@@ -352,6 +364,16 @@ void PreprocessSolver::ComputeConvergenceAndInfeasibility(const PrimalDualHybrid
   const DetailedOptimalityCriteria oc = EffectiveOptimalityCriteria(params.termination_criteria.get());
   const double primal_ratio = EpsilonRatio(oc.eps_optimal_primal_residual_absolute, oc.eps_optimal_primal_residual_relative);
   const double dual_ratio = EpsilonRatio(oc.eps_optimal_dual_residual_absolute, oc.eps_optimal_dual_residual_relative);
+  if (presolve_ != nullptr && (ci != nullptr || ii != nullptr)) {
+    // pdhg.cc:1530-1548: under presolve the convergence and infeasibility information are those of the ORIGINAL
+    // problem (trivial scaling) at the recovered point; the point metadata stay those of the working problem.
+    RecoverOriginalOnDevice(x, y);
+    presolve_->original->ComputeConvergenceAndInfeasibility(params, presolve_->x.get(), presolve_->y.get(), presolve_->x.get(), presolve_->y.get(), candidate_type, ci,
+                                                            ii, nullptr);
+    if (md == nullptr) return;
+    ci = nullptr;
+    ii = nullptr;
+  }
   const KktTotals t = ComputeKktTotals(ws_, problem_, x, y, x_start, y_start, primal_ratio, dual_ratio,
                                        params.handle_some_primal_gradients_on_finite_bounds_as_residuals);
   auto apply = [&](double v) { return problem_.objective_scaling_factor * (v + problem_.objective_offset); };
@@ -460,8 +482,96 @@ std::optional<TerminationReasonAndPointType> PreprocessSolver::UpdateIterationSt
   return CheckSimpleTerminationCriteria(params.termination_criteria.get(), full_stats, interrupt);
 }
 
+// RecoverOriginalSolution (pdhg.cc:1288-1341) with the caller's postsolve in the place of Glop's.
+void PreprocessSolver::RecoverOriginalOnDevice(const double* x, const double* y) {
+  DeviceProblem& p = problem_;
+  PreprocessSolver& o = *presolve_->original;
+  std::vector<double> hx(p.n), hy(p.m), ox(o.problem_.n), oy(o.problem_.m);
+  if (p.n > 0) {
+    double* t = ws_.scratch_n[2].get();
+    CopyVector(ws_, t, x, p.n);
+    MultiplyInPlace(ws_, t, p.col_scale.get(), p.n);
+    PDLP_CUDA_CHECK(cudaMemcpyAsync(hx.data(), t, p.n * sizeof(double), cudaMemcpyDeviceToHost, ws_.stream));
+  }
+  if (p.m > 0) {
+    double* t = ws_.scratch_m[2].get();
+    CopyVector(ws_, t, y, p.m);
+    MultiplyInPlace(ws_, t, p.row_scale.get(), p.m);
+    PDLP_CUDA_CHECK(cudaMemcpyAsync(hy.data(), t, p.m * sizeof(double), cudaMemcpyDeviceToHost, ws_.stream));
+  }
+  ws_.Sync();
+  presolve_->postsolve(hx.data(), hy.data(), ox.data(), oy.data());
+  if (presolve_->x.size() == 0) {
+    presolve_->x.Resize(o.problem_.n > 0 ? o.problem_.n : 1);
+    presolve_->y.Resize(o.problem_.m > 0 ? o.problem_.m : 1);
+  }
+  presolve_->x.Upload(ox.data(), o.problem_.n, o.ws_.stream);
+  presolve_->y.Upload(oy.data(), o.problem_.m, o.ws_.stream);
+  // "Glop's preprocessor sometimes violates the primal bounds constraints. To be safe we project both." (:1332-1337)
+  ProjectToPrimalBounds(o.ws_, o.problem_, presolve_->x.get());
+  ProjectToDualBounds(o.ws_, o.problem_, presolve_->y.get());
+  o.ws_.Sync();
+}
+
+// The presolver solved the problem completely (pdhg.cc:986-1034).
+SolverResult PreprocessSolver::FinishPresolvedOnly(const PrimalDualHybridGradientParams& params, int presolve_reason, const InterruptFlag* interrupt,
+                                                   IterationCallback callback) {
+  WallTimer timer;
+  timer.Start();
+  SolveLog log;
+  if (view_.name != nullptr) log.instance_name = std::string(view_.name);
+  log.params.mut() = params;
+  PreprocessSolver& o = *presolve_->original;
+  ReplaceLargeBoundsWithInfinity(o.ws_, o.problem_.clb.get(), o.problem_.cub.get(), o.problem_.m, params.infinite_constraint_bound_threshold);
+  log.original_problem_stats.mut() = o.ComputeStats();
+  if (auto r = CheckProblemStats(log.original_problem_stats.get(), true); r.has_value()) return *r;
+  original_bound_norms_ = BoundNormsFromProblemStats(log.original_problem_stats.get());
+  callback_ = std::move(callback);
+  log.preprocessed_problem_stats.mut() = ComputeStats();  // the (empty or unused) presolved problem; trivial scaling
+  IterationStats stats;
+  stats.cumulative_time_sec = timer.Get();
+  log.preprocessing_time_sec = stats.cumulative_time_sec.get();
+  // Zero working vectors (:992-995); their recovered image is the presolver's solution.
+  DVec zx(problem_.n > 0 ? problem_.n : 1), zy(problem_.m > 0 ? problem_.m : 1);
+  zx.Zero(ws_.stream);
+  zy.Zero(ws_.stream);
+  ConvergenceInformation ci;
+  InfeasibilityInformation ii;
+  ComputeConvergenceAndInfeasibility(params, zx.get(), zy.get(), zx.get(), zy.get(), POINT_TYPE_PRESOLVER_SOLUTION, &ci, &ii, nullptr);
+  stats.convergence_information.push_back(ci);
+  stats.infeasibility_information.push_back(ii);
+  auto earned = CheckIterateTerminationCriteria(params.termination_criteria.get(), stats, original_bound_norms_, false);
+  if (!earned.has_value()) earned = CheckSimpleTerminationCriteria(params.termination_criteria.get(), stats, interrupt);
+  int reason;
+  if (earned.has_value() && (earned->reason == TERMINATION_REASON_OPTIMAL || earned->reason == TERMINATION_REASON_PRIMAL_INFEASIBLE ||
+                             earned->reason == TERMINATION_REASON_DUAL_INFEASIBLE)) {
+    reason = earned->reason;
+  } else if (presolve_reason == TERMINATION_REASON_OPTIMAL) {
+    reason = TERMINATION_REASON_NUMERICAL_ERROR;
+    std::fputs("WARNING: Presolve claimed to solve the LP optimally but the solution doesn't satisfy the optimality criteria.\n", stderr);
+  } else {
+    reason = presolve_reason;
+  }
+  log.iteration_count = stats.iteration_number;
+  log.termination_reason = reason;
+  log.solution_type = POINT_TYPE_PRESOLVER_SOLUTION;
+  log.solve_time_sec = stats.cumulative_time_sec.get();
+  log.solution_stats.mut() = stats;
+  return ConstructOriginalSolverResult(params, zx.get(), zy.get(), std::move(log));
+}
+
 // pdhg.cc:1568-1643.
 SolverResult PreprocessSolver::ConstructOriginalSolverResult(const PrimalDualHybridGradientParams& params, const double* x, const double* y, SolveLog log) {
+  if (presolve_ != nullptr) {
+    // :1571-1585: recover the original solution; the reduced costs are computed with respect to the original
+    // problem.  The original's PreprocessSolver does both (its scaling vectors are all ones).
+    RecoverOriginalOnDevice(x, y);
+    PreprocessSolver& o = *presolve_->original;
+    o.set_solution_sink(sink_);
+    o.callback_ = callback_;
+    o.original_bound_norms_ = original_bound_norms_;
+    return o.ConstructOriginalSolverResult(params, presolve_->x.get(), presolve_->y.get(), std::move(log));
+  }
   DeviceProblem& p = problem_;
   SolverResult result;
   const bool zero_objective = log.termination_reason == TERMINATION_REASON_PRIMAL_INFEASIBLE;

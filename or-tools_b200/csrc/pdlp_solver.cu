@@ -84,7 +84,7 @@ void Solver::RunDeviceIterations(int target_iteration) {
   const TerminationCriteria& tc = params_.termination_criteria.get();
   // The work counted against kkt_matrix_pass_limit includes polishing work; the host
   // re-checks exactly at the next event, the device only needs a conservative stop.
-  host_.kkt_pass_limit = tc.kkt_matrix_pass_limit;
+  host_.kkt_pass_limit = tc.kkt_matrix_pass_limit - kkt_passes_from_polishing_;  // the reference tests full_work_stats (:2147), which includes polishing work
   PushState();
   const bool mp = params_.linesearch_rule == MALITSKY_POCK_LINESEARCH_RULE;
   const bool constant = params_.linesearch_rule == CONSTANT_STEP_SIZE_RULE;
@@ -98,7 +98,9 @@ void Solver::RunDeviceIterations(int target_iteration) {
     if (host_.active == 0) break;
     if (++guard > 100000) throw std::runtime_error("pdlp_b200: device iteration loop made no progress");
   }
-  if (host_.iterations_completed > iterations_completed_) have_delta_ = true;
+  // A delta exists once a step has been ACCEPTED (a forced numerical termination without an accepted step
+  // advances the count but leaves no new delta).
+  if (host_.iterations_completed - (host_.force_numerical != 0 && host_.accepted_last == 0 ? 1 : 0) > iterations_completed_) have_delta_ = true;
   iterations_completed_ = host_.iterations_completed;
 }
 
@@ -378,6 +380,7 @@ Solver::Outcome Solver::Solve(IterationType type, const InterruptFlag* interrupt
   host_.iterations_completed = 0;
   iterations_completed_ = 0;
   IterationStats work_from_feasibility_polishing = WorkFromFeasibilityPolishing(log);
+  kkt_passes_from_polishing_ = work_from_feasibility_polishing.cumulative_kkt_matrix_passes;
   cudaEvent_t ev0, ev1;
   PDLP_CUDA_CHECK(cudaEventCreate(&ev0));
   PDLP_CUDA_CHECK(cudaEventCreate(&ev1));
@@ -400,6 +403,7 @@ Solver::Outcome Solver::Solve(IterationType type, const InterruptFlag* interrupt
       if (polished.has_value()) return finish(std::move(*polished));
       next_feasibility_polishing_iteration *= 2;
       work_from_feasibility_polishing = WorkFromFeasibilityPolishing(log);
+      kkt_passes_from_polishing_ = work_from_feasibility_polishing.cumulative_kkt_matrix_passes;
     }
     const int target = NextEventIteration(iterations_completed_, type, next_feasibility_polishing_iteration);
     const double t0 = timer_.Get();

@@ -198,6 +198,9 @@ __global__ void __launch_bounds__(kBlock) decide_adaptive_kernel(StepState* st, 
     s.active = 0;
     if (!constant_step) s.num_rejected_steps += s.inner - 1;
     s.inner = 0;
+    // The reference's `for (iterations_completed_ = 0;; ++iterations_completed_)` (:2716) counts the
+    // iteration whose step forced numerical termination before the final check sees it.
+    s.iterations_completed += 1;
     *st = s;
     return;
   }
@@ -240,6 +243,7 @@ __global__ void __launch_bounds__(kBlock) decide_adaptive_kernel(StepState* st, 
         s.active = 0;
         s.num_rejected_steps += s.inner - 1;
         s.inner = 0;
+        s.iterations_completed += 1;  // counted by the reference's for loop (:2716)
       }
     }
   }
@@ -359,6 +363,7 @@ __global__ void __launch_bounds__(kBlock) decide_mp_kernel(StepState* st, const 
       s.num_rejected_steps += s.inner;
       s.inner = 0;
       s.mp_tau = -1.0;
+      s.iterations_completed += 1;  // counted by the reference's for loop (:2716)
     }
   }
   *st = s;

@@ -30,7 +30,8 @@ def test_trial_steps_match_the_restated_adaptive_rule(seed, qp_case, step, w):
     finally:
         dp.close()
     assert (st["iterations_completed"], st["num_rejected_steps"]) == (want["completed"], want["rejected"])
-    assert st["iterations_completed"] + st["num_rejected_steps"] == trials
+    assert st["iterations_completed"] + st["num_rejected_steps"] + st["pending_rejected_steps"] == trials == st["total_trials"]
+    assert not st["forced_numerical_termination"]
     np.testing.assert_allclose(x, want["x"], rtol=1e-9, atol=1e-9)
     np.testing.assert_allclose(y, want["y"], rtol=1e-9, atol=1e-9)
     assert abs(st["step_size"] - want["step"]) <= 1e-9 * want["step"]
