@@ -215,6 +215,8 @@ class Solver {
   int agreed_seconds_iteration_ = 0;
   InterruptFlag agreed_interrupt_;
   double device_loop_seconds_ = 0.0;
+  // PDLP_B200_DEBUG_TIMING: host wall time of the loop by phase (every phase ends in a device sync), printed at the end of Solve().
+  struct { double steps = 0, restart_choice = 0, termination = 0, apply_restart = 0; int events = 0, checks = 0, restarts = 0, bounds = 0, tr_passes = 0; } phase_;
   // Holders for the result of feasibility polishing (device vectors must outlive Solve()).
   DVec polished_x_, polished_y_;
 };

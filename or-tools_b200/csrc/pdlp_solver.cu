@@ -5,6 +5,8 @@
 // (termination check, major iteration, artificial restart, work limit); between events
 // the device runs trial steps back to back without a host round trip.
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 
 #include "pdlp_driver.h"
 #include "pdlp_logging.h"
@@ -144,18 +146,24 @@ double Solver::DistanceTraveledFromLastStart(const double* x, const double* y) {
 
 Solver::Bounds Solver::BoundsAtCurrent() {  // pdhg.cc:1806-1816
   const double radius = DistanceTraveledFromLastStart(X(), Y());
+  int tr_passes = 0;
   const LocalizedBounds b = ComputeLocalizedLagrangianBounds(ws_, problem_, X(), Y(), Kty(), host_.primal_weight, radius,
                                                              params_.use_diagonal_qp_trust_region_solver,
-                                                             params_.diagonal_qp_trust_region_solver_tolerance, nullptr);
+                                                             params_.diagonal_qp_trust_region_solver_tolerance, &tr_passes);
+  phase_.bounds += 1;
+  phase_.tr_passes += tr_passes;
   return {b.lagrangian_value, b.lower_bound, b.upper_bound, b.radius};
 }
 Solver::Bounds Solver::BoundsAtAverage() {  // pdhg.cc:1818-1834
   const double* xa = PrimalAverage();
   const double* ya = DualAverage();
   const double radius = DistanceTraveledFromLastStart(xa, ya);
+  int tr_passes = 0;
   const LocalizedBounds b = ComputeLocalizedLagrangianBounds(ws_, problem_, xa, ya, nullptr, host_.primal_weight, radius,
                                                              params_.use_diagonal_qp_trust_region_solver,
-                                                             params_.diagonal_qp_trust_region_solver_tolerance, nullptr);
+                                                             params_.diagonal_qp_trust_region_solver_tolerance, &tr_passes);
+  phase_.bounds += 1;
+  phase_.tr_passes += tr_passes;
   return {b.lagrangian_value, b.lower_bound, b.upper_bound, b.radius};
 }
 
@@ -309,7 +317,11 @@ std::optional<Solver::Outcome> Solver::MajorIterationAndTerminationCheck(Iterati
   }
   const int major_iteration_cycle = iterations_completed_ % params_.major_iteration_frequency;
   const bool is_major_iteration = major_iteration_cycle == 0 && iterations_completed_ > 0;
+  const double t_begin = timer_.Get();
   const int restart = force_numerical_termination ? static_cast<int>(RESTART_CHOICE_NO_RESTART) : ChooseRestartToApply(is_major_iteration);
+  const double t_chosen = timer_.Get();
+  phase_.events += 1;
+  phase_.restart_choice += t_chosen - t_begin;
   IterationStats stats = CreateSimpleIterationStats(restart);
   const IterationStats full_work_stats = AddWorkStats(stats, work_from_feasibility_polishing);
   const bool check_termination = major_iteration_cycle % params_.termination_check_frequency == 0 ||
@@ -330,6 +342,8 @@ std::optional<Solver::Outcome> Solver::MajorIterationAndTerminationCheck(Iterati
         params_, force_numerical_termination, X(), Y(), has_avg ? it_.avg_x.get() : nullptr, has_avg ? it_.avg_y.get() : nullptr, dx, dy,
         it_.x_start.get(), it_.y_start.get(), interrupt, type, full_work_stats, stats);
     if (params_.record_iteration_stats) log.iteration_stats.push_back(stats);
+    phase_.checks += 1;
+    phase_.termination += timer_.Get() - t_chosen;
     if (maybe_reason.has_value()) {
       const IterationStats terminating_full_stats = AddWorkStats(stats, work_from_feasibility_polishing);
       return PickSolutionAndConstructOutcome(terminating_full_stats, maybe_reason->reason, maybe_reason->type, std::move(log));
@@ -337,7 +351,13 @@ std::optional<Solver::Outcome> Solver::MajorIterationAndTerminationCheck(Iterati
   } else if (params_.record_iteration_stats) {
     log.iteration_stats.push_back(stats);
   }
+  const double t_checked = timer_.Get();
   ApplyRestartChoice(restart);
+  if (restart == RESTART_CHOICE_WEIGHTED_AVERAGE_RESET || restart == RESTART_CHOICE_RESTART_TO_AVERAGE) {
+    ws_.Sync();
+    phase_.restarts += 1;
+    phase_.apply_restart += timer_.Get() - t_checked;
+  }
   return std::nullopt;
 }
 
@@ -393,6 +413,12 @@ Solver::Outcome Solver::Solve(IterationType type, const InterruptFlag* interrupt
     device_loop_seconds_ = ms * 1e-3;
     cudaEventDestroy(ev0);
     cudaEventDestroy(ev1);
+    if (std::getenv("PDLP_B200_DEBUG_TIMING") != nullptr) {
+      std::fprintf(stderr, "pdlp_b200 loop phases: %d iterations, %lld trials, steps %.4f s; %d events: restart choice %.4f s (%d bounds, %d trust-region passes), "
+                   "%d termination checks %.4f s, %d restarts applied %.4f s; device loop %.4f s\n", iterations_completed_, static_cast<long long>(host_.total_trials),
+                   phase_.steps, phase_.events, phase_.restart_choice, phase_.bounds, phase_.tr_passes, phase_.checks, phase_.termination, phase_.restarts,
+                   phase_.apply_restart, device_loop_seconds_);
+    }
     return o;
   };
   for (;;) {
@@ -411,6 +437,7 @@ Solver::Outcome Solver::Solve(IterationType type, const InterruptFlag* interrupt
     RunDeviceIterations(target);
     // Keep the polling interval near 20 ms of work when a time limit or interrupt is live.
     const double dt = timer_.Get() - t0;
+    phase_.steps += dt;
     const int done = iterations_completed_ - before;
     if (done > 0 && dt > 0.0 && !pre_->sharded()) {
       const double per_iteration = dt / done;

@@ -218,8 +218,9 @@ def transportation_lp(num_sources, num_sinks, seed=0, first_source=0, last_sourc
         num_rows = S + D
     vals = np.ones((n, 2))
     K = _csc_from_columns(num_rows, n, rows, vals, 2)
-    cost_rng = np.random.Generator(np.random.PCG64([seed, 1]))
-    cost = cost_rng.uniform(1.0, 100.0, S * D)[first_source * D: last_source * D] if block * D < 5e7 else cost_rng.uniform(1.0, 100.0, n)
+    # The block's slice of ONE cost stream of S D draws (one 64-bit output per double), so that every
+    # sharding of the same (S, D, seed) is the same LP and no rank generates the other blocks' costs.
+    cost = np.random.Generator(np.random.PCG64([seed, 1]).advance(first_source * D)).uniform(1.0, 100.0, n)
     qp = QuadraticProgram()
     qp.constraint_matrix = K
     if local_rows:
