@@ -283,7 +283,27 @@ def relative_kkt(stats, eps, bound_norm, objective_norm):
             "objective_gap": gap / (eps + eps * (abs(stats["primal_objective"]) + abs(stats["dual_objective"])))}
 
 
-def parity_check(qp, name, x, y, device_objective, iterations, world):
+def compare_with_n1(out, name, scale, world, iterations, objective, eps):
+    """N = 1: remembers (iterations, objective) of this workload in the temp directory.  N > 1: adds out["vs_n1"] when this
+    box has run the N = 1 solve of the same LP; returns False when the two objectives differ by more than 4 eps (two
+    eps-optimal points of one LP)."""
+    ref_path = os.path.join(tempfile.gettempdir(), f"pdlp_b200_bench_n1_{name}_s{scale:g}.json")
+    if world == 1:
+        try:
+            with open(ref_path, "w") as f:
+                json.dump({"iterations": int(iterations), "primal_objective": objective}, f)
+        except OSError:
+            pass
+    elif os.path.exists(ref_path):
+        with open(ref_path) as f:
+            ref = json.load(f)
+        out["vs_n1"] = {"iterations_n1": ref["iterations"], "iteration_ratio": iterations / max(1, ref["iterations"]),
+                        "objective_rel_diff": abs(objective - ref["primal_objective"]) / (1.0 + abs(objective))}
+        return out["vs_n1"]["objective_rel_diff"] <= 4 * eps
+    return True
+
+
+def parity_check(qp, name, scale, x, y, device_objective, iterations, world):
     """The oracle's view of the device's solution (rank 0, whole problem): ComputeConvergenceInformation
     (iteration_stats.cc:349-419) at (x, y) on the ORIGINAL problem; every relative KKT error must be
     within the requested eps (1e-6 relative slack for the different summation order), the device's own
@@ -314,21 +334,63 @@ def parity_check(qp, name, x, y, device_objective, iterations, world):
         out["objective_vs_planted_rel"] = abs(stats["primal_objective"] - opt) / (1.0 + abs(opt))
         out["objective_vs_planted_tolerance"] = 20 * eps
         ok = ok and out["objective_vs_planted_rel"] <= 20 * eps
-    ref_path = os.path.join(tempfile.gettempdir(), f"pdlp_b200_bench_n1_{name}.json")
-    if world == 1:
-        try:
-            with open(ref_path, "w") as f:
-                json.dump({"iterations": int(iterations), "primal_objective": stats["primal_objective"]}, f)
-        except OSError:
-            pass
-    elif os.path.exists(ref_path):
-        with open(ref_path) as f:
-            ref = json.load(f)
-        out["vs_n1"] = {"iterations_n1": ref["iterations"], "iteration_ratio": iterations / max(1, ref["iterations"]),
-                        "objective_rel_diff": abs(stats["primal_objective"] - ref["primal_objective"]) / scale}
-        ok = ok and out["vs_n1"]["objective_rel_diff"] <= 4 * eps  # two eps-optimal points of the same LP
+    ok = compare_with_n1(out, name, scale, world, iterations, stats["primal_objective"], eps) and ok
     out["ok"] = bool(ok)
     out["seconds"] = time.time() - t0
+    return out
+
+
+def transportation_parity(qp, x, y, local_rows, device_objective, iterations, reduce_sum):
+    """ComputeConvergenceInformation (iteration_stats.cc:349-419) restated in numpy for the structure of
+    the transportation LP (synthetic.transportation_lp): K x is a row sum and a column sum of x seen as a
+    (sources, sinks) table, K^T y is y_supply[s] + y_demand[d].  For the c5 lines whose matrix never
+    exists on one host (sharded) or is too large for a second copy in the oracle (1e9 nnz): every rank
+    passes its own block (whole sources; `local_rows` layout: sink rows first, then its supply rows) and
+    `reduce_sum` adds small vectors over the ranks.  tests/test_bench_helpers.py pins it to the oracle."""
+    cub = np.asarray(qp.constraint_upper_bounds)
+    m, n = len(cub), len(x)
+    # Rows: local_rows -> [D sink rows, the block's supply rows]; whole problem -> [S supply rows, D sink rows].  The sink rows are the equalities.
+    finite = np.isfinite(np.asarray(qp.constraint_lower_bounds))
+    if local_rows:
+        D = int(finite.sum())  # the sink rows are the equalities
+        nblock = m - D
+        demand, supply = cub[:D], cub[D:]
+        y_d, y_s = y[:D], y[D:]
+    else:
+        nblock = int((~finite).sum())
+        D = m - nblock
+        supply, demand = cub[:nblock], cub[nblock:]
+        y_s, y_d = y[:nblock], y[nblock:]
+    assert D * nblock == n, (D, nblock, n, m)
+    X = np.asarray(x).reshape(nblock, D)
+    c = np.asarray(qp.objective_vector).reshape(nblock, D)
+    sink_activity = reduce_sum(X.sum(axis=0))
+    supply_violation = np.maximum(X.sum(axis=1) - supply, 0.0)
+    # Reduced costs c - K^T y; x >= 0 only: a negative reduced cost is dual residual, a positive one pairs with the bound 0.
+    dual_res2 = 0.0
+    chunk = max(1, (1 << 24) // max(1, D))
+    for a in range(0, nblock, chunk):
+        r = c[a:a + chunk] - y_d[None, :] - y_s[a:a + chunk, None]
+        dual_res2 += float(np.square(np.minimum(r, 0.0)).sum())
+    # Supply rows have no lower bound: a positive dual there makes the dual objective -inf (iteration_stats.cc:294-316); PDHG
+    # iterates are projected onto y_s <= 0, so it does not occur at a solver's point.
+    sums = reduce_sum(np.array([float(np.square(supply_violation).sum()), dual_res2, float((c * X).sum()), float((supply * np.minimum(y_s, 0.0)).sum()),
+                                float(np.square(supply).sum()), float(np.square(c).sum())]))
+    primal_res = math.sqrt(sums[0] + float(np.square(sink_activity - demand).sum()))
+    dual_res = math.sqrt(sums[1])
+    primal_obj = sums[2]
+    dual_obj = sums[3] + float(demand @ y_d)
+    if reduce_sum(np.array([float((y_s > 0.0).sum())]))[0] > 0:
+        dual_obj = -math.inf
+    eps = 1e-4
+    bound_norm = math.sqrt(sums[4] + float(np.square(demand).sum()))
+    ratios = relative_kkt({"primal_objective": primal_obj, "dual_objective": dual_obj, "l2_primal_residual": primal_res, "l2_dual_residual": dual_res}, eps,
+                          bound_norm, math.sqrt(sums[5]))
+    out = {"checker": "numpy restatement of ComputeConvergenceInformation on the transportation structure (row / column sums of the (sources, sinks) table), "
+                      "each rank its own block, pinned to the CPU oracle by tests/test_bench_helpers.py", "eps": eps, "relative_kkt_over_eps": ratios,
+           "checker_primal_objective": primal_obj, "checker_dual_objective": dual_obj, "device_primal_objective": device_objective, "iterations": int(iterations)}
+    out["objective_vs_checker_rel"] = abs(device_objective - primal_obj) / (1.0 + abs(primal_obj))
+    out["ok"] = bool(all(v <= 1.0 + 1e-6 for v in ratios.values()) and out["objective_vs_checker_rel"] <= 1e-9)
     return out
 
 
@@ -527,15 +589,21 @@ def main():
                 xs = np.concatenate([q[0] for q in parts])
                 ys = sharing.gather([q[1] for q in parts])
                 check_qp = whole_qp
-            if rank == 0 and (not sharded or whole_qp is not None) and len(ci):
-                parity = parity_check(check_qp, name, xs, ys, ci[0].primal_objective, its, world)
-            elif rank == 0:
-                parity = {"ok": None, "why": "the whole problem does not exist on one host (c5 blocks are generated per rank); solver-reported statistics only",
-                          "device_primal_objective": ci[0].primal_objective if len(ci) else None,
-                          "device_relative_kkt_over_eps": relative_kkt({"primal_objective": ci[0].primal_objective, "dual_objective": ci[0].dual_objective,
-                                                                        "l2_primal_residual": ci[0].l2_primal_residual, "l2_dual_residual": ci[0].l2_dual_residual},
-                                                                       workload_eps(name), result.solve_log.original_problem_stats.combined_bounds_l2_norm,
-                                                                       result.solve_log.original_problem_stats.objective_vector_l2_norm) if len(ci) else None}
+            structure_check = name == "c5" and (sharded or args.scale > 2) and len(ci) > 0
+            if structure_check:
+                # Collective: every rank checks its own block; small vectors are added over the ranks.
+                def reduce_sum(v):
+                    if world == 1:
+                        return v
+                    t = torch.from_numpy(np.ascontiguousarray(v, dtype=np.float64)).cuda()
+                    dist.all_reduce(t)
+                    return t.cpu().numpy()
+                t_check = time.time()
+                parity = transportation_parity(qp, xs, ys, sharded, ci[0].primal_objective, its, reduce_sum)
+                parity["ok"] = bool(compare_with_n1(parity, name, args.scale, world, its, parity["checker_primal_objective"], parity["eps"]) and parity["ok"])
+                parity["seconds"] = time.time() - t_check
+            elif rank == 0 and (not sharded or whole_qp is not None) and len(ci):
+                parity = parity_check(check_qp, name, args.scale, xs, ys, ci[0].primal_objective, its, world)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:

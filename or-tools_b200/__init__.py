@@ -118,6 +118,8 @@ _lib.pdlp_b200_solve.argtypes = [
     ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_size_t), ctypes.POINTER(_CCounters),
 ]
 _lib.pdlp_b200_solve_sharded.argtypes = [ctypes.POINTER(_CProblem), ctypes.POINTER(_CShard)] + _lib.pdlp_b200_solve.argtypes[1:]
+# (original, presolved or NULL, presolve_status, postsolve, postsolve_user) + the tail of pdlp_b200_solve.
+_lib.pdlp_b200_solve_presolved.argtypes = [ctypes.POINTER(_CProblem), ctypes.POINTER(_CProblem), ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p] + _lib.pdlp_b200_solve.argtypes[1:]
 _lib.pdlp_b200_problem_create_sharded.argtypes = [ctypes.POINTER(_CProblem), ctypes.POINTER(_CShard), ctypes.c_int, ctypes.POINTER(ctypes.c_void_p)]
 _lib.pdlp_b200_unique_id.argtypes = [ctypes.c_void_p]
 _lib.pdlp_b200_validate_params.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_void_p)]

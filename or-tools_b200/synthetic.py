@@ -12,8 +12,10 @@ INF = np.inf
 
 def _csc_from_columns(m, n, rows, vals, per_col):
     """rows/vals: (n, per_col) arrays, rows sorted inside each column."""
-    indptr = np.arange(0, n * per_col + 1, per_col, dtype=np.int64)
-    return sp.csc_matrix((vals.reshape(-1), rows.reshape(-1).astype(np.int64), indptr), shape=(m, n))
+    # 32-bit indices where they fit (scipy's own choice; the 1e9-nnz LP then needs 6 GB of index arrays instead of 12).
+    idx = np.int32 if max(m, n * per_col) < 2 ** 31 else np.int64
+    indptr = np.arange(0, n * per_col + 1, per_col, dtype=idx)
+    return sp.csc_matrix((vals.reshape(-1), rows.reshape(-1).astype(idx, copy=False), indptr), shape=(m, n))
 
 
 def random_sparse_lp(m, n, nnz_per_col=5, seed=0, equality_fraction=0.5, qp_diagonal=False):
@@ -208,14 +210,19 @@ def transportation_lp(num_sources, num_sinks, seed=0, first_source=0, last_sourc
     last_source = S if last_source is None else last_source
     block = last_source - first_source
     n = block * D
-    s_idx = np.repeat(np.arange(first_source, last_source, dtype=np.int64), D)
-    d_idx = np.tile(np.arange(D, dtype=np.int64), block)
+    # Row pairs of every column, written in place (no index temporaries of the matrix's size).
+    rows = np.empty((block, D, 2), dtype=np.int32 if S + D < 2 ** 31 else np.int64)
+    sources = np.arange(first_source, last_source, dtype=rows.dtype)
+    sinks = np.arange(D, dtype=rows.dtype)
     if local_rows:
-        rows = np.stack([d_idx, D + (s_idx - first_source)], axis=1)
+        rows[:, :, 0] = sinks[None, :]
+        rows[:, :, 1] = (D + (sources - first_source))[:, None]
         num_rows = D + block
     else:
-        rows = np.stack([s_idx, S + d_idx], axis=1)
+        rows[:, :, 0] = sources[:, None]
+        rows[:, :, 1] = (S + sinks)[None, :]
         num_rows = S + D
+    rows = rows.reshape(n, 2)
     vals = np.ones((n, 2))
     K = _csc_from_columns(num_rows, n, rows, vals, 2)
     # The block's slice of ONE cost stream of S D draws (one 64-bit output per double), so that every
