@@ -81,12 +81,16 @@ typedef struct {
   double upload_seconds;        /* host->device copies, CSR build, communicator set-up */
   int symmetric_buffers;        /* exchange buffers NCCL registered as symmetric windows (0: plain all-reduce) */
   long long peer_exchanges;     /* exchange steps that went through peer memory instead of ncclAllReduce (counted in `collectives` too) */
+  int interrupts_seen_on_device; /* times the step-decision kernel itself saw the interrupt flag and stopped the loop (one GPU) */
 } pdlp_b200_counters;
 
 /* Solves `problem`.
  *   params / params_len   serialized PrimalDualHybridGradientParams (NULL / 0 = defaults)
  *   initial_primal/dual   both NULL (start at zero) or both given (sizes n and m)
- *   interrupt             NULL, or a flag polled during the solve (non-zero = stop)
+ *   interrupt             NULL, or a flag tested after every iteration like the reference's interrupt_solve
+ *                         (termination.cc:178): the step-decision kernel reads a host-mapped copy that the waiting
+ *                         host keeps up to date, so the solve stops within one iteration of the flag being raised
+ *                         (sharded solves: at the next host event, where the ranks agree on it)
  *   device                CUDA device ordinal, or -1 for the current device
  *   primal/dual/reduced   caller-allocated outputs of sizes n, m, n; written only when
  *                         the result carries a solution (*has_solution = 1)

@@ -115,6 +115,7 @@ struct SolveCounters {
   int symmetric_buffers = 0;         // exchange buffers NCCL accepted as symmetric windows (0: plain all-reduce path)
   long long peer_exchanges = 0;      // exchange steps through peer memory (pdlp_peer.cuh) instead of ncclAllReduce
   double upload_seconds = 0.0;       // host -> device copies, CSR build, communicator set-up (before preprocessing)
+  int interrupts_seen_on_device = 0; // times the decision kernel stopped the loop on the interrupt flag (one GPU; pdlp_step_state.h)
 };
 const SolveCounters& LastSolveCounters();
 

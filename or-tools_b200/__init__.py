@@ -89,6 +89,7 @@ class _CCounters(ctypes.Structure):
         ("upload_seconds", ctypes.c_double),
         ("symmetric_buffers", ctypes.c_int),
         ("peer_exchanges", ctypes.c_longlong),
+        ("interrupts_seen_on_device", ctypes.c_int),
     ]
 
 

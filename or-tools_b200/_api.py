@@ -259,7 +259,7 @@ def primal_dual_hybrid_gradient(qp, params, initial_solution=None, interrupt_sol
     _last_counters.clear()
     _last_counters.update(
         kernel_launches=counters.kernel_launches, trial_steps=counters.trial_steps, setup_seconds=counters.setup_seconds,
-        loop_seconds=counters.loop_seconds, device_loop_seconds=counters.device_loop_seconds, collectives=counters.collectives, upload_seconds=counters.upload_seconds, symmetric_buffers=counters.symmetric_buffers, peer_exchanges=counters.peer_exchanges,
+        loop_seconds=counters.loop_seconds, device_loop_seconds=counters.device_loop_seconds, collectives=counters.collectives, upload_seconds=counters.upload_seconds, symmetric_buffers=counters.symmetric_buffers, peer_exchanges=counters.peer_exchanges, interrupts_seen_on_device=counters.interrupts_seen_on_device,
     )
     return result
 

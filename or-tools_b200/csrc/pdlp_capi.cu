@@ -437,6 +437,7 @@ static pdlp_b200_status SolveCommon(const pdlp_b200_problem* problem, const pdlp
       counters->upload_seconds = c.upload_seconds;
       counters->symmetric_buffers = c.symmetric_buffers;
       counters->peer_exchanges = c.peer_exchanges;
+      counters->interrupts_seen_on_device = c.interrupts_seen_on_device;
     }
     return PDLP_B200_OK;
   });

@@ -159,7 +159,12 @@ class Solver {
     const double* y = nullptr;
   };
   Outcome Solve(IterationType type, const InterruptFlag* interrupt, SolveLog log);
+  ~Solver();
+  Solver(const Solver&) = delete;
+  Solver& operator=(const Solver&) = delete;
   long long TrialSteps() const { return host_.total_trials; }
+  // Times the device-resident loop stopped because the decision kernel saw the interrupt flag.
+  int InterruptsSeenOnDevice() const { return interrupts_seen_on_device_; }
   double DeviceLoopSeconds() const { return device_loop_seconds_; }
 
  private:
@@ -215,6 +220,14 @@ class Solver {
   int agreed_seconds_iteration_ = 0;
   InterruptFlag agreed_interrupt_;
   double device_loop_seconds_ = 0.0;
+  // Per-iteration interrupt (termination.cc:178; one GPU): the caller's flag lives in memory the device cannot be
+  // assumed to read, so the solver owns a host-mapped pinned int that the decision kernel reads after every accepted
+  // step; the host copies the caller's flag into it while it waits for the device (PullState).
+  void EnableDeviceInterrupt(const InterruptFlag* interrupt);
+  const InterruptFlag* interrupt_ = nullptr;
+  int* mapped_interrupt_ = nullptr;
+  cudaEvent_t pulled_ = nullptr;
+  int interrupts_seen_on_device_ = 0;
   // PDLP_B200_DEBUG_TIMING: host wall time of the loop by phase (every phase ends in a device sync), printed at the end of Solve().
   struct { double steps = 0, restart_choice = 0, termination = 0, apply_restart = 0; int events = 0, checks = 0, restarts = 0, bounds = 0, tr_passes = 0; } phase_;
   // Holders for the result of feasibility polishing (device vectors must outlive Solve()).

@@ -351,6 +351,7 @@ SolverResult PreprocessSolver::PreprocessAndSolve(const PrimalDualHybridGradient
   g_last_counters.symmetric_buffers = comm_.symmetric_buffers();
   g_last_counters.peer_exchanges = comm_.peer_exchanges();
   g_last_counters.trial_steps = solver.TrialSteps();
+  g_last_counters.interrupts_seen_on_device = solver.InterruptsSeenOnDevice();
   g_last_counters.device_loop_seconds = solver.DeviceLoopSeconds();
   g_last_counters.setup_seconds = result.solve_log.preprocessing_time_sec;
   g_last_counters.loop_seconds = result.solve_log.solve_time_sec - result.solve_log.preprocessing_time_sec;

@@ -6,7 +6,9 @@
 // the device runs trial steps back to back without a host round trip.
 #include <algorithm>
 #include <cstdio>
+#include <chrono>
 #include <cstdlib>
+#include <thread>
 
 #include "pdlp_driver.h"
 #include "pdlp_logging.h"
@@ -74,7 +76,41 @@ void Solver::PushState() {
 }
 void Solver::PullState() {
   PDLP_CUDA_CHECK(cudaMemcpyAsync(&host_, it_.state.get(), sizeof(StepState), cudaMemcpyDeviceToHost, ws_.stream));
-  ws_.Sync();
+  if (mapped_interrupt_ == nullptr) {
+    ws_.Sync();
+    return;
+  }
+  // Wait by polling, forwarding the caller's flag to the one the decision kernel reads.
+  PDLP_CUDA_CHECK(cudaEventRecord(pulled_, ws_.stream));
+  for (;;) {
+    const cudaError_t e = cudaEventQuery(pulled_);
+    if (e == cudaSuccess) break;
+    if (e != cudaErrorNotReady) PDLP_CUDA_CHECK(e);
+    if (interrupt_->IsSet()) *reinterpret_cast<volatile int*>(mapped_interrupt_) = 1;
+    std::this_thread::sleep_for(std::chrono::microseconds(20));
+  }
+  if (host_.stopped_by_interrupt != 0) interrupts_seen_on_device_ += 1;
+}
+
+void Solver::EnableDeviceInterrupt(const InterruptFlag* interrupt) {
+  interrupt_ = interrupt;
+  if (interrupt == nullptr || pre_->sharded()) return;  // sharded: all ranks must stop at the same iteration, agreed on at host events
+  if (mapped_interrupt_ == nullptr) {
+    PDLP_CUDA_CHECK(cudaHostAlloc(reinterpret_cast<void**>(&mapped_interrupt_), sizeof(int), cudaHostAllocMapped));
+    PDLP_CUDA_CHECK(cudaEventCreateWithFlags(&pulled_, cudaEventDisableTiming));
+  }
+  *mapped_interrupt_ = 0;
+  int* device_view = nullptr;
+  PDLP_CUDA_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&device_view), mapped_interrupt_, 0));
+  host_.interrupt_flag = device_view;
+}
+
+Solver::~Solver() {
+  if (mapped_interrupt_ != nullptr) {
+    cudaStreamSynchronize(ws_.stream);  // no kernel may still read the flag
+    cudaFreeHost(mapped_interrupt_);
+  }
+  if (pulled_ != nullptr) cudaEventDestroy(pulled_);
 }
 
 // Runs trial steps on the device until iterations_completed reaches the target, the
@@ -83,6 +119,8 @@ void Solver::RunDeviceIterations(int target_iteration) {
   host_.target_iteration = target_iteration;
   host_.active = 1;
   host_.force_numerical = 0;
+  host_.stopped_by_interrupt = 0;
+  if (mapped_interrupt_ != nullptr) *reinterpret_cast<volatile int*>(mapped_interrupt_) = interrupt_->IsSet() ? 1 : 0;
   const TerminationCriteria& tc = params_.termination_criteria.get();
   // The work counted against kkt_matrix_pass_limit includes polishing work; the host
   // re-checks exactly at the next event, the device only needs a conservative stop.
@@ -382,7 +420,9 @@ IterationStats Solver::TotalWorkSoFar(const SolveLog& log) const {  // pdhg.cc:2
 Solver::Outcome Solver::Solve(IterationType type, const InterruptFlag* interrupt, SolveLog log) {
   preprocessing_time_sec_ = log.preprocessing_time_sec;
   timer_.Start();
-  poll_always_ = interrupt != nullptr;
+  EnableDeviceInterrupt(interrupt);
+  // One GPU: the decision kernel reads the flag itself, no host event is needed for it.  Sharded: the host polls.
+  poll_always_ = interrupt != nullptr && mapped_interrupt_ == nullptr;
   if (pre_->sharded()) {
     double v = poll_always_ ? 1.0 : 0.0;
     pre_->AgreeOnMax(&v, 1);

@@ -12,6 +12,12 @@ namespace pdlp_b200 {
 namespace {
 
 constexpr double kDivergentMovement = 1.0e100;  // primal_dual_hybrid_gradient.cc:553
+
+// The caller's interrupt flag as the device sees it: one 4-byte read of host-mapped memory by one thread per
+// accepted step (the host forwards the caller's flag into it while it waits for the device, Solver::PullState).
+__host__ __device__ inline bool InterruptRaised(const StepState& s) {
+  return s.interrupt_flag != nullptr && *reinterpret_cast<const volatile int*>(s.interrupt_flag) != 0;
+}
 constexpr int kMaxInnerTrials = 60;             // :2231, :2299
 
 struct OneSum {
@@ -251,6 +257,7 @@ __global__ void __launch_bounds__(kBlock) decide_adaptive_kernel(StepState* st, 
     if (s.iterations_completed >= s.target_iteration) s.active = 0;
     const double passes = s.iterations_completed + s.passes_per_rejected_step * s.num_rejected_steps;
     if (passes >= s.kkt_pass_limit) s.active = 0;
+    if (s.active != 0 && InterruptRaised(s)) { s.active = 0; s.stopped_by_interrupt = 1; }
   }
   *st = s;
 }
@@ -353,6 +360,7 @@ __global__ void __launch_bounds__(kBlock) decide_mp_kernel(StepState* st, const 
     if (s.iterations_completed >= s.target_iteration) s.active = 0;
     const double passes = s.iterations_completed + s.passes_per_rejected_step * s.num_rejected_steps;
     if (passes >= s.kkt_pass_limit) s.active = 0;
+    if (s.active != 0 && InterruptRaised(s)) { s.active = 0; s.stopped_by_interrupt = 1; }
   } else {
     s.mp_new_tau = s.mp_downscaling * s.mp_new_tau;
     s.inner += 1;

@@ -22,7 +22,11 @@ struct StepState {
   int avg_num_terms;
   int first_mp_add_pending;  // Malitsky-Pock: old x must be added to the empty average
   int avg_pending;           // adaptive / constant rule: the accepted iterate has not entered the average yet (applied by the next K1 / K2 or the batch-end flush)
+  int stopped_by_interrupt;   // the decision kernel saw *interrupt_flag != 0 after an accepted step and switched the loop off
   long long total_trials;
+  // Host-mapped pinned flag (termination.cc:178 polls interrupt_solve at every iteration): read by the decision
+  // kernel after every accepted step.  Null when the solve has no interrupt flag or is sharded.
+  const int* interrupt_flag;
   double step_size, primal_weight;
   double avg_weight_sum, avg_weight_sum_dual;  // differ only under Malitsky-Pock (:2260-2272)
   double avg_ratio, avg_ratio_dual;            // w / (W + w) of the pending average update

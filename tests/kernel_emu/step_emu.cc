@@ -36,6 +36,12 @@ int LaunchRows(const Op& op, const RowBlocks& rb, int max_grid, double* partials
 }
 }  // namespace
 
+// The interrupt flag of the step state (pdlp_step_state.h): raised before trial `g_interrupt_at` of the next batch
+// (-1: the batch has no flag), so that the decision kernel's reaction can be followed trial by trial.
+static int g_interrupt_at = -1;
+static int g_interrupt_flag = 0;
+extern "C" void emu_set_interrupt_at(int trial) { g_interrupt_at = trial; }
+
 // x, y: in = start point, out = current iterate after the last accepted step.  q may be null (LP).
 // state_out = {step_size, iterations_completed, num_rejected_steps, last_movement, last_nonlinearity,
 //              avg_weight_sum, active, total_trials}.
@@ -70,6 +76,8 @@ extern "C" int emu_adaptive_trials(int n, int m, const int* csr_ptr, const int* 
   state.mp_tau = -1.0;
   state.mp_new_tau = -1.0;
   StepState* st = &state;
+  g_interrupt_flag = 0;
+  if (g_interrupt_at >= 0) state.interrupt_flag = &g_interrupt_flag;
 
   std::vector<double> part[3] = {std::vector<double>(kMaxGrid * 2), std::vector<double>(kMaxGrid * 2), std::vector<double>(kMaxGrid * 2)};
   double* p0 = part[0].data(); double* p1 = part[1].data(); double* p2 = part[2].data();
@@ -78,6 +86,7 @@ extern "C" int emu_adaptive_trials(int n, int m, const int* csr_ptr, const int* 
   KtyStepOp k3{st, csc_val, csc_idx, yb[0].data(), yb[1].data(), xb[0].data(), xb[1].data(), kty[0].data(), kty[1].data()};
   AverageOp flush{{}, st, xb[0].data(), xb[1].data(), yb[0].data(), yb[1].data(), ax.data(), ay.data(), n, 1};
   for (int t = 0; t < trials; ++t) {
+    if (t == g_interrupt_at) g_interrupt_flag = 1;
     const int g1 = LaunchMap(k1, n, p0);
     const int g2 = LaunchRows(k2, by_row, max_grid, p1);
     const int g3 = LaunchRows(k3, by_col, max_grid, p2);
@@ -94,6 +103,7 @@ extern "C" int emu_adaptive_trials(int n, int m, const int* csr_ptr, const int* 
   state_out[0] = state.step_size; state_out[1] = state.iterations_completed; state_out[2] = state.num_rejected_steps;
   state_out[3] = state.last_movement; state_out[4] = state.last_nonlinearity; state_out[5] = state.avg_weight_sum;
   state_out[6] = state.active; state_out[7] = static_cast<double>(state.total_trials);
+  state_out[8] = state.stopped_by_interrupt;
   return 0;
 }
 
