@@ -6,7 +6,9 @@
 #define PDLP_B200_DRIVER_H_
 
 #include <chrono>
+#include <atomic>
 #include <memory>
+#include <thread>
 
 #include "pdlp_ops.cuh"
 #include "primal_dual_hybrid_gradient.h"
@@ -183,6 +185,7 @@ class Solver {
 
   IterationStats CreateSimpleIterationStats(int restart_used) const;
   double DistanceTraveledFromLastStart(const double* x, const double* y);
+  Bounds BoundsAt(const double* x, const double* y, const double* kty_or_null);
   Bounds BoundsAtCurrent();
   Bounds BoundsAtAverage();
   bool ShouldDoAdaptiveRestartHeuristic(double candidate_normalized_gap) const;
@@ -204,6 +207,7 @@ class Solver {
   StepState host_{};  // mirror of the device state, valid after PullState()
   int iterations_completed_ = 0;
   bool have_delta_ = false;
+  int kty_of_average_at_ = -1;  // iteration at which BoundsAtAverage left K^T y_avg in ws_.scratch_n[1] (-1: not there)
   double normalized_gap_at_last_trial_ = std::numeric_limits<double>::infinity();
   double normalized_gap_at_last_restart_ = std::numeric_limits<double>::infinity();
   double preprocessing_time_sec_ = 0.0;
@@ -222,11 +226,13 @@ class Solver {
   double device_loop_seconds_ = 0.0;
   // Per-iteration interrupt (termination.cc:178; one GPU): the caller's flag lives in memory the device cannot be
   // assumed to read, so the solver owns a host-mapped pinned int that the decision kernel reads after every accepted
-  // step; the host copies the caller's flag into it while it waits for the device (PullState).
+  // step; a watcher thread copies the caller's flag into it for the duration of Solve().
   void EnableDeviceInterrupt(const InterruptFlag* interrupt);
+  void StopWatcher();
   const InterruptFlag* interrupt_ = nullptr;
   int* mapped_interrupt_ = nullptr;
-  cudaEvent_t pulled_ = nullptr;
+  std::thread watcher_;
+  std::atomic<bool> watcher_stop_{false};
   int interrupts_seen_on_device_ = 0;
   // PDLP_B200_DEBUG_TIMING: host wall time of the loop by phase (every phase ends in a device sync), printed at the end of Solve().
   struct { double steps = 0, restart_choice = 0, termination = 0, apply_restart = 0; int events = 0, checks = 0, restarts = 0, bounds = 0, tr_passes = 0; } phase_;

@@ -131,10 +131,11 @@ void ComputeReducedCosts(Workspace& ws, const DeviceProblem& p, const double* x,
 
 // ---- restarts (trust_region.cc:886-1016, sou.cc:446-527) ----
 double SquaredDistance(Workspace& ws, const double* a, const double* b, int64_t count, Side side);
-// Euclidean-norm localized Lagrangian bounds at (x, y).  kty may be null (computed).
+// Euclidean-norm localized Lagrangian bounds at (x, y).  kty may be null (computed).  With a start point the radius is the
+// weighted distance of (x, y) from it (pdhg.cc:1795-1804), reduced inside the gradient passes, and `radius` is ignored.
 LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProblem& p, const double* x, const double* y, const double* kty_or_null,
                                                  double primal_weight, double radius, bool use_diagonal_qp_solver, double diagonal_qp_tolerance,
-                                                 int* tr_passes, bool max_norm = false);
+                                                 int* tr_passes, bool max_norm = false, const double* x_start = nullptr, const double* y_start = nullptr);
 
 // K v from caller-owned device CSR arrays with the work-block table in a static device array
 // (pdlp_noalloc.cu; the kernel side of pdlp_b200_matvec_no_alloc, which has no counterpart in the reference).

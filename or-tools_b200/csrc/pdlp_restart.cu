@@ -31,13 +31,13 @@ struct DeviceRunner {
 
 LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProblem& p, const double* x, const double* y, const double* kty_or_null,
                                                  double primal_weight, double radius, bool use_diagonal_qp_solver, double diagonal_qp_tolerance,
-                                                 int* tr_passes, bool max_norm) {
+                                                 int* tr_passes, bool max_norm, const double* x_start, const double* y_start) {
   const SparseRows& csr = p.K.by_row;
   const RestartProblemView view{csr.val.get(), csr.idx.get(), p.c.get(), p.q_or_null(), p.vlb.get(), p.vub.get(), p.clb.get(), p.cub.get(), p.n, p.m, p.is_lp,
                                 ws.dual_skip_below, ws.scratch_n[0].get(), ws.scratch_m[0].get(), ws.scratch_n[1].get(), ws.scratch_nm[0].get(),
                                 ws.scratch_nm[1].get()};
   DeviceRunner run{ws, p};
-  return LocalizedLagrangianBoundsWith(run, view, x, y, kty_or_null, primal_weight, radius, use_diagonal_qp_solver, diagonal_qp_tolerance, tr_passes, max_norm);
+  return LocalizedLagrangianBoundsWith(run, view, x, y, kty_or_null, primal_weight, radius, use_diagonal_qp_solver, diagonal_qp_tolerance, tr_passes, max_norm, x_start, y_start);
 }
 
 }  // namespace pdlp_b200

@@ -56,19 +56,54 @@ struct OneSumSlot {
   __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
 };
 
+// What the two gradient passes reduce besides the Lagrangian value.  With `crit` set they also do the work of
+// CriticalOp for their half of the joint problem (the gradient entry is in a register there: no second pass over
+// gradient, centre and bounds) and of the first Newton pass of the trust-region step (all sums at step size 0), and
+// with a start point the squared distance to it (DistanceTraveledFromLastStart, pdhg.cc:1795-1804).
+//   slot 0 value   1 squared distance to the start point   2 max |objective| (max)
+//   slot 3 fixed radius^2 at step 0   4 free coefficient at step 0   5 number of entries fixed at step 0
+struct GradientSlots {
+  static constexpr int kNumSlots = 6;
+  __host__ __device__ static constexpr int SlotKindOf(int s) { return s == 2 ? kMax : kSum; }
+};
+struct GradientTotals { double value = 0, distance2 = 0, max_objective = 0, fixed_r2 = 0, free_coef = 0, num_fixed = 0; };
+__host__ __device__ inline void AddCritical(double obj, double w, double center, double lb, double ub, bool counts, double* crit, double* coef, Slots<6>& r) {
+  double cs = INFINITY;
+  if (obj != 0.0) {
+    const double dist = obj > 0.0 ? lb - center : ub - center;
+    cs = -w * dist / obj;
+  }
+  const double a = obj * obj / w;
+  *crit = cs;
+  *coef = a;
+  r.v[2] = fmax(r.v[2], fabs(obj));
+  if (!counts) return;
+  if (cs <= 0.0) { r.v[3] += a * (cs * cs); r.v[5] += 1.0; }
+  else r.v[4] += a;
+}
+
 // ComputeDualGradient (sou.cc:502-527) fused with K x.
-struct DualGradOp : AlwaysActive, OneSumSlot {
+struct DualGradOp : AlwaysActive, GradientSlots {
   const double* val; const int* idx; const double* x;
   const double* y; const double* clb; const double* cub; double* gy;
   int skip_below;
+  const double* y_start;       // null: no distance
+  double* crit; double* coef;  // the dual half of the joint arrays (null: not computed)
+  double w_dual;
   __device__ double Load(int64_t k) const { return val[k] * x[idx[k]]; }
   __device__ double RowInit() const { return 0.0; }
   __device__ double RowAdd(double acc, double staged, int) const { return acc + staged; }
   __device__ double RowMerge(double a, double b) const { return a + b; }
-  __device__ void RowFinish(int i, double kx, Slots<1>& r) const {
-    const double coeff = DualSubgradientCoefficient(clb[i], cub[i], y[i], kx);
-    if (i >= skip_below) r.v[0] += coeff * y[i];
-    gy[i] = coeff - kx;
+  __device__ void RowFinish(int i, double kx, Slots<6>& r) const {
+    const double lb = clb[i], ub = cub[i], yi = y[i];
+    const double coeff = DualSubgradientCoefficient(lb, ub, yi, kx);
+    const bool counts = i >= skip_below;
+    if (counts) r.v[0] += coeff * yi;
+    const double g = coeff - kx;
+    gy[i] = g;
+    if (y_start != nullptr && counts) { const double d = yi - y_start[i]; r.v[1] += d * d; }
+    // The dual entry of the joint problem: objective -g, bounds of the dual variable (JointView).
+    if (crit != nullptr) AddCritical(-g, w_dual, yi, isfinite(ub) ? -INFINITY : 0.0, isfinite(lb) ? INFINITY : 0.0, counts, crit + i, coef + i, r);
   }
 };
 
@@ -84,12 +119,19 @@ __device__ __forceinline__ double PrimalGradAt(double xj, double cj, const doubl
   *value = xj * (g - 0.5 * qx);
   return g;
 }
-struct PrimalGradMapOp : AlwaysActive, OneSumSlot {
+struct PrimalGradMapOp : AlwaysActive, GradientSlots {
   const double* kty; const double* x; const double* c; const double* q; double* gx;
-  __device__ void Apply(int64_t j, Slots<1>& r) const {
+  const double* x_start;       // null: no distance
+  double* crit; double* coef;  // the primal half of the joint arrays (null: not computed)
+  const double* vlb; const double* vub; double w_primal;
+  __device__ void Apply(int64_t j, Slots<6>& r) const {
     double v;
-    gx[j] = PrimalGradAt(x[j], c[j], q, j, kty[j], &v);
+    const double xj = x[j];
+    const double g = PrimalGradAt(xj, c[j], q, j, kty[j], &v);
+    gx[j] = g;
     r.v[0] += v;
+    if (x_start != nullptr) { const double d = xj - x_start[j]; r.v[1] += d * d; }
+    if (crit != nullptr) AddCritical(g, w_primal, xj, vlb[j], vub[j], true, crit + j, coef + j, r);
   }
 };
 
@@ -148,6 +190,24 @@ struct BoundsDeltaOp : AlwaysActive {
   }
 };
 
+// The same two sums from the critical step sizes alone: an entry fixed at its bound (crit <= step) moves by
+// bound - centre = -crit objective / w, a free one by -step objective / w, so objective x movement is
+// -coef min(step, crit) either way; for a dual entry the objective is -gy, hence the sign.  Reads two arrays
+// instead of gradient, centre and both bounds.
+struct RadiusDeltaOp : AlwaysActive {
+  static constexpr int kNumSlots = 2;
+  __host__ __device__ static constexpr int SlotKindOf(int) { return kSum; }
+  const double* crit; const double* coef; double step; int64_t n; int64_t dual_skip_below;
+  __device__ void Apply(int64_t i, Slots<2>& r) const {
+    if (i >= n && i - n < dual_skip_below) return;
+    const double a = coef[i];
+    if (a == 0.0) return;  // objective entry 0: no movement (and crit = inf)
+    const double t = a * fmin(step, crit[i]);
+    if (i < n) r.v[0] -= t;
+    else r.v[1] += t;
+  }
+};
+
 // Diagonal-QP solver pieces (trust_region.cc:615-753).
 __device__ __forceinline__ double ProjectedScaledDifference(const JointView& p, int64_t i, double scaling) {
   const double w = p.Weight(i);
@@ -197,14 +257,22 @@ struct RestartProblemView {
 //   void ColumnDot(y, out)                    out = K^T y (row-stream pass over the CSC copy)
 //   const double* Primal(op, count)           dense pass over this rank's columns
 //   const double* Joint(op, count)            dense pass over (columns, rows)
+// x_start / y_start (both or neither): the radius is the weighted distance of (x, y) from that point
+// (DistanceTraveledFromLastStart, pdhg.cc:1795-1804), reduced inside the two gradient passes; `radius` is then ignored.
 template <class Runner>
 LocalizedBounds LocalizedLagrangianBoundsWith(Runner& run, const RestartProblemView& p, const double* x, const double* y, const double* kty_or_null,
                                               double primal_weight, double radius, bool use_diagonal_qp_solver, double diagonal_qp_tolerance,
-                                              int* tr_passes, bool max_norm = false) {
+                                              int* tr_passes, bool max_norm = false, const double* x_start = nullptr, const double* y_start = nullptr) {
   double* gx = p.gx;
   double* gy = p.gy;
-  double primal_value = 0.0, dual_value = 0.0;
-  if (p.m > 0) dual_value = run.CsrRows(DualGradOp{{}, {}, p.csr_val, p.csr_idx, x, y, p.clb, p.cub, gy, static_cast<int>(p.dual_skip_below)})[0];
+  // The default solver (joint problem, linear-time root search) takes its critical step sizes from the gradient passes.
+  const bool fused = !max_norm && !use_diagonal_qp_solver;
+  auto totals_of = [](const double* h) { return GradientTotals{h[0], h[1], h[2], h[3], h[4], h[5]}; };
+  GradientTotals primal, dual;
+  if (p.m > 0) {
+    dual = totals_of(run.CsrRows(DualGradOp{{}, {}, p.csr_val, p.csr_idx, x, y, p.clb, p.cub, gy, static_cast<int>(p.dual_skip_below), y_start,
+                                            fused ? p.crit + p.n : nullptr, fused ? p.coef + p.n : nullptr, 0.5 / primal_weight}));
+  }
   if (p.n > 0) {
     // When K^T y is not cached it is computed first; the gradient and its value then come
     // from the same kernel either way, so "bounds at the average" and "bounds at the
@@ -215,8 +283,10 @@ LocalizedBounds LocalizedLagrangianBoundsWith(Runner& run, const RestartProblemV
       run.ColumnDot(y, p.kty_scratch);
       kty = p.kty_scratch;
     }
-    primal_value = run.Primal(PrimalGradMapOp{{}, {}, kty, x, p.c, p.q, gx}, p.n)[0];
+    primal = totals_of(run.Primal(PrimalGradMapOp{{}, {}, kty, x, p.c, p.q, gx, x_start, fused ? p.crit : nullptr, fused ? p.coef : nullptr, p.vlb, p.vub, 0.5 * primal_weight}, p.n));
   }
+  const double primal_value = primal.value, dual_value = dual.value;
+  if (x_start != nullptr || y_start != nullptr) radius = std::sqrt((0.5 * primal_weight) * primal.distance2 + (0.5 / primal_weight) * dual.distance2);
   const double lagrangian = primal_value + dual_value;
   const int64_t total = p.n + p.m;
   JointView view{gx, gy, x, y, p.vlb, p.vub, p.clb, p.cub, p.q, p.n, 0.5 * primal_weight, 0.5 / primal_weight, p.dual_skip_below};
@@ -247,13 +317,14 @@ LocalizedBounds LocalizedLagrangianBoundsWith(Runner& run, const RestartProblemV
     return out;
   }
 
-  // SolveTrustRegionStepSize (trust_region.cc:332-449) for a view of the joint index range.
-  auto solve_step = [&](const JointView& v, double target_radius) -> double {
+  // SolveTrustRegionStepSize (trust_region.cc:332-449) for a view of the joint index range.  `first` (the fused path):
+  // the critical step sizes are already in p.crit / p.coef and the sums at step size 0 are known.
+  auto solve_step = [&](const JointView& v, double target_radius, const GradientTotals* first) -> double {
     double step = 0.0;
     if (!(target_radius > 0.0)) return step;
     double* crit = p.crit;
     double* coef = p.coef;
-    const double max_obj = run.Joint(CriticalOp{{}, v, crit, coef}, total)[0];
+    const double max_obj = first != nullptr ? first->max_objective : run.Joint(CriticalOp{{}, v, crit, coef}, total)[0];
     if (!(max_obj > 0.0)) return step;  // every objective entry is zero: step 0 (trust_region.cc:349-358)
     // Root of phi(d) = fixed_r2(d) + d^2 free_coef(d) - r^2 (concave piecewise in d^2) by Newton from
     // the left: from a point left of the root the Newton step lands left of the root again, and
@@ -265,21 +336,28 @@ LocalizedBounds LocalizedLagrangianBoundsWith(Runner& run, const RestartProblemV
     const double r2 = target_radius * target_radius;
     double delta = 0.0, increment = 0.0;
     double prev_fixed = -1.0;
+    bool have_first = first != nullptr;
     for (;;) {
-      RadiusPassOp op{{}, crit, coef, {}, p.n, v.dual_skip_below};
-      static const double kAhead[kRadiusCandidates] = {0.0, 1.0, 3.0, 7.0, 15.0};
-      for (int k = 0; k < kRadiusCandidates; ++k) op.delta[k] = delta + kAhead[k] * increment;
-      const double* h = run.Joint(op, total);
-      ++passes;
-      // Rightmost candidate that is not right of the root (candidate 0 never is).
+      double at, fixed_r2, free_coef, num_fixed;
       int pick = 0;
-      for (int k = 1; k < kRadiusCandidates && increment > 0.0; ++k) {
-        const double d = op.delta[k];
-        const double phi = h[3 * k] + (d * d) * h[3 * k + 1] - r2;
-        if (phi <= 0.0 && d > op.delta[pick]) pick = k;
+      if (have_first) {  // the pass at step size 0 came with the gradients
+        have_first = false;
+        at = 0.0; fixed_r2 = first->fixed_r2; free_coef = first->free_coef; num_fixed = first->num_fixed;
+      } else {
+        RadiusPassOp op{{}, crit, coef, {}, p.n, v.dual_skip_below};
+        static const double kAhead[kRadiusCandidates] = {0.0, 1.0, 3.0, 7.0, 15.0};
+        for (int k = 0; k < kRadiusCandidates; ++k) op.delta[k] = delta + kAhead[k] * increment;
+        const double* h = run.Joint(op, total);
+        ++passes;
+        // Rightmost candidate that is not right of the root (candidate 0 never is).
+        for (int k = 1; k < kRadiusCandidates && increment > 0.0; ++k) {
+          const double d = op.delta[k];
+          const double phi = h[3 * k] + (d * d) * h[3 * k + 1] - r2;
+          if (phi <= 0.0 && d > op.delta[pick]) pick = k;
+        }
+        at = op.delta[pick];
+        fixed_r2 = h[3 * pick]; free_coef = h[3 * pick + 1]; num_fixed = h[3 * pick + 2];
       }
-      const double at = op.delta[pick];
-      const double fixed_r2 = h[3 * pick], free_coef = h[3 * pick + 1], num_fixed = h[3 * pick + 2];
       if (!(free_coef > 0.0)) { step = DBL_MAX; break; }  // trust_region.cc:438-446
       // No breakpoint crossed since the last pass: the Newton point is the exact root.
       if (pick == 0 && num_fixed == prev_fixed) { step = at; break; }
@@ -301,16 +379,20 @@ LocalizedBounds LocalizedLagrangianBoundsWith(Runner& run, const RestartProblemV
     primal_view.part = 1; primal_view.w_primal = 1.0; primal_view.w_dual = 1.0;
     dual_view.part = 2; dual_view.w_primal = 1.0; dual_view.w_dual = 1.0;
     if (p.n > 0) {
-      const double step = solve_step(primal_view, std::sqrt(2.0) * radius / std::sqrt(primal_weight));
+      const double step = solve_step(primal_view, std::sqrt(2.0) * radius / std::sqrt(primal_weight), nullptr);
       primal_delta = run.Joint(BoundsDeltaOp{{}, primal_view, step}, total)[0];
     }
     if (p.m > 0) {
-      const double step = solve_step(dual_view, std::sqrt(2.0) * radius * std::sqrt(primal_weight));
+      const double step = solve_step(dual_view, std::sqrt(2.0) * radius * std::sqrt(primal_weight), nullptr);
       dual_delta = run.Joint(BoundsDeltaOp{{}, dual_view, step}, total)[1];
     }
   } else {
-    const double step = solve_step(view, radius);
-    const double* h = run.Joint(BoundsDeltaOp{{}, view, step}, total);
+    // Shared rows of a sharded solve are replicated: max over ranks took them once, the sums counted them on rank 0.
+    GradientTotals first = primal;
+    first.max_objective = std::max(primal.max_objective, dual.max_objective);
+    first.fixed_r2 += dual.fixed_r2; first.free_coef += dual.free_coef; first.num_fixed += dual.num_fixed;
+    const double step = solve_step(view, radius, &first);
+    const double* h = run.Joint(RadiusDeltaOp{{}, p.crit, p.coef, step, p.n, p.dual_skip_below}, total);
     primal_delta = h[0];
     dual_delta = h[1];
   }

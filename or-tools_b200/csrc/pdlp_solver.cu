@@ -76,41 +76,43 @@ void Solver::PushState() {
 }
 void Solver::PullState() {
   PDLP_CUDA_CHECK(cudaMemcpyAsync(&host_, it_.state.get(), sizeof(StepState), cudaMemcpyDeviceToHost, ws_.stream));
-  if (mapped_interrupt_ == nullptr) {
-    ws_.Sync();
-    return;
-  }
-  // Wait by polling, forwarding the caller's flag to the one the decision kernel reads.
-  PDLP_CUDA_CHECK(cudaEventRecord(pulled_, ws_.stream));
-  for (;;) {
-    const cudaError_t e = cudaEventQuery(pulled_);
-    if (e == cudaSuccess) break;
-    if (e != cudaErrorNotReady) PDLP_CUDA_CHECK(e);
-    if (interrupt_->IsSet()) *reinterpret_cast<volatile int*>(mapped_interrupt_) = 1;
-    std::this_thread::sleep_for(std::chrono::microseconds(20));
-  }
+  ws_.Sync();
   if (host_.stopped_by_interrupt != 0) interrupts_seen_on_device_ += 1;
 }
 
 void Solver::EnableDeviceInterrupt(const InterruptFlag* interrupt) {
   interrupt_ = interrupt;
   if (interrupt == nullptr || pre_->sharded()) return;  // sharded: all ranks must stop at the same iteration, agreed on at host events
-  if (mapped_interrupt_ == nullptr) {
-    PDLP_CUDA_CHECK(cudaHostAlloc(reinterpret_cast<void**>(&mapped_interrupt_), sizeof(int), cudaHostAllocMapped));
-    PDLP_CUDA_CHECK(cudaEventCreateWithFlags(&pulled_, cudaEventDisableTiming));
-  }
+  if (mapped_interrupt_ == nullptr) PDLP_CUDA_CHECK(cudaHostAlloc(reinterpret_cast<void**>(&mapped_interrupt_), sizeof(int), cudaHostAllocMapped));
   *mapped_interrupt_ = 0;
   int* device_view = nullptr;
   PDLP_CUDA_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&device_view), mapped_interrupt_, 0));
   host_.interrupt_flag = device_view;
+  // The solving thread spends a batch of trial steps inside kernel launches (the launch queue is shorter than a batch)
+  // and then in a stream synchronize: a watcher forwards the caller's flag meanwhile.
+  StopWatcher();
+  watcher_stop_.store(false);
+  watcher_ = std::thread([this] {
+    while (!watcher_stop_.load(std::memory_order_relaxed)) {
+      if (interrupt_->IsSet()) *reinterpret_cast<volatile int*>(mapped_interrupt_) = 1;
+      std::this_thread::sleep_for(std::chrono::microseconds(50));
+    }
+  });
+}
+
+void Solver::StopWatcher() {
+  if (watcher_.joinable()) {
+    watcher_stop_.store(true);
+    watcher_.join();
+  }
 }
 
 Solver::~Solver() {
+  StopWatcher();
   if (mapped_interrupt_ != nullptr) {
     cudaStreamSynchronize(ws_.stream);  // no kernel may still read the flag
     cudaFreeHost(mapped_interrupt_);
   }
-  if (pulled_ != nullptr) cudaEventDestroy(pulled_);
 }
 
 // Runs trial steps on the device until iterations_completed reaches the target, the
@@ -182,27 +184,21 @@ double Solver::DistanceTraveledFromLastStart(const double* x, const double* y) {
   return std::sqrt((0.5 * host_.primal_weight) * dp + (0.5 / host_.primal_weight) * dd);
 }
 
-Solver::Bounds Solver::BoundsAtCurrent() {  // pdhg.cc:1806-1816
-  const double radius = DistanceTraveledFromLastStart(X(), Y());
+Solver::Bounds Solver::BoundsAt(const double* x, const double* y, const double* kty_or_null) {
+  // The radius (DistanceTraveledFromLastStart) comes out of the same passes as the gradients.
   int tr_passes = 0;
-  const LocalizedBounds b = ComputeLocalizedLagrangianBounds(ws_, problem_, X(), Y(), Kty(), host_.primal_weight, radius,
-                                                             params_.use_diagonal_qp_trust_region_solver,
-                                                             params_.diagonal_qp_trust_region_solver_tolerance, &tr_passes);
+  const LocalizedBounds b = ComputeLocalizedLagrangianBounds(ws_, problem_, x, y, kty_or_null, host_.primal_weight, 0.0, params_.use_diagonal_qp_trust_region_solver,
+                                                             params_.diagonal_qp_trust_region_solver_tolerance, &tr_passes, false, it_.x_start.get(), it_.y_start.get());
   phase_.bounds += 1;
   phase_.tr_passes += tr_passes;
   return {b.lagrangian_value, b.lower_bound, b.upper_bound, b.radius};
 }
+Solver::Bounds Solver::BoundsAtCurrent() { return BoundsAt(X(), Y(), Kty()); }                          // pdhg.cc:1806-1816
 Solver::Bounds Solver::BoundsAtAverage() {  // pdhg.cc:1818-1834
-  const double* xa = PrimalAverage();
-  const double* ya = DualAverage();
-  const double radius = DistanceTraveledFromLastStart(xa, ya);
-  int tr_passes = 0;
-  const LocalizedBounds b = ComputeLocalizedLagrangianBounds(ws_, problem_, xa, ya, nullptr, host_.primal_weight, radius,
-                                                             params_.use_diagonal_qp_trust_region_solver,
-                                                             params_.diagonal_qp_trust_region_solver_tolerance, &tr_passes);
-  phase_.bounds += 1;
-  phase_.tr_passes += tr_passes;
-  return {b.lagrangian_value, b.lower_bound, b.upper_bound, b.radius};
+  const Bounds b = BoundsAt(PrimalAverage(), DualAverage(), nullptr);
+  // K^T y of the dual average is now in the bounds' scratch vector: a restart to the average at this event copies it.
+  kty_of_average_at_ = (problem_.n > 0 && host_.avg_weight_sum > 0.0 && host_.avg_weight_sum_dual > 0.0) ? iterations_completed_ : -1;
+  return b;
 }
 
 bool Solver::ShouldDoAdaptiveRestartHeuristic(double candidate_normalized_gap) const {  // pdhg.cc:1853-1867
@@ -292,9 +288,13 @@ void Solver::ApplyRestartChoice(int restart_to_apply) {  // pdhg.cc:2042-2094
       if (pre_->Logs(params_, 4)) LogInfoWithoutPrefix(Format("Restarted to average on iteration %d after %d iterations", iterations_completed_, host_.avg_num_terms));  // :2055-2059
       CopyVector(ws_, it_.x[host_.cur].get(), it_.avg_x.get(), problem_.n);
       CopyVector(ws_, it_.y[host_.cur].get(), it_.avg_y.get(), problem_.m);
-      RowDot(ws_, problem_.K.by_col, it_.y[host_.cur].get(), it_.kty[host_.cur].get());
+      // K^T y of the new current iterate: the same product, by the same kernel over the same values, that the restart
+      // choice of this event left in the bounds' scratch vector (nothing between here and there writes scratch_n[1]).
+      if (kty_of_average_at_ == iterations_completed_) CopyVector(ws_, it_.kty[host_.cur].get(), ws_.scratch_n[1].get(), problem_.n);
+      else RowDot(ws_, problem_.K.by_col, it_.y[host_.cur].get(), it_.kty[host_.cur].get());
       break;
   }
+  kty_of_average_at_ = -1;
   host_.primal_weight = ComputeNewPrimalWeight();
   host_.ratio_last_two_step_sizes = 1.0;
   if (params_.restart_strategy == ADAPTIVE_HEURISTIC) {
@@ -453,6 +453,7 @@ Solver::Outcome Solver::Solve(IterationType type, const InterruptFlag* interrupt
     device_loop_seconds_ = ms * 1e-3;
     cudaEventDestroy(ev0);
     cudaEventDestroy(ev1);
+    StopWatcher();
     if (std::getenv("PDLP_B200_DEBUG_TIMING") != nullptr) {
       std::fprintf(stderr, "pdlp_b200 loop phases: %d iterations, %lld trials, steps %.4f s; %d events: restart choice %.4f s (%d bounds, %d trust-region passes), "
                    "%d termination checks %.4f s, %d restarts applied %.4f s; device loop %.4f s\n", iterations_completed_, static_cast<long long>(host_.total_trials),

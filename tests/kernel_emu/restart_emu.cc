@@ -64,6 +64,10 @@ struct EmuRunner {
 static int g_max_norm = 0;
 // The next emu_localized_bounds call computes the max-norm bounds (trust_region.cc:797-884) when set.
 extern "C" void emu_set_max_norm(int on) { g_max_norm = on; }
+// The next emu_localized_bounds calls take their radius from the distance to this point (null, null: from the argument).
+static const double* g_x_start = nullptr;
+static const double* g_y_start = nullptr;
+extern "C" void emu_set_start_point(const double* x_start, const double* y_start) { g_x_start = x_start; g_y_start = y_start; }
 
 extern "C" int emu_localized_bounds(int n, int m, const int* csr_ptr, const int* csr_idx, const double* csr_val, const int* csr_blocks, int csr_num_blocks,
                                     const int* csc_ptr, const int* csc_idx, const double* csc_val, const int* csc_blocks, int csc_num_blocks, const double* c,
@@ -78,7 +82,7 @@ extern "C" int emu_localized_bounds(int n, int m, const int* csr_ptr, const int*
   std::vector<double> gx(std::max(n, 1)), gy(std::max(m, 1)), kty(std::max(n, 1)), crit(n + m + 1), coef(n + m + 1);
   const RestartProblemView view{csr_val, csr_idx, c, q, vlb, vub, clb, cub, n, m, q == nullptr, 0, gx.data(), gy.data(), kty.data(), crit.data(), coef.data()};
   int passes = 0;
-  const LocalizedBounds b = LocalizedLagrangianBoundsWith(run, view, x, y, nullptr, primal_weight, radius, use_diagonal_qp_solver != 0, tolerance, &passes, g_max_norm != 0);
+  const LocalizedBounds b = LocalizedLagrangianBoundsWith(run, view, x, y, nullptr, primal_weight, radius, use_diagonal_qp_solver != 0, tolerance, &passes, g_max_norm != 0, g_x_start, g_y_start);
   out[0] = b.lagrangian_value; out[1] = b.lower_bound; out[2] = b.upper_bound; out[3] = b.radius; out[4] = passes;
   return 0;
 }

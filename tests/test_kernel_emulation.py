@@ -194,7 +194,7 @@ def reference_adaptive_trials(K, c, q, vlb, vub, clb, cub, x, y, step, w, trials
                 nonlinearity=nonlinearity, weight_sum=weight_sum)
 
 
-def emulated_adaptive_trials(lib, K, c, q, vlb, vub, clb, cub, x, y, step, w, trials, max_grid=3, defer=0, constant=False):
+def emulated_adaptive_trials(lib, K, c, q, vlb, vub, clb, cub, x, y, step, w, trials, max_grid=3, defer=0, constant=False, interrupt_at=-1):
     import scipy.sparse as sp
     csr, csc = sp.csr_matrix(K), sp.csc_matrix(K)
     csr.sort_indices(); csc.sort_indices()
@@ -205,15 +205,17 @@ def emulated_adaptive_trials(lib, K, c, q, vlb, vub, clb, cub, x, y, step, w, tr
     rb, _, _ = pdlp_b200.work_blocks(arrays["rp"])
     cb, _, _ = pdlp_b200.work_blocks(arrays["cp"])
     rb, cb = i32(rb), i32(cb)
-    xo, yo, ax, ay, st = f64(x).copy(), f64(y).copy(), np.zeros(n), np.zeros(m), np.zeros(8)
+    xo, yo, ax, ay, st = f64(x).copy(), f64(y).copy(), np.zeros(n), np.zeros(m), np.zeros(9)
     p = lambda a: ctypes.c_void_p(a.ctypes.data) if a is not None else ctypes.c_void_p(None)
     vecs = [f64(c), None if q is None else f64(q), f64(vlb), f64(vub), f64(clb), f64(cub)]
+    lib.emu_set_interrupt_at(int(interrupt_at))  # the flag is raised before this trial of the batch (-1: no flag)
     rc = lib.emu_adaptive_trials(n, m, p(arrays["rp"]), p(arrays["ri"]), p(arrays["rv"]), p(rb), len(rb) - 1, p(arrays["cp"]), p(arrays["ci"]), p(arrays["cv"]),
                                  p(cb), len(cb) - 1, *[p(v) for v in vecs], p(xo), p(yo), p(ax), p(ay), ctypes.c_double(step), ctypes.c_double(w), trials, int(constant),
                                  max_grid, defer, p(st))
+    lib.emu_set_interrupt_at(-1)
     assert rc == 0
     return dict(x=xo, y=yo, avg_x=ax, avg_y=ay, step=st[0], completed=int(st[1]), rejected=int(st[2]), movement=st[3], nonlinearity=st[4], weight_sum=st[5],
-                active=int(st[6]), total_trials=int(st[7]))
+                active=int(st[6]), total_trials=int(st[7]), stopped_by_interrupt=int(st[8]))
 
 
 def step_problem(seed, qp):
@@ -252,6 +254,29 @@ def test_adaptive_trial_steps_follow_the_reference_step_rule(step_libs, qp, defe
         np.testing.assert_allclose(got[key], want[key], rtol=1e-11, atol=1e-12, err_msg=key)
     for key in ("step", "movement", "nonlinearity", "weight_sum"):
         np.testing.assert_allclose(got[key], want[key], rtol=1e-10, err_msg=key)
+
+
+def test_decision_kernel_stops_at_the_first_accepted_step_after_the_interrupt(step_libs):
+    """termination.cc:178 tests interrupt_solve between iterations: a flag raised during an iteration's rejected trials
+    stops the loop when that iteration completes, not earlier and not a whole polling interval later."""
+    prob = step_problem(2, False)
+    step, w, trials = 50.0, 0.2, 14
+    free = [reference_adaptive_trials(*prob, step, w, k) for k in range(trials + 1)]
+    accepted_at = [k for k in range(trials) if free[k + 1]["completed"] > free[k]["completed"]]  # trial k was accepted
+    rejected_at = [k for k in range(trials) if k not in accepted_at]
+    assert rejected_at and accepted_at
+    for raise_before in (rejected_at[0], accepted_at[2]):
+        got = emulated_adaptive_trials(step_libs[0], *prob, step, w, trials, interrupt_at=raise_before)
+        stop = min(k for k in accepted_at if k >= raise_before)  # the trial that completes the running iteration
+        assert got["stopped_by_interrupt"] == 1 and got["active"] == 0
+        assert got["total_trials"] == stop + 1, (got["total_trials"], stop)
+        want = free[stop + 1]
+        assert got["completed"] == want["completed"]
+        for key in ("x", "y", "avg_x", "avg_y"):
+            np.testing.assert_allclose(got[key], want[key], rtol=1e-11, atol=1e-12, err_msg=key)
+    # No flag: nothing stops.
+    got = emulated_adaptive_trials(step_libs[0], *prob, step, w, trials)
+    assert got["stopped_by_interrupt"] == 0 and got["active"] == 1 and got["total_trials"] == trials
 
 
 def test_constant_size_steps_follow_the_reference(step_libs):
@@ -628,6 +653,23 @@ def test_localized_lagrangian_bounds_match_the_oracle(qp_case, diagonal):
             assert abs(got[key] - want[key]) <= (1e-5 if diagonal else 1e-10) * scale, (radius, key, got[key], want[key])
         passes.append(int(out[4]))
     assert passes[0] == 0 and max(passes) >= 2
+    # The radius as the solver gets it: the weighted distance from the last restart point, reduced inside the gradient
+    # passes (DistanceTraveledFromLastStart, primal_dual_hybrid_gradient.cc:1795-1804); the radius argument is ignored.
+    rng = np.random.default_rng(99)
+    xs, ys = f64(x + 0.3 * rng.standard_normal(n)), f64(y + 0.3 * rng.standard_normal(m))
+    w = 0.6
+    radius = float(np.sqrt(0.5 * w * np.sum((x - xs) ** 2) + 0.5 / w * np.sum((y - ys) ** 2)))
+    want = oracle.localized_bounds(x, y, 1, w, radius, diagonal, tol)
+    lib.emu_set_start_point(p(xs), p(ys))
+    try:
+        out = np.zeros(5)
+        assert lib.emu_localized_bounds(n, m, p(arr[0]), p(arr[1]), p(arr[2]), p(rb), len(rb) - 1, p(arc[0]), p(arc[1]), p(arc[2]), p(cb), len(cb) - 1,
+                                        *[p(v) for v in vec], ctypes.c_double(w), ctypes.c_double(-1.0), int(diagonal), ctypes.c_double(tol), 3, p(out)) == 0
+    finally:
+        lib.emu_set_start_point(p(None), p(None))
+    assert abs(out[3] - radius) <= 1e-12 * radius
+    for key, got in zip(("lagrangian_value", "lower_bound", "upper_bound"), out[:3]):
+        assert abs(got - want[key]) <= (1e-5 if diagonal else 1e-10) * max(1.0, abs(want["lagrangian_value"])), ("start point", key, got, want[key])
     if not diagonal:  # PrimalDualNorm::kMaxNorm: the primal and the dual problem solved separately (trust_region.cc:797-884)
         lib.emu_set_max_norm(1)
         try:
