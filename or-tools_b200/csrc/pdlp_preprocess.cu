@@ -2,6 +2,7 @@
 // initial step size / primal weight, termination checks and result construction.
 //   follows ortools/pdlp/primal_dual_hybrid_gradient.cc:711-1105, 1204-1286, 1414-1643.
 // Glop presolve (:1107-1202) is host-only and not part of this path.
+#include <exception>
 #include <random>
 
 #include <chrono>
@@ -90,8 +91,20 @@ PreprocessSolver::PreprocessSolver(const QpView& qp, const PrimalDualHybridGradi
   problem_.objective_scaling_factor = qp.objective_scaling_factor;
   // Sharded: the CSR copy's work blocks are cut at the shared / private row boundary (pdlp_launch.cuh:EnqueueRows).
   const int64_t row_cut = comm_.sharded() ? ws_.shared_rows : -1;
-  if (qp.col_ptr32 != nullptr) BuildDeviceMatrix(qp.n, qp.m, qp.nnz, qp.col_ptr32, qp.row_idx32, qp.val, ws_.stream, &problem_.K, row_cut);
-  else BuildDeviceMatrix(qp.n, qp.m, qp.nnz, qp.col_ptr, qp.row_idx, qp.val, ws_.stream, &problem_.K, row_cut);
+  // A failure on one rank only (a malformed block, out of memory) must not leave the other ranks waiting in the next
+  // collective: the ranks agree on whether every block was built before anyone goes on.
+  std::exception_ptr build_error;
+  try {
+    if (qp.col_ptr32 != nullptr) BuildDeviceMatrix(qp.n, qp.m, qp.nnz, qp.col_ptr32, qp.row_idx32, qp.val, ws_.stream, &problem_.K, row_cut);
+    else BuildDeviceMatrix(qp.n, qp.m, qp.nnz, qp.col_ptr, qp.row_idx, qp.val, ws_.stream, &problem_.K, row_cut);
+  } catch (...) {
+    if (!comm_.sharded()) throw;
+    build_error = std::current_exception();
+  }
+  if (comm_.sharded() && AgreeOnCode(build_error ? 1 : 0) != 0) {
+    if (build_error) std::rethrow_exception(build_error);
+    throw std::runtime_error("pdlp_b200: another rank could not build its block of the constraint matrix");
+  }
   problem_.K.by_col.sharded_rows = comm_.sharded();
   problem_.K.by_row.partial_sums = comm_.sharded();
   auto up = [&](DVec& d, const double* h, int64_t count) {
@@ -420,29 +433,61 @@ void PreprocessSolver::ComputeConvergenceAndInfeasibility(const PrimalDualHybrid
       md->active_primal_variable_change = static_cast<int64_t>(t.active_primal_change);
       md->active_dual_variable_change = static_cast<int64_t>(t.active_dual_change);
     }
-    if (!seeds_.empty() && !comm_.sharded()) AddRandomProjections(x, y, md);  // host-side diagnostic of the whole vector: single GPU only
+    if (!seeds_.empty()) AddRandomProjections(x, y, md);  // host-side diagnostic (sharded: partial sums added over the ranks)
   }
 }
 
 // iteration_stats.cc:321-346,598-610.  Rarely used diagnostics: computed on the host
 // from a copy of the point.  parity unpinned (absl::Gaussian; depends on the shard count
-// by design, solvers.proto:397-403): one shard is used here.
+// by design, solvers.proto:397-403): one shard per GPU is used here.
+// Column-sharded solves: the random direction is assembled from one Gaussian stream per owner - the shared rows'
+// stream is the same on every rank (seeded without a rank) and counted on rank 0, every rank's columns and private
+// rows draw from a stream seeded with its rank - and the partial dot products and squared norms are added over
+// the ranks, so all ranks record the same projection of the WHOLE point onto one unit direction per seed.
 void PreprocessSolver::AddRandomProjections(const double* x, const double* y, PointMetadata* md) {
   std::vector<double> hx(problem_.n), hy(problem_.m);
   if (problem_.n > 0) PDLP_CUDA_CHECK(cudaMemcpyAsync(hx.data(), x, problem_.n * sizeof(double), cudaMemcpyDeviceToHost, ws_.stream));
   if (problem_.m > 0) PDLP_CUDA_CHECK(cudaMemcpyAsync(hy.data(), y, problem_.m * sizeof(double), cudaMemcpyDeviceToHost, ws_.stream));
   ws_.Sync();
-  auto project = [](const std::vector<double>& v, std::mt19937& seed_gen) {
-    std::mt19937 rnd(seed_gen());
+  // Adds the dot product of v[begin, end) with a Gaussian stream, and the stream's squared norm.
+  auto accumulate = [](const std::vector<double>& v, int64_t begin, int64_t end, std::mt19937& rnd, double* dot, double* norm2) {
     std::normal_distribution<double> gauss(0.0, 1.0);
-    double d = 0, n2 = 0;
-    for (double e : v) { const double g = gauss(rnd); d += g * e; n2 += g * g; }
-    return d / std::sqrt(n2);
+    for (int64_t i = begin; i < end; ++i) { const double g = gauss(rnd); *dot += g * v[i]; *norm2 += g * g; }
   };
-  for (int32_t seed : seeds_) {
-    std::mt19937 gen(seed);
-    md->random_primal_projections.v.push_back(project(hx, gen));
-    md->random_dual_projections.v.push_back(project(hy, gen));
+  const bool sharded = comm_.sharded();
+  const int64_t shared = sharded ? ws_.shared_rows : 0;
+  std::vector<double> sums(4 * seeds_.size(), 0.0);  // per seed: primal dot, primal norm^2, dual dot, dual norm^2
+  for (size_t k = 0; k < seeds_.size(); ++k) {
+    std::mt19937 gen(seeds_[k]);
+    const uint32_t primal_seed = gen(), dual_seed = gen();
+    double* s = &sums[4 * k];
+    if (!sharded) {
+      std::mt19937 primal_rnd(primal_seed), dual_rnd(dual_seed);
+      accumulate(hx, 0, problem_.n, primal_rnd, s + 0, s + 1);
+      accumulate(hy, 0, problem_.m, dual_rnd, s + 2, s + 3);
+      continue;
+    }
+    const uint32_t owner = static_cast<uint32_t>(comm_.rank()) + 1u;
+    std::seed_seq primal_seq{primal_seed, owner}, private_seq{dual_seed, owner};
+    std::mt19937 primal_rnd(primal_seq), private_rnd(private_seq), shared_rnd(dual_seed);
+    accumulate(hx, 0, problem_.n, primal_rnd, s + 0, s + 1);
+    if (comm_.rank() == 0) accumulate(hy, 0, shared, shared_rnd, s + 2, s + 3);
+    accumulate(hy, shared, problem_.m, private_rnd, s + 2, s + 3);
+  }
+  if (sharded) {
+    constexpr size_t kChunk = 32;  // doubles per all-reduce (ws_.totals holds kMaxSlots * 4)
+    for (size_t at = 0; at < sums.size(); at += kChunk) {
+      const size_t count = std::min(kChunk, sums.size() - at);
+      PDLP_CUDA_CHECK(cudaMemcpyAsync(ws_.totals.get(), sums.data() + at, count * sizeof(double), cudaMemcpyHostToDevice, ws_.stream));
+      comm_.AllReduce(ws_.totals.get(), count, false, ws_.stream);
+      const double* total = FetchTotals(ws_, static_cast<int>(count));
+      std::copy(total, total + count, sums.begin() + at);
+    }
+  }
+  for (size_t k = 0; k < seeds_.size(); ++k) {
+    const double* s = &sums[4 * k];
+    md->random_primal_projections.v.push_back(s[0] / std::sqrt(s[1]));
+    md->random_dual_projections.v.push_back(s[2] / std::sqrt(s[3]));
   }
 }
 

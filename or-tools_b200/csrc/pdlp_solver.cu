@@ -441,18 +441,20 @@ Solver::Outcome Solver::Solve(IterationType type, const InterruptFlag* interrupt
   iterations_completed_ = 0;
   IterationStats work_from_feasibility_polishing = WorkFromFeasibilityPolishing(log);
   kkt_passes_from_polishing_ = work_from_feasibility_polishing.cumulative_kkt_matrix_passes;
-  cudaEvent_t ev0, ev1;
-  PDLP_CUDA_CHECK(cudaEventCreate(&ev0));
-  PDLP_CUDA_CHECK(cudaEventCreate(&ev1));
-  PDLP_CUDA_CHECK(cudaEventRecord(ev0, ws_.stream));
+  struct EventPair {  // destroyed on every way out of Solve(), a throwing kernel launch or collective included
+    cudaEvent_t begin = nullptr, end = nullptr;
+    EventPair() { PDLP_CUDA_CHECK(cudaEventCreate(&begin)); PDLP_CUDA_CHECK(cudaEventCreate(&end)); }
+    ~EventPair() { if (begin != nullptr) cudaEventDestroy(begin); if (end != nullptr) cudaEventDestroy(end); }
+    EventPair(const EventPair&) = delete;
+    EventPair& operator=(const EventPair&) = delete;
+  } events;
+  PDLP_CUDA_CHECK(cudaEventRecord(events.begin, ws_.stream));
   auto finish = [&](Outcome o) {
-    cudaEventRecord(ev1, ws_.stream);
-    cudaEventSynchronize(ev1);
+    cudaEventRecord(events.end, ws_.stream);
+    cudaEventSynchronize(events.end);
     float ms = 0.0f;
-    cudaEventElapsedTime(&ms, ev0, ev1);
+    cudaEventElapsedTime(&ms, events.begin, events.end);
     device_loop_seconds_ = ms * 1e-3;
-    cudaEventDestroy(ev0);
-    cudaEventDestroy(ev1);
     StopWatcher();
     if (std::getenv("PDLP_B200_DEBUG_TIMING") != nullptr) {
       std::fprintf(stderr, "pdlp_b200 loop phases: %d iterations, %lld trials, steps %.4f s; %d events: restart choice %.4f s (%d bounds, %d trust-region passes), "

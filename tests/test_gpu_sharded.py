@@ -135,6 +135,17 @@ def _worker(rank, world, port, out_dir):
         res["interrupt"] = _log_summary(r)
         res["interrupt"]["callbacks"] = seen
 
+        # Random projections (iteration_stats.cc:321-346): one unit direction per seed for the WHOLE point, partial sums
+        # added over the ranks; the transport case has private rows, so all three streams (columns, shared rows, private rows) are in play.
+        tq, tp = cases()["transport"]
+        tp.random_projection_seeds.extend([7, 8, 9])
+        tp.termination_criteria.iteration_limit = 64
+        r = pdlp_b200.primal_dual_hybrid_gradient_sharded(tq, tp, device=rank)
+        md = [m for m in r.solve_log.solution_stats.point_metadata if m.point_type == r.solve_log.solution_type]
+        ci = [c for c in r.solve_log.solution_stats.convergence_information if c.candidate_type == r.solve_log.solution_type]
+        res["projections"] = {"primal": list(md[0].random_primal_projections), "dual": list(md[0].random_dual_projections),
+                              "l2_primal_variable": ci[0].l2_primal_variable, "l2_dual_variable": ci[0].l2_dual_variable}
+
         # A time limit: every rank stops at the same iteration although their clocks differ.
         timed = params(1e-13)
         timed.termination_criteria.time_sec_limit = 0.05
@@ -300,6 +311,18 @@ def test_warm_start_interrupt_time_limit_and_errors_are_collective(two_rank_run)
     assert res[0]["interrupt"]["iterations"] == res[1]["interrupt"]["iterations"] >= 128
     assert res[0]["interrupt"]["callbacks"] == res[1]["interrupt"]["callbacks"]
     assert res[0]["time_limit"]["iterations"] == res[1]["time_limit"]["iterations"]
+
+
+@needs_two
+def test_random_projections_of_a_sharded_solve(two_rank_run):
+    res, _ = two_rank_run
+    a, b = res[0]["projections"], res[1]["projections"]
+    assert a == b  # the same numbers on every rank
+    assert len(a["primal"]) == len(a["dual"]) == 3
+    # Projections onto unit directions: bounded by the norm of the point, different per seed, not all zero.
+    assert all(abs(v) <= a["l2_primal_variable"] * (1 + 1e-12) for v in a["primal"]) and len(set(a["primal"])) == 3
+    assert all(abs(v) <= a["l2_dual_variable"] * (1 + 1e-12) for v in a["dual"]) and len(set(a["dual"])) == 3
+    assert any(v != 0.0 for v in a["primal"]) and any(v != 0.0 for v in a["dual"])
 
 
 @needs_two
