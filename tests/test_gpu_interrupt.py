@@ -28,6 +28,10 @@ def _never_converging_params():
 
 def test_flag_raised_mid_solve_stops_the_device_loop_between_host_events():
     qp = fixtures.random_lp(2000, 4000, 5, 3)
+    # CUDA context, library load and the first allocations must not eat the 0.25 s before the flag goes up.
+    warm = _never_converging_params()
+    warm.termination_criteria.iteration_limit = 64
+    pdlp_b200.primal_dual_hybrid_gradient(qp, warm, device=0)
     flag = np.zeros(1, dtype=np.int32)
     raised = {}
 
