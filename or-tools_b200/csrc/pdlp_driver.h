@@ -231,6 +231,7 @@ class Solver {
   void StopWatcher();
   const InterruptFlag* interrupt_ = nullptr;
   int* mapped_interrupt_ = nullptr;
+  const volatile int* outer_stop_enqueue_ = nullptr;
   std::thread watcher_;
   std::atomic<bool> watcher_stop_{false};
   int interrupts_seen_on_device_ = 0;

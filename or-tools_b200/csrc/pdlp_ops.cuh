@@ -54,6 +54,9 @@ struct Workspace {
   // only.  dual_skip_below = first dual row whose reduction terms count on this rank (0 on rank 0
   // and on a single GPU, shared_rows elsewhere).
   int64_t shared_rows = 0, dual_skip_below = 0;
+  // One GPU, a solve with an interrupt flag: the host-mapped copy of the flag that the decision kernel reads (pdlp_step_state.h).
+  // The enqueue loops stop queueing trial steps once it is up.  Null otherwise.
+  const volatile int* stop_enqueue = nullptr;
   int64_t SkipBelow(Side side) const { return side == Side::kDual ? dual_skip_below : 0; }
   void Init(int64_t n_, int64_t m_);
   void Destroy();

@@ -88,6 +88,8 @@ void Solver::EnableDeviceInterrupt(const InterruptFlag* interrupt) {
   int* device_view = nullptr;
   PDLP_CUDA_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&device_view), mapped_interrupt_, 0));
   host_.interrupt_flag = device_view;
+  if (ws_.stop_enqueue != mapped_interrupt_) outer_stop_enqueue_ = ws_.stop_enqueue;  // a polishing phase runs inside the main solver's Solve()
+  ws_.stop_enqueue = mapped_interrupt_;
   // The solving thread spends a batch of trial steps inside kernel launches (the launch queue is shorter than a batch)
   // and then in a stream synchronize: a watcher forwards the caller's flag meanwhile.
   StopWatcher();
@@ -101,6 +103,7 @@ void Solver::EnableDeviceInterrupt(const InterruptFlag* interrupt) {
 }
 
 void Solver::StopWatcher() {
+  if (mapped_interrupt_ != nullptr && ws_.stop_enqueue == mapped_interrupt_) ws_.stop_enqueue = outer_stop_enqueue_;
   if (watcher_.joinable()) {
     watcher_stop_.store(true);
     watcher_.join();

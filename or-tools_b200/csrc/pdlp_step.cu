@@ -64,6 +64,7 @@ void EnqueueAdaptiveTrials(Workspace& ws, const DeviceProblem& p, Iterate& it, i
     ws.profile->push_back(e);
   };
   for (int t = 0; t < trials; ++t) {
+    if (t > 0 && ws.stop_enqueue != nullptr && *ws.stop_enqueue != 0) break;  // interrupt raised: the device stops at its next accepted step, do not queue a batch of no-ops behind it
     mark();
     const int g1 = EnqueueMap(ws, k1, p.n, 0);
     mark();
@@ -97,6 +98,7 @@ void EnqueueMalitskyPockTrials(Workspace& ws, const DeviceProblem& p, Iterate& i
   KtyStepOp k3{st, csc.val.get(), csc.idx.get(), it.y[0].get(), it.y[1].get(), it.x[0].get(), it.x[1].get(), it.kty[0].get(), it.kty[1].get()};
   AverageOp k5{{}, st, it.x[0].get(), it.x[1].get(), it.y[0].get(), it.y[1].get(), it.avg_x.get(), it.avg_y.get(), p.n, 0};
   for (int t = 0; t < trials; ++t) {
+    if (t > 0 && ws.stop_enqueue != nullptr && *ws.stop_enqueue != 0) break;  // see EnqueueAdaptiveTrials
     mp_begin_kernel<<<1, 1, 0, ws.stream>>>(st);
     ++ws.launches;
     // The primal step is recomputed per dual trial (same tau, same result): keeping it
