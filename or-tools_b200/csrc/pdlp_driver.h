@@ -232,6 +232,7 @@ class Solver {
   const InterruptFlag* interrupt_ = nullptr;
   int* mapped_interrupt_ = nullptr;
   const volatile int* outer_stop_enqueue_ = nullptr;
+  cudaEvent_t chunk_done_[2] = {nullptr, nullptr};  // throttle of the blind enqueue while an interrupt flag is live
   std::thread watcher_;
   std::atomic<bool> watcher_stop_{false};
   int interrupts_seen_on_device_ = 0;

@@ -87,6 +87,16 @@ static __global__ void peer_combine_sums_kernel(PeerView view, unsigned long lon
   if (threadIdx.x == 0) PeerCombineSums(view, epoch, out, count, max != 0);
 }
 
+// The sums of rows [r0, r0 + nrows) of one work block into slot [rank] of every rank's region, by the whole CTA:
+// consecutive threads store consecutive rows, one destination after the other.
+__device__ __forceinline__ void PeerBlockPush(const PeerView& view, int parity, int r0, int nrows, const double* sums) {
+#pragma unroll 1
+  for (int r = 0; r < view.world; ++r) {
+    double* dst = view.RowSlot(r, parity, view.rank) + r0;
+    for (int i = threadIdx.x; i < nrows; i += kBlock) dst[i] = sums[i];
+  }
+}
+
 // Phase 1 of a sharded CSR pass in peer mode: this rank's part of every shared row sum, pushed into slot
 // [rank] of every rank's region.  Same interface as PartialRowOp (pdlp_skeletons.cuh).
 template <class Op>
@@ -109,10 +119,12 @@ struct PeerPartialRowOp {
   __device__ double RowInit() const { return op.RowInit(); }
   __device__ double RowAdd(double acc, double staged, int row) const { return op.RowAdd(acc, staged, row); }
   __device__ double RowMerge(double a, double b) const { return op.RowMerge(a, b); }
-  __device__ void RowFinish(int row, double acc, Slots<0>&) const {
+  __device__ void RowFinish(int row, double acc, Slots<0>&) const {  // a row longer than a work block: one thread
 #pragma unroll 1
     for (int r = 0; r < view.world; ++r) view.RowSlot(r, parity, view.rank)[row] = acc;
   }
+  __device__ bool PushesRow(int) const { return true; }
+  __device__ void BlockPush(int r0, int nrows, const double* sums) const { PeerBlockPush(view, parity, r0, nrows, sums); }
 };
 
 // Phase 1 and the private rows in ONE row-stream launch (a CSR block cut into shared rows [0, cut_row) and
@@ -143,10 +155,12 @@ struct PeerCutRowOpBase {
   __device__ double RowInit() const { return op.RowInit(); }
   __device__ double RowAdd(double acc, double staged, int row) const { return op.RowAdd(acc, staged, row); }
   __device__ double RowMerge(double a, double b) const { return op.RowMerge(a, b); }
-  __device__ void Push(int row, double acc) const {
+  __device__ void Push(int row, double acc) const {  // a row longer than a work block: one thread
 #pragma unroll 1
     for (int r = 0; r < view.world; ++r) view.RowSlot(r, parity, view.rank)[row] = acc;
   }
+  __device__ bool PushesRow(int row) const { return row < cut_row; }
+  __device__ void BlockPush(int r0, int nrows, const double* sums) const { PeerBlockPush(view, parity, r0, nrows, sums); }
 };
 template <class Op>
 struct PeerCutRowOp<Op, true> : PeerCutRowOpBase<Op> {

@@ -176,6 +176,15 @@ struct HasRowPrefetch : std::false_type {};
 template <class Op>
 struct HasRowPrefetch<Op, std::void_t<typename Op::Pre>> : std::true_type {};
 
+// An op that hands the sums of some rows to other GPUs (pdlp_peer.cuh) declares `bool PushesRow(int row)` and
+// `void BlockPush(int r0, int nrows, const double* sums)`: the kernel then collects those rows' sums of a work block in
+// shared memory and the whole CTA stores them, so that a warp writes 256 contiguous bytes per destination instead of
+// one 8-byte store per row from a single lane (NVLink moves packets, and 8-byte packets are mostly header).
+template <class Op, class = void>
+struct HasBlockPush : std::false_type {};
+template <class Op>
+struct HasBlockPush<Op, std::void_t<decltype(std::declval<const Op&>().PushesRow(0))>> : std::true_type {};
+
 struct NoPre {};
 template <class Op, bool = HasRowPrefetch<Op>::value>
 struct PreOf { using type = NoPre; };
@@ -238,6 +247,7 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
   // the next block's indices into exactly the positions it has already read this block's from.
   __shared__ int idx_buf[HasSplitLoad<Op>::value ? kStreamChunk : 1];
   __shared__ double long_row_buf[kBlock / 32];
+  __shared__ double push_buf[HasBlockPush<Op>::value ? kMaxRowsPerBlock : 1];  // sums of this block's pushed rows
   using Pre = typename PreOf<Op>::type;
   constexpr int kPreRows = sizeof(Pre) > 16 ? 2 : 4;  // rows per thread whose epilogue operands are fetched before the barrier
   Slots<Op::kNumSlots> red;
@@ -351,7 +361,14 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
             }
             // All 32 lanes take part in the shuffles (t divides 32).
             for (int off = t >> 1; off > 0; off >>= 1) a = op.RowMerge(a, __shfl_xor_sync(0xffffffffu, a, off));
-            if (lane == 0 && rr < nrows) OpRowFinish(op, r0 + rr, a, pre[u], red);
+            if (lane == 0 && rr < nrows) {
+              if constexpr (HasBlockPush<Op>::value) {
+                if (op.PushesRow(r0 + rr)) push_buf[rr] = a;
+                else OpRowFinish(op, r0 + rr, a, pre[u], red);
+              } else {
+                OpRowFinish(op, r0 + rr, a, pre[u], red);
+              }
+            }
           }
         }
         // Rows beyond the prefetched ones (only when a block has more than kPreRows * groups rows).
@@ -363,9 +380,21 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
             for (int q = row_raw[rr] - p0 + lane; q < q1; q += t) a = op.RowAdd(a, staged[Skew(q, shift)], r0 + rr);
           }
           for (int off = t >> 1; off > 0; off >>= 1) a = op.RowMerge(a, __shfl_xor_sync(0xffffffffu, a, off));
-          if (lane == 0 && rr < nrows) OpRowFinish(op, r0 + rr, a, OpRowPrefetch(op, r0 + rr), red);
+          if (lane == 0 && rr < nrows) {
+            if constexpr (HasBlockPush<Op>::value) {
+              if (op.PushesRow(r0 + rr)) push_buf[rr] = a;
+              else OpRowFinish(op, r0 + rr, a, OpRowPrefetch(op, r0 + rr), red);
+            } else {
+              OpRowFinish(op, r0 + rr, a, OpRowPrefetch(op, r0 + rr), red);
+            }
+          }
         }
         __syncthreads();
+        // A work block lies on one side of the shared / private cut.  The next block writes push_buf only behind its
+        // own barrier, which no thread passes before every thread has left this loop.
+        if constexpr (HasBlockPush<Op>::value) {
+          if (op.PushesRow(r0)) op.BlockPush(r0, nrows, push_buf);
+        }
       }
       b += stride;
       r0 = nr0; r1 = nr1; p0 = np0; p1 = np1;

@@ -83,7 +83,10 @@ void Solver::PullState() {
 void Solver::EnableDeviceInterrupt(const InterruptFlag* interrupt) {
   interrupt_ = interrupt;
   if (interrupt == nullptr || pre_->sharded()) return;  // sharded: all ranks must stop at the same iteration, agreed on at host events
-  if (mapped_interrupt_ == nullptr) PDLP_CUDA_CHECK(cudaHostAlloc(reinterpret_cast<void**>(&mapped_interrupt_), sizeof(int), cudaHostAllocMapped));
+  if (mapped_interrupt_ == nullptr) {
+    PDLP_CUDA_CHECK(cudaHostAlloc(reinterpret_cast<void**>(&mapped_interrupt_), sizeof(int), cudaHostAllocMapped));
+    for (cudaEvent_t& e : chunk_done_) PDLP_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
   *mapped_interrupt_ = 0;
   int* device_view = nullptr;
   PDLP_CUDA_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&device_view), mapped_interrupt_, 0));
@@ -116,6 +119,7 @@ Solver::~Solver() {
     cudaStreamSynchronize(ws_.stream);  // no kernel may still read the flag
     cudaFreeHost(mapped_interrupt_);
   }
+  for (cudaEvent_t e : chunk_done_) if (e != nullptr) cudaEventDestroy(e);
 }
 
 // Runs trial steps on the device until iterations_completed reaches the target, the
@@ -137,8 +141,25 @@ void Solver::RunDeviceIterations(int target_iteration) {
   for (;;) {
     const int need = target_iteration - host_.iterations_completed;
     const int trials = need + 2 + need / 8;
-    if (mp) EnqueueMalitskyPockTrials(ws_, problem_, it_, trials);
-    else EnqueueAdaptiveTrials(ws_, problem_, it_, trials, constant);
+    auto enqueue = [&](int count) {
+      if (mp) EnqueueMalitskyPockTrials(ws_, problem_, it_, count);
+      else EnqueueAdaptiveTrials(ws_, problem_, it_, count, constant);
+    };
+    if (mapped_interrupt_ == nullptr) {
+      enqueue(trials);
+    } else {
+      // With an interrupt flag the host must not run a whole batch ahead of the device: once the decision kernel has
+      // switched the loop off, every launch still queued is a no-op that costs its launch latency (thousands of them
+      // are tens of milliseconds).  At most two chunks are queued behind the one that is running.
+      constexpr int kChunk = 32;
+      int k = 0;
+      for (int left = trials; left > 0; left -= kChunk, ++k) {
+        enqueue(std::min(kChunk, left));
+        PDLP_CUDA_CHECK(cudaEventRecord(chunk_done_[k & 1], ws_.stream));
+        if (k >= 1) PDLP_CUDA_CHECK(cudaEventSynchronize(chunk_done_[(k - 1) & 1]));
+        if (*reinterpret_cast<volatile int*>(mapped_interrupt_) != 0) break;
+      }
+    }
     PullState();
     if (host_.active == 0) break;
     if (++guard > 100000) throw std::runtime_error("pdlp_b200: device iteration loop made no progress");
