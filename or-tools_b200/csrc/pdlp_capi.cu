@@ -824,12 +824,28 @@ static pdlp_b200_status TrialStepsImpl(pdlp_b200_device_problem* h, int steps, d
     const long long before = ws.launches;
     std::vector<cudaEvent_t> marks;
     if (kernel_seconds != nullptr) ws.profile = &marks;
+    std::vector<cudaEvent_t> peer_marks;
+    if (kernel_seconds != nullptr && std::getenv("PDLP_B200_DEBUG_TIMING") != nullptr) ws.profile_peer = &peer_marks;
     PDLP_CUDA_CHECK(cudaEventRecord(e0, ws.stream));
     EnqueueAdaptiveTrials(ws, p, it, steps, false);
     PDLP_CUDA_CHECK(cudaEventRecord(e1, ws.stream));
     ws.profile = nullptr;
+    ws.profile_peer = nullptr;
     PDLP_CUDA_CHECK(cudaMemcpyAsync(&st, it.state.get(), sizeof(st), cudaMemcpyDeviceToHost, ws.stream));
     ws.Sync();
+    if (peer_marks.size() >= 4 && peer_marks.size() % 4 == 0) {  // the fused peer pass: before, after push + private rows, after signal, after wait + finish
+      double phase[3] = {0, 0, 0};
+      const size_t calls = peer_marks.size() / 4;
+      for (size_t c = 0; c < calls; ++c)
+        for (int k = 0; k < 3; ++k) {
+          float kms = 0;
+          cudaEventElapsedTime(&kms, peer_marks[4 * c + k], peer_marks[4 * c + k + 1]);
+          phase[k] += kms * 1e3 / calls;
+        }
+      std::fprintf(stderr, "[pdlp_b200] rank %d K x pass in peer mode, us per step: push + private rows %.1f, signal %.1f, wait + finish %.1f\n", ws.comm != nullptr ? ws.comm->rank() : 0,
+                   phase[0], phase[1], phase[2]);
+    }
+    for (cudaEvent_t e : peer_marks) cudaEventDestroy(e);
     float ms = 0;
     PDLP_CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
     cudaEventDestroy(e0);

@@ -69,6 +69,12 @@ SolverResult ErrorSolverResult(int reason, const std::string& message);  // pdhg
 extern thread_local SolveCounters g_last_counters;
 
 class Solver;
+
+// K x / K^T y of the three points of a termination check when the caller already has them (Solver computes the
+// products of all points of a host event with one stream of each matrix copy); a null entry is computed where needed.
+struct ProductsOfPoint { const double* kx = nullptr; const double* kty = nullptr; };
+struct ProductsOfCheck { ProductsOfPoint current, average, difference; };
+
 class PreprocessSolver;
 
 // What the reference keeps in PresolveInfo (pdhg.cc:395-417) when Glop presolve ran: the original problem
@@ -97,15 +103,18 @@ class PreprocessSolver {
   // empty solution with `presolve_reason` (a TerminationReason) unless the point earns a better one.
   SolverResult FinishPresolvedOnly(const PrimalDualHybridGradientParams& params, int presolve_reason, const InterruptFlag* interrupt, IterationCallback callback);
 
+  using ProductsOfPoint = pdlp_b200::ProductsOfPoint;
+  using ProductsOfCheck = pdlp_b200::ProductsOfCheck;
   // pdhg.cc:1434-1518.  Points are device pointers; avg / delta may be null.
   std::optional<TerminationReasonAndPointType> UpdateIterationStatsAndCheckTermination(
       const PrimalDualHybridGradientParams& params, bool force_numerical_termination, const double* x_cur, const double* y_cur,
       const double* x_avg, const double* y_avg, const double* dx, const double* dy, const double* x_start, const double* y_start,
-      const InterruptFlag* interrupt, IterationType type, const IterationStats& full_stats, IterationStats& stats);
+      const InterruptFlag* interrupt, IterationType type, const IterationStats& full_stats, IterationStats& stats,
+      const ProductsOfCheck* products = nullptr);
   // pdhg.cc:1520-1564.
   void ComputeConvergenceAndInfeasibility(const PrimalDualHybridGradientParams& params, const double* x, const double* y, const double* x_start,
                                           const double* y_start, int candidate_type, ConvergenceInformation* ci, InfeasibilityInformation* ii,
-                                          PointMetadata* md);
+                                          PointMetadata* md, ProductsOfPoint products = {});
   // pdhg.cc:1568-1643.  x, y are device pointers into the scaled space.
   SolverResult ConstructOriginalSolverResult(const PrimalDualHybridGradientParams& params, const double* x, const double* y, SolveLog log);
 
@@ -185,7 +194,19 @@ class Solver {
 
   IterationStats CreateSimpleIterationStats(int restart_used) const;
   double DistanceTraveledFromLastStart(const double* x, const double* y);
-  Bounds BoundsAt(const double* x, const double* y, const double* kty_or_null);
+  Bounds BoundsAt(const double* x, const double* y, const double* kty_or_null, const double* kx_or_null);
+  // Host events (one GPU): K x of the current iterate, the average and the last difference, K^T y of the average and
+  // the difference - everything the restart bounds and the termination statistics of this event multiply by K - from
+  // ONE pass over the CSR copy and ONE over the CSC copy (pdlp_kkt.cu:ComputeProducts).  K^T y of the current iterate
+  // is the cached one.  Valid until the iterate changes (a restart, the next trial steps).
+  struct EventProducts {
+    bool valid = false;
+    const double* kx_cur = nullptr;
+    const double* kx_avg = nullptr; const double* kty_avg = nullptr;    // null: no average at this event
+    const double* kx_diff = nullptr; const double* kty_diff = nullptr;  // null: not a termination check, or no accepted step yet
+  } event_;
+  DVec event_m_[3], event_n_[2];
+  void PrepareEventProducts(const double* dx, const double* dy);
   Bounds BoundsAtCurrent();
   Bounds BoundsAtAverage();
   bool ShouldDoAdaptiveRestartHeuristic(double candidate_normalized_gap) const;

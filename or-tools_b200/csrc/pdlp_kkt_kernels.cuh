@@ -116,6 +116,33 @@ struct KktColOp : AlwaysActive {
   }
 };
 
+// Products of P vectors with one stream of the matrix (rowstream_multi_kernel): out[p][row] = sum val v[p][idx].
+template <int P>
+struct MultiDotOp : AlwaysActive {
+  static constexpr int kPoints = P;
+  const double* val; const int* idx;
+  const double* in[P]; double* out[P];
+  __device__ double Value(int64_t k) const { return val[k]; }
+  __device__ int Index(int64_t k) const { return idx[k]; }
+  __device__ double Gather(int point, int index) const { return in[point][index]; }
+  __device__ void Store(int point, int row, double sum) const { out[point][row] = sum; }
+};
+
+// The two epilogues as dense passes over a product that is already there (same code, same slots).  Every thread has
+// a row here, where the fused kernels run their epilogue on one lane per row: the vectors are read coalesced.
+struct KktRowMapOp : AlwaysActive {
+  static constexpr int kNumSlots = KktRowOp::kNumSlots;
+  __host__ __device__ static constexpr int SlotKindOf(int s) { return KktRowOp::SlotKindOf(s); }
+  KktRowOp row; const double* kx;
+  __device__ void Apply(int64_t i, Slots<kNumSlots>& r) const { row.RowFinish(static_cast<int>(i), kx[i], r); }
+};
+struct KktColMapOp : AlwaysActive {
+  static constexpr int kNumSlots = KktColOp::kNumSlots;
+  __host__ __device__ static constexpr int SlotKindOf(int s) { return KktColOp::SlotKindOf(s); }
+  KktColOp col; const double* kty;
+  __device__ void Apply(int64_t j, Slots<kNumSlots>& r) const { col.RowFinish(static_cast<int>(j), kty[j], r); }
+};
+
 struct ReducedCostOp : AlwaysActive, NoSlots {
   const double* val; const int* idx; const double* y;
   const double* x; const double* c; const double* q; const double* vlb; const double* vub; double* rc;

@@ -52,6 +52,14 @@ inline int EnqueueRowsPeer(Workspace& ws, const Op& op, const SparseRows& s, int
   unsigned long long epoch = 0;
   int grid = 0;
   if (shared_rows > 0) epoch = ws.comm->NextRowEpoch();  // the same on every rank
+  auto mark = [&]() {
+    if (ws.profile_peer == nullptr) return;
+    cudaEvent_t e;
+    PDLP_CUDA_CHECK(cudaEventCreate(&e));
+    PDLP_CUDA_CHECK(cudaEventRecord(e, ws.stream));
+    ws.profile_peer->push_back(e);
+  };
+  mark();
   if (shared_rows > 0 && shared_blocks > 0 && private_blocks > 0) {
     // One launch over the whole block: shared rows push, private rows finish in place (PeerCutRowOp).
     using Cut = PeerCutRowOp<Op>;
@@ -59,7 +67,9 @@ inline int EnqueueRowsPeer(Workspace& ws, const Op& op, const SparseRows& s, int
     cut_op.op = op; cut_op.view = view; cut_op.parity = static_cast<int>(epoch & 1); cut_op.cut_row = static_cast<int>(s.cut_row);
     grid = RowStreamGrid<Cut>(s);
     rowstream_kernel<Cut><<<grid, kBlock, 0, ws.stream>>>(cut_op, s.View(), partials);
+    mark();
     peer_signal_rows_kernel<<<1, 32, 0, ws.stream>>>(view, epoch);
+    mark();
     ws.launches += 2;
   } else {
     if (shared_rows > 0) {
@@ -86,6 +96,7 @@ inline int EnqueueRowsPeer(Workspace& ws, const Op& op, const SparseRows& s, int
     ++ws.launches;
     grid += g;
   }
+  mark();
   return grid > 0 ? grid : 1;
 }
 

@@ -57,6 +57,8 @@ struct Workspace {
   // One GPU, a solve with an interrupt flag: the host-mapped copy of the flag that the decision kernel reads (pdlp_step_state.h).
   // The enqueue loops stop queueing trial steps once it is up.  Null otherwise.
   const volatile int* stop_enqueue = nullptr;
+  // PDLP_B200_DEBUG_TIMING under pdlp_b200_trial_steps_profiled: events around the three launches of a peer-mode CSR pass.
+  std::vector<cudaEvent_t>* profile_peer = nullptr;
   int64_t SkipBelow(Side side) const { return side == Side::kDual ? dual_skip_below : 0; }
   void Init(int64_t n_, int64_t m_);
   void Destroy();
@@ -128,6 +130,20 @@ struct KktTotals {
 // and ComputeInfeasibilityInformation need for the point (x, y).
 KktTotals ComputeKktTotals(Workspace& ws, const DeviceProblem& p, const double* x, const double* y, const double* x_start, const double* y_start,
                            double cw_primal_offset, double cw_dual_offset, bool handle_some_primal_gradients_on_finite_bounds_as_residuals);
+// K x and K^T y of up to three points with ONE stream of each matrix copy (rowstream_multi_kernel): what a host
+// event needs of the current iterate, the average and the last difference at once.  Every sum is bit-identical to
+// the one a single-point pass forms.  One GPU only (a sharded CSR pass needs its exchange).
+struct PointProducts {
+  const double* x = nullptr;  // n entries (null: no K x wanted for this point)
+  const double* y = nullptr;  // m entries (null: no K^T y wanted)
+  double* kx = nullptr;       // out, m entries
+  double* kty = nullptr;      // out, n entries
+};
+void ComputeProducts(Workspace& ws, const DeviceProblem& p, const PointProducts* points, int count);
+// ComputeKktTotals from products that are already there: two dense passes.
+KktTotals ComputeKktTotalsFromProducts(Workspace& ws, const DeviceProblem& p, const double* x, const double* y, const double* x_start, const double* y_start,
+                                       const double* kx, const double* kty, double cw_primal_offset, double cw_dual_offset,
+                                       bool handle_some_primal_gradients_on_finite_bounds_as_residuals);
 // iteration_stats.cc:533-565; rc must not alias x.
 void ComputeReducedCosts(Workspace& ws, const DeviceProblem& p, const double* x, const double* y, bool zero_objective,
                          bool handle_some_primal_gradients_on_finite_bounds_as_residuals, double* rc);
@@ -138,7 +154,8 @@ double SquaredDistance(Workspace& ws, const double* a, const double* b, int64_t 
 // weighted distance of (x, y) from it (pdhg.cc:1795-1804), reduced inside the gradient passes, and `radius` is ignored.
 LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProblem& p, const double* x, const double* y, const double* kty_or_null,
                                                  double primal_weight, double radius, bool use_diagonal_qp_solver, double diagonal_qp_tolerance,
-                                                 int* tr_passes, bool max_norm = false, const double* x_start = nullptr, const double* y_start = nullptr);
+                                                 int* tr_passes, bool max_norm = false, const double* x_start = nullptr, const double* y_start = nullptr,
+                                                 const double* kx_or_null = nullptr);  // K x when the caller has it: no pass over the matrix
 
 // K v from caller-owned device CSR arrays with the work-block table in a static device array
 // (pdlp_noalloc.cu; the kernel side of pdlp_b200_matvec_no_alloc, which has no counterpart in the reference).

@@ -374,7 +374,8 @@ SolverResult PreprocessSolver::PreprocessAndSolve(const PrimalDualHybridGradient
 // pdhg.cc:1520-1564 + iteration_stats.cc:349-518, assembled from the fused totals.
 void PreprocessSolver::ComputeConvergenceAndInfeasibility(const PrimalDualHybridGradientParams& params, const double* x, const double* y,
                                                           const double* x_start, const double* y_start, int candidate_type,
-                                                          ConvergenceInformation* ci, InfeasibilityInformation* ii, PointMetadata* md) {
+                                                          ConvergenceInformation* ci, InfeasibilityInformation* ii, PointMetadata* md,
+                                                          ProductsOfPoint products) {
   const DetailedOptimalityCriteria oc = EffectiveOptimalityCriteria(params.termination_criteria.get());
   const double primal_ratio = EpsilonRatio(oc.eps_optimal_primal_residual_absolute, oc.eps_optimal_primal_residual_relative);
   const double dual_ratio = EpsilonRatio(oc.eps_optimal_dual_residual_absolute, oc.eps_optimal_dual_residual_relative);
@@ -388,8 +389,10 @@ void PreprocessSolver::ComputeConvergenceAndInfeasibility(const PrimalDualHybrid
     ci = nullptr;
     ii = nullptr;
   }
-  const KktTotals t = ComputeKktTotals(ws_, problem_, x, y, x_start, y_start, primal_ratio, dual_ratio,
-                                       params.handle_some_primal_gradients_on_finite_bounds_as_residuals);
+  const bool flag = params.handle_some_primal_gradients_on_finite_bounds_as_residuals;
+  const bool have_products = !comm_.sharded() && (products.kx != nullptr || problem_.m == 0) && (products.kty != nullptr || problem_.n == 0);
+  const KktTotals t = have_products ? ComputeKktTotalsFromProducts(ws_, problem_, x, y, x_start, y_start, products.kx, products.kty, primal_ratio, dual_ratio, flag)
+                                    : ComputeKktTotals(ws_, problem_, x, y, x_start, y_start, primal_ratio, dual_ratio, flag);
   auto apply = [&](double v) { return problem_.objective_scaling_factor * (v + problem_.objective_offset); };
   if (ci != nullptr) {
     ci->l_inf_primal_residual = t.primal_res_linf;
@@ -495,19 +498,21 @@ void PreprocessSolver::AddRandomProjections(const double* x, const double* y, Po
 std::optional<TerminationReasonAndPointType> PreprocessSolver::UpdateIterationStatsAndCheckTermination(
     const PrimalDualHybridGradientParams& params, bool force_numerical_termination, const double* x_cur, const double* y_cur, const double* x_avg,
     const double* y_avg, const double* dx, const double* dy, const double* x_start, const double* y_start, const InterruptFlag* interrupt,
-    IterationType type, const IterationStats& full_stats, IterationStats& stats) {
-  auto add_point = [&](const double* x, const double* y, int point_type, bool convergence) {
+    IterationType type, const IterationStats& full_stats, IterationStats& stats, const ProductsOfCheck* products) {
+  auto add_point = [&](const double* x, const double* y, int point_type, bool convergence, ProductsOfPoint of_point) {
     ConvergenceInformation ci;
     InfeasibilityInformation ii;
     PointMetadata md;
-    ComputeConvergenceAndInfeasibility(params, x, y, x_start, y_start, point_type, convergence ? &ci : nullptr, &ii, &md);
+    ComputeConvergenceAndInfeasibility(params, x, y, x_start, y_start, point_type, convergence ? &ci : nullptr, &ii, &md, of_point);
     if (convergence) stats.convergence_information.push_back(ci);
     stats.infeasibility_information.push_back(ii);
     stats.point_metadata.push_back(md);
   };
-  add_point(x_cur, y_cur, POINT_TYPE_CURRENT_ITERATE, true);
-  if (x_avg != nullptr && y_avg != nullptr) add_point(x_avg, y_avg, POINT_TYPE_AVERAGE_ITERATE, true);
-  if (dx != nullptr && dy != nullptr) add_point(dx, dy, POINT_TYPE_ITERATE_DIFFERENCE, false);
+  const ProductsOfCheck none;
+  const ProductsOfCheck& have = products != nullptr ? *products : none;
+  add_point(x_cur, y_cur, POINT_TYPE_CURRENT_ITERATE, true, have.current);
+  if (x_avg != nullptr && y_avg != nullptr) add_point(x_avg, y_avg, POINT_TYPE_AVERAGE_ITERATE, true, have.average);
+  if (dx != nullptr && dy != nullptr) add_point(dx, dy, POINT_TYPE_ITERATE_DIFFERENCE, false, have.difference);
   if (Logs(params, 2)) {  // :1471-1501
     constexpr int kLogEvery = 15;
     const double now = std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();

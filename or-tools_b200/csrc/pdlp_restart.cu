@@ -25,19 +25,20 @@ struct DeviceRunner {
   template <class Op> const double* CsrRows(const Op& op) { return RunRows(ws, op, p.K.by_row); }
   void ColumnDot(const double* y, double* out) { RowDot(ws, p.K.by_col, y, out); }
   template <class Op> const double* Primal(const Op& op, int64_t count) { return RunMap(ws, op, count, Side::kSharded); }
+  template <class Op> const double* Dual(const Op& op, int64_t count) { return RunMap(ws, op, count, Side::kDual); }
   template <class Op> const double* Joint(const Op& op, int64_t count) { return RunMap(ws, op, count, Side::kJoint); }
 };
 }  // namespace
 
 LocalizedBounds ComputeLocalizedLagrangianBounds(Workspace& ws, const DeviceProblem& p, const double* x, const double* y, const double* kty_or_null,
                                                  double primal_weight, double radius, bool use_diagonal_qp_solver, double diagonal_qp_tolerance,
-                                                 int* tr_passes, bool max_norm, const double* x_start, const double* y_start) {
+                                                 int* tr_passes, bool max_norm, const double* x_start, const double* y_start, const double* kx_or_null) {
   const SparseRows& csr = p.K.by_row;
   const RestartProblemView view{csr.val.get(), csr.idx.get(), p.c.get(), p.q_or_null(), p.vlb.get(), p.vub.get(), p.clb.get(), p.cub.get(), p.n, p.m, p.is_lp,
                                 ws.dual_skip_below, ws.scratch_n[0].get(), ws.scratch_m[0].get(), ws.scratch_n[1].get(), ws.scratch_nm[0].get(),
                                 ws.scratch_nm[1].get()};
   DeviceRunner run{ws, p};
-  return LocalizedLagrangianBoundsWith(run, view, x, y, kty_or_null, primal_weight, radius, use_diagonal_qp_solver, diagonal_qp_tolerance, tr_passes, max_norm, x_start, y_start);
+  return LocalizedLagrangianBoundsWith(run, view, x, y, kty_or_null, primal_weight, radius, use_diagonal_qp_solver, diagonal_qp_tolerance, tr_passes, max_norm, x_start, y_start, kx_or_null);
 }
 
 }  // namespace pdlp_b200

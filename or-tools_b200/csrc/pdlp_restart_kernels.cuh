@@ -107,6 +107,13 @@ struct DualGradOp : AlwaysActive, GradientSlots {
   }
 };
 
+// The same epilogue as a dense pass when K x is already there (a host event computes the products of all its points
+// with one stream of the matrix, pdlp_kkt.cu:ComputeProducts).
+struct DualGradMapOp : AlwaysActive, GradientSlots {
+  DualGradOp row; const double* kx;
+  __device__ void Apply(int64_t i, Slots<6>& r) const { row.RowFinish(static_cast<int>(i), kx[i], r); }
+};
+
 // ComputePrimalGradient (sou.cc:446-474).
 __device__ __forceinline__ double PrimalGradAt(double xj, double cj, const double* q, int64_t j, double kty, double* value) {
   if (q == nullptr) {
@@ -256,13 +263,15 @@ struct RestartProblemView {
 //   const double* CsrRows(op)                 row-stream pass over the CSR copy
 //   void ColumnDot(y, out)                    out = K^T y (row-stream pass over the CSC copy)
 //   const double* Primal(op, count)           dense pass over this rank's columns
+//   const double* Dual(op, count)             dense pass over this rank's rows
 //   const double* Joint(op, count)            dense pass over (columns, rows)
 // x_start / y_start (both or neither): the radius is the weighted distance of (x, y) from that point
 // (DistanceTraveledFromLastStart, pdhg.cc:1795-1804), reduced inside the two gradient passes; `radius` is then ignored.
 template <class Runner>
 LocalizedBounds LocalizedLagrangianBoundsWith(Runner& run, const RestartProblemView& p, const double* x, const double* y, const double* kty_or_null,
                                               double primal_weight, double radius, bool use_diagonal_qp_solver, double diagonal_qp_tolerance,
-                                              int* tr_passes, bool max_norm = false, const double* x_start = nullptr, const double* y_start = nullptr) {
+                                              int* tr_passes, bool max_norm = false, const double* x_start = nullptr, const double* y_start = nullptr,
+                                              const double* kx_or_null = nullptr) {
   double* gx = p.gx;
   double* gy = p.gy;
   // The default solver (joint problem, linear-time root search) takes its critical step sizes from the gradient passes.
@@ -270,8 +279,9 @@ LocalizedBounds LocalizedLagrangianBoundsWith(Runner& run, const RestartProblemV
   auto totals_of = [](const double* h) { return GradientTotals{h[0], h[1], h[2], h[3], h[4], h[5]}; };
   GradientTotals primal, dual;
   if (p.m > 0) {
-    dual = totals_of(run.CsrRows(DualGradOp{{}, {}, p.csr_val, p.csr_idx, x, y, p.clb, p.cub, gy, static_cast<int>(p.dual_skip_below), y_start,
-                                            fused ? p.crit + p.n : nullptr, fused ? p.coef + p.n : nullptr, 0.5 / primal_weight}));
+    const DualGradOp row{{}, {}, p.csr_val, p.csr_idx, x, y, p.clb, p.cub, gy, static_cast<int>(p.dual_skip_below), y_start,
+                         fused ? p.crit + p.n : nullptr, fused ? p.coef + p.n : nullptr, 0.5 / primal_weight};
+    dual = totals_of(kx_or_null != nullptr ? run.Dual(DualGradMapOp{{}, {}, row, kx_or_null}, p.m) : run.CsrRows(row));
   }
   if (p.n > 0) {
     // When K^T y is not cached it is computed first; the gradient and its value then come

@@ -405,6 +405,83 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
   BlockReduceAndStore<Op>(red, partials);
 }
 
+// ---- skeleton 2b: several products with ONE stream of the matrix ----
+// out_p[row] = sum_k val[k] v_p[idx[k]] for p = 0 .. kPoints - 1.  A thread keeps its nonzeros' values and indices in
+// registers and the work block is staged, reduced and stored once per point, so the matrix (12 bytes per nonzero, the
+// bulk of a pass) is read once and only the gathers - served by L1 / L2 - repeat.  Used at host events, where the
+// termination statistics and the restart bounds need K x and K^T y of the current iterate, the average and the last
+// difference at the same time (pdlp_kkt.cu).  Every row sum is formed exactly as rowstream_kernel forms it (same
+// threads per row, same order of additions, same shuffle tree), so the sums are bit-identical to single passes.
+// Op interface: kPoints; Begin(); double Value(int64_t k); int Index(int64_t k); double Gather(int point, int index);
+//               void Store(int point, int row, double sum).
+template <class Op>
+__global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_multi_kernel(const Op op_in, RowBlocks rb) {
+  __shared__ double staged[kStagedSize];
+  __shared__ int row_raw[kMaxRowsPerBlock + 1];
+  __shared__ double long_row_buf[kBlock / 32];
+  Op op = op_in;
+  if (!op.Begin()) return;
+  for (int b = blockIdx.x; b < rb.num_blocks; b += gridDim.x) {
+    const int r0 = rb.block_start[b], r1 = rb.block_start[b + 1];
+    const int p0 = rb.block_nz[b], p1 = rb.block_nz[b + 1];
+    const int nz = p1 - p0, nrows = r1 - r0;
+    if (nz > kStreamChunk) {
+      // One long row: CTA-wide strided reduce per point (the row's values come from L2 after the first point).
+#pragma unroll
+      for (int pt = 0; pt < Op::kPoints; ++pt) {
+        double a = 0.0;
+        for (int k = p0 + threadIdx.x; k < p1; k += kBlock) a = a + op.Value(k) * op.Gather(pt, op.Index(k));
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) a = a + __shfl_xor_sync(0xffffffffu, a, off);
+        if ((threadIdx.x & 31) == 0) long_row_buf[threadIdx.x >> 5] = a;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+          double t = long_row_buf[0];
+          for (int w = 1; w < kBlock / 32; ++w) t = t + long_row_buf[w];
+          op.Store(pt, r0, t);
+        }
+        __syncthreads();
+      }
+      continue;
+    }
+    double v[kPerThread];
+    int jx[kPerThread];
+#pragma unroll
+    for (int i = 0; i < kPerThread; ++i) {
+      const int k = threadIdx.x + i * kBlock;
+      v[i] = k < nz ? op.Value(p0 + k) : 0.0;
+      jx[i] = k < nz ? op.Index(p0 + k) : 0;
+    }
+    for (int i = threadIdx.x; i <= nrows; i += kBlock) row_raw[i] = rb.row_ptr[r0 + i];
+    const int shift = BankPadFor(nz, nrows);
+    int log_t = 0;
+    while (log_t < 5 && (2 << log_t) * nrows <= kBlock) ++log_t;
+    const int t = 1 << log_t;
+    const int sub = threadIdx.x >> log_t, lane = threadIdx.x & (t - 1);
+    const int groups = kBlock >> log_t;
+#pragma unroll
+    for (int pt = 0; pt < Op::kPoints; ++pt) {
+#pragma unroll
+      for (int i = 0; i < kPerThread; ++i) {
+        const int k = threadIdx.x + i * kBlock;
+        if (k < nz) staged[Skew(k, shift)] = v[i] * op.Gather(pt, jx[i]);
+      }
+      __syncthreads();
+      for (int base = 0; base < nrows; base += groups) {
+        const int rr = base + sub;
+        double a = 0.0;
+        if (rr < nrows) {
+          const int q1 = row_raw[rr + 1] - p0;
+          for (int q = row_raw[rr] - p0 + lane; q < q1; q += t) a = a + staged[Skew(q, shift)];
+        }
+        for (int off = t >> 1; off > 0; off >>= 1) a = a + __shfl_xor_sync(0xffffffffu, a, off);
+        if (lane == 0 && rr < nrows) op.Store(pt, r0 + rr, a);
+      }
+      __syncthreads();
+    }
+  }
+}
+
 // ---- the two phases of a column-sharded pass over the CSR block (launched by
 // pdlp_launch.cuh:EnqueueRows around the all-reduce of the shared rows' sums) ----
 // An op whose row accumulator combines with max instead of + declares `bool RowCombineMax() const`.

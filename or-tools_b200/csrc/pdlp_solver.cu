@@ -208,21 +208,54 @@ double Solver::DistanceTraveledFromLastStart(const double* x, const double* y) {
   return std::sqrt((0.5 * host_.primal_weight) * dp + (0.5 / host_.primal_weight) * dd);
 }
 
-Solver::Bounds Solver::BoundsAt(const double* x, const double* y, const double* kty_or_null) {
+Solver::Bounds Solver::BoundsAt(const double* x, const double* y, const double* kty_or_null, const double* kx_or_null) {
   // The radius (DistanceTraveledFromLastStart) comes out of the same passes as the gradients.
   int tr_passes = 0;
   const LocalizedBounds b = ComputeLocalizedLagrangianBounds(ws_, problem_, x, y, kty_or_null, host_.primal_weight, 0.0, params_.use_diagonal_qp_trust_region_solver,
-                                                             params_.diagonal_qp_trust_region_solver_tolerance, &tr_passes, false, it_.x_start.get(), it_.y_start.get());
+                                                             params_.diagonal_qp_trust_region_solver_tolerance, &tr_passes, false, it_.x_start.get(), it_.y_start.get(),
+                                                             kx_or_null);
   phase_.bounds += 1;
   phase_.tr_passes += tr_passes;
   return {b.lagrangian_value, b.lower_bound, b.upper_bound, b.radius};
 }
-Solver::Bounds Solver::BoundsAtCurrent() { return BoundsAt(X(), Y(), Kty()); }                          // pdhg.cc:1806-1816
+Solver::Bounds Solver::BoundsAtCurrent() { return BoundsAt(X(), Y(), Kty(), event_.valid ? event_.kx_cur : nullptr); }  // pdhg.cc:1806-1816
 Solver::Bounds Solver::BoundsAtAverage() {  // pdhg.cc:1818-1834
-  const Bounds b = BoundsAt(PrimalAverage(), DualAverage(), nullptr);
-  // K^T y of the dual average is now in the bounds' scratch vector: a restart to the average at this event copies it.
-  kty_of_average_at_ = (problem_.n > 0 && host_.avg_weight_sum > 0.0 && host_.avg_weight_sum_dual > 0.0) ? iterations_completed_ : -1;
+  const bool has_primal = host_.avg_weight_sum > 0.0, has_dual = host_.avg_weight_sum_dual > 0.0;
+  // The event's products are those of (avg_x, avg_y); a side without weight falls back to the current iterate's.
+  const double* kx = !event_.valid ? nullptr : (has_primal ? event_.kx_avg : event_.kx_cur);
+  const double* kty = !event_.valid ? nullptr : (has_dual ? event_.kty_avg : Kty());
+  const Bounds b = BoundsAt(PrimalAverage(), DualAverage(), kty, kx);
+  // Without the event's products K^T y of the dual average is now in the bounds' scratch vector: a restart to the
+  // average at this event copies it from there (or from the event's products).
+  kty_of_average_at_ = (kty == nullptr && problem_.n > 0 && has_primal && has_dual) ? iterations_completed_ : -1;
   return b;
+}
+
+// One pass over each copy of K for every product this host event needs (one GPU; see EventProducts).
+void Solver::PrepareEventProducts(const double* dx, const double* dy) {
+  event_ = EventProducts{};
+  if (pre_->sharded() || problem_.n == 0 || problem_.m == 0) return;
+  const bool has_avg = host_.avg_weight_sum > 0.0 && host_.avg_weight_sum_dual > 0.0;
+  if (event_m_[0].size() == 0) {
+    for (DVec& v : event_m_) v.Resize(problem_.m);
+    for (DVec& v : event_n_) v.Resize(problem_.n);
+  }
+  PointProducts points[3];
+  int count = 0;
+  points[count++] = PointProducts{X(), nullptr, event_m_[0].get(), nullptr};  // K^T y of the current iterate is cached
+  event_.kx_cur = event_m_[0].get();
+  if (has_avg) {
+    points[count++] = PointProducts{it_.avg_x.get(), it_.avg_y.get(), event_m_[1].get(), event_n_[0].get()};
+    event_.kx_avg = event_m_[1].get();
+    event_.kty_avg = event_n_[0].get();
+  }
+  if (dx != nullptr && dy != nullptr) {
+    points[count++] = PointProducts{dx, dy, event_m_[2].get(), event_n_[1].get()};
+    event_.kx_diff = event_m_[2].get();
+    event_.kty_diff = event_n_[1].get();
+  }
+  ComputeProducts(ws_, problem_, points, count);
+  event_.valid = true;
 }
 
 bool Solver::ShouldDoAdaptiveRestartHeuristic(double candidate_normalized_gap) const {  // pdhg.cc:1853-1867
@@ -314,8 +347,14 @@ void Solver::ApplyRestartChoice(int restart_to_apply) {  // pdhg.cc:2042-2094
       CopyVector(ws_, it_.y[host_.cur].get(), it_.avg_y.get(), problem_.m);
       // K^T y of the new current iterate: the same product, by the same kernel over the same values, that the restart
       // choice of this event left in the bounds' scratch vector (nothing between here and there writes scratch_n[1]).
-      if (kty_of_average_at_ == iterations_completed_) CopyVector(ws_, it_.kty[host_.cur].get(), ws_.scratch_n[1].get(), problem_.n);
-      else RowDot(ws_, problem_.K.by_col, it_.y[host_.cur].get(), it_.kty[host_.cur].get());
+      if (event_.valid && event_.kty_avg != nullptr) {
+        CopyVector(ws_, it_.kty[host_.cur].get(), event_.kty_avg, problem_.n);
+        event_.kx_cur = event_.kx_avg;  // the current iterate IS the average now: the bounds below reuse its K x
+      } else {
+        event_.valid = false;
+        if (kty_of_average_at_ == iterations_completed_) CopyVector(ws_, it_.kty[host_.cur].get(), ws_.scratch_n[1].get(), problem_.n);
+        else RowDot(ws_, problem_.K.by_col, it_.y[host_.cur].get(), it_.kty[host_.cur].get());
+      }
       break;
   }
   kty_of_average_at_ = -1;
@@ -380,6 +419,28 @@ std::optional<Solver::Outcome> Solver::MajorIterationAndTerminationCheck(Iterati
   const int major_iteration_cycle = iterations_completed_ % params_.major_iteration_frequency;
   const bool is_major_iteration = major_iteration_cycle == 0 && iterations_completed_ > 0;
   const double t_begin = timer_.Get();
+  // What this event will multiply by K: the termination check its three points, the restart choice the current iterate
+  // and the average.  All of it comes from one pass over each matrix copy, made first (one GPU).  The predicates below
+  // only decide what is computed ahead; a product that turns out to be missing is computed where it is needed.
+  const double* dx = nullptr;
+  const double* dy = nullptr;
+  {
+    const IterationStats preview = AddWorkStats(CreateSimpleIterationStats(RESTART_CHOICE_NO_RESTART), work_from_feasibility_polishing);
+    const bool will_check = major_iteration_cycle % params_.termination_check_frequency == 0 || force_numerical_termination ||
+                            CheckSimpleTerminationCriteria(params_.termination_criteria.get(), preview, interrupt).has_value();
+    const bool has_weight = host_.avg_weight_sum > 0.0 || host_.avg_weight_sum_dual > 0.0;
+    const bool will_bound = !force_numerical_termination && has_weight && params_.restart_strategy == ADAPTIVE_HEURISTIC &&
+                            (is_major_iteration || host_.avg_num_terms >= iterations_completed_ / 2);
+    if (will_check && have_delta_) {
+      double* dxb = ws_.scratch_n[2].get();
+      double* dyb = ws_.scratch_m[2].get();
+      SubtractVectors(ws_, dxb, it_.x[host_.cur].get(), it_.x[host_.cur ^ 1].get(), problem_.n);
+      SubtractVectors(ws_, dyb, it_.y[host_.cur].get(), it_.y[host_.cur ^ 1].get(), problem_.m);
+      dx = dxb; dy = dyb;
+    }
+    if (will_check || will_bound) PrepareEventProducts(dx, dy);
+    else event_ = EventProducts{};
+  }
   const int restart = force_numerical_termination ? static_cast<int>(RESTART_CHOICE_NO_RESTART) : ChooseRestartToApply(is_major_iteration);
   const double t_chosen = timer_.Get();
   phase_.events += 1;
@@ -391,18 +452,22 @@ std::optional<Solver::Outcome> Solver::MajorIterationAndTerminationCheck(Iterati
                                  force_numerical_termination;
   if (check_termination) {
     const bool has_avg = host_.avg_weight_sum > 0.0 && host_.avg_weight_sum_dual > 0.0;
-    const double* dx = nullptr;
-    const double* dy = nullptr;
-    if (have_delta_) {
+    if (have_delta_ && dx == nullptr) {  // a limit was reached between the preview and here
       double* dxb = ws_.scratch_n[2].get();
       double* dyb = ws_.scratch_m[2].get();
       SubtractVectors(ws_, dxb, it_.x[host_.cur].get(), it_.x[host_.cur ^ 1].get(), problem_.n);
       SubtractVectors(ws_, dyb, it_.y[host_.cur].get(), it_.y[host_.cur ^ 1].get(), problem_.m);
       dx = dxb; dy = dyb;
     }
+    PreprocessSolver::ProductsOfCheck products;
+    if (event_.valid) {
+      products.current = {event_.kx_cur, Kty()};
+      if (has_avg) products.average = {event_.kx_avg, event_.kty_avg};
+      products.difference = {event_.kx_diff, event_.kty_diff};
+    }
     const auto maybe_reason = pre_->UpdateIterationStatsAndCheckTermination(
         params_, force_numerical_termination, X(), Y(), has_avg ? it_.avg_x.get() : nullptr, has_avg ? it_.avg_y.get() : nullptr, dx, dy,
-        it_.x_start.get(), it_.y_start.get(), interrupt, type, full_work_stats, stats);
+        it_.x_start.get(), it_.y_start.get(), interrupt, type, full_work_stats, stats, &products);
     if (params_.record_iteration_stats) log.iteration_stats.push_back(stats);
     phase_.checks += 1;
     phase_.termination += timer_.Get() - t_chosen;
@@ -420,6 +485,7 @@ std::optional<Solver::Outcome> Solver::MajorIterationAndTerminationCheck(Iterati
     phase_.restarts += 1;
     phase_.apply_restart += timer_.Get() - t_checked;
   }
+  event_ = EventProducts{};  // the iterate moves on
   return std::nullopt;
 }
 

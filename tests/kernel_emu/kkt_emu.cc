@@ -51,3 +51,34 @@ extern "C" int emu_reduced_costs(int n, const int* csc_ptr, const int* csc_idx, 
   RunRows(ReducedCostOp{{}, {}, csc_val, csc_idx, y, x, c, q, vlb, vub, rc, zero_objective, flag}, csc.View(), max_grid, nullptr);
   return 0;
 }
+
+// The split form of the same statistics (pdlp_kkt.cu: ComputeProducts + ComputeKktTotalsFromProducts): K x and K^T y
+// of THREE points - (x, y), (x_other, y_other), (x_start, y_start) - by rowstream_multi_kernel with one stream of each
+// matrix copy, then the two dense epilogue passes for the first point.  kx_out: 3 m doubles, kty_out: 3 n doubles.
+extern "C" int emu_kkt_totals_split(int n, int m, const int* csr_ptr, const int* csr_idx, const double* csr_val, const int* csr_blocks, int csr_num_blocks,
+                                    const int* csc_ptr, const int* csc_idx, const double* csc_val, const int* csc_blocks, int csc_num_blocks, const double* c,
+                                    const double* q, const double* vlb, const double* vub, const double* clb, const double* cub, const double* row_scale,
+                                    const double* col_scale, const double* x, const double* y, const double* x_start, const double* y_start, double cw_primal_offset,
+                                    double cw_dual_offset, int flag, int max_grid, const double* x_other, const double* y_other, double* row_totals, double* col_totals,
+                                    double* kx_out, double* kty_out) {
+  cuda_emu::defer_async = false;
+  HostRows csr{csr_ptr, csr_idx, csr_val, csr_blocks, csr_num_blocks, m, {}};
+  HostRows csc{csc_ptr, csc_idx, csc_val, csc_blocks, csc_num_blocks, n, {}};
+  const RowBlocks by_row = csr.View(), by_col = csc.View();
+  MultiDotOp<3> rows{{}, csr_val, csr_idx, {x, x_other, x_start}, {kx_out, kx_out + m, kx_out + 2 * m}};
+  MultiDotOp<3> cols{{}, csc_val, csc_idx, {y, y_other, y_start}, {kty_out, kty_out + n, kty_out + 2 * n}};
+  const int grid_r = std::max(1, std::min(by_row.num_blocks, max_grid)), grid_c = std::max(1, std::min(by_col.num_blocks, max_grid));
+  cuda_emu::Launch(grid_r, kBlock, [=]() { rowstream_multi_kernel<MultiDotOp<3>>(rows, by_row); });
+  cuda_emu::Launch(grid_c, kBlock, [=]() { rowstream_multi_kernel<MultiDotOp<3>>(cols, by_col); });
+  auto run_map = [&](auto op, int64_t count, double* totals) {
+    using Op = decltype(op);
+    const int grid = GridFor(count);
+    std::vector<double> partials(static_cast<size_t>(grid) * Op::kNumSlots, 0.0);
+    double* p = partials.data();
+    cuda_emu::Launch(grid, kBlock, [=]() { map_reduce_kernel<Op>(op, count, p); });
+    cuda_emu::Launch(1, kBlock, [=]() { finalize_kernel<Op>(p, grid, totals); });
+  };
+  run_map(KktRowMapOp{{}, KktRowOp{{}, csr_val, csr_idx, x, y, y_start, row_scale, clb, cub, cw_primal_offset, 0}, kx_out}, m, row_totals);
+  run_map(KktColMapOp{{}, KktColOp{{}, csc_val, csc_idx, y, x, x_start, col_scale, c, q, vlb, vub, cw_dual_offset, flag}, kty_out}, n, col_totals);
+  return 0;
+}

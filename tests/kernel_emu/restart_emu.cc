@@ -57,6 +57,8 @@ struct EmuRunner {
   const double* Primal(const Op& op, int64_t count) { return Map(op, count); }
   template <class Op>
   const double* Joint(const Op& op, int64_t count) { return Map(op, count); }
+  template <class Op>
+  const double* Dual(const Op& op, int64_t count) { return Map(op, count); }
 };
 }  // namespace
 
@@ -67,6 +69,9 @@ extern "C" void emu_set_max_norm(int on) { g_max_norm = on; }
 // The next emu_localized_bounds calls take their radius from the distance to this point (null, null: from the argument).
 static const double* g_x_start = nullptr;
 static const double* g_y_start = nullptr;
+// The next calls hand the bounds a precomputed K x (the host-event path: one multi-point pass computes it, pdlp_kkt.cu).
+static int g_precomputed_kx = 0;
+extern "C" void emu_set_precomputed_kx(int on) { g_precomputed_kx = on; }
 extern "C" void emu_set_start_point(const double* x_start, const double* y_start) { g_x_start = x_start; g_y_start = y_start; }
 
 extern "C" int emu_localized_bounds(int n, int m, const int* csr_ptr, const int* csr_idx, const double* csr_val, const int* csr_blocks, int csr_num_blocks,
@@ -82,7 +87,18 @@ extern "C" int emu_localized_bounds(int n, int m, const int* csr_ptr, const int*
   std::vector<double> gx(std::max(n, 1)), gy(std::max(m, 1)), kty(std::max(n, 1)), crit(n + m + 1), coef(n + m + 1);
   const RestartProblemView view{csr_val, csr_idx, c, q, vlb, vub, clb, cub, n, m, q == nullptr, 0, gx.data(), gy.data(), kty.data(), crit.data(), coef.data()};
   int passes = 0;
-  const LocalizedBounds b = LocalizedLagrangianBoundsWith(run, view, x, y, nullptr, primal_weight, radius, use_diagonal_qp_solver != 0, tolerance, &passes, g_max_norm != 0, g_x_start, g_y_start);
+  std::vector<double> kx(std::max(m, 1), 0.0);
+  if (g_precomputed_kx != 0) {
+    for (int i = 0; i < m; ++i) {
+      double a = 0.0;
+      for (int k = csr_ptr[i]; k < csr_ptr[i + 1]; ++k) a += csr_val[k] * x[csr_idx[k]];
+      kx[i] = a;
+    }
+  }
+  const int launches_before = run.launches;
+  const LocalizedBounds b = LocalizedLagrangianBoundsWith(run, view, x, y, nullptr, primal_weight, radius, use_diagonal_qp_solver != 0, tolerance, &passes, g_max_norm != 0, g_x_start, g_y_start,
+                                                          g_precomputed_kx != 0 ? kx.data() : nullptr);
+  (void)launches_before;
   out[0] = b.lagrangian_value; out[1] = b.lower_bound; out[2] = b.upper_bound; out[3] = b.radius; out[4] = passes;
   return 0;
 }

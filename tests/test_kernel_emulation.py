@@ -597,6 +597,24 @@ def test_kkt_passes_match_the_oracles_convergence_and_infeasibility_information(
                                      zero_objective, int(flag), 3, p(rc)) == 0
         np.testing.assert_allclose(rc, oracle.reduced_costs(params, x, y, bool(zero_objective)), rtol=1e-11, atol=1e-12)
 
+    # The split form used at host events (pdlp_kkt.cu: ComputeProducts + ComputeKktTotalsFromProducts): K x and K^T y of
+    # THREE points with one stream of each matrix copy, then dense epilogue passes.  Every row sum is formed as the
+    # single-point kernel forms it; the reduction slots add the same per-row terms in another order (a thread per row
+    # instead of a lane per row group), so the totals agree to rounding and the max slots exactly.
+    x_other, y_other = f64(rng.standard_normal(n)), f64(rng.standard_normal(m))
+    r2, t2, kx, kty = np.zeros(9), np.zeros(15), np.zeros(3 * m), np.zeros(3 * n)
+    assert lib.emu_kkt_totals_split(n, m, p(arr[0]), p(arr[1]), p(arr[2]), p(rb), len(rb) - 1, p(arc[0]), p(arc[1]), p(arc[2]), p(cb), len(cb) - 1, *[p(v) for v in vec],
+                                    ctypes.c_double(cw_p), ctypes.c_double(cw_d), int(flag), 3, p(x_other), p(y_other), p(r2), p(t2), p(kx), p(kty)) == 0
+    np.testing.assert_allclose(r2, r, rtol=1e-13, atol=0)
+    np.testing.assert_allclose(t2, t, rtol=1e-13, atol=0)
+    for s in (1, 2, 4, 6):
+        assert r2[s] == r[s]  # max slots
+    for s in (4, 6, 7, 10, 11, 12):
+        assert t2[s] == t[s]
+    for k, (xv, yv) in enumerate(((vec[8], vec[9]), (x_other, y_other), (vec[10], vec[11]))):
+        np.testing.assert_allclose(kx[k * m:(k + 1) * m], csr @ xv, rtol=1e-12, atol=1e-12)
+        np.testing.assert_allclose(kty[k * n:(k + 1) * n], csc.T @ yv, rtol=1e-12, atol=1e-12)
+
 
 # ---- restart criteria: localized Lagrangian bounds against the oracle ----
 
@@ -661,12 +679,14 @@ def test_localized_lagrangian_bounds_match_the_oracle(qp_case, diagonal):
     radius = float(np.sqrt(0.5 * w * np.sum((x - xs) ** 2) + 0.5 / w * np.sum((y - ys) ** 2)))
     want = oracle.localized_bounds(x, y, 1, w, radius, diagonal, tol)
     lib.emu_set_start_point(p(xs), p(ys))
+    lib.emu_set_precomputed_kx(1)  # and K x handed in, as at a host event that computed the products of all its points at once
     try:
         out = np.zeros(5)
         assert lib.emu_localized_bounds(n, m, p(arr[0]), p(arr[1]), p(arr[2]), p(rb), len(rb) - 1, p(arc[0]), p(arc[1]), p(arc[2]), p(cb), len(cb) - 1,
                                         *[p(v) for v in vec], ctypes.c_double(w), ctypes.c_double(-1.0), int(diagonal), ctypes.c_double(tol), 3, p(out)) == 0
     finally:
         lib.emu_set_start_point(p(None), p(None))
+        lib.emu_set_precomputed_kx(0)
     assert abs(out[3] - radius) <= 1e-12 * radius
     for key, got in zip(("lagrangian_value", "lower_bound", "upper_bound"), out[:3]):
         assert abs(got - want[key]) <= (1e-5 if diagonal else 1e-10) * max(1.0, abs(want["lagrangian_value"])), ("start point", key, got, want[key])
