@@ -2,7 +2,7 @@
 `ncu --set full` capture (B200_PROFILING.md): set-up (transpose, stats, Ruiz / L2 rescaling),
 three trial steps (primal step, K x + dual step, K^T y + step test, decision, averaging), one
 termination check (KKT row / column passes), one restart evaluation (Lagrangian gradients + the
-trust-region root find) and the reduced costs.
+trust-region root find), the reduced costs, and a 70-iteration solve (host events with their products pass).
 
     python scripts/profile_kernels.py [workload=c3] [scale=1.0]
     ncu --set full --clock-control none --import-source on -k regex:pdlp_b200 -c 120 -o gpurun_out/prof_all python scripts/profile_kernels.py
@@ -35,6 +35,12 @@ def main():
     k = dp.kkt_stats(p, x, y)                 # KktRowOp / KktColOp
     b = dp.localized_bounds(x, y, weight, 1.0)  # DualGradOp, PrimalGradMapOp, trust-region passes
     rc = dp.reduced_costs(p, x, y)
+    dp.close()
+    # A short solve: the host events' products pass (rowstream_multi_kernel), the dense KKT / gradient passes on it
+    # and the trust-region passes, as the solver launches them.
+    p.termination_criteria.iteration_limit = 70
+    r = pdlp_b200.primal_dual_hybrid_gradient(qp, p)
+    print(f"short solve: {r.solve_log.iteration_count} iterations, reason {r.solve_log.termination_reason}")
     print(f"{name}: n={n} m={m} nnz={qp.constraint_matrix.nnz}  3 steps in {seconds * 1e3:.3f} ms, {launches} launches; "
           f"gap {k.convergence_information[0].primal_objective - k.convergence_information[0].dual_objective:.4g}, bounds {b}, |rc| {np.abs(rc).max():.4g}")
 
