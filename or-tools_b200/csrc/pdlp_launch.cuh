@@ -9,6 +9,7 @@
 #define PDLP_B200_LAUNCH_CUH_
 
 #include <algorithm>
+#include <cstdlib>
 #include <type_traits>
 
 #include "pdlp_ops.cuh"
@@ -39,6 +40,36 @@ inline int EnqueueMap(Workspace& ws, const Op& op, int64_t count, int region = 0
   ++ws.launches;
   return grid;
 }
+// How many CTAs of a fused peer pass take the shared rows (RowBlocks::split_ctas).  The shared part is bound by the
+// NVLink stores (8 bytes per row and peer at ~60 % of 900 GB/s per direction) or by its own stream, the private part by
+// HBM (~3.7 TB/s for this kernel on the whole GPU): the share f of the grid that makes both sides finish together,
+// max(t_link, t_shared / f) = t_private / (1 - f).  PDLP_B200_PEER_SHARED_CTAS_PCT overrides (0 = no split).
+inline int PeerSharedCtas(const SparseRows& s, int world, int grid) {
+  static const int forced = [] {
+    const char* env = std::getenv("PDLP_B200_PEER_SHARED_CTAS_PCT");
+    return env != nullptr ? std::atoi(env) : -1;
+  }();
+  if (grid < 2 || s.cut_block <= 0 || s.cut_block >= s.num_blocks) return 0;
+  double f;
+  if (forced >= 0) {
+    if (forced == 0) return 0;
+    f = forced / 100.0;
+  } else {
+    const double shared_rows = s.cut_row, private_rows = s.rows - s.cut_row;
+    const double t_link = (world - 1) * 8.0 * shared_rows / 540e9;
+    const double t_shared = (12.0 * static_cast<double>(s.cut_nnz) + 16.0 * shared_rows) / 3.7e12;
+    const double t_private = (12.0 * static_cast<double>(s.nnz - s.cut_nnz) + 64.0 * private_rows) / 3.7e12;
+    // Link-bound shared side: t_link = t_private / (1 - f).  Stream-bound: t_shared / f = t_private / (1 - f).
+    const double f_stream = t_shared / (t_shared + t_private);
+    const double f_link = t_link > t_private ? 0.5 : 1.0 - t_private / std::max(t_link, 1e-12);
+    f = std::max(f_stream, std::min(f_link, 0.5));
+    if (!(f > 0.0)) f = f_stream;
+  }
+  int ctas = static_cast<int>(f * grid + 0.5);
+  ctas = std::max(1, std::min(ctas, grid - 1));
+  return std::min(ctas, s.cut_block);
+}
+
 // A pass over the column-sharded CSR block with the shared rows' sums exchanged through peer memory
 // (pdlp_peer.cuh): push + signal, then the private rows (which hide the transfer), then wait + finish.
 template <class Op>
@@ -66,7 +97,10 @@ inline int EnqueueRowsPeer(Workspace& ws, const Op& op, const SparseRows& s, int
     Cut cut_op;
     cut_op.op = op; cut_op.view = view; cut_op.parity = static_cast<int>(epoch & 1); cut_op.cut_row = static_cast<int>(s.cut_row);
     grid = RowStreamGrid<Cut>(s);
-    rowstream_kernel<Cut><<<grid, kBlock, 0, ws.stream>>>(cut_op, s.View(), partials);
+    RowBlocks blocks = s.View();
+    blocks.split_block = shared_blocks;
+    blocks.split_ctas = PeerSharedCtas(s, view.world, grid);
+    rowstream_kernel<Cut><<<grid, kBlock, 0, ws.stream>>>(cut_op, blocks, partials);
     mark();
     peer_signal_rows_kernel<<<1, 32, 0, ws.stream>>>(view, epoch);
     mark();

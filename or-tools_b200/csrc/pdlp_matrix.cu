@@ -198,6 +198,7 @@ void BuildDeviceMatrixT(int64_t n, int64_t m, int64_t nnz, const I* col_ptr, con
   // All rows shared (cut at m) or none (cut at 0) are expressed with the block counts alone.
   csr.cut_row = row_cut < 0 ? 0 : static_cast<int>(std::min<int64_t>(row_cut, m));
   csr.cut_block = row_cut < 0 ? -1 : (row_cut >= m ? csr.num_blocks : (row_cut == 0 ? 0 : csr_blocks.cut_block));
+  csr.cut_nnz = host_ptr[csr.cut_row];
 }
 }  // namespace
 

@@ -29,6 +29,7 @@ struct SparseRows {
   // Column-sharded CSR block: work blocks [0, cut_block) hold exactly the rows shared with other
   // ranks (rows [0, cut_row)), the rest the rows private to this rank.  -1: no cut.
   int cut_block = -1, cut_row = 0;
+  int64_t cut_nnz = 0;  // nonzeros of the rows above the cut (the shared part's share of the work)
   RowBlocks View() const { return RowBlocks{ptr.get(), block_start.get(), block_nz.get(), num_blocks, rows}; }
   // Work blocks [first, first + count): same row / nonzero numbering, so ops index rows as usual.
   RowBlocks ViewOfBlocks(int first, int count) const { return RowBlocks{ptr.get(), block_start.get() + first, block_nz.get() + first, count, rows}; }

@@ -138,6 +138,11 @@ struct RowBlocks {
   const int* block_nz;     // num_blocks + 1 (row_ptr[block_start[b]]: first nonzero of each work block)
   int num_blocks;
   int rows;
+  // Ops that push row sums to other GPUs (HasBlockPush): CTAs [0, split_ctas) take the work blocks [0, split_block) - the
+  // rows whose sums travel over NVLink - and the other CTAs the rest, AT THE SAME TIME, so the link is busy for the whole
+  // launch instead of a burst at its start that every CTA then waits behind.  split_ctas = 0: one sequence over all CTAs.
+  int split_block = 0;
+  int split_ctas = 0;
 };
 
 constexpr int kMaxRowsPerBlock = 4 * kBlock;
@@ -255,22 +260,29 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
   for (int s = 0; s < Op::kNumSlots; ++s) red.v[s] = SlotIdentity(Op::SlotKindOf(s));
   Op op = op_in;
   if (op.Begin()) {
-    const int stride = gridDim.x;
+    int stride = gridDim.x;
     int b = blockIdx.x;
+    int end = rb.num_blocks;
+    if constexpr (HasBlockPush<Op>::value) {
+      if (rb.split_ctas > 0) {
+        if (static_cast<int>(blockIdx.x) < rb.split_ctas) { stride = rb.split_ctas; end = rb.split_block; }
+        else { b = rb.split_block + (blockIdx.x - rb.split_ctas); stride = gridDim.x - rb.split_ctas; }
+      }
+    }
     // Metadata of the current work block and of the next one (b + stride).
     int r0 = 0, r1 = 0, p0 = 0, p1 = 0, nr0 = 0, nr1 = 0, np0 = 0, np1 = 0;
-    if (b < rb.num_blocks) { r0 = rb.block_start[b]; r1 = rb.block_start[b + 1]; p0 = rb.block_nz[b]; p1 = rb.block_nz[b + 1]; }
-    if (b + stride < rb.num_blocks) {
+    if (b < end) { r0 = rb.block_start[b]; r1 = rb.block_start[b + 1]; p0 = rb.block_nz[b]; p1 = rb.block_nz[b + 1]; }
+    if (b + stride < end) {
       nr0 = rb.block_start[b + stride]; nr1 = rb.block_start[b + stride + 1];
       np0 = rb.block_nz[b + stride]; np1 = rb.block_nz[b + stride + 1];
     }
     PrefetchIndices(op, idx_buf, p0, p1 - p0);
-    while (b < rb.num_blocks) {
+    while (b < end) {
       const int nz = p1 - p0;
       // Metadata two blocks ahead: in flight for a whole block before it is needed.
       const int b2 = b + 2 * stride;
       int fr0 = 0, fr1 = 0, fp0 = 0, fp1 = 0;
-      if (b2 < rb.num_blocks) { fr0 = rb.block_start[b2]; fr1 = rb.block_start[b2 + 1]; fp0 = rb.block_nz[b2]; fp1 = rb.block_nz[b2 + 1]; }
+      if (b2 < end) { fr0 = rb.block_start[b2]; fr1 = rb.block_start[b2 + 1]; fp0 = rb.block_nz[b2]; fp1 = rb.block_nz[b2 + 1]; }
       const int next_nz = np1 - np0;  // 0 when there is no next block
       if (nz > kStreamChunk) {
         // One long row (r1 == r0 + 1 by construction): CTA-wide strided reduce.

@@ -309,7 +309,16 @@ extern "C" int emu_peer_dual_fused(int m_local, const int* ptr, const int* idx, 
                                    double* dy2_private) {
   cuda_emu::defer_async = false;
   HostRows csr{ptr, idx, val, block_start, num_blocks, m_local, {}};
-  const RowBlocks all = csr.View();
+  RowBlocks all = csr.View();
+  // The launcher's static split (pdlp_launch.cuh:PeerSharedCtas): the first CTAs take the shared rows' work blocks, the
+  // others the private rows', concurrently.  Odd ranks run unsplit, so both block orders are exercised.
+  int cut_block = 0;
+  while (cut_block < num_blocks && block_start[cut_block] < cut_row) ++cut_block;
+  const int grid_size = std::max(1, std::min(num_blocks, max_grid));
+  if ((rank & 1) == 0 && grid_size >= 2 && cut_block > 0 && cut_block < num_blocks) {
+    all.split_block = cut_block;
+    all.split_ctas = std::max(1, std::min(grid_size / 2, cut_block));
+  }
   StepState state = FreshState(step_size, primal_weight);
   const PeerView view = ViewOf(rank, world, cap_rows, regions);
   PeerCutRowOp<DualStepOp> op;
