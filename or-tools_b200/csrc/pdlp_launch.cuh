@@ -95,16 +95,19 @@ inline int EnqueueRowsPeer(Workspace& ws, const Op& op, const SparseRows& s, int
     // One launch over the whole block: shared rows push, private rows finish in place (PeerCutRowOp).
     using Cut = PeerCutRowOp<Op>;
     Cut cut_op;
-    cut_op.op = op; cut_op.view = view; cut_op.parity = static_cast<int>(epoch & 1); cut_op.cut_row = static_cast<int>(s.cut_row);
+    cut_op.op = op; cut_op.view = view; cut_op.parity = static_cast<int>(epoch & 1); cut_op.cut_row = static_cast<int>(s.cut_row); cut_op.epoch = epoch;
     grid = RowStreamGrid<Cut>(s);
     RowBlocks blocks = s.View();
     blocks.split_block = shared_blocks;
     blocks.split_ctas = PeerSharedCtas(s, view.world, grid);
     rowstream_kernel<Cut><<<grid, kBlock, 0, ws.stream>>>(cut_op, blocks, partials);
     mark();
-    peer_signal_rows_kernel<<<1, 32, 0, ws.stream>>>(view, epoch);
+    ++ws.launches;
+    if (blocks.split_ctas == 0) {  // a split launch signals from inside, as soon as its pushing CTAs are done
+      peer_signal_rows_kernel<<<1, 32, 0, ws.stream>>>(view, epoch);
+      ++ws.launches;
+    }
     mark();
-    ws.launches += 2;
   } else {
     if (shared_rows > 0) {
       if (shared_blocks > 0) {

@@ -39,6 +39,11 @@ __device__ __forceinline__ void PeerStoreFlag(unsigned long long* p, unsigned lo
 // Slots are written by other GPUs: read them from L2, never from a stale L1 line.
 __device__ __forceinline__ double PeerLoadSlot(const double* p) { return __ldcg(p); }
 #endif
+#ifdef PDLP_EMULATE
+inline unsigned int PeerCountUp(unsigned int* p) { return (*p)++; }  // emulated CTAs run one after the other
+#else
+__device__ __forceinline__ unsigned int PeerCountUp(unsigned int* p) { return atomicAdd(p, 1u); }
+#endif
 
 // Blocks the calling thread until every rank's flag in MY region has reached `epoch`.
 __device__ __forceinline__ void PeerWait(const unsigned long long* my_flags, int world, unsigned long long epoch) {
@@ -87,6 +92,25 @@ static __global__ void peer_combine_sums_kernel(PeerView view, unsigned long lon
   if (threadIdx.x == 0) PeerCombineSums(view, epoch, out, count, max != 0);
 }
 
+// In-kernel signal of a split launch (RowBlocks::split_ctas pushing CTAs): called by every thread of a pushing CTA when
+// it has stored its last row (also when the op is switched off: signals are unconditional).  Each thread fences its own
+// stores system-wide, the CTA counts itself done, and the LAST one to do so publishes "row epoch complete" to every
+// rank - while the other CTAs of the same launch are still streaming the private rows, so the flags are on their way
+// long before the launch ends and the finishing kernel finds them set.
+__device__ __forceinline__ void PeerSharedCtaDone(const PeerView& view, unsigned long long epoch, int pushing_ctas) {
+  PeerFenceSystem();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int* counter = view.DoneCounter();
+    if (PeerCountUp(counter) + 1u == static_cast<unsigned int>(pushing_ctas)) {
+      *counter = 0u;  // for the next launch on this stream
+      PeerFenceSystem();
+#pragma unroll 1
+      for (int r = 0; r < view.world; ++r) PeerStoreFlag(view.RowFlags(r) + view.rank, epoch);
+    }
+  }
+}
+
 // The sums of rows [r0, r0 + nrows) of one work block into slot [rank] of every rank's region, by the whole CTA:
 // consecutive threads store consecutive rows, one destination after the other.
 __device__ __forceinline__ void PeerBlockPush(const PeerView& view, int parity, int r0, int nrows, const double* sums) {
@@ -125,6 +149,7 @@ struct PeerPartialRowOp {
   }
   __device__ bool PushesRow(int) const { return true; }
   __device__ void BlockPush(int r0, int nrows, const double* sums) const { PeerBlockPush(view, parity, r0, nrows, sums); }
+  __device__ void PushingCtaDone(int) const {}  // never launched split: a signal kernel follows
 };
 
 // Phase 1 and the private rows in ONE row-stream launch (a CSR block cut into shared rows [0, cut_row) and
@@ -142,7 +167,9 @@ struct PeerCutRowOpBase {
   PeerView view;
   int parity;
   int cut_row;
+  unsigned long long epoch;
   __device__ bool Begin() { return op.Begin(); }
+  __device__ void PushingCtaDone(int pushing_ctas) const { PeerSharedCtaDone(view, epoch, pushing_ctas); }
   __device__ double Load(int64_t k) const { return op.Load(k); }
   template <class O = Op, class = std::enable_if_t<HasSplitLoad<O>::value>>
   __device__ const int* IndexAddress(int64_t k) const { return op.IndexAddress(k); }

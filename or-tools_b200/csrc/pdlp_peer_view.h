@@ -20,6 +20,7 @@ constexpr int kPeerSumsPerRank = 16;  // doubles per rank in a scalar exchange
 //   [0, 256)                 row flags:  unsigned long long [kMaxPeers] (+ padding)
 //   [256, 512)               sums flags: unsigned long long [kMaxPeers]
 //   [512, 512 + S)           sums slots: double [2][kMaxPeers][kPeerSumsPerRank], S = 2048
+//   [3072, 3076)             own use: how many pushing CTAs of the running launch are done (pdlp_peer.cuh:PeerSharedCtaDone)
 //   [4096, ...)              row slots:  double [2][world][cap_rows]
 struct PeerView {
   int rank = 0, world = 1;
@@ -31,6 +32,7 @@ struct PeerView {
     return RowSlotsOffset() + sizeof(double) * 2 * static_cast<size_t>(world) * static_cast<size_t>(cap_rows);
   }
   PDLP_HD unsigned long long* RowFlags(int owner) const { return reinterpret_cast<unsigned long long*>(base[owner]); }
+  PDLP_HD unsigned int* DoneCounter() const { return reinterpret_cast<unsigned int*>(base[rank] + 3072); }
   PDLP_HD unsigned long long* SumFlags(int owner) const { return reinterpret_cast<unsigned long long*>(base[owner] + 256); }
   PDLP_HD double* SumSlot(int owner, int parity, int source) const {
     return reinterpret_cast<double*>(base[owner] + 512) + (static_cast<size_t>(parity) * kMaxPeers + source) * kPeerSumsPerRank;

@@ -414,6 +414,10 @@ __global__ void __launch_bounds__(kBlock, PDLP_ROWSTREAM_MIN_CTAS) rowstream_ker
     }
     CpAsyncWaitAll();
   }
+  if constexpr (HasBlockPush<Op>::value) {
+    // A split launch signals from inside (pdlp_peer.cuh:PeerSharedCtaDone), switched-off op included.
+    if (rb.split_ctas > 0 && static_cast<int>(blockIdx.x) < rb.split_ctas) op.PushingCtaDone(rb.split_ctas);
+  }
   BlockReduceAndStore<Op>(red, partials);
 }
 

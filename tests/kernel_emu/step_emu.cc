@@ -323,10 +323,10 @@ extern "C" int emu_peer_dual_fused(int m_local, const int* ptr, const int* idx, 
   const PeerView view = ViewOf(rank, world, cap_rows, regions);
   PeerCutRowOp<DualStepOp> op;
   op.op = DualStepOp{{}, &state, val, idx, xbar, y0, y1, clb, cub, skip_below, nullptr};
-  op.view = view; op.parity = static_cast<int>(epoch & 1); op.cut_row = cut_row;
+  op.view = view; op.parity = static_cast<int>(epoch & 1); op.cut_row = cut_row; op.epoch = epoch;
   std::vector<double> partials(kMaxGrid, 0.0);
   const int grid = LaunchRows(op, all, max_grid, partials.data());
-  cuda_emu::Launch(1, 32, [=]() { peer_signal_rows_kernel(view, epoch); });
+  if (all.split_ctas == 0) cuda_emu::Launch(1, 32, [=]() { peer_signal_rows_kernel(view, epoch); });  // a split launch has signalled from inside
   double total = 0.0;
   for (int b = 0; b < grid; ++b) total += partials[b];
   *dy2_private = total;
