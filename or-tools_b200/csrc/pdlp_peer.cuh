@@ -88,6 +88,45 @@ __device__ __forceinline__ void PeerCombineSums(const PeerView& view, unsigned l
     out[i] = a;
   }
 }
+// The same exchange by a whole CTA (every thread calls; `values` and `count` identical in all threads): thread r serves
+// destination / source r, so the eight release stores - each a system-scope fence - and the eight acquire polls run
+// side by side instead of one after the other on a single thread.
+__device__ __forceinline__ void PeerPushSumsCta(const PeerView& view, unsigned long long epoch, const double* values, int count) {
+  const int r = threadIdx.x;
+  if (r < view.world) {
+    double* slot = view.SumSlot(r, static_cast<int>(epoch & 1), view.rank);
+    for (int i = 0; i < count; ++i) slot[i] = values[i];
+    PeerFenceSystem();
+    PeerStoreFlag(view.SumFlags(r) + view.rank, epoch);
+  }
+}
+// out: shared memory, `count` doubles, valid for every thread on return.
+__device__ __forceinline__ void PeerCombineSumsCta(const PeerView& view, unsigned long long epoch, double* out, int count, bool max) {
+  const int t = threadIdx.x;
+  if (t < view.world) {
+    while (PeerLoadFlag(view.SumFlags(view.rank) + t) < epoch) {
+#if !defined(PDLP_EMULATE)
+      __nanosleep(64);
+#endif
+    }
+  }
+  __syncthreads();
+  if (t < count) {
+    const int parity = static_cast<int>(epoch & 1);
+    double v[kMaxPeers];
+#pragma unroll
+    for (int r = 0; r < kMaxPeers; ++r) {
+      if (r < view.world) v[r] = PeerLoadSlot(view.SumSlot(view.rank, parity, r) + t);
+    }
+    double a = v[0];
+#pragma unroll
+    for (int r = 1; r < kMaxPeers; ++r) {
+      if (r < view.world) a = max ? fmax(a, v[r]) : a + v[r];
+    }
+    out[t] = a;
+  }
+  __syncthreads();
+}
 static __global__ void peer_combine_sums_kernel(PeerView view, unsigned long long epoch, double* out, int count, int max) {
   if (threadIdx.x == 0) PeerCombineSums(view, epoch, out, count, max != 0);
 }
@@ -98,16 +137,18 @@ static __global__ void peer_combine_sums_kernel(PeerView view, unsigned long lon
 // rank - while the other CTAs of the same launch are still streaming the private rows, so the flags are on their way
 // long before the launch ends and the finishing kernel finds them set.
 __device__ __forceinline__ void PeerSharedCtaDone(const PeerView& view, unsigned long long epoch, int pushing_ctas) {
+  __shared__ int last_pushing_cta;
   PeerFenceSystem();
   __syncthreads();
   if (threadIdx.x == 0) {
     unsigned int* counter = view.DoneCounter();
-    if (PeerCountUp(counter) + 1u == static_cast<unsigned int>(pushing_ctas)) {
-      *counter = 0u;  // for the next launch on this stream
-      PeerFenceSystem();
-#pragma unroll 1
-      for (int r = 0; r < view.world; ++r) PeerStoreFlag(view.RowFlags(r) + view.rank, epoch);
-    }
+    last_pushing_cta = PeerCountUp(counter) + 1u == static_cast<unsigned int>(pushing_ctas) ? 1 : 0;
+    if (last_pushing_cta) *counter = 0u;  // for the next launch on this stream
+  }
+  __syncthreads();
+  if (last_pushing_cta != 0 && static_cast<int>(threadIdx.x) < view.world) {  // one thread per destination: the release stores run side by side
+    PeerFenceSystem();
+    PeerStoreFlag(view.RowFlags(threadIdx.x) + view.rank, epoch);
   }
 }
 
@@ -219,15 +260,25 @@ struct PeerFinishRowOp {
   int combine_max;
   const double* slots;  // resolved by Begin(): my region, this epoch's half, source 0
   __device__ bool Begin() {
-    PeerWait(view.RowFlags(view.rank), view.world, epoch);
+    // One thread per CTA polls the flags (system-scope acquire loads are slow, and 300 000 threads polling the same
+    // eight words is what the finishing kernel spent its time on); the barrier hands the ordering to the others.
+    // Every thread of the CTA calls Begin() at the top of the kernel, so the barrier is uniform.
+    if (threadIdx.x == 0) PeerWait(view.RowFlags(view.rank), view.world, epoch);
+    __syncthreads();
     slots = view.RowSlot(view.rank, static_cast<int>(epoch & 1), 0);
     return op.Begin();
   }
   __device__ void Apply(int64_t i, Slots<Op::kNumSlots>& acc) const {
-    double a = PeerLoadSlot(slots + i);
-    for (int r = 1; r < view.world; ++r) {
-      const double b = PeerLoadSlot(slots + static_cast<size_t>(r) * static_cast<size_t>(view.cap_rows) + i);
-      a = combine_max ? fmax(a, b) : a + b;
+    // All ranks' sums of the row in flight together, then added in rank order.
+    double v[kMaxPeers];
+#pragma unroll
+    for (int r = 0; r < kMaxPeers; ++r) {
+      if (r < view.world) v[r] = PeerLoadSlot(slots + static_cast<size_t>(r) * static_cast<size_t>(view.cap_rows) + i);
+    }
+    double a = v[0];
+#pragma unroll
+    for (int r = 1; r < kMaxPeers; ++r) {
+      if (r < view.world) a = combine_max ? fmax(a, v[r]) : a + v[r];
     }
     const int row = static_cast<int>(i);
     OpRowFinish(op, row, a, OpRowPrefetch(op, row), acc);

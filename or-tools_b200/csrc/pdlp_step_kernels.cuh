@@ -177,8 +177,7 @@ __global__ void __launch_bounds__(kBlock) decide_adaptive_kernel(StepState* st, 
   __shared__ double buf[kBlock];
   __shared__ double peer_sums[4];
   if (peer.world > 1) {
-    if (threadIdx.x == 0) PeerCombineSums(peer, peer_epoch, peer_sums, 4, false);
-    __syncthreads();
+    PeerCombineSumsCta(peer, peer_epoch, peer_sums, 4, false);
   }
   if (st->active == 0) {
     // avg_pending and reset_average stay as they are: the batch-end flush consumes them.
@@ -314,8 +313,7 @@ __global__ void __launch_bounds__(kBlock) decide_mp_kernel(StepState* st, const 
   __shared__ double buf[kBlock];
   __shared__ double peer_sums[4];
   if (peer.world > 1) {
-    if (threadIdx.x == 0) PeerCombineSums(peer, peer_epoch, peer_sums, 4, false);
-    __syncthreads();
+    PeerCombineSumsCta(peer, peer_epoch, peer_sums, 4, false);
   }
   if (st->active == 0) {
     if (threadIdx.x == 0) { st->accepted_last = 0; st->reset_average = 0; st->first_mp_add_pending = 0; }
@@ -410,7 +408,7 @@ __global__ void __launch_bounds__(kBlock) fold_and_push_step_partials_kernel(con
   v[1] = ReducePartialsSum(p2, g2, 1, 0, buf);
   v[2] = ReducePartialsSum(p3, g3, 2, 0, buf);
   v[3] = ReducePartialsSum(p3, g3, 2, 1, buf);
-  if (threadIdx.x == 0) PeerPushSums(view, epoch, v, 4);
+  PeerPushSumsCta(view, epoch, v, 4);
 }
 
 }  // namespace

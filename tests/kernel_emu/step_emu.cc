@@ -291,12 +291,22 @@ extern "C" int emu_peer_sums(int world, long long cap_rows, void* const* regions
   for (int r = 0; r < world; ++r) {
     const PeerView view = ViewOf(r, world, cap_rows, regions);
     const double* mine = values + static_cast<size_t>(r) * count;
-    cuda_emu::Launch(1, 1, [=]() { PeerPushSums(view, epoch, mine, count); });
+    // Even epochs through the one-thread forms, odd epochs (the sums of the test) through the CTA-wide forms the step kernels use.
+    if (!(epoch & 1)) cuda_emu::Launch(1, 1, [=]() { PeerPushSums(view, epoch, mine, count); });
+    else cuda_emu::Launch(1, kBlock, [=]() { PeerPushSumsCta(view, epoch, mine, count); });
   }
   for (int r = 0; r < world; ++r) {
     const PeerView view = ViewOf(r, world, cap_rows, regions);
     double* dst = out + static_cast<size_t>(r) * count;
-    cuda_emu::Launch(1, 32, [=]() { peer_combine_sums_kernel(view, epoch, dst, count, max); });
+    if (!(epoch & 1)) {
+      cuda_emu::Launch(1, 32, [=]() { peer_combine_sums_kernel(view, epoch, dst, count, max); });
+    } else {
+      cuda_emu::Launch(1, kBlock, [=]() {
+        __shared__ double combined[kPeerSumsPerRank];
+        PeerCombineSumsCta(view, epoch, combined, count, max != 0);
+        if (static_cast<int>(threadIdx.x) < count) dst[threadIdx.x] = combined[threadIdx.x];
+      });
+    }
   }
   return 0;
 }
