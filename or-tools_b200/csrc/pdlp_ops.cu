@@ -81,10 +81,8 @@ void FillVector(Workspace& ws, double* v, int64_t count, double value) {
 
 void ScaleMatrixValues(Workspace& ws, SparseRows& s, const double* idx_scale, const double* row_scale) {
   if (s.rows == 0 || s.nnz == 0) return;
-  const int64_t warps_needed = s.rows;
-  int64_t grid = (warps_needed * 32 + kBlock - 1) / kBlock;
-  if (grid > kMaxGrid) grid = kMaxGrid;
-  scale_matrix_kernel<<<static_cast<int>(grid), kBlock, 0, ws.stream>>>(s.ptr.get(), s.idx.get(), s.val.get(), s.rows, idx_scale, row_scale);
+  const int grid = std::max(1, std::min(s.num_blocks, kMaxGrid));
+  scale_matrix_kernel<<<grid, kBlock, 0, ws.stream>>>(s.View(), s.idx.get(), s.val.get(), idx_scale, row_scale);
   ++ws.launches;
 }
 

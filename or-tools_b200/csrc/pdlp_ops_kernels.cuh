@@ -79,16 +79,28 @@ struct FillOp : AlwaysActive, NoSlots {
   __device__ void Apply(int64_t i, Slots<0>&) const { v[i] = value; }
 };
 
-// Matrix scaling runs per row so the row factor is read once per row.
-__global__ void __launch_bounds__(kBlock) scale_matrix_kernel(const int* ptr, const int* idx, double* val, int rows, const double* idx_scale,
-                                                             const double* row_scale) {
-  // One warp per row, grid-stride.
-  const int lane = threadIdx.x & 31;
-  const int64_t warp = (static_cast<int64_t>(blockIdx.x) * kBlock + threadIdx.x) >> 5;
-  const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * kBlock) >> 5;
-  for (int64_t r = warp; r < rows; r += nwarps) {
-    const double rs = row_scale[r];
-    for (int k = ptr[r] + lane; k < ptr[r + 1]; k += 32) val[k] *= idx_scale[idx[k]] * rs;
+// Matrix scaling over the work blocks of the row-stream kernel: a CTA takes a block (<= kStreamChunk nonzeros unless
+// it is one long row), keeps the block's row offsets in shared memory and gives every THREAD a nonzero, whose row it
+// finds by bisection in those offsets - the value stream is read and written fully coalesced whatever the row
+// lengths are.  (A warp per row, the first version, ran at 8 % of the HBM peak on the CSC copy of C3, whose
+// "rows" hold three nonzeros: profiles/r01_ncu_every_kernel_c3_v10.md.)
+__global__ void __launch_bounds__(kBlock) scale_matrix_kernel(RowBlocks rb, const int* idx, double* val, const double* idx_scale, const double* row_scale) {
+  __shared__ int row_raw[kMaxRowsPerBlock + 1];
+  for (int b = blockIdx.x; b < rb.num_blocks; b += gridDim.x) {
+    const int r0 = rb.block_start[b], nrows = rb.block_start[b + 1] - r0;
+    const int p0 = rb.block_nz[b], p1 = rb.block_nz[b + 1];
+    for (int i = threadIdx.x; i <= nrows; i += kBlock) row_raw[i] = rb.row_ptr[r0 + i];
+    __syncthreads();
+    for (int k = p0 + threadIdx.x; k < p1; k += kBlock) {
+      // The row of nonzero k: the last one whose first nonzero is <= k (empty rows share their successor's offset).
+      int lo = 0, hi = nrows;
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (row_raw[mid] <= k) lo = mid; else hi = mid;
+      }
+      val[k] *= idx_scale[idx[k]] * row_scale[r0 + lo];
+    }
+    __syncthreads();
   }
 }
 

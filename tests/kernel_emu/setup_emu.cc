@@ -32,10 +32,10 @@ void Map(const Op& op, int64_t count) {
 }
 void ScaleMatrix(HostRows& s, const double* idx_scale, const double* row_scale) {
   if (s.rows == 0) return;
-  int64_t grid = (static_cast<int64_t>(s.rows) * 32 + kBlock - 1) / kBlock;
-  if (grid > 4) grid = 4;  // (grid-stride: any grid gives the same result)
-  const int* ptr = s.ptr; const int* idx = s.idx; double* val = s.val; const int rows = s.rows;
-  cuda_emu::Launch(static_cast<int>(grid), kBlock, [=]() { scale_matrix_kernel(ptr, idx, val, rows, idx_scale, row_scale); });
+  const RowBlocks rb = s.View();
+  const int grid = std::max(1, std::min(rb.num_blocks, 3));  // (grid-stride over work blocks: any grid gives the same result)
+  const int* idx = s.idx; double* val = s.val;
+  cuda_emu::Launch(grid, kBlock, [=]() { scale_matrix_kernel(rb, idx, val, idx_scale, row_scale); });
 }
 }  // namespace
 
