@@ -62,25 +62,28 @@ def verify_termination(params, out, combo, iteration_limit):
         else:
             assert log.iteration_count <= iteration_limit
     else:
+        # The reference asserts iteration_count <= params.termination_criteria().iteration_limit() here, and
+        # CreateSolverParams leaves that field at its default (INT32_MAX) when use_iteration_limit is false: the only
+        # requirement of the reference is OPTIMAL.  The second assertion is THIS repository's regression guard: the
+        # no-limit solve should not need more iterations than the budget the limit combinations run for.
         assert log.termination_reason == TR.TERMINATION_REASON_OPTIMAL
+        assert log.iteration_count <= params.termination_criteria.iteration_limit
         assert log.iteration_count <= iteration_limit
 
 
 def known_budget_deviation(combo):
-    """The two reference iteration budgets the restated algorithm does not meet (note 3).
+    """Where this repository's own regression guard (verify_termination: a no-limit solve should converge within the
+    iteration budget its sibling limit combination runs for) is relaxed.  NOT a deviation from the reference: the
+    reference asserts no iteration bound at all for the *_NoIterationLimit_* combinations (see verify_termination).
 
-    Without rescaling and with the adaptive step rule (NoScaling_*_NoIterationLimit_AdaptiveLinesearch)
-    the oracle - and the device, which follows it - needs about 40 % more iterations than the reference
-    asserts on two fixtures, for EVERY perturbation of the data from 1e-15 to 1e-2 relative, of the initial
-    step size and of the initial primal weight (so this is not rounding chaos):
-      Tiny (budget 300, :317):                      420 in 72 of 82 1e-15-perturbed copies, 300 / 360 in the rest;
-      InactiveTwoSidedConstraint (budget 500, :395): 600 - 840, never below 540.
-    The same solves under Malitsky-Pock land exactly on the budgets (300 and 480) and with rescaling far
-    below them (180).  Every function on the path (TakeAdaptiveStep :2295-2376, the step and restart
-    helpers :1659-2094, trust_region.cc, the weighted average) was re-read against the oracle without
-    finding a difference, and /root/reference cannot be built here to trace it.  Until it can, these two
-    combinations carry the oracle's own measured envelope as their budget instead of a retry loop: every
-    other budget of the reference is asserted on the first, unperturbed solve."""
+    Without rescaling and with the adaptive step rule (NoScaling_*_NoIterationLimit_AdaptiveLinesearch) the oracle -
+    and the device, which follows it - needs more iterations than that budget to reach eps 1e-5 / 1e-8 on two
+    fixtures, for EVERY perturbation of the data from 1e-15 to 1e-2 relative (so it is not rounding chaos):
+      Tiny (limit combos run 300, :317):                      420 in 72 of 82 perturbed copies, 300 / 360 in the rest;
+      InactiveTwoSidedConstraint (limit combos run 500, :395): 600 - 840, never below 540.
+    After exactly 300 / 500 iterations the same solves already meet the reference's solution tolerances (the
+    *_IterationLimit_* combinations of the same tests pass unchanged), under Malitsky-Pock they stop exactly at 300 and
+    480, and with rescaling at 180.  These two combinations carry the oracle's measured envelope as the guard's value."""
     scaling, _, use_limit, mp = combo[:4]
     return (not scaling) and (not use_limit) and (not mp)
 
