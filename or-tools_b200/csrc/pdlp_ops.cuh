@@ -12,6 +12,8 @@
 #include "pdlp_restart_types.h"
 #include "pdlp_step_state.h"
 
+#include <nvtx3/nvToolsExt.h>  // header-only: ranges cost nothing unless a profiler has injected its library
+
 namespace pdlp_b200 {
 
 // The (rescaled) problem in HBM.  Primal-side vectors have length n, dual-side m.
@@ -33,6 +35,15 @@ struct DeviceProblem {
 //             count on rank 0 only, the rest are private to the rank; totals are all-reduced
 //   kJoint    the concatenation (primal block, dual rows) of the trust-region ops
 enum class Side { kDual, kSharded, kJoint };
+
+// NVTX range over a phase of the solve (tracing): set-up stages, trial-step batches, the three parts of a host
+// event.  `nsys` / `ncu --nvtx` group the kernels by them.
+struct TraceRange {
+  explicit TraceRange(const char* name) { nvtxRangePushA(name); }
+  ~TraceRange() { nvtxRangePop(); }
+  TraceRange(const TraceRange&) = delete;
+  TraceRange& operator=(const TraceRange&) = delete;
+};
 
 // Launch context: stream, per-kernel partial buffers, totals, pinned read-back.
 struct Workspace {

@@ -63,6 +63,7 @@ SolverResult ErrorSolverResult(int reason, const std::string& message) {
 }
 
 PreprocessSolver::PreprocessSolver(const QpView& qp, const PrimalDualHybridGradientParams& params) : view_(qp) {
+  const TraceRange trace("pdlp/setup/upload_and_transpose");
   // num_threads / num_shards (pdhg.cc:71-96) configure the reference's CPU thread pool;
   // the device path accepts and ignores them.
   ws_.Init(qp.n, qp.m);
@@ -146,6 +147,7 @@ int PreprocessSolver::AgreeOnCode(int code) {
 
 // sharded_optimization_utils.cc:270-343.
 QuadraticProgramStats PreprocessSolver::ComputeStats() {
+  const TraceRange trace("pdlp/setup/stats");
   DeviceProblem& p = problem_;
   QuadraticProgramStats s;
   // Row / column Linf norms with unit scaling (ones live in scratch).
@@ -209,6 +211,7 @@ QuadraticProgramStats PreprocessSolver::ComputeStats() {
 
 // sharded_optimization_utils.cc:367-444 + sharded_quadratic_program.cc:134-167.
 void PreprocessSolver::ApplyRescaling(const PrimalDualHybridGradientParams& params) {
+  const TraceRange trace("pdlp/setup/rescaling");
   DeviceProblem& p = problem_;
   double* row = p.row_scale.get();
   double* col = p.col_scale.get();

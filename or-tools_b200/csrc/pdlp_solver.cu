@@ -125,6 +125,7 @@ Solver::~Solver() {
 // Runs trial steps on the device until iterations_completed reaches the target, the
 // KKT-pass limit is hit, or a step forces numerical termination.
 void Solver::RunDeviceIterations(int target_iteration) {
+  const TraceRange trace("pdlp/trial_steps");
   host_.target_iteration = target_iteration;
   host_.active = 1;
   host_.force_numerical = 0;
@@ -233,6 +234,7 @@ Solver::Bounds Solver::BoundsAtAverage() {  // pdhg.cc:1818-1834
 
 // One pass over each copy of K for every product this host event needs (one GPU; see EventProducts).
 void Solver::PrepareEventProducts(const double* dx, const double* dy) {
+  const TraceRange trace("pdlp/event_products");
   event_ = EventProducts{};
   if (pre_->sharded() || problem_.n == 0 || problem_.m == 0) return;
   const bool has_avg = host_.avg_weight_sum > 0.0 && host_.avg_weight_sum_dual > 0.0;
@@ -288,6 +290,7 @@ int Solver::DetermineDistanceBasedRestartChoice() {  // pdhg.cc:1869-1902
 }
 
 int Solver::ChooseRestartToApply(bool is_major_iteration) {  // pdhg.cc:1904-1965
+  const TraceRange trace("pdlp/restart_choice");
   if (!(host_.avg_weight_sum > 0.0) && !(host_.avg_weight_sum_dual > 0.0)) return RESTART_CHOICE_NO_RESTART;
   const int restart_length = host_.avg_num_terms;
   if (restart_length >= iterations_completed_ / 2 && params_.restart_strategy == ADAPTIVE_HEURISTIC) {
@@ -334,6 +337,7 @@ double Solver::ComputeNewPrimalWeight() {  // pdhg.cc:1983-2010
 }
 
 void Solver::ApplyRestartChoice(int restart_to_apply) {  // pdhg.cc:2042-2094
+  const TraceRange trace("pdlp/apply_restart");
   switch (restart_to_apply) {
     case RESTART_CHOICE_UNSPECIFIED:
     case RESTART_CHOICE_NO_RESTART:
@@ -465,6 +469,7 @@ std::optional<Solver::Outcome> Solver::MajorIterationAndTerminationCheck(Iterati
       if (has_avg) products.average = {event_.kx_avg, event_.kty_avg};
       products.difference = {event_.kx_diff, event_.kty_diff};
     }
+    const TraceRange trace("pdlp/termination_check");
     const auto maybe_reason = pre_->UpdateIterationStatsAndCheckTermination(
         params_, force_numerical_termination, X(), Y(), has_avg ? it_.avg_x.get() : nullptr, has_avg ? it_.avg_y.get() : nullptr, dx, dy,
         it_.x_start.get(), it_.y_start.get(), interrupt, type, full_work_stats, stats, &products);
@@ -540,10 +545,11 @@ Solver::Outcome Solver::Solve(IterationType type, const InterruptFlag* interrupt
   } events;
   PDLP_CUDA_CHECK(cudaEventRecord(events.begin, ws_.stream));
   auto finish = [&](Outcome o) {
-    cudaEventRecord(events.end, ws_.stream);
-    cudaEventSynchronize(events.end);
+    // A sticky error raised inside the loop surfaces here at the latest, not in the caller's next CUDA call.
+    PDLP_CUDA_CHECK(cudaEventRecord(events.end, ws_.stream));
+    PDLP_CUDA_CHECK(cudaEventSynchronize(events.end));
     float ms = 0.0f;
-    cudaEventElapsedTime(&ms, events.begin, events.end);
+    PDLP_CUDA_CHECK(cudaEventElapsedTime(&ms, events.begin, events.end));
     device_loop_seconds_ = ms * 1e-3;
     StopWatcher();
     if (std::getenv("PDLP_B200_DEBUG_TIMING") != nullptr) {

@@ -92,3 +92,20 @@ def test_transportation_checker_over_two_blocks_adds_up_to_the_whole():
         assert _close(got["checker_primal_objective"], ci["primal_objective"]) and _close(got["checker_dual_objective"], ci["dual_objective"])
         for k, v in want.items():
             assert _close(got["relative_kkt_over_eps"][k], v), (k, got["relative_kkt_over_eps"][k], v)
+
+
+def test_n1_reference_is_keyed_by_workload_and_scale(tmp_path, monkeypatch):
+    """An N = 1 solve leaves (iterations, objective) behind; an N > 1 solve of the SAME workload and scale compares with
+    it (two eps-optimal points of one LP may differ by 4 eps), another scale finds nothing to compare with."""
+    import tempfile
+    monkeypatch.setattr(tempfile, "tempdir", str(tmp_path))
+    out = {}
+    assert bench.compare_with_n1(out, "c5", 8.0, 1, 9024, 1143586.5, 1e-4) and "vs_n1" not in out
+    out = {}
+    assert bench.compare_with_n1(out, "c5", 8.0, 8, 9600, 1143530.3, 1e-4)
+    assert out["vs_n1"]["iterations_n1"] == 9024 and abs(out["vs_n1"]["iteration_ratio"] - 9600 / 9024) < 1e-12
+    assert 4e-5 < out["vs_n1"]["objective_rel_diff"] < 6e-5
+    out = {}
+    assert not bench.compare_with_n1(out, "c5", 8.0, 8, 9600, 1143586.5 * (1 + 1e-3), 1e-4)  # not the same optimum
+    out = {}
+    assert bench.compare_with_n1(out, "c5", 2.0, 8, 100, 1.0, 1e-4) and "vs_n1" not in out  # no N = 1 run of that scale on this box
