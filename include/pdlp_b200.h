@@ -307,6 +307,14 @@ pdlp_b200_status pdlp_b200_trial_steps_profiled(pdlp_b200_device_problem* h, int
 pdlp_b200_status pdlp_b200_matvec_no_alloc(int64_t rows, int64_t cols, const int32_t* row_ptr, const int32_t* col_idx, const double* values,
                                            const double* v, double* out, int device, void* stream);
 
+/* Host only (no device needed): internal::ComputeStatuses (primal_dual_hybrid_gradient.h:164, .cc:2835-2883), the
+ * Glop basis statuses of a PDLP point, which the reference computes before it asks Glop's preprocessor to recover the
+ * original solution (:1295).  For the postsolve callback of pdlp_b200_solve_presolved.  Values are Glop's
+ * (lp_types.h:201-241): 0 BASIC, 1 FIXED_VALUE, 2 AT_LOWER_BOUND, 3 AT_UPPER_BOUND (4 FREE is never produced).
+ * Only the four bound vectors of `problem` are read. */
+pdlp_b200_status pdlp_b200_compute_statuses(const pdlp_b200_problem* problem, const double* primal_solution /*n*/, const double* dual_solution /*m*/,
+                                            int8_t* variable_statuses /*n*/, int8_t* constraint_statuses /*m*/);
+
 /* Host only (no device needed): the work-block partition the row-stream kernels run on
  * (at most 2048 nonzeros and 1024 rows per block, a longer row alone in its block),
  * from `rows + 1` compressed offsets.  cut in (0, rows): no block straddles that row (the

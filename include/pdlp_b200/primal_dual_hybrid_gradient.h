@@ -128,6 +128,38 @@ SolverResult PrimalDualHybridGradient(QuadraticProgram qp, const PrimalDualHybri
                                       const std::atomic<bool>* interrupt_solve = nullptr,
                                       std::function<void(const IterationCallbackInfo&)> iteration_stats_callback = nullptr);
 
+// Glop's basis statuses (ortools/lp_data/lp_types.h:201-241), with Glop's numbering, for the presolve hand-off: the
+// reference turns a PDLP point into a glop::ProblemSolution with internal::ComputeStatuses before it asks Glop's
+// preprocessor to recover the original solution (primal_dual_hybrid_gradient.cc:1295).  A caller's postsolve callback
+// (pdlp_b200_solve_presolved) does the same with this restatement.
+enum class VariableStatus : int8_t { BASIC = 0, FIXED_VALUE = 1, AT_LOWER_BOUND = 2, AT_UPPER_BOUND = 3, FREE = 4 };
+enum class ConstraintStatus : int8_t { BASIC = 0, FIXED_VALUE = 1, AT_LOWER_BOUND = 2, AT_UPPER_BOUND = 3, FREE = 4 };
+struct ProblemStatuses {  // the two status rows of glop::ProblemSolution
+  std::vector<VariableStatus> variable_statuses;
+  std::vector<ConstraintStatus> constraint_statuses;
+};
+namespace internal {
+// primal_dual_hybrid_gradient.h:164, .cc:2835-2883.  Host code.
+inline ProblemStatuses ComputeStatuses(const QuadraticProgram& qp, const PrimalAndDualSolution& solution) {
+  ProblemStatuses out;
+  out.constraint_statuses.resize(solution.dual_solution.size());
+  out.variable_statuses.resize(solution.primal_solution.size());
+  for (size_t i = 0; i < solution.dual_solution.size(); ++i) {
+    if (qp.constraint_lower_bounds[i] == qp.constraint_upper_bounds[i]) out.constraint_statuses[i] = ConstraintStatus::FIXED_VALUE;
+    else if (solution.dual_solution[i] > 0) out.constraint_statuses[i] = ConstraintStatus::AT_LOWER_BOUND;
+    else if (solution.dual_solution[i] < 0) out.constraint_statuses[i] = ConstraintStatus::AT_UPPER_BOUND;
+    else out.constraint_statuses[i] = ConstraintStatus::BASIC;
+  }
+  for (size_t j = 0; j < solution.primal_solution.size(); ++j) {
+    const bool at_lb = solution.primal_solution[j] <= qp.variable_lower_bounds[j];
+    const bool at_ub = solution.primal_solution[j] >= qp.variable_upper_bounds[j];
+    out.variable_statuses[j] = at_lb ? (at_ub ? VariableStatus::FIXED_VALUE : VariableStatus::AT_LOWER_BOUND)
+                                     : (at_ub ? VariableStatus::AT_UPPER_BOUND : VariableStatus::BASIC);
+  }
+  return out;
+}
+}  // namespace internal
+
 }  // namespace pdlp_b200
 
 // The reference's namespace (primal_dual_hybrid_gradient.h:28, quadratic_program.h:30).

@@ -121,6 +121,7 @@ _lib.pdlp_b200_solve.argtypes = [
 _lib.pdlp_b200_solve_sharded.argtypes = [ctypes.POINTER(_CProblem), ctypes.POINTER(_CShard)] + _lib.pdlp_b200_solve.argtypes[1:]
 # (original, presolved or NULL, presolve_status, postsolve, postsolve_user) + the tail of pdlp_b200_solve.
 _lib.pdlp_b200_solve_presolved.argtypes = [ctypes.POINTER(_CProblem), ctypes.POINTER(_CProblem), ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p] + _lib.pdlp_b200_solve.argtypes[1:]
+_lib.pdlp_b200_compute_statuses.argtypes = [ctypes.POINTER(_CProblem), ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
 _lib.pdlp_b200_problem_create_sharded.argtypes = [ctypes.POINTER(_CProblem), ctypes.POINTER(_CShard), ctypes.c_int, ctypes.POINTER(ctypes.c_void_p)]
 _lib.pdlp_b200_unique_id.argtypes = [ctypes.c_void_p]
 _lib.pdlp_b200_validate_params.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_void_p)]
@@ -138,6 +139,7 @@ EXPORTED_SYMBOLS = [
     "pdlp_b200_reduced_costs", "pdlp_b200_localized_bounds", "pdlp_b200_trial_steps", "pdlp_b200_trial_steps_profiled",
     "pdlp_b200_check_termination", "pdlp_b200_unique_id", "pdlp_b200_solve_sharded", "pdlp_b200_problem_create_sharded", "pdlp_b200_release_communicators",
     "pdlp_b200_work_blocks", "pdlp_b200_matvec_no_alloc", "pdlp_b200_format_iteration_stats", "pdlp_b200_localized_bounds_max_norm", "pdlp_b200_solve_presolved",
+    "pdlp_b200_compute_statuses",
 ]
 
 
@@ -192,7 +194,10 @@ PointType = types.SimpleNamespace(**_enums["PointType"])
 RestartChoice = types.SimpleNamespace(**_enums["RestartChoice"])
 
 from ._api import (  # noqa: E402
+    ConstraintStatus,
     DeviceProblem,
+    VariableStatus,
+    compute_statuses,
     IterationCallbackInfo,
     PrimalAndDualSolution,
     QuadraticProgram,

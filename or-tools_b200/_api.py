@@ -1,6 +1,7 @@
 """ctypes binding of include/pdlp_b200.h with the reference's Python names
 (/root/reference/ortools/pdlp/python/pdlp.cc:48-150)."""
 import ctypes
+import enum
 import math
 
 import numpy as np
@@ -262,6 +263,39 @@ def primal_dual_hybrid_gradient(qp, params, initial_solution=None, interrupt_sol
         loop_seconds=counters.loop_seconds, device_loop_seconds=counters.device_loop_seconds, collectives=counters.collectives, upload_seconds=counters.upload_seconds, symmetric_buffers=counters.symmetric_buffers, peer_exchanges=counters.peer_exchanges, interrupts_seen_on_device=counters.interrupts_seen_on_device,
     )
     return result
+
+
+class VariableStatus(enum.IntEnum):
+    """Glop's VariableStatus with Glop's numbering (ortools/lp_data/lp_types.h:201-219)."""
+    BASIC = 0
+    FIXED_VALUE = 1
+    AT_LOWER_BOUND = 2
+    AT_UPPER_BOUND = 3
+    FREE = 4
+
+
+class ConstraintStatus(enum.IntEnum):
+    """Glop's ConstraintStatus (lp_types.h:235-241)."""
+    BASIC = 0
+    FIXED_VALUE = 1
+    AT_LOWER_BOUND = 2
+    AT_UPPER_BOUND = 3
+    FREE = 4
+
+
+def compute_statuses(qp, primal_solution, dual_solution):
+    """internal::ComputeStatuses (primal_dual_hybrid_gradient.h:164, .cc:2835-2883): the Glop basis statuses of a PDLP
+    point, (constraint_statuses, variable_statuses) as lists of ConstraintStatus / VariableStatus.  Host code (no GPU):
+    what a postsolve callback of primal_dual_hybrid_gradient_presolved needs before it calls a Glop-style
+    `RecoverSolution`."""
+    mar = _Marshalled(qp)
+    x, y = _f64(primal_solution), _f64(dual_solution)
+    if x.size != mar.n or y.size != mar.m:
+        raise ValueError(f"solution sizes {x.size}, {y.size} do not match the problem ({mar.n} variables, {mar.m} constraints)")
+    vs, cs = np.zeros(max(mar.n, 1), dtype=np.int8), np.zeros(max(mar.m, 1), dtype=np.int8)
+    _check(_lib.pdlp_b200_compute_statuses(ctypes.byref(mar.c_problem), x.ctypes.data if x.size else None, y.ctypes.data if y.size else None,
+                                           vs.ctypes.data, cs.ctypes.data))
+    return [ConstraintStatus(int(v)) for v in cs[: mar.m]], [VariableStatus(int(v)) for v in vs[: mar.n]]
 
 
 POSTSOLVE_TYPE = ctypes.CFUNCTYPE(None, _c_double_p, _c_double_p, _c_double_p, _c_double_p, ctypes.c_void_p)

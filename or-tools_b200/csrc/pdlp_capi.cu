@@ -569,6 +569,32 @@ void pdlp_b200_problem_destroy(pdlp_b200_device_problem* h) {
   delete h;
 }
 
+pdlp_b200_status pdlp_b200_compute_statuses(const pdlp_b200_problem* problem, const double* primal_solution, const double* dual_solution,
+                                            int8_t* variable_statuses, int8_t* constraint_statuses) {
+  return Guard([&]() -> pdlp_b200_status {
+    if (problem == nullptr || problem->num_variables < 0 || problem->num_constraints < 0) return Fail(PDLP_B200_BAD_ARGUMENT, "bad argument");
+    const int64_t n = problem->num_variables, m = problem->num_constraints;
+    if ((n > 0 && (primal_solution == nullptr || variable_statuses == nullptr || problem->variable_lower_bounds == nullptr || problem->variable_upper_bounds == nullptr)) ||
+        (m > 0 && (dual_solution == nullptr || constraint_statuses == nullptr || problem->constraint_lower_bounds == nullptr || problem->constraint_upper_bounds == nullptr))) {
+      return Fail(PDLP_B200_BAD_ARGUMENT, "null vector");
+    }
+    // The same rules as internal::ComputeStatuses of the C++ mirror (include/pdlp_b200/primal_dual_hybrid_gradient.h), on raw arrays.
+    for (int64_t i = 0; i < m; ++i) {
+      ConstraintStatus s = ConstraintStatus::BASIC;
+      if (problem->constraint_lower_bounds[i] == problem->constraint_upper_bounds[i]) s = ConstraintStatus::FIXED_VALUE;
+      else if (dual_solution[i] > 0) s = ConstraintStatus::AT_LOWER_BOUND;
+      else if (dual_solution[i] < 0) s = ConstraintStatus::AT_UPPER_BOUND;
+      constraint_statuses[i] = static_cast<int8_t>(s);
+    }
+    for (int64_t j = 0; j < n; ++j) {
+      const bool at_lb = primal_solution[j] <= problem->variable_lower_bounds[j], at_ub = primal_solution[j] >= problem->variable_upper_bounds[j];
+      const VariableStatus s = at_lb ? (at_ub ? VariableStatus::FIXED_VALUE : VariableStatus::AT_LOWER_BOUND) : (at_ub ? VariableStatus::AT_UPPER_BOUND : VariableStatus::BASIC);
+      variable_statuses[j] = static_cast<int8_t>(s);
+    }
+    return PDLP_B200_OK;
+  });
+}
+
 pdlp_b200_status pdlp_b200_work_blocks(const int64_t* offsets, int64_t rows, int64_t cut, int32_t* block_start, int64_t* num_blocks,
                                        int32_t* cut_block, int32_t* max_row_nnz) {
   return Guard([&]() -> pdlp_b200_status {

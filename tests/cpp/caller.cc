@@ -46,6 +46,12 @@ int main(int argc, char** argv) {
     const pdlp::SolverResult r3 = pdlp::PrimalDualHybridGradient(TestLp(), params, start);
     if (r3.solve_log.termination_reason != pdlp::TERMINATION_REASON_INVALID_INITIAL_SOLUTION) return 3;
     if (!pdlp::IsLinearProgram(TestLp()) || !pdlp::HasValidBounds(TestLp()) || !pdlp::ValidateQuadraticProgramDimensions(TestLp()).empty()) return 4;
+    // internal::ComputeStatuses (primal_dual_hybrid_gradient.h:164; ComputeStatusesTest.AtOptimum, ..._test.cc:2076-2092).
+    const pdlp::ProblemStatuses st = pdlp::internal::ComputeStatuses(TestLp(), pdlp::PrimalAndDualSolution{{-1, 8, 1, 2.5}, {-2, 0, 2.375, 2.0 / 3}});
+    using CS = pdlp::ConstraintStatus;
+    using VS = pdlp::VariableStatus;
+    if (st.constraint_statuses != std::vector<CS>{CS::FIXED_VALUE, CS::BASIC, CS::AT_LOWER_BOUND, CS::AT_LOWER_BOUND}) return 5;
+    if (st.variable_statuses != std::vector<VS>{VS::BASIC, VS::BASIC, VS::BASIC, VS::AT_LOWER_BOUND}) return 6;
     std::printf("cpu ok: %s | %s\n", r1.solve_log.termination_string.get().c_str(), r2.solve_log.termination_string.get().c_str());
     return 0;
   }

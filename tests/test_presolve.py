@@ -148,3 +148,30 @@ def test_presolver_that_solves_everything_gives_a_presolver_solution():
     # A presolver that reports infeasibility is passed through when the point earns nothing better.
     bad = pdlp_b200.primal_dual_hybrid_gradient_presolved(qp, None, postsolve, params(), presolve_status=TR.TERMINATION_REASON_PRIMAL_OR_DUAL_INFEASIBLE)
     assert bad.solve_log.termination_reason in (TR.TERMINATION_REASON_PRIMAL_OR_DUAL_INFEASIBLE, TR.TERMINATION_REASON_OPTIMAL)
+
+
+# ---- internal::ComputeStatuses (primal_dual_hybrid_gradient.h:164, .cc:2835-2883): host code, no GPU ----
+
+CS, VS = pdlp_b200.ConstraintStatus, pdlp_b200.VariableStatus
+
+
+def test_compute_statuses_at_optimum():  # primal_dual_hybrid_gradient_test.cc:2076-2092
+    lp = fixtures.make_test_lp()
+    constraint_statuses, variable_statuses = pdlp_b200.compute_statuses(lp, [-1, 8, 1, 2.5], [-2, 0, 2.375, 2.0 / 3])
+    assert constraint_statuses == [CS.FIXED_VALUE, CS.BASIC, CS.AT_LOWER_BOUND, CS.AT_LOWER_BOUND]
+    assert variable_statuses == [VS.BASIC, VS.BASIC, VS.BASIC, VS.AT_LOWER_BOUND]
+
+
+def test_compute_statuses_cover_more_cases():  # :2094-2113
+    lp = fixtures.make_test_lp()
+    lp.variable_upper_bounds = np.array(lp.variable_upper_bounds, dtype=float)
+    lp.variable_upper_bounds[3] = 2.5
+    lp.variable_upper_bounds[1] = 8
+    constraint_statuses, variable_statuses = pdlp_b200.compute_statuses(lp, [-1, 8, 1, 2.5], [-2, 0, 2.375, -1])
+    assert constraint_statuses == [CS.FIXED_VALUE, CS.BASIC, CS.AT_LOWER_BOUND, CS.AT_UPPER_BOUND]
+    assert variable_statuses == [VS.BASIC, VS.AT_UPPER_BOUND, VS.BASIC, VS.FIXED_VALUE]
+
+
+def test_compute_statuses_rejects_wrong_sizes():
+    with pytest.raises(ValueError):
+        pdlp_b200.compute_statuses(fixtures.make_test_lp(), [0, 0, 0], [0, 0, 0, 0])
