@@ -138,6 +138,26 @@ struct ProblemStatuses {  // the two status rows of glop::ProblemSolution
   std::vector<VariableStatus> variable_statuses;
   std::vector<ConstraintStatus> constraint_statuses;
 };
+// Glop's ProblemStatus (lp_types.h:105-160, Glop's numbering) and the table that turns a preprocessor's verdict into
+// the TerminationReason handed to pdlp_b200_solve_presolved (GlopStatusToTerminationReason, pdhg.cc:1123-1143).
+enum class GlopProblemStatus : int8_t {
+  OPTIMAL = 0, PRIMAL_INFEASIBLE, DUAL_INFEASIBLE, INFEASIBLE_OR_UNBOUNDED, PRIMAL_UNBOUNDED, DUAL_UNBOUNDED, INIT, PRIMAL_FEASIBLE, DUAL_FEASIBLE,
+  ABNORMAL, INVALID_PROBLEM, IMPRECISE
+};
+inline int GlopStatusToTerminationReason(GlopProblemStatus glop_status) {
+  switch (glop_status) {
+    case GlopProblemStatus::OPTIMAL: return TERMINATION_REASON_OPTIMAL;
+    case GlopProblemStatus::INVALID_PROBLEM: return TERMINATION_REASON_INVALID_PROBLEM;
+    case GlopProblemStatus::ABNORMAL:
+    case GlopProblemStatus::IMPRECISE: return TERMINATION_REASON_NUMERICAL_ERROR;
+    case GlopProblemStatus::PRIMAL_INFEASIBLE:
+    case GlopProblemStatus::DUAL_INFEASIBLE:
+    case GlopProblemStatus::INFEASIBLE_OR_UNBOUNDED:
+    case GlopProblemStatus::DUAL_UNBOUNDED:
+    case GlopProblemStatus::PRIMAL_UNBOUNDED: return TERMINATION_REASON_PRIMAL_OR_DUAL_INFEASIBLE;
+    default: return TERMINATION_REASON_OTHER;  // (the reference also logs a warning)
+  }
+}
 namespace internal {
 // primal_dual_hybrid_gradient.h:164, .cc:2835-2883.  Host code.
 inline ProblemStatuses ComputeStatuses(const QuadraticProgram& qp, const PrimalAndDualSolution& solution) {

@@ -196,6 +196,8 @@ RestartChoice = types.SimpleNamespace(**_enums["RestartChoice"])
 from ._api import (  # noqa: E402
     ConstraintStatus,
     DeviceProblem,
+    GlopProblemStatus,
+    glop_status_to_termination_reason,
     VariableStatus,
     compute_statuses,
     IterationCallbackInfo,

@@ -283,6 +283,39 @@ class ConstraintStatus(enum.IntEnum):
     FREE = 4
 
 
+class GlopProblemStatus(enum.IntEnum):
+    """Glop's ProblemStatus with Glop's numbering (ortools/lp_data/lp_types.h:105-160)."""
+    OPTIMAL = 0
+    PRIMAL_INFEASIBLE = 1
+    DUAL_INFEASIBLE = 2
+    INFEASIBLE_OR_UNBOUNDED = 3
+    PRIMAL_UNBOUNDED = 4
+    DUAL_UNBOUNDED = 5
+    INIT = 6
+    PRIMAL_FEASIBLE = 7
+    DUAL_FEASIBLE = 8
+    ABNORMAL = 9
+    INVALID_PROBLEM = 10
+    IMPRECISE = 11
+
+
+def glop_status_to_termination_reason(glop_status):
+    """GlopStatusToTerminationReason (primal_dual_hybrid_gradient.cc:1123-1143): a preprocessor's verdict as the
+    TerminationReason number `primal_dual_hybrid_gradient_presolved(presolve_status=...)` takes."""
+    from . import TerminationReason  # (defined after this module is imported)
+    s = GlopProblemStatus(glop_status)
+    if s == GlopProblemStatus.OPTIMAL:
+        return TerminationReason.TERMINATION_REASON_OPTIMAL
+    if s == GlopProblemStatus.INVALID_PROBLEM:
+        return TerminationReason.TERMINATION_REASON_INVALID_PROBLEM
+    if s in (GlopProblemStatus.ABNORMAL, GlopProblemStatus.IMPRECISE):
+        return TerminationReason.TERMINATION_REASON_NUMERICAL_ERROR
+    if s in (GlopProblemStatus.PRIMAL_INFEASIBLE, GlopProblemStatus.DUAL_INFEASIBLE, GlopProblemStatus.INFEASIBLE_OR_UNBOUNDED,
+             GlopProblemStatus.DUAL_UNBOUNDED, GlopProblemStatus.PRIMAL_UNBOUNDED):
+        return TerminationReason.TERMINATION_REASON_PRIMAL_OR_DUAL_INFEASIBLE
+    return TerminationReason.TERMINATION_REASON_OTHER
+
+
 def compute_statuses(qp, primal_solution, dual_solution):
     """internal::ComputeStatuses (primal_dual_hybrid_gradient.h:164, .cc:2835-2883): the Glop basis statuses of a PDLP
     point, (constraint_statuses, variable_statuses) as lists of ConstraintStatus / VariableStatus.  Host code (no GPU):

@@ -175,3 +175,14 @@ def test_compute_statuses_cover_more_cases():  # :2094-2113
 def test_compute_statuses_rejects_wrong_sizes():
     with pytest.raises(ValueError):
         pdlp_b200.compute_statuses(fixtures.make_test_lp(), [0, 0, 0], [0, 0, 0, 0])
+
+
+def test_glop_status_to_termination_reason_table():  # primal_dual_hybrid_gradient.cc:1123-1143
+    G, f = pdlp_b200.GlopProblemStatus, pdlp_b200.glop_status_to_termination_reason
+    assert f(G.OPTIMAL) == TR.TERMINATION_REASON_OPTIMAL
+    assert f(G.INVALID_PROBLEM) == TR.TERMINATION_REASON_INVALID_PROBLEM
+    assert f(G.ABNORMAL) == f(G.IMPRECISE) == TR.TERMINATION_REASON_NUMERICAL_ERROR
+    for s in (G.PRIMAL_INFEASIBLE, G.DUAL_INFEASIBLE, G.INFEASIBLE_OR_UNBOUNDED, G.DUAL_UNBOUNDED, G.PRIMAL_UNBOUNDED):
+        assert f(s) == TR.TERMINATION_REASON_PRIMAL_OR_DUAL_INFEASIBLE
+    for s in (G.INIT, G.PRIMAL_FEASIBLE, G.DUAL_FEASIBLE):
+        assert f(s) == TR.TERMINATION_REASON_OTHER
