@@ -347,6 +347,21 @@ void oracle_scaling_vectors(void* h, int which, int iters, double* row_scale_ino
   std::copy(r.begin(), r.end(), row_scale_inout);
   std::copy(c.begin(), c.end(), col_scale_inout);
 }
+// ShardedQuadraticProgram::RescaleQuadraticProgram with given vectors (sharded_quadratic_program.cc:134-167) and
+// ReplaceLargeConstraintBoundsWithInfinity (:119-130), for the goldens of sharded_quadratic_program_test.cc.
+void oracle_rescale_with(void* h, const double* col_scale, const double* row_scale) {
+  auto* p = static_cast<OracleProblem*>(h);
+  const Vec col(col_scale, col_scale + p->sq->PrimalSize()), row(row_scale, row_scale + p->sq->DualSize());
+  p->sq->Rescale(col, row);
+  for (size_t i = 0; i < row.size(); ++i) p->row_scale[i] *= row[i];
+  for (size_t i = 0; i < col.size(); ++i) p->col_scale[i] *= col[i];
+}
+void oracle_replace_large_constraint_bounds(void* h, double threshold) { static_cast<OracleProblem*>(h)->sq->ReplaceLargeConstraintBoundsWithInfinity(threshold); }
+// Values of the transposed copy, in its own compressed order (rows of K, columns ascending).
+void oracle_problem_get_transposed_values(void* h, double* val) {
+  const Csc& kt = static_cast<OracleProblem*>(h)->sq->Kt();
+  std::copy(kt.val.begin(), kt.val.end(), val);
+}
 // Reads the (possibly rescaled) problem data back: any pointer may be null.
 void oracle_problem_get(void* h, double* val, double* c, double* q, double* vlb, double* vub, double* clb, double* cub) {
   const Qp& qp = static_cast<OracleProblem*>(h)->sq->qp();

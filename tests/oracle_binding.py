@@ -199,6 +199,20 @@ class Problem:
         self.lib.oracle_rescale(self.h, int(ruiz), int(l2), _p(rs), _p(cs))
         return rs[: self.m], cs[: self.n]
 
+    def rescale_with(self, col_scale, row_scale):
+        """RescaleQuadraticProgram (sharded_quadratic_program.cc:134-167) with the given scaling vectors."""
+        col_scale, row_scale = _f(col_scale), _f(row_scale)  # named: the arrays must outlive the call
+        self.lib.oracle_rescale_with(self.h, _p(col_scale), _p(row_scale))
+
+    def replace_large_constraint_bounds_with_infinity(self, threshold):
+        self.lib.oracle_replace_large_constraint_bounds(self.h, ctypes.c_double(threshold))
+
+    def transposed_values(self):
+        nnz = self.mar.v.size
+        out = np.zeros(max(nnz, 1))
+        self.lib.oracle_problem_get_transposed_values(self.h, _p(out))
+        return out[:nnz]
+
     def scaling_vectors(self, which, iters, row_scale, col_scale):
         rs = np.ascontiguousarray(row_scale, dtype=np.float64).copy(); cs = np.ascontiguousarray(col_scale, dtype=np.float64).copy()
         self.lib.oracle_scaling_vectors(self.h, int(which), int(iters), _p(rs), _p(cs))

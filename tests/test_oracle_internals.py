@@ -172,3 +172,36 @@ def test_sigma_max_diagonal():
     qp.constraint_matrix = sp.csc_matrix(np.diag([2.0, 1.0, -3.0, -1.0]))
     v, iters = ob.Problem(qp, 2, 2).sigma_max(0.01, 0.001, 1)
     assert abs(v - 3.0) < 1e-4 and iters < 300
+
+
+# ---- sharded_quadratic_program_test.cc: the data transformations of ShardedQuadraticProgram ----
+
+def test_rescale_problem_basic():  # RescaleProblem.BasicTest, :91-123
+    """TestDiagonalQp1 rescaled with rows [0.5] and columns [1, 0.5]: min 4 x1^2 + 0.25 x2^2 - x1 - 0.5 x2 + 5,
+    -inf <= 0.5 x1 + 0.25 x2 <= 0.5, 1 <= x1 <= 2, -4 <= x2 <= 8; both copies of K carry the scaling."""
+    p = ob.Problem(fixtures.diagonal_qp1(), num_threads=2, num_shards=10)
+    p.rescale_with([1, 0.5], [0.5])
+    got = p.get()
+    assert got["clb"].tolist() == [-np.inf] and got["cub"].tolist() == [0.5]
+    assert got["vlb"].tolist() == [1, -4] and got["vub"].tolist() == [2, 8]
+    assert got["c"].tolist() == [-1, -0.5]
+    assert got["val"].tolist() == [0.5, 0.25]            # K = [[0.5, 0.25]] by columns
+    assert p.transposed_values().tolist() == [0.5, 0.25]  # K^T = [[0.5], [0.25]]
+    assert got["q"].tolist() == [4, 0.25]
+
+
+def test_replace_large_constraint_bounds_with_infinity():  # :125-135
+    p = ob.Problem(fixtures.make_test_lp(), num_threads=2, num_shards=2)
+    p.replace_large_constraint_bounds_with_infinity(3.0)
+    got = p.get()
+    assert got["clb"].tolist() == [np.inf, -np.inf, -np.inf, -1]
+    assert got["cub"].tolist() == [np.inf, np.inf, np.inf, 1]
+
+
+def test_sharded_quadratic_program_basic():  # ShardedQuadraticProgramTest.BasicTest, :32-49
+    qp = fixtures.diagonal_qp1()
+    p = ob.Problem(qp, num_threads=2, num_shards=10)
+    assert (p.n, p.m) == (2, 1)
+    assert p.transposed_values().tolist() == [1, 1]
+    # K^T v and K v through the two copies.
+    assert p.matvec(0, [3.0]).tolist() == [3, 3] and p.matvec(1, [2.0, 5.0]).tolist() == [7]
