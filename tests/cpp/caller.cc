@@ -46,6 +46,11 @@ int main(int argc, char** argv) {
     const pdlp::SolverResult r3 = pdlp::PrimalDualHybridGradient(TestLp(), params, start);
     if (r3.solve_log.termination_reason != pdlp::TERMINATION_REASON_INVALID_INITIAL_SOLUTION) return 3;
     if (!pdlp::IsLinearProgram(TestLp()) || !pdlp::HasValidBounds(TestLp()) || !pdlp::ValidateQuadraticProgramDimensions(TestLp()).empty()) return 4;
+    // HasValidBoundsTest (quadratic_program_test.cc:134-148): a constraint and a variable with lower > upper bound.
+    pdlp::QuadraticProgram crossed_row = TestLp(), crossed_column = TestLp();
+    crossed_row.constraint_lower_bounds[1] = 8;  // upper bound 7
+    crossed_column.variable_lower_bounds[3] = 4;  // upper bound 3.5
+    if (pdlp::HasValidBounds(crossed_row) || pdlp::HasValidBounds(crossed_column)) return 7;
     // internal::ComputeStatuses (primal_dual_hybrid_gradient.h:164; ComputeStatusesTest.AtOptimum, ..._test.cc:2076-2092).
     const pdlp::ProblemStatuses st = pdlp::internal::ComputeStatuses(TestLp(), pdlp::PrimalAndDualSolution{{-1, 8, 1, 2.5}, {-2, 0, 2.375, 2.0 / 3}});
     using CS = pdlp::ConstraintStatus;

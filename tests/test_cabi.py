@@ -153,3 +153,41 @@ def test_python_surface_mirrors_the_reference_module():
     with pytest.raises(ValueError):
         pdlp_b200.validate_quadratic_program_dimensions(qp)
     assert qp.apply_objective_scaling_and_offset(2.0) == qp.objective_scaling_factor * (2.0 + qp.objective_offset)
+
+
+# ---- quadratic_program_test.cc:63-132: ValidateQuadraticProgramDimensions ----
+
+def _resized(field, size):
+    def mutate(qp):
+        setattr(qp, field, np.zeros(size))
+    return mutate
+
+
+def _matrix(rows, cols):
+    def mutate(qp):
+        import scipy.sparse as sp
+        qp.constraint_matrix = sp.csc_matrix((rows, cols))
+    return mutate
+
+
+def test_validate_dimensions_accepts_a_valid_problem():  # :63-67
+    pdlp_b200.validate_quadratic_program_dimensions(fixtures.diagonal_qp1())
+
+
+@pytest.mark.parametrize("mutate", [
+    _resized("constraint_lower_bounds", 10),   # :69
+    _resized("constraint_upper_bounds", 10),   # :77
+    _resized("objective_vector", 10),          # :85
+    _resized("variable_lower_bounds", 10),     # :93
+    _resized("variable_upper_bounds", 10),     # :101
+    _matrix(10, 2),                            # :109
+    _matrix(2, 10),                            # :117
+    lambda qp: qp.set_objective_matrix_diagonal(np.ones(10)),  # :125
+], ids=["constraint_lb", "constraint_ub", "objective", "variable_lb", "variable_ub", "matrix_rows", "matrix_cols", "objective_matrix"])
+def test_validate_dimensions_rejects_inconsistent_sizes(mutate):
+    qp = pdlp_b200.QuadraticProgram()
+    qp.resize_and_initialize(2, 3)
+    pdlp_b200.validate_quadratic_program_dimensions(qp)
+    mutate(qp)
+    with pytest.raises(ValueError, match="Inconsistent dimensions"):
+        pdlp_b200.validate_quadratic_program_dimensions(qp)
