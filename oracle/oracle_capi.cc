@@ -300,6 +300,22 @@ int oracle_shard_starts(int64_t n, int num_shards, const int64_t* masses /*nulla
   return sh->NumShards();
 }
 
+// ShardedWeightedAverage (sharded_optimization_utils.cc:43-79) fed `count` vectors of length n with their weights;
+// clear_after_add >= 0: Clear() after that many adds.  meta_out = {HasNonzeroWeight, NumTerms}.
+void oracle_weighted_average(int64_t n, int num_shards, int count, const double* vectors, const double* weights, int clear_after_add, double* avg_out,
+                             double* meta_out) {
+  Sharder sh(n, num_shards, nullptr);
+  WeightedAverage avg(&sh);
+  for (int k = 0; k < count; ++k) {
+    avg.Add(Vec(vectors + k * n, vectors + (k + 1) * n), weights[k]);
+    if (k + 1 == clear_after_add) avg.Clear();
+  }
+  const Vec out = avg.ComputeAverage();
+  std::copy(out.begin(), out.end(), avg_out);
+  meta_out[0] = avg.HasNonzeroWeight() ? 1.0 : 0.0;
+  meta_out[1] = avg.NumTerms();
+}
+
 struct OracleProblem { ShardedQp* sq; Vec col_scale, row_scale; };
 
 void* oracle_problem_create(int64_t n, int64_t m, int64_t nnz, const int64_t* col_ptr, const int64_t* row_idx, const double* val, const double* c, const double* q_diag,
@@ -361,6 +377,20 @@ void oracle_replace_large_constraint_bounds(void* h, double threshold) { static_
 void oracle_problem_get_transposed_values(void* h, double* val) {
   const Csc& kt = static_cast<OracleProblem*>(h)->sq->Kt();
   std::copy(kt.val.begin(), kt.val.end(), val);
+}
+// ProjectToPrimalVariableBounds / ProjectToDualVariableBounds (sharded_optimization_utils.cc:701-750), in place.
+void oracle_project(void* h, double* x /*nullable*/, double* y /*nullable*/) {
+  const ShardedQp& sq = *static_cast<OracleProblem*>(h)->sq;
+  if (x != nullptr) {
+    Vec v(x, x + sq.PrimalSize());
+    ProjectToPrimalVariableBounds(sq, v);
+    std::copy(v.begin(), v.end(), x);
+  }
+  if (y != nullptr) {
+    Vec v(y, y + sq.DualSize());
+    ProjectToDualVariableBounds(sq, v);
+    std::copy(v.begin(), v.end(), y);
+  }
 }
 // Reads the (possibly rescaled) problem data back: any pointer may be null.
 void oracle_problem_get(void* h, double* val, double* c, double* q, double* vlb, double* vub, double* clb, double* cub) {

@@ -213,6 +213,13 @@ class Problem:
         self.lib.oracle_problem_get_transposed_values(self.h, _p(out))
         return out[:nnz]
 
+    def project(self, x=None, y=None):
+        """ProjectToPrimalVariableBounds / ProjectToDualVariableBounds (sharded_optimization_utils.cc:701-750): copies."""
+        px = None if x is None else _f(x).copy()
+        py = None if y is None else _f(y).copy()
+        self.lib.oracle_project(self.h, _p(px) if px is not None else None, _p(py) if py is not None else None)
+        return px, py
+
     def scaling_vectors(self, which, iters, row_scale, col_scale):
         rs = np.ascontiguousarray(row_scale, dtype=np.float64).copy(); cs = np.ascontiguousarray(col_scale, dtype=np.float64).copy()
         self.lib.oracle_scaling_vectors(self.h, int(which), int(iters), _p(rs), _p(cs))
@@ -273,6 +280,17 @@ def trust_region(obj, lb, ub, center, w, radius, diag=None, num_shards=1, tol=1e
     lib.oracle_trust_region(ctypes.c_int64(obj.size), _p(obj), _p(diag) if diag is not None else None, _p(lb), _p(ub), _p(center), _p(w),
                             ctypes.c_double(radius), int(num_shards), ctypes.c_double(tol), _p(sol), _p(out))
     return sol[: obj.size], out[0], out[1]
+
+
+def weighted_average(vectors, weights, num_shards=1, clear_after_add=-1):
+    """ShardedWeightedAverage after Add(vectors[k], weights[k]) for every k: (average, has_nonzero_weight, num_terms)."""
+    v = np.ascontiguousarray(np.atleast_2d(np.asarray(vectors, dtype=np.float64)))
+    w = _f(weights)
+    n = v.shape[1]
+    count = 0 if len(w) == 0 else v.shape[0]
+    out, meta = np.zeros(max(n, 1)), np.zeros(2)
+    load().oracle_weighted_average(ctypes.c_int64(n), int(num_shards), int(count), _p(v.reshape(-1)), _p(w if w.size else np.zeros(1)), int(clear_after_add), _p(out), _p(meta))
+    return out[:n], bool(meta[0]), int(meta[1])
 
 
 def shard_starts(n, num_shards, masses=None):

@@ -205,3 +205,39 @@ def test_sharded_quadratic_program_basic():  # ShardedQuadraticProgramTest.Basic
     assert p.transposed_values().tolist() == [1, 1]
     # K^T v and K v through the two copies.
     assert p.matvec(0, [3.0]).tolist() == [3, 3] and p.matvec(1, [2.0, 5.0]).tolist() == [7]
+
+
+# ---- sharded_optimization_utils_test.cc:41-131: ShardedWeightedAverage (the update every accepted step applies) ----
+
+def test_weighted_average_simple():  # :41-59
+    avg, has_weight, terms = ob.weighted_average([[4, 1], [1, 7]], [1.0, 2.0], num_shards=2)
+    assert has_weight and terms == 2 and avg.tolist() == [2.0, 5.0]
+    avg, has_weight, terms = ob.weighted_average([[4, 1], [1, 7]], [1.0, 2.0], num_shards=2, clear_after_add=2)
+    assert not has_weight and terms == 0
+
+
+def test_weighted_average_of_nothing_is_zero():  # ZeroAverage, :91-99
+    avg, has_weight, terms = ob.weighted_average(np.zeros((1, 1)), [])
+    assert not has_weight and avg.tolist() == [0.0]
+
+
+def test_weighted_average_of_one_vector_has_no_roundoff():  # AveragesEqualWithoutRoundoff, :103-115
+    data = [1.0, 1.0 / 3, 3.0 / 7, 3.14159]
+    for count in (1, 2, 3):
+        avg, _, _ = ob.weighted_average([data] * count, [341.45, 1.4134, 7.23][:count])
+        assert avg.tolist() == data  # exactly
+
+
+def test_weighted_average_counts_zero_weight_terms():  # AddsZeroWeight, :117-127
+    avg, has_weight, terms = ob.weighted_average([[1.0]], [0.0])
+    assert not has_weight and avg.tolist() == [0.0] and terms == 1
+
+
+# ---- sharded_optimization_utils_test.cc:596-612: projections onto the variable bounds / dual sign constraints ----
+
+def test_projections_onto_bounds_of_test_lp():
+    p = ob.Problem(fixtures.make_test_lp(), num_threads=2, num_shards=2)
+    x, _ = p.project(x=[-3, -3, 5, 5])
+    assert x.tolist() == [-3, -2, 5, 3.5]
+    _, y = p.project(y=[1, 1, -1, -1])
+    assert y.tolist() == [1, 0, 0, -1]
