@@ -456,13 +456,17 @@ def test_feasibility_polishing_finds_valid_solution(backend):
 
 
 def test_feasibility_polishing_details_in_log(backend):
+    """FeasibilityPolishingDetailsInLog (:1740), ...UsesInfiniteTolerances (:1775), ...WorkStatsAreCorrect (:1816) and
+    FeasibilityObjectivesAreZero (:1857) on one solve."""
     p = polishing_params()
     p.record_iteration_stats = True
     out = backend.solve(polishing_primal_lp(), p)
     assert out.solve_log.termination_reason == TR.TERMINATION_REASON_OPTIMAL
     primal_optimal = dual_optimal = total_iterations = 0
     primal_infos = dual_infos = 0
+    total_feasibility_time = 0.0
     for phase in out.solve_log.feasibility_polishing_details:
+        total_feasibility_time += phase.solve_time_sec
         assert phase.polishing_phase_type in (PH_PRIMAL, PH_DUAL)
         assert phase.HasField("solution_stats") and phase.solution_stats.iteration_number == phase.iteration_count
         assert 0 <= phase.iteration_count <= phase.main_iteration_count / 4
@@ -489,6 +493,10 @@ def test_feasibility_polishing_details_in_log(backend):
     last = out.solve_log.iteration_stats[-1]
     assert total_iterations >= 1 and last.iteration_number >= 1
     assert last.iteration_number + total_iterations == out.solve_log.iteration_count
+    # solve_time_sec covers the main and the feasibility iterations; the main loop's cumulative_time_sec does not
+    # include the phases' time (:1843-1853).
+    assert total_feasibility_time > 0.0 and last.cumulative_time_sec > 0.0
+    assert total_feasibility_time + last.cumulative_time_sec <= out.solve_log.solve_time_sec
 
 
 def test_feasibility_polishing_callbacks(backend):
