@@ -150,6 +150,41 @@ def test_presolver_that_solves_everything_gives_a_presolver_solution():
     assert bad.solve_log.termination_reason in (TR.TERMINATION_REASON_PRIMAL_OR_DUAL_INFEASIBLE, TR.TERMINATION_REASON_OPTIMAL)
 
 
+@pytest.mark.gpu
+def test_presolve_solves_to_optimality_goldens():  # PresolveTest.PresolveSolvesToOptimality, :1976-2003
+    """Glop's preprocessor solves TestLp completely; here the caller's presolver does (it hands back the optimum).  The
+    statistics of the result are the reference's goldens for that point."""
+    x_opt, y_opt = np.array([-1.0, 8.0, 1.0, 2.5]), np.array([-2.0, 0.0, 2.375, 2.0 / 3.0])
+    p = pdlp_b200.PrimalDualHybridGradientParams()
+    out = pdlp_b200.primal_dual_hybrid_gradient_presolved(fixtures.make_test_lp(), None, lambda x, y: (x_opt, y_opt), p,
+                                                          presolve_status=pdlp_b200.glop_status_to_termination_reason(pdlp_b200.GlopProblemStatus.OPTIMAL))
+    log = out.solve_log
+    assert log.termination_reason == TR.TERMINATION_REASON_OPTIMAL and log.iteration_count == 0
+    assert log.solution_type == PT.POINT_TYPE_PRESOLVER_SOLUTION
+    np.testing.assert_allclose(out.primal_solution, x_opt, atol=1e-10, rtol=0)
+    np.testing.assert_allclose(out.dual_solution, y_opt, atol=1e-10, rtol=0)
+    infos = [c for c in log.solution_stats.convergence_information if c.candidate_type == PT.POINT_TYPE_PRESOLVER_SOLUTION]
+    assert len(infos) == 1
+    c = infos[0]
+    for name, want in (("primal_objective", -34.0), ("dual_objective", -34.0), ("corrected_dual_objective", -34.0), ("l_inf_primal_residual", 0.0),
+                       ("l2_primal_residual", 0.0), ("l_inf_dual_residual", 0.0), ("l2_dual_residual", 0.0), ("l_inf_primal_variable", 8.0),
+                       ("l2_primal_variable", 8.5), ("l_inf_dual_variable", 2.375)):
+        assert abs(getattr(c, name) - want) <= 4e-15 * max(1.0, abs(want)), (name, getattr(c, name))  # EXPECT_DOUBLE_EQ: 4 ulps
+    assert abs(c.l2_dual_variable - 3.17569983538) <= 1e-10
+
+
+@pytest.mark.gpu
+def test_presolve_infeasible():  # PresolveTest.PresolveInfeasible, :2027-2036
+    qp = fixtures.small_primal_infeasible_lp()
+    n, m = len(qp.objective_vector), len(qp.constraint_lower_bounds)
+    verdict = pdlp_b200.glop_status_to_termination_reason(pdlp_b200.GlopProblemStatus.PRIMAL_INFEASIBLE)
+    out = pdlp_b200.primal_dual_hybrid_gradient_presolved(qp, None, lambda x, y: (np.zeros(n), np.zeros(m)), pdlp_b200.PrimalDualHybridGradientParams(),
+                                                          presolve_status=verdict)
+    assert out.solve_log.termination_reason == TR.TERMINATION_REASON_PRIMAL_OR_DUAL_INFEASIBLE
+    assert out.solve_log.solution_type == PT.POINT_TYPE_PRESOLVER_SOLUTION
+    assert out.solve_log.iteration_count == 0
+
+
 # ---- internal::ComputeStatuses (primal_dual_hybrid_gradient.h:164, .cc:2835-2883): host code, no GPU ----
 
 CS, VS = pdlp_b200.ConstraintStatus, pdlp_b200.VariableStatus
