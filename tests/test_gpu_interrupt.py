@@ -52,7 +52,7 @@ def test_flag_raised_mid_solve_stops_the_device_loop_between_host_events():
     # Not at a host event: those sit at multiples of 4096 (and at the artificial restarts of the first iterations).
     assert log.iteration_count > 64 and log.iteration_count % 4096 != 0, log.iteration_count
     # The flag is seen within one iteration; what follows is the drain of at most two 32-trial chunks, the final
-    # termination check and the download of the result (a few ms at this size; measured 3-6 ms).  The two assertions
+    # termination check and the download of the result (a few ms at this size).  The two assertions
     # above are the proof of the device-side stop; this bound only guards against a regression to batch granularity
     # (a batch of 4096 iterations is well over 100 ms) without being sensitive to a loaded host.
     assert returned - raised["t"] < 0.1, returned - raised["t"]
