@@ -32,31 +32,39 @@ def test_flag_raised_mid_solve_stops_the_device_loop_between_host_events():
     warm = _never_converging_params()
     warm.termination_criteria.iteration_limit = 64
     pdlp_b200.primal_dual_hybrid_gradient(qp, warm, device=0)
-    flag = np.zeros(1, dtype=np.int32)
-    raised = {}
+    def attempt(delay):
+        flag = np.zeros(1, dtype=np.int32)
+        raised = {}
 
-    def raise_later():
-        time.sleep(0.25)
-        raised["t"] = time.perf_counter()
-        flag[0] = 1
+        def raise_later():
+            time.sleep(delay)
+            raised["t"] = time.perf_counter()
+            flag[0] = 1
 
-    t = threading.Thread(target=raise_later)
-    t.start()
-    result = pdlp_b200.primal_dual_hybrid_gradient(qp, _never_converging_params(), interrupt_solve=flag, device=0)
-    returned = time.perf_counter()
-    t.join()
-    log = result.solve_log
-    assert log.termination_reason == TR.TERMINATION_REASON_INTERRUPTED_BY_USER
-    counters = pdlp_b200.last_solve_counters()
+        t = threading.Thread(target=raise_later)
+        t.start()
+        result = pdlp_b200.primal_dual_hybrid_gradient(qp, _never_converging_params(), interrupt_solve=flag, device=0)
+        returned = time.perf_counter()
+        t.join()
+        return result.solve_log, pdlp_b200.last_solve_counters(), returned - raised["t"]
+
+    # The flag may go up while the host happens to be at one of its own events (a millisecond every 4096 iterations, and
+    # the artificial restarts at powers of two): the host then sees it first, which is correct but shows nothing about
+    # the device.  Such an attempt is repeated with another delay.
+    for delay in (0.25, 0.31, 0.37):
+        log, counters, latency = attempt(delay)
+        assert log.termination_reason == TR.TERMINATION_REASON_INTERRUPTED_BY_USER
+        assert log.iteration_count < 400000
+        if counters["interrupts_seen_on_device"] == 1:
+            break
     assert counters["interrupts_seen_on_device"] == 1, counters
     # Not at a host event: those sit at multiples of 4096 (and at the artificial restarts of the first iterations).
     assert log.iteration_count > 64 and log.iteration_count % 4096 != 0, log.iteration_count
     # The flag is seen within one iteration; what follows is the drain of at most two 32-trial chunks, the final
-    # termination check and the download of the result (a few ms at this size).  The two assertions
-    # above are the proof of the device-side stop; this bound only guards against a regression to batch granularity
-    # (a batch of 4096 iterations is well over 100 ms) without being sensitive to a loaded host.
-    assert returned - raised["t"] < 0.1, returned - raised["t"]
-    assert log.iteration_count < 400000
+    # termination check and the download of the result (a few ms at this size).  The assertions above are the proof of
+    # the device-side stop; this bound only guards against a regression to batch granularity (a batch of 4096
+    # iterations is well over 100 ms) without being sensitive to a loaded host.
+    assert latency < 0.1, latency
 
 
 def test_flag_already_raised_stops_at_iteration_zero_like_the_reference():
