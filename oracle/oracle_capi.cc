@@ -300,6 +300,35 @@ int oracle_shard_starts(int64_t n, int num_shards, const int64_t* masses /*nulla
   return sh->NumShards();
 }
 
+// The sharded BLAS-1 of sharder.h:241-335 by name, on vectors of length n with `num_shards` shards, for the small
+// examples of sharder_test.cc:260-405.  Vector results go to out_vec (n doubles), scalar results are returned.
+double oracle_blas1(const char* op, int64_t n, int num_shards, const double* a, const double* b, double scalar, double* out_vec) {
+  Sharder sh(n, num_shards, nullptr);
+  const std::string name(op);
+  const Vec va = a != nullptr ? Vec(a, a + n) : Vec(), vb = b != nullptr ? Vec(b, b + n) : Vec();
+  auto store = [&](const Vec& v) { std::copy(v.begin(), v.end(), out_vec); return 0.0; };
+  if (name == "SetZero") { Vec d = va; SetZero(sh, d); return store(d); }
+  if (name == "ZeroVector") return store(ZeroVector(sh));
+  if (name == "OnesVector") return store(OnesVector(sh));
+  if (name == "AddScaledVector") { Vec d = va; AddScaledVector(scalar, vb, sh, d); return store(d); }
+  if (name == "AssignVector") { Vec d; AssignVector(va, sh, d); return store(d); }
+  if (name == "CloneVector") return store(CloneVector(va, sh));
+  if (name == "CoefficientWiseProductInPlace") { Vec d = va; CwiseProductInPlace(vb, sh, d); return store(d); }
+  if (name == "CoefficientWiseQuotientInPlace") { Vec d = va; CwiseQuotientInPlace(vb, sh, d); return store(d); }
+  if (name == "Dot") return Dot(va, vb, sh);
+  if (name == "LInfNorm") return LInfNorm(va, sh);
+  if (name == "L1Norm") return L1Norm(va, sh);
+  if (name == "SquaredNorm") return SquaredNorm(va, sh);
+  if (name == "Norm") return Norm(va, sh);
+  if (name == "SquaredDistance") return SquaredDistance(va, vb, sh);
+  if (name == "Distance") return Distance(va, vb, sh);
+  if (name == "ScaledLInfNorm") return ScaledLInfNorm(va, vb, sh);
+  if (name == "ScaledSquaredNorm") return ScaledSquaredNorm(va, vb, sh);
+  if (name == "ScaledNorm") return ScaledNorm(va, vb, sh);
+  ORACLE_CHECK(false && "unknown BLAS-1 op");
+  return 0.0;
+}
+
 // ShardedWeightedAverage (sharded_optimization_utils.cc:43-79) fed `count` vectors of length n with their weights;
 // clear_after_add >= 0: Clear() after that many adds.  meta_out = {HasNonzeroWeight, NumTerms}.
 void oracle_weighted_average(int64_t n, int num_shards, int count, const double* vectors, const double* weights, int clear_after_add, double* avg_out,

@@ -22,6 +22,7 @@ def load():
         build()
     lib = ctypes.CDLL(ORACLE_LIB)
     lib.oracle_sigma_max.restype = ctypes.c_double
+    lib.oracle_blas1.restype = ctypes.c_double
     lib.oracle_problem_create.restype = ctypes.c_void_p
     return lib
 
@@ -280,6 +281,16 @@ def trust_region(obj, lb, ub, center, w, radius, diag=None, num_shards=1, tol=1e
     lib.oracle_trust_region(ctypes.c_int64(obj.size), _p(obj), _p(diag) if diag is not None else None, _p(lb), _p(ub), _p(center), _p(w),
                             ctypes.c_double(radius), int(num_shards), ctypes.c_double(tol), _p(sol), _p(out))
     return sol[: obj.size], out[0], out[1]
+
+
+def blas1(op, n, a=None, b=None, scalar=0.0, num_shards=2):
+    """A sharded BLAS-1 function of sharder.h by its reference name: (scalar result, vector result)."""
+    va = None if a is None else _f(a)
+    vb = None if b is None else _f(b)
+    out = np.zeros(max(n, 1))
+    r = load().oracle_blas1(op.encode(), ctypes.c_int64(n), int(num_shards), _p(va) if va is not None else None, _p(vb) if vb is not None else None,
+                            ctypes.c_double(scalar), _p(out))
+    return r, out[:n]
 
 
 def weighted_average(vectors, weights, num_shards=1, clear_after_add=-1):

@@ -241,3 +241,59 @@ def test_projections_onto_bounds_of_test_lp():
     assert x.tolist() == [-3, -2, 5, 3.5]
     _, y = p.project(y=[1, 1, -1, -1])
     assert y.tolist() == [1, 0, 0, -1]
+
+
+# ---- sharder_test.cc:260-405: the sharded BLAS-1 every vector pass of the reference goes through ----
+
+@pytest.mark.parametrize("op, a, b, scalar, want", [
+    ("SetZero", [1, 7, 0], None, 0.0, [0.0, 0.0, 0.0]),                         # :260 (the reference resizes a 2-vector to 3)
+    ("ZeroVector", None, None, 0.0, [0.0, 0.0, 0.0]),                           # :267
+    ("OnesVector", None, None, 0.0, [1.0, 1.0, 1.0]),                           # :272
+    ("AddScaledVector", [4, 5, 20], [1, 7, 3], 2.0, [6, 19, 26]),              # :277
+    ("AssignVector", [1, 7, 3], None, 0.0, [1, 7, 3]),                          # :285
+    ("CloneVector", [1, 7, 3], None, 0.0, [1, 7, 3]),                           # :293
+    ("CoefficientWiseProductInPlace", [4, 5, 20], [1, 2, 3], 0.0, [4, 10, 60]),  # :299
+    ("CoefficientWiseQuotientInPlace", [4, 6, 20], [1, 2, 5], 0.0, [4, 3, 4]),  # :308
+])
+def test_sharded_vector_operations(op, a, b, scalar, want):
+    _, got = ob.blas1(op, 3, a, b, scalar)
+    assert got.tolist() == want
+
+
+@pytest.mark.parametrize("op, a, b, want, tol", [
+    ("Dot", [1, 2, 3], [4, 5, 6], 32.0, 1e-13),                     # :317
+    ("LInfNorm", [-1, 2, -3], None, 3.0, 0.0),                      # :325
+    ("L1Norm", [-1, 2, -3], None, 6.0, 0.0),                        # :339
+    ("SquaredNorm", [1, 2, 3], None, 14.0, 1e-13),                  # :353
+    ("Norm", [1, 2, 3], None, 14.0 ** 0.5, 1e-13),                  # :360
+    ("SquaredDistance", [1, 1, 1], [1, 2, 3], 5.0, 1e-13),          # :367
+    ("Distance", [1, 1, 1], [1, 2, 3], 5.0 ** 0.5, 1e-13),          # :375
+    ("ScaledLInfNorm", [-1, 2, -3], [4, 6, 1], 12.0, 0.0),          # :383
+    ("ScaledSquaredNorm", [-1, 2, -3], [4, 6, 1], 169.0, 0.0),      # :391
+    ("ScaledNorm", [-1, 2, -3], [4, 6, 1], 13.0, 0.0),              # :399
+])
+def test_sharded_reductions(op, a, b, want, tol):
+    got, _ = ob.blas1(op, 3, a, b)
+    assert abs(got - want) <= tol
+
+
+def test_norms_of_empty_vectors():  # LInfNormTest.EmptyExample :332, L1NormTest.EmptyExample :346
+    assert ob.blas1("LInfNorm", 0, np.zeros(0))[0] == 0 and ob.blas1("L1Norm", 0, np.zeros(0))[0] == 0
+
+
+@pytest.mark.parametrize("size", [10, 1000, 100 * 1000])
+def test_various_sizes_threaded(size):  # VariousSizesTest.LargeMatVec / LargeVectors, sharder_test.cc:431-460: 5 threads, 15 shards
+    import scipy.sparse as sp
+    rng = np.random.default_rng(size)
+    nnz = 8 * size
+    K = sp.coo_matrix((rng.standard_normal(nnz), (rng.integers(0, size, nnz), rng.integers(0, size, nnz))), shape=(size, size)).tocsc()
+    K.sum_duplicates()
+    qp = pdlp_b200.QuadraticProgram()
+    qp.resize_and_initialize(size, size)
+    qp.constraint_matrix = K
+    p = ob.Problem(qp, num_threads=5, num_shards=15)
+    v = rng.uniform(-1, 1, size)
+    assert np.linalg.norm(K.T @ v - p.matvec(0, v)) <= 1.0e-8
+    assert np.linalg.norm(K @ v - p.matvec(1, v)) <= 1.0e-8
+    got, _ = ob.blas1("SquaredNorm", size, v, num_shards=5)
+    assert abs(got - float(v @ v)) <= size * 1.0e-14
