@@ -407,6 +407,16 @@ void oracle_problem_get_transposed_values(void* h, double* val) {
   const Csc& kt = static_cast<OracleProblem*>(h)->sq->Kt();
   std::copy(kt.val.begin(), kt.val.end(), val);
 }
+// SetRandomProjections (iteration_stats.cc:598-610): one primal and one dual projection per seed.
+void oracle_random_projections(void* h, const double* x, const double* y, const int* seeds, int count, double* primal_out, double* dual_out) {
+  const ShardedQp& sq = *static_cast<OracleProblem*>(h)->sq;
+  const Vec vx(x, x + sq.PrimalSize()), vy(y, y + sq.DualSize());
+  for (int k = 0; k < count; ++k) {
+    std::mt19937 gen(seeds[k]);
+    primal_out[k] = RandomProjection(vx, sq.PrimalSharder(), gen);
+    dual_out[k] = RandomProjection(vy, sq.DualSharder(), gen);
+  }
+}
 // ProjectToPrimalVariableBounds / ProjectToDualVariableBounds (sharded_optimization_utils.cc:701-750), in place.
 void oracle_project(void* h, double* x /*nullable*/, double* y /*nullable*/) {
   const ShardedQp& sq = *static_cast<OracleProblem*>(h)->sq;

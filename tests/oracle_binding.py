@@ -214,6 +214,14 @@ class Problem:
         self.lib.oracle_problem_get_transposed_values(self.h, _p(out))
         return out[:nnz]
 
+    def random_projections(self, x, y, seeds):
+        """SetRandomProjections (iteration_stats.cc:598-610): (primal projections, dual projections), one per seed."""
+        x, y = _f(x), _f(y)
+        s = np.ascontiguousarray(seeds, dtype=np.int32)
+        po, do = np.zeros(max(len(s), 1)), np.zeros(max(len(s), 1))
+        self.lib.oracle_random_projections(self.h, _p(x), _p(y), ctypes.c_void_p(s.ctypes.data), len(s), _p(po), _p(do))
+        return po[: len(s)], do[: len(s)]
+
     def project(self, x=None, y=None):
         """ProjectToPrimalVariableBounds / ProjectToDualVariableBounds (sharded_optimization_utils.cc:701-750): copies."""
         px = None if x is None else _f(x).copy()

@@ -297,3 +297,20 @@ def test_various_sizes_threaded(size):  # VariousSizesTest.LargeMatVec / LargeVe
     assert np.linalg.norm(K @ v - p.matvec(1, v)) <= 1.0e-8
     got, _ = ob.blas1("SquaredNorm", size, v, num_shards=5)
     assert abs(got - float(v @ v)) <= size * 1.0e-14
+
+
+# ---- iteration_stats_test.cc:132-161: random projections (values unpinned: absl::Gaussian; the properties hold) ----
+
+def test_random_projection_of_the_zero_vector_is_zero():
+    p = ob.Problem(fixtures.make_test_lp(), num_threads=2, num_shards=10)
+    primal, dual = p.random_projections(np.zeros(4), np.zeros(4), [1])
+    assert primal.tolist() == [0.0] and dual.tolist() == [0.0]
+
+
+def test_two_random_projections_of_a_vector():
+    p = ob.Problem(fixtures.make_test_lp(), num_threads=2, num_shards=10)
+    primal, dual = p.random_projections(np.ones(4), np.zeros(4), [1, 2])
+    assert len(primal) == 2 and len(dual) == 2
+    # The primal point has norm 2; a projection onto a unit direction can only reduce it, and is 0 with probability 0.
+    assert all(-2.0 <= v <= 2.0 and v != 0.0 for v in primal)
+    assert all(v == 0.0 for v in dual)
