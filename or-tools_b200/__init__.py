@@ -223,7 +223,7 @@ from .mp_model import (  # noqa: E402
     qp_to_mpmodel_proto,
 )
 from . import qp_io  # noqa: E402
-from .qp_io import read_quadratic_program_or_die  # noqa: E402
+from .qp_io import combine_repeated_triplets_in_place, read_quadratic_program_or_die, set_matrix_from_triplets  # noqa: E402
 from .sharding import (  # noqa: E402
     ColumnShard,
     RowSharing,

@@ -42,6 +42,44 @@ _MAX_FIXED_LINE = _FIELD_START[-1] + _FIELD_LENGTH[-1]
 _BOUND_TYPES = {"LO", "UP", "FX", "FR", "MI", "PL", "BV", "LI", "UI", "SC"}
 
 
+def combine_repeated_triplets_in_place(triplets):
+    """internal::CombineRepeatedTripletsInPlace (quadratic_program.cc:346-364): sums CONSECUTIVE (row, column, value)
+    entries with equal row and column, in place; entries that repeat further apart stay separate."""
+    if not triplets:
+        return
+    out = 0
+    for k in range(1, len(triplets)):
+        row, col, value = triplets[k]
+        if triplets[out][0] == row and triplets[out][1] == col:
+            triplets[out] = (row, col, triplets[out][2] + value)
+        else:
+            out += 1
+            triplets[out] = (row, col, value)
+    del triplets[out + 1:]
+
+
+def set_matrix_from_triplets(rows, cols, values, shape):
+    """SetEigenMatrixFromTriplets (quadratic_program.cc:315-343): the compressed column-major matrix of the triplets
+    sorted by (column, row) with repeated entries summed; an entry whose values sum to zero stays stored, as Eigen's
+    insert() keeps it."""
+    rows = np.asarray(rows, dtype=np.int64).reshape(-1)
+    cols = np.asarray(cols, dtype=np.int64).reshape(-1)
+    values = np.asarray(values, dtype=np.float64).reshape(-1)
+    order = np.lexsort((rows, cols))  # stable: equal entries keep their order, so the sums associate as the reference's
+    rows, cols, values = rows[order], cols[order], values[order]
+    if len(rows):
+        first = np.ones(len(rows), dtype=bool)
+        first[1:] = (rows[1:] != rows[:-1]) | (cols[1:] != cols[:-1])
+        starts = np.flatnonzero(first)
+        group = np.cumsum(first) - 1
+        summed = np.zeros(len(starts))
+        np.add.at(summed, group, values)  # left to right within a group
+        rows, cols, values = rows[starts], cols[starts], summed
+    indptr = np.zeros(shape[1] + 1, dtype=np.int64)
+    np.add.at(indptr, cols + 1, 1)
+    return _sp.csc_matrix((values, rows, np.cumsum(indptr)), shape=shape)
+
+
 class MpsParseError(ValueError):
     pass
 
@@ -326,10 +364,7 @@ class _Parser:
         c = np.zeros(n)
         for j, v in self.obj.items():
             c[j] = v
-        K = _sp.coo_matrix((np.array(self.trip_v, dtype=np.float64), (np.array(self.trip_r, dtype=np.int64), np.array(self.trip_c, dtype=np.int64))),
-                           shape=(m, n)).tocsc()  # duplicates are summed
-        K.sort_indices()
-        qp.constraint_matrix = K
+        qp.constraint_matrix = set_matrix_from_triplets(self.trip_r, self.trip_c, self.trip_v, (m, n))  # quadratic_program_io.cc:257
         qp.objective_offset = self.objective_offset
         if self.maximize:
             qp.objective_scaling_factor = -1.0

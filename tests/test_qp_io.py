@@ -274,3 +274,30 @@ def test_read_then_solve(backend, tmp_path):
     r = backend.solve(qp, p)
     assert r.solve_log.termination_reason == pdlp_b200.TerminationReason.TERMINATION_REASON_OPTIMAL
     np.testing.assert_allclose(r.primal_solution, [-1, 8, 1, 2.5], atol=1e-6)
+
+
+# ---- quadratic_program_test.cc:426-487: the triplet helpers behind the MPS reader's matrix ----
+
+@pytest.mark.parametrize("triplets,expected", [
+    ([], []),
+    ([(1, 2, 3.0)], [(1, 2, 3.0)]),
+    ([(1, 2, 3.0), (2, 1, 1.0), (1, 1, 0.0)], [(1, 2, 3.0), (2, 1, 1.0), (1, 1, 0.0)]),
+    ([(1, 2, 3.0), (1, 2, -1.0), (1, 1, 0.0)], [(1, 2, 2.0), (1, 1, 0.0)]),
+    ([(1, 2, 3.0), (2, 1, 1.0), (2, 1, 1.0)], [(1, 2, 3.0), (2, 1, 2.0)]),
+    ([(1, 2, 3.0), (1, 2, 1.0), (1, 2, 2.0)], [(1, 2, 6.0)]),
+])
+def test_combine_repeated_triplets_in_place(triplets, expected):
+    pdlp_b200.combine_repeated_triplets_in_place(triplets)
+    assert triplets == expected
+
+
+def test_set_matrix_from_triplets_handles_an_empty_matrix():
+    K = pdlp_b200.set_matrix_from_triplets([], [], [], (2, 2))
+    np.testing.assert_array_equal(K.toarray(), [[0, 0], [0, 0]])
+
+
+def test_set_matrix_from_triplets_is_correct_for_a_tiny_matrix():
+    triplets = [(0, 0, 1.0), (1, 0, -1.0), (0, 0, 0.0), (1, 1, 1.0), (0, 0, 1.0)]
+    K = pdlp_b200.set_matrix_from_triplets([t[0] for t in triplets], [t[1] for t in triplets], [t[2] for t in triplets], (2, 2))
+    np.testing.assert_array_equal(K.toarray(), [[2, 0], [-1, 1]])
+    assert K.has_sorted_indices and K.nnz == 3 and K.indptr.tolist() == [0, 2, 3]
