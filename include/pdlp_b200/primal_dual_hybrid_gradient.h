@@ -18,6 +18,7 @@
 #ifndef PDLP_B200_PRIMAL_DUAL_HYBRID_GRADIENT_H_
 #define PDLP_B200_PRIMAL_DUAL_HYBRID_GRADIENT_H_
 
+#include <algorithm>
 #include <atomic>
 #include <cstdint>
 #include <functional>
@@ -33,6 +34,34 @@ namespace pdlp_b200 {
 
 using VectorXd = std::vector<double>;
 
+// One (row, column, value) entry: the role of Eigen::Triplet<double, int64_t> in quadratic_program.h:194-213.
+struct Triplet {
+  Triplet() = default;
+  Triplet(int64_t row, int64_t col, double value) : row_(row), col_(col), value_(value) {}
+  int64_t row() const { return row_; }
+  int64_t col() const { return col_; }
+  double value() const { return value_; }
+ private:
+  int64_t row_ = 0, col_ = 0;
+  double value_ = 0.0;
+};
+
+namespace internal {
+// quadratic_program.cc:346-364: sums consecutive entries with equal row and column, in place.
+inline void CombineRepeatedTripletsInPlace(std::vector<Triplet>& triplets) {
+  if (triplets.empty()) return;
+  size_t out = 0;
+  for (size_t p = 1; p < triplets.size(); ++p) {
+    if (triplets[out].row() == triplets[p].row() && triplets[out].col() == triplets[p].col()) {
+      triplets[out] = Triplet(triplets[out].row(), triplets[out].col(), triplets[out].value() + triplets[p].value());
+    } else {
+      triplets[++out] = triplets[p];
+    }
+  }
+  triplets.resize(out + 1);
+}
+}  // namespace internal
+
 // Compressed sparse column matrix, rows x cols.
 struct SparseMatrixCsc {
   int64_t rows = 0, cols = 0;
@@ -40,10 +69,34 @@ struct SparseMatrixCsc {
   std::vector<int64_t> inner_index;     // row of every nonzero
   std::vector<double> values;
   int64_t nonZeros() const { return static_cast<int64_t>(values.size()); }
+  // What Eigen's setFromTriplets(begin, end) leaves behind: compressed columns, rows ascending, repeated entries summed.
+  template <typename It> void setFromTriplets(It begin, It end);
 };
+// SetEigenMatrixFromTriplets (quadratic_program.cc:315-343): `matrix` keeps its rows x cols; entries sorted by
+// (column, row), repeated ones summed, an entry that sums to zero stays stored.
+inline void SetEigenMatrixFromTriplets(std::vector<Triplet> triplets, SparseMatrixCsc& matrix) {
+  std::stable_sort(triplets.begin(), triplets.end(), [](const Triplet& a, const Triplet& b) {
+    return a.col() != b.col() ? a.col() < b.col() : a.row() < b.row();
+  });
+  internal::CombineRepeatedTripletsInPlace(triplets);
+  matrix.outer_index.assign(matrix.cols + 1, 0);
+  matrix.inner_index.clear();
+  matrix.values.clear();
+  for (const Triplet& t : triplets) {
+    ++matrix.outer_index[t.col() + 1];
+    matrix.inner_index.push_back(t.row());
+    matrix.values.push_back(t.value());
+  }
+  for (int64_t j = 0; j < matrix.cols; ++j) matrix.outer_index[j + 1] += matrix.outer_index[j];
+}
+template <typename It> void SparseMatrixCsc::setFromTriplets(It begin, It end) {
+  SetEigenMatrixFromTriplets(std::vector<Triplet>(begin, end), *this);
+}
 
 // quadratic_program.h:53-143.
 struct QuadraticProgram {
+  QuadraticProgram() = default;
+  QuadraticProgram(int64_t num_variables, int64_t num_constraints) { ResizeAndInitialize(num_variables, num_constraints); }  // quadratic_program.h:55-57
   VectorXd objective_vector;
   std::optional<VectorXd> objective_matrix;  // diagonal; the 1/2 is implicit
   SparseMatrixCsc constraint_matrix;
@@ -98,6 +151,23 @@ struct IterationCallbackInfo {
   IterationStats iteration_stats;
   QuadraticProgramBoundNorms bound_norms;
 };
+
+// iteration_stats.h:89-102 (iteration_stats.cc:567-597): the entry of `stats` for one candidate point, if present.
+inline std::optional<ConvergenceInformation> GetConvergenceInformation(const IterationStats& stats, int candidate_type) {
+  for (const ConvergenceInformation& info : stats.convergence_information) if (info.candidate_type == candidate_type) return info;
+  return std::nullopt;
+}
+inline std::optional<InfeasibilityInformation> GetInfeasibilityInformation(const IterationStats& stats, int candidate_type) {
+  for (const InfeasibilityInformation& info : stats.infeasibility_information) if (info.candidate_type == candidate_type) return info;
+  return std::nullopt;
+}
+inline std::optional<PointMetadata> GetPointMetadata(const IterationStats& stats, int point_type) {
+  for (const PointMetadata& metadata : stats.point_metadata) if (metadata.point_type == point_type) return metadata;
+  return std::nullopt;
+}
+// The generated-code spellings of the enum name tables (solve_log.pb.h).
+inline const char* TerminationReason_Name(int reason) { return TerminationReasonName(reason); }
+inline const char* PointType_Name(int point_type) { return PointTypeName(point_type); }
 
 // Device placement; not part of the reference API (defaults reproduce it).
 struct DeviceOptions {

@@ -165,7 +165,7 @@ def _describe():
     return text
 
 
-_classes, _enums, _file_protos = _schema.build(_describe())
+_classes, _enums, _file_protos, _enum_wrappers = _schema.build(_describe())
 
 
 def _namespace(file_key, names):
@@ -176,7 +176,7 @@ def _namespace(file_key, names):
     for ename, values in _enums.items():
         if "." in ename:
             continue
-        setattr(ns, ename, types.SimpleNamespace(**values))
+        setattr(ns, ename, _enum_wrappers[ename])  # solve_log_pb2.TerminationReason.Name(...) as in a generated module
         for k, v in values.items():
             setattr(ns, k, v)
     return ns
@@ -189,9 +189,9 @@ TerminationCriteria = _classes["TerminationCriteria"]
 SolveLog = _classes["SolveLog"]
 IterationStats = _classes["IterationStats"]
 QuadraticProgramStats = _classes["QuadraticProgramStats"]
-TerminationReason = types.SimpleNamespace(**_enums["TerminationReason"])
-PointType = types.SimpleNamespace(**_enums["PointType"])
-RestartChoice = types.SimpleNamespace(**_enums["RestartChoice"])
+TerminationReason = _enum_wrappers["TerminationReason"]
+PointType = _enum_wrappers["PointType"]
+RestartChoice = _enum_wrappers["RestartChoice"]
 
 from ._api import (  # noqa: E402
     ConstraintStatus,

@@ -8,6 +8,7 @@ The classes are wire- and text-format compatible with
 compiled from the reference .proto files (fixture under tests/golden/).
 """
 from google.protobuf import descriptor_pb2, descriptor_pool, message_factory
+from google.protobuf.internal import enum_type_wrapper
 
 _PACKAGE = "operations_research.pdlp"
 _FILES = {"solvers": "ortools/pdlp/solvers.proto", "solve_log": "ortools/pdlp/solve_log.proto"}
@@ -32,7 +33,8 @@ def _container(file_proto, nested_index, dotted, kind):
 
 
 def build(describe_text):
-    """Parses the description and returns {message_name: class}, {enum_name: {value_name: number}}."""
+    """Parses the description and returns {message_name: class}, {enum_name: {value_name: number}}, the file
+    protos and {enum_name: EnumTypeWrapper} (what a generated _pb2 module exposes: `.Name()`, `.Value()`, `.keys()`)."""
     files = {}
     for key, name in _FILES.items():
         fp = descriptor_pb2.FileDescriptorProto()
@@ -123,4 +125,5 @@ def build(describe_text):
     classes = {}
     for name in msg_names:
         classes[name] = message_factory.GetMessageClass(pool.FindMessageTypeByName(_PACKAGE + "." + name))
-    return classes, enums, files
+    wrappers = {name: enum_type_wrapper.EnumTypeWrapper(pool.FindEnumTypeByName(_PACKAGE + "." + name)) for name in enums}
+    return classes, enums, files, wrappers

@@ -57,6 +57,38 @@ int main(int argc, char** argv) {
     using VS = pdlp::VariableStatus;
     if (st.constraint_statuses != std::vector<CS>{CS::FIXED_VALUE, CS::BASIC, CS::AT_LOWER_BOUND, CS::AT_LOWER_BOUND}) return 5;
     if (st.variable_statuses != std::vector<VS>{VS::BASIC, VS::BASIC, VS::BASIC, VS::AT_LOWER_BOUND}) return 6;
+    // CombineRepeatedTripletsInPlace / SetEigenMatrixFromTriplets (quadratic_program_test.cc:426-487).
+    std::vector<pdlp::Triplet> t1 = {{1, 2, 3.0}, {1, 2, -1.0}, {1, 1, 0.0}};
+    pdlp::internal::CombineRepeatedTripletsInPlace(t1);
+    if (t1.size() != 2 || t1[0].row() != 1 || t1[0].col() != 2 || t1[0].value() != 2.0 || t1[1].col() != 1 || t1[1].value() != 0.0) return 8;
+    std::vector<pdlp::Triplet> t2 = {{1, 2, 3.0}, {1, 2, 1.0}, {1, 2, 2.0}}, t3;
+    pdlp::internal::CombineRepeatedTripletsInPlace(t2);
+    pdlp::internal::CombineRepeatedTripletsInPlace(t3);
+    if (t2.size() != 1 || t2[0].value() != 6.0 || !t3.empty()) return 9;
+    pdlp::SparseMatrixCsc tiny;
+    tiny.rows = tiny.cols = 2;
+    pdlp::SetEigenMatrixFromTriplets({{0, 0, 1.0}, {1, 0, -1.0}, {0, 0, 0.0}, {1, 1, 1.0}, {0, 0, 1.0}}, tiny);  // dense [[2, 0], [-1, 1]]
+    if (tiny.outer_index != std::vector<int64_t>{0, 2, 3} || tiny.inner_index != std::vector<int64_t>{0, 1, 1} || tiny.values != std::vector<double>{2, -1, 1}) return 13;
+    pdlp::SparseMatrixCsc none;
+    none.rows = none.cols = 2;
+    pdlp::SetEigenMatrixFromTriplets({}, none);
+    if (none.outer_index != std::vector<int64_t>{0, 0, 0} || none.nonZeros() != 0) return 14;
+    // The sample's way of building TestLp gives the same arrays as the ones typed in above.
+    pdlp::QuadraticProgram built(4, 4);
+    const std::vector<pdlp::Triplet> entries = {{0, 0, 2}, {0, 1, 1}, {0, 2, 1}, {0, 3, 2}, {1, 0, 1}, {1, 2, 1}, {2, 0, 4}, {3, 2, 1.5}, {3, 3, -1}};
+    built.constraint_matrix.setFromTriplets(entries.begin(), entries.end());
+    const pdlp::QuadraticProgram typed = TestLp();
+    if (built.constraint_matrix.outer_index != typed.constraint_matrix.outer_index || built.constraint_matrix.inner_index != typed.constraint_matrix.inner_index ||
+        built.constraint_matrix.values != typed.constraint_matrix.values || built.variable_lower_bounds.size() != 4) return 15;
+    // GetConvergenceInformation / GetInfeasibilityInformation / GetPointMetadata (iteration_stats.cc:567-597).
+    pdlp::IterationStats stats;
+    stats.convergence_information.emplace_back();
+    stats.convergence_information.back().candidate_type = pdlp::POINT_TYPE_AVERAGE_ITERATE;
+    stats.convergence_information.back().primal_objective = 1.5;
+    if (pdlp::GetConvergenceInformation(stats, pdlp::POINT_TYPE_CURRENT_ITERATE).has_value()) return 16;
+    if (pdlp::GetConvergenceInformation(stats, pdlp::POINT_TYPE_AVERAGE_ITERATE)->primal_objective != 1.5) return 17;
+    if (pdlp::GetInfeasibilityInformation(stats, pdlp::POINT_TYPE_AVERAGE_ITERATE).has_value() || pdlp::GetPointMetadata(stats, pdlp::POINT_TYPE_AVERAGE_ITERATE).has_value()) return 18;
+    if (std::strcmp(pdlp::TerminationReason_Name(pdlp::TERMINATION_REASON_OPTIMAL), "TERMINATION_REASON_OPTIMAL") != 0) return 19;
     std::printf("cpu ok: %s | %s\n", r1.solve_log.termination_string.get().c_str(), r2.solve_log.termination_string.get().c_str());
     return 0;
   }

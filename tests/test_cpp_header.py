@@ -14,10 +14,10 @@ BUILD = os.path.join(ROOT, "tests", "_build")
 LIBDIR = os.path.join(ROOT, "or-tools_b200", "lib")
 
 
-def build():
+def build(name="cpp_caller", source=("tests", "cpp", "caller.cc")):
     os.makedirs(BUILD, exist_ok=True)
-    exe = os.path.join(BUILD, "cpp_caller")
-    src = os.path.join(ROOT, "tests", "cpp", "caller.cc")
+    exe = os.path.join(BUILD, name)
+    src = os.path.join(ROOT, *source)
     deps = [src, os.path.join(LIBDIR, "libpdlp_b200.so")] + [os.path.join(ROOT, "include", "pdlp_b200", h) for h in os.listdir(os.path.join(ROOT, "include", "pdlp_b200"))]
     if not os.path.exists(exe) or os.path.getmtime(exe) < max(os.path.getmtime(d) for d in deps):
         subprocess.run(["g++", "-std=c++17", "-O1", "-Wall", "-I" + os.path.join(ROOT, "include"), src, "-L" + LIBDIR, "-lpdlp_b200",
@@ -36,3 +36,20 @@ def test_reference_style_caller_solves_test_lp_on_the_device():
     run = subprocess.run([build(), "gpu"], capture_output=True, text=True, timeout=300)
     assert run.returncode == 0, (run.returncode, run.stdout, run.stderr)
     assert "gpu ok: OPTIMAL" in run.stdout
+
+
+def test_the_sample_program_compiles_against_the_header():
+    """samples/simple_pdlp_program.cc: the reference's sample (ortools/pdlp/samples/simple_pdlp_program.cc) on this header."""
+    assert os.path.exists(build("simple_pdlp_program", ("samples", "simple_pdlp_program.cc")))
+
+
+@pytest.mark.gpu
+def test_the_sample_program_solves_config_1_on_the_device():
+    run = subprocess.run([build("simple_pdlp_program", ("samples", "simple_pdlp_program.cc"))], capture_output=True, text=True, timeout=300)
+    assert run.returncode == 0, (run.returncode, run.stdout, run.stderr)
+    lines = run.stdout.splitlines()
+    assert lines[0] == "Solve successful"
+    primal = [float(v) for v in lines[lines.index("Primal solution:") + 1: lines.index("Dual solution:")]]
+    assert max(abs(a - b) for a, b in zip(primal, [-1, 8, 1, 2.5])) < 1e-4  # test_util.h:45-48
+    objective = [float(line.split(":")[1]) for line in lines if line.startswith("Primal objective")]
+    assert len(objective) == 1 and abs(objective[0] + 34.0) < 1e-4

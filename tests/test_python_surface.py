@@ -160,3 +160,31 @@ def test_starting_point(backend):
     result = backend.solve(tiny_lp(), params, initial_solution=([1.0, 0.0, 6.0, 2.0], [0.5, 4.0, 0.0]))
     assert result.solve_log.termination_reason == solve_log_pb2.TERMINATION_REASON_OPTIMAL
     assert result.solve_log.iteration_count == 0
+
+
+# ---- samples/simple_pdlp_program.py (BASELINE.json config 1) ----
+
+def test_simple_pdlp_program_sample(backend, capsys):
+    import importlib.util
+    import os
+
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "samples", "simple_pdlp_program.py")
+    spec = importlib.util.spec_from_file_location("simple_pdlp_program", path)
+    sample = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(sample)
+    result = sample.main(solve=backend.solve)
+    out = capsys.readouterr().out
+    assert out.startswith("Solve successful\n")
+    assert "Solution type: POINT_TYPE_" in out and "Iterations:" in out
+    np.testing.assert_allclose(result.primal_solution, [-1, 8, 1, 2.5], atol=1e-4)  # test_util.h:45-48
+    np.testing.assert_allclose(result.dual_solution, [-2, 0, 2.375, 2 / 3], atol=1e-4)
+    primal = [float(line.split(":")[1]) for line in out.splitlines() if line.startswith("Primal objective")]
+    assert len(primal) == 1 and abs(primal[0] + 34.0) < 1e-4
+
+
+def test_enum_namespaces_behave_like_generated_modules():
+    assert solve_log_pb2.TerminationReason.Name(solve_log_pb2.TERMINATION_REASON_OPTIMAL) == "TERMINATION_REASON_OPTIMAL"
+    assert solve_log_pb2.TerminationReason.Value("TERMINATION_REASON_ITERATION_LIMIT") == solve_log_pb2.TERMINATION_REASON_ITERATION_LIMIT
+    assert solve_log_pb2.PointType.Name(pdlp.PointType.POINT_TYPE_AVERAGE_ITERATE) == "POINT_TYPE_AVERAGE_ITERATE"
+    assert "RESTART_CHOICE_NO_RESTART" in solve_log_pb2.RestartChoice.keys()
+    assert solvers_pb2.PrimalDualHybridGradientParams.RestartStrategy.Name(solvers_pb2.PrimalDualHybridGradientParams.ADAPTIVE_HEURISTIC) == "ADAPTIVE_HEURISTIC"
