@@ -122,6 +122,9 @@ def _tight():
     params = solvers_pb2.PrimalDualHybridGradientParams()
     params.termination_criteria.simple_optimality_criteria.eps_optimal_relative = 0.0
     params.termination_criteria.simple_optimality_criteria.eps_optimal_absolute = 1.0e-10
+    # Not in the reference's test (its limit is INT32_MAX): a guard that turns a solve that does not converge into a
+    # failed assertion instead of a hung suite.  The oracle needs 320 / 192 iterations.
+    params.termination_criteria.iteration_limit = 20000
     return params
 
 
