@@ -39,17 +39,16 @@ def test_reference_style_caller_solves_test_lp_on_the_device():
 
 
 def test_the_sample_program_compiles_against_the_header():
-    """samples/simple_pdlp_program.cc: the reference's sample (ortools/pdlp/samples/simple_pdlp_program.cc) on this header."""
-    assert os.path.exists(build("simple_pdlp_program", ("samples", "simple_pdlp_program.cc")))
+    """samples/config1_small_lp.cc: BASELINE.json config 1 (the reference's sample LP) on this header."""
+    assert os.path.exists(build("config1_small_lp", ("samples", "config1_small_lp.cc")))
 
 
 @pytest.mark.gpu
 def test_the_sample_program_solves_config_1_on_the_device():
-    run = subprocess.run([build("simple_pdlp_program", ("samples", "simple_pdlp_program.cc"))], capture_output=True, text=True, timeout=300)
+    run = subprocess.run([build("config1_small_lp", ("samples", "config1_small_lp.cc"))], capture_output=True, text=True, timeout=300)
     assert run.returncode == 0, (run.returncode, run.stdout, run.stderr)
     lines = run.stdout.splitlines()
-    assert lines[0] == "Solve successful"
-    primal = [float(v) for v in lines[lines.index("Primal solution:") + 1: lines.index("Dual solution:")]]
+    assert lines[0].startswith("TERMINATION_REASON_OPTIMAL after ")
+    assert abs(float(lines[1].split()[2]) + 34.0) < 1e-4
+    primal = [float(line.split()[1]) for line in lines if line.startswith("x")]
     assert max(abs(a - b) for a, b in zip(primal, [-1, 8, 1, 2.5])) < 1e-4  # test_util.h:45-48
-    objective = [float(line.split(":")[1]) for line in lines if line.startswith("Primal objective")]
-    assert len(objective) == 1 and abs(objective[0] + 34.0) < 1e-4

@@ -165,24 +165,25 @@ def test_starting_point(backend):
     assert result.solve_log.iteration_count == 0
 
 
-# ---- samples/simple_pdlp_program.py (BASELINE.json config 1) ----
+# ---- samples/config1_small_lp.py (BASELINE.json config 1) ----
 
-def test_simple_pdlp_program_sample(backend, capsys):
+def test_config1_sample(backend):
     import importlib.util
+    import io
     import os
 
-    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "samples", "simple_pdlp_program.py")
-    spec = importlib.util.spec_from_file_location("simple_pdlp_program", path)
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "samples", "config1_small_lp.py")
+    spec = importlib.util.spec_from_file_location("config1_small_lp", path)
     sample = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(sample)
-    result = sample.main(solve=backend.solve)
-    out = capsys.readouterr().out
-    assert out.startswith("Solve successful\n")
-    assert "Solution type: POINT_TYPE_" in out and "Iterations:" in out
+    text = io.StringIO()
+    result = sample.run(solve=backend.solve, out=text)
+    lines = text.getvalue().splitlines()
+    assert lines[0].startswith("TERMINATION_REASON_OPTIMAL after ") and "returned point: POINT_TYPE_" in lines[0]
+    assert lines[1].startswith("objective: primal ") and abs(float(lines[1].split()[2]) + 34.0) < 1e-4
     np.testing.assert_allclose(result.primal_solution, [-1, 8, 1, 2.5], atol=1e-4)  # test_util.h:45-48
     np.testing.assert_allclose(result.dual_solution, [-2, 0, 2.375, 2 / 3], atol=1e-4)
-    primal = [float(line.split(":")[1]) for line in out.splitlines() if line.startswith("Primal objective")]
-    assert len(primal) == 1 and abs(primal[0] + 34.0) < 1e-4
+    assert [line.split()[0] for line in lines[4:]] == ["x0", "x1", "x2", "x3", "y0", "y1", "y2", "y3"]
 
 
 def test_enum_namespaces_behave_like_generated_modules():
