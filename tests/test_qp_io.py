@@ -301,3 +301,209 @@ def test_set_matrix_from_triplets_is_correct_for_a_tiny_matrix():
     K = pdlp_b200.set_matrix_from_triplets([t[0] for t in triplets], [t[1] for t in triplets], [t[2] for t in triplets], (2, 2))
     np.testing.assert_array_equal(K.toarray(), [[2, 0], [-1, 1]])
     assert K.has_sorted_indices and K.nnz == 3 and K.indptr.tolist() == [0, 2, 3]
+
+
+# ---- The reference's own MPS files (data re-typed; the expected values follow mps_reader_template.h:200-260 by hand) ----
+
+MAXIMIZATION_MPS = """\
+* Generated by MPModelProtoExporter
+*   Name             : SupportedMaximizationProblem
+*   Format           : Free
+*   Constraints      : 0
+*   Variables        : 1
+*     Binary         : 0
+*     Integer        : 0
+*     Continuous     : 1
+NAME          SupportedMaximizationProblem
+OBJSENSE
+  MAX
+ROWS
+ N  COST
+COLUMNS
+    X_ONE   COST         1
+BOUNDS
+ UP BOUND   X_ONE        4
+ENDATA
+"""  # ortools/linear_solver/testdata/maximization.mps (model_builder_test.py:167-173 reads it and checks the name)
+
+EXAMPLE_MPS = """\
+NAME          EXAMPLE
+ROWS
+ N  OBJ
+ G  ROW01
+ L  ROW02
+ E  ROW03
+ G  ROW04
+ L  ROW05
+COLUMNS
+    COL01     OBJ                1.0
+    COL01     ROW01              3.0   ROW05              5.6
+    COL02     ROW01              1.0   ROW02              2.0
+    COL03     ROW02              1.1   ROW03              1.0
+    COL04     ROW01             -2.0   ROW04              2.8
+    COL05     OBJ                2.0
+    COL05     ROW01             -1.0   ROW05              1.0
+    COL06     ROW03              1.0
+    COL07     ROW04             -1.2
+    COL08     OBJ               -1.0
+    COL08     ROW01             -1.0   ROW05              1.9
+RHS
+    RHS1      ROW01              2.5
+    RHS1      ROW02              2.1
+    RHS1      ROW03              4.0
+    RHS1      ROW04              1.8
+    RHS1      ROW05             15.0
+RANGES
+    RNG1      ROW04              3.2
+    RNG1      ROW05             12.0
+BOUNDS
+ LO BND1      COL01              2.5
+ UP BND1      COL02              4.1
+ LO BND1      COL05              0.5
+ UP BND1      COL05              4.0
+ UP BND1      COL08              4.3
+ENDATA
+"""  # examples/cpp/test2.mps: fixed format, RANGES on a G and an L row
+
+MIN_SIZE_MPS = """\
+NAME          MIN_SIZE_MAX_FEATURES
+
+ROWS
+ N  COST
+ E  ROW1
+ L  ROW2
+ G  ROW3
+ E  ROW4
+ E  ROW5
+ G  ROW6
+ E  ROW7
+ L  ROW8
+ N  UNCONST.
+
+COLUMNS
+    X1        ROW1              1      UNCONST.            1
+    X2        ROW1              1      UNCONST.            2
+    X1        COST              1
+    X2        COST              2
+    X1        ROW2              3
+    X2        ROW2              4
+    X1        ROW3              1
+    X2        ROW3              2
+    X3        ROW3              3      ROW7                1
+    X4        ROW3              4      ROW7                1
+    X5        ROW3              5      ROW4                2
+    X6        ROW3              6      ROW4                13
+    X7        ROW5              1      ROW6                7
+    X8        ROW5              3      ROW6                2
+    X7        ROW8              1
+    X8        ROW8              1
+
+
+RHS
+              ROW1              2
+              ROW2              6
+              ROW3              -85
+              ROW4              2
+              ROW5              8
+              ROW6              0
+              ROW7              50
+              ROW8              50
+
+BOUNDS
+ FR           X1
+ UP           X2                125.
+ FX           X3                12
+ MI           X4
+ LO           X5                5.
+ PL           X6
+
+RANGES
+    RANGE1    ROW2              20.
+              ROW3              25.
+              ROW4              12.
+              ROW7              -100.
+ENDATA
+
+"""  # examples/cpp/test.mps: fixed-format lines with empty name fields, a second N row, negative range on an E row
+
+
+def test_reference_maximization_mps():
+    qp = qp_io.parse_mps(MAXIMIZATION_MPS, include_names=True)
+    assert qp.problem_name == "SupportedMaximizationProblem"
+    assert qp.objective_scaling_factor == -1.0 and list(qp.objective_vector) == [-1.0]  # max x  ==  -(min -x)
+    assert qp.variable_names == ["X_ONE"] and list(qp.variable_lower_bounds) == [0.0] and list(qp.variable_upper_bounds) == [4.0]
+    assert qp.constraint_matrix.shape == (0, 1)
+
+
+def test_reference_example_mps():
+    qp = qp_io.parse_mps(EXAMPLE_MPS, include_names=True)
+    inf = np.inf
+    assert qp.problem_name == "EXAMPLE" and qp.objective_scaling_factor == 1.0 and qp.objective_offset == 0.0
+    assert qp.variable_names == ["COL0%d" % j for j in range(1, 9)] and qp.constraint_names == ["ROW0%d" % i for i in range(1, 6)]
+    np.testing.assert_array_equal(qp.objective_vector, [1, 0, 0, 0, 2, 0, 0, -1])
+    np.testing.assert_array_equal(qp.variable_lower_bounds, [2.5, 0, 0, 0, 0.5, 0, 0, 0])
+    np.testing.assert_array_equal(qp.variable_upper_bounds, [inf, 4.1, inf, inf, 4.0, inf, inf, 4.3])
+    # G row with range R: [rhs, rhs + |R|]; L row: [rhs - |R|, rhs]  (mps_reader_template.h:1061-1087)
+    np.testing.assert_array_equal(qp.constraint_lower_bounds, [2.5, -inf, 4.0, 1.8, 3.0])
+    np.testing.assert_array_equal(qp.constraint_upper_bounds, [inf, 2.1, 4.0, 5.0, 15.0])
+    np.testing.assert_array_equal(qp.constraint_matrix.toarray(), [
+        [3.0, 1.0, 0, -2.0, -1.0, 0, 0, -1.0],
+        [0, 2.0, 1.1, 0, 0, 0, 0, 0],
+        [0, 0, 1.0, 0, 0, 1.0, 0, 0],
+        [0, 0, 0, 2.8, 0, 0, -1.2, 0],
+        [5.6, 0, 0, 0, 1.0, 0, 0, 1.9]])
+
+
+def test_reference_min_size_mps_is_rejected_in_both_formats():
+    # Fixed format: the name is longer than its 8-column field and "-100." reaches column 37; free format: " FR X1" has
+    # two fields.  ParseString tries fixed, then free, and reports the second error (mps_reader_template.h:697-701).
+    with pytest.raises(qp_io.MpsParseError) as e:
+        qp_io.parse_mps(MIN_SIZE_MPS)
+    assert str(e.value) == 'Not enough fields in BOUNDS section. Line 45: " FR           X1".'
+
+
+def test_reference_min_size_mps_made_fixed_format():
+    """The same file with an 8-column name and the range written as -100: every line is fixed format, so the empty set
+    names (RHS, RANGES, BOUNDS) are empty fields and not missing ones."""
+    inf = np.inf
+    qp = qp_io.parse_mps(MIN_SIZE_MPS.replace("MIN_SIZE_MAX_FEATURES", "MINSIZE").replace("-100.", "-100"), include_names=True)
+    assert qp.problem_name == "MINSIZE"
+    assert qp.constraint_names == ["ROW%d" % i for i in range(1, 9)] + ["UNCONST."]  # the second N row is a free constraint
+    np.testing.assert_array_equal(qp.objective_vector, [1, 2, 0, 0, 0, 0, 0, 0])
+    np.testing.assert_array_equal(qp.variable_lower_bounds, [-inf, 0, 12, -inf, 5, 0, 0, 0])  # FR, UP, FX, MI, LO, PL
+    np.testing.assert_array_equal(qp.variable_upper_bounds, [inf, 125, 12, inf, inf, inf, inf, inf])
+    # ranges: L 20 -> [6 - 20, 6]; G 25 -> [-85, -60]; E +12 -> [2, 14]; E -100 -> [-50, 50]
+    np.testing.assert_array_equal(qp.constraint_lower_bounds, [2, -14, -85, 2, 8, 0, -50, -inf, -inf])
+    np.testing.assert_array_equal(qp.constraint_upper_bounds, [2, 6, -60, 14, 8, inf, 50, 50, inf])
+    np.testing.assert_array_equal(qp.constraint_matrix.toarray(), [
+        [1, 1, 0, 0, 0, 0, 0, 0],
+        [3, 4, 0, 0, 0, 0, 0, 0],
+        [1, 2, 3, 4, 5, 6, 0, 0],
+        [0, 0, 0, 0, 2, 13, 0, 0],
+        [0, 0, 0, 0, 0, 0, 1, 3],
+        [0, 0, 0, 0, 0, 0, 7, 2],
+        [0, 0, 1, 1, 0, 0, 0, 0],
+        [0, 0, 0, 0, 0, 0, 1, 1],
+        [1, 2, 0, 0, 0, 0, 0, 0]])
+
+
+def test_reference_example_mps_solves_to_the_highs_optimum(backend):
+    """External validity on a file the reference ships: PDLP's objective on examples/cpp/test2.mps against HiGHS."""
+    from scipy.optimize import linprog
+
+    qp = qp_io.parse_mps(EXAMPLE_MPS)
+    K = qp.constraint_matrix.toarray()
+    lo, hi = np.asarray(qp.constraint_lower_bounds), np.asarray(qp.constraint_upper_bounds)
+    A = np.vstack([K[np.isfinite(hi)], -K[np.isfinite(lo)]])
+    b = np.concatenate([hi[np.isfinite(hi)], -lo[np.isfinite(lo)]])
+    bounds = [(l if np.isfinite(l) else None, u if np.isfinite(u) else None) for l, u in zip(qp.variable_lower_bounds, qp.variable_upper_bounds)]
+    highs = linprog(np.asarray(qp.objective_vector), A_ub=A, b_ub=b, bounds=bounds, method="highs")
+    assert highs.status == 0
+    p = pdlp_b200.PrimalDualHybridGradientParams()
+    p.termination_criteria.simple_optimality_criteria.eps_optimal_absolute = 1e-8
+    p.termination_criteria.simple_optimality_criteria.eps_optimal_relative = 1e-8
+    p.termination_criteria.iteration_limit = 50000
+    out = backend.solve(qp, p)
+    assert out.solve_log.termination_reason == pdlp_b200.TerminationReason.TERMINATION_REASON_OPTIMAL
+    objective = float(np.dot(qp.objective_vector, out.primal_solution)) + qp.objective_offset
+    assert abs(objective - highs.fun) <= 1e-6 * max(1.0, abs(highs.fun)), (objective, highs.fun)
