@@ -507,3 +507,34 @@ def test_reference_example_mps_solves_to_the_highs_optimum(backend):
     assert out.solve_log.termination_reason == pdlp_b200.TerminationReason.TERMINATION_REASON_OPTIMAL
     objective = float(np.dot(qp.objective_vector, out.primal_solution)) + qp.objective_offset
     assert abs(objective - highs.fun) <= 1e-6 * max(1.0, abs(highs.fun)), (objective, highs.fun)
+
+
+SOLOMON = "/root/reference/ortools/routing/testdata/solomon_bp_c101.mps"
+
+
+@pytest.mark.skipif(not os.path.exists(SOLOMON), reason="the reference tree is only present in the build container")
+def test_a_real_model_of_the_reference_tree_read_and_solved_on_the_oracle():
+    """External validity beyond synthetic inputs: the LP relaxation of the 151 x 2550 set-partitioning
+    model under ortools/routing/testdata (free-format MPS with integrality markers, which the reader drops), PDLP
+    objective against HiGHS.  CPU only: the file is not copied into this repository."""
+    import backends
+    import scipy.sparse as sp
+    from scipy.optimize import linprog
+
+    qp = qp_io.read_quadratic_program_or_die(SOLOMON)
+    K = qp.constraint_matrix.tocsr()
+    assert K.shape == (151, 2550) and K.nnz == 7600
+    lo, hi = np.asarray(qp.constraint_lower_bounds), np.asarray(qp.constraint_upper_bounds)
+    eq = lo == hi
+    ub, lb = np.isfinite(hi) & ~eq, np.isfinite(lo) & ~eq
+    highs = linprog(np.asarray(qp.objective_vector), A_ub=sp.vstack([K[ub], -K[lb]]), b_ub=np.concatenate([hi[ub], -lo[lb]]), A_eq=K[eq], b_eq=lo[eq],
+                    bounds=list(zip(qp.variable_lower_bounds, qp.variable_upper_bounds)), method="highs")
+    assert highs.status == 0
+    p = pdlp_b200.PrimalDualHybridGradientParams()
+    p.termination_criteria.simple_optimality_criteria.eps_optimal_absolute = 1e-6
+    p.termination_criteria.simple_optimality_criteria.eps_optimal_relative = 1e-6
+    p.termination_criteria.iteration_limit = 200000
+    out = backends.make("oracle").solve(qp, p)
+    assert out.solve_log.termination_reason == pdlp_b200.TerminationReason.TERMINATION_REASON_OPTIMAL
+    objective = float(np.dot(qp.objective_vector, out.primal_solution)) + qp.objective_offset
+    assert abs(objective - highs.fun) <= 1e-5 * max(1.0, abs(highs.fun)), (objective, highs.fun)
