@@ -777,3 +777,35 @@ def test_rowstream_shared_memory_protocol_is_race_free():
         pytest.skip("ThreadSanitizer cannot run here: " + text.strip().splitlines()[0])
     assert "ThreadSanitizer" not in text, text[:4000]
     assert run.returncode == 0 and "wrong rows: 0" in text, text[:2000]
+
+
+@pytest.mark.parametrize("shape", ["no_rows", "no_columns", "empty_rows_and_columns"])
+def test_adaptive_trial_steps_on_degenerate_shapes(step_libs, shape):
+    """A problem with variables and no constraint (model_builder_helper_test.py:104-126 solves one through PDLP), its
+    mirror, and a matrix whose only nonzero leaves whole rows and columns empty: the kernels must run over zero work
+    blocks / zero-length rows and the step rule must see nonlinearity 0 (limit = inf: accept, grow)."""
+    import scipy.sparse as sp
+    if shape == "no_rows":
+        K = sp.csr_matrix((0, 3))
+    elif shape == "no_columns":
+        K = sp.csr_matrix((2, 0))
+    else:
+        K = sp.csr_matrix(([2.0], ([1], [2])), shape=(4, 5))
+    m, n = K.shape
+    rng = np.random.default_rng(5)
+    c = rng.standard_normal(n)
+    vlb, vub = np.full(n, -1.0), np.full(n, 2.0)
+    # Rows that 0 = (K x)_i cannot satisfy keep y moving (a feasible row pulls y to 0 and the movement to 0 with it).
+    clb, cub = np.full(m, 0.5), np.full(m, 0.5)
+    x0, y0 = np.zeros(n), rng.standard_normal(m)
+    step, w, trials = 0.3, 1.5, 6
+    want = reference_adaptive_trials(K, c, None, vlb, vub, clb, cub, x0, y0, step, w, trials)
+    got = emulated_adaptive_trials(step_libs[0], K, c, None, vlb, vub, clb, cub, x0, y0, step, w, trials)
+    # want["rejected"] counts a rejected trial still pending at the end of the batch; the device adds those to
+    # num_rejected_steps at the next accepted step (pdlp_step_state.h: inner), so compare through the trial total.
+    assert got["active"] == 1 and got["total_trials"] == trials
+    assert (got["completed"], got["total_trials"] - got["completed"]) == (want["completed"], want["rejected"])
+    for key in ("x", "y", "avg_x", "avg_y"):
+        np.testing.assert_allclose(got[key], want[key], rtol=1e-12, atol=1e-13, err_msg=key)
+    for key in ("step", "movement", "nonlinearity", "weight_sum"):
+        np.testing.assert_allclose(got[key], want[key], rtol=1e-12, err_msg=key)

@@ -1,0 +1,48 @@
+"""Cases added after this round's GPU budget was spent: their oracle variants run in the CPU suite, their device
+variants have not yet run on a B200.  The file sorts after every validated test file (and before the allocation
+test, which must be last in its process) so that a surprise here cannot hide results that were green on the device."""
+import numpy as np
+import pytest
+
+import pdlp_b200
+from pdlp_b200 import mp_model as mpm
+
+TR = pdlp_b200.TerminationReason
+
+
+def _solver_for(backend):
+    import test_mp_model
+
+    return test_mp_model._solver_for(backend)
+
+
+def test_solve_with_pdlp_one_bounded_variable_no_constraints(backend):
+    """ortools/linear_solver/python/model_builder_helper_test.py:104-126: maximise x on [0, 1] through an MPModelRequest
+    with solver_type PDLP_LINEAR_PROGRAMMING; OPTIMAL with objective 1.  A problem with variables and no constraint."""
+    request = pdlp_b200.MPModelRequest()
+    variable = request.model.variable.add()
+    variable.lower_bound, variable.upper_bound, variable.objective_coefficient = 0.0, 1.0, 1.0
+    request.model.maximize = True
+    request.solver_type = mpm.PDLP_LINEAR_PROGRAMMING
+    response = pdlp_b200.pdlp_solve_proto(request, solver=_solver_for(backend))
+    assert response.status == mpm.MPSOLVER_OPTIMAL
+    assert response.objective_value == pytest.approx(1.0, abs=1e-7)
+    assert list(response.variable_value) == pytest.approx([1.0], abs=1e-7)
+    assert len(response.dual_value) == 0
+
+
+def test_constraints_without_variables(backend):
+    """The mirror case: rows and no column.  Feasible iff 0 lies in every row's bounds; the optimum is the offset."""
+    qp = pdlp_b200.QuadraticProgram()
+    qp.resize_and_initialize(0, 2)
+    qp.constraint_lower_bounds = [-1.0, -np.inf]
+    qp.constraint_upper_bounds = [1.0, 0.0]
+    qp.objective_offset = 3.0
+    p = pdlp_b200.PrimalDualHybridGradientParams()
+    p.termination_criteria.iteration_limit = 1000
+    out = backend.solve(qp, p)
+    assert out.solve_log.termination_reason == TR.TERMINATION_REASON_OPTIMAL
+    assert len(out.primal_solution) == 0 and len(out.dual_solution) == 2
+    for info in out.solve_log.solution_stats.convergence_information:
+        if info.candidate_type == out.solve_log.solution_type:
+            assert info.primal_objective == pytest.approx(3.0)
