@@ -504,4 +504,16 @@ double oracle_sigma_max(void* h, double rel_err, double fail_prob, int seed, int
   return r.singular_value;
 }
 
+// The same with the active subspaces of a primal and / or a dual point (either may be NULL).
+double oracle_sigma_max_at(void* h, const double* x, const double* y, double rel_err, double fail_prob, int seed, int* iterations) {
+  const ShardedQp& sq = *static_cast<OracleProblem*>(h)->sq;
+  std::mt19937 gen(seed);
+  Vec vx, vy;
+  if (x) vx.assign(x, x + sq.PrimalSize());
+  if (y) vy.assign(y, y + sq.DualSize());
+  const auto r = EstimateMaximumSingularValueOfConstraintMatrix(sq, x ? &vx : nullptr, y ? &vy : nullptr, rel_err, fail_prob, gen);
+  if (iterations) *iterations = r.num_iterations;
+  return r.singular_value;
+}
+
 }  // extern "C"

@@ -395,5 +395,34 @@ inline SingularValueAndIterations EstimateMaximumSingularValue(const ShardedQp& 
   return {std::sqrt(estimate), iters, desired_relative_error};
 }
 
+// ComputePrimalActiveSetIndicator / ComputeDualActiveSetIndicator (sharded_optimization_utils.cc:617-672): 1 where the
+// coordinate is not held by a bound (for y: the implicit sign bound of a one-sided or free row), else 0.
+inline Vec PrimalActiveSetIndicator(const ShardedQp& sq, const Vec& x) {
+  const Qp& qp = sq.qp();
+  Vec ind(sq.PrimalSize());
+  sq.PrimalSharder().ForEach([&](int, int64_t b, int64_t e) {
+    for (int64_t j = b; j < e; ++j) ind[j] = (x[j] == qp.vlb[j] || x[j] == qp.vub[j]) ? 0.0 : 1.0;
+  });
+  return ind;
+}
+inline Vec DualActiveSetIndicator(const ShardedQp& sq, const Vec& y) {
+  const Qp& qp = sq.qp();
+  Vec ind(sq.DualSize());
+  sq.DualSharder().ForEach([&](int, int64_t b, int64_t e) {
+    for (int64_t i = b; i < e; ++i) ind[i] = (y[i] == 0.0 && (std::isinf(qp.clb[i]) || std::isinf(qp.cub[i]))) ? 0.0 : 1.0;
+  });
+  return ind;
+}
+// EstimateMaximumSingularValueOfConstraintMatrix (sharded_optimization_utils.cc:676-699): the public form, on the
+// columns / rows that the given points leave free.
+inline SingularValueAndIterations EstimateMaximumSingularValueOfConstraintMatrix(const ShardedQp& sq, const Vec* primal_solution, const Vec* dual_solution,
+                                                                                double desired_relative_error, double failure_probability, std::mt19937& gen) {
+  Vec primal_indicator, dual_indicator;
+  if (primal_solution) primal_indicator = PrimalActiveSetIndicator(sq, *primal_solution);
+  if (dual_solution) dual_indicator = DualActiveSetIndicator(sq, *dual_solution);
+  return EstimateMaximumSingularValue(sq, primal_solution ? &primal_indicator : nullptr, dual_solution ? &dual_indicator : nullptr, desired_relative_error,
+                                      failure_probability, gen);
+}
+
 }  // namespace oracle
 #endif  // PDLP_ORACLE_QP_H_

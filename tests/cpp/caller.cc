@@ -80,14 +80,32 @@ int main(int argc, char** argv) {
     const pdlp::QuadraticProgram typed = TestLp();
     if (built.constraint_matrix.outer_index != typed.constraint_matrix.outer_index || built.constraint_matrix.inner_index != typed.constraint_matrix.inner_index ||
         built.constraint_matrix.values != typed.constraint_matrix.values || built.variable_lower_bounds.size() != 4) return 15;
-    // GetConvergenceInformation / GetInfeasibilityInformation / GetPointMetadata (iteration_stats.cc:567-597).
+    // GetConvergenceInformation / GetInfeasibilityInformation / GetPointMetadata, the "GetsCorrectEntry" cases of
+    // iteration_stats_test.cc:256-336: two entries (current = 1, average = 2), none for the iterate difference.
     pdlp::IterationStats stats;
-    stats.convergence_information.emplace_back();
-    stats.convergence_information.back().candidate_type = pdlp::POINT_TYPE_AVERAGE_ITERATE;
-    stats.convergence_information.back().primal_objective = 1.5;
-    if (pdlp::GetConvergenceInformation(stats, pdlp::POINT_TYPE_CURRENT_ITERATE).has_value()) return 16;
-    if (pdlp::GetConvergenceInformation(stats, pdlp::POINT_TYPE_AVERAGE_ITERATE)->primal_objective != 1.5) return 17;
-    if (pdlp::GetInfeasibilityInformation(stats, pdlp::POINT_TYPE_AVERAGE_ITERATE).has_value() || pdlp::GetPointMetadata(stats, pdlp::POINT_TYPE_AVERAGE_ITERATE).has_value()) return 18;
+    const int kinds[2] = {pdlp::POINT_TYPE_CURRENT_ITERATE, pdlp::POINT_TYPE_AVERAGE_ITERATE};
+    for (int k = 0; k < 2; ++k) {
+      stats.convergence_information.emplace_back();
+      stats.convergence_information.back().candidate_type = kinds[k];
+      stats.convergence_information.back().primal_objective = k + 1.0;
+      stats.infeasibility_information.emplace_back();
+      stats.infeasibility_information.back().candidate_type = kinds[k];
+      stats.infeasibility_information.back().primal_ray_linear_objective = k + 1.0;
+      stats.point_metadata.emplace_back();
+      stats.point_metadata.back().point_type = kinds[k];
+      stats.point_metadata.back().active_primal_variable_count = k + 1;
+    }
+    for (int k = 0; k < 2; ++k) {
+      const auto ci = pdlp::GetConvergenceInformation(stats, kinds[k]);
+      if (!ci.has_value() || ci->candidate_type != kinds[k] || ci->primal_objective != k + 1.0) return 16;
+      const auto ii = pdlp::GetInfeasibilityInformation(stats, kinds[k]);
+      if (!ii.has_value() || ii->candidate_type != kinds[k] || ii->primal_ray_linear_objective != k + 1.0) return 17;
+      const auto pm = pdlp::GetPointMetadata(stats, kinds[k]);
+      if (!pm.has_value() || pm->point_type != kinds[k] || pm->active_primal_variable_count != k + 1) return 18;
+    }
+    if (pdlp::GetConvergenceInformation(stats, pdlp::POINT_TYPE_ITERATE_DIFFERENCE).has_value() ||
+        pdlp::GetInfeasibilityInformation(stats, pdlp::POINT_TYPE_ITERATE_DIFFERENCE).has_value() ||
+        pdlp::GetPointMetadata(stats, pdlp::POINT_TYPE_ITERATE_DIFFERENCE).has_value()) return 20;
     if (std::strcmp(pdlp::TerminationReason_Name(pdlp::TERMINATION_REASON_OPTIMAL), "TERMINATION_REASON_OPTIMAL") != 0) return 19;
     std::printf("cpu ok: %s | %s\n", r1.solve_log.termination_string.get().c_str(), r2.solve_log.termination_string.get().c_str());
     return 0;

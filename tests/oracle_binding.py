@@ -22,6 +22,7 @@ def load():
         build()
     lib = ctypes.CDLL(ORACLE_LIB)
     lib.oracle_sigma_max.restype = ctypes.c_double
+    lib.oracle_sigma_max_at.restype = ctypes.c_double
     lib.oracle_blas1.restype = ctypes.c_double
     lib.oracle_problem_create.restype = ctypes.c_void_p
     return lib
@@ -278,6 +279,15 @@ class Problem:
     def sigma_max(self, rel_err=0.2, fail_prob=0.0005, seed=1):
         it = ctypes.c_int(0)
         v = self.lib.oracle_sigma_max(self.h, ctypes.c_double(rel_err), ctypes.c_double(fail_prob), int(seed), ctypes.byref(it))
+        return v, it.value
+
+    def sigma_max_at(self, x=None, y=None, rel_err=0.2, fail_prob=0.0005, seed=1):
+        """EstimateMaximumSingularValueOfConstraintMatrix on the subspaces that x and / or y leave active."""
+        it = ctypes.c_int(0)
+        x = None if x is None else _f(x)
+        y = None if y is None else _f(y)
+        v = self.lib.oracle_sigma_max_at(self.h, _p(x) if x is not None else None, _p(y) if y is not None else None, ctypes.c_double(rel_err),
+                                         ctypes.c_double(fail_prob), int(seed), ctypes.byref(it))
         return v, it.value
 
 

@@ -174,6 +174,24 @@ def test_sigma_max_diagonal():
     assert abs(v - 3.0) < 1e-4 and iters < 300
 
 
+@pytest.mark.parametrize("x, y, want", [
+    # x_1 at its bound (-2): the matrix loses column 1 (:529-541); y_1 = 0 on a one-sided row: it loses row 1 (:544-557).
+    ([0.0, -2.0, 0.0, 3.0], None, 4.73818),
+    (None, [1.0, 0.0, 1.0, 3.0], 4.64203),
+    ([0.0, -2.0, 0.0, 3.0], [1.0, 0.0, 1.0, 3.0], 4.60829),
+], ids=["active_primal_subspace", "active_dual_subspace", "both"])
+def test_sigma_max_on_active_subspaces(x, y, want):
+    v, iters = ob.Problem(fixtures.make_test_lp(), 2, 2).sigma_max_at(x, y, 0.01, 0.001, 1)
+    assert abs(v - want) < 0.01 and iters < 300
+    # and against the singular values of the projected matrix itself
+    K = fixtures.make_test_lp().constraint_matrix.toarray()
+    if x is not None:
+        K = K[:, [0, 2, 3]]
+    if y is not None:
+        K = K[[0, 2, 3], :]
+    assert abs(v - np.linalg.svd(K, compute_uv=False)[0]) < 0.01 * want
+
+
 # ---- sharded_quadratic_program_test.cc: the data transformations of ShardedQuadraticProgram ----
 
 def test_rescale_problem_basic():  # RescaleProblem.BasicTest, :91-123
