@@ -278,7 +278,7 @@ def test_localized_bounds_one_dim_qp_unit_weight(backend):
     assert abs(b["lower_bound"] - (-1.0 - 0.75)) < 1e-5
 
 
-# kMaxNorm variants (oracle only; the device path never needs them)
+# kMaxNorm variants (NormsBehaveDifferently, :756-805; on the device through pdlp_b200_localized_bounds_max_norm)
 def test_localized_bounds_max_norm(backend):
     p = backend.problem(fixtures.make_test_lp())
     b = p.localized_bounds([0, 0, 0, 3.0], np.zeros(4), 1.0, 0.1, max_norm=True)
