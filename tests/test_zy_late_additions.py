@@ -46,3 +46,38 @@ def test_constraints_without_variables(backend):
     for info in out.solve_log.solution_stats.convergence_information:
         if info.candidate_type == out.solve_log.solution_type:
             assert info.primal_objective == pytest.approx(3.0)
+
+
+# ---- primal_dual_hybrid_gradient_test.cc:1186-1273: with a presolver in the loop, nonzeros below 1e-50 are rejected ----
+
+def _test_lp_with_tiny(field, index, lower_index=None):
+    import fixtures
+
+    qp = fixtures.make_test_lp()
+    values = np.array(getattr(qp, field), dtype=float)
+    values[index] = 1.0e-60
+    setattr(qp, field, values)
+    if lower_index is not None:  # :1225-1235 keeps the bounds consistent: 0 <= x_1 <= 1e-60
+        lower = np.array(qp.variable_lower_bounds, dtype=float)
+        lower[lower_index] = 0.0
+        qp.variable_lower_bounds = lower
+    return qp
+
+
+TINY_VALUES = {
+    "constraint_lower_bound": lambda: _test_lp_with_tiny("constraint_lower_bounds", 2),
+    "variable_bound": lambda: _test_lp_with_tiny("variable_upper_bounds", 1, lower_index=1),
+    "objective_vector": lambda: _test_lp_with_tiny("objective_vector", 3),
+}
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", sorted(TINY_VALUES))
+def test_detects_excessively_small_values_with_presolve(case):
+    """Detects...WithPresolve: the same problems solve to OPTIMAL without a presolver
+    (test_excessively_small_values_ok_without_presolve); in the hand-off - the device path's form of use_glop - the
+    original problem's statistics are checked with the small-value rule on (CheckProblemStats, pdhg.cc:731-897)."""
+    qp = TINY_VALUES[case]()
+    identity = lambda x, y: (x, y)
+    out = pdlp_b200.primal_dual_hybrid_gradient_presolved(qp, TINY_VALUES[case](), identity, pdlp_b200.PrimalDualHybridGradientParams())
+    assert out.solve_log.termination_reason == TR.TERMINATION_REASON_INVALID_PROBLEM, out.solve_log.termination_string
