@@ -81,3 +81,43 @@ def test_detects_excessively_small_values_with_presolve(case):
     identity = lambda x, y: (x, y)
     out = pdlp_b200.primal_dual_hybrid_gradient_presolved(qp, TINY_VALUES[case](), identity, pdlp_b200.PrimalDualHybridGradientParams())
     assert out.solve_log.termination_reason == TR.TERMINATION_REASON_INVALID_PROBLEM, out.solve_log.termination_string
+
+
+# ---- the boundary is re-entrant (one solve owns its own pool; here: its own stream and workspace) ----
+
+@pytest.mark.gpu
+@pytest.mark.timeout(600)
+def test_concurrent_solves_from_two_threads_match_sequential_ones():
+    """Two host threads solve different LPs on the same GPU at the same time.  Every reduction in the kernels has a fixed
+    order, so each result must equal, bit for bit, the one the same problem gives when solved alone."""
+    import threading
+
+    import fixtures
+
+    p = pdlp_b200.PrimalDualHybridGradientParams()
+    p.termination_criteria.simple_optimality_criteria.eps_optimal_absolute = 1e-6
+    p.termination_criteria.simple_optimality_criteria.eps_optimal_relative = 1e-6
+    p.termination_criteria.iteration_limit = 50000
+    problems = [fixtures.random_lp(300, 600, 5, 11), fixtures.random_lp(500, 900, 4, 12)]
+    alone = [pdlp_b200.primal_dual_hybrid_gradient(q, p, device=0) for q in problems]
+    together = [None, None]
+    errors = []
+
+    def work(k):
+        try:
+            for _ in range(3):  # several solves per thread, so that set-up, loop and download phases interleave
+                together[k] = pdlp_b200.primal_dual_hybrid_gradient(problems[k], p, device=0)
+        except Exception as e:  # noqa: BLE001 - reported by the assertion below
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=work, args=(k,)) for k in range(2)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    for a, b in zip(alone, together):
+        assert a.solve_log.termination_reason == b.solve_log.termination_reason == TR.TERMINATION_REASON_OPTIMAL
+        assert a.solve_log.iteration_count == b.solve_log.iteration_count
+        np.testing.assert_array_equal(a.primal_solution, b.primal_solution)
+        np.testing.assert_array_equal(a.dual_solution, b.dual_solution)
