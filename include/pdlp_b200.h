@@ -204,7 +204,8 @@ pdlp_b200_status pdlp_b200_check_termination(const uint8_t* params, size_t param
 pdlp_b200_status pdlp_b200_format_iteration_stats(const uint8_t* params, size_t params_len, const uint8_t* stats, size_t stats_len, const double* bound_norms /*4*/,
                                                   int iteration_type, int preferred_candidate, char** header, char** line);
 
-/* Serialized PrimalDualHybridGradientParams holding every schema default. */
+/* Serialized PrimalDualHybridGradientParams with every field at its schema default: under proto2 presence rules that
+ * is the message with no field set, so *params_len is 0 (and *params a valid pointer to free). */
 pdlp_b200_status pdlp_b200_default_params(uint8_t** params, size_t* params_len);
 
 /* Line-oriented description of the two schemas (message / field / number / type /

@@ -191,3 +191,27 @@ def test_validate_dimensions_rejects_inconsistent_sizes(mutate):
     mutate(qp)
     with pytest.raises(ValueError, match="Inconsistent dimensions"):
         pdlp_b200.validate_quadratic_program_dimensions(qp)
+
+
+# ---- the header as plain C: what a cgo / JNI / FFI binding compiles against ----
+
+def build_c_caller():
+    import subprocess
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    libdir = os.path.join(root, "or-tools_b200", "lib")
+    out_dir = os.path.join(root, "tests", "_build")
+    os.makedirs(out_dir, exist_ok=True)
+    exe, src = os.path.join(out_dir, "c_caller"), os.path.join(root, "tests", "c", "caller.c")
+    deps = [src, os.path.join(root, "include", "pdlp_b200.h"), os.path.join(libdir, "libpdlp_b200.so")]
+    if not os.path.exists(exe) or os.path.getmtime(exe) < max(os.path.getmtime(d) for d in deps):
+        subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I" + os.path.join(root, "include"), src, "-L" + libdir, "-lpdlp_b200", "-lm",
+                        "-Wl,-rpath," + libdir, "-o", exe], check=True)
+    return exe
+
+
+def test_header_compiles_as_c99_and_host_entry_points_work_from_c():
+    import subprocess
+
+    run = subprocess.run([build_c_caller(), "cpu"], capture_output=True, text=True, timeout=120)
+    assert run.returncode == 0 and "cpu ok" in run.stdout, (run.returncode, run.stdout, run.stderr)

@@ -121,3 +121,14 @@ def test_concurrent_solves_from_two_threads_match_sequential_ones():
         assert a.solve_log.iteration_count == b.solve_log.iteration_count
         np.testing.assert_array_equal(a.primal_solution, b.primal_solution)
         np.testing.assert_array_equal(a.dual_solution, b.dual_solution)
+
+
+@pytest.mark.gpu
+def test_plain_c_caller_solves_test_lp():
+    """tests/c/caller.c (gcc -std=c99 against include/pdlp_b200.h): pdlp_b200_solve with NULL params, a callback and counters."""
+    import subprocess
+
+    import test_cabi
+
+    run = subprocess.run([test_cabi.build_c_caller(), "gpu"], capture_output=True, text=True, timeout=300)
+    assert run.returncode == 0 and "gpu ok" in run.stdout, (run.returncode, run.stdout, run.stderr)
