@@ -485,6 +485,15 @@ void oracle_localized_bounds(void* h, const double* x, const double* y, int norm
                                                                        nullptr, nullptr, use_diagonal_qp_solver != 0, tol);
   out[0] = b.lagrangian_value; out[1] = b.lower_bound; out[2] = b.upper_bound; out[3] = b.radius;
 }
+// The same with the caller's K x and K^T y (trust_region.h: primal_product / dual_product, used by the solver's restart test).
+void oracle_localized_bounds_cached(void* h, const double* x, const double* y, const double* kx, const double* kty, int norm, double primal_weight, double radius,
+                                    int use_diagonal_qp_solver, double tol, double* out) {
+  const ShardedQp& sq = *static_cast<OracleProblem*>(h)->sq;
+  const Vec vx(x, x + sq.PrimalSize()), vy(y, y + sq.DualSize()), vkx(kx, kx + sq.DualSize()), vkty(kty, kty + sq.PrimalSize());
+  const LocalizedLagrangianBounds b = ComputeLocalizedLagrangianBounds(sq, vx, vy, norm == 0 ? PrimalDualNorm::kMaxNorm : PrimalDualNorm::kEuclideanNorm, primal_weight, radius,
+                                                                       &vkx, &vkty, use_diagonal_qp_solver != 0, tol);
+  out[0] = b.lagrangian_value; out[1] = b.lower_bound; out[2] = b.upper_bound; out[3] = b.radius;
+}
 // Plain vector trust-region problem.  diag nullable (linear objective).  out2 = {step_size, objective_value}.
 void oracle_trust_region(int64_t n, const double* obj, const double* diag, const double* lb, const double* ub, const double* center, const double* w, double radius,
                          int num_shards, double tol, double* solution, double* out2) {

@@ -276,6 +276,14 @@ class Problem:
                                          ctypes.c_double(tol), _p(out))
         return dict(lagrangian_value=out[0], lower_bound=out[1], upper_bound=out[2], radius=out[3])
 
+    def localized_bounds_cached(self, x, y, kx, kty, primal_weight, radius, use_diagonal=False, tol=1e-8, max_norm=False):
+        """ComputeLocalizedLagrangianBounds with the caller's primal_product = K x and dual_product = K^T y."""
+        x, y, kx, kty = _f(x), _f(y), _f(kx), _f(kty)
+        out = np.zeros(4)
+        self.lib.oracle_localized_bounds_cached(self.h, _p(x), _p(y), _p(kx), _p(kty), 0 if max_norm else 1, ctypes.c_double(primal_weight), ctypes.c_double(radius),
+                                                int(use_diagonal), ctypes.c_double(tol), _p(out))
+        return dict(lagrangian_value=out[0], lower_bound=out[1], upper_bound=out[2], radius=out[3])
+
     def sigma_max(self, rel_err=0.2, fail_prob=0.0005, seed=1):
         it = ctypes.c_int(0)
         v = self.lib.oracle_sigma_max(self.h, ctypes.c_double(rel_err), ctypes.c_double(fail_prob), int(seed), ctypes.byref(it))

@@ -332,3 +332,21 @@ def test_two_random_projections_of_a_vector():
     # The primal point has norm 2; a projection onto a unit direction can only reduce it, and is 0 with probability 0.
     assert all(-2.0 <= v <= 2.0 and v != 0.0 for v in primal)
     assert all(v == 0.0 for v in dual)
+
+
+# ---- trust_region_test.cc:758-792: ComputeLocalizedLagrangianBounds with the caller's K x and K^T y ----
+
+@pytest.mark.parametrize("max_norm", [False, True], ids=["euclidean", "max"])
+@pytest.mark.parametrize("diag", [False, True], ids=["linear_time", "diagonal_qp"])
+def test_localized_bounds_accept_cached_products(max_norm, diag):
+    p = ob.Problem(fixtures.make_test_lp(), num_threads=2, num_shards=2)
+    x, y = [0.0, 0.0, 0.0, 3.0], np.zeros(4)  # x_3 has a lower bound of 2.5
+    primal2 = 0.5 * (1.0 + 64.0 + 1.0 + 0.25)
+    dual2 = 0.5 * (4.0 + 2.375 * 2.375 + 4.0 / 9.0)
+    radius = math.sqrt(max(primal2, dual2)) if max_norm else math.sqrt(primal2 + dual2)
+    b = p.localized_bounds_cached(x, y, [6.0, 0.0, 0.0, -3.0], np.zeros(4), 1.0, radius, use_diagonal=diag, tol=1e-6, max_norm=max_norm)
+    assert b["lagrangian_value"] == 3.0
+    assert b["lower_bound"] <= -20.0 <= b["upper_bound"]
+    # and the cached products change nothing when they are the true ones
+    same = p.localized_bounds(x, y, 0 if max_norm else 1, 1.0, radius, diag, 1e-6)
+    assert (b["lower_bound"], b["upper_bound"]) == (same["lower_bound"], same["upper_bound"])
