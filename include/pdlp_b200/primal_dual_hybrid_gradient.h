@@ -141,7 +141,7 @@ enum class IterationType {
   kNormal = 0,
   kPrimalFeasibility = 1,
   kDualFeasibility = 2,
-  kPresolveTermination = 3,  // never produced here: Glop presolve is outside the device path
+  kPresolveTermination = 3,  // only from the presolve hand-off (pdlp_b200_solve_presolved) when the caller's presolver solved the problem
   kNormalTermination = 4,
   kFeasibilityPolishingTermination = 5,
 };  // enumerator order = the reference's (primal_dual_hybrid_gradient.h:70-83)
