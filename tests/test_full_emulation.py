@@ -66,3 +66,23 @@ def test_python_surface_solves_through_the_host_driver(emulated_library):
     TinyLp / TestLp (hundreds of iterations of the device-resident loop), a warm start at the optimum, an iteration limit."""
     tail = run_device_tests(emulated_library, ["tests/test_python_surface.py"], 900)
     assert " passed" in tail and "failed" not in tail
+
+
+def test_c_and_cpp_callers_in_device_mode(emulated_library):
+    """tests/c/caller.c, tests/cpp/caller.cc and samples/config1_small_lp.cc linked against the emulated library and run
+    in the mode the GPU box runs them in (a TestLp solve through pdlp_b200_solve / PrimalDualHybridGradient)."""
+    out_dir = os.path.join(ROOT, "tests", "_build", "emu_callers")
+    os.makedirs(out_dir, exist_ok=True)
+    libdir, libname = os.path.dirname(emulated_library), os.path.basename(emulated_library)[3:-3]
+    link = ["-L" + libdir, "-l" + libname, "-Wl,-rpath," + libdir]
+    include = "-I" + os.path.join(ROOT, "include")
+    builds = [
+        ("c_caller", ["gcc", "-std=c99", include, os.path.join(ROOT, "tests", "c", "caller.c")] + link + ["-lm"], ["gpu"], "gpu ok"),
+        ("cpp_caller", ["g++", "-std=c++17", include, os.path.join(ROOT, "tests", "cpp", "caller.cc")] + link, ["gpu"], "gpu ok: OPTIMAL"),
+        ("config1_small_lp", ["g++", "-std=c++17", include, os.path.join(ROOT, "samples", "config1_small_lp.cc")] + link, [], "TERMINATION_REASON_OPTIMAL after "),
+    ]
+    for name, compile_cmd, args, expected in builds:
+        exe = os.path.join(out_dir, name)
+        subprocess.run(compile_cmd + ["-o", exe], check=True)
+        run = subprocess.run([exe] + args, capture_output=True, text=True, timeout=300)
+        assert run.returncode == 0 and expected in run.stdout, (name, run.returncode, run.stdout, run.stderr)
