@@ -28,13 +28,35 @@ def emulated_library():
     return build.build()
 
 
-def run_device_tests(library, selection, timeout):
-    env = dict(os.environ, PDLP_B200_LIBRARY=library)
-    cmd = [sys.executable, "-m", "pytest", "-q", "-m", "gpu", "-p", "no:cacheprovider", "--timeout", "120"] + selection
-    run = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=timeout)
-    tail = "\n".join(run.stdout.splitlines()[-25:])
-    assert run.returncode == 0, tail + "\n" + run.stderr[-2000:]
-    return tail
+# Groups of `-m gpu` tests run on the emulated library, each in its own child pytest, all at the same time (an emulated
+# solve is single-threaded).  Left out: problems of thousands of rows (minutes per solve at ~1 ms per emulated launch) and
+# the test that times a flag raised 0.25 s into a solve against the wall clock.
+GROUPS = {
+    "degenerate_shapes_and_presolve": ["tests/test_zy_late_additions.py", "tests/test_presolve.py", "-k", "not concurrent and not plain_c and not reports_on_the_original"],
+    "reference_behaviour": ["tests/test_reference_pdhg_behaviour.py", "tests/test_logging.py"],
+    "reference_units": ["tests/test_reference_units.py", "tests/test_gpu_trial_steps.py", "tests/test_gpu_forced_termination.py"],
+    "python_surface_and_boundary": ["tests/test_python_surface.py", "tests/test_qp_io.py", "tests/test_mp_model.py", "tests/test_cabi.py", "tests/test_solve_cli.py"],
+    "device_against_oracle": ["tests/test_gpu_solve.py", "-k", "not test_random_lp_parity"],
+}
+
+
+@pytest.fixture(scope="module")
+def device_runs(emulated_library):
+    env = dict(os.environ, PDLP_B200_LIBRARY=emulated_library)
+    children = {}
+    for name, selection in GROUPS.items():
+        cmd = [sys.executable, "-m", "pytest", "-q", "-m", "gpu", "-p", "no:cacheprovider", "--timeout", "300"] + selection
+        children[name] = subprocess.Popen(cmd, cwd=ROOT, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    results = {}
+    for name, child in children.items():
+        try:
+            out, _ = child.communicate(timeout=1500)
+        except subprocess.TimeoutExpired:
+            child.kill()
+            out, _ = child.communicate()
+            out += "\n(killed after 1500 s)"
+        results[name] = (child.returncode, "\n".join(out.splitlines()[-30:]))
+    return results
 
 
 def test_the_emulated_library_is_not_the_product(emulated_library):
@@ -45,27 +67,15 @@ def test_the_emulated_library_is_not_the_product(emulated_library):
     assert not os.path.exists(os.path.join(ROOT, "or-tools_b200", "lib", os.path.basename(emulated_library)))
 
 
-def test_degenerate_shapes_and_presolve_rules_through_the_host_driver(emulated_library):
-    """Problems without rows / without columns, the with-presolve small-value checks, a presolver that solves everything,
-    the presolve goldens: device tests that were written after the last run on a B200."""
-    tail = run_device_tests(emulated_library, ["tests/test_zy_late_additions.py", "tests/test_presolve.py",
-                                               "-k", "not concurrent and not plain_c and not reports_on_the_original"], 600)
-    assert " passed" in tail and "failed" not in tail
-
-
-def test_reference_behaviour_and_unit_tests_through_the_host_driver(emulated_library):
-    """The reference's behavioural tests (restart bookkeeping, check cadence, callbacks, warm starts, interrupts, every
-    Detects* case, feasibility polishing, all three step rules) and its unit goldens (statistics, rescaling, KKT passes,
-    reduced costs, localized bounds) in their [device] variants: about 100 solves of the reference's small fixtures."""
-    tail = run_device_tests(emulated_library, ["tests/test_reference_pdhg_behaviour.py", "tests/test_reference_units.py", "tests/test_logging.py"], 1200)
-    assert " passed" in tail and "failed" not in tail
-
-
-def test_python_surface_solves_through_the_host_driver(emulated_library):
-    """The reference's Python tests (pdlp_test.py) and the config-1 sample on the emulated device: tight-tolerance solves of
-    TinyLp / TestLp (hundreds of iterations of the device-resident loop), a warm start at the optimum, an iteration limit."""
-    tail = run_device_tests(emulated_library, ["tests/test_python_surface.py"], 900)
-    assert " passed" in tail and "failed" not in tail
+@pytest.mark.parametrize("group", sorted(GROUPS))
+def test_device_tests_through_the_emulated_host_driver(device_runs, group):
+    """degenerate_shapes_and_presolve: problems without rows / columns, the with-presolve small-value checks, a presolver
+    that solves everything - written after the last run on a B200.  reference_behaviour / reference_units: the reference's
+    behavioural tests (restarts, cadence, callbacks, warm starts, interrupts, Detects*, polishing, three step rules) and unit
+    goldens in their [device] variants.  python_surface_and_boundary: pdlp_test.py, the sample, file readers, MPModelProto
+    requests, the C ABI, the command line.  device_against_oracle: iteration traces and objectives against the oracle."""
+    code, tail = device_runs[group]
+    assert code == 0 and " passed" in tail and " failed" not in tail, tail
 
 
 def test_c_and_cpp_callers_in_device_mode(emulated_library):
