@@ -22,10 +22,12 @@
 namespace pdlp_b200 {
 
 #ifdef PDLP_EMULATE
-inline void PeerFenceSystem() {}
-inline unsigned long long PeerLoadFlag(const unsigned long long* p) { return *reinterpret_cast<const volatile unsigned long long*>(p); }
-inline void PeerStoreFlag(unsigned long long* p, unsigned long long v) { *reinterpret_cast<volatile unsigned long long*>(p) = v; }
-inline double PeerLoadSlot(const double* p) { return *p; }
+// Host stand-ins (tests only): ranks may be host threads of one process (tests/emu_lib), so the flags keep their
+// release / acquire meaning.
+inline void PeerFenceSystem() { __atomic_thread_fence(__ATOMIC_SEQ_CST); }
+inline unsigned long long PeerLoadFlag(const unsigned long long* p) { return __atomic_load_n(p, __ATOMIC_ACQUIRE); }
+inline void PeerStoreFlag(unsigned long long* p, unsigned long long v) { __atomic_store_n(p, v, __ATOMIC_RELEASE); }
+inline double PeerLoadSlot(const double* p) { return *reinterpret_cast<const volatile double*>(p); }
 #else
 __device__ __forceinline__ void PeerFenceSystem() { __threadfence_system(); }
 __device__ __forceinline__ unsigned long long PeerLoadFlag(const unsigned long long* p) {

@@ -11,6 +11,7 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 CSRC = os.path.join(ROOT, "or-tools_b200", "csrc")
 OUT = os.path.join(ROOT, "tests", "_build", "emu_lib")
 LIB = os.path.join(ROOT, "tests", "_build", "libpdlp_b200_emu.so")
+FAKE_NCCL = os.path.join(ROOT, "tests", "_build", "libfake_nccl.so")
 
 sys.path.insert(0, HERE)
 import rewrite_launches  # noqa: E402
@@ -30,6 +31,15 @@ def stale():
     for base in (os.path.join(ROOT, "include"), os.path.join(ROOT, "include", "pdlp_b200")):
         deps += [os.path.join(base, n) for n in os.listdir(base) if n.endswith(".h")]
     return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build_fake_nccl():
+    """NCCL for ranks that are host threads of one process (fake_nccl.cc); named through PDLP_B200_NCCL_LIBRARY."""
+    src = os.path.join(HERE, "fake_nccl.cc")
+    if not os.path.exists(FAKE_NCCL) or os.path.getmtime(FAKE_NCCL) < os.path.getmtime(src):
+        os.makedirs(os.path.dirname(FAKE_NCCL), exist_ok=True)
+        subprocess.run(["g++", "-std=c++20", "-O1", "-g", "-fPIC", "-shared", "-pthread", src, "-o", FAKE_NCCL], check=True)
+    return FAKE_NCCL
 
 
 def build(verbose=False):
@@ -69,3 +79,4 @@ def build(verbose=False):
 
 if __name__ == "__main__":
     print(build(verbose=True))
+    print(build_fake_nccl())

@@ -5,7 +5,7 @@
 // runs device tests against it.  It is never built by __graft_entry__.build(), never installed under or-tools_b200/lib
 // and never loaded by the package on its own: the product has no CPU path.
 //
-// Model: one device; every stream is synchronous (work runs at the call); "device" memory is host memory; events are
+// Model: eight identical devices in name (a rank of a sharded solve is a host thread); every stream is synchronous (work runs at the call); "device" memory is host memory; events are
 // time stamps.  What this checks is the host driver's logic (launch order, sizes, state hand-over, degenerate
 // shapes) together with the kernels' index logic - not timing, not the hardware memory model, not asynchrony.
 #ifndef PDLP_TESTS_EMU_CUDA_RUNTIME_H_
@@ -34,9 +34,11 @@ struct cudaIpcMemHandle_t { char reserved[64]; };
 
 inline const char* cudaGetErrorString(cudaError_t e) { return e == cudaSuccess ? "no error" : "emulated CUDA runtime: unsupported call or allocation failure"; }
 inline cudaError_t cudaGetLastError() { return cudaSuccess; }
-inline cudaError_t cudaGetDeviceCount(int* n) { *n = 1; return cudaSuccess; }
-inline cudaError_t cudaSetDevice(int d) { return d == 0 ? cudaSuccess : cudaErrorInvalidValue; }
-inline cudaError_t cudaGetDevice(int* d) { *d = 0; return cudaSuccess; }
+// Eight "devices" that differ in name only: a rank of an emulated sharded solve is a host thread of this process.
+inline thread_local int emu_current_device = 0;
+inline cudaError_t cudaGetDeviceCount(int* n) { *n = 8; return cudaSuccess; }
+inline cudaError_t cudaSetDevice(int d) { if (d < 0 || d >= 8) return cudaErrorInvalidValue; emu_current_device = d; return cudaSuccess; }
+inline cudaError_t cudaGetDevice(int* d) { *d = emu_current_device; return cudaSuccess; }
 inline cudaError_t cudaDeviceSynchronize() { return cudaSuccess; }
 inline cudaError_t cudaDeviceGetAttribute(int* v, cudaDeviceAttr, int) { *v = 2; return cudaSuccess; }  // two "SMs": small grids
 template <class K>
@@ -76,9 +78,9 @@ inline cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t a, cudaEvent_t b)
   return cudaSuccess;
 }
 
-// Peer memory needs a second process with a device of its own: not modelled.
-inline cudaError_t cudaIpcGetMemHandle(cudaIpcMemHandle_t*, void*) { return cudaErrorNotSupported; }
-inline cudaError_t cudaIpcOpenMemHandle(void**, cudaIpcMemHandle_t, unsigned) { return cudaErrorNotSupported; }
-inline cudaError_t cudaIpcCloseMemHandle(void*) { return cudaErrorNotSupported; }
+// Peer memory: the ranks are host threads of one process, so a handle is the pointer itself.
+inline cudaError_t cudaIpcGetMemHandle(cudaIpcMemHandle_t* h, void* p) { std::memset(h, 0, sizeof *h); std::memcpy(h->reserved, &p, sizeof p); h->reserved[63] = 1; return cudaSuccess; }
+inline cudaError_t cudaIpcOpenMemHandle(void** p, cudaIpcMemHandle_t h, unsigned) { std::memcpy(p, h.reserved, sizeof *p); return cudaSuccess; }
+inline cudaError_t cudaIpcCloseMemHandle(void*) { return cudaSuccess; }
 
 #endif  // PDLP_TESTS_EMU_CUDA_RUNTIME_H_

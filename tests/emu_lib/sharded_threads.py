@@ -1,0 +1,79 @@
+"""TEST INFRASTRUCTURE ONLY.  Run by tests/test_full_emulation.py in a child process with PDLP_B200_LIBRARY = the emulated
+library and PDLP_B200_NCCL_LIBRARY = the fake NCCL: a column-sharded solve whose ranks are host threads of this process
+(the emulated peer memory is plain memory, tests/emu_lib/include/cuda_runtime.h), checked against the one-rank solve of
+the same library.      python sharded_threads.py <world> <peer|nccl>      prints one JSON line."""
+import json
+import os
+import sys
+import threading
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import fixtures  # noqa: E402
+import pdlp_b200  # noqa: E402
+from pdlp_b200 import sharding  # noqa: E402
+import scipy.sparse as sp  # noqa: E402
+
+
+def solve_sharded(qp, params, world):
+    K = sp.csc_matrix(qp.constraint_matrix)
+    starts = sharding.column_partition(K.indptr, world)
+    sharing = sharding.RowSharing.from_matrix(K, starts)
+    uid = sharding.unique_id()
+    results, errors = [None] * world, []
+
+    def rank_main(rank):
+        try:
+            lo, hi = int(starts[rank]), int(starts[rank + 1])
+            block = sharding.take_columns(qp, lo, hi, sharing.local_rows(rank))
+            shard = sharding.ColumnShard(rank, world, int(starts[-1]), lo, uid, int(sharing.shared.size))
+            r = pdlp_b200.primal_dual_hybrid_gradient(block, params, device=rank, shard=shard)
+            results[rank] = (r, pdlp_b200.last_solve_counters())
+        except Exception as e:  # noqa: BLE001
+            errors.append(f"rank {rank}: {e!r}")
+
+    threads = [threading.Thread(target=rank_main, args=(r,)) for r in range(world)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    if errors:
+        raise RuntimeError("; ".join(errors))
+    x = np.concatenate([r[0].primal_solution for r in results])
+    y = sharing.gather([r[0].dual_solution for r in results])
+    return results, x, y, sharing
+
+
+def main():
+    world, mode = int(sys.argv[1]), sys.argv[2]
+    if mode == "nccl":
+        os.environ["PDLP_B200_PEER_EXCHANGE"] = "0"
+    qp = fixtures.random_lp(40, 100, 4, 21)  # 448 iterations on the oracle
+    params = pdlp_b200.PrimalDualHybridGradientParams()
+    params.termination_criteria.simple_optimality_criteria.eps_optimal_absolute = 1e-6
+    params.termination_criteria.simple_optimality_criteria.eps_optimal_relative = 1e-6
+    params.termination_criteria.iteration_limit = 20000
+    single = pdlp_b200.primal_dual_hybrid_gradient(qp, params, device=0)
+    results, x, y, sharing = solve_sharded(qp, params, world)
+    logs = [r[0].solve_log for r in results]
+    c = np.asarray(qp.objective_vector)
+    out = {
+        "world": world, "mode": mode,
+        "single_reason": int(single.solve_log.termination_reason), "single_iterations": int(single.solve_log.iteration_count),
+        "reasons": [int(l.termination_reason) for l in logs], "iterations": [int(l.iteration_count) for l in logs],
+        "objective_single": float(c @ single.primal_solution), "objective_sharded": float(c @ x),
+        "x_distance": float(np.linalg.norm(x - single.primal_solution) / max(1.0, np.linalg.norm(single.primal_solution))),
+        "y_distance": float(np.linalg.norm(y - single.dual_solution) / max(1.0, np.linalg.norm(single.dual_solution))),
+        "peer_exchanges": [int(r[1]["peer_exchanges"]) for r in results], "collectives": [int(r[1]["collectives"]) for r in results],
+        "shared_rows": int(sharing.shared.size), "rows": int(qp.constraint_matrix.shape[0]),
+        "duals_identical_on_shared_rows": bool(all(np.array_equal(results[0][0].dual_solution[:sharing.shared.size], r[0].dual_solution[:sharing.shared.size]) for r in results)),
+    }
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

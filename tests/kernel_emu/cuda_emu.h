@@ -33,7 +33,11 @@
 #define __host__
 #define __forceinline__ inline
 #define __launch_bounds__(...)
+#ifdef PDLP_EMU_FIBERS
+#define __shared__ static thread_local  // the contexts of a CTA share one host thread; ranks are host threads
+#else
 #define __shared__ static
+#endif
 
 namespace cuda_emu {
 
@@ -49,7 +53,11 @@ struct Cta {
 };
 
 inline thread_local Dim thread_idx, block_idx, grid_dim, block_dim;
+#ifdef PDLP_EMU_FIBERS
+inline thread_local Cta* current_cta = nullptr;
+#else
 inline Cta* current_cta = nullptr;
+#endif
 inline bool defer_async = false;  // cp.async lands at wait_group instead of at issue
 inline int fdividef_ulps = 0;     // error injected into __fdividef (the intrinsic is good to 2 ulp)
 
@@ -137,8 +145,7 @@ struct FiberScheduler {
   unsigned current = 0;
   const std::function<void()>* body = nullptr;
 };
-inline thread_local FiberScheduler fiber_scheduler;
-inline std::mutex launch_mutex;  // `__shared__` arrays are function statics: one CTA at a time in the process
+inline thread_local FiberScheduler fiber_scheduler;  // host threads launch independently: `__shared__` is thread_local in this mode
 
 inline void FiberYield(FiberState state) {
   FiberScheduler& s = fiber_scheduler;
@@ -154,7 +161,6 @@ inline void FiberEntry() {
 
 template <class F>
 void Launch(unsigned grid, unsigned block, F body) {
-  std::lock_guard<std::mutex> one_cta_at_a_time(launch_mutex);
   FiberScheduler& s = fiber_scheduler;
   if (s.fibers.size() < block) s.fibers.resize(block);
   while (s.stacks.size() < block) s.stacks.push_back(std::make_unique<char[]>(FiberScheduler::kStackBytes));

@@ -96,3 +96,61 @@ def test_c_and_cpp_callers_in_device_mode(emulated_library):
         subprocess.run(compile_cmd + ["-o", exe], check=True)
         run = subprocess.run([exe] + args, capture_output=True, text=True, timeout=300)
         assert run.returncode == 0 and expected in run.stdout, (name, run.returncode, run.stdout, run.stderr)
+
+
+# ---- the column-sharded solve with ranks as host threads (peer-memory path at 2, 4 and 8 ranks; NCCL path at 2) ----
+
+SHARDED = [(2, "peer"), (4, "peer"), (8, "peer"), (2, "nccl")]
+
+
+@pytest.fixture(scope="module")
+def sharded_runs(emulated_library):
+    import json
+
+    import build  # tests/emu_lib/build.py
+
+    env = dict(os.environ, PDLP_B200_LIBRARY=emulated_library, PDLP_B200_NCCL_LIBRARY=build.build_fake_nccl())
+    script = os.path.join(ROOT, "tests", "emu_lib", "sharded_threads.py")
+    children = {cfg: subprocess.Popen([sys.executable, script, str(cfg[0]), cfg[1]], cwd=ROOT, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+                for cfg in SHARDED}
+    results = {}
+    for cfg, child in children.items():
+        try:
+            out, err = child.communicate(timeout=900)
+        except subprocess.TimeoutExpired:  # a rank waiting for a flag that never comes: the hang a real run would show
+            child.kill()
+            out, err = child.communicate()
+            err += "\n(killed after 900 s)"
+        lines = [line for line in out.splitlines() if line.startswith("{")]
+        results[cfg] = (child.returncode, json.loads(lines[-1]) if lines else None, err[-3000:])
+    return results
+
+
+@pytest.mark.parametrize("world, mode", SHARDED)
+def test_sharded_solve_with_ranks_as_host_threads(sharded_runs, world, mode):
+    """The shipped exchange paths through the whole host driver: communicator and peer-region set-up (IPC handles through an
+    all-reduce, the agreement on failure), the fused peer pass with its CTA split and in-kernel signal, the finishing kernel,
+    the scalar exchange inside the step-decision kernel, host events with their collectives, the gather of the result.  Peer
+    memory is plain memory here and NCCL a thread rendezvous (tests/emu_lib/fake_nccl.cc), so this says nothing about NVLink
+    ordering - the 2-GPU tests on the B200 box do - but every rank must finish, agree, and match the one-rank solve."""
+    code, got, err = sharded_runs[(world, mode)]
+    assert code == 0 and got is not None, err
+    optimal = int(__import__("pdlp_b200").TerminationReason.TERMINATION_REASON_OPTIMAL)
+    assert got["single_reason"] == optimal and got["reasons"] == [optimal] * world
+    assert len(set(got["iterations"])) == 1  # the ranks stop at the same iteration
+    assert 0.5 <= got["iterations"][0] / got["single_iterations"] <= 2.0, got
+    assert abs(got["objective_sharded"] - got["objective_single"]) <= 1e-5 * abs(got["objective_single"]), got  # both 1e-6 optimal
+    assert got["x_distance"] < 1e-2 and got["y_distance"] < 1e-3 and got["duals_identical_on_shared_rows"]
+    assert len(set(got["collectives"])) == 1 and got["collectives"][0] > got["iterations"][0]  # at least one exchange per trial step
+    if mode == "peer":
+        assert len(set(got["peer_exchanges"])) == 1 and got["peer_exchanges"][0] > got["iterations"][0], got
+    else:
+        assert got["peer_exchanges"] == [0] * world
+
+
+def test_peer_and_nccl_exchange_give_the_same_bits(sharded_runs):
+    """Both paths add the ranks' row sums in rank order: the solves must agree to the last bit."""
+    peer, nccl = sharded_runs[(2, "peer")][1], sharded_runs[(2, "nccl")][1]
+    assert peer is not None and nccl is not None
+    assert peer["iterations"] == nccl["iterations"] and peer["objective_sharded"] == nccl["objective_sharded"]
+    assert peer["x_distance"] == nccl["x_distance"] and peer["y_distance"] == nccl["y_distance"]
