@@ -1,6 +1,7 @@
 // Minimal host stand-in for the CUDA constructs pdlp_skeletons.cuh uses, so that the kernel
 // skeletons compile as plain C++ (g++ -std=c++20 -DPDLP_EMULATE) and run on CPU: one CTA at a time,
-// one host thread per CUDA thread, __syncthreads and warp shuffles as barriers.  Test
+// one context per CUDA thread (a host thread each, or with PDLP_EMU_FIBERS user-level contexts switched at barriers by
+// the launching thread - what the tests use, except the ThreadSanitizer check), __syncthreads and warp shuffles as barriers.  Test
 // infrastructure only (tests/test_kernel_emulation.py); it checks index logic and synchronisation
 // placement, not performance and not the hardware's memory model.
 //

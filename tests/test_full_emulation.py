@@ -37,6 +37,10 @@ GROUPS = {
     "reference_units": ["tests/test_reference_units.py", "tests/test_gpu_trial_steps.py", "tests/test_gpu_forced_termination.py"],
     "python_surface_and_boundary": ["tests/test_python_surface.py", "tests/test_qp_io.py", "tests/test_mp_model.py", "tests/test_cabi.py", "tests/test_solve_cli.py"],
     "device_against_oracle": ["tests/test_gpu_solve.py", "-k", "not test_random_lp_parity"],
+    # Two of the reference's sixteen parameter combinations over its 12 LP and 4 QP tests (all 320 [device] cases pass on
+    # the emulated library - 12 minutes in one process - with `pytest tests/test_reference_pdhg.py -m gpu` under the same
+    # PDLP_B200_LIBRARY).
+    "reference_parameter_combinations": ["tests/test_reference_pdhg.py", "-k", "device-Scaling_1T_IterLimit_Adaptive or device-NoScaling_4T_NoIterLimit_Adaptive"],
 }
 
 
@@ -73,7 +77,8 @@ def test_device_tests_through_the_emulated_host_driver(device_runs, group):
     that solves everything - written after the last run on a B200.  reference_behaviour / reference_units: the reference's
     behavioural tests (restarts, cadence, callbacks, warm starts, interrupts, Detects*, polishing, three step rules) and unit
     goldens in their [device] variants.  python_surface_and_boundary: pdlp_test.py, the sample, file readers, MPModelProto
-    requests, the C ABI, the command line.  device_against_oracle: iteration traces and objectives against the oracle."""
+    requests, the C ABI, the command line.  device_against_oracle: iteration traces and objectives against the oracle.
+    reference_parameter_combinations: the reference's LP / QP solve tests under two of the adaptive-rule combinations (the Malitsky-Pock ones take minutes here; that rule runs in device_against_oracle)."""
     code, tail = device_runs[group]
     assert code == 0 and " passed" in tail and " failed" not in tail, tail
 

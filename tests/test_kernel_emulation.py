@@ -27,7 +27,7 @@ def _build():
     out = os.path.join(BUILD, "rowstream_emu.so")
     sources = [os.path.join(EMU, "rowstream_emu.cc"), os.path.join(EMU, "cuda_emu.h"), os.path.join(CSRC, "pdlp_skeletons.cuh")]
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(s) for s in sources):
-        subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-Wno-attributes",
+        subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-DPDLP_EMU_FIBERS", "-Wno-unknown-pragmas", "-Wno-attributes",
                         "-I" + EMU, "-I" + CSRC, sources[0], "-o", out], check=True)
     return ctypes.CDLL(out)
 
@@ -136,7 +136,7 @@ def _build_step():
                os.path.join(CSRC, "pdlp_step_kernels.cuh"), os.path.join(CSRC, "pdlp_step_state.h"), os.path.join(CSRC, "pdlp_peer.cuh"), os.path.join(CSRC, "pdlp_peer_view.h")]
     os.makedirs(BUILD, exist_ok=True)
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(s) for s in sources):
-        subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-Wno-attributes",
+        subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-DPDLP_EMU_FIBERS", "-Wno-unknown-pragmas", "-Wno-attributes",
                         "-I" + EMU, "-I" + CSRC, sources[0], "-o", out], check=True)
     return ctypes.CDLL(out)
 
@@ -519,7 +519,7 @@ def _build_kkt():
     sources = [os.path.join(EMU, "kkt_emu.cc"), os.path.join(EMU, "cuda_emu.h"), os.path.join(CSRC, "pdlp_skeletons.cuh"), os.path.join(CSRC, "pdlp_kkt_kernels.cuh")]
     os.makedirs(BUILD, exist_ok=True)
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(s) for s in sources):
-        subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-Wno-attributes", "-I" + EMU, "-I" + CSRC,
+        subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-DPDLP_EMU_FIBERS", "-Wno-unknown-pragmas", "-Wno-attributes", "-I" + EMU, "-I" + CSRC,
                         sources[0], "-o", out], check=True)
     return ctypes.CDLL(out)
 
@@ -624,7 +624,7 @@ def _build_restart():
                os.path.join(CSRC, "pdlp_restart_kernels.cuh"), os.path.join(CSRC, "pdlp_restart_types.h")]
     os.makedirs(BUILD, exist_ok=True)
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(s) for s in sources):
-        subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-Wno-attributes", "-I" + EMU, "-I" + CSRC,
+        subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-DPDLP_EMU_FIBERS", "-Wno-unknown-pragmas", "-Wno-attributes", "-I" + EMU, "-I" + CSRC,
                         sources[0], "-o", out], check=True)
     return ctypes.CDLL(out)
 
@@ -732,7 +732,7 @@ def test_rescaling_matches_the_oracle(qp_case, ruiz, l2):
     sources = [os.path.join(EMU, "setup_emu.cc"), os.path.join(EMU, "cuda_emu.h"), os.path.join(CSRC, "pdlp_skeletons.cuh"), os.path.join(CSRC, "pdlp_ops_kernels.cuh")]
     os.makedirs(BUILD, exist_ok=True)
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(f) for f in sources):
-        subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-Wno-attributes", "-I" + EMU, "-I" + CSRC,
+        subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-shared", "-fPIC", "-DPDLP_EMU_FIBERS", "-Wno-unknown-pragmas", "-Wno-attributes", "-I" + EMU, "-I" + CSRC,
                         sources[0], "-o", out], check=True)
     lib = ctypes.CDLL(out)
     csr, csc = sp.csr_matrix(K), sp.csc_matrix(K)
