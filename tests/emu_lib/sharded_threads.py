@@ -1,7 +1,11 @@
 """TEST INFRASTRUCTURE ONLY.  Run by tests/test_full_emulation.py in a child process with PDLP_B200_LIBRARY = the emulated
 library and PDLP_B200_NCCL_LIBRARY = the fake NCCL: a column-sharded solve whose ranks are host threads of this process
 (the emulated peer memory is plain memory, tests/emu_lib/include/cuda_runtime.h), checked against the one-rank solve of
-the same library.      python sharded_threads.py <world> <peer|nccl>      prints one JSON line."""
+the same library.      python sharded_threads.py <world> <peer|nccl> [random|flow]      prints one JSON line.
+
+random: a random sparse LP, nearly every row shared by all ranks.  flow: a small multi-commodity flow LP in the benchmark's
+block-angular order (config 3 in miniature): conservation rows private to a rank, capacity rows shared - the layout that makes
+the fused peer pass split its grid between pushing and private CTAs and signal from inside the kernel."""
 import json
 import os
 import sys
@@ -52,17 +56,26 @@ def main():
     world, mode = int(sys.argv[1]), sys.argv[2]
     if mode == "nccl":
         os.environ["PDLP_B200_PEER_EXCHANGE"] = "0"
-    qp = fixtures.random_lp(40, 100, 4, 21)  # 448 iterations on the oracle
+    problem = sys.argv[3] if len(sys.argv) > 3 else "random"
+    if problem == "flow":
+        from pdlp_b200 import synthetic
+
+        qp = synthetic.multicommodity_flow_lp(num_commodities=8, grid_side=6, num_arcs=120, pairs_per_commodity=3, commodity_block=1, seed=3)  # 408 x 960
+        eps = 1e-4  # 448 iterations on the oracle
+    else:
+        qp = fixtures.random_lp(40, 100, 4, 21)  # 448 iterations on the oracle
+        eps = 1e-6
     params = pdlp_b200.PrimalDualHybridGradientParams()
-    params.termination_criteria.simple_optimality_criteria.eps_optimal_absolute = 1e-6
-    params.termination_criteria.simple_optimality_criteria.eps_optimal_relative = 1e-6
+    params.termination_criteria.simple_optimality_criteria.eps_optimal_absolute = eps
+    params.termination_criteria.simple_optimality_criteria.eps_optimal_relative = eps
     params.termination_criteria.iteration_limit = 20000
     single = pdlp_b200.primal_dual_hybrid_gradient(qp, params, device=0)
     results, x, y, sharing = solve_sharded(qp, params, world)
     logs = [r[0].solve_log for r in results]
     c = np.asarray(qp.objective_vector)
     out = {
-        "world": world, "mode": mode,
+        "world": world, "mode": mode, "problem": problem, "eps": eps,
+        "private_rows": [int(p.size) for p in sharing.private],
         "single_reason": int(single.solve_log.termination_reason), "single_iterations": int(single.solve_log.iteration_count),
         "reasons": [int(l.termination_reason) for l in logs], "iterations": [int(l.iteration_count) for l in logs],
         "objective_single": float(c @ single.primal_solution), "objective_sharded": float(c @ x),
