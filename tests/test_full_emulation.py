@@ -163,3 +163,18 @@ def test_peer_and_nccl_exchange_give_the_same_bits(sharded_runs):
     assert peer is not None and nccl is not None
     assert peer["iterations"] == nccl["iterations"] and peer["objective_sharded"] == nccl["objective_sharded"]
     assert peer["x_distance"] == nccl["x_distance"] and peer["y_distance"] == nccl["y_distance"]
+
+
+def test_interrupt_raised_mid_solve_is_seen_by_the_decision_kernel(emulated_library):
+    """tests/emu_lib/interrupt_mid_solve.py: host events 4096 iterations apart, the flag raised 2 s into the solve from another
+    thread.  The loop must stop between host events, and the counter must say that the decision kernel saw the flag."""
+    import json
+
+    env = dict(os.environ, PDLP_B200_LIBRARY=emulated_library)
+    run = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "emu_lib", "interrupt_mid_solve.py")], cwd=ROOT, env=env, capture_output=True, text=True, timeout=600)
+    assert run.returncode == 0, run.stderr[-2000:]
+    got = json.loads([line for line in run.stdout.splitlines() if line.startswith("{")][-1])
+    assert got["reason"] == int(__import__("pdlp_b200").TerminationReason.TERMINATION_REASON_INTERRUPTED_BY_USER)
+    assert got["seen_on_device"] == 1, got
+    assert 0 < got["iterations"] < 4096, got  # before the first host event after iteration 0's
+    assert got["latency"] < 5.0, got  # at most two 32-trial chunks are queued behind the running one, also here
