@@ -27,22 +27,31 @@ def main():
     p.major_iteration_frequency = 4096
     p.termination_check_frequency = 4096
     p.termination_criteria.iteration_limit = 400000
-    flag = np.zeros(1, dtype=np.int32)
-    raised = {}
+    def attempt(delay):
+        flag = np.zeros(1, dtype=np.int32)
+        raised = {}
 
-    def raise_later():
-        time.sleep(2.0)
-        raised["t"] = time.perf_counter()
-        flag[0] = 1
+        def raise_later():
+            time.sleep(delay)
+            raised["t"] = time.perf_counter()
+            flag[0] = 1
 
-    t = threading.Thread(target=raise_later)
-    t.start()
-    result = pdlp_b200.primal_dual_hybrid_gradient(qp, p, interrupt_solve=flag, device=0)
-    returned = time.perf_counter()
-    t.join()
-    log = result.solve_log
-    print(json.dumps({"reason": int(log.termination_reason), "iterations": int(log.iteration_count), "latency": returned - raised["t"],
-                      "seen_on_device": int(pdlp_b200.last_solve_counters()["interrupts_seen_on_device"])}))
+        t = threading.Thread(target=raise_later)
+        t.start()
+        result = pdlp_b200.primal_dual_hybrid_gradient(qp, p, interrupt_solve=flag, device=0)
+        returned = time.perf_counter()
+        t.join()
+        log = result.solve_log
+        return {"reason": int(log.termination_reason), "iterations": int(log.iteration_count), "latency": returned - raised["t"],
+                "seen_on_device": int(pdlp_b200.last_solve_counters()["interrupts_seen_on_device"]), "delay": delay}
+
+    # The flag may go up while the host is at one of its own events (the artificial restarts of the first iterations): the
+    # host then sees it first, which is correct but shows nothing about the device.  Such an attempt is repeated.
+    for delay in (2.0, 2.7, 3.5):
+        got = attempt(delay)
+        if got["seen_on_device"] == 1:
+            break
+    print(json.dumps(got))
 
 
 if __name__ == "__main__":
