@@ -22,10 +22,10 @@ def sources():
     return [n for n in names if n.endswith((".cu", ".cc"))], [n for n in names if n.endswith((".cuh", ".h"))]
 
 
-def stale():
-    if not os.path.exists(LIB):
+def stale(lib=LIB):
+    if not os.path.exists(lib):
         return True
-    t = os.path.getmtime(LIB)
+    t = os.path.getmtime(lib)
     deps = [os.path.join(CSRC, n) for n in os.listdir(CSRC)] + [os.path.join(HERE, "include", "cuda_runtime.h"), os.path.join(HERE, "rewrite_launches.py"),
                                                                os.path.join(ROOT, "tests", "kernel_emu", "cuda_emu.h"), os.path.abspath(__file__)]
     for base in (os.path.join(ROOT, "include"), os.path.join(ROOT, "include", "pdlp_b200")):
@@ -42,9 +42,13 @@ def build_fake_nccl():
     return FAKE_NCCL
 
 
-def build(verbose=False):
-    if not stale():
-        return LIB
+def build(verbose=False, asan=False, tsan=False):
+    """tsan=True: under ThreadSanitizer with one host thread per CUDA thread (libpdlp_b200_emu_tsan.so), the stand-in for
+    compute-sanitizer's racecheck.  asan=True: the same library under AddressSanitizer (tests/_build/libpdlp_b200_emu_asan.so), the stand-in for
+    compute-sanitizer's memcheck: "device" memory is heap memory, so a kernel or a copy that leaves its buffer is reported."""
+    lib = LIB[:-3] + "_asan.so" if asan else (LIB[:-3] + "_tsan.so" if tsan else LIB)
+    if not stale(lib):
+        return lib
     os.makedirs(OUT, exist_ok=True)
     units, headers = sources()
     for n in units + headers:
@@ -56,10 +60,15 @@ def build(verbose=False):
              "-include", os.path.join(HERE, "include", "cuda_runtime.h"),
              "-I" + os.path.join(HERE, "include"), "-I" + os.path.join(ROOT, "tests", "kernel_emu"), "-I" + OUT,
              "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(ROOT, "include", "pdlp_b200")]
+    if asan:
+        flags += ["-fsanitize=address", "-fno-omit-frame-pointer", "-DPDLP_EMU_UCONTEXT"]
+    if tsan:  # the racecheck stand-in: one host thread per CUDA thread (no fibers), so ThreadSanitizer sees every access pair
+        flags = [f for f in flags if f != "-DPDLP_EMU_FIBERS"] + ["-fsanitize=thread"]
+    suffix = ".asan.o" if asan else (".tsan.o" if tsan else ".o")
 
     def compile_one(n):
         src = os.path.join(OUT, n if not n.endswith(".cu") else n[:-3] + ".cu.cc")
-        obj = src + ".o"
+        obj = src + suffix
         run = subprocess.run(["g++"] + flags + ["-c", src, "-o", obj], capture_output=True, text=True)
         return n, obj, run
 
@@ -71,12 +80,12 @@ def build(verbose=False):
             if verbose and run.stderr:
                 print(run.stderr[:2000])
             objs.append(obj)
-    run = subprocess.run(["g++", "-shared", "-pthread", "-o", LIB] + objs + ["-ldl"], capture_output=True, text=True)
+    run = subprocess.run(["g++", "-shared", "-pthread"] + (["-fsanitize=address"] if asan else []) + (["-fsanitize=thread"] if tsan else []) + ["-o", lib] + objs + ["-ldl"], capture_output=True, text=True)
     if run.returncode != 0:
         raise RuntimeError("link of the emulated library failed:\n" + run.stderr[:4000])
-    return LIB
+    return lib
 
 
 if __name__ == "__main__":
-    print(build(verbose=True))
+    print(build(verbose=True, asan="--asan" in sys.argv, tsan="--tsan" in sys.argv))
     print(build_fake_nccl())

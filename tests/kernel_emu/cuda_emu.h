@@ -81,7 +81,7 @@ inline void AsyncWaitAll() {
 // a warp at __syncthreads, the other half in a shuffle) are reported as a deadlock - on the device that is a hang.
 // The thread mode below stays the default: ThreadSanitizer needs real threads for the race check.
 enum class FiberState { kReady, kAtCtaBarrier, kAtWarpBarrier, kDone };
-#if defined(__x86_64__)
+#if defined(__x86_64__) && !defined(PDLP_EMU_UCONTEXT)  // (AddressSanitizer follows swapcontext, not a hand-written switch)
 // A context is a stack pointer: the callee-saved registers live on the context's own stack while it is switched out.
 // (glibc's swapcontext also saves the signal mask - a system call per switch - which a solve pays millions of times.)
 extern "C" void pdlp_emu_switch(void** save_sp, void* load_sp);
