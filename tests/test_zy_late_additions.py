@@ -1,6 +1,7 @@
-"""Cases added after this round's GPU budget was spent: their oracle variants run in the CPU suite, their device
-variants have not yet run on a B200.  The file sorts after every validated test file (and before the allocation
-test, which must be last in its process) so that a surprise here cannot hide results that were green on the device."""
+"""Cases added after this round's GPU budget was spent: their oracle variants run in the CPU suite, and their device
+variants run there too on the whole-library emulation (tests/test_full_emulation.py: the host driver and the kernels as
+host C++) - but not yet on a B200.  The file sorts after every test file that has run on the hardware (and before the
+allocation test, which must be last in its process) so that a surprise there cannot hide results that were green."""
 import numpy as np
 import pytest
 
