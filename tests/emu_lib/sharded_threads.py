@@ -23,7 +23,7 @@ from pdlp_b200 import sharding  # noqa: E402
 import scipy.sparse as sp  # noqa: E402
 
 
-def solve_sharded(qp, params, world):
+def solve_sharded(qp, params, world, corrupt_rank=-1):
     K = sp.csc_matrix(qp.constraint_matrix)
     starts = sharding.column_partition(K.indptr, world)
     sharing = sharding.RowSharing.from_matrix(K, starts)
@@ -34,6 +34,10 @@ def solve_sharded(qp, params, world):
         try:
             lo, hi = int(starts[rank]), int(starts[rank + 1])
             block = sharding.take_columns(qp, lo, hi, sharing.local_rows(rank))
+            if rank == corrupt_rank:  # a row index outside the block: BuildDeviceMatrix rejects it on this rank only
+                bad = sp.csc_matrix(block.constraint_matrix).copy()
+                bad.indices[0] = bad.shape[0] + 7
+                block.constraint_matrix = bad
             shard = sharding.ColumnShard(rank, world, int(starts[-1]), lo, uid, int(sharing.shared.size))
             r = pdlp_b200.primal_dual_hybrid_gradient(block, params, device=rank, shard=shard)
             results[rank] = (r, pdlp_b200.last_solve_counters())
@@ -45,6 +49,8 @@ def solve_sharded(qp, params, world):
         t.start()
     for t in threads:
         t.join()
+    if corrupt_rank >= 0:
+        return errors, [r is not None for r in results]
     if errors:
         raise RuntimeError("; ".join(errors))
     x = np.concatenate([r[0].primal_solution for r in results])
@@ -57,6 +63,13 @@ def main():
     if mode == "nccl":
         os.environ["PDLP_B200_PEER_EXCHANGE"] = "0"
     problem = sys.argv[3] if len(sys.argv) > 3 else "random"
+    if problem == "bad_block":
+        # One rank's block is not a valid CSC matrix.  Every rank must come back with an error - the others must not be
+        # left waiting in a collective for a rank that has given up (PreprocessSolver agrees on a failed build).
+        qp = fixtures.random_lp(40, 100, 4, 21)
+        errors, returned = solve_sharded(qp, pdlp_b200.PrimalDualHybridGradientParams(), world, corrupt_rank=world - 1)
+        print(json.dumps({"world": world, "problem": problem, "errors": errors, "returned_a_result": returned}))
+        return
     if problem == "flow":
         from pdlp_b200 import synthetic
 

@@ -178,3 +178,21 @@ def test_interrupt_raised_mid_solve_is_seen_by_the_decision_kernel(emulated_libr
     assert got["seen_on_device"] == 1, got
     assert 0 < got["iterations"] < 4096, got  # before the first host event after iteration 0's
     assert got["latency"] < 5.0, got  # at most two 32-trial chunks are queued behind the running one, also here
+
+
+def test_a_rank_that_cannot_build_its_block_fails_every_rank(emulated_library):
+    """Rank 3 of 4 holds a block that is not a valid CSC matrix.  It must report that, and the other ranks must come back
+    with an error of their own instead of waiting in the next collective for a rank that has given up."""
+    import json
+
+    import build  # tests/emu_lib/build.py
+
+    env = dict(os.environ, PDLP_B200_LIBRARY=emulated_library, PDLP_B200_NCCL_LIBRARY=build.build_fake_nccl())
+    run = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "emu_lib", "sharded_threads.py"), "4", "peer", "bad_block"], cwd=ROOT, env=env,
+                         capture_output=True, text=True, timeout=300)  # a hang ends here
+    assert run.returncode == 0, run.stderr[-2000:]
+    got = json.loads([line for line in run.stdout.splitlines() if line.startswith("{")][-1])
+    assert got["returned_a_result"] == [False] * 4 and len(got["errors"]) == 4
+    by_rank = {e.split(":")[0]: e for e in got["errors"]}
+    assert "not a valid compressed CSC matrix" in by_rank["rank 3"]
+    assert all("another rank could not build its block" in by_rank[f"rank {r}"] for r in range(3))
