@@ -44,7 +44,12 @@ inline cudaError_t cudaDeviceGetAttribute(int* v, cudaDeviceAttr, int) { *v = 2;
 template <class K>
 inline cudaError_t cudaOccupancyMaxActiveBlocksPerMultiprocessor(int* n, K, int, size_t) { *n = 2; return cudaSuccess; }
 
+// Fault injection: the test sets *pdlp_emu_fail_allocation() = k and the k-th cudaMalloc from then on (k >= 1) reports that
+// the device is out of memory, once.
+extern "C" inline long long* pdlp_emu_fail_allocation() { static long long countdown = 0; return &countdown; }
 inline cudaError_t cudaMalloc(void** p, size_t bytes) {
+  long long& countdown = *pdlp_emu_fail_allocation();
+  if (countdown > 0 && --countdown == 0) { *p = nullptr; return cudaErrorMemoryAllocation; }
   *p = std::aligned_alloc(256, (bytes + 255) / 256 * 256 + 256);
   return *p != nullptr ? cudaSuccess : cudaErrorMemoryAllocation;
 }

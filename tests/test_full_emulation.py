@@ -196,3 +196,16 @@ def test_a_rank_that_cannot_build_its_block_fails_every_rank(emulated_library):
     by_rank = {e.split(":")[0]: e for e in got["errors"]}
     assert "not a valid compressed CSC matrix" in by_rank["rank 3"]
     assert all("another rank could not build its block" in by_rank[f"rank {r}"] for r in range(3))
+
+
+def test_every_device_allocation_of_a_solve_may_fail(emulated_library):
+    """tests/emu_lib/allocation_failures.py: each of the solve's device allocations reports out-of-memory once, in turn.
+    Every attempt must return the ABI's CUDA-error status (a RuntimeError here), and the next solve must be untouched."""
+    import json
+
+    env = dict(os.environ, PDLP_B200_LIBRARY=emulated_library)
+    run = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "emu_lib", "allocation_failures.py")], cwd=ROOT, env=env, capture_output=True, text=True, timeout=600)
+    assert run.returncode == 0, run.stdout[-1000:] + run.stderr[-2000:]
+    got = json.loads([line for line in run.stdout.splitlines() if line.startswith("{")][-1])
+    assert got["allocations_per_solve"] >= 20 and got["failed_cleanly"] == got["allocations_per_solve"]
+    assert all(m.startswith("pdlp_b200 status 2: CUDA error") for m in got["messages"]) and got["solve_after_failures_identical"]
