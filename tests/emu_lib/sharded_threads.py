@@ -75,10 +75,15 @@ def main():
 
         qp = synthetic.multicommodity_flow_lp(num_commodities=8, grid_side=6, num_arcs=120, pairs_per_commodity=3, commodity_block=1, seed=3)  # 408 x 960
         eps = 1e-4  # 448 iterations on the oracle
+    elif problem == "qp_mp":  # a diagonal QP under the Malitsky-Pock rule with feasibility-polishing-free defaults
+        qp = fixtures.random_lp(40, 100, 4, 21, qp_diagonal=True)
+        eps = 1e-6
     else:
         qp = fixtures.random_lp(40, 100, 4, 21)  # 448 iterations on the oracle
         eps = 1e-6
     params = pdlp_b200.PrimalDualHybridGradientParams()
+    if problem == "qp_mp":
+        params.linesearch_rule = params.MALITSKY_POCK_LINESEARCH_RULE
     params.termination_criteria.simple_optimality_criteria.eps_optimal_absolute = eps
     params.termination_criteria.simple_optimality_criteria.eps_optimal_relative = eps
     params.termination_criteria.iteration_limit = 20000
@@ -86,12 +91,14 @@ def main():
     results, x, y, sharing = solve_sharded(qp, params, world)
     logs = [r[0].solve_log for r in results]
     c = np.asarray(qp.objective_vector)
+    q = None if qp.objective_matrix is None else np.asarray(qp.objective_matrix)
+    objective = lambda v: float(c @ v + (0.0 if q is None else 0.5 * (q * v) @ v))  # noqa: E731
     out = {
         "world": world, "mode": mode, "problem": problem, "eps": eps,
         "private_rows": [int(p.size) for p in sharing.private],
         "single_reason": int(single.solve_log.termination_reason), "single_iterations": int(single.solve_log.iteration_count),
         "reasons": [int(l.termination_reason) for l in logs], "iterations": [int(l.iteration_count) for l in logs],
-        "objective_single": float(c @ single.primal_solution), "objective_sharded": float(c @ x),
+        "objective_single": objective(single.primal_solution), "objective_sharded": objective(x),
         "x_distance": float(np.linalg.norm(x - single.primal_solution) / max(1.0, np.linalg.norm(single.primal_solution))),
         "y_distance": float(np.linalg.norm(y - single.dual_solution) / max(1.0, np.linalg.norm(single.dual_solution))),
         "peer_exchanges": [int(r[1]["peer_exchanges"]) for r in results], "collectives": [int(r[1]["collectives"]) for r in results],

@@ -105,7 +105,7 @@ def test_c_and_cpp_callers_in_device_mode(emulated_library):
 
 # ---- the column-sharded solve with ranks as host threads (peer-memory path at 2, 4 and 8 ranks; NCCL path at 2) ----
 
-SHARDED = [(2, "peer", "random"), (4, "peer", "random"), (8, "peer", "random"), (2, "nccl", "random"), (2, "peer", "flow"), (8, "peer", "flow")]
+SHARDED = [(2, "peer", "random"), (4, "peer", "random"), (8, "peer", "random"), (2, "nccl", "random"), (2, "peer", "flow"), (8, "peer", "flow"), (4, "peer", "qp_mp")]
 
 
 @pytest.fixture(scope="module")
@@ -139,7 +139,8 @@ def test_sharded_solve_with_ranks_as_host_threads(sharded_runs, world, mode, pro
     memory is plain memory here and NCCL a thread rendezvous (tests/emu_lib/fake_nccl.cc), so this says nothing about NVLink
     ordering - the 2-GPU tests on the B200 box do - but every rank must finish, agree, and match the one-rank solve.
     "random": nearly every row shared; "flow": config 3 in miniature, private conservation rows and shared capacity rows, the
-    layout in which the fused pass splits its grid and signals from inside the kernel."""
+    layout in which the fused pass splits its grid and signals from inside the kernel; "qp_mp": a diagonal QP under the
+    Malitsky-Pock rule (its own decision kernel and two-sided averaging)."""
     code, got, err = sharded_runs[(world, mode, problem)]
     assert code == 0 and got is not None, err
     optimal = int(__import__("pdlp_b200").TerminationReason.TERMINATION_REASON_OPTIMAL)
