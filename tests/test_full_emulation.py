@@ -10,7 +10,13 @@ costs milliseconds.
 This is test infrastructure, not a CPU path of the product: the package never builds, ships or picks this library, and
 without PDLP_B200_LIBRARY pointing at it a solve on a machine without a GPU fails loudly (tests/test_cabi.py).  It
 checks what the kernel-level emulation cannot: launch order, buffer sizes, the device-resident loop's state hand-over,
-the degenerate shapes, the presolve hand-off - everything except timing, asynchrony and the hardware memory model."""
+the degenerate shapes, the presolve hand-off - everything except timing, asynchrony and the hardware memory model.
+
+Also here: column-sharded solves whose ranks are host threads of one process (peer memory = plain memory, NCCL = a thread
+rendezvous, tests/emu_lib/fake_nccl.cc) at 2, 4 and 8 ranks; the per-iteration interrupt; a rank that cannot build its
+block; every device allocation of a solve failing in turn.  Sanitizer variants of the same library (AddressSanitizer,
+ThreadSanitizer with one host thread per CUDA thread) are run by scripts/emulated_asan.sh / emulated_tsan.sh, not here:
+they take the better part of an hour (logs under profiles/)."""
 import os
 import subprocess
 import sys
